@@ -1,0 +1,279 @@
+/*
+ * textblaster_b200.h -- C ABI of the B200-native TextBlaster quality-filter hot path.
+ *
+ * The reference (kris927b/TextBlaster, Rust) has no FFI today: its boundary for this path is the
+ * trait object `ProcessingStep` (src/executor.rs:8-15) built by `build_pipeline_from_config`
+ * (src/worker_logic.rs:39-134) and driven by `PipelineExecutor::run_single_async`
+ * (src/executor.rs:30-57).  This header is what a `-sys` crate over the CUDA library would bind;
+ * every entry point cites the reference interface it stands in for.  Plain pointers and sizes only,
+ * no torch / C++ types.  INTEGRATION.md shows the Rust (and ctypes) binding.
+ *
+ * Semantics mirrored from the reference:
+ *   - a batch is one Arrow string column: contiguous UTF-8 `values` + n+1 offsets (i32 as in
+ *     arrow::StringArray, src/pipeline/readers/parquet_reader.rs:108-112, or i64);
+ *   - steps run in the configured order and a document stops at the first step that filters it
+ *     (src/executor.rs:32-46); statistics of later steps are undefined for that document;
+ *   - "filtered" is data (keep = 0, failed_step, reason bits + counters), not an error;
+ *   - C4QualityFilter rewrites the content (src/pipeline/filters/c4_filters.rs:254-258); the
+ *     content after the chain is returned in `content` / `content_offsets`.
+ *
+ * All integer counters are bit-exact against the reference algorithm; ratios are single IEEE-754
+ * double divisions of those counters (helpers at the end of this header).
+ */
+#ifndef TEXTBLASTER_B200_H
+#define TEXTBLASTER_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define TB_ABI_VERSION 1
+#define TB_MAX_STEPS 8
+#define TB_MAX_NGRAMS 12 /* entries per top_n_grams / dup_n_grams list */
+#define TB_MAX_NGRAM_N 32 /* largest n-gram order accepted */
+
+/* ---- status codes (tb_last_error() has the text) ---------------------------------------- */
+enum {
+  TB_OK = 0,
+  TB_ERR_INVALID_ARGUMENT = 1,
+  TB_ERR_CONFIG_VALIDATION = 2, /* PipelineError::ConfigValidationError, src/error.rs:62-63 */
+  TB_ERR_CUDA = 3,
+  TB_ERR_OUT_OF_MEMORY = 4,
+  TB_ERR_UNSUPPORTED = 5,
+  TB_ERR_INVALID_UTF8 = 6 /* the reference only ever sees Rust `String`s (valid UTF-8) */
+};
+
+/* ---- step configuration: src/config/pipeline.rs:26-37 (enum StepConfig, the three in-scope
+ *      variants) ------------------------------------------------------------------------- */
+typedef enum {
+  TB_STEP_C4_QUALITY = 1,        /* StepConfig::C4QualityFilter        */
+  TB_STEP_GOPHER_QUALITY = 2,    /* StepConfig::GopherQualityFilter    */
+  TB_STEP_GOPHER_REPETITION = 3  /* StepConfig::GopherRepetitionFilter */
+} tb_step_type;
+
+/* C4QualityParams, src/config/pipeline.rs:66-79; field meaning src/pipeline/filters/c4_filters.rs:98-139 */
+typedef struct tb_c4_params {
+  int32_t split_paragraph;
+  int32_t remove_citations;
+  int32_t filter_no_terminal_punct;
+  int32_t filter_lorem_ipsum;
+  int32_t filter_javascript;
+  int32_t filter_curly_bracket;
+  int32_t filter_policy;
+  int32_t _pad;
+  uint64_t min_num_sentences;
+  uint64_t min_words_per_line;
+  uint64_t max_word_length;
+} tb_c4_params;
+
+/* GopherQualityParams, src/config/pipeline.rs:161-176.  `has` bit i set <=> the i-th Option is Some. */
+enum {
+  TB_GQ_HAS_MIN_DOC_WORDS = 1 << 0,
+  TB_GQ_HAS_MAX_DOC_WORDS = 1 << 1,
+  TB_GQ_HAS_MIN_AVG_WORD_LENGTH = 1 << 2,
+  TB_GQ_HAS_MAX_AVG_WORD_LENGTH = 1 << 3,
+  TB_GQ_HAS_MAX_SYMBOL_WORD_RATIO = 1 << 4,
+  TB_GQ_HAS_MAX_BULLET_LINES_RATIO = 1 << 5,
+  TB_GQ_HAS_MAX_ELLIPSIS_LINES_RATIO = 1 << 6,
+  TB_GQ_HAS_MAX_NON_ALPHA_WORDS_RATIO = 1 << 7,
+  TB_GQ_HAS_MIN_STOP_WORDS = 1 << 8,
+  TB_GQ_HAS_STOP_WORDS = 1 << 9 /* else DEFAULT_STOP_WORDS, gopher_quality.rs:10 */
+};
+typedef struct tb_gq_params {
+  uint32_t has;
+  int32_t n_stop_words;
+  uint64_t min_doc_words;
+  uint64_t max_doc_words;
+  double min_avg_word_length;
+  double max_avg_word_length;
+  double max_symbol_word_ratio;
+  double max_bullet_lines_ratio;
+  double max_ellipsis_lines_ratio;
+  double max_non_alpha_words_ratio;
+  uint64_t min_stop_words;
+  const uint8_t* stop_words_utf8;     /* concatenated entries, used as given (not lower-cased) */
+  const int32_t* stop_words_offsets;  /* n_stop_words + 1 */
+} tb_gq_params;
+
+/* GopherRepetitionParams, src/config/pipeline.rs:102-115 */
+enum {
+  TB_GR_HAS_DUP_LINE_FRAC = 1 << 0,
+  TB_GR_HAS_DUP_PARA_FRAC = 1 << 1,
+  TB_GR_HAS_DUP_LINE_CHAR_FRAC = 1 << 2,
+  TB_GR_HAS_DUP_PARA_CHAR_FRAC = 1 << 3
+};
+typedef struct tb_gr_params {
+  uint32_t has;
+  int32_t n_top;
+  int32_t n_dup;
+  int32_t _pad;
+  double dup_line_frac;
+  double dup_para_frac;
+  double dup_line_char_frac;
+  double dup_para_char_frac;
+  uint32_t top_n[TB_MAX_NGRAMS];
+  double top_frac[TB_MAX_NGRAMS];
+  uint32_t dup_n[TB_MAX_NGRAMS];
+  double dup_frac[TB_MAX_NGRAMS];
+} tb_gr_params;
+
+typedef struct tb_step_cfg {
+  int32_t type; /* tb_step_type */
+  int32_t _pad;
+  union {
+    tb_c4_params c4;
+    tb_gq_params gq;
+    tb_gr_params gr;
+  } u;
+} tb_step_cfg;
+
+/* ---- per-document results ------------------------------------------------------------------
+ * One array of the matching struct per configured step.  reason bits are in the order the
+ * reference pushes reasons, so "; ".join over set bits reproduces its reason string. */
+
+/* c4_filters.rs:166-173 (doc-level), :207-240 (line counters -> metadata keys line-filter-*), :261-269 */
+enum {
+  TB_C4_REASON_LOREM_IPSUM = 1 << 0,
+  TB_C4_REASON_CURLY_BRACKET = 1 << 1,
+  TB_C4_REASON_TOO_FEW_SENTENCES = 1 << 2
+};
+typedef struct tb_c4_stats {
+  uint32_t reason_bits;
+  uint32_t n_lines;              /* lines examined (0 on the early doc-level exit) */
+  uint32_t too_long_word;        /* "line-filter-too_long_word"    */
+  uint32_t no_terminal_punc;     /* "line-filter-no_terminal_punc" */
+  uint32_t too_few_words;        /* "line-filter-too_few_words"    */
+  uint32_t n_kept_lines;
+  uint32_t n_sentences;          /* split_into_sentences(rewritten content).len() */
+  uint32_t rewritten;            /* 1 if content was rewritten (line filtering ran) */
+} tb_c4_stats;
+
+/* gopher_quality.rs:198-295, in push order */
+enum {
+  TB_GQ_REASON_SHORT_DOC = 1 << 0,
+  TB_GQ_REASON_LONG_DOC = 1 << 1,
+  TB_GQ_REASON_BELOW_AVG = 1 << 2,
+  TB_GQ_REASON_ABOVE_AVG = 1 << 3,
+  TB_GQ_REASON_TOO_MANY_HASHES = 1 << 4,
+  TB_GQ_REASON_TOO_MANY_ELLIPSIS_UNITS = 1 << 5,
+  TB_GQ_REASON_TOO_MANY_BULLETS = 1 << 6,
+  TB_GQ_REASON_TOO_MANY_END_ELLIPSIS_LINES = 1 << 7,
+  TB_GQ_REASON_BELOW_ALPHA = 1 << 8,
+  TB_GQ_REASON_TOO_FEW_STOP_WORDS = 1 << 9
+};
+typedef struct tb_gq_stats {
+  uint32_t reason_bits;
+  uint32_t n_words;             /* n_total_words == n_non_symbol_words, gopher_quality.rs:74,85 */
+  uint64_t sum_word_chars;      /* :92 */
+  uint32_t n_hash;              /* :104 */
+  uint32_t n_ellipsis_units;    /* :115 */
+  uint32_t n_lines;             /* :127 */
+  uint32_t n_bullet_lines;      /* :134-141 */
+  uint32_t n_ellipsis_lines;    /* :152-158 */
+  uint32_t n_alpha_words;       /* :169-172 */
+  uint32_t n_stop_words;        /* :184-187 */
+  uint32_t flags;               /* TB_DOCFLAG_* */
+} tb_gq_stats;
+
+/* gopher_rep.rs:95-195, in push order: 4 fixed bits, then top_n_grams[i], then dup_n_grams[i] */
+enum {
+  TB_GR_REASON_DUP_PARA_FRAC = 1 << 0,
+  TB_GR_REASON_DUP_PARA_CHAR_FRAC = 1 << 1,
+  TB_GR_REASON_DUP_LINE_FRAC = 1 << 2,
+  TB_GR_REASON_DUP_LINE_CHAR_FRAC = 1 << 3,
+  TB_GR_REASON_TOP_SHIFT = 4,                   /* bit 4+i  : top_n_grams[i] */
+  TB_GR_REASON_DUP_SHIFT = 4 + TB_MAX_NGRAMS,   /* bit 16+i : dup_n_grams[i] */
+  TB_GR_REASON_EMPTY = 1u << 31                 /* "skipping empty content", gopher_rep.rs:60-74 */
+};
+typedef struct tb_gr_stats {
+  uint32_t reason_bits;
+  uint32_t flags;               /* TB_DOCFLAG_* */
+  uint64_t char_len;            /* trimmed.chars().count(), gopher_rep.rs:58 (before .max(1)) */
+  uint32_t n_paras;
+  uint32_t para_dup_elems;
+  uint64_t para_dup_bytes;
+  uint32_t n_lines;
+  uint32_t line_dup_elems;
+  uint64_t line_dup_bytes;
+  uint64_t n_words;
+  uint64_t top_bytes[TB_MAX_NGRAMS];  /* find_top_duplicate, text.rs:211-238 */
+  uint64_t dup_bytes[TB_MAX_NGRAMS];  /* find_all_duplicate, text.rs:241-259 */
+} tb_gr_stats;
+
+/* Document flags (information, never affects decisions) */
+enum {
+  TB_DOCFLAG_COMPLEX_SCRIPT = 1 << 0 /* has Han/Kana/Thai/Lao/Khmer/Burmese text: ICU4X new_auto()
+                                        (text.rs:107) would re-segment it with dictionary/LSTM data;
+                                        we apply plain UAX #29 -- parity unpinned for such documents */
+};
+
+typedef struct tb_batch_out {
+  int64_t n_docs;
+  int32_t n_steps;
+  int32_t content_rewritten;       /* 1 if a C4 step ran: content/content_offsets are valid */
+  uint8_t* keep;                   /* [n_docs] 1 = passed every step */
+  int8_t* failed_step;             /* [n_docs] index into the pipeline, -1 = passed */
+  void* step_stats[TB_MAX_STEPS];  /* [n_docs] of tb_c4_stats / tb_gq_stats / tb_gr_stats */
+  uint8_t* content;                /* content after the chain (all docs), or NULL */
+  int64_t* content_offsets;        /* [n_docs + 1] */
+  int64_t content_bytes;
+  double gpu_ms;                   /* device time of the kernels of this call (CUDA events) */
+  int32_t gpu_launches;            /* kernels launched by this call */
+  int32_t _pad;
+  void* _owner;                    /* internal */
+} tb_batch_out;
+
+typedef struct tb_ctx tb_ctx;
+typedef struct tb_pipeline tb_pipeline;
+
+/* Creates the per-device context (streams, Unicode tables in HBM).  Replaces nothing in the
+ * reference (it has no device); lifetime = the worker's `Arc<PipelineExecutor>` (src/bin/worker.rs:149). */
+int tb_ctx_create(int device, tb_ctx** out);
+void tb_ctx_destroy(tb_ctx* ctx);
+/* Thread-local text of the last failure on this thread (ctx may be NULL). */
+const char* tb_last_error(const tb_ctx* ctx);
+int tb_abi_version(void);
+
+/* build_pipeline_from_config (src/worker_logic.rs:39-134) + StepConfig::validate
+ * (src/config/pipeline.rs:53-63): validates with the reference's rules and messages, uploads
+ * parameters.  The handle is immutable afterwards (ProcessingStep: Send + Sync). */
+int tb_pipeline_create(tb_ctx* ctx, const tb_step_cfg* steps, size_t n_steps, tb_pipeline** out);
+void tb_pipeline_destroy(tb_pipeline* p);
+/* ProcessingStep::name (c4_filters.rs:143-145, gopher_quality.rs:65-67, gopher_rep.rs:48-50) */
+const char* tb_step_name(int32_t step_type);
+
+/* PipelineExecutor::run_batch_parallel_async (src/executor.rs:60-70) for a whole Arrow string
+ * column held in HOST memory: pinned double-buffered H2D on a side stream, kernels, D2H of results.
+ * offsets: n_docs + 1 entries of int32 (offsets_are_i64 == 0) or int64.  Results stay valid until
+ * tb_batch_out_release.  Result order == input order (tests/executor_test.rs:284-291). */
+int tb_pipeline_run_batch(tb_pipeline* p, const uint8_t* utf8, const void* offsets,
+                          int offsets_are_i64, int64_t n_docs, tb_batch_out* out);
+
+/* Same, inputs already resident in device memory (utf8_dev, int64 offsets_dev); results are copied
+ * to host.  Used by bench.py's device-resident `value` and by callers that decode Parquet on GPU. */
+int tb_pipeline_run_batch_device(tb_pipeline* p, const uint8_t* utf8_dev, const int64_t* offsets_dev,
+                                 int64_t n_docs, int64_t n_bytes, tb_batch_out* out);
+
+void tb_batch_out_release(tb_pipeline* p, tb_batch_out* out);
+
+/* Options (set before running; default in brackets) */
+enum {
+  TB_OPT_RETURN_CONTENT = 1, /* [1] copy rewritten content back to the host */
+  TB_OPT_VALIDATE_UTF8 = 2,  /* [0] check inputs on the device, TB_ERR_INVALID_UTF8 on failure */
+  TB_OPT_CHUNK_BYTES = 3     /* [256 MiB] H2D staging chunk */
+};
+int tb_pipeline_set_option(tb_pipeline* p, int32_t option, int64_t value);
+
+/* Name of the dominant kernel and its accumulated device time since pipeline creation; used by
+ * bench.py for the roofline line. */
+int tb_pipeline_kernel_times(tb_pipeline* p, int32_t max_entries, const char** names, double* ms,
+                             int64_t* launches);
+void tb_pipeline_reset_kernel_times(tb_pipeline* p);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TEXTBLASTER_B200_H */
