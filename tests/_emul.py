@@ -1,0 +1,67 @@
+"""Loader for the host emulation harness (tests/host_emul/tb_emul.cpp) -- test infrastructure.
+
+It runs the kernel bodies with 32 host threads standing in for the lanes of a warp, so the kernel
+logic can be compared with the oracle without a GPU.  Never imported by the product package."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+from textblaster_b200 import _abi
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_SRC = os.path.join(_HERE, "host_emul", "tb_emul.cpp")
+_SO = os.path.join(_HERE, "host_emul", "libtb_emul.so")
+_CSRC = os.path.join(_HERE, "..", "textblaster_b200", "csrc")
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        deps = [_SRC] + [os.path.join(_CSRC, f) for f in os.listdir(_CSRC) if f.endswith((".cuh", ".h", ".inc"))]
+        if not os.path.exists(_SO) or any(os.path.getmtime(d) > os.path.getmtime(_SO) for d in deps):
+            subprocess.run(["g++", "-std=c++20", "-O2", "-fPIC", "-shared", "-pthread", "-x", "c++", _SRC, "-o", _SO], check=True)
+        L = C.CDLL(_SO)
+        L.tbe_run_chain.restype = C.c_int
+        L.tbe_run_chain.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p,
+                                    C.c_void_p, C.c_void_p, C.c_void_p]
+        _lib = L
+    return _lib
+
+
+class EmulResult:
+    pass
+
+
+def run_chain(steps, texts):
+    """steps: config param objects; texts: list[str].  Returns keep, failed_step, stats[], contents."""
+    keepalive = []
+    arr = (_abi.tb_step_cfg * max(len(steps), 1))()
+    types = []
+    for i, s in enumerate(steps):
+        arr[i] = s.to_c(keepalive)
+        types.append(arr[i].type)
+    enc = [t.encode("utf-8") for t in texts]
+    blob = np.frombuffer(b"".join(enc) + b"\0", dtype=np.uint8).copy()
+    off = np.zeros(len(enc) + 1, np.int64)
+    if enc:
+        off[1:] = np.cumsum([len(e) for e in enc])
+    n = len(enc)
+    keep = np.zeros(n + 1, np.uint8)
+    failed = np.zeros(n + 1, np.int8)
+    stats = [np.zeros(n + 1, _abi.stats_dtype(t)) for t in types]
+    sp = (C.c_void_p * max(len(steps), 1))(*[s.ctypes.data for s in stats])
+    content = np.zeros(len(blob) + 64, np.uint8)
+    coff = np.zeros(n + 2, np.int64)
+    rc = lib().tbe_run_chain(C.addressof(arr), len(steps), blob.ctypes.data, off.ctypes.data, n, keep.ctypes.data,
+                             failed.ctypes.data, C.addressof(sp), content.ctypes.data, coff.ctypes.data)
+    if rc not in (0, 100):
+        raise RuntimeError(f"emulation failed rc={rc}")
+    r = EmulResult()
+    r.keep, r.failed_step, r.stats = keep[:n], failed[:n], [s[:n] for s in stats]
+    r.contents = None
+    if rc == 100:
+        r.contents = [bytes(content[coff[i]:coff[i + 1]]).decode("utf-8") for i in range(n)]
+    return r

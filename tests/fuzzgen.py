@@ -1,0 +1,96 @@
+"""Adversarial document generator for the parity tests (seeded; pure Python).
+
+Mixes ASCII prose with the characters the filters are sensitive to: all White_Space variants, the
+PUNCTUATION members, UAX #29 Mid*/quote/Extend/ZWJ/Regional_Indicator classes, case-mapping
+specials (U+0130, U+03A3 final sigma, U+212A), citations, policy phrases, long words, duplicate
+lines / paragraphs / n-grams, and every newline flavour.
+"""
+import random
+
+SPECIAL = [
+    "\xe6", "\xc5", "Ж", "ж", "Σ", "σ", "ς", "א", "ב", "́", "‍", "\xad",
+    "\U0001f600", "\U0001f1e9", "\U0001f1f0", "\xa0", " ", " ", "　", "١", "’", "“", "”",
+    "…", "\xb7", "❤", "️", "\x85", "\x0b", "—", "״", "،", "٫", "．", "․",
+    " ", " ", "\xdf", "İ", "K", "中", "文", "ア", "カ", "ก", "•", "１",
+    "\xa7", "\r", "\t", "{", "#", "[", "]", ",", "\x00", "\x1f", "\x7f", " ", "\x0c",
+]
+WORDS = [
+    "the", "be", "to", "of", "and", "that", "have", "with", "lorem", "ipsum", "javascript", "privacy", "policy", "cookie",
+    "cookies", "uses", "use", "terms", "hello", "world", "a", "I", "x1", "3.14", "don't", "foo_bar", "U.S.A.", "e.g.",
+    "Mr.", "10,000", "...", "…", "-", "•", "#", "[1]", "[2, 3]", "[4,5,6]", "[7,", "[a]", "[١٢]",
+    "(see)", "\"quoted\"", "end.", "stop!", "why?", "ok”", "caf\xe9", "na\xefve", "Жук",
+    "ΣΟΦΟΣ", "İstanbul", "Kelvin", "TERMS OF USE", "Use Of Cookies", "JavaScript",
+    "LOREM IPSUM", "cooKie policy", "a:b", "1.5.2", "it's", "rock'n'roll", "\U0001f1e9\U0001f1f0\U0001f1e9",
+]
+
+
+class FuzzGen:
+    def __init__(self, seed):
+        self.rng = random.Random(seed)
+
+    def word(self):
+        rng = self.rng
+        r = rng.random()
+        if r < 0.7:
+            return rng.choice(WORDS)
+        if r < 0.85:
+            return "".join(rng.choice("abcdefghijklmnopqrstuvwxyzABCDEFGH0123456789") for _ in range(rng.randint(1, 12)))
+        if r < 0.97:
+            return "".join(rng.choice(SPECIAL + list("ab1.',:;")) for _ in range(rng.randint(1, 6)))
+        return rng.choice("wZ9") * rng.randint(30, 1200)
+
+    def line(self):
+        rng = self.rng
+        n = rng.randint(0, 30)
+        s = "".join(self.word() + rng.choice([" ", " ", " ", "  ", "\t", ",", ", ", ". ", "\xa0"]) for _ in range(n))
+        if rng.random() < 0.6:
+            s = s.rstrip() + rng.choice([".", "!", "?", "...", "…", "\"", "'", "”", " .", "."])
+        if rng.random() < 0.1:
+            s = "  " + s + "  "
+        return s
+
+    def doc(self, max_lines=12):
+        rng = self.rng
+        lines = []
+        for _ in range(rng.randint(0, max_lines)):
+            lines.append(self.line())
+            if rng.random() < 0.2:
+                lines.append(rng.choice(lines))
+        doc = ""
+        for ln in lines:
+            doc += ln + rng.choice(["\n", "\n", "\n\n", "\r\n", "\n\n\n", " \n"])
+        if rng.random() < 0.5:
+            doc = doc.rstrip("\n")
+        if rng.random() < 0.1:
+            doc = rng.choice(["\n", " ", "\n\n"]) + doc
+        return doc
+
+    def docs(self, n, max_lines=12):
+        return [self.doc(max_lines) for _ in range(n)]
+
+
+def english_doc(rng, target_bytes):
+    """C4-shaped ASCII prose with repeated boilerplate, for multi-tile (> 1 KiB) coverage."""
+    vocab = ["alpha", "beta", "gamma", "delta", "the", "of", "and", "to", "with", "that", "have", "be", "system",
+             "data", "value", "people", "time", "year", "work", "government", "company", "number", "a", "in", "is"]
+    out = []
+    size = 0
+    boiler = "Click here to read more about our products and services today."
+    while size < target_bytes:
+        nsent = rng.randint(1, 5)
+        line = []
+        for _ in range(nsent):
+            nw = rng.randint(3, 20)
+            ws = [rng.choice(vocab) for _ in range(nw)]
+            ws[0] = ws[0].capitalize()
+            line.append(" ".join(ws) + rng.choice([".", ".", ".", "?", "!", ""]))
+        text = " ".join(line)
+        if rng.random() < 0.15:
+            text = boiler
+        if rng.random() < 0.05:
+            text += " [%d]" % rng.randint(1, 99)
+        out.append(text)
+        size += len(text) + 1
+        if rng.random() < 0.3:
+            out.append("")
+    return "\n".join(out)

@@ -1,0 +1,143 @@
+// tb_emul.cpp -- TEST INFRASTRUCTURE ONLY (never linked into or loaded by the product).
+//
+// Runs the exact warp bodies of the CUDA kernels (textblaster_b200/csrc/tb_bodies.cuh) on the host:
+// 32 threads play the lanes of a warp, warp collectives become barriers (tb_simt.cuh, TB_HOST_EMUL).
+// It exists so that the kernel logic can be checked against the oracle on a machine with no GPU
+// (`pytest -m "not gpu"`); the GPU tests check the real kernels through the C ABI.  Scratch memory
+// is filled with garbage first, like cudaMalloc'd memory, to expose reads of unwritten slots.
+#define TB_HOST_EMUL 1
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <functional>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "../../textblaster_b200/csrc/tb_bodies.cuh"
+#include "../../textblaster_b200/csrc/tb_hostutil.h"
+#include "../../textblaster_b200/csrc/unicode_tables.inc"
+
+thread_local SimtWarp* simt_warp = nullptr;
+thread_local int simt_lane = 0;
+
+namespace {
+
+// Launch `fn(d, lane)` for every document as one emulated warp (32 threads in lock step at the
+// collectives).  `pred(d)` is the warp-uniform early-exit test of the __global__ wrapper.
+void run_warps(int64_t n, const std::function<bool(int64_t)>& pred, const std::function<void(int64_t, int)>& fn) {
+  SimtWarp warp;
+  std::vector<std::thread> th;
+  for (int lane = 0; lane < 32; lane++) {
+    th.emplace_back([&, lane]() {
+      simt_warp = &warp; simt_lane = lane;
+      for (int64_t d = 0; d < n; d++) {
+        bool go = pred(d);
+        warp.bar.arrive_and_wait();  // every lane has sampled the predicate before anyone runs
+        if (!go) continue;
+        fn(d, lane);
+        warp.bar.arrive_and_wait();  // kernels never share state between warps mid-flight
+      }
+    });
+  }
+  for (auto& t : th) t.join();
+}
+
+template <class T> T* garbage(size_t n) {
+  T* p = (T*)malloc(n * sizeof(T) + 64);
+  memset(p, 0xCD, n * sizeof(T) + 64);
+  return p;
+}
+
+size_t stat_size(int type) {
+  return type == TB_STEP_C4_QUALITY ? sizeof(tb_c4_stats) : type == TB_STEP_GOPHER_QUALITY ? sizeof(tb_gq_stats) : sizeof(tb_gr_stats);
+}
+
+}  // namespace
+
+extern "C" int tbe_run_chain(const tb_step_cfg* steps, size_t n_steps, const uint8_t* utf8, const int64_t* offsets,
+                             int64_t n, uint8_t* keep, int8_t* failed_out, void** stats_out, uint8_t* content_out,
+                             int64_t* content_off_out) {
+  std::vector<void*> frees;
+  auto G8 = [&](size_t c) { auto* p = garbage<uint8_t>(c); frees.push_back(p); return p; };
+  auto G32 = [&](size_t c) { auto* p = garbage<uint32_t>(c); frees.push_back(p); return p; };
+  auto G64 = [&](size_t c) { auto* p = garbage<int64_t>(c); frees.push_back(p); return p; };
+  const int64_t base = n ? offsets[0] : 0;
+  const int64_t nb = n ? offsets[n] - base : 0;
+  const size_t n1 = (size_t)n + 1, units = (size_t)nb / 2 + n1 + 1, lines = (size_t)nb + n1 + 1;
+  // tables
+  std::vector<uint64_t> pw(TB_POWTAB);
+  { uint32_t a = 1, b = 1; for (int i = 0; i < TB_POWTAB; i++) { pw[i] = ((uint64_t)a << 32) | b; a = tb_mm(a, TB_B1); b = tb_mm(b, TB_B2); } }
+  UcTables uc{tb_uc_stage1, tb_uc_stage2, &tb_uc_lower[0][0], &tb_uc_cased[0][0], &tb_uc_caseign[0][0], pw.data(),
+              TB_UC_NLOWER, TB_UC_NCASED, TB_UC_NCASEIGN};
+  uint16_t ascii[128];
+  for (int i = 0; i < 128; i++) ascii[i] = tb_uc_stage2[(uint32_t)tb_uc_stage1[0] * 256u + i];
+
+  uint8_t* text = G8((size_t)nb + 64);
+  if (nb) memcpy(text, utf8 + base, (size_t)nb);
+  int64_t *rs0 = G64(n1), *re0 = G64(n1), *rs = G64(n1), *re = G64(n1), *ts = G64(n1), *te = G64(n1), *len = G64(n1), *out_off = G64(n1 + 1);
+  uint8_t *alive = G8(n1), *rewritten = G8(n1);
+  int8_t* failed = (int8_t*)G8(n1);
+  for (int64_t d = 0; d < n; d++) body_init_ranges(offsets, 1, 0, base, rs0, re0, alive, failed, d);
+  memcpy(rs, rs0, (size_t)n * 8); memcpy(re, re0, (size_t)n * 8);
+  memset(rewritten, 0, (size_t)n);
+  KBatch b{text, rs, re, alive, failed, n, uc};
+  auto alive_pred = [&](int64_t d) { return alive[d] != 0; };
+  bool has_c4 = false;
+  for (size_t s = 0; s < n_steps; s++) {
+    const tb_step_cfg& sc = steps[s];
+    uint8_t* stats = G8(n1 * stat_size(sc.type));
+    if (sc.type == TB_STEP_GOPHER_QUALITY) {
+      const tb_gq_params& q = sc.u.gq;
+      GqCfg cfg{q.has, q.min_doc_words, q.max_doc_words, q.min_stop_words, q.min_avg_word_length, q.max_avg_word_length,
+                q.max_symbol_word_ratio, q.max_bullet_lines_ratio, q.max_ellipsis_lines_ratio, q.max_non_alpha_words_ratio};
+      uint32_t mask, maxlen;
+      std::vector<SwEntry> tab = tb_build_stop_table(tb_stop_words_of(q), &mask, &maxlen);
+      SwTable sw{tab.data(), mask, maxlen};
+      run_warps(n, alive_pred, [&](int64_t d, int lane) { body_gq(b, ascii, sw, cfg, (int)s, (tb_gq_stats*)stats, d, lane); });
+    } else if (sc.type == TB_STEP_GOPHER_REPETITION) {
+      const tb_gr_params& q = sc.u.gr;
+      GrCfg g{};
+      g.has = q.has; g.n_top = q.n_top; g.n_dup = q.n_dup;
+      g.dup_line_frac = q.dup_line_frac; g.dup_para_frac = q.dup_para_frac;
+      g.dup_line_char_frac = q.dup_line_char_frac; g.dup_para_char_frac = q.dup_para_char_frac;
+      for (int k = 0; k < TB_MAX_NGRAMS; k++) { g.top_n[k] = q.top_n[k]; g.top_frac[k] = q.top_frac[k]; g.dup_n[k] = q.dup_n[k]; g.dup_frac[k] = q.dup_frac[k]; }
+      uint32_t K = 10u + (uint32_t)g.n_dup; K += K & 1u;
+      GrScratch gs{(uint64_t*)G64(units), G32(units), (uint64_t*)G64(units), G32(units), G8(units),
+                   (GrDoc*)G8(n1 * sizeof(GrDoc)), G32(units * K + n1 * TB_REP_DOC_EXTRA), K};
+      for (int64_t d = 0; d < n; d++) body_trim(b, ascii, ts, te, d);
+      run_warps(n, alive_pred, [&](int64_t d, int lane) { body_gr_scan(b, ascii, ts, te, gs, d, lane); });
+      uint32_t* s_tab = G32(TB_REP_SMEM_TABLE);
+      run_warps(n, alive_pred, [&](int64_t d, int lane) { body_gr_rep(b, s_tab, ts, te, gs, g, (int)s, (tb_gr_stats*)stats, d, lane); });
+    } else if (sc.type == TB_STEP_C4_QUALITY) {
+      if (!sc.u.c4.split_paragraph || has_c4) return 5;
+      C4Cfg cfg = tb_c4cfg_of(sc.u.c4);
+      C4Scratch cs{G8((size_t)nb + 64), G8((size_t)nb + 64), G64(n1), G32(n1), G32(n1), G32(lines), G32(lines), G32(lines),
+                   G64(n1), G64(n1), G64(n1), G64(n1), G32(4 * n1)};
+      run_warps(n, alive_pred, [&](int64_t d, int lane) { body_c4_a(b, ascii, cfg, cs, d, lane); });
+      run_warps(n, [&](int64_t d) { return alive[d] && !cs.docflags[d] && cs.nlines[d] != 0; },
+                [&](int64_t d, int lane) { body_c4_b(b, ascii, cfg, cs, d, lane); });
+      run_warps(n, [&](int64_t) { return true; }, [&](int64_t d, int lane) { body_c4_c(b, cfg, cs, d, lane); });
+      { KBatch fb = b; fb.text = cs.F; fb.rs = cs.frs; fb.re = cs.fre; for (int64_t d = 0; d < n; d++) body_trim(fb, ascii, cs.frs, cs.fre, d); }
+      run_warps(n, alive_pred, [&](int64_t d, int lane) { body_c4_d(b, ascii, cfg, cs, (int)s, (tb_c4_stats*)stats, rewritten, rs, re, d, lane); });
+      b.text = cs.F;
+      has_c4 = true;
+    } else {
+      return 1;
+    }
+    memcpy(stats_out[s], stats, (size_t)n * stat_size(sc.type));
+  }
+  memcpy(keep, alive, (size_t)n);
+  memcpy(failed_out, failed, (size_t)n);
+  if (has_c4 && content_out) {
+    for (int64_t d = 0; d < n; d++) body_final_len(rs0, re0, rs, re, rewritten, len, d);
+    int64_t acc = 0;
+    for (int64_t d = 0; d < n; d++) { out_off[d] = acc; acc += len[d]; }
+    out_off[n] = acc;
+    run_warps(n, [&](int64_t) { return true; },
+              [&](int64_t d, int lane) { body_pack(text, rs0, b.text, rs, rewritten, out_off, content_out, d, lane); });
+    memcpy(content_off_out, out_off, n1 * 8);
+  }
+  for (void* p : frees) free(p);
+  return has_c4 ? 100 : 0;
+}

@@ -1,0 +1,646 @@
+// tb_api.cu -- the C ABI (include/textblaster_b200.h): context, pipeline construction with the
+// reference's validation rules, and the batch executor (chunked, double-buffered H2D on a copy
+// stream, kernels on a compute stream, results to pinned host memory).
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "tb_hostutil.h"
+#include "tb_kernels.cuh"
+#include "unicode_tables.inc"
+
+static_assert(TB_WB_OTHER == WB_OTHER && TB_WB_CR == WB_CR && TB_WB_LF == WB_LF && TB_WB_NEWLINE == WB_NEWLINE &&
+              TB_WB_EXTEND == WB_EXTEND && TB_WB_ZWJ == WB_ZWJ && TB_WB_REGIONAL_INDICATOR == WB_RI &&
+              TB_WB_FORMAT == WB_FORMAT && TB_WB_KATAKANA == WB_KATAKANA && TB_WB_HEBREW_LETTER == WB_HEBREW &&
+              TB_WB_ALETTER == WB_ALETTER && TB_WB_SINGLE_QUOTE == WB_SQ && TB_WB_DOUBLE_QUOTE == WB_DQ &&
+              TB_WB_MIDNUMLET == WB_MIDNUMLET && TB_WB_MIDLETTER == WB_MIDLETTER && TB_WB_MIDNUM == WB_MIDNUM &&
+              TB_WB_NUMERIC == WB_NUMERIC && TB_WB_EXTENDNUMLET == WB_EXTENDNUMLET && TB_WB_WSEGSPACE == WB_WSEG,
+              "Word_Break numbering");
+static_assert(TB_SB_OTHER == SB_OTHER && TB_SB_CR == SB_CR && TB_SB_LF == SB_LF && TB_SB_SEP == SB_SEP &&
+              TB_SB_EXTEND == SB_EXTEND && TB_SB_FORMAT == SB_FORMAT && TB_SB_SP == SB_SP && TB_SB_LOWER == SB_LOWER &&
+              TB_SB_UPPER == SB_UPPER && TB_SB_OLETTER == SB_OLETTER && TB_SB_NUMERIC == SB_NUMERIC &&
+              TB_SB_ATERM == SB_ATERM && TB_SB_SCONTINUE == SB_SCONTINUE && TB_SB_STERM == SB_STERM &&
+              TB_SB_CLOSE == SB_CLOSE, "Sentence_Break numbering");
+
+namespace {
+
+thread_local std::string g_err;
+int fail(int code, const std::string& msg) { g_err = msg; return code; }
+#define CK(call)                                                                                   \
+  do {                                                                                             \
+    cudaError_t e_ = (call);                                                                       \
+    if (e_ != cudaSuccess) {                                                                       \
+      return fail(e_ == cudaErrorMemoryAllocation ? TB_ERR_OUT_OF_MEMORY : TB_ERR_CUDA,            \
+                  std::string(#call) + ": " + cudaGetErrorString(e_));                             \
+    }                                                                                              \
+  } while (0)
+
+// format!("{}", f64): shortest round-trip digits, no exponent, no trailing ".0"
+std::string rust_f64(double v) {
+  if (std::isnan(v)) return "NaN";
+  if (std::isinf(v)) return v > 0 ? "inf" : "-inf";
+  char buf[64];
+  for (int p = 1; p <= 17; p++) {
+    snprintf(buf, sizeof buf, "%.*g", p, v);
+    if (strtod(buf, nullptr) == v) break;
+  }
+  std::string s = buf;
+  if (s.find('e') != std::string::npos || s.find('E') != std::string::npos) {
+    // expand the exponent form
+    char big[512];
+    snprintf(big, sizeof big, "%.340f", v);
+    std::string t = big;
+    // trim to the shortest prefix that round-trips
+    size_t dot = t.find('.');
+    size_t keep = dot;
+    for (size_t n = dot; n <= t.size(); n++) { if (strtod(t.substr(0, n).c_str(), nullptr) == v) { keep = n; break; } }
+    s = t.substr(0, keep);
+    if (!s.empty() && s.back() == '.') s.pop_back();
+  }
+  return s;
+}
+
+struct DevBuf {  // grow-only device allocation
+  void* p = nullptr; size_t cap = 0;
+  int ensure(size_t bytes) {
+    if (bytes <= cap) return TB_OK;
+    if (p) cudaFree(p);
+    p = nullptr; cap = 0;
+    size_t want = bytes + bytes / 8 + 256;
+    cudaError_t e = cudaMalloc(&p, want);
+    if (e != cudaSuccess) { cudaGetLastError(); e = cudaMalloc(&p, bytes); want = bytes; }
+    if (e != cudaSuccess) { p = nullptr; return fail(TB_ERR_OUT_OF_MEMORY, "cudaMalloc of " + std::to_string(bytes) + " bytes failed"); }
+    cap = want;
+    return TB_OK;
+  }
+  void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+  template <class T> T* as() const { return (T*)p; }
+};
+struct HostBuf {  // grow-only pinned host allocation
+  void* p = nullptr; size_t cap = 0;
+  int ensure(size_t bytes) {
+    if (bytes <= cap) return TB_OK;
+    if (p) cudaFreeHost(p);
+    p = nullptr; cap = 0;
+    size_t want = bytes + bytes / 8 + 256;
+    if (cudaMallocHost(&p, want) != cudaSuccess) { cudaGetLastError(); p = nullptr; return fail(TB_ERR_OUT_OF_MEMORY, "cudaMallocHost failed"); }
+    cap = want;
+    return TB_OK;
+  }
+  void release() { if (p) cudaFreeHost(p); p = nullptr; cap = 0; }
+  template <class T> T* as() const { return (T*)p; }
+};
+
+size_t stat_size(int type) {
+  return type == TB_STEP_C4_QUALITY ? sizeof(tb_c4_stats) : type == TB_STEP_GOPHER_QUALITY ? sizeof(tb_gq_stats) : sizeof(tb_gr_stats);
+}
+
+struct StepHost {
+  int type;
+  C4Cfg c4;
+  GqCfg gq;
+  GrCfg gr;
+  SwTable sw{nullptr, 0, 0};
+  DevBuf sw_dev;
+};
+
+struct ResultSet {  // host-side results of one run
+  HostBuf keep, failed, content, content_off;
+  HostBuf stats[TB_MAX_STEPS];
+  bool in_use = false;
+};
+
+struct KTime { const char* name; double ms; int64_t launches; };
+
+}  // namespace
+
+struct tb_ctx {
+  int device = 0;
+  cudaStream_t compute = nullptr, copy = nullptr, d2h = nullptr;
+  UcTables uc{};
+  DevBuf t_stage1, t_stage2, t_lower, t_cased, t_caseign, t_pow;
+};
+
+struct tb_pipeline {
+  tb_ctx* ctx = nullptr;
+  std::vector<StepHost> steps;
+  int64_t opt_return_content = 1, opt_validate = 0, opt_chunk = 256ll << 20;
+  std::mutex mu;
+  // device buffers (grow-only)
+  DevBuf text[2], offs[2], packed[2];
+  DevBuf rs0, re0, rs, re, ts, te, alive, failed, rewritten, len, out_off, bad;
+  DevBuf stats[TB_MAX_STEPS];
+  // GopherRepetition scratch
+  DevBuf g_wh, g_wl, g_lh, g_ll, g_lg, g_doc, g_work;
+  // C4 scratch
+  DevBuf c_P, c_F, c_plen, c_nlines, c_docflags, c_lwc, c_lmax, c_lflags, c_prs, c_pre, c_frs, c_fre, c_cnt;
+  cudaEvent_t ev_h2d[2] = {nullptr, nullptr}, ev_done[2] = {nullptr, nullptr}, ev_d2h[2] = {nullptr, nullptr};
+  std::vector<ResultSet*> results;
+  // kernel timing
+  std::vector<cudaEvent_t> ev_pool;
+  struct Pending { int k; cudaEvent_t a, b; };
+  std::vector<Pending> pending;
+  std::vector<KTime> ktimes;
+  size_t ev_next = 0;
+  int launches_this_run = 0;
+  double ms_this_run = 0;
+};
+
+namespace {
+
+int upload(DevBuf& b, const void* src, size_t bytes) {
+  int rc = b.ensure(bytes ? bytes : 1);
+  if (rc) return rc;
+  if (bytes) CK(cudaMemcpy(b.p, src, bytes, cudaMemcpyHostToDevice));
+  return TB_OK;
+}
+
+int ktime_index(tb_pipeline* p, const char* name) {
+  for (size_t i = 0; i < p->ktimes.size(); i++) if (strcmp(p->ktimes[i].name, name) == 0) return (int)i;
+  p->ktimes.push_back(KTime{name, 0.0, 0});
+  return (int)p->ktimes.size() - 1;
+}
+cudaEvent_t next_event(tb_pipeline* p) {
+  if (p->ev_next == p->ev_pool.size()) { cudaEvent_t e; cudaEventCreate(&e); p->ev_pool.push_back(e); }
+  return p->ev_pool[p->ev_next++];
+}
+struct Timed {  // brackets one kernel launch with events on the compute stream
+  tb_pipeline* p; int k; cudaEvent_t a, b;
+  Timed(tb_pipeline* p_, const char* name) : p(p_) {
+    k = ktime_index(p, name); a = next_event(p); b = next_event(p);
+    cudaEventRecord(a, p->ctx->compute);
+  }
+  ~Timed() { cudaEventRecord(b, p->ctx->compute); p->pending.push_back({k, a, b}); p->launches_this_run++; }
+};
+void resolve_times(tb_pipeline* p) {
+  for (auto& q : p->pending) {
+    float ms = 0;
+    if (cudaEventElapsedTime(&ms, q.a, q.b) == cudaSuccess) { p->ktimes[q.k].ms += ms; p->ktimes[q.k].launches++; p->ms_this_run += ms; }
+  }
+  p->pending.clear();
+  p->ev_next = 0;
+}
+
+// ---- validation: src/config/pipeline.rs:82-99, :118-158, :179-257 -----------------------------
+int validate_step(const tb_step_cfg& s) {
+  if (s.type == TB_STEP_C4_QUALITY) {
+    const tb_c4_params& p = s.u.c4;
+    if (p.min_num_sentences == 0) return fail(TB_ERR_CONFIG_VALIDATION, "C4QualityParams: min_num_sentences must be greater than 0");
+    if (p.min_words_per_line == 0) return fail(TB_ERR_CONFIG_VALIDATION, "C4QualityParams: min_words_per_line must be greater than 0");
+    if (p.max_word_length == 0) return fail(TB_ERR_CONFIG_VALIDATION, "C4QualityParams: max_word_length must be greater than 0");
+    return TB_OK;
+  }
+  if (s.type == TB_STEP_GOPHER_REPETITION) {
+    const tb_gr_params& p = s.u.gr;
+    struct { const char* name; uint32_t bit; double v; } fr[4] = {{"dup_line_frac", TB_GR_HAS_DUP_LINE_FRAC, p.dup_line_frac},
+                                                                  {"dup_para_frac", TB_GR_HAS_DUP_PARA_FRAC, p.dup_para_frac},
+                                                                  {"dup_line_char_frac", TB_GR_HAS_DUP_LINE_CHAR_FRAC, p.dup_line_char_frac},
+                                                                  {"dup_para_char_frac", TB_GR_HAS_DUP_PARA_CHAR_FRAC, p.dup_para_char_frac}};
+    for (auto& f : fr)
+      if ((p.has & f.bit) && !(f.v >= 0.0 && f.v <= 1.0))
+        return fail(TB_ERR_CONFIG_VALIDATION, std::string("GopherRepetitionParams: ") + f.name + " must be between 0.0 and 1.0, got " + rust_f64(f.v));
+    if (p.n_top < 0 || p.n_top > TB_MAX_NGRAMS || p.n_dup < 0 || p.n_dup > TB_MAX_NGRAMS)
+      return fail(TB_ERR_INVALID_ARGUMENT, "GopherRepetitionFilter: at most " + std::to_string(TB_MAX_NGRAMS) + " entries per n-gram list");
+    for (int which = 0; which < 2; which++) {
+      const char* name = which ? "dup_n_grams" : "top_n_grams";
+      int n = which ? p.n_dup : p.n_top;
+      for (int i = 0; i < n; i++) {
+        uint32_t size = which ? p.dup_n[i] : p.top_n[i];
+        double fraction = which ? p.dup_frac[i] : p.top_frac[i];
+        if (size == 0)
+          return fail(TB_ERR_CONFIG_VALIDATION, std::string("GopherRepetitionParams: n-gram size in ") + name + " at index " + std::to_string(i) + " must be greater than 0");
+        if (!(fraction >= 0.0 && fraction <= 1.0))
+          return fail(TB_ERR_CONFIG_VALIDATION, std::string("GopherRepetitionParams: n-gram fraction in ") + name + " at index " + std::to_string(i) + " must be between 0.0 and 1.0, got " + rust_f64(fraction));
+        if (size > TB_MAX_NGRAM_N) return fail(TB_ERR_UNSUPPORTED, "GopherRepetitionFilter: n-gram order above " + std::to_string(TB_MAX_NGRAM_N));
+      }
+    }
+    return TB_OK;
+  }
+  if (s.type == TB_STEP_GOPHER_QUALITY) {
+    const tb_gq_params& p = s.u.gq;
+    bool hmin = p.has & TB_GQ_HAS_MIN_DOC_WORDS, hmax = p.has & TB_GQ_HAS_MAX_DOC_WORDS;
+    if (hmin && p.min_doc_words == 0) return fail(TB_ERR_CONFIG_VALIDATION, "GopherQualityParams: min_doc_words must be greater than 0");
+    if (hmax && p.max_doc_words == 0) return fail(TB_ERR_CONFIG_VALIDATION, "GopherQualityParams: max_doc_words must be greater than 0");
+    if (hmin && hmax && p.min_doc_words > p.max_doc_words)
+      return fail(TB_ERR_CONFIG_VALIDATION, "GopherQualityParams: min_doc_words (" + std::to_string(p.min_doc_words) + ") cannot be greater than max_doc_words (" + std::to_string(p.max_doc_words) + ")");
+    bool amin = p.has & TB_GQ_HAS_MIN_AVG_WORD_LENGTH, amax = p.has & TB_GQ_HAS_MAX_AVG_WORD_LENGTH;
+    if (amin && !(p.min_avg_word_length > 0.0)) return fail(TB_ERR_CONFIG_VALIDATION, "GopherQualityParams: min_avg_word_length must be greater than 0.0");
+    if (amax && !(p.max_avg_word_length > 0.0)) return fail(TB_ERR_CONFIG_VALIDATION, "GopherQualityParams: max_avg_word_length must be greater than 0.0");
+    if (amin && amax && p.min_avg_word_length > p.max_avg_word_length)
+      return fail(TB_ERR_CONFIG_VALIDATION, "GopherQualityParams: min_avg_word_length (" + rust_f64(p.min_avg_word_length) + ") cannot be greater than max_avg_word_length (" + rust_f64(p.max_avg_word_length) + ")");
+    struct { const char* name; uint32_t bit; double v; } rr[4] = {{"max_symbol_word_ratio", TB_GQ_HAS_MAX_SYMBOL_WORD_RATIO, p.max_symbol_word_ratio},
+                                                                  {"max_bullet_lines_ratio", TB_GQ_HAS_MAX_BULLET_LINES_RATIO, p.max_bullet_lines_ratio},
+                                                                  {"max_ellipsis_lines_ratio", TB_GQ_HAS_MAX_ELLIPSIS_LINES_RATIO, p.max_ellipsis_lines_ratio},
+                                                                  {"max_non_alpha_words_ratio", TB_GQ_HAS_MAX_NON_ALPHA_WORDS_RATIO, p.max_non_alpha_words_ratio}};
+    for (auto& r : rr)
+      if ((p.has & r.bit) && r.v < 0.0)
+        return fail(TB_ERR_CONFIG_VALIDATION, std::string("GopherQualityParams: ") + r.name + " must be non-negative, got " + rust_f64(r.v));
+    if ((p.has & TB_GQ_HAS_STOP_WORDS) && (p.n_stop_words < 0 || (p.n_stop_words > 0 && (!p.stop_words_utf8 || !p.stop_words_offsets))))
+      return fail(TB_ERR_INVALID_ARGUMENT, "GopherQualityFilter: stop word list pointers missing");
+    return TB_OK;
+  }
+  return fail(TB_ERR_INVALID_ARGUMENT, "unknown step type " + std::to_string(s.type));
+}
+
+int build_stop_table(StepHost& sh, const tb_gq_params& p) {
+  uint32_t mask = 0, maxlen = 0;
+  std::vector<SwEntry> tab = tb_build_stop_table(tb_stop_words_of(p), &mask, &maxlen);
+  int rc = upload(sh.sw_dev, tab.data(), tab.size() * sizeof(SwEntry));
+  if (rc) return rc;
+  sh.sw = SwTable{sh.sw_dev.as<SwEntry>(), mask, maxlen};
+  return TB_OK;
+}
+
+struct Chunk { int64_t d0, d1, b0, b1; };
+
+inline int64_t off_at(const void* offsets, int is64, int64_t i) {
+  return is64 ? ((const int64_t*)offsets)[i] : (int64_t)((const int32_t*)offsets)[i];
+}
+
+ResultSet* acquire_results(tb_pipeline* p) {
+  for (auto* r : p->results) if (!r->in_use) { r->in_use = true; return r; }
+  auto* r = new ResultSet();
+  r->in_use = true;
+  p->results.push_back(r);
+  return r;
+}
+
+// Device buffers for a chunk of n docs / nb bytes.
+int ensure_chunk_buffers(tb_pipeline* p, int64_t n, int64_t nb, bool host_input) {
+  int rc;
+  size_t n1 = (size_t)n + 1;
+#define ENS(buf, bytes) if ((rc = (buf).ensure(bytes))) return rc
+  if (host_input) { for (int i = 0; i < 2; i++) { ENS(p->text[i], (size_t)nb + 64); ENS(p->offs[i], n1 * 8); } }
+  for (int i = 0; i < 2; i++) ENS(p->packed[i], (size_t)nb + 64);
+  ENS(p->rs0, n1 * 8); ENS(p->re0, n1 * 8); ENS(p->rs, n1 * 8); ENS(p->re, n1 * 8); ENS(p->ts, n1 * 8); ENS(p->te, n1 * 8);
+  ENS(p->alive, n1); ENS(p->failed, n1); ENS(p->rewritten, n1); ENS(p->len, n1 * 8); ENS(p->out_off, (n1 + 1) * 8); ENS(p->bad, 16);
+  size_t units = (size_t)nb / 2 + n1 + 1;
+  for (size_t s = 0; s < p->steps.size(); s++) {
+    const StepHost& sh = p->steps[s];
+    ENS(p->stats[s], n1 * stat_size(sh.type));
+    if (sh.type == TB_STEP_GOPHER_REPETITION) {
+      uint32_t K = 10u + (uint32_t)sh.gr.n_dup; K += K & 1u;
+      ENS(p->g_wh, units * 8); ENS(p->g_wl, units * 4); ENS(p->g_lh, units * 8); ENS(p->g_ll, units * 4); ENS(p->g_lg, units);
+      ENS(p->g_doc, n1 * sizeof(GrDoc));
+      ENS(p->g_work, (units * K + n1 * TB_REP_DOC_EXTRA) * 4);
+    } else if (sh.type == TB_STEP_C4_QUALITY) {
+      size_t lines = (size_t)nb + n1 + 1;
+      ENS(p->c_P, (size_t)nb + 64); ENS(p->c_F, (size_t)nb + 64);
+      ENS(p->c_plen, n1 * 8); ENS(p->c_nlines, n1 * 4); ENS(p->c_docflags, n1 * 4);
+      ENS(p->c_lwc, lines * 4); ENS(p->c_lmax, lines * 4); ENS(p->c_lflags, lines * 4);
+      ENS(p->c_prs, n1 * 8); ENS(p->c_pre, n1 * 8); ENS(p->c_frs, n1 * 8); ENS(p->c_fre, n1 * 8); ENS(p->c_cnt, n1 * 16);
+    }
+  }
+#undef ENS
+  return TB_OK;
+}
+
+// Enqueue every kernel of the chain for one chunk whose text is at `text` (device) with ranges in
+// rs0/re0 (already initialised).  Leaves packed content in p->packed[pb] and offsets in out_off.
+int enqueue_chain(tb_pipeline* p, const uint8_t* text, int64_t n, int pb, bool want_content, bool* has_c4) {
+  tb_ctx* c = p->ctx;
+  cudaStream_t st = c->compute;
+  CK(cudaMemcpyAsync(p->rs.p, p->rs0.p, (size_t)n * 8, cudaMemcpyDeviceToDevice, st));
+  CK(cudaMemcpyAsync(p->re.p, p->re0.p, (size_t)n * 8, cudaMemcpyDeviceToDevice, st));
+  CK(cudaMemsetAsync(p->rewritten.p, 0, (size_t)n, st));
+  KBatch b{text, p->rs.as<int64_t>(), p->re.as<int64_t>(), p->alive.as<uint8_t>(), p->failed.as<int8_t>(), n, c->uc};
+  *has_c4 = false;
+  if (p->opt_validate) {
+    CK(cudaMemsetAsync(p->bad.p, 0, 4, st));
+    { Timed t(p, "k_validate_utf8"); tb_launch_validate_utf8(st, text, b.rs, b.re, n, p->bad.as<int32_t>()); }
+  }
+  for (size_t s = 0; s < p->steps.size(); s++) {
+    StepHost& sh = p->steps[s];
+    if (sh.type == TB_STEP_GOPHER_QUALITY) {
+      Timed t(p, "k_gq");
+      tb_launch_gq(st, b, sh.sw, sh.gq, (int)s, p->stats[s].as<tb_gq_stats>());
+    } else if (sh.type == TB_STEP_GOPHER_REPETITION) {
+      uint32_t K = 10u + (uint32_t)sh.gr.n_dup; K += K & 1u;
+      GrScratch g{p->g_wh.as<uint64_t>(), p->g_wl.as<uint32_t>(), p->g_lh.as<uint64_t>(), p->g_ll.as<uint32_t>(),
+                  p->g_lg.as<uint8_t>(), p->g_doc.as<GrDoc>(), p->g_work.as<uint32_t>(), K};
+      { Timed t(p, "k_trim"); tb_launch_trim(st, b, p->ts.as<int64_t>(), p->te.as<int64_t>()); }
+      { Timed t(p, "k_gr_scan"); tb_launch_gr_scan(st, b, p->ts.as<int64_t>(), p->te.as<int64_t>(), g); }
+      { Timed t(p, "k_gr_rep"); tb_launch_gr_rep(st, b, p->ts.as<int64_t>(), p->te.as<int64_t>(), g, sh.gr, (int)s, p->stats[s].as<tb_gr_stats>()); }
+    } else {
+      C4Scratch cs{p->c_P.as<uint8_t>(), p->c_F.as<uint8_t>(), p->c_plen.as<int64_t>(), p->c_nlines.as<uint32_t>(),
+                   p->c_docflags.as<uint32_t>(), p->c_lwc.as<uint32_t>(), p->c_lmax.as<uint32_t>(), p->c_lflags.as<uint32_t>(),
+                   p->c_prs.as<int64_t>(), p->c_pre.as<int64_t>(), p->c_frs.as<int64_t>(), p->c_fre.as<int64_t>(), p->c_cnt.as<uint32_t>()};
+      { Timed t(p, "k_c4_a"); tb_launch_c4_a(st, b, sh.c4, cs); }
+      { Timed t(p, "k_c4_b"); tb_launch_c4_b(st, b, sh.c4, cs); }
+      { Timed t(p, "k_c4_c"); tb_launch_c4_c(st, b, sh.c4, cs); }
+      {  // content = kept.join("\n").trim()   (c4_filters.rs:258)
+        KBatch fb = b; fb.text = cs.F; fb.rs = cs.frs; fb.re = cs.fre;
+        Timed t(p, "k_trim"); tb_launch_trim(st, fb, cs.frs, cs.fre);
+      }
+      { Timed t(p, "k_c4_d"); tb_launch_c4_d(st, b, sh.c4, cs, (int)s, p->stats[s].as<tb_c4_stats>(), p->rewritten.as<uint8_t>()); }
+      b.text = cs.F;  // every document still alive now lives in F
+      *has_c4 = true;
+    }
+  }
+  if (*has_c4 && want_content) {
+    { Timed t(p, "k_final_len"); tb_launch_final_len(st, n, p->rs0.as<int64_t>(), p->re0.as<int64_t>(), b.rs, b.re, p->rewritten.as<uint8_t>(), p->len.as<int64_t>()); }
+    { Timed t(p, "k_scan_i64"); tb_launch_scan_i64(st, p->len.as<int64_t>(), p->out_off.as<int64_t>(), n); }
+    { Timed t(p, "k_pack"); tb_launch_pack(st, n, text, p->rs0.as<int64_t>(), b.text, b.rs, p->rewritten.as<uint8_t>(), p->out_off.as<int64_t>(), p->packed[pb].as<uint8_t>()); }
+  }
+  CK(cudaGetLastError());
+  return TB_OK;
+}
+
+int run_impl(tb_pipeline* p, const uint8_t* utf8, const void* offsets, int is64, int64_t n_docs, bool device_input,
+             const int64_t* offsets_dev, tb_batch_out* out) {
+  tb_ctx* c = p->ctx;
+  CK(cudaSetDevice(c->device));
+  memset(out, 0, sizeof *out);
+  out->n_docs = n_docs;
+  out->n_steps = (int32_t)p->steps.size();
+  p->launches_this_run = 0; p->ms_this_run = 0;
+  bool any_c4 = false;
+  for (auto& s : p->steps) any_c4 |= s.type == TB_STEP_C4_QUALITY;
+  const bool want_content = any_c4 && p->opt_return_content;
+
+  ResultSet* rsx = acquire_results(p);
+  out->_owner = rsx;
+  int rc;
+  size_t n1 = (size_t)n_docs + 1;
+  if ((rc = rsx->keep.ensure(n1)) || (rc = rsx->failed.ensure(n1))) return rc;
+  for (size_t s = 0; s < p->steps.size(); s++) if ((rc = rsx->stats[s].ensure(n1 * stat_size(p->steps[s].type)))) return rc;
+  const int64_t base0 = n_docs ? off_at(offsets, is64, 0) : 0;
+  const int64_t total_bytes = n_docs ? off_at(offsets, is64, n_docs) - base0 : 0;
+  if (want_content) { if ((rc = rsx->content.ensure((size_t)total_bytes + 64)) || (rc = rsx->content_off.ensure(n1 * 8))) return rc; }
+  for (int64_t i = 0; i < n_docs; i++) if (off_at(offsets, is64, i + 1) < off_at(offsets, is64, i)) return fail(TB_ERR_INVALID_ARGUMENT, "offsets must be non-decreasing");
+
+  // chunk plan
+  std::vector<Chunk> chunks;
+  int64_t max_n = 0, max_b = 0;
+  for (int64_t d = 0; d < n_docs;) {
+    int64_t b0 = off_at(offsets, is64, d), e = d;
+    while (e < n_docs && (e == d || off_at(offsets, is64, e + 1) - b0 <= p->opt_chunk)) e++;
+    chunks.push_back({d, e, b0, off_at(offsets, is64, e)});
+    max_n = std::max(max_n, e - d); max_b = std::max(max_b, off_at(offsets, is64, e) - b0);
+    d = e;
+  }
+  if ((rc = ensure_chunk_buffers(p, max_n, max_b, !device_input))) return rc;
+
+  uint8_t* h_keep = rsx->keep.as<uint8_t>();
+  int8_t* h_failed = rsx->failed.as<int8_t>();
+  int64_t* h_coff = rsx->content_off.as<int64_t>();
+  uint8_t* h_content = rsx->content.as<uint8_t>();
+  int64_t content_base = 0;
+  int32_t h_bad = 0;
+
+  auto enqueue_h2d = [&](size_t ci) -> int {
+    const Chunk& ch = chunks[ci];
+    int buf = (int)(ci & 1);
+    if (device_input) return TB_OK;
+    CK(cudaStreamWaitEvent(c->copy, p->ev_done[buf], 0));
+    int64_t nb = ch.b1 - ch.b0, n = ch.d1 - ch.d0;
+    if (nb) CK(cudaMemcpyAsync(p->text[buf].p, utf8 + ch.b0, (size_t)nb, cudaMemcpyHostToDevice, c->copy));
+    size_t osz = is64 ? 8 : 4;
+    CK(cudaMemcpyAsync(p->offs[buf].p, (const uint8_t*)offsets + (size_t)ch.d0 * osz, (size_t)(n + 1) * osz, cudaMemcpyHostToDevice, c->copy));
+    CK(cudaEventRecord(p->ev_h2d[buf], c->copy));
+    return TB_OK;
+  };
+
+  if (!chunks.empty()) if ((rc = enqueue_h2d(0))) return rc;
+  for (size_t ci = 0; ci < chunks.size(); ci++) {
+    const Chunk& ch = chunks[ci];
+    int buf = (int)(ci & 1);
+    int64_t n = ch.d1 - ch.d0;
+    if (ci + 1 < chunks.size()) if ((rc = enqueue_h2d(ci + 1))) return rc;
+    const uint8_t* text;
+    if (device_input) {
+      text = utf8 + ch.b0;
+      tb_launch_init_ranges(c->compute, offsets_dev, 1, ch.d0, n, ch.b0, p->rs0.as<int64_t>(), p->re0.as<int64_t>(), p->alive.as<uint8_t>(), p->failed.as<int8_t>());
+    } else {
+      CK(cudaStreamWaitEvent(c->compute, p->ev_h2d[buf], 0));
+      text = p->text[buf].as<uint8_t>();
+      tb_launch_init_ranges(c->compute, p->offs[buf].p, is64, 0, n, ch.b0, p->rs0.as<int64_t>(), p->re0.as<int64_t>(), p->alive.as<uint8_t>(), p->failed.as<int8_t>());
+    }
+    p->launches_this_run++;
+    // packed[buf] may still be read by the D2H of chunk ci-2
+    CK(cudaStreamWaitEvent(c->compute, p->ev_d2h[buf], 0));
+    bool has_c4 = false;
+    if ((rc = enqueue_chain(p, text, n, buf, want_content, &has_c4))) return rc;
+    // small results
+    CK(cudaMemcpyAsync(h_keep + ch.d0, p->alive.p, (size_t)n, cudaMemcpyDeviceToHost, c->compute));
+    CK(cudaMemcpyAsync(h_failed + ch.d0, p->failed.p, (size_t)n, cudaMemcpyDeviceToHost, c->compute));
+    for (size_t s = 0; s < p->steps.size(); s++) {
+      size_t sz = stat_size(p->steps[s].type);
+      CK(cudaMemcpyAsync(rsx->stats[s].as<uint8_t>() + (size_t)ch.d0 * sz, p->stats[s].p, (size_t)n * sz, cudaMemcpyDeviceToHost, c->compute));
+    }
+    if (want_content) CK(cudaMemcpyAsync(h_coff + ch.d0, p->out_off.p, (size_t)(n + 1) * 8, cudaMemcpyDeviceToHost, c->compute));
+    if (p->opt_validate) CK(cudaMemcpyAsync(&h_bad, p->bad.p, 4, cudaMemcpyDeviceToHost, c->compute));
+    CK(cudaEventRecord(p->ev_done[buf], c->compute));
+    CK(cudaStreamSynchronize(c->compute));
+    resolve_times(p);
+    if (p->opt_validate && h_bad) return fail(TB_ERR_INVALID_UTF8, "input contains " + std::to_string(h_bad) + " document(s) with invalid UTF-8 (first chunk doc " + std::to_string(ch.d0) + ")");
+    if (want_content) {
+      int64_t tot = h_coff[ch.d0 + n];
+      for (int64_t i = 0; i <= n; i++) h_coff[ch.d0 + i] += content_base;  // chunk-relative -> absolute
+      CK(cudaStreamWaitEvent(c->d2h, p->ev_done[buf], 0));
+      if (tot) CK(cudaMemcpyAsync(h_content + content_base, p->packed[buf].p, (size_t)tot, cudaMemcpyDeviceToHost, c->d2h));
+      CK(cudaEventRecord(p->ev_d2h[buf], c->d2h));
+      content_base += tot;
+    }
+  }
+  CK(cudaStreamSynchronize(c->d2h));
+  CK(cudaStreamSynchronize(c->copy));
+  out->keep = h_keep;
+  out->failed_step = h_failed;
+  for (size_t s = 0; s < p->steps.size(); s++) out->step_stats[s] = rsx->stats[s].p;
+  if (want_content) {
+    if (n_docs == 0) h_coff[0] = 0;
+    out->content_rewritten = 1; out->content = h_content; out->content_offsets = h_coff; out->content_bytes = content_base;
+  }
+  out->gpu_ms = p->ms_this_run;
+  out->gpu_launches = p->launches_this_run;
+  return TB_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int tb_abi_version(void) { return TB_ABI_VERSION; }
+const char* tb_last_error(const tb_ctx*) { return g_err.c_str(); }
+const char* tb_step_name(int32_t t) {
+  switch (t) {
+    case TB_STEP_C4_QUALITY: return "C4QualityFilter";
+    case TB_STEP_GOPHER_QUALITY: return "GopherQualityFilter";
+    case TB_STEP_GOPHER_REPETITION: return "GopherRepetitionFilter";
+    default: return "";
+  }
+}
+
+int tb_ctx_create(int device, tb_ctx** out) {
+  if (!out) return fail(TB_ERR_INVALID_ARGUMENT, "out is NULL");
+  *out = nullptr;
+  int count = 0;
+  if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0) { cudaGetLastError(); return fail(TB_ERR_CUDA, "no CUDA device available (this library has no CPU path)"); }
+  if (device < 0 || device >= count) return fail(TB_ERR_INVALID_ARGUMENT, "device index out of range");
+  CK(cudaSetDevice(device));
+  auto* c = new tb_ctx();
+  c->device = device;
+  CK(cudaStreamCreateWithFlags(&c->compute, cudaStreamNonBlocking));
+  CK(cudaStreamCreateWithFlags(&c->copy, cudaStreamNonBlocking));
+  CK(cudaStreamCreateWithFlags(&c->d2h, cudaStreamNonBlocking));
+  int rc;
+  if ((rc = upload(c->t_stage1, tb_uc_stage1, sizeof tb_uc_stage1)) || (rc = upload(c->t_stage2, tb_uc_stage2, sizeof tb_uc_stage2)) ||
+      (rc = upload(c->t_lower, tb_uc_lower, sizeof tb_uc_lower)) || (rc = upload(c->t_cased, tb_uc_cased, sizeof tb_uc_cased)) ||
+      (rc = upload(c->t_caseign, tb_uc_caseign, sizeof tb_uc_caseign))) { delete c; return rc; }
+  std::vector<uint64_t> pw(TB_POWTAB);
+  uint32_t a = 1, b = 1;
+  for (int i = 0; i < TB_POWTAB; i++) { pw[i] = ((uint64_t)a << 32) | b; a = tb_mm(a, TB_B1); b = tb_mm(b, TB_B2); }
+  if ((rc = upload(c->t_pow, pw.data(), pw.size() * 8))) { delete c; return rc; }
+  c->uc = UcTables{c->t_stage1.as<uint16_t>(), c->t_stage2.as<uint16_t>(), c->t_lower.as<uint32_t>(), c->t_cased.as<uint32_t>(),
+                   c->t_caseign.as<uint32_t>(), c->t_pow.as<uint64_t>(), TB_UC_NLOWER, TB_UC_NCASED, TB_UC_NCASEIGN};
+  *out = c;
+  return TB_OK;
+}
+
+void tb_ctx_destroy(tb_ctx* c) {
+  if (!c) return;
+  cudaSetDevice(c->device);
+  for (DevBuf* b : {&c->t_stage1, &c->t_stage2, &c->t_lower, &c->t_cased, &c->t_caseign, &c->t_pow}) b->release();
+  if (c->compute) cudaStreamDestroy(c->compute);
+  if (c->copy) cudaStreamDestroy(c->copy);
+  if (c->d2h) cudaStreamDestroy(c->d2h);
+  delete c;
+}
+
+int tb_pipeline_create(tb_ctx* ctx, const tb_step_cfg* steps, size_t n_steps, tb_pipeline** out) {
+  if (!ctx || !out || (n_steps && !steps)) return fail(TB_ERR_INVALID_ARGUMENT, "NULL argument");
+  *out = nullptr;
+  if (n_steps > TB_MAX_STEPS) return fail(TB_ERR_INVALID_ARGUMENT, "at most " + std::to_string(TB_MAX_STEPS) + " steps");
+  int n_c4 = 0;
+  for (size_t i = 0; i < n_steps; i++) {
+    int rc = validate_step(steps[i]);
+    if (rc) return rc;
+    n_c4 += steps[i].type == TB_STEP_C4_QUALITY;
+    if (steps[i].type == TB_STEP_C4_QUALITY && !steps[i].u.c4.split_paragraph)
+      return fail(TB_ERR_UNSUPPORTED, "C4QualityFilter: split_paragraph = false (sentence-wise lines) is not implemented on the GPU path");
+  }
+  if (n_c4 > 1) return fail(TB_ERR_UNSUPPORTED, "at most one C4QualityFilter step per pipeline");
+  CK(cudaSetDevice(ctx->device));
+  auto* p = new tb_pipeline();
+  p->ctx = ctx;
+  p->steps.resize(n_steps);
+  for (size_t i = 0; i < n_steps; i++) {
+    StepHost& sh = p->steps[i];
+    sh.type = steps[i].type;
+    if (sh.type == TB_STEP_C4_QUALITY) {
+      const tb_c4_params& q = steps[i].u.c4;
+      sh.c4 = tb_c4cfg_of(q);
+    } else if (sh.type == TB_STEP_GOPHER_QUALITY) {
+      const tb_gq_params& q = steps[i].u.gq;
+      sh.gq = GqCfg{q.has, q.min_doc_words, q.max_doc_words, q.min_stop_words, q.min_avg_word_length, q.max_avg_word_length,
+                    q.max_symbol_word_ratio, q.max_bullet_lines_ratio, q.max_ellipsis_lines_ratio, q.max_non_alpha_words_ratio};
+      int rc = build_stop_table(sh, q);
+      if (rc) { tb_pipeline_destroy(p); return rc; }
+    } else {
+      const tb_gr_params& q = steps[i].u.gr;
+      GrCfg g{};
+      g.has = q.has; g.n_top = q.n_top; g.n_dup = q.n_dup;
+      g.dup_line_frac = q.dup_line_frac; g.dup_para_frac = q.dup_para_frac;
+      g.dup_line_char_frac = q.dup_line_char_frac; g.dup_para_char_frac = q.dup_para_char_frac;
+      for (int k = 0; k < TB_MAX_NGRAMS; k++) { g.top_n[k] = q.top_n[k]; g.top_frac[k] = q.top_frac[k]; g.dup_n[k] = q.dup_n[k]; g.dup_frac[k] = q.dup_frac[k]; }
+      sh.gr = g;
+    }
+  }
+  for (int i = 0; i < 2; i++) {
+    CK(cudaEventCreateWithFlags(&p->ev_h2d[i], cudaEventDisableTiming));
+    CK(cudaEventCreateWithFlags(&p->ev_done[i], cudaEventDisableTiming));
+    CK(cudaEventCreateWithFlags(&p->ev_d2h[i], cudaEventDisableTiming));
+  }
+  *out = p;
+  return TB_OK;
+}
+
+void tb_pipeline_destroy(tb_pipeline* p) {
+  if (!p) return;
+  cudaSetDevice(p->ctx->device);
+  cudaDeviceSynchronize();
+  for (DevBuf* b : {&p->text[0], &p->text[1], &p->offs[0], &p->offs[1], &p->packed[0], &p->packed[1], &p->rs0, &p->re0, &p->rs,
+                    &p->re, &p->ts, &p->te, &p->alive, &p->failed, &p->rewritten, &p->len, &p->out_off, &p->bad, &p->g_wh,
+                    &p->g_wl, &p->g_lh, &p->g_ll, &p->g_lg, &p->g_doc, &p->g_work, &p->c_P, &p->c_F, &p->c_plen, &p->c_nlines,
+                    &p->c_docflags, &p->c_lwc, &p->c_lmax, &p->c_lflags, &p->c_prs, &p->c_pre, &p->c_frs, &p->c_fre, &p->c_cnt})
+    b->release();
+  for (auto& b : p->stats) b.release();
+  for (auto& s : p->steps) s.sw_dev.release();
+  for (auto* r : p->results) {
+    r->keep.release(); r->failed.release(); r->content.release(); r->content_off.release();
+    for (auto& s : r->stats) s.release();
+    delete r;
+  }
+  for (int i = 0; i < 2; i++) {
+    if (p->ev_h2d[i]) cudaEventDestroy(p->ev_h2d[i]);
+    if (p->ev_done[i]) cudaEventDestroy(p->ev_done[i]);
+    if (p->ev_d2h[i]) cudaEventDestroy(p->ev_d2h[i]);
+  }
+  for (auto e : p->ev_pool) cudaEventDestroy(e);
+  delete p;
+}
+
+int tb_pipeline_set_option(tb_pipeline* p, int32_t option, int64_t value) {
+  if (!p) return fail(TB_ERR_INVALID_ARGUMENT, "NULL pipeline");
+  std::lock_guard<std::mutex> lk(p->mu);
+  switch (option) {
+    case TB_OPT_RETURN_CONTENT: p->opt_return_content = value != 0; return TB_OK;
+    case TB_OPT_VALIDATE_UTF8: p->opt_validate = value != 0; return TB_OK;
+    case TB_OPT_CHUNK_BYTES:
+      if (value < (1 << 16)) return fail(TB_ERR_INVALID_ARGUMENT, "chunk size must be at least 64 KiB");
+      p->opt_chunk = value; return TB_OK;
+    default: return fail(TB_ERR_INVALID_ARGUMENT, "unknown option");
+  }
+}
+
+int tb_pipeline_run_batch(tb_pipeline* p, const uint8_t* utf8, const void* offsets, int offsets_are_i64, int64_t n_docs,
+                          tb_batch_out* out) {
+  if (!p || !out || n_docs < 0 || (n_docs > 0 && !offsets)) return fail(TB_ERR_INVALID_ARGUMENT, "NULL or negative argument");
+  std::lock_guard<std::mutex> lk(p->mu);
+  int rc = run_impl(p, utf8, offsets, offsets_are_i64, n_docs, false, nullptr, out);
+  if (rc) { cudaDeviceSynchronize(); cudaGetLastError(); if (out->_owner) { ((ResultSet*)out->_owner)->in_use = false; out->_owner = nullptr; } }
+  return rc;
+}
+
+int tb_pipeline_run_batch_device(tb_pipeline* p, const uint8_t* utf8_dev, const int64_t* offsets_dev, int64_t n_docs,
+                                 int64_t n_bytes, tb_batch_out* out) {
+  if (!p || !out || n_docs < 0 || (n_docs > 0 && !offsets_dev)) return fail(TB_ERR_INVALID_ARGUMENT, "NULL or negative argument");
+  (void)n_bytes;
+  std::lock_guard<std::mutex> lk(p->mu);
+  CK(cudaSetDevice(p->ctx->device));
+  std::vector<int64_t> h_off((size_t)n_docs + 1, 0);
+  if (n_docs) CK(cudaMemcpy(h_off.data(), offsets_dev, ((size_t)n_docs + 1) * 8, cudaMemcpyDeviceToHost));
+  int rc = run_impl(p, utf8_dev, h_off.data(), 1, n_docs, true, offsets_dev, out);
+  if (rc) { cudaDeviceSynchronize(); cudaGetLastError(); if (out->_owner) { ((ResultSet*)out->_owner)->in_use = false; out->_owner = nullptr; } }
+  return rc;
+}
+
+void tb_batch_out_release(tb_pipeline* p, tb_batch_out* out) {
+  if (!p || !out || !out->_owner) return;
+  std::lock_guard<std::mutex> lk(p->mu);
+  ((ResultSet*)out->_owner)->in_use = false;
+  memset(out, 0, sizeof *out);
+}
+
+int tb_pipeline_kernel_times(tb_pipeline* p, int32_t max_entries, const char** names, double* ms, int64_t* launches) {
+  if (!p) return 0;
+  std::lock_guard<std::mutex> lk(p->mu);
+  int n = (int)std::min<size_t>(p->ktimes.size(), (size_t)std::max(0, max_entries));
+  for (int i = 0; i < n; i++) { names[i] = p->ktimes[i].name; ms[i] = p->ktimes[i].ms; launches[i] = p->ktimes[i].launches; }
+  return (int)p->ktimes.size();
+}
+void tb_pipeline_reset_kernel_times(tb_pipeline* p) {
+  if (!p) return;
+  std::lock_guard<std::mutex> lk(p->mu);
+  for (auto& k : p->ktimes) { k.ms = 0; k.launches = 0; }
+}
+
+}  // extern "C"

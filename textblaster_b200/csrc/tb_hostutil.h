@@ -1,0 +1,50 @@
+// tb_hostutil.h -- host-side helpers shared by the C ABI (tb_api.cu) and the host emulation
+// harness (tests/host_emul): building the stop-word table the kernels probe.
+#pragma once
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/textblaster_b200.h"
+#include "tb_lanes.cuh"
+
+// Entries are inserted exactly as configured: the reference does not lower-case the list
+// (gopher_quality.rs:46-58), only the word being looked up (:186).
+inline std::vector<SwEntry> tb_build_stop_table(const std::vector<std::string>& words, uint32_t* mask, uint32_t* maxlen) {
+  uint32_t T = 16;
+  while (T < 2 * words.size() + 2) T <<= 1;
+  std::vector<SwEntry> tab(T);
+  memset(tab.data(), 0, T * sizeof(SwEntry));
+  *maxlen = 0;
+  for (const auto& w : words) {
+    LowKey k; k.init();
+    for (unsigned char c : w) k.push(c);
+    if (k.len == 0) continue;  // the empty string can never equal a word
+    if (k.len > *maxlen) *maxlen = k.len;
+    uint32_t s = (uint32_t)sw_slot_hash(k.lo, k.hi, k.ext, k.len) & (T - 1);
+    bool dup = false;
+    while (tab[s].used) {
+      if (tab[s].len == k.len && tab[s].lo == k.lo && tab[s].hi == k.hi && tab[s].ext == k.ext) { dup = true; break; }
+      s = (s + 1) & (T - 1);
+    }
+    if (!dup) tab[s] = SwEntry{k.lo, k.hi, k.ext, k.len, 1};
+  }
+  *mask = T - 1;
+  return tab;
+}
+inline std::vector<std::string> tb_stop_words_of(const tb_gq_params& p) {
+  std::vector<std::string> words;
+  if (p.has & TB_GQ_HAS_STOP_WORDS) {
+    for (int i = 0; i < p.n_stop_words; i++)
+      words.emplace_back((const char*)p.stop_words_utf8 + p.stop_words_offsets[i],
+                         (size_t)(p.stop_words_offsets[i + 1] - p.stop_words_offsets[i]));
+  } else {
+    words = {"the", "be", "to", "of", "and", "that", "have", "with"};  // DEFAULT_STOP_WORDS, gopher_quality.rs:10
+  }
+  return words;
+}
+inline C4Cfg tb_c4cfg_of(const tb_c4_params& q) {
+  return C4Cfg{(uint32_t)q.remove_citations, (uint32_t)q.filter_no_terminal_punct, (uint32_t)q.filter_lorem_ipsum,
+               (uint32_t)q.filter_javascript, (uint32_t)q.filter_curly_bracket, (uint32_t)q.filter_policy,
+               q.min_num_sentences, q.min_words_per_line, q.max_word_length};
+}

@@ -1,0 +1,171 @@
+// tb_kernels.cu -- __global__ wrappers and launchers for the warp bodies in tb_bodies.cuh.
+// One warp per document, 4 warps per CTA; documents are independent, so the hardware block
+// scheduler does the load balancing (grid = ceil(n_docs / 4) CTAs, many waves over the 148 SMs).
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "tb_bodies.cuh"
+
+namespace {
+
+__device__ __forceinline__ void load_ascii(uint16_t* s_ascii, const UcTables& uc) {
+  if (threadIdx.x < 128) s_ascii[threadIdx.x] = uc.stage2[(uint32_t)uc.stage1[0] * 256u + threadIdx.x];
+  __syncthreads();
+}
+__device__ __forceinline__ int64_t warp_doc() { return ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; }
+__device__ __forceinline__ int64_t thread_doc() { return (int64_t)blockIdx.x * blockDim.x + threadIdx.x; }
+
+__global__ void k_init_ranges(const void* off, int off64, int64_t doc0, int64_t n, int64_t base, int64_t* rs,
+                              int64_t* re, uint8_t* alive, int8_t* failed) {
+  int64_t d = thread_doc();
+  if (d < n) body_init_ranges(off, off64, doc0, base, rs, re, alive, failed, d);
+}
+__global__ void __launch_bounds__(TB_BLOCK) k_validate_utf8(const uint8_t* t, const int64_t* rs, const int64_t* re,
+                                                             int64_t n, int32_t* bad) {
+  int64_t d = warp_doc();
+  if (d < n) body_validate_utf8(t, rs, re, bad, d, threadIdx.x & 31);
+}
+__global__ void __launch_bounds__(TB_BLOCK) k_gq(KBatch a, SwTable sw, GqCfg cfg, int step, tb_gq_stats* out) {
+  __shared__ uint16_t s_ascii[128];
+  load_ascii(s_ascii, a.uc);
+  int64_t d = warp_doc();
+  if (d >= a.n || !a.alive[d]) return;
+  body_gq(a, s_ascii, sw, cfg, step, out, d, threadIdx.x & 31);
+}
+__global__ void k_trim(KBatch a, int64_t* ts, int64_t* te) {
+  __shared__ uint16_t s_ascii[128];
+  load_ascii(s_ascii, a.uc);
+  int64_t d = thread_doc();
+  if (d < a.n) body_trim(a, s_ascii, ts, te, d);
+}
+__global__ void __launch_bounds__(TB_BLOCK) k_gr_scan(KBatch a, const int64_t* ts, const int64_t* te, GrScratch s) {
+  __shared__ uint16_t s_ascii[128];
+  load_ascii(s_ascii, a.uc);
+  int64_t d = warp_doc();
+  if (d >= a.n || !a.alive[d]) return;
+  body_gr_scan(a, s_ascii, ts, te, s, d, threadIdx.x & 31);
+}
+__global__ void __launch_bounds__(TB_BLOCK) k_gr_rep(KBatch a, const int64_t* ts, const int64_t* te, GrScratch s,
+                                                     GrCfg cfg, int step, tb_gr_stats* out) {
+  __shared__ uint32_t s_tab[TB_BLOCK / 32][TB_REP_SMEM_TABLE];
+  int64_t d = warp_doc();
+  if (d >= a.n || !a.alive[d]) return;
+  body_gr_rep(a, s_tab[threadIdx.x >> 5], ts, te, s, cfg, step, out, d, threadIdx.x & 31);
+}
+__global__ void __launch_bounds__(TB_BLOCK) k_c4_a(KBatch a, C4Cfg cfg, C4Scratch s) {
+  __shared__ uint16_t s_ascii[128];
+  load_ascii(s_ascii, a.uc);
+  int64_t d = warp_doc();
+  if (d >= a.n || !a.alive[d]) return;
+  body_c4_a(a, s_ascii, cfg, s, d, threadIdx.x & 31);
+}
+__global__ void __launch_bounds__(TB_BLOCK) k_c4_b(KBatch a, C4Cfg cfg, C4Scratch s) {
+  __shared__ uint16_t s_ascii[128];
+  load_ascii(s_ascii, a.uc);
+  int64_t d = warp_doc();
+  if (d >= a.n || !a.alive[d] || s.docflags[d] || s.nlines[d] == 0) return;
+  body_c4_b(a, s_ascii, cfg, s, d, threadIdx.x & 31);
+}
+__global__ void __launch_bounds__(TB_BLOCK) k_c4_c(KBatch a, C4Cfg cfg, C4Scratch s) {
+  int64_t d = warp_doc();
+  if (d >= a.n) return;
+  body_c4_c(a, cfg, s, d, threadIdx.x & 31);
+}
+__global__ void __launch_bounds__(TB_BLOCK) k_c4_d(KBatch a, C4Cfg cfg, C4Scratch s, int step, tb_c4_stats* out,
+                                                   uint8_t* rewritten, int64_t* rs_out, int64_t* re_out) {
+  __shared__ uint16_t s_ascii[128];
+  load_ascii(s_ascii, a.uc);
+  int64_t d = warp_doc();
+  if (d >= a.n || !a.alive[d]) return;
+  body_c4_d(a, s_ascii, cfg, s, step, out, rewritten, rs_out, re_out, d, threadIdx.x & 31);
+}
+__global__ void k_final_len(int64_t n, const int64_t* rs0, const int64_t* re0, const int64_t* rs, const int64_t* re,
+                            const uint8_t* rewritten, int64_t* len) {
+  int64_t d = thread_doc();
+  if (d < n) body_final_len(rs0, re0, rs, re, rewritten, len, d);
+}
+// single-block exclusive scan over the documents of a chunk (not a hot kernel)
+__global__ void k_scan_i64(const int64_t* in, int64_t* out, int64_t n) {
+  __shared__ int64_t s_w[32];
+  __shared__ int64_t s_carry;
+  int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  if (threadIdx.x == 0) s_carry = 0;
+  __syncthreads();
+  for (int64_t base = 0; base < n; base += blockDim.x) {
+    int64_t i = base + threadIdx.x;
+    int64_t v = i < n ? in[i] : 0, x = v;
+    for (int o = 1; o < 32; o <<= 1) { int64_t y = __shfl_up_sync(0xFFFFFFFFu, x, o); if (lane >= o) x += y; }
+    if (lane == 31) s_w[wid] = x;
+    __syncthreads();
+    if (wid == 0) {
+      int64_t w = lane < (int)(blockDim.x >> 5) ? s_w[lane] : 0, y = w;
+      for (int o = 1; o < 32; o <<= 1) { int64_t z = __shfl_up_sync(0xFFFFFFFFu, y, o); if (lane >= o) y += z; }
+      s_w[lane] = y - w;
+    }
+    __syncthreads();
+    int64_t carry = s_carry;
+    if (i < n) out[i] = carry + s_w[wid] + x - v;
+    __syncthreads();
+    if (threadIdx.x == blockDim.x - 1) s_carry = carry + s_w[wid] + x;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) out[n] = s_carry;
+}
+__global__ void __launch_bounds__(TB_BLOCK) k_pack(int64_t n, const uint8_t* orig, const int64_t* rs0, const uint8_t* cur,
+                                                   const int64_t* rs, const uint8_t* rewritten, const int64_t* out_off,
+                                                   uint8_t* out) {
+  int64_t d = warp_doc();
+  if (d < n) body_pack(orig, rs0, cur, rs, rewritten, out_off, out, d, threadIdx.x & 31);
+}
+
+inline int blocks_for_warps(int64_t n) { return (int)((n * 32 + TB_BLOCK - 1) / TB_BLOCK); }
+inline int blocks_for_threads(int64_t n) { return (int)((n + 255) / 256); }
+
+}  // namespace
+
+void tb_launch_init_ranges(cudaStream_t st, const void* off, int off64, int64_t doc0, int64_t n, int64_t base,
+                           int64_t* rs, int64_t* re, uint8_t* alive, int8_t* failed) {
+  if (n) k_init_ranges<<<blocks_for_threads(n), 256, 0, st>>>(off, off64, doc0, n, base, rs, re, alive, failed);
+}
+void tb_launch_validate_utf8(cudaStream_t st, const uint8_t* text, const int64_t* rs, const int64_t* re, int64_t n,
+                             int32_t* bad) {
+  if (n) k_validate_utf8<<<blocks_for_warps(n), TB_BLOCK, 0, st>>>(text, rs, re, n, bad);
+}
+void tb_launch_gq(cudaStream_t st, const KBatch& b, const SwTable& sw, const GqCfg& cfg, int step, tb_gq_stats* out) {
+  if (b.n) k_gq<<<blocks_for_warps(b.n), TB_BLOCK, 0, st>>>(b, sw, cfg, step, out);
+}
+void tb_launch_trim(cudaStream_t st, const KBatch& b, int64_t* ts, int64_t* te) {
+  if (b.n) k_trim<<<blocks_for_threads(b.n), 256, 0, st>>>(b, ts, te);
+}
+void tb_launch_gr_scan(cudaStream_t st, const KBatch& b, const int64_t* ts, const int64_t* te, const GrScratch& s) {
+  if (b.n) k_gr_scan<<<blocks_for_warps(b.n), TB_BLOCK, 0, st>>>(b, ts, te, s);
+}
+void tb_launch_gr_rep(cudaStream_t st, const KBatch& b, const int64_t* ts, const int64_t* te, const GrScratch& s,
+                      const GrCfg& cfg, int step, tb_gr_stats* out) {
+  if (b.n) k_gr_rep<<<blocks_for_warps(b.n), TB_BLOCK, 0, st>>>(b, ts, te, s, cfg, step, out);
+}
+void tb_launch_c4_a(cudaStream_t st, const KBatch& b, const C4Cfg& cfg, const C4Scratch& s) {
+  if (b.n) k_c4_a<<<blocks_for_warps(b.n), TB_BLOCK, 0, st>>>(b, cfg, s);
+}
+void tb_launch_c4_b(cudaStream_t st, const KBatch& b, const C4Cfg& cfg, const C4Scratch& s) {
+  if (b.n) k_c4_b<<<blocks_for_warps(b.n), TB_BLOCK, 0, st>>>(b, cfg, s);
+}
+void tb_launch_c4_c(cudaStream_t st, const KBatch& b, const C4Cfg& cfg, const C4Scratch& s) {
+  if (b.n) k_c4_c<<<blocks_for_warps(b.n), TB_BLOCK, 0, st>>>(b, cfg, s);
+}
+void tb_launch_c4_d(cudaStream_t st, const KBatch& b, const C4Cfg& cfg, const C4Scratch& s, int step, tb_c4_stats* out,
+                    uint8_t* rewritten) {
+  // the new ranges are written over the batch's own rs/re (only for documents that were rewritten)
+  if (b.n) k_c4_d<<<blocks_for_warps(b.n), TB_BLOCK, 0, st>>>(b, cfg, s, step, out, rewritten, (int64_t*)b.rs, (int64_t*)b.re);
+}
+void tb_launch_final_len(cudaStream_t st, int64_t n, const int64_t* rs0, const int64_t* re0, const int64_t* rs,
+                         const int64_t* re, const uint8_t* rewritten, int64_t* len) {
+  if (n) k_final_len<<<blocks_for_threads(n), 256, 0, st>>>(n, rs0, re0, rs, re, rewritten, len);
+}
+void tb_launch_scan_i64(cudaStream_t st, const int64_t* in, int64_t* out, int64_t n) {
+  k_scan_i64<<<1, 1024, 0, st>>>(in, out, n);
+}
+void tb_launch_pack(cudaStream_t st, int64_t n, const uint8_t* orig, const int64_t* rs0, const uint8_t* cur,
+                    const int64_t* rs, const uint8_t* rewritten, const int64_t* out_off, uint8_t* out) {
+  if (n) k_pack<<<blocks_for_warps(n), TB_BLOCK, 0, st>>>(n, orig, rs0, cur, rs, rewritten, out_off, out);
+}

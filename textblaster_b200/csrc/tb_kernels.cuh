@@ -1,0 +1,93 @@
+// tb_kernels.cuh -- device-side parameter blocks and host launch prototypes (internal).
+#pragma once
+#include <stdint.h>
+#if defined(TB_HOST_EMUL)
+typedef void* cudaStream_t;  // host emulation harness (tests/host_emul): no CUDA runtime
+#else
+#include <cuda_runtime.h>
+#endif
+
+#include "../../include/textblaster_b200.h"
+#include "tb_lanes.cuh"
+
+// Current view of the batch chunk on the device.
+struct KBatch {
+  const uint8_t* text;   // buffer the ranges index into
+  const int64_t* rs;     // [n] range start (sot)
+  const int64_t* re;     // [n] range end (eot)
+  uint8_t* alive;        // [n] 1 while the document is still in the pipeline
+  int8_t* failed;        // [n] index of the step that filtered it, -1
+  int64_t n;
+  UcTables uc;
+};
+
+struct GqCfg {
+  uint32_t has;
+  uint64_t min_doc_words, max_doc_words, min_stop_words;
+  double min_avg_word_length, max_avg_word_length, max_symbol_word_ratio, max_bullet_lines_ratio,
+      max_ellipsis_lines_ratio, max_non_alpha_words_ratio;
+};
+
+struct GrCfg {
+  uint32_t has;
+  int32_t n_top, n_dup;
+  double dup_line_frac, dup_para_frac, dup_line_char_frac, dup_para_char_frac;
+  uint32_t top_n[TB_MAX_NGRAMS];
+  double top_frac[TB_MAX_NGRAMS];
+  uint32_t dup_n[TB_MAX_NGRAMS];
+  double dup_frac[TB_MAX_NGRAMS];
+};
+
+// per-document result of the repetition scan pass
+struct GrDoc {
+  uint64_t char_len;
+  uint32_t W, NL, flags, empty;
+};
+
+// scratch of the repetition filter; all arrays are indexed from ubase(d) = (rs[d] >> 1) + d units
+struct GrScratch {
+  uint64_t* wh; uint32_t* wl;               // words: hash, byte length
+  uint64_t* lh; uint32_t* ll; uint8_t* lg;  // line pieces: hash, byte length, "preceded by >= 2 newlines"
+  GrDoc* doc;                               // [n]
+  uint32_t* work;                           // rep work area, K words per unit + TB_REP_DOC_EXTRA per doc
+  uint32_t K;
+};
+#define TB_REP_DOC_EXTRA 20u  // words: 16 (minimum table) + 2 (woff tail) + pad
+#define TB_REP_MIN_TABLE 16u
+#define TB_REP_SMEM_TABLE 1024u
+
+// scratch of the C4 filter
+struct C4Scratch {
+  uint8_t* P;          // processed lines, doc d at [rs0[d], rs0[d] + plen[d])
+  uint8_t* F;          // final content, doc d inside [rs0[d], ...)
+  int64_t* plen;       // [n]
+  uint32_t* nlines;    // [n] lines of the original content
+  uint32_t* docflags;  // [n] C4F_*
+  uint32_t* lwc;       // per line: word count          (indexed rs0[d] + d + line)
+  uint32_t* lmax;      // per line: longest word, chars
+  uint32_t* lflags;    // per line: C4L_*
+  int64_t* prs; int64_t* pre;   // [n] ranges of P
+  int64_t* frs; int64_t* fre;   // [n] ranges of F (untrimmed), then trimmed in place
+  uint32_t* cnt;       // [n][4] too_long_word, no_terminal_punc, too_few_words, kept
+};
+
+void tb_launch_init_ranges(cudaStream_t st, const void* off, int off64, int64_t doc0, int64_t n, int64_t base,
+                           int64_t* rs, int64_t* re, uint8_t* alive, int8_t* failed);
+void tb_launch_gq(cudaStream_t st, const KBatch& b, const SwTable& sw, const GqCfg& cfg, int step, tb_gq_stats* out);
+void tb_launch_trim(cudaStream_t st, const KBatch& b, int64_t* ts, int64_t* te);
+void tb_launch_gr_scan(cudaStream_t st, const KBatch& b, const int64_t* ts, const int64_t* te, const GrScratch& s);
+void tb_launch_gr_rep(cudaStream_t st, const KBatch& b, const int64_t* ts, const int64_t* te, const GrScratch& s,
+                      const GrCfg& cfg, int step, tb_gr_stats* out);
+void tb_launch_c4_a(cudaStream_t st, const KBatch& b, const C4Cfg& cfg, const C4Scratch& s);
+void tb_launch_c4_b(cudaStream_t st, const KBatch& b, const C4Cfg& cfg, const C4Scratch& s);
+void tb_launch_c4_c(cudaStream_t st, const KBatch& b, const C4Cfg& cfg, const C4Scratch& s);
+void tb_launch_c4_d(cudaStream_t st, const KBatch& b, const C4Cfg& cfg, const C4Scratch& s, int step, tb_c4_stats* out,
+                    uint8_t* rewritten);
+void tb_launch_validate_utf8(cudaStream_t st, const uint8_t* text, const int64_t* rs, const int64_t* re, int64_t n,
+                             int32_t* bad);
+// final content: lengths -> exclusive scan -> packed copy
+void tb_launch_final_len(cudaStream_t st, int64_t n, const int64_t* rs0, const int64_t* re0, const int64_t* rs,
+                         const int64_t* re, const uint8_t* rewritten, int64_t* len);
+void tb_launch_scan_i64(cudaStream_t st, const int64_t* in, int64_t* out, int64_t n);  // out[n] = total
+void tb_launch_pack(cudaStream_t st, int64_t n, const uint8_t* orig, const int64_t* rs0, const uint8_t* cur,
+                    const int64_t* rs, const uint8_t* rewritten, const int64_t* out_off, uint8_t* out);

@@ -1,0 +1,110 @@
+// tb_sentmachine.cuh -- per-lane UAX #29 sentence segmentation, counting the non-empty trimmed
+// pieces that split_into_sentences returns (/root/reference src/utils/text.rs:59-101; consumed by
+// C4QualityFilter only through .len(), src/pipeline/filters/c4_filters.rs:261-262).
+//
+// Same ownership scheme as tb_wordmachine.cuh: the lane owning [p0, p1) counts the sentence
+// segments that START in its stretch and contain at least one non-White_Space character.
+#pragma once
+#include "tb_common.cuh"
+
+#define SB_PARASEPMASK (BIT(SB_SEP) | BIT(SB_CR) | BIT(SB_LF))
+#define SB_SATERMMASK (BIT(SB_STERM) | BIT(SB_ATERM))
+#define SB_EFMASK (BIT(SB_EXTEND) | BIT(SB_FORMAT))
+// after one of these the rules need no older context
+#define SB_NOSYNCMASK (SB_SATERMMASK | BIT(SB_CLOSE) | BIT(SB_SP) | SB_EFMASK)
+
+struct SbState {
+  uint32_t prev, l1;
+  uint32_t st;  // 0 none; 1 ATerm; 2 ATerm Close+; 3 ATerm Close* Sp+; 4 STerm; 5 STerm Close+; 6 STerm Close* Sp+
+  uint32_t before_letter;  // (Upper|Lower) immediately before the ATerm (SB7)
+  TB_HD void reset() { prev = SB_SOT; l1 = SB_SOT; st = 0; before_letter = 0; }
+};
+
+// SB8 look-ahead: skip  not(OLetter|Upper|Lower|ParaSep|SATerm)  then require Lower
+TB_HD bool sb_lower_ahead(const Classifier& C, const TextRange& R, int64_t pos) {
+  const uint32_t stop = BIT(SB_OLETTER) | BIT(SB_UPPER) | BIT(SB_LOWER) | SB_PARASEPMASK | SB_SATERMMASK;
+  while (pos < R.re) {
+    int len; uint32_t cp;
+    uint32_t c = CI_SB(C.at(R.t, pos, &len, &cp));
+    if (BIT(c) & stop) return c == SB_LOWER;
+    pos += len;
+  }
+  return false;
+}
+
+TB_HD bool sb_break_before(const Classifier& C, const TextRange& R, const SbState& s, uint32_t cls, int64_t i) {
+  if (s.prev == SB_SOT) return true;                                   // SB1
+  if (s.prev == SB_CR && cls == SB_LF) return false;                   // SB3
+  if (BIT(s.prev) & SB_PARASEPMASK) return true;                       // SB4
+  uint32_t mb = BIT(cls);
+  if (mb & SB_EFMASK) return false;                                    // SB5
+  uint32_t st = s.st;
+  if (st == 0) return false;                                           // SB998
+  if (st == 1 && cls == SB_NUMERIC) return false;                      // SB6
+  if (st == 1 && s.before_letter && cls == SB_UPPER) return false;     // SB7
+  if (st <= 3 && sb_lower_ahead(C, R, i)) return false;                // SB8
+  if (mb & (BIT(SB_SCONTINUE) | SB_SATERMMASK)) return false;          // SB8a
+  if ((st == 1 || st == 2 || st == 4 || st == 5) && (mb & (BIT(SB_CLOSE) | BIT(SB_SP) | SB_PARASEPMASK))) return false;  // SB9
+  if (mb & (BIT(SB_SP) | SB_PARASEPMASK)) return false;                // SB10
+  return true;                                                         // SB11
+}
+
+TB_HD void sb_advance(SbState& s, uint32_t cls) {
+  bool ignored = (BIT(cls) & SB_EFMASK) && s.prev != SB_SOT && !(BIT(s.prev) & SB_PARASEPMASK);
+  if (!ignored) {
+    if (cls == SB_ATERM) { s.before_letter = (s.l1 == SB_UPPER || s.l1 == SB_LOWER); s.st = 1; }
+    else if (cls == SB_STERM) s.st = 4;
+    else if (cls == SB_CLOSE && (s.st == 1 || s.st == 2 || s.st == 4 || s.st == 5)) s.st = s.st < 4 ? 2 : 5;
+    else if (cls == SB_SP && s.st != 0) s.st = s.st < 4 ? 3 : 6;
+    else s.st = 0;
+    s.l1 = cls;
+  }
+  s.prev = cls;
+}
+
+TB_HD void sb_sync(const Classifier& C, const TextRange& R, int64_t q, SbState& s) {
+  s.reset();
+  if (q <= R.rs) return;
+  int64_t j = q;
+  for (;;) {
+    j = C.prev_lead(R.t, j, R.rs);
+    int len; uint32_t cp;
+    uint32_t cls = CI_SB(C.at(R.t, j, &len, &cp));
+    if (j <= R.rs) break;
+    if (!(BIT(cls) & SB_NOSYNCMASK)) break;
+  }
+  while (j < q) {
+    int len; uint32_t cp;
+    uint32_t cls = CI_SB(C.at(R.t, j, &len, &cp));
+    sb_advance(s, cls);
+    j += len;
+  }
+}
+
+// Number of sentence pieces (non-empty after trim) whose segment starts in [p0, p1).
+TB_HD uint32_t tb_count_sentences(const Classifier& C, const TextRange& R, int64_t p0, int64_t p1) {
+  const uint8_t* t = R.t;
+  int64_t q = p0;
+  if (q > R.rs) while (q < R.re && tb_is_cont(tb_byte(t, q))) q++;
+  if (q >= p1 || q >= R.re) return 0;
+  SbState s;
+  sb_sync(C, R, q, s);
+  uint32_t count = 0;
+  bool open = false;  // we own a segment in which no non-whitespace was seen yet
+  int64_t i = q;
+  while (i < R.re) {
+    int len; uint32_t cp;
+    uint32_t ci = C.at(t, i, &len, &cp);
+    uint32_t cls = CI_SB(ci);
+    if (sb_break_before(C, R, s, cls, i)) {
+      if (i >= p1) break;
+      open = true;
+    } else if (!open && i >= p1) {
+      break;
+    }
+    if (open && !(ci & CI_WS)) { count++; open = false; }
+    sb_advance(s, cls);
+    i += len;
+  }
+  return count;
+}

@@ -1,0 +1,112 @@
+// tb_simt.cuh -- the handful of warp-level primitives the kernel bodies use.
+//
+// Device build: thin wrappers over the CUDA intrinsics (full-warp masks only).
+// TB_HOST_EMUL build (tests/host_emul, test infrastructure only, never linked into the shipped
+// library): 32 host threads play the lanes of one warp; every collective is a barrier plus an
+// exchange through a small per-warp mailbox, atomics are GCC builtins.  This lets the exact kernel
+// bodies run against the oracle on a machine without a GPU.
+#pragma once
+#include <stdint.h>
+
+#include "tb_common.cuh"
+
+#if !defined(TB_HOST_EMUL)
+
+#define SIMT_FULL 0xFFFFFFFFu
+TB_D uint32_t simt_shfl(uint32_t v, int src) { return __shfl_sync(SIMT_FULL, v, src); }
+TB_D uint64_t simt_shfl(uint64_t v, int src) { return __shfl_sync(SIMT_FULL, v, src); }
+TB_D uint32_t simt_shfl_up(uint32_t v, int o) { return __shfl_up_sync(SIMT_FULL, v, o); }
+TB_D uint64_t simt_shfl_xor(uint64_t v, int o) { return __shfl_xor_sync(SIMT_FULL, v, o); }
+TB_D uint32_t simt_sum(uint32_t v) { return __reduce_add_sync(SIMT_FULL, v); }
+TB_D uint32_t simt_or(uint32_t v) { return __reduce_or_sync(SIMT_FULL, v); }
+TB_D bool simt_any(bool p) { return __any_sync(SIMT_FULL, p) != 0; }
+TB_D void simt_sync() { __syncwarp(); }
+TB_D uint32_t simt_cas(uint32_t* a, uint32_t cmp, uint32_t val) { return atomicCAS(a, cmp, val); }
+TB_D uint32_t simt_atomic_add(uint32_t* a, uint32_t v) { return atomicAdd(a, v); }
+TB_D uint32_t simt_atomic_min(uint32_t* a, uint32_t v) { return atomicMin(a, v); }
+TB_D uint32_t simt_atomic_max(uint32_t* a, uint32_t v) { return atomicMax(a, v); }
+TB_D uint32_t simt_atomic_or(uint32_t* a, uint32_t v) { return atomicOr(a, v); }
+TB_D int simt_popc(uint32_t v) { return __popc(v); }
+TB_D int simt_ffs(uint32_t v) { return __ffs(v); }
+
+#else  // ---------------------------------------------------------------- host emulation
+
+#include <barrier>
+#include <cstring>
+
+struct SimtWarp {
+  std::barrier<> bar{32};
+  uint64_t box[32];
+};
+extern thread_local SimtWarp* simt_warp;
+extern thread_local int simt_lane;
+
+inline uint64_t simt_exchange_(uint64_t v, int src_lane, bool valid) {
+  SimtWarp* w = simt_warp;
+  w->box[simt_lane] = v;
+  w->bar.arrive_and_wait();
+  uint64_t r = valid ? w->box[src_lane] : v;
+  w->bar.arrive_and_wait();
+  return r;
+}
+inline uint32_t simt_shfl(uint32_t v, int src) { return (uint32_t)simt_exchange_(v, src & 31, true); }
+inline uint64_t simt_shfl(uint64_t v, int src) { return simt_exchange_(v, src & 31, true); }
+inline uint32_t simt_shfl_up(uint32_t v, int o) { return (uint32_t)simt_exchange_(v, simt_lane - o, simt_lane - o >= 0); }
+inline uint64_t simt_shfl_xor(uint64_t v, int o) { return simt_exchange_(v, simt_lane ^ o, true); }
+inline uint32_t simt_sum(uint32_t v) {
+  SimtWarp* w = simt_warp;
+  w->box[simt_lane] = v;
+  w->bar.arrive_and_wait();
+  uint32_t s = 0;
+  for (int i = 0; i < 32; i++) s += (uint32_t)w->box[i];
+  w->bar.arrive_and_wait();
+  return s;
+}
+inline uint32_t simt_or(uint32_t v) {
+  SimtWarp* w = simt_warp;
+  w->box[simt_lane] = v;
+  w->bar.arrive_and_wait();
+  uint32_t s = 0;
+  for (int i = 0; i < 32; i++) s |= (uint32_t)w->box[i];
+  w->bar.arrive_and_wait();
+  return s;
+}
+inline bool simt_any(bool p) { return simt_or(p ? 1u : 0u) != 0; }
+inline void simt_sync() { simt_warp->bar.arrive_and_wait(); }
+inline uint32_t simt_cas(uint32_t* a, uint32_t cmp, uint32_t val) {
+  __atomic_compare_exchange_n(a, &cmp, val, false, __ATOMIC_SEQ_CST, __ATOMIC_SEQ_CST);
+  return cmp;
+}
+inline uint32_t simt_atomic_add(uint32_t* a, uint32_t v) { return __atomic_fetch_add(a, v, __ATOMIC_SEQ_CST); }
+inline uint32_t simt_atomic_or(uint32_t* a, uint32_t v) { return __atomic_fetch_or(a, v, __ATOMIC_SEQ_CST); }
+inline uint32_t simt_atomic_min(uint32_t* a, uint32_t v) {
+  uint32_t old = __atomic_load_n(a, __ATOMIC_SEQ_CST);
+  while (v < old && !__atomic_compare_exchange_n(a, &old, v, false, __ATOMIC_SEQ_CST, __ATOMIC_SEQ_CST)) {}
+  return old;
+}
+inline uint32_t simt_atomic_max(uint32_t* a, uint32_t v) {
+  uint32_t old = __atomic_load_n(a, __ATOMIC_SEQ_CST);
+  while (v > old && !__atomic_compare_exchange_n(a, &old, v, false, __ATOMIC_SEQ_CST, __ATOMIC_SEQ_CST)) {}
+  return old;
+}
+inline int simt_popc(uint32_t v) { return __builtin_popcount(v); }
+inline int simt_ffs(uint32_t v) { return __builtin_ffs((int)v); }
+
+#endif
+
+// ---- composite helpers (same code on both builds) --------------------------------------------
+TB_D uint64_t simt_sum64(uint64_t v) {
+  for (int o = 16; o; o >>= 1) v += simt_shfl_xor(v, o);
+  return v;
+}
+TB_D uint64_t simt_max64(uint64_t v) {
+  for (int o = 16; o; o >>= 1) { uint64_t x = simt_shfl_xor(v, o); v = x > v ? x : v; }
+  return v;
+}
+// exclusive prefix sum across the warp; *total gets the warp sum
+TB_D uint32_t simt_exscan(uint32_t v, int lane, uint32_t* total) {
+  uint32_t x = v;
+  for (int o = 1; o < 32; o <<= 1) { uint32_t y = simt_shfl_up(x, o); if (lane >= o) x += y; }
+  *total = simt_shfl(x, 31);
+  return x - v;
+}
