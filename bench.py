@@ -1,0 +1,320 @@
+#!/usr/bin/env python3
+"""bench.py -- docs/s and text GB/s through the C4 + Gopher filter chain (BASELINE.json metric).
+
+Workload (BASELINE.json configs[1]): C4QualityFilter + GopherQualityFilter + GopherRepetitionFilter
+over 1,000,000 synthetic C4-shaped documents (~2 KB median, log-normal) per GPU.  One "step" is one
+pass of the whole chain over that batch.  Two measurements per run:
+
+  value : inputs already resident in HBM (tb_pipeline_run_batch_device), results copied back;
+  e2e   : the call a user makes (tb_pipeline_run_batch) on pinned HOST buffers -- H2D of the text
+          and offsets and D2H of keep mask / statistics / rewritten content inside the timed region.
+
+N > 1 (torchrun): documents are sharded across ranks (weak scaling: 1M docs per GPU), no data-path
+collective -- the path is embarrassingly parallel; NCCL is used only for the timing barrier / max.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--docs D] [--impl reference]
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+import numpy as np  # noqa: E402
+
+METRIC = "docs/s through C4+Gopher filter chain"
+UNIT = "docs/s"
+
+
+def shipped_chain():
+    """BASELINE.json configs[1] order (C4 -> GopherQuality -> GopherRepetition), parameters of the
+    reference's config/pipeline_config.yaml:6-32,56-66 with the default English stop words."""
+    from textblaster_b200.config import C4QualityParams, GopherQualityParams, GopherRepetitionParams
+
+    c4 = C4QualityParams(True, True, True, 5, 3, 1000, True, True, True, True)
+    gq = GopherQualityParams(min_doc_words=50, max_doc_words=100000, min_avg_word_length=3.0, max_avg_word_length=10.0,
+                             max_symbol_word_ratio=0.1, max_bullet_lines_ratio=0.9, max_ellipsis_lines_ratio=0.3,
+                             max_non_alpha_words_ratio=0.8, min_stop_words=2)
+    gr = GopherRepetitionParams(dup_line_frac=0.3, dup_para_frac=0.3, dup_line_char_frac=0.2, dup_para_char_frac=0.2,
+                                top_n_grams=[(2, 0.2), (3, 0.18), (4, 0.16)],
+                                dup_n_grams=[(5, 0.15), (6, 0.14), (7, 0.13), (8, 0.12), (9, 0.11), (10, 0.10)])
+    return [c4, gq, gr]
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index = index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "200"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, smax, reasons = [], [], set()
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0]))
+                smax.append(float(f[1]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(smax) if smax else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def ncu_traffic(kernel):
+    """dram bytes per launch of the dominant kernel from the committed ncu capture, if any."""
+    p = os.path.join(ROOT, "profiles", "roofline_traffic.json")
+    if os.path.exists(p):
+        try:
+            return json.load(open(p)).get(kernel)
+        except Exception:
+            return None
+    return None
+
+
+def cpu_baseline(utf8, off, steps, budget_s=12.0, threads=None):
+    """The oracle (C++ restatement of the reference CPU chain, kind "port") timed on this box's host
+    cores on a bounded sample of the same workload."""
+    import oracle
+
+    threads = threads or (os.cpu_count() or 1)
+    pl = oracle.OraclePipeline(steps)
+    n = len(off) - 1
+    probe = min(n, 2000)
+    t0 = time.perf_counter()
+    pl.run_packed(utf8[off[0]:off[probe]], off[:probe + 1] - off[0], nthreads=threads)
+    rate = probe / max(time.perf_counter() - t0, 1e-6)
+    sample = int(min(n, max(probe, rate * budget_s)))
+    t0 = time.perf_counter()
+    r = pl.run_packed(utf8[off[0]:off[sample]], off[:sample + 1] - off[0], nthreads=threads)
+    dt = time.perf_counter() - t0
+    nbytes = int(off[sample] - off[0])
+    return {"value": sample / dt, "unit": UNIT, "cores": threads, "kind": "port",
+            "sample": f"first {sample} docs ({nbytes / 1e6:.1f} MB) of the workload, {dt:.2f} s, oracle/tb_oracle.cpp with {threads} threads",
+            "text_gbs": nbytes / dt / 1e9, "keep_rate": float(r.keep.mean()) if sample else None}
+
+
+def run_reference(args, rank, world):
+    """--impl reference: the reference's own CPU implementation is Rust + ICU4X and cannot be built in
+    this image (no cargo/rustc), so this arm times the oracle port on all host threads."""
+    if rank != 0:
+        return
+    from textblaster_b200 import synth
+
+    steps = shipped_chain()
+    threads = os.cpu_count() or 1
+    import oracle
+
+    pl = oracle.OraclePipeline(steps)
+    probe_u, probe_o = synth.generate(2000, seed=synth.BASE_SEED + 2)
+    t0 = time.perf_counter()
+    pl.run_packed(probe_u, probe_o, nthreads=threads)
+    rate = 2000 / max(time.perf_counter() - t0, 1e-6)
+    total_steps = args.steps + args.warmup
+    sample = int(max(2000, min(args.docs, rate * min(20.0, 150.0 / max(total_steps, 1)))))
+    utf8, off = synth.generate(sample, seed=synth.BASE_SEED + 2)
+    for _ in range(args.warmup):
+        pl.run_packed(utf8, off, nthreads=threads)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        r = pl.run_packed(utf8, off, nthreads=threads)
+    dt = (time.perf_counter() - t0) / max(args.steps, 1)
+    v = sample / dt
+    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "u8", "data": "synthetic",
+            "config": {"workload": "C4QualityFilter+GopherQualityFilter+GopherRepetitionFilter chain, synthetic C4-shaped docs (~2 KB median)",
+                       "docs_per_step": sample, "bytes_per_step": int(off[-1]), "note": "bounded sample of the 1M-doc workload"},
+            "text_gbs": float(off[-1]) / dt / 1e9,
+            "cpu_baseline": {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
+                             "sample": f"{sample} docs ({off[-1] / 1e6:.1f} MB) per step, C++ restatement of the reference CPU chain (the Rust reference cannot be built here)"},
+            "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "keep_rate": float(r.keep.mean())}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--docs", type=int, default=1_000_000, help="documents per GPU per step")
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--chunk-mb", type=int, default=256)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 0)
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+
+    import torch
+    import torch.distributed as dist
+
+    from textblaster_b200 import _abi, synth
+    from textblaster_b200.executor import GpuBatchPipeline
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (no CPU fallback); use --impl reference for the CPU arm")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- synthetic shard of this rank, generated straight into pinned host memory
+    holder = {}
+
+    def alloc(nbytes):
+        holder["t"] = torch.empty(max(nbytes, 1), dtype=torch.uint8, pin_memory=True)
+        return holder["t"].numpy()
+
+    t_gen = time.perf_counter()
+    utf8, off = synth.generate(args.docs, seed=synth.BASE_SEED + 2, first_index=rank * args.docs, out=alloc)
+    off_t = torch.from_numpy(off).pin_memory()
+    off = off_t.numpy()
+    n_docs, n_bytes = args.docs, int(off[-1])
+    t_gen = time.perf_counter() - t_gen
+    steps = shipped_chain()
+    pipe = GpuBatchPipeline(steps, device=local_rank)
+    pipe.set_option(_abi.TB_OPT_CHUNK_BYTES, args.chunk_mb << 20)
+    d_text = holder["t"].cuda(non_blocking=False)
+    d_off = off_t.cuda()
+    out = _abi.tb_batch_out()
+
+    def step_device():
+        pipe.run_device_raw(d_text.data_ptr(), d_off.data_ptr(), n_docs, n_bytes, out)
+        r = (out.gpu_launches, out.gpu_ms, int(np.ctypeslib.as_array(out.keep, (n_docs,)).sum()) if n_docs else 0, int(out.content_bytes))
+        pipe.release(out)
+        return r
+
+    def step_host():
+        pipe.run_raw(utf8.ctypes.data, off.ctypes.data, True, n_docs, out)
+        r = (out.gpu_launches, out.gpu_ms, int(np.ctypeslib.as_array(out.keep, (n_docs,)).sum()) if n_docs else 0, int(out.content_bytes))
+        pipe.release(out)
+        return r
+
+    def timed(fn):
+        for _ in range(args.warmup):
+            fn()
+        pipe.reset_kernel_times()
+        barrier()
+        sampler = ClockSampler(local_rank)
+        sampler.start()
+        launches = 0
+        gpu_ms = 0.0
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            l, ms, kept, cbytes = fn()
+            launches += l
+            gpu_ms += ms
+        barrier()
+        dt = time.perf_counter() - t0
+        clocks = sampler.stop()
+        t = torch.tensor([dt], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item()), launches, gpu_ms, kept, cbytes, clocks, pipe.kernel_times()
+
+    dt_dev, launches, gpu_ms, kept, cbytes, clocks, ktimes = timed(step_device)
+    dt_e2e, launches_e, gpu_ms_e, _, _, clocks_e, _ = timed(step_host)
+
+    if rank == 0:
+        K = max(args.steps, 1)
+        value = world * n_docs * K / dt_dev
+        e2e = world * n_docs * K / dt_e2e
+        # roofline of the dominant kernel (device-resident run)
+        dom = max(ktimes.items(), key=lambda kv: kv[1][0]) if ktimes else ("", (0.0, 0))
+        dom_name, (dom_ms, dom_launches) = dom
+        alg_bytes_step = n_bytes + 8 * (n_docs + 1) + 16 * n_docs  # text once + i64 offsets + minimal per-doc output
+        launches_per_step = max(dom_launches / K, 1)
+        alg_bytes_launch = alg_bytes_step / launches_per_step
+        avg_ms = dom_ms / max(dom_launches, 1)
+        achieved = alg_bytes_launch / (avg_ms * 1e-3) / 1e9 if avg_ms > 0 else 0.0
+        peak, peak_src = measured_peaks()
+        stats_bytes = sum(C.sizeof(_abi.STATS_STRUCT[p.CTYPE]) for p in steps)
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": dt_dev / K * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "u8", "data": "synthetic",
+            "config": {"workload": "C4QualityFilter+GopherQualityFilter+GopherRepetitionFilter chain, 1M synthetic C4-shaped docs (~2 KB median) per GPU (BASELINE.json configs[1])",
+                       "docs_per_gpu_per_step": n_docs, "bytes_per_gpu_per_step": n_bytes, "sharding": "documents by rank, no collective",
+                       "chunk_mb": args.chunk_mb, "l2": "inputs (%.2f GB per step) larger than the 126 MB L2" % (n_bytes / 1e9),
+                       "generator_s": round(t_gen, 2)},
+            "text_gbs": world * n_bytes * K / dt_dev / 1e9,
+            "gpu_ms_per_step": gpu_ms / K, "keep_rate": kept / max(n_docs, 1),
+            "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": n_bytes + 8 * (n_docs + 1),
+                    "d2h_bytes_per_step": n_docs * (2 + stats_bytes) + cbytes + 8 * (n_docs + 1), "text_gbs": world * n_bytes * K / dt_e2e / 1e9,
+                    "ms_per_step": dt_e2e / K * 1e3},
+            "gpu_launches": launches,
+            "roofline": {"bound": "hbm", "kernel": dom_name, "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": achieved / peak if peak else None, "traffic": ncu_traffic(dom_name), "peak_source": peak_src,
+                         "algorithmic_bytes_per_launch": alg_bytes_launch, "avg_launch_ms": avg_ms,
+                         "share_of_gpu_time": dom_ms / max(sum(v[0] for v in ktimes.values()), 1e-9)},
+            "kernels_ms_per_step": {k: round(v[0] / K, 3) for k, v in sorted(ktimes.items(), key=lambda kv: -kv[1][0])},
+            "clocks": clocks,
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            line["cpu_baseline"] = cpu_baseline(utf8, off, steps)
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

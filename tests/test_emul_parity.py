@@ -1,0 +1,56 @@
+"""CPU check of the kernel logic: the exact warp bodies of the CUDA kernels, run by the host emulation
+harness (tests/host_emul), against the oracle -- bit-exact counters, decisions and rewritten content.
+The real kernels are checked the same way on the GPU in test_gpu_parity.py."""
+import random
+
+import pytest
+
+import _emul
+import fuzzgen
+import oracle
+from parity_cases import CHAINS, step_types
+from parity_util import compare
+from test_oracle_golden import C4_LINE_CASES
+
+GOLDEN_DOCS = [d for d, _ in C4_LINE_CASES] + [
+    "This is fine. Lorem ipsum dolor sit amet.", "code {}.", "", "   \n   ",
+    "One sentence. Two sentences. Three sentences. Four sentences.",
+    "Foo bar baz. [1]\nThis line stays here.", "Keep this line please.\nno punct here\nab.\n",
+    "a b c d e f a b g h i j", "a b c a b d a b e a b", "a b c d e a b f g",
+    "word1 ... word2 … word3 word4 word5 word6 word7 word8", "- item 1\n- item 2\n- item 3\nnormal line",
+    "Line one...\nLine two…\nLine three...\nNormal line", "the quick brown fox and the lazy dog", "Hello world . !",
+    "This is line one.\nThis is line two.\nThis is line one.", "P one.\n\nP two.\n\nP one.", "\n", "\n\n", "a\n", "a\n\n",
+    "x", "#", ". ! ?", "word 123 456 !!!",
+]
+
+
+def _check(name, texts):
+    steps = CHAINS[name]
+    o = oracle.OraclePipeline(steps).run_texts(texts)
+    e = _emul.run_chain(steps, texts)
+    compare(o, e.keep, e.failed_step, e.stats, e.contents, step_types(steps), texts, label=name)
+
+
+@pytest.mark.parametrize("name", sorted(CHAINS))
+def test_golden_documents(name):
+    _check(name, GOLDEN_DOCS)
+
+
+@pytest.mark.parametrize("name", sorted(CHAINS))
+def test_fuzzed_documents(name):
+    _check(name, fuzzgen.FuzzGen(11).docs(120))
+
+
+@pytest.mark.parametrize("name", ["baseline_order", "shipped_order", "c4_then_open", "gr_open", "gq_open"])
+def test_multi_tile_documents(name):
+    rng = random.Random(3)
+    texts = [fuzzgen.english_doc(rng, sz) for sz in (200, 900, 1023, 1024, 1025, 1100, 3000, 8000, 20000)]
+    texts += [fuzzgen.FuzzGen(4).doc(max_lines=80) for _ in range(10)]
+    _check(name, texts)
+
+
+def test_word_spanning_many_tiles():
+    # a single segment longer than several tiles is walked by the lane that owns its first byte
+    texts = ["start " + "a" * 5000 + " end. Another sentence here. And a third one.", "a" * 3000, "é" * 1500 + " x"]
+    for name in ("gq_open", "gr_open", "c4_lax"):
+        _check(name, texts)

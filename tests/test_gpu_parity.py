@@ -1,0 +1,285 @@
+"""GPU parity tests: the CUDA kernels, called through the C ABI (tb_pipeline_run_batch), against the
+CPU oracle on the same inputs.  Bar: every integer counter, keep / failed_step decision, reason bit
+and the rewritten content bit-exact; the f64 ratios are single divisions of those integers, so the
+reason strings are compared verbatim (tolerance: 0).  Nothing here reads /root/reference."""
+import ctypes as C
+import os
+import random
+
+import numpy as np
+import pytest
+
+import fuzzgen
+import multilingual
+import oracle
+from parity_cases import CHAINS, GQ_OPEN, GR_OPEN, step_types
+from parity_util import compare
+from test_emul_parity import GOLDEN_DOCS
+from test_oracle_golden import C4_LINE_CASES, c4_default
+from textblaster_b200 import _abi, synth
+from textblaster_b200.config import GopherRepetitionParams
+from textblaster_b200.data_model import TextDocument
+from textblaster_b200.error import DocumentFiltered, StepError
+from textblaster_b200.executor import (C4QualityFilter, GopherQualityFilter, GopherRepetitionFilter, GpuBatchPipeline,
+                                       PipelineExecutor)
+
+pytestmark = pytest.mark.gpu
+NCPU = os.cpu_count() or 1
+_pipes = {}
+
+
+def pipe(name):
+    if name not in _pipes:
+        _pipes[name] = GpuBatchPipeline(CHAINS[name])
+    return _pipes[name]
+
+
+def check_texts(name, texts, **kw):
+    steps = CHAINS[name]
+    res = pipe(name).run_texts(texts)
+    ores = oracle.OraclePipeline(steps).run_texts(texts, nthreads=NCPU)
+    contents = [res.content_of(i) for i in range(res.n_docs)] if res.content is not None else None
+    compare(ores, res.keep, res.failed_step, res.stats, contents, step_types(steps), texts, label=name)
+    for i in range(0, len(texts), max(1, len(texts) // 50)):  # reason strings + metadata, sampled
+        md, reason = res.metadata_and_reason(i)
+        assert reason == ores.reason(i) and md == ores.metadata(i)
+    return res
+
+
+def check_packed(name, utf8, off, p=None):
+    steps = CHAINS[name]
+    res = (p or pipe(name)).run_packed(utf8, off)
+    ores = oracle.OraclePipeline(steps).run_packed(utf8, off.astype(np.int64), nthreads=NCPU)
+    compare(ores, res.keep, res.failed_step, res.stats, None, step_types(steps), None, label=name)
+    if res.content is not None:
+        ob, oo = ores.content_packed()
+        assert np.array_equal(res.content_offsets, oo) and np.array_equal(res.content, ob)
+    return res, ores
+
+
+def _same_stats(r, ref):
+    """statistics agree on every row whose step executed (later steps are undefined after a failure)"""
+    ran = ref.failed_step.astype(np.int64)
+    for s_i, (x, y) in enumerate(zip(r.stats, ref.stats)):
+        m = (ran < 0) | (ran >= s_i)
+        assert np.array_equal(x[m], y[m])
+
+
+@pytest.mark.parametrize("name", sorted(CHAINS))
+def test_golden_documents(name):
+    check_texts(name, GOLDEN_DOCS)
+
+
+@pytest.mark.parametrize("name", sorted(CHAINS))
+def test_fuzzed_documents(name):
+    check_texts(name, fuzzgen.FuzzGen(101).docs(1500))
+
+
+@pytest.mark.parametrize("name", ["baseline_order", "shipped_order", "c4_then_open", "gr_open", "gq_open"])
+def test_multi_tile_documents(name):
+    rng = random.Random(5)
+    texts = [fuzzgen.english_doc(rng, sz) for sz in (200, 900, 1023, 1024, 1025, 1100, 3000, 8000, 20000, 70000)]
+    texts += fuzzgen.FuzzGen(6).docs(60, max_lines=120)
+    texts += ["start " + "a" * 5000 + " end. Another sentence here. And a third one.", "a" * 3000, "é" * 1500 + " x"]
+    check_texts(name, texts)
+
+
+@pytest.mark.parametrize("name", ["baseline_order", "shipped_order", "c4_then_open"])
+def test_synthetic_c4_corpus(name):
+    """BASELINE.json config 2 shape (2 KB median, log-normal), 20k documents."""
+    utf8, off = synth.generate(20000, seed=synth.BASE_SEED + 2)
+    res, ores = check_packed(name, utf8, off)
+    assert 0 < int(res.keep.sum()) < res.n_docs or name == "shipped_order"
+
+
+def test_int32_offsets_and_chunking():
+    """Arrow StringArray offsets are i32 (parquet_reader.rs:108-112); tiny chunks force the
+    double-buffered multi-chunk path and must not change any result."""
+    utf8, off = synth.generate(3000, seed=11, median_bytes=1200)
+    p = GpuBatchPipeline(CHAINS["baseline_order"])
+    ref, _ = check_packed("baseline_order", utf8, off, p)
+    r32 = p.run_packed(utf8, off.astype(np.int32))
+    p.set_option(_abi.TB_OPT_CHUNK_BYTES, 1 << 16)
+    rch = p.run_packed(utf8, off)
+    for r in (r32, rch):
+        assert np.array_equal(r.keep, ref.keep) and np.array_equal(r.failed_step, ref.failed_step)
+        _same_stats(r, ref)
+        assert np.array_equal(r.content, ref.content) and np.array_equal(r.content_offsets, ref.content_offsets)
+    # a sliced column: offsets[0] != 0
+    k = 500
+    rs = p.run_packed(utf8, off[k:])
+    assert np.array_equal(rs.keep, ref.keep[k:]) and np.array_equal(rs.failed_step, ref.failed_step[k:])
+    p.close()
+
+
+def test_device_resident_entry_point():
+    import torch
+
+    utf8, off = synth.generate(4000, seed=12)
+    p = GpuBatchPipeline(CHAINS["baseline_order"])
+    host = p.run_packed(utf8, off)
+    tu = torch.from_numpy(utf8.copy()).cuda()
+    to = torch.from_numpy(off.copy()).cuda()
+    out = _abi.tb_batch_out()
+    p.run_device_raw(tu.data_ptr(), to.data_ptr(), len(off) - 1, int(off[-1]), out)
+    keep = np.ctypeslib.as_array(out.keep, (out.n_docs,)).copy()
+    failed = np.ctypeslib.as_array(out.failed_step, (out.n_docs,)).copy()
+    nb = int(out.content_bytes)
+    content = np.ctypeslib.as_array(out.content, (nb,)).copy()
+    assert out.gpu_launches > 0
+    p.release(out)
+    assert np.array_equal(keep, host.keep) and np.array_equal(failed, host.failed_step) and np.array_equal(content, host.content)
+    p.close()
+
+
+def test_empty_and_degenerate_batches():
+    p = pipe("baseline_order")
+    r = p.run_packed(np.zeros(0, np.uint8), np.zeros(1, np.int64))
+    assert r.n_docs == 0 and len(r.keep) == 0
+    check_texts("baseline_order", ["", "", ""])
+    check_texts("gr_open", ["", " ", "\n"])
+    check_texts("gq_open", [""])
+
+
+def test_long_documents_ngram_sweep():
+    """BASELINE.json config 3 in miniature: 10-200 KB documents, n = 2..10 for both n-gram lists;
+    the per-document tables exceed shared memory and spill to the global work area."""
+    sweep = GopherRepetitionParams(dup_line_frac=0.3, dup_para_frac=0.3, dup_line_char_frac=0.2, dup_para_char_frac=0.2,
+                                   top_n_grams=[(n, 0.2) for n in range(2, 11)], dup_n_grams=[(n, 0.15) for n in range(2, 11)])
+    rng = random.Random(9)
+    sizes = [int(10_000 * (20 ** rng.random())) for _ in range(60)]
+    texts = [fuzzgen.english_doc(rng, sz) for sz in sizes]
+    p = GpuBatchPipeline([sweep])
+    res = p.run_texts(texts)
+    ores = oracle.OraclePipeline([sweep]).run_texts(texts, nthreads=NCPU)
+    compare(ores, res.keep, res.failed_step, res.stats, None, [_abi.TB_STEP_GOPHER_REPETITION], texts, label="sweep")
+    assert res.stats[0]["n_words"].max() > 10000
+    p.close()
+
+
+@pytest.mark.parametrize("name", ["gq_open", "gq_shipped", "gr_open", "c4_lax", "c4_then_open", "shipped_order"])
+def test_multilingual_stress(name):
+    """BASELINE.json config 5: bit-exact decisions on non-ASCII-heavy text (rule-based scripts)."""
+    check_texts(name, multilingual.corpus(31, 700))
+
+
+def test_complex_script_subset_is_flagged():
+    """Han / Kana / Thai: plain UAX #29 on both sides (bit-exact vs the oracle) and flagged, because
+    ICU4X new_auto() would use dictionary / LSTM data we do not have (declared divergence)."""
+    texts = multilingual.corpus(32, 90, langs=["han", "kana", "thai"])
+    for name in ("gq_open", "gr_open"):
+        res = check_texts(name, texts)
+        assert (res.stats[0]["flags"] & _abi.TB_DOCFLAG_COMPLEX_SCRIPT).all()
+
+
+# ---- the reference's own unit tests, driven through the ProcessingStep mirror -------------------
+def _doc(i, c):
+    return TextDocument(id=i, content=c, source="test_source")
+
+
+def test_c4_step_reference_cases():  # c4_filters.rs:594-790
+    f = C4QualityFilter(True, True, True, 5, 3, 1000, True, True, True, True)
+    assert f.name() == "C4QualityFilter"
+    for text, expected in C4_LINE_CASES:
+        out = f.process(_doc("d", text))
+        assert out.content.strip() == expected and out.metadata["c4_filter_status"] == "passed"
+    with pytest.raises(DocumentFiltered) as e:
+        f.process(_doc("fail_sentences", "One sentence. Two sentences. Three sentences. Four sentences."))
+    assert "too_few_sentences (found 4, required 5)" in e.value.reason
+    assert e.value.document.metadata["c4_filter_status"] == "filtered"
+    with pytest.raises(DocumentFiltered) as e:
+        f.process(_doc("lorem", "This is fine. Lorem ipsum dolor sit amet. This is also fine."))
+    assert e.value.reason == "lorem_ipsum" and e.value.document.content.startswith("This is fine. Lorem")
+    with pytest.raises(DocumentFiltered) as e:
+        f.process(_doc("curly", "This is fine.\nSome code block {}.\nAnother good line."))
+    assert "curly_bracket" in e.value.reason
+
+
+def test_gopher_quality_step_reference_cases():  # gopher_quality.rs:360-829
+    f = GopherQualityFilter(min_doc_words=3)
+    assert f.name() == "GopherQualityFilter"
+    assert f.process(_doc("a", "Hello world test . !")).metadata["gopher_quality_filter_status"] == "passed"
+    with pytest.raises(DocumentFiltered) as e:
+        f.process(_doc("b", "Hello world . !"))
+    assert "gopher_short_doc (2 non-symbol words, required 3)" in e.value.reason
+    f = GopherQualityFilter(min_avg_word_length=3.0, max_avg_word_length=5.0)
+    with pytest.raises(DocumentFiltered) as e:
+        f.process(_doc("c", ". ! ."))
+    assert "gopher_below_avg_threshold (avg len 0.00, required 3.00 - 0 non-symbol words)" in e.value.reason
+    f = GopherQualityFilter(min_stop_words=1, stop_words=["custom", "words"])
+    f.process(_doc("d", "this is a custom test with other words"))
+    with pytest.raises(DocumentFiltered) as e:
+        f.process(_doc("e", "this is a regular sentence"))
+    assert "gopher_too_few_stop_words (found 0, required 1)" in e.value.reason
+
+
+def test_gopher_repetition_step_reference_cases():  # gopher_rep.rs:412-642
+    f = GopherRepetitionFilter(dup_line_frac=0.3)
+    assert f.name() == "GopherRepetitionFilter"
+    with pytest.raises(DocumentFiltered) as e:
+        f.process(_doc("l", "This is line one.\nThis is line two.\nThis is line one."))
+    assert "dup_line_frac (ratio 0.33, max 0.30)" in e.value.reason
+    f = GopherRepetitionFilter(top_n_grams=[(2, 0.3)])
+    f.process(_doc("p", "a b c d e f a b g h i j"))
+    with pytest.raises(DocumentFiltered) as e:
+        f.process(_doc("q", "a b c a b d a b e a b"))
+    assert "top_2_gram (ratio 0.57, max 0.30)" in e.value.reason
+    f = GopherRepetitionFilter(dup_n_grams=[(2, 0.1)])
+    with pytest.raises(DocumentFiltered) as e:
+        f.process(_doc("r", "a b c d e a b f g"))
+    assert "duplicated_2_n_grams (ratio 0.12, max 0.10)" in e.value.reason
+    with pytest.raises(DocumentFiltered) as e:
+        GopherRepetitionFilter().process(_doc("s", "   "))
+    assert e.value.reason == "skipping empty content"
+    assert e.value.document.metadata["gopher_repetition_filter_reason"] == "skipping empty content"
+
+
+def test_fused_executor_short_circuit_and_order():  # executor.rs:30-70
+    steps = [C4QualityFilter(True, True, True, 5, 3, 1000, True, True, True, True), GopherQualityFilter(min_doc_words=20),
+             GopherRepetitionFilter(dup_line_frac=0.3)]
+    ex = PipelineExecutor(steps)
+    good = "This is the first sentence. This is the second sentence. This is the third sentence. This is the fourth sentence. This is the fifth sentence."
+    docs = [_doc("0", "Some code block {}."), _doc("1", "One. Two. Three. Four. Five sentences are here now."), _doc("2", good)]
+    out = ex.run_batch(docs)
+    assert isinstance(out[0], StepError) and out[0].step_name == "C4QualityFilter"
+    assert isinstance(out[1], StepError) and out[1].step_name == "GopherQualityFilter"
+    assert "gopher_quality_filter_status" not in out[0].source.document.metadata
+    assert out[1].source.document.metadata["c4_filter_status"] == "passed"
+    assert "gopher_repetition_filter_status" not in out[1].source.document.metadata
+    assert isinstance(out[2], TextDocument) and out[2].id == "2"
+    assert out[2].metadata == {"c4_filter_status": "passed", "gopher_quality_filter_status": "passed",
+                               "gopher_repetition_filter_status": "passed"}
+    oc = ex.run_outcomes(docs)
+    assert [o.kind for o in oc] == ["Filtered", "Filtered", "Success"]
+
+
+def test_size_independent_properties_at_scale():
+    """Properties that hold at any size (no oracle): determinism, batch-splitting invariance, and
+    idempotence of C4's rewrite on this corpus (a kept document run again is kept unchanged; this
+    holds because the generator never starts a line with a citation)."""
+    utf8, off = synth.generate(60000, seed=synth.BASE_SEED + 4)
+    p = GpuBatchPipeline(CHAINS["baseline_order"])
+    r1 = p.run_packed(utf8, off)
+    r2 = p.run_packed(utf8, off)
+    assert np.array_equal(r1.keep, r2.keep) and np.array_equal(r1.content, r2.content)
+    _same_stats(r1, r2)
+    # halves == whole
+    h = 30000
+    ra = p.run_packed(utf8[: off[h]], off[: h + 1])
+    rb = p.run_packed(utf8, off[h:])
+    assert np.array_equal(np.concatenate([ra.keep, rb.keep]), r1.keep)
+    assert np.array_equal(np.concatenate([ra.failed_step, rb.failed_step]), r1.failed_step)
+    # idempotence: C4 applied to its own output changes nothing and keeps every kept document
+    c4 = GpuBatchPipeline(CHAINS["c4_shipped"])
+    first = c4.run_packed(utf8, off)
+    kept = np.nonzero(first.keep)[0]
+    lens = np.diff(first.content_offsets)[kept]
+    off2 = np.zeros(len(kept) + 1, np.int64)
+    off2[1:] = np.cumsum(lens)
+    buf2 = np.concatenate([first.content[first.content_offsets[i]:first.content_offsets[i + 1]] for i in kept[:5000]]) if len(kept) else np.zeros(0, np.uint8)
+    off2 = off2[:min(len(kept), 5000) + 1]
+    second = c4.run_packed(buf2, off2)
+    assert second.keep.all()
+    assert np.array_equal(second.content, buf2) and np.array_equal(second.content_offsets, off2)
+    p.close()
+    c4.close()

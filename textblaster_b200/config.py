@@ -88,6 +88,7 @@ class C4QualityParams:
     filter_policy: bool
 
     TYPE = "C4QualityFilter"
+    CTYPE = _abi.TB_STEP_C4_QUALITY
 
     @classmethod
     def from_dict(cls, d: dict) -> "C4QualityParams":
@@ -133,6 +134,7 @@ class GopherRepetitionParams:
     dup_n_grams: List[Tuple[int, float]] = field(default_factory=list)
 
     TYPE = "GopherRepetitionFilter"
+    CTYPE = _abi.TB_STEP_GOPHER_REPETITION
 
     @classmethod
     def from_dict(cls, d: dict) -> "GopherRepetitionParams":
@@ -214,6 +216,7 @@ class GopherQualityParams:
     stop_words: Optional[List[str]] = None
 
     TYPE = "GopherQualityFilter"
+    CTYPE = _abi.TB_STEP_GOPHER_QUALITY
 
     @classmethod
     def from_dict(cls, d: dict) -> "GopherQualityParams":
