@@ -20,6 +20,7 @@
 
 thread_local SimtWarp* simt_warp = nullptr;
 thread_local int simt_lane = 0;
+thread_local SimtBlock* simt_block = nullptr;
 
 namespace {
 
@@ -38,6 +39,30 @@ void run_warps(int64_t n, const std::function<bool(int64_t)>& pred, const std::f
         fn(d, lane);
         warp.bar.arrive_and_wait();  // kernels never share state between warps mid-flight
       }
+    });
+  }
+  for (auto& t : th) t.join();
+}
+
+// One emulated CTA of `nthreads` threads per listed document (block-level collectives only).
+void run_blocks(const uint32_t* list, uint32_t count, int nthreads, const std::function<void(int64_t, int)>& fn) {
+  SimtBlock blk(nthreads);
+  std::vector<std::thread> th;
+  for (int t = 0; t < nthreads; t++) {
+    th.emplace_back([&, t]() {
+      simt_block = &blk;
+      for (uint32_t i = 0; i < count; i++) { fn((int64_t)list[i], t); blk.bar.arrive_and_wait(); }
+    });
+  }
+  for (auto& t : th) t.join();
+}
+void run_warps_list(const uint32_t* list, uint32_t count, const std::function<void(int64_t, int)>& fn) {
+  SimtWarp warp;
+  std::vector<std::thread> th;
+  for (int lane = 0; lane < 32; lane++) {
+    th.emplace_back([&, lane]() {
+      simt_warp = &warp; simt_lane = lane;
+      for (uint32_t i = 0; i < count; i++) { fn((int64_t)list[i], lane); warp.bar.arrive_and_wait(); }
     });
   }
   for (auto& t : th) t.join();
@@ -102,13 +127,16 @@ extern "C" int tbe_run_chain(const tb_step_cfg* steps, size_t n_steps, const uin
       g.dup_line_frac = q.dup_line_frac; g.dup_para_frac = q.dup_para_frac;
       g.dup_line_char_frac = q.dup_line_char_frac; g.dup_para_char_frac = q.dup_para_char_frac;
       for (int k = 0; k < TB_MAX_NGRAMS; k++) { g.top_n[k] = q.top_n[k]; g.top_frac[k] = q.top_frac[k]; g.dup_n[k] = q.dup_n[k]; g.dup_frac[k] = q.dup_frac[k]; }
-      uint32_t K = 10u + (uint32_t)g.n_dup; K += K & 1u;
       GrScratch gs{(uint64_t*)G64(units), G32(units), (uint64_t*)G64(units), G32(units), G8(units),
-                   (GrDoc*)G8(n1 * sizeof(GrDoc)), G32(units * K + n1 * TB_REP_DOC_EXTRA), K};
+                   (GrDoc*)G8(n1 * sizeof(GrDoc)), G32(units * TB_REP_K + n1 * TB_REP_DOC_EXTRA), G32(3 * n1), G32(16), n};
+      memset(gs.counters, 0, 32);
       for (int64_t d = 0; d < n; d++) body_trim(b, ascii, ts, te, d);
       run_warps(n, alive_pred, [&](int64_t d, int lane) { body_gr_scan(b, ascii, ts, te, gs, d, lane); });
-      uint32_t* s_tab = G32(TB_REP_SMEM_TABLE);
-      run_warps(n, alive_pred, [&](int64_t d, int lane) { body_gr_rep(b, s_tab, ts, te, gs, g, (int)s, (tb_gr_stats*)stats, d, lane); });
+      uint8_t* smem_s = (uint8_t*)G64(TB_REP_S_SMEM / 8 + 2);
+      uint8_t* smem_m = (uint8_t*)G64(TB_REP_M_SMEM / 8 + 2);
+      run_warps_list(gs.lists, gs.counters[0], [&](int64_t d, int lane) { body_gr_rep_s(b, smem_s, ts, te, gs, g, (int)s, (tb_gr_stats*)stats, d, lane); });
+      run_blocks(gs.lists + n, gs.counters[1], TB_REP_M_THREADS, [&](int64_t d, int tid) { body_gr_rep_m(b, smem_m, ts, te, gs, g, (int)s, (tb_gr_stats*)stats, d, tid); });
+      run_warps_list(gs.lists + 2 * n, gs.counters[2], [&](int64_t d, int lane) { body_gr_rep_l(b, ts, te, gs, g, (int)s, (tb_gr_stats*)stats, d, lane); });
     } else if (sc.type == TB_STEP_C4_QUALITY) {
       if (!sc.u.c4.split_paragraph || has_c4) return 5;
       C4Cfg cfg = tb_c4cfg_of(sc.u.c4);

@@ -49,6 +49,17 @@ def test_multi_tile_documents(name):
     _check(name, texts)
 
 
+def test_repetition_tiers():
+    """tb_rep.cuh picks shared-memory (warp / CTA) or global work areas by document size; a document
+    with many repeated n-grams exercises the candidate walk in each tier."""
+    rng = random.Random(8)
+    base = fuzzgen.english_doc(rng, 1500)
+    texts = [fuzzgen.english_doc(rng, 2500), fuzzgen.english_doc(rng, 12000), fuzzgen.english_doc(rng, 36000),
+             (base + "\n") * 3, (base + "\n") * 9, (base + "\n") * 30, "a b c d e f g " * 700, "x y " * 5000]
+    _check("gr_open", texts)
+    _check("gr_shipped", texts)
+
+
 def test_word_spanning_many_tiles():
     # a single segment longer than several tiles is walked by the lane that owns its first byte
     texts = ["start " + "a" * 5000 + " end. Another sentence here. And a third one.", "a" * 3000, "é" * 1500 + " x"]

@@ -122,7 +122,7 @@ struct KTime { const char* name; double ms; int64_t launches; };
 }  // namespace
 
 struct tb_ctx {
-  int device = 0;
+  int device = 0, sm_count = 148;
   cudaStream_t compute = nullptr, copy = nullptr, d2h = nullptr;
   UcTables uc{};
   DevBuf t_stage1, t_stage2, t_lower, t_cased, t_caseign, t_pow;
@@ -138,7 +138,7 @@ struct tb_pipeline {
   DevBuf rs0, re0, rs, re, ts, te, alive, failed, rewritten, len, out_off, bad;
   DevBuf stats[TB_MAX_STEPS];
   // GopherRepetition scratch
-  DevBuf g_wh, g_wl, g_lh, g_ll, g_lg, g_doc, g_work;
+  DevBuf g_wh, g_wl, g_lh, g_ll, g_lg, g_doc, g_work, g_lists, g_counters;
   // C4 scratch
   DevBuf c_P, c_F, c_plen, c_nlines, c_docflags, c_lwc, c_lmax, c_lflags, c_prs, c_pre, c_frs, c_fre, c_cnt;
   cudaEvent_t ev_h2d[2] = {nullptr, nullptr}, ev_done[2] = {nullptr, nullptr}, ev_d2h[2] = {nullptr, nullptr};
@@ -286,10 +286,10 @@ int ensure_chunk_buffers(tb_pipeline* p, int64_t n, int64_t nb, bool host_input)
     const StepHost& sh = p->steps[s];
     ENS(p->stats[s], n1 * stat_size(sh.type));
     if (sh.type == TB_STEP_GOPHER_REPETITION) {
-      uint32_t K = 10u + (uint32_t)sh.gr.n_dup; K += K & 1u;
       ENS(p->g_wh, units * 8); ENS(p->g_wl, units * 4); ENS(p->g_lh, units * 8); ENS(p->g_ll, units * 4); ENS(p->g_lg, units);
       ENS(p->g_doc, n1 * sizeof(GrDoc));
-      ENS(p->g_work, (units * K + n1 * TB_REP_DOC_EXTRA) * 4);
+      ENS(p->g_work, (units * TB_REP_K + n1 * TB_REP_DOC_EXTRA) * 4);
+      ENS(p->g_lists, 3 * n1 * 4); ENS(p->g_counters, 64);
     } else if (sh.type == TB_STEP_C4_QUALITY) {
       size_t lines = (size_t)nb + n1 + 1;
       ENS(p->c_P, (size_t)nb + 64); ENS(p->c_F, (size_t)nb + 64);
@@ -322,12 +322,15 @@ int enqueue_chain(tb_pipeline* p, const uint8_t* text, int64_t n, int pb, bool w
       Timed t(p, "k_gq");
       tb_launch_gq(st, b, sh.sw, sh.gq, (int)s, p->stats[s].as<tb_gq_stats>());
     } else if (sh.type == TB_STEP_GOPHER_REPETITION) {
-      uint32_t K = 10u + (uint32_t)sh.gr.n_dup; K += K & 1u;
       GrScratch g{p->g_wh.as<uint64_t>(), p->g_wl.as<uint32_t>(), p->g_lh.as<uint64_t>(), p->g_ll.as<uint32_t>(),
-                  p->g_lg.as<uint8_t>(), p->g_doc.as<GrDoc>(), p->g_work.as<uint32_t>(), K};
+                  p->g_lg.as<uint8_t>(), p->g_doc.as<GrDoc>(), p->g_work.as<uint32_t>(), p->g_lists.as<uint32_t>(),
+                  p->g_counters.as<uint32_t>(), n};
+      CK(cudaMemsetAsync(p->g_counters.p, 0, 32, st));
       { Timed t(p, "k_trim"); tb_launch_trim(st, b, p->ts.as<int64_t>(), p->te.as<int64_t>()); }
       { Timed t(p, "k_gr_scan"); tb_launch_gr_scan(st, b, p->ts.as<int64_t>(), p->te.as<int64_t>(), g); }
-      { Timed t(p, "k_gr_rep"); tb_launch_gr_rep(st, b, p->ts.as<int64_t>(), p->te.as<int64_t>(), g, sh.gr, (int)s, p->stats[s].as<tb_gr_stats>()); }
+      { Timed t(p, "k_gr_rep_s"); tb_launch_gr_rep(st, b, p->ts.as<int64_t>(), p->te.as<int64_t>(), g, sh.gr, (int)s, p->stats[s].as<tb_gr_stats>(), c->sm_count, 0); }
+      { Timed t(p, "k_gr_rep_m"); tb_launch_gr_rep(st, b, p->ts.as<int64_t>(), p->te.as<int64_t>(), g, sh.gr, (int)s, p->stats[s].as<tb_gr_stats>(), c->sm_count, 1); }
+      { Timed t(p, "k_gr_rep_l"); tb_launch_gr_rep(st, b, p->ts.as<int64_t>(), p->te.as<int64_t>(), g, sh.gr, (int)s, p->stats[s].as<tb_gr_stats>(), c->sm_count, 2); }
     } else {
       C4Scratch cs{p->c_P.as<uint8_t>(), p->c_F.as<uint8_t>(), p->c_plen.as<int64_t>(), p->c_nlines.as<uint32_t>(),
                    p->c_docflags.as<uint32_t>(), p->c_lwc.as<uint32_t>(), p->c_lmax.as<uint32_t>(), p->c_lflags.as<uint32_t>(),
@@ -488,6 +491,8 @@ int tb_ctx_create(int device, tb_ctx** out) {
   CK(cudaSetDevice(device));
   auto* c = new tb_ctx();
   c->device = device;
+  { cudaDeviceProp prop; if (cudaGetDeviceProperties(&prop, device) == cudaSuccess) c->sm_count = prop.multiProcessorCount; }
+  if (tb_kernels_init() != 0) { cudaGetLastError(); delete c; return fail(TB_ERR_CUDA, "cudaFuncSetAttribute(dynamic shared memory) failed: not an sm_100-class device?"); }
   CK(cudaStreamCreateWithFlags(&c->compute, cudaStreamNonBlocking));
   CK(cudaStreamCreateWithFlags(&c->copy, cudaStreamNonBlocking));
   CK(cudaStreamCreateWithFlags(&c->d2h, cudaStreamNonBlocking));
@@ -569,7 +574,7 @@ void tb_pipeline_destroy(tb_pipeline* p) {
   cudaDeviceSynchronize();
   for (DevBuf* b : {&p->text[0], &p->text[1], &p->offs[0], &p->offs[1], &p->packed[0], &p->packed[1], &p->rs0, &p->re0, &p->rs,
                     &p->re, &p->ts, &p->te, &p->alive, &p->failed, &p->rewritten, &p->len, &p->out_off, &p->bad, &p->g_wh,
-                    &p->g_wl, &p->g_lh, &p->g_ll, &p->g_lg, &p->g_doc, &p->g_work, &p->c_P, &p->c_F, &p->c_plen, &p->c_nlines,
+                    &p->g_wl, &p->g_lh, &p->g_ll, &p->g_lg, &p->g_doc, &p->g_work, &p->g_lists, &p->g_counters, &p->c_P, &p->c_F, &p->c_plen, &p->c_nlines,
                     &p->c_docflags, &p->c_lwc, &p->c_lmax, &p->c_lflags, &p->c_prs, &p->c_pre, &p->c_frs, &p->c_fre, &p->c_cnt})
     b->release();
   for (auto& b : p->stats) b.release();

@@ -7,9 +7,10 @@
 // No tensor cores (byte/integer work); every pass reads its text once from HBM.
 #pragma once
 #include "tb_kernels.cuh"
+#include "tb_rep.cuh"
 #include "tb_simt.cuh"
 
-#define TB_BLOCK 128
+#define TB_BLOCK 32  // one warp per CTA: a document never waits for a longer neighbour in its CTA
 
 // ---------------------------------------------------------------------------------------------
 TB_D void body_init_ranges(const void* off, int off64, int64_t doc0, int64_t base, int64_t* rs, int64_t* re,
@@ -185,225 +186,58 @@ TB_D void body_gr_scan(const KBatch& a, const uint16_t* s_ascii, const int64_t* 
   if (lane == 0) {
     GrDoc g; g.char_len = nchars; g.W = W; g.NL = NL; g.flags = flags ? TB_DOCFLAG_COMPLEX_SCRIPT : 0; g.empty = (R.re <= R.rs);
     s.doc[d] = g;
+    uint32_t big = W > NL ? W : NL;
+    uint32_t tier = big <= TB_REP_S_CAP ? 0u : big <= TB_REP_M_CAP ? 1u : 2u;
+    uint32_t k = simt_atomic_add(&s.counters[tier], 1u);
+    s.lists[(uint64_t)tier * (uint64_t)s.n + k] = (uint32_t)d;
   }
 }
 
 // ---------------------------------------------------------------------------------------------
-// GopherRepetitionFilter, pass 2: duplicate lines / paragraphs, top and duplicate n-grams.
-// Open-addressing tables of element indices (keys live in the arrays; equality = 62-bit hash +
-// byte length); in shared memory when they fit, else in the document's global work area.
+// GopherRepetitionFilter, pass 2 (tb_rep.cuh): three tiers by document size
 // ---------------------------------------------------------------------------------------------
-#define T_EMPTY 0xFFFFFFFFu
-TB_D uint32_t tab_size(uint32_t count) {
-  uint32_t t = TB_REP_MIN_TABLE;
-  while (t < 2u * count) t <<= 1;
-  return t;
-}
-TB_D void tab_clear(uint32_t* tab, uint32_t T, int lane) {
-  for (uint32_t i = lane; i < T; i += 32) tab[i] = T_EMPTY;
-  simt_sync();
-}
+#define TB_REP_S_SMEM (TB_REP_S_CAP * 8 + TB_REP_S_CAP * 8 + (TB_REP_S_CAP + 2) * 4 + 2 * TB_REP_S_CAP * 2 + TB_REP_S_CAP * 2)
+#define TB_REP_M_SMEM (TB_REP_M_CAP * 8 + TB_REP_M_CAP * 8 + (TB_REP_M_CAP + 2) * 4 + 2 * TB_REP_M_CAP * 2 + TB_REP_M_CAP * 2 + 64 * 8)
 
-// find_duplicates (text.rs:197-208) over n pieces: dup_elems = n - distinct, dup_bytes = total - distinct bytes
-TB_D void dedup_pieces(uint32_t* tab, const uint64_t* h, const uint32_t* len, uint32_t n, int lane, uint32_t* dup_elems,
-                       uint64_t* dup_bytes) {
-  uint32_t T = tab_size(n);
-  tab_clear(tab, T, lane);
-  uint32_t distinct = 0; uint64_t dbytes = 0, total = 0;
-  for (uint32_t i = lane; i < n; i += 32) {
-    uint64_t hi = h[i]; uint32_t li = len[i];
-    uint32_t sl = (uint32_t)tb_mix64(hi ^ ((uint64_t)li << 40)) & (T - 1);
-    total += li;
-    for (;;) {
-      uint32_t old = simt_cas(&tab[sl], T_EMPTY, i);
-      if (old == T_EMPTY) { distinct++; dbytes += li; break; }
-      if (h[old] == hi && len[old] == li) break;
-      sl = (sl + 1) & (T - 1);
-    }
-  }
-  simt_sync();
-  distinct = simt_sum(distinct); dbytes = simt_sum64(dbytes); total = simt_sum64(total);
-  *dup_elems = n - distinct; *dup_bytes = total - dbytes;
+// tier S: one warp, working arrays carved from `smem` (TB_REP_S_SMEM bytes, 8-byte aligned)
+TB_D void body_gr_rep_s(const KBatch& a, uint8_t* smem, const int64_t* ts, const int64_t* te, const GrScratch& s,
+                        const GrCfg& cfg, int step, tb_gr_stats* out, int64_t d, int lane) {
+  RepArrays A;
+  A.wh = (uint64_t*)smem;
+  A.H = A.wh + TB_REP_S_CAP;
+  A.woff = (uint32_t*)(A.H + TB_REP_S_CAP);
+  uint16_t* tab = (uint16_t*)(A.woff + TB_REP_S_CAP + 2);
+  uint16_t* cnt = tab + 2 * TB_REP_S_CAP;
+  WarpGroup g{lane};
+  rep_body<WarpGroup, uint16_t>(g, a, ts, te, s, cfg, step, out, d, A, tab, cnt);
 }
-
-TB_D void body_gr_rep(const KBatch& a, uint32_t* s_tab, const int64_t* ts, const int64_t* te, const GrScratch& s,
-                      const GrCfg& cfg, int step, tb_gr_stats* out, int64_t d, int lane) {
-  const GrDoc g = s.doc[d];
-  tb_gr_stats st;
-  st.reason_bits = 0; st.flags = g.flags; st.char_len = g.char_len; st.n_paras = 0; st.para_dup_elems = 0; st.para_dup_bytes = 0;
-  st.n_lines = 0; st.line_dup_elems = 0; st.line_dup_bytes = 0; st.n_words = 0;
-  for (int k = 0; k < TB_MAX_NGRAMS; k++) { st.top_bytes[k] = 0; st.dup_bytes[k] = 0; }
-  if (g.empty) {  // gopher_rep.rs:60-74
-    if (lane == 0) { st.reason_bits = TB_GR_REASON_EMPTY; out[d] = st; a.alive[d] = 0; a.failed[d] = (int8_t)step; }
-    return;
-  }
+// tier M: one CTA, working arrays carved from `smem` (TB_REP_M_SMEM bytes)
+TB_D void body_gr_rep_m(const KBatch& a, uint8_t* smem, const int64_t* ts, const int64_t* te, const GrScratch& s,
+                        const GrCfg& cfg, int step, tb_gr_stats* out, int64_t d, int tid) {
+  RepArrays A;
+  A.wh = (uint64_t*)smem;
+  A.H = A.wh + TB_REP_M_CAP;
+  A.woff = (uint32_t*)(A.H + TB_REP_M_CAP);
+  uint16_t* tab = (uint16_t*)(A.woff + TB_REP_M_CAP + 2);
+  uint16_t* cnt = tab + 2 * TB_REP_M_CAP;
+  BlockGroup g{tid, (uint64_t*)(cnt + TB_REP_M_CAP)};
+  rep_body<BlockGroup, uint16_t>(g, a, ts, te, s, cfg, step, out, d, A, tab, cnt);
+}
+// tier L: one warp, working arrays in the document's region of the global work area
+TB_D void body_gr_rep_l(const KBatch& a, const int64_t* ts, const int64_t* te, const GrScratch& s, const GrCfg& cfg, int step,
+                        tb_gr_stats* out, int64_t d, int lane) {
   const int64_t rs = ts[d], re = te[d];
   const uint64_t ub = (uint64_t)(rs >> 1) + (uint64_t)d;
   const uint32_t U = (uint32_t)((re - rs) >> 1) + 1u;
-  const uint64_t* wh = s.wh + ub; const uint32_t* wl = s.wl + ub;
-  const uint64_t* lh = s.lh + ub; const uint32_t* ll = s.ll + ub; const uint8_t* lg = s.lg + ub;
-  // work area layout (32-bit words): C[2U] J[2U] gtab[4U+16] cnt[U] fo[n_dup*U] woff[U+1]
-  uint32_t* work = s.work + ub * s.K + (uint64_t)d * TB_REP_DOC_EXTRA;
-  uint64_t* Cc = (uint64_t*)work;
-  uint64_t* Jj = Cc + U;
-  uint32_t* gtab = (uint32_t*)(Jj + U);
-  uint32_t* cnt = gtab + 4u * U + TB_REP_MIN_TABLE;
-  uint32_t* fo = cnt + U;
-  uint32_t* woff = fo + (uint32_t)cfg.n_dup * U;
-  const uint32_t W = g.W, NL = g.NL;
-  const uint32_t maxcount = W > NL ? W : NL;
-  uint32_t* tab = tab_size(maxcount) <= TB_REP_SMEM_TABLE ? s_tab : gtab;
-  const double text_char_len = (double)(g.char_len ? g.char_len : 1);
-  uint32_t reasons = 0;
-
-  // ---- lines (gopher_rep.rs:120-156)
-  uint32_t de; uint64_t db;
-  dedup_pieces(tab, lh, ll, NL, lane, &de, &db);
-  st.n_lines = NL; st.line_dup_elems = de; st.line_dup_bytes = db;
-  {
-    double r1 = (double)de / (double)(NL ? NL : 1u), r2 = (double)db / text_char_len;
-    if ((cfg.has & TB_GR_HAS_DUP_LINE_FRAC) && r1 > cfg.dup_line_frac) reasons |= TB_GR_REASON_DUP_LINE_FRAC;
-    if ((cfg.has & TB_GR_HAS_DUP_LINE_CHAR_FRAC) && r2 > cfg.dup_line_char_frac) reasons |= TB_GR_REASON_DUP_LINE_CHAR_FRAC;
-  }
-  // ---- paragraphs (gopher_rep.rs:80-116): fold the ordered line pieces; a single '\n' joins
-  // lines inside a paragraph, a run of >= 2 separates paragraphs.
-  uint32_t NP = 0;
-  if (lane == 0) {
-    Hash2 cur; cur.init(); uint32_t curlen = 0;
-    for (uint32_t k = 0; k < NL; k++) {
-      Hash2 hk = tb_unpack(lh[k]);
-      if (k == 0) { cur = hk; curlen = ll[k]; continue; }
-      if (lg[k]) { Cc[NP] = cur.pack(); cnt[NP] = curlen; NP++; cur = hk; curlen = ll[k]; }
-      else { cur.push('\n'); cur = tb_hcat(cur, hk, tb_pow_pack(a.uc.powtab, ll[k])); curlen += 1 + ll[k]; }
-    }
-    if (NL) { Cc[NP] = cur.pack(); cnt[NP] = curlen; NP++; }
-  }
-  NP = simt_shfl(NP, 0);
-  simt_sync();
-  dedup_pieces(tab, Cc, cnt, NP, lane, &de, &db);
-  st.n_paras = NP; st.para_dup_elems = de; st.para_dup_bytes = db;
-  {
-    double r1 = (double)de / (double)(NP ? NP : 1u), r2 = (double)db / text_char_len;
-    if ((cfg.has & TB_GR_HAS_DUP_PARA_FRAC) && r1 > cfg.dup_para_frac) reasons |= TB_GR_REASON_DUP_PARA_FRAC;
-    if ((cfg.has & TB_GR_HAS_DUP_PARA_CHAR_FRAC) && r2 > cfg.dup_para_char_frac) reasons |= TB_GR_REASON_DUP_PARA_CHAR_FRAC;
-  }
-  simt_sync();
-
-  // ---- n-grams (gopher_rep.rs:159-196)
-  uint32_t nmax = 0;
-  for (int k = 0; k < cfg.n_top; k++) nmax = cfg.top_n[k] > nmax ? cfg.top_n[k] : nmax;
-  for (int k = 0; k < cfg.n_dup; k++) nmax = cfg.dup_n[k] > nmax ? cfg.dup_n[k] : nmax;
-  if (nmax > W) nmax = W;
-  uint64_t top_val[TB_MAX_NGRAMS];
-  uint32_t dup_any = 0;  // bit k: dup_n_grams[k] has at least one repeated key
-  for (int k = 0; k < TB_MAX_NGRAMS; k++) top_val[k] = 0;
-  if (nmax) {
-    // byte offsets of the words in the concatenation; C = concat hash, J = " "-joined hash
-    uint32_t run = 0;
-    for (uint32_t b0 = 0; b0 < W; b0 += 32) {
-      uint32_t i = b0 + lane, v = i < W ? wl[i] : 0, tot, pre = simt_exscan(v, lane, &tot);
-      if (i < W) { woff[i] = run + pre; Cc[i] = wh[i]; Jj[i] = wh[i]; }
-      run += tot;
-    }
-    if (lane == 0) woff[W] = run;
-    simt_sync();
-    for (uint32_t n = 1; n <= nmax; n++) {
-      const uint32_t cn = W - n + 1;  // number of n-grams
-      if (n > 1) {
-        for (uint32_t i = lane; i < cn; i += 32) {
-          uint32_t j = i + n - 1;
-          Hash2 hj = tb_unpack(wh[j]);
-          uint64_t pw = tb_pow_pack(a.uc.powtab, wl[j]);
-          Cc[i] = tb_hcat(tb_unpack(Cc[i]), hj, pw).pack();
-          Hash2 jj = tb_unpack(Jj[i]); jj.push(' ');
-          Jj[i] = tb_hcat(jj, hj, pw).pack();
-        }
-        simt_sync();
-      }
-      const uint32_t T = tab_size(cn);
-      for (int k = 0; k < cfg.n_top; k++) {
-        if (cfg.top_n[k] != n) continue;
-        // find_top_duplicate (text.rs:211-238): max count, then the longest key among those
-        tab_clear(tab, T, lane);
-        for (uint32_t i = lane; i < cn; i += 32) cnt[i] = 0;
-        simt_sync();
-        for (uint32_t i = lane; i < cn; i += 32) {
-          // key length = concatenated bytes + (n - 1) spaces; equal joined strings <=> equal hash + length
-          uint32_t len = woff[i + n] - woff[i] + n - 1;
-          uint64_t key = Jj[i];
-          uint32_t sl = (uint32_t)tb_mix64(key ^ ((uint64_t)len << 40)) & (T - 1);
-          for (;;) {
-            uint32_t old = simt_cas(&tab[sl], T_EMPTY, i);
-            if (old == T_EMPTY) { simt_atomic_add(&cnt[i], 1u); break; }
-            if (Jj[old] == key && woff[old + n] - woff[old] + n - 1 == len) { simt_atomic_add(&cnt[old], 1u); break; }
-            sl = (sl + 1) & (T - 1);
-          }
-        }
-        simt_sync();
-        uint64_t best = 0;
-        for (uint32_t i = lane; i < cn; i += 32) {
-          uint32_t c = cnt[i];
-          if (c) { uint64_t v = ((uint64_t)c << 32) | (woff[i + n] - woff[i] + n - 1); best = v > best ? v : best; }
-        }
-        top_val[k] = simt_max64(best);
-        simt_sync();
-      }
-      for (int k = 0; k < cfg.n_dup; k++) {
-        if (cfg.dup_n[k] != n) continue;
-        // first occurrence (smallest position) of every concatenated key -> fo_k[i]
-        uint32_t* fok = fo + (uint32_t)k * U;
-        tab_clear(tab, T, lane);
-        for (uint32_t i = lane; i < cn; i += 32) {
-          uint32_t len = woff[i + n] - woff[i];
-          uint64_t key = Cc[i];
-          uint32_t sl = (uint32_t)tb_mix64(key ^ ((uint64_t)len << 40)) & (T - 1);
-          for (;;) {
-            uint32_t old = simt_cas(&tab[sl], T_EMPTY, i);
-            if (old == T_EMPTY) break;
-            if (Cc[old] == key && woff[old + n] - woff[old] == len) { simt_atomic_min(&tab[sl], i); break; }
-            sl = (sl + 1) & (T - 1);
-          }
-          fok[i] = sl;
-        }
-        simt_sync();
-        bool any = false;
-        for (uint32_t i = lane; i < cn; i += 32) { uint32_t f = tab[fok[i]]; fok[i] = f; any |= (f != i); }
-        if (simt_any(any)) dup_any |= 1u << k;
-        simt_sync();
-      }
-    }
-  }
-  // find_all_duplicate (text.rs:241-259): the greedy scan is sequential; one lane per configured n.
-  uint64_t dupv = 0;
-  if (lane < cfg.n_dup && ((dup_any >> lane) & 1u)) {
-    const uint32_t n = cfg.dup_n[lane];
-    uint32_t* fok = fo + (uint32_t)lane * U;
-    const uint32_t SEEN = 0x80000000u;
-    uint32_t idx = 0;
-    while (idx + n <= W) {
-      uint32_t c = fok[idx] & ~SEEN;
-      uint32_t v = fok[c];
-      if (v & SEEN) { dupv += woff[idx + n] - woff[idx]; idx += n; }
-      else { fok[c] = v | SEEN; idx += 1; }
-    }
-  }
-  simt_sync();
-  for (int k = 0; k < cfg.n_dup; k++) {
-    uint64_t v = simt_shfl(dupv, k);
-    st.dup_bytes[k] = v;
-    if (cfg.dup_n[k] > 0 && (double)v / text_char_len > cfg.dup_frac[k]) reasons |= 1u << (TB_GR_REASON_DUP_SHIFT + k);
-  }
-  for (int k = 0; k < cfg.n_top; k++) {
-    uint32_t c = (uint32_t)(top_val[k] >> 32), len = (uint32_t)top_val[k];
-    uint64_t v = c > 1 ? (uint64_t)len * c : 0;
-    st.top_bytes[k] = v;
-    if (cfg.top_n[k] > 0 && (double)v / text_char_len > cfg.top_frac[k]) reasons |= 1u << (TB_GR_REASON_TOP_SHIFT + k);
-  }
-  if (lane == 0) {
-    st.n_words = W; st.reason_bits = reasons;
-    out[d] = st;
-    if (reasons) { a.alive[d] = 0; a.failed[d] = (int8_t)step; }
-  }
+  uint32_t* work = s.work + ub * TB_REP_K + (uint64_t)d * TB_REP_DOC_EXTRA;
+  RepArrays A;
+  A.wh = (uint64_t*)(s.wh + ub);  // read in place
+  A.H = (uint64_t*)work;
+  A.woff = (uint32_t*)(A.H + U);
+  uint32_t* tab = A.woff + U + 2;
+  uint32_t* cnt = tab + 4u * U + TB_REP_MIN_TABLE;
+  WarpGroup g{lane};
+  rep_body<WarpGroup, uint32_t>(g, a, ts, te, s, cfg, step, out, d, A, tab, cnt);
 }
 
 // ---------------------------------------------------------------------------------------------

@@ -45,12 +45,47 @@ __global__ void __launch_bounds__(TB_BLOCK) k_gr_scan(KBatch a, const int64_t* t
   if (d >= a.n || !a.alive[d]) return;
   body_gr_scan(a, s_ascii, ts, te, s, d, threadIdx.x & 31);
 }
-__global__ void __launch_bounds__(TB_BLOCK) k_gr_rep(KBatch a, const int64_t* ts, const int64_t* te, GrScratch s,
-                                                     GrCfg cfg, int step, tb_gr_stats* out) {
-  __shared__ uint32_t s_tab[TB_BLOCK / 32][TB_REP_SMEM_TABLE];
-  int64_t d = warp_doc();
-  if (d >= a.n || !a.alive[d]) return;
-  body_gr_rep(a, s_tab[threadIdx.x >> 5], ts, te, s, cfg, step, out, d, threadIdx.x & 31);
+// Repetition pass 2, persistent CTAs pulling document ids of their tier from the lists the scan pass built.
+__global__ void __launch_bounds__(32) k_gr_rep_s(KBatch a, const int64_t* ts, const int64_t* te, GrScratch s, GrCfg cfg,
+                                                 int step, tb_gr_stats* out) {
+  __shared__ __align__(16) uint8_t smem[TB_REP_S_SMEM];
+  const int lane = threadIdx.x;
+  const uint32_t count = s.counters[0];
+  for (;;) {
+    uint32_t i = 0;
+    if (lane == 0) i = atomicAdd(&s.counters[4], 1u);
+    i = __shfl_sync(0xFFFFFFFFu, i, 0);
+    if (i >= count) break;
+    body_gr_rep_s(a, smem, ts, te, s, cfg, step, out, (int64_t)s.lists[i], lane);
+    __syncwarp();
+  }
+}
+__global__ void __launch_bounds__(TB_REP_M_THREADS) k_gr_rep_m(KBatch a, const int64_t* ts, const int64_t* te, GrScratch s,
+                                                               GrCfg cfg, int step, tb_gr_stats* out) {
+  extern __shared__ __align__(16) uint8_t dsmem[];
+  __shared__ uint32_t s_i;
+  const uint32_t count = s.counters[1];
+  for (;;) {
+    __syncthreads();
+    if (threadIdx.x == 0) s_i = atomicAdd(&s.counters[5], 1u);
+    __syncthreads();
+    uint32_t i = s_i;
+    if (i >= count) break;
+    body_gr_rep_m(a, dsmem, ts, te, s, cfg, step, out, (int64_t)s.lists[(uint64_t)s.n + i], (int)threadIdx.x);
+  }
+}
+__global__ void __launch_bounds__(32) k_gr_rep_l(KBatch a, const int64_t* ts, const int64_t* te, GrScratch s, GrCfg cfg,
+                                                 int step, tb_gr_stats* out) {
+  const int lane = threadIdx.x;
+  const uint32_t count = s.counters[2];
+  for (;;) {
+    uint32_t i = 0;
+    if (lane == 0) i = atomicAdd(&s.counters[6], 1u);
+    i = __shfl_sync(0xFFFFFFFFu, i, 0);
+    if (i >= count) break;
+    body_gr_rep_l(a, ts, te, s, cfg, step, out, (int64_t)s.lists[2 * (uint64_t)s.n + i], lane);
+    __syncwarp();
+  }
 }
 __global__ void __launch_bounds__(TB_BLOCK) k_c4_a(KBatch a, C4Cfg cfg, C4Scratch s) {
   __shared__ uint16_t s_ascii[128];
@@ -141,8 +176,14 @@ void tb_launch_gr_scan(cudaStream_t st, const KBatch& b, const int64_t* ts, cons
   if (b.n) k_gr_scan<<<blocks_for_warps(b.n), TB_BLOCK, 0, st>>>(b, ts, te, s);
 }
 void tb_launch_gr_rep(cudaStream_t st, const KBatch& b, const int64_t* ts, const int64_t* te, const GrScratch& s,
-                      const GrCfg& cfg, int step, tb_gr_stats* out) {
-  if (b.n) k_gr_rep<<<blocks_for_warps(b.n), TB_BLOCK, 0, st>>>(b, ts, te, s, cfg, step, out);
+                      const GrCfg& cfg, int step, tb_gr_stats* out, int sm_count, int tier) {
+  if (!b.n) return;
+  if (tier == 0) k_gr_rep_s<<<sm_count * 16, 32, 0, st>>>(b, ts, te, s, cfg, step, out);
+  else if (tier == 1) k_gr_rep_m<<<sm_count * 2, TB_REP_M_THREADS, TB_REP_M_SMEM, st>>>(b, ts, te, s, cfg, step, out);
+  else k_gr_rep_l<<<sm_count * 8, 32, 0, st>>>(b, ts, te, s, cfg, step, out);
+}
+int tb_kernels_init() {
+  return (int)cudaFuncSetAttribute(k_gr_rep_m, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TB_REP_M_SMEM);
 }
 void tb_launch_c4_a(cudaStream_t st, const KBatch& b, const C4Cfg& cfg, const C4Scratch& s) {
   if (b.n) k_c4_a<<<blocks_for_warps(b.n), TB_BLOCK, 0, st>>>(b, cfg, s);

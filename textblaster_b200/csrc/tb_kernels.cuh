@@ -49,12 +49,14 @@ struct GrScratch {
   uint64_t* wh; uint32_t* wl;               // words: hash, byte length
   uint64_t* lh; uint32_t* ll; uint8_t* lg;  // line pieces: hash, byte length, "preceded by >= 2 newlines"
   GrDoc* doc;                               // [n]
-  uint32_t* work;                           // rep work area, K words per unit + TB_REP_DOC_EXTRA per doc
-  uint32_t K;
+  uint32_t* work;                           // tier-L work area, TB_REP_K words per unit + TB_REP_DOC_EXTRA per doc
+  uint32_t* lists;                          // [3][n] document ids per tier (S, M, L), filled by the scan pass
+  uint32_t* counters;                       // [8]: list lengths [0..2], work cursors [4..6]
+  int64_t n;
 };
-#define TB_REP_DOC_EXTRA 20u  // words: 16 (minimum table) + 2 (woff tail) + pad
+#define TB_REP_K 8u           // tier-L words per unit: H[2U] woff[U+1] tab[4U+16] cnt[U]
+#define TB_REP_DOC_EXTRA 20u  // words: 16 (minimum table) + 1 (woff tail) + pad
 #define TB_REP_MIN_TABLE 16u
-#define TB_REP_SMEM_TABLE 1024u
 
 // scratch of the C4 filter
 struct C4Scratch {
@@ -77,7 +79,8 @@ void tb_launch_gq(cudaStream_t st, const KBatch& b, const SwTable& sw, const GqC
 void tb_launch_trim(cudaStream_t st, const KBatch& b, int64_t* ts, int64_t* te);
 void tb_launch_gr_scan(cudaStream_t st, const KBatch& b, const int64_t* ts, const int64_t* te, const GrScratch& s);
 void tb_launch_gr_rep(cudaStream_t st, const KBatch& b, const int64_t* ts, const int64_t* te, const GrScratch& s,
-                      const GrCfg& cfg, int step, tb_gr_stats* out);
+                      const GrCfg& cfg, int step, tb_gr_stats* out, int sm_count, int tier);  // tier 0 S, 1 M, 2 L
+int tb_kernels_init();  // per-process function attributes (dynamic shared memory opt-in)
 void tb_launch_c4_a(cudaStream_t st, const KBatch& b, const C4Cfg& cfg, const C4Scratch& s);
 void tb_launch_c4_b(cudaStream_t st, const KBatch& b, const C4Cfg& cfg, const C4Scratch& s);
 void tb_launch_c4_c(cudaStream_t st, const KBatch& b, const C4Cfg& cfg, const C4Scratch& s);

@@ -1,0 +1,403 @@
+// tb_rep.cuh -- GopherRepetitionFilter pass 2: duplicate lines / paragraphs, top n-grams and
+// duplicate n-grams of one document, written once against a "group" of cooperating threads:
+//   tier S  one warp  per document, all working arrays in shared memory   (W, NL <= 512)
+//   tier M  one CTA   per document, all working arrays in shared memory   (W, NL <= 4096)
+//   tier L  one warp  per document, working arrays in the global work area (anything larger)
+// Replaces text.rs:197-259 as called from gopher_rep.rs:86-196.
+//
+// Open-addressing tables hold element indices; the keys live in the arrays (equality = 62-bit
+// polynomial hash + byte length).  find_all_duplicate's greedy scan is order dependent; it is
+// reduced to a short sequential pass over the *candidate* positions only (those whose key already
+// occurred earlier), see rep_dup_walk.
+#pragma once
+#include "tb_kernels.cuh"
+#include "tb_simt.cuh"
+
+#define TB_REP_S_CAP 512u
+#define TB_REP_M_CAP 4096u
+#define TB_REP_M_THREADS 256
+
+// ---- thread groups ---------------------------------------------------------------------------
+struct WarpGroup {
+  int tid;
+  static constexpr int kSize = 32;
+  TB_D int size() const { return 32; }
+  TB_D void sync() const { simt_sync(); }
+  TB_D uint32_t sum(uint32_t v) const { return simt_sum(v); }
+  TB_D uint64_t sum64(uint64_t v) const { return simt_sum64(v); }
+  TB_D uint64_t max64(uint64_t v) const { return simt_max64(v); }
+  TB_D bool any(bool p) const { return simt_any(p); }
+  TB_D uint32_t exscan(uint32_t v, uint32_t* total) const { return simt_exscan(v, tid, total); }
+  TB_D uint32_t bcast(uint32_t v) const { return simt_shfl(v, 0); }
+};
+
+#if !defined(TB_HOST_EMUL)
+// One CTA; `red` is shared scratch of at least (blockDim/32 + 2) u64.
+struct BlockGroup {
+  int tid;
+  uint64_t* red;
+  TB_D int size() const { return (int)blockDim.x; }
+  TB_D void sync() const { __syncthreads(); }
+  TB_D uint64_t sum64(uint64_t v) const {
+    v = simt_sum64(v);
+    int w = tid >> 5, nw = (int)blockDim.x >> 5;
+    __syncthreads();
+    if ((tid & 31) == 0) red[w] = v;
+    __syncthreads();
+    uint64_t s = 0;
+    for (int i = 0; i < nw; i++) s += red[i];
+    return s;
+  }
+  TB_D uint32_t sum(uint32_t v) const { return (uint32_t)sum64(v); }
+  TB_D uint64_t max64(uint64_t v) const {
+    v = simt_max64(v);
+    int w = tid >> 5, nw = (int)blockDim.x >> 5;
+    __syncthreads();
+    if ((tid & 31) == 0) red[w] = v;
+    __syncthreads();
+    uint64_t s = 0;
+    for (int i = 0; i < nw; i++) s = red[i] > s ? red[i] : s;
+    return s;
+  }
+  TB_D bool any(bool p) const { return __syncthreads_or(p ? 1 : 0) != 0; }
+  TB_D uint32_t exscan(uint32_t v, uint32_t* total) const {
+    uint32_t wt, pre = simt_exscan(v, tid & 31, &wt);
+    int w = tid >> 5, nw = (int)blockDim.x >> 5;
+    __syncthreads();
+    if ((tid & 31) == 0) red[w] = wt;
+    __syncthreads();
+    uint32_t base = 0, tot = 0;
+    for (int i = 0; i < nw; i++) { uint32_t x = (uint32_t)red[i]; if (i < w) base += x; tot += x; }
+    *total = tot;
+    return base + pre;
+  }
+  TB_D uint32_t bcast(uint32_t v) const {
+    __syncthreads();
+    if (tid == 0) red[0] = v;
+    __syncthreads();
+    return (uint32_t)red[0];
+  }
+};
+#else
+// host emulation: N threads share one barrier + mailbox (tb_simt.cuh SimtBlock)
+struct BlockGroup {
+  int tid;
+  uint64_t* red;  // unused
+  TB_D int size() const { return simt_block->n; }
+  TB_D void sync() const { simt_block->bar.arrive_and_wait(); }
+  TB_D uint64_t sum64(uint64_t v) const {
+    SimtBlock* b = simt_block; b->box[tid] = v; b->bar.arrive_and_wait();
+    uint64_t s = 0; for (int i = 0; i < b->n; i++) s += b->box[i];
+    b->bar.arrive_and_wait(); return s;
+  }
+  TB_D uint32_t sum(uint32_t v) const { return (uint32_t)sum64(v); }
+  TB_D uint64_t max64(uint64_t v) const {
+    SimtBlock* b = simt_block; b->box[tid] = v; b->bar.arrive_and_wait();
+    uint64_t s = 0; for (int i = 0; i < b->n; i++) s = b->box[i] > s ? b->box[i] : s;
+    b->bar.arrive_and_wait(); return s;
+  }
+  TB_D bool any(bool p) const { return sum64(p ? 1 : 0) != 0; }
+  TB_D uint32_t exscan(uint32_t v, uint32_t* total) const {
+    SimtBlock* b = simt_block; b->box[tid] = v; b->bar.arrive_and_wait();
+    uint32_t base = 0, tot = 0;
+    for (int i = 0; i < b->n; i++) { if (i < tid) base += (uint32_t)b->box[i]; tot += (uint32_t)b->box[i]; }
+    b->bar.arrive_and_wait(); *total = tot; return base;
+  }
+  TB_D uint32_t bcast(uint32_t v) const {
+    SimtBlock* b = simt_block; if (tid == 0) b->box[0] = v; b->bar.arrive_and_wait();
+    uint32_t r = (uint32_t)b->box[0]; b->bar.arrive_and_wait(); return r;
+  }
+};
+#endif
+
+// ---- tables ----------------------------------------------------------------------------------
+template <class IdxT> struct IdxTraits;
+template <> struct IdxTraits<uint16_t> { static constexpr uint32_t kEmpty = 0xFFFFu; };
+template <> struct IdxTraits<uint32_t> { static constexpr uint32_t kEmpty = 0xFFFFFFFFu; };
+
+// atomics on 16-bit table slots: CAS on the containing 32-bit word
+TB_D uint32_t idx_cas(uint32_t* a, uint32_t cmp, uint32_t val) { return simt_cas(a, cmp, val); }
+TB_D uint32_t idx_cas(uint16_t* a, uint32_t cmp, uint32_t val) {
+  uint32_t* w = (uint32_t*)((uintptr_t)a & ~(uintptr_t)3);
+  const uint32_t sh = ((uintptr_t)a & 2) ? 16u : 0u;
+  uint32_t cur = *(volatile uint32_t*)w;
+  for (;;) {
+    uint32_t have = (cur >> sh) & 0xFFFFu;
+    if (have != cmp) return have;
+    uint32_t want = (cur & ~(0xFFFFu << sh)) | (val << sh);
+    uint32_t old = simt_cas(w, cur, want);
+    if (old == cur) return cmp;
+    cur = old;
+  }
+}
+TB_D void idx_min(uint32_t* a, uint32_t val) { simt_atomic_min(a, val); }
+TB_D void idx_min(uint16_t* a, uint32_t val) {
+  uint32_t* w = (uint32_t*)((uintptr_t)a & ~(uintptr_t)3);
+  const uint32_t sh = ((uintptr_t)a & 2) ? 16u : 0u;
+  uint32_t cur = *(volatile uint32_t*)w;
+  for (;;) {
+    uint32_t have = (cur >> sh) & 0xFFFFu;
+    if (have <= val) return;
+    uint32_t want = (cur & ~(0xFFFFu << sh)) | (val << sh);
+    uint32_t old = simt_cas(w, cur, want);
+    if (old == cur) return;
+    cur = old;
+  }
+}
+TB_D void idx_inc(uint32_t* a) { simt_atomic_add(a, 1u); }
+TB_D void idx_inc(uint16_t* a) {
+  uint32_t* w = (uint32_t*)((uintptr_t)a & ~(uintptr_t)3);
+  simt_atomic_add(w, ((uintptr_t)a & 2) ? 0x10000u : 1u);  // counts stay < 65536, no carry across halves
+}
+
+TB_D uint32_t rep_tab_size(uint32_t count) {
+  uint32_t t = TB_REP_MIN_TABLE;
+  while (t < 2u * count) t <<= 1;
+  return t;
+}
+template <class G, class IdxT>
+TB_D void rep_fill(const G& g, IdxT* a, uint32_t n, uint32_t v) {
+  for (uint32_t i = g.tid; i < n; i += g.size()) a[i] = (IdxT)v;
+  g.sync();
+}
+
+// find_duplicates (text.rs:197-208) over n pieces: dup_elems = n - distinct, dup_bytes = total - distinct bytes
+template <class G, class IdxT>
+TB_D void rep_dedup(const G& g, IdxT* tab, const uint64_t* h, const uint32_t* len, uint32_t n, uint32_t* dup_elems,
+                    uint64_t* dup_bytes) {
+  const uint32_t EMPTY = IdxTraits<IdxT>::kEmpty;
+  uint32_t T = rep_tab_size(n);
+  rep_fill(g, tab, T, EMPTY);
+  uint32_t distinct = 0; uint64_t dbytes = 0, total = 0;
+  for (uint32_t i = g.tid; i < n; i += g.size()) {
+    uint64_t hi = h[i]; uint32_t li = len[i];
+    uint32_t sl = (uint32_t)tb_mix64(hi ^ ((uint64_t)li << 40)) & (T - 1);
+    total += li;
+    for (;;) {
+      uint32_t old = idx_cas(&tab[sl], EMPTY, i);
+      if (old == EMPTY) { distinct++; dbytes += li; break; }
+      if (h[old] == hi && len[old] == li) break;
+      sl = (sl + 1) & (T - 1);
+    }
+  }
+  g.sync();
+  distinct = g.sum(distinct); dbytes = g.sum64(dbytes); total = g.sum64(total);
+  *dup_elems = n - distinct; *dup_bytes = total - dbytes;
+}
+
+// The greedy scan of find_all_duplicate (text.rs:241-259) given fo[i] = first position with the same
+// key.  Positions whose key is new (fo[i] == i) only ever insert; they are pre-marked "seen".  A hit at
+// q skips q+1..q+n-1: first occurrences inside that window were never visited, so their mark is
+// removed; a later occurrence of such a key then inserts instead of hitting.  Only candidates
+// (fo[q] < q), in increasing order, need the sequential pass.
+template <class G, class IdxT>
+TB_D uint64_t rep_dup_walk(const G& g, IdxT* fo, IdxT* cand, const uint32_t* woff, uint32_t cn, uint32_t n) {
+  const uint32_t EMPTY = IdxTraits<IdxT>::kEmpty;
+  // ordered compaction of the candidates
+  uint32_t ncand = 0;
+  for (uint32_t b0 = 0; b0 < cn; b0 += g.size()) {
+    uint32_t i = b0 + g.tid;
+    uint32_t is = (i < cn && fo[i] != i) ? 1u : 0u, tot, pre = g.exscan(is, &tot);
+    if (is) cand[ncand + pre] = (IdxT)i;
+    ncand += tot;
+  }
+  g.sync();
+  uint64_t rep = 0;
+  if (g.tid == 0) {
+    uint32_t skip_until = 0;
+    for (uint32_t k = 0; k < ncand; k++) {
+      uint32_t q = cand[k];
+      if (q < skip_until) continue;
+      uint32_t c = fo[q];
+      if (fo[c] == c) {  // key seen: hit
+        rep += woff[q + n] - woff[q];
+        uint32_t e = q + n < cn ? q + n : cn;
+        for (uint32_t p = q + 1; p < e; p++) if (fo[p] == p) fo[p] = (IdxT)EMPTY;
+        skip_until = q + n;
+      } else {
+        fo[c] = (IdxT)c;  // its first occurrence was skipped: this one inserts
+      }
+    }
+  }
+  g.sync();
+  return rep;  // valid on tid 0
+}
+
+struct RepArrays {
+  // per-document working arrays (shared memory for tiers S/M, global work area for tier L)
+  uint64_t* wh;    // [cap] word hashes
+  uint64_t* H;     // [cap] current n-gram key hash / paragraph hashes
+  uint32_t* woff;  // [cap + 1] byte offsets of the words in their concatenation / paragraph lengths
+};
+
+template <class G, class IdxT>
+TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t* te, const GrScratch& s, const GrCfg& cfg,
+                   int step, tb_gr_stats* out, int64_t d, RepArrays A, IdxT* tab, IdxT* cnt) {
+  (void)te;
+  const uint32_t EMPTY = IdxTraits<IdxT>::kEmpty;
+  const GrDoc gd = s.doc[d];
+  tb_gr_stats st;
+  st.reason_bits = 0; st.flags = gd.flags; st.char_len = gd.char_len; st.n_paras = 0; st.para_dup_elems = 0; st.para_dup_bytes = 0;
+  st.n_lines = 0; st.line_dup_elems = 0; st.line_dup_bytes = 0; st.n_words = 0;
+  for (int k = 0; k < TB_MAX_NGRAMS; k++) { st.top_bytes[k] = 0; st.dup_bytes[k] = 0; }
+  if (gd.empty) {  // gopher_rep.rs:60-74
+    if (g.tid == 0) { st.reason_bits = TB_GR_REASON_EMPTY; out[d] = st; a.alive[d] = 0; a.failed[d] = (int8_t)step; }
+    return;
+  }
+  const int64_t rs = ts[d];
+  const uint64_t ub = (uint64_t)(rs >> 1) + (uint64_t)d;
+  const uint64_t* wh_g = s.wh + ub; const uint32_t* wl_g = s.wl + ub;
+  const uint64_t* lh = s.lh + ub; const uint32_t* ll = s.ll + ub; const uint8_t* lg = s.lg + ub;
+  const uint32_t W = gd.W, NL = gd.NL;
+  const double text_char_len = (double)(gd.char_len ? gd.char_len : 1);
+  uint32_t reasons = 0;
+
+  // ---- lines (gopher_rep.rs:120-156)
+  uint32_t de; uint64_t db;
+  rep_dedup(g, tab, lh, ll, NL, &de, &db);
+  st.n_lines = NL; st.line_dup_elems = de; st.line_dup_bytes = db;
+  {
+    double r1 = (double)de / (double)(NL ? NL : 1u), r2 = (double)db / text_char_len;
+    if ((cfg.has & TB_GR_HAS_DUP_LINE_FRAC) && r1 > cfg.dup_line_frac) reasons |= TB_GR_REASON_DUP_LINE_FRAC;
+    if ((cfg.has & TB_GR_HAS_DUP_LINE_CHAR_FRAC) && r2 > cfg.dup_line_char_frac) reasons |= TB_GR_REASON_DUP_LINE_CHAR_FRAC;
+  }
+  // ---- paragraphs (gopher_rep.rs:80-116): fold the ordered line pieces; a single '\n' joins lines
+  // inside a paragraph, a run of >= 2 separates paragraphs.
+  uint32_t NP = 0;
+  if (g.tid == 0) {
+    Hash2 cur; cur.init(); uint32_t curlen = 0;
+    for (uint32_t k = 0; k < NL; k++) {
+      Hash2 hk = tb_unpack(lh[k]);
+      if (k == 0) { cur = hk; curlen = ll[k]; continue; }
+      if (lg[k]) { A.H[NP] = cur.pack(); A.woff[NP] = curlen; NP++; cur = hk; curlen = ll[k]; }
+      else { cur.push('\n'); cur = tb_hcat(cur, hk, tb_pow_pack(a.uc.powtab, ll[k])); curlen += 1 + ll[k]; }
+    }
+    if (NL) { A.H[NP] = cur.pack(); A.woff[NP] = curlen; NP++; }
+  }
+  NP = g.bcast(NP);
+  g.sync();
+  rep_dedup(g, tab, A.H, A.woff, NP, &de, &db);
+  st.n_paras = NP; st.para_dup_elems = de; st.para_dup_bytes = db;
+  {
+    double r1 = (double)de / (double)(NP ? NP : 1u), r2 = (double)db / text_char_len;
+    if ((cfg.has & TB_GR_HAS_DUP_PARA_FRAC) && r1 > cfg.dup_para_frac) reasons |= TB_GR_REASON_DUP_PARA_FRAC;
+    if ((cfg.has & TB_GR_HAS_DUP_PARA_CHAR_FRAC) && r2 > cfg.dup_para_char_frac) reasons |= TB_GR_REASON_DUP_PARA_CHAR_FRAC;
+  }
+  g.sync();
+
+  // ---- n-grams (gopher_rep.rs:159-196)
+  uint32_t ntop_max = 0, ndup_max = 0;
+  for (int k = 0; k < cfg.n_top; k++) ntop_max = cfg.top_n[k] > ntop_max ? cfg.top_n[k] : ntop_max;
+  for (int k = 0; k < cfg.n_dup; k++) ndup_max = cfg.dup_n[k] > ndup_max ? cfg.dup_n[k] : ndup_max;
+  if (ntop_max > W) ntop_max = W;
+  if (ndup_max > W) ndup_max = W;
+  if (ntop_max || ndup_max) {
+    // byte offsets of the words in the concatenation; word hashes into the working array
+    uint32_t run = 0;
+    for (uint32_t b0 = 0; b0 < W; b0 += g.size()) {
+      uint32_t i = b0 + g.tid, v = i < W ? wl_g[i] : 0, tot, pre = g.exscan(v, &tot);
+      if (i < W) { A.woff[i] = run + pre; if (A.wh != wh_g) A.wh[i] = wh_g[i]; }
+      run += tot;
+    }
+    if (g.tid == 0) A.woff[W] = run;
+    g.sync();
+  }
+  const uint64_t* wh = A.wh;
+  const uint32_t* woff = A.woff;
+  // -- top n-grams: keys are the " "-joined strings (find_top_duplicate, text.rs:211-238)
+  for (uint32_t n = 1; n <= ntop_max; n++) {
+    const uint32_t cn = W - n + 1;
+    for (uint32_t i = g.tid; i < cn; i += g.size()) {
+      if (n == 1) { A.H[i] = wh[i]; continue; }
+      uint32_t j = i + n - 1;
+      Hash2 jj = tb_unpack(A.H[i]); jj.push(' ');
+      A.H[i] = tb_hcat(jj, tb_unpack(wh[j]), tb_pow_pack(a.uc.powtab, woff[j + 1] - woff[j])).pack();
+    }
+    g.sync();
+    for (int k = 0; k < cfg.n_top; k++) {
+      if (cfg.top_n[k] != n) continue;
+      const uint32_t T = rep_tab_size(cn);
+      for (uint32_t i = g.tid; i < T; i += g.size()) tab[i] = (IdxT)EMPTY;
+      for (uint32_t i = g.tid; i < cn; i += g.size()) cnt[i] = 0;
+      g.sync();
+      for (uint32_t i = g.tid; i < cn; i += g.size()) {
+        // key length = concatenated bytes + (n - 1) spaces; equal joined strings <=> equal hash + length
+        uint32_t len = woff[i + n] - woff[i] + n - 1;
+        uint64_t key = A.H[i];
+        uint32_t sl = (uint32_t)tb_mix64(key ^ ((uint64_t)len << 40)) & (T - 1);
+        for (;;) {
+          uint32_t old = idx_cas(&tab[sl], EMPTY, i);
+          if (old == EMPTY) { idx_inc(&cnt[i]); break; }
+          if (A.H[old] == key && woff[old + n] - woff[old] + n - 1 == len) { idx_inc(&cnt[old]); break; }
+          sl = (sl + 1) & (T - 1);
+        }
+      }
+      g.sync();
+      uint64_t best = 0;
+      for (uint32_t i = g.tid; i < cn; i += g.size()) {
+        uint32_t c = cnt[i];
+        if (c) { uint64_t v = ((uint64_t)c << 32) | (woff[i + n] - woff[i] + n - 1); best = v > best ? v : best; }
+      }
+      best = g.max64(best);
+      uint32_t c = (uint32_t)(best >> 32), len = (uint32_t)best;
+      uint64_t v = c > 1 ? (uint64_t)len * c : 0;
+      st.top_bytes[k] = v;
+      if ((double)v / text_char_len > cfg.top_frac[k]) reasons |= 1u << (TB_GR_REASON_TOP_SHIFT + k);
+      g.sync();
+    }
+  }
+  // -- duplicate n-grams: keys are the concatenated strings (find_all_duplicate, text.rs:241-259)
+  for (uint32_t n = 1; n <= ndup_max; n++) {
+    const uint32_t cn = W - n + 1;
+    for (uint32_t i = g.tid; i < cn; i += g.size()) {
+      if (n == 1) { A.H[i] = wh[i]; continue; }
+      uint32_t j = i + n - 1;
+      A.H[i] = tb_hcat(tb_unpack(A.H[i]), tb_unpack(wh[j]), tb_pow_pack(a.uc.powtab, woff[j + 1] - woff[j])).pack();
+    }
+    g.sync();
+    for (int k = 0; k < cfg.n_dup; k++) {
+      if (cfg.dup_n[k] != n) continue;
+      const uint32_t T = rep_tab_size(cn);
+      rep_fill(g, tab, T, EMPTY);
+      bool dup = false;
+      for (uint32_t i = g.tid; i < cn; i += g.size()) {
+        uint32_t len = woff[i + n] - woff[i];
+        uint64_t key = A.H[i];
+        uint32_t sl = (uint32_t)tb_mix64(key ^ ((uint64_t)len << 40)) & (T - 1);
+        for (;;) {
+          uint32_t old = idx_cas(&tab[sl], EMPTY, i);
+          if (old == EMPTY) break;
+          if (A.H[old] == key && woff[old + n] - woff[old] == len) { idx_min(&tab[sl], i); dup = true; break; }
+          sl = (sl + 1) & (T - 1);
+        }
+      }
+      g.sync();
+      uint64_t v = 0;
+      if (g.any(dup)) {
+        // fo[i] = smallest position carrying the same key (re-probe: the slot of an existing key is stable)
+        for (uint32_t i = g.tid; i < cn; i += g.size()) {
+          uint32_t len = woff[i + n] - woff[i];
+          uint64_t key = A.H[i];
+          uint32_t sl = (uint32_t)tb_mix64(key ^ ((uint64_t)len << 40)) & (T - 1);
+          for (;;) {
+            uint32_t old = tab[sl];
+            if (A.H[old] == key && woff[old + n] - woff[old] == len) { cnt[i] = (IdxT)old; break; }
+            sl = (sl + 1) & (T - 1);
+          }
+        }
+        g.sync();
+        v = rep_dup_walk(g, cnt, tab, woff, cn, n);  // the table is dead now: reuse it for the candidate list
+      }
+      if (g.tid == 0) {
+        st.dup_bytes[k] = v;
+        if ((double)v / text_char_len > cfg.dup_frac[k]) reasons |= 1u << (TB_GR_REASON_DUP_SHIFT + k);
+      }
+      g.sync();
+    }
+  }
+  if (g.tid == 0) {
+    st.n_words = W; st.reason_bits = reasons;
+    out[d] = st;
+    if (reasons) { a.alive[d] = 0; a.failed[d] = (int8_t)step; }
+  }
+}

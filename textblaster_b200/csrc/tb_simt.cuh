@@ -40,6 +40,13 @@ struct SimtWarp {
 };
 extern thread_local SimtWarp* simt_warp;
 extern thread_local int simt_lane;
+struct SimtBlock {  // one emulated CTA of n threads (block-level collectives only)
+  int n;
+  std::barrier<> bar;
+  uint64_t box[1024];
+  explicit SimtBlock(int n_) : n(n_), bar(n_) {}
+};
+extern thread_local SimtBlock* simt_block;
 
 inline uint64_t simt_exchange_(uint64_t v, int src_lane, bool valid) {
   SimtWarp* w = simt_warp;
