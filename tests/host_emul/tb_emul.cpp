@@ -136,7 +136,7 @@ extern "C" int tbe_run_chain(const tb_step_cfg* steps, size_t n_steps, const uin
       uint8_t* smem_m = (uint8_t*)G64(TB_REP_M_SMEM / 8 + 2);
       run_warps_list(gs.lists, gs.counters[0], [&](int64_t d, int lane) { body_gr_rep_s(b, smem_s, ts, te, gs, g, (int)s, (tb_gr_stats*)stats, d, lane); });
       run_blocks(gs.lists + n, gs.counters[1], TB_REP_M_THREADS, [&](int64_t d, int tid) { body_gr_rep_m(b, smem_m, ts, te, gs, g, (int)s, (tb_gr_stats*)stats, d, tid); });
-      run_warps_list(gs.lists + 2 * n, gs.counters[2], [&](int64_t d, int lane) { body_gr_rep_l(b, ts, te, gs, g, (int)s, (tb_gr_stats*)stats, d, lane); });
+      run_blocks(gs.lists + 2 * n, gs.counters[2], TB_REP_L_THREADS, [&](int64_t d, int tid) { body_gr_rep_l(b, nullptr, ts, te, gs, g, (int)s, (tb_gr_stats*)stats, d, tid); });
     } else if (sc.type == TB_STEP_C4_QUALITY) {
       if (!sc.u.c4.split_paragraph || has_c4) return 5;
       C4Cfg cfg = tb_c4cfg_of(sc.u.c4);

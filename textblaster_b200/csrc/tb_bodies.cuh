@@ -196,18 +196,17 @@ TB_D void body_gr_scan(const KBatch& a, const uint16_t* s_ascii, const int64_t* 
 // ---------------------------------------------------------------------------------------------
 // GopherRepetitionFilter, pass 2 (tb_rep.cuh): three tiers by document size
 // ---------------------------------------------------------------------------------------------
-#define TB_REP_S_SMEM (TB_REP_S_CAP * 8 + TB_REP_S_CAP * 8 + (TB_REP_S_CAP + 2) * 4 + 2 * TB_REP_S_CAP * 2 + TB_REP_S_CAP * 2)
-#define TB_REP_M_SMEM (TB_REP_M_CAP * 8 + TB_REP_M_CAP * 8 + (TB_REP_M_CAP + 2) * 4 + 2 * TB_REP_M_CAP * 2 + TB_REP_M_CAP * 2 + 64 * 8)
+#define TB_REP_S_SMEM (TB_REP_S_CAP * 8 + (TB_REP_S_CAP + 2) * 4 + 2 * TB_REP_S_CAP * 4 + TB_REP_S_CAP * 2)
+#define TB_REP_M_SMEM (TB_REP_M_CAP * 8 + (TB_REP_M_CAP + 2) * 4 + 2 * TB_REP_M_CAP * 4 + TB_REP_M_CAP * 2 + 64 * 8)
 
 // tier S: one warp, working arrays carved from `smem` (TB_REP_S_SMEM bytes, 8-byte aligned)
 TB_D void body_gr_rep_s(const KBatch& a, uint8_t* smem, const int64_t* ts, const int64_t* te, const GrScratch& s,
                         const GrCfg& cfg, int step, tb_gr_stats* out, int64_t d, int lane) {
   RepArrays A;
-  A.wh = (uint64_t*)smem;
-  A.H = A.wh + TB_REP_S_CAP;
+  A.H = (uint64_t*)smem;
   A.woff = (uint32_t*)(A.H + TB_REP_S_CAP);
-  uint16_t* tab = (uint16_t*)(A.woff + TB_REP_S_CAP + 2);
-  uint16_t* cnt = tab + 2 * TB_REP_S_CAP;
+  uint32_t* tab = A.woff + TB_REP_S_CAP + 2;
+  uint16_t* cnt = (uint16_t*)(tab + 2 * TB_REP_S_CAP);
   WarpGroup g{lane};
   rep_body<WarpGroup, uint16_t>(g, a, ts, te, s, cfg, step, out, d, A, tab, cnt);
 }
@@ -215,29 +214,27 @@ TB_D void body_gr_rep_s(const KBatch& a, uint8_t* smem, const int64_t* ts, const
 TB_D void body_gr_rep_m(const KBatch& a, uint8_t* smem, const int64_t* ts, const int64_t* te, const GrScratch& s,
                         const GrCfg& cfg, int step, tb_gr_stats* out, int64_t d, int tid) {
   RepArrays A;
-  A.wh = (uint64_t*)smem;
-  A.H = A.wh + TB_REP_M_CAP;
+  A.H = (uint64_t*)smem;
   A.woff = (uint32_t*)(A.H + TB_REP_M_CAP);
-  uint16_t* tab = (uint16_t*)(A.woff + TB_REP_M_CAP + 2);
-  uint16_t* cnt = tab + 2 * TB_REP_M_CAP;
+  uint32_t* tab = A.woff + TB_REP_M_CAP + 2;
+  uint16_t* cnt = (uint16_t*)(tab + 2 * TB_REP_M_CAP);
   BlockGroup g{tid, (uint64_t*)(cnt + TB_REP_M_CAP)};
   rep_body<BlockGroup, uint16_t>(g, a, ts, te, s, cfg, step, out, d, A, tab, cnt);
 }
-// tier L: one warp, working arrays in the document's region of the global work area
-TB_D void body_gr_rep_l(const KBatch& a, const int64_t* ts, const int64_t* te, const GrScratch& s, const GrCfg& cfg, int step,
-                        tb_gr_stats* out, int64_t d, int lane) {
+// tier L: one CTA, working arrays in the document's region of the global work area; `red` = 64 u64 of shared scratch
+TB_D void body_gr_rep_l(const KBatch& a, uint64_t* red, const int64_t* ts, const int64_t* te, const GrScratch& s,
+                        const GrCfg& cfg, int step, tb_gr_stats* out, int64_t d, int tid) {
   const int64_t rs = ts[d], re = te[d];
   const uint64_t ub = (uint64_t)(rs >> 1) + (uint64_t)d;
   const uint32_t U = (uint32_t)((re - rs) >> 1) + 1u;
   uint32_t* work = s.work + ub * TB_REP_K + (uint64_t)d * TB_REP_DOC_EXTRA;
   RepArrays A;
-  A.wh = (uint64_t*)(s.wh + ub);  // read in place
   A.H = (uint64_t*)work;
   A.woff = (uint32_t*)(A.H + U);
   uint32_t* tab = A.woff + U + 2;
-  uint32_t* cnt = tab + 4u * U + TB_REP_MIN_TABLE;
-  WarpGroup g{lane};
-  rep_body<WarpGroup, uint32_t>(g, a, ts, te, s, cfg, step, out, d, A, tab, cnt);
+  uint32_t* cnt = tab + 2u * U + TB_REP_MIN_TABLE;
+  BlockGroup g{tid, red};
+  rep_body<BlockGroup, uint32_t>(g, a, ts, te, s, cfg, step, out, d, A, tab, cnt);
 }
 
 // ---------------------------------------------------------------------------------------------

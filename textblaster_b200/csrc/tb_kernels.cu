@@ -9,7 +9,7 @@
 namespace {
 
 __device__ __forceinline__ void load_ascii(uint16_t* s_ascii, const UcTables& uc) {
-  if (threadIdx.x < 128) s_ascii[threadIdx.x] = uc.stage2[(uint32_t)uc.stage1[0] * 256u + threadIdx.x];
+  for (uint32_t i = threadIdx.x; i < 128; i += blockDim.x) s_ascii[i] = uc.stage2[(uint32_t)uc.stage1[0] * 256u + i];
   __syncthreads();
 }
 __device__ __forceinline__ int64_t warp_doc() { return ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; }
@@ -74,17 +74,18 @@ __global__ void __launch_bounds__(TB_REP_M_THREADS) k_gr_rep_m(KBatch a, const i
     body_gr_rep_m(a, dsmem, ts, te, s, cfg, step, out, (int64_t)s.lists[(uint64_t)s.n + i], (int)threadIdx.x);
   }
 }
-__global__ void __launch_bounds__(32) k_gr_rep_l(KBatch a, const int64_t* ts, const int64_t* te, GrScratch s, GrCfg cfg,
-                                                 int step, tb_gr_stats* out) {
-  const int lane = threadIdx.x;
+__global__ void __launch_bounds__(TB_REP_L_THREADS) k_gr_rep_l(KBatch a, const int64_t* ts, const int64_t* te, GrScratch s,
+                                                               GrCfg cfg, int step, tb_gr_stats* out) {
+  __shared__ uint64_t s_red[64];
+  __shared__ uint32_t s_i;
   const uint32_t count = s.counters[2];
   for (;;) {
-    uint32_t i = 0;
-    if (lane == 0) i = atomicAdd(&s.counters[6], 1u);
-    i = __shfl_sync(0xFFFFFFFFu, i, 0);
+    __syncthreads();
+    if (threadIdx.x == 0) s_i = atomicAdd(&s.counters[6], 1u);
+    __syncthreads();
+    uint32_t i = s_i;
     if (i >= count) break;
-    body_gr_rep_l(a, ts, te, s, cfg, step, out, (int64_t)s.lists[2 * (uint64_t)s.n + i], lane);
-    __syncwarp();
+    body_gr_rep_l(a, s_red, ts, te, s, cfg, step, out, (int64_t)s.lists[2 * (uint64_t)s.n + i], (int)threadIdx.x);
   }
 }
 __global__ void __launch_bounds__(TB_BLOCK) k_c4_a(KBatch a, C4Cfg cfg, C4Scratch s) {
@@ -178,9 +179,9 @@ void tb_launch_gr_scan(cudaStream_t st, const KBatch& b, const int64_t* ts, cons
 void tb_launch_gr_rep(cudaStream_t st, const KBatch& b, const int64_t* ts, const int64_t* te, const GrScratch& s,
                       const GrCfg& cfg, int step, tb_gr_stats* out, int sm_count, int tier) {
   if (!b.n) return;
-  if (tier == 0) k_gr_rep_s<<<sm_count * 16, 32, 0, st>>>(b, ts, te, s, cfg, step, out);
-  else if (tier == 1) k_gr_rep_m<<<sm_count * 2, TB_REP_M_THREADS, TB_REP_M_SMEM, st>>>(b, ts, te, s, cfg, step, out);
-  else k_gr_rep_l<<<sm_count * 8, 32, 0, st>>>(b, ts, te, s, cfg, step, out);
+  if (tier == 0) k_gr_rep_s<<<sm_count * 20, 32, 0, st>>>(b, ts, te, s, cfg, step, out);
+  else if (tier == 1) k_gr_rep_m<<<sm_count * 5, TB_REP_M_THREADS, TB_REP_M_SMEM, st>>>(b, ts, te, s, cfg, step, out);
+  else k_gr_rep_l<<<sm_count * 2, TB_REP_L_THREADS, 0, st>>>(b, ts, te, s, cfg, step, out);
 }
 int tb_kernels_init() {
   return (int)cudaFuncSetAttribute(k_gr_rep_m, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TB_REP_M_SMEM);

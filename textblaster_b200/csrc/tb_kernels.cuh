@@ -54,7 +54,7 @@ struct GrScratch {
   uint32_t* counters;                       // [8]: list lengths [0..2], work cursors [4..6]
   int64_t n;
 };
-#define TB_REP_K 8u           // tier-L words per unit: H[2U] woff[U+1] tab[4U+16] cnt[U]
+#define TB_REP_K 6u           // tier-L words per unit: H[2U] woff[U+2] tab[2U+16] cnt[U]
 #define TB_REP_DOC_EXTRA 20u  // words: 16 (minimum table) + 1 (woff tail) + pad
 #define TB_REP_MIN_TABLE 16u
 

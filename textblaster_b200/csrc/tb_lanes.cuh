@@ -17,7 +17,10 @@ struct SwEntry { uint64_t lo, hi, ext; uint32_t len, used; };
 struct SwTable { const SwEntry* e; uint32_t mask, maxlen; };
 
 TB_HD uint64_t sw_slot_hash(uint64_t lo, uint64_t hi, uint64_t ext, uint32_t len) {
-  return tb_mix64(lo ^ (hi * 0x9E3779B97F4A7C15ull) ^ (ext + len));
+  uint32_t h = (uint32_t)lo * 0x9E3779B1u ^ (uint32_t)(lo >> 32) * 0x85EBCA77u ^ (uint32_t)hi * 0xC2B2AE3Du ^
+               (uint32_t)(hi >> 32) * 0x27D4EB2Fu ^ (uint32_t)ext ^ (len * 0x165667B1u);
+  h ^= h >> 15; h *= 0x2C1B3C6Du; h ^= h >> 13;
+  return h;
 }
 TB_HD bool sw_lookup(const SwTable& sw, const LowKey& k) {
   if (k.len == 0 || k.len > sw.maxlen) return false;
@@ -301,7 +304,13 @@ TB_HD uint32_t c4_line_end_flags(const Classifier& C, const TextRange& R, int64_
 }
 // javascript / policy substrings starting at byte i (lower-cased compare)
 TB_HD uint32_t c4_pattern_flags(const uint8_t* t, int64_t i, int64_t re, uint32_t b, bool js, bool policy) {
-  uint32_t fb = (b - 'A') < 26u ? b + 32u : b;
+  uint32_t fb = b | 0x20u;
+  // cheap reject: only j / t / p / c / u can start a pattern, and the next two bytes must continue it
+  // ("jav", "ter", "pri", "coo", "use"); the exact (Kelvin-sign aware) compare runs on the few survivors
+  if (!(fb == 'j' || fb == 't' || fb == 'p' || fb == 'c' || fb == 'u') || i + 2 >= re) return 0;
+  uint32_t b1 = tb_byte(t, i + 1) | 0x20u, b2 = tb_byte(t, i + 2) | 0x20u;
+  uint32_t tri = (fb << 16) | (b1 << 8) | b2;
+  if (tri != 0x6A6176u && tri != 0x746572u && tri != 0x707269u && tri != 0x636F6Fu && tri != 0x757365u) return 0;
   if (js && fb == 'j') return c4_fold_match(t, i, re, "javascript", 10) ? C4L_JS : 0;
   if (!policy) return 0;
   switch (fb) {

@@ -1,8 +1,8 @@
 // tb_rep.cuh -- GopherRepetitionFilter pass 2: duplicate lines / paragraphs, top n-grams and
 // duplicate n-grams of one document, written once against a "group" of cooperating threads:
-//   tier S  one warp  per document, all working arrays in shared memory   (W, NL <= 512)
-//   tier M  one CTA   per document, all working arrays in shared memory   (W, NL <= 4096)
-//   tier L  one warp  per document, working arrays in the global work area (anything larger)
+//   tier S  one warp  per document, working arrays in shared memory        (W, NL <= 512)
+//   tier M  one CTA   per document, working arrays in shared memory        (W, NL <= 2048)
+//   tier L  one CTA   per document, working arrays in the global work area (anything larger; L2 resident)
 // Replaces text.rs:197-259 as called from gopher_rep.rs:86-196.
 //
 // Open-addressing tables hold element indices; the keys live in the arrays (equality = 62-bit
@@ -14,8 +14,9 @@
 #include "tb_simt.cuh"
 
 #define TB_REP_S_CAP 512u
-#define TB_REP_M_CAP 4096u
+#define TB_REP_M_CAP 2048u
 #define TB_REP_M_THREADS 256
+#define TB_REP_L_THREADS 512
 
 // ---- thread groups ---------------------------------------------------------------------------
 struct WarpGroup {
@@ -115,69 +116,46 @@ template <class IdxT> struct IdxTraits;
 template <> struct IdxTraits<uint16_t> { static constexpr uint32_t kEmpty = 0xFFFFu; };
 template <> struct IdxTraits<uint32_t> { static constexpr uint32_t kEmpty = 0xFFFFFFFFu; };
 
-// atomics on 16-bit table slots: CAS on the containing 32-bit word
+// table slots are 32-bit (native atomics); the per-position counters may be 16-bit in shared memory
 TB_D uint32_t idx_cas(uint32_t* a, uint32_t cmp, uint32_t val) { return simt_cas(a, cmp, val); }
-TB_D uint32_t idx_cas(uint16_t* a, uint32_t cmp, uint32_t val) {
-  uint32_t* w = (uint32_t*)((uintptr_t)a & ~(uintptr_t)3);
-  const uint32_t sh = ((uintptr_t)a & 2) ? 16u : 0u;
-  uint32_t cur = *(volatile uint32_t*)w;
-  for (;;) {
-    uint32_t have = (cur >> sh) & 0xFFFFu;
-    if (have != cmp) return have;
-    uint32_t want = (cur & ~(0xFFFFu << sh)) | (val << sh);
-    uint32_t old = simt_cas(w, cur, want);
-    if (old == cur) return cmp;
-    cur = old;
-  }
-}
 TB_D void idx_min(uint32_t* a, uint32_t val) { simt_atomic_min(a, val); }
-TB_D void idx_min(uint16_t* a, uint32_t val) {
-  uint32_t* w = (uint32_t*)((uintptr_t)a & ~(uintptr_t)3);
-  const uint32_t sh = ((uintptr_t)a & 2) ? 16u : 0u;
-  uint32_t cur = *(volatile uint32_t*)w;
-  for (;;) {
-    uint32_t have = (cur >> sh) & 0xFFFFu;
-    if (have <= val) return;
-    uint32_t want = (cur & ~(0xFFFFu << sh)) | (val << sh);
-    uint32_t old = simt_cas(w, cur, want);
-    if (old == cur) return;
-    cur = old;
-  }
-}
 TB_D void idx_inc(uint32_t* a) { simt_atomic_add(a, 1u); }
 TB_D void idx_inc(uint16_t* a) {
   uint32_t* w = (uint32_t*)((uintptr_t)a & ~(uintptr_t)3);
   simt_atomic_add(w, ((uintptr_t)a & 2) ? 0x10000u : 1u);  // counts stay < 65536, no carry across halves
 }
 
-TB_D uint32_t rep_tab_size(uint32_t count) {
-  uint32_t t = TB_REP_MIN_TABLE;
-  while (t < 2u * count) t <<= 1;
-  return t;
+// table size: load factor 0.5; any size works because slots are picked by multiply-high
+TB_D uint32_t rep_tab_size(uint32_t count) { return 2u * count < TB_REP_MIN_TABLE ? TB_REP_MIN_TABLE : 2u * count; }
+TB_D uint32_t rep_slot(uint64_t key, uint32_t len, uint32_t T) {
+  uint32_t h = ((uint32_t)(key >> 32) * 0x9E3779B1u) ^ ((uint32_t)key * 0x85EBCA77u) ^ (len * 0xC2B2AE3Du);
+  h ^= h >> 15; h *= 0x2C1B3C6Du; h ^= h >> 13;
+  return (uint32_t)(((uint64_t)h * T) >> 32);
 }
-template <class G, class IdxT>
-TB_D void rep_fill(const G& g, IdxT* a, uint32_t n, uint32_t v) {
-  for (uint32_t i = g.tid; i < n; i += g.size()) a[i] = (IdxT)v;
+TB_D uint32_t rep_next(uint32_t sl, uint32_t T) { return sl + 1 == T ? 0u : sl + 1; }
+template <class G>
+TB_D void rep_fill(const G& g, uint32_t* a, uint32_t n, uint32_t v) {
+  for (uint32_t i = g.tid; i < n; i += g.size()) a[i] = v;
   g.sync();
 }
 
 // find_duplicates (text.rs:197-208) over n pieces: dup_elems = n - distinct, dup_bytes = total - distinct bytes
-template <class G, class IdxT>
-TB_D void rep_dedup(const G& g, IdxT* tab, const uint64_t* h, const uint32_t* len, uint32_t n, uint32_t* dup_elems,
+template <class G>
+TB_D void rep_dedup(const G& g, uint32_t* tab, const uint64_t* h, const uint32_t* len, uint32_t n, uint32_t* dup_elems,
                     uint64_t* dup_bytes) {
-  const uint32_t EMPTY = IdxTraits<IdxT>::kEmpty;
+  const uint32_t EMPTY = 0xFFFFFFFFu;
   uint32_t T = rep_tab_size(n);
   rep_fill(g, tab, T, EMPTY);
   uint32_t distinct = 0; uint64_t dbytes = 0, total = 0;
   for (uint32_t i = g.tid; i < n; i += g.size()) {
     uint64_t hi = h[i]; uint32_t li = len[i];
-    uint32_t sl = (uint32_t)tb_mix64(hi ^ ((uint64_t)li << 40)) & (T - 1);
+    uint32_t sl = rep_slot(hi, li, T);
     total += li;
     for (;;) {
       uint32_t old = idx_cas(&tab[sl], EMPTY, i);
       if (old == EMPTY) { distinct++; dbytes += li; break; }
       if (h[old] == hi && len[old] == li) break;
-      sl = (sl + 1) & (T - 1);
+      sl = rep_next(sl, T);
     }
   }
   g.sync();
@@ -191,14 +169,14 @@ TB_D void rep_dedup(const G& g, IdxT* tab, const uint64_t* h, const uint32_t* le
 // removed; a later occurrence of such a key then inserts instead of hitting.  Only candidates
 // (fo[q] < q), in increasing order, need the sequential pass.
 template <class G, class IdxT>
-TB_D uint64_t rep_dup_walk(const G& g, IdxT* fo, IdxT* cand, const uint32_t* woff, uint32_t cn, uint32_t n) {
+TB_D uint64_t rep_dup_walk(const G& g, IdxT* fo, uint32_t* cand, const uint32_t* woff, uint32_t cn, uint32_t n) {
   const uint32_t EMPTY = IdxTraits<IdxT>::kEmpty;
   // ordered compaction of the candidates
   uint32_t ncand = 0;
   for (uint32_t b0 = 0; b0 < cn; b0 += g.size()) {
     uint32_t i = b0 + g.tid;
     uint32_t is = (i < cn && fo[i] != i) ? 1u : 0u, tot, pre = g.exscan(is, &tot);
-    if (is) cand[ncand + pre] = (IdxT)i;
+    if (is) cand[ncand + pre] = i;
     ncand += tot;
   }
   g.sync();
@@ -225,16 +203,15 @@ TB_D uint64_t rep_dup_walk(const G& g, IdxT* fo, IdxT* cand, const uint32_t* wof
 
 struct RepArrays {
   // per-document working arrays (shared memory for tiers S/M, global work area for tier L)
-  uint64_t* wh;    // [cap] word hashes
   uint64_t* H;     // [cap] current n-gram key hash / paragraph hashes
   uint32_t* woff;  // [cap + 1] byte offsets of the words in their concatenation / paragraph lengths
 };
 
 template <class G, class IdxT>
 TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t* te, const GrScratch& s, const GrCfg& cfg,
-                   int step, tb_gr_stats* out, int64_t d, RepArrays A, IdxT* tab, IdxT* cnt) {
+                   int step, tb_gr_stats* out, int64_t d, RepArrays A, uint32_t* tab, IdxT* cnt) {
   (void)te;
-  const uint32_t EMPTY = IdxTraits<IdxT>::kEmpty;
+  const uint32_t EMPTY = 0xFFFFFFFFu;
   const GrDoc gd = s.doc[d];
   tb_gr_stats st;
   st.reason_bits = 0; st.flags = gd.flags; st.char_len = gd.char_len; st.n_paras = 0; st.para_dup_elems = 0; st.para_dup_bytes = 0;
@@ -296,13 +273,13 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
     uint32_t run = 0;
     for (uint32_t b0 = 0; b0 < W; b0 += g.size()) {
       uint32_t i = b0 + g.tid, v = i < W ? wl_g[i] : 0, tot, pre = g.exscan(v, &tot);
-      if (i < W) { A.woff[i] = run + pre; if (A.wh != wh_g) A.wh[i] = wh_g[i]; }
+      if (i < W) A.woff[i] = run + pre;
       run += tot;
     }
     if (g.tid == 0) A.woff[W] = run;
     g.sync();
   }
-  const uint64_t* wh = A.wh;
+  const uint64_t* wh = wh_g;  // read in place (coalesced, once per pass)
   const uint32_t* woff = A.woff;
   // -- top n-grams: keys are the " "-joined strings (find_top_duplicate, text.rs:211-238)
   for (uint32_t n = 1; n <= ntop_max; n++) {
@@ -317,19 +294,19 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
     for (int k = 0; k < cfg.n_top; k++) {
       if (cfg.top_n[k] != n) continue;
       const uint32_t T = rep_tab_size(cn);
-      for (uint32_t i = g.tid; i < T; i += g.size()) tab[i] = (IdxT)EMPTY;
+      for (uint32_t i = g.tid; i < T; i += g.size()) tab[i] = EMPTY;
       for (uint32_t i = g.tid; i < cn; i += g.size()) cnt[i] = 0;
       g.sync();
       for (uint32_t i = g.tid; i < cn; i += g.size()) {
         // key length = concatenated bytes + (n - 1) spaces; equal joined strings <=> equal hash + length
         uint32_t len = woff[i + n] - woff[i] + n - 1;
         uint64_t key = A.H[i];
-        uint32_t sl = (uint32_t)tb_mix64(key ^ ((uint64_t)len << 40)) & (T - 1);
+        uint32_t sl = rep_slot(key, len, T);
         for (;;) {
           uint32_t old = idx_cas(&tab[sl], EMPTY, i);
           if (old == EMPTY) { idx_inc(&cnt[i]); break; }
           if (A.H[old] == key && woff[old + n] - woff[old] + n - 1 == len) { idx_inc(&cnt[old]); break; }
-          sl = (sl + 1) & (T - 1);
+          sl = rep_next(sl, T);
         }
       }
       g.sync();
@@ -363,12 +340,12 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
       for (uint32_t i = g.tid; i < cn; i += g.size()) {
         uint32_t len = woff[i + n] - woff[i];
         uint64_t key = A.H[i];
-        uint32_t sl = (uint32_t)tb_mix64(key ^ ((uint64_t)len << 40)) & (T - 1);
+        uint32_t sl = rep_slot(key, len, T);
         for (;;) {
           uint32_t old = idx_cas(&tab[sl], EMPTY, i);
           if (old == EMPTY) break;
           if (A.H[old] == key && woff[old + n] - woff[old] == len) { idx_min(&tab[sl], i); dup = true; break; }
-          sl = (sl + 1) & (T - 1);
+          sl = rep_next(sl, T);
         }
       }
       g.sync();
@@ -378,11 +355,11 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
         for (uint32_t i = g.tid; i < cn; i += g.size()) {
           uint32_t len = woff[i + n] - woff[i];
           uint64_t key = A.H[i];
-          uint32_t sl = (uint32_t)tb_mix64(key ^ ((uint64_t)len << 40)) & (T - 1);
+          uint32_t sl = rep_slot(key, len, T);
           for (;;) {
             uint32_t old = tab[sl];
             if (A.H[old] == key && woff[old + n] - woff[old] == len) { cnt[i] = (IdxT)old; break; }
-            sl = (sl + 1) & (T - 1);
+            sl = rep_next(sl, T);
           }
         }
         g.sync();
