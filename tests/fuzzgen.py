@@ -94,3 +94,15 @@ def english_doc(rng, target_bytes):
         if rng.random() < 0.3:
             out.append("")
     return "\n".join(out)
+
+
+def ascii_doc(rng, n_tokens=400):
+    """Pure-ASCII text dense in the characters the UAX #29 word rules care about (Mid*, quotes, '_',
+    digits, runs of spaces, tabs, VT/FF) -- exercises the bit-parallel fast path of the word pass."""
+    atoms = ["a", "b", "Z", "0", "7", ".", ",", ";", ":", "'", "\"", "_", "-", " ", " ", " ", "  ", "\t", "\n", "\n\n",
+             "\x0b", "\x0c", "(", ")", "#", "...", "don't", "3.14", "1,000", "a.b.c", "x_y", "_x", "9_", "a:b", "a'", "'a", "1.",
+             ".1", "a..b", "1,,2", "a'b'c", "U.S.A.", "the", "of", "and", "javascript", "privacy policy", "[1]", "[2, 3]", "{", "!", "?"]
+    out = []
+    for _ in range(n_tokens):
+        out.append(rng.choice(atoms))
+    return "".join(out)

@@ -95,8 +95,12 @@ extern "C" int tbe_run_chain(const tb_step_cfg* steps, size_t n_steps, const uin
   { uint32_t a = 1, b = 1; for (int i = 0; i < TB_POWTAB; i++) { pw[i] = ((uint64_t)a << 32) | b; a = tb_mm(a, TB_B1); b = tb_mm(b, TB_B2); } }
   UcTables uc{tb_uc_stage1, tb_uc_stage2, &tb_uc_lower[0][0], &tb_uc_cased[0][0], &tb_uc_caseign[0][0], pw.data(),
               TB_UC_NLOWER, TB_UC_NCASED, TB_UC_NCASEIGN};
-  uint16_t ascii[128];
-  for (int i = 0; i < 128; i++) ascii[i] = tb_uc_stage2[(uint32_t)tb_uc_stage1[0] * 256u + i];
+  uint16_t ascii[192];
+  for (int i = 0; i < 128; i++) {
+    ascii[i] = tb_uc_stage2[(uint32_t)tb_uc_stage1[0] * 256u + i];
+    ((uint8_t*)(ascii + 128))[i] = (uint8_t)tb_ascii_flags(ascii[i]);
+    if (!tb_ascii_class_ok(ascii[i])) return 7;  // the ASCII fast path would not be exact
+  }
 
   uint8_t* text = G8((size_t)nb + 64);
   if (nb) memcpy(text, utf8 + base, (size_t)nb);

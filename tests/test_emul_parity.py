@@ -49,6 +49,14 @@ def test_multi_tile_documents(name):
     _check(name, texts)
 
 
+@pytest.mark.parametrize("name", ["gq_open", "gq_shipped", "gr_open", "c4_lax", "c4_then_open", "baseline_order"])
+def test_ascii_fast_path(name):
+    rng = random.Random(17)
+    texts = [fuzzgen.ascii_doc(rng, rng.choice([5, 40, 400, 1500])) for _ in range(60)]
+    texts += ["a" * 31 + " " + "b" * 40, "x" * 100, "ab " * 200, "a.b" * 30, "1,2" * 40, "it's " * 50, "a\r\nb c\r\n" * 20]
+    _check(name, texts)
+
+
 def test_repetition_tiers():
     """tb_rep.cuh picks shared-memory (warp / CTA) or global work areas by document size; a document
     with many repeated n-grams exercises the candidate walk in each tier."""

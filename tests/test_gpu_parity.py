@@ -92,6 +92,15 @@ def test_synthetic_c4_corpus(name):
     assert 0 < int(res.keep.sum()) < res.n_docs or name == "shipped_order"
 
 
+@pytest.mark.parametrize("name", ["gq_open", "gq_shipped", "gr_open", "c4_lax", "c4_then_open", "baseline_order"])
+def test_ascii_fast_path(name):
+    """pure-ASCII text dense in Mid*/quote/underscore/digit patterns: the bit-parallel word pass"""
+    rng = random.Random(19)
+    texts = [fuzzgen.ascii_doc(rng, rng.choice([5, 40, 400, 1500, 6000])) for _ in range(600)]
+    texts += ["a" * 31 + " " + "b" * 40, "x" * 100, "ab " * 200, "a.b" * 30, "1,2" * 40, "it's " * 50, "a\r\nb c\r\n" * 20]
+    check_texts(name, texts)
+
+
 def test_int32_offsets_and_chunking():
     """Arrow StringArray offsets are i32 (parquet_reader.rs:108-112); tiny chunks force the
     double-buffered multi-chunk path and must not change any result."""

@@ -59,6 +59,7 @@ TB_D void body_validate_utf8(const uint8_t* t, const int64_t* rs, const int64_t*
 TB_D void body_gq(const KBatch& a, const uint16_t* s_ascii, const SwTable& sw, const GqCfg& cfg, int step,
                   tb_gq_stats* out, int64_t d, int lane) {
   Classifier C{s_ascii, a.uc};
+  C.key_maxlen = sw.maxlen;
   TextRange R{a.text, a.rs[d], a.re[d]};
   GqAcc acc; acc.zero();
   for (int64_t base = R.rs; base < R.re; base += TB_TILE) {
@@ -302,7 +303,7 @@ TB_D void body_c4_b(const KBatch& a, const uint16_t* s_ascii, const C4Cfg& cfg, 
     if (p0 < R.re) {
       uint64_t lbase = lb + nl + pre;
       C4bSink sink{s.lwc, s.lmax, lbase, p0, p1, nlmask};
-      tb_walk_words<0>(C, R, p0, p1, sink);
+      tb_walk_words_fast<0>(C, R, p0, p1, sink);
       uint32_t line = 0, fl = 0;
       for (int64_t i = p0; i < p1; i++) {
         uint32_t b = t[i];

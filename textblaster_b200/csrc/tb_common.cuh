@@ -83,8 +83,10 @@ TB_HD uint32_t tb_cinfo_trie(const UcTables& u, uint32_t cp) {
 
 // Classifier: ASCII from a 128-entry table (shared memory on the device), the rest via the trie.
 struct Classifier {
-  const uint16_t* ascii;  // [128]
+  const uint16_t* ascii;  // [128] cinfo of the ASCII code points, followed by 128 bytes of fast-path class flags
   UcTables u;
+  uint32_t key_maxlen = 0xFFFFFFFFu;  // longest stop word: longer words need no lower-cased key
+  TB_HD const uint8_t* aflags() const { return (const uint8_t*)(ascii + 128); }
   TB_HD uint32_t of_cp(uint32_t cp) const { return cp < 128u ? ascii[cp] : tb_cinfo_trie(u, cp); }
   // classify the code point starting at i; returns cinfo, sets *len (and *cp)
   TB_HD uint32_t at(const uint8_t* t, int64_t i, int* len, uint32_t* cp) const {

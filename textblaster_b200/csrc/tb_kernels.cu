@@ -8,8 +8,14 @@
 
 namespace {
 
+// ASCII row of the cinfo table + the fast path's per-byte class flags (tb_fastwords.cuh) into shared memory
 __device__ __forceinline__ void load_ascii(uint16_t* s_ascii, const UcTables& uc) {
-  for (uint32_t i = threadIdx.x; i < 128; i += blockDim.x) s_ascii[i] = uc.stage2[(uint32_t)uc.stage1[0] * 256u + i];
+  uint8_t* af = (uint8_t*)(s_ascii + 128);
+  for (uint32_t i = threadIdx.x; i < 128; i += blockDim.x) {
+    uint16_t ci = uc.stage2[(uint32_t)uc.stage1[0] * 256u + i];
+    s_ascii[i] = ci;
+    af[i] = (uint8_t)tb_ascii_flags(ci);
+  }
   __syncthreads();
 }
 __device__ __forceinline__ int64_t warp_doc() { return ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; }
@@ -26,20 +32,20 @@ __global__ void __launch_bounds__(TB_BLOCK) k_validate_utf8(const uint8_t* t, co
   if (d < n) body_validate_utf8(t, rs, re, bad, d, threadIdx.x & 31);
 }
 __global__ void __launch_bounds__(TB_BLOCK) k_gq(KBatch a, SwTable sw, GqCfg cfg, int step, tb_gq_stats* out) {
-  __shared__ uint16_t s_ascii[128];
+  __shared__ uint16_t s_ascii[192];
   load_ascii(s_ascii, a.uc);
   int64_t d = warp_doc();
   if (d >= a.n || !a.alive[d]) return;
   body_gq(a, s_ascii, sw, cfg, step, out, d, threadIdx.x & 31);
 }
 __global__ void k_trim(KBatch a, int64_t* ts, int64_t* te) {
-  __shared__ uint16_t s_ascii[128];
+  __shared__ uint16_t s_ascii[192];
   load_ascii(s_ascii, a.uc);
   int64_t d = thread_doc();
   if (d < a.n) body_trim(a, s_ascii, ts, te, d);
 }
 __global__ void __launch_bounds__(TB_BLOCK) k_gr_scan(KBatch a, const int64_t* ts, const int64_t* te, GrScratch s) {
-  __shared__ uint16_t s_ascii[128];
+  __shared__ uint16_t s_ascii[192];
   load_ascii(s_ascii, a.uc);
   int64_t d = warp_doc();
   if (d >= a.n || !a.alive[d]) return;
@@ -89,14 +95,14 @@ __global__ void __launch_bounds__(TB_REP_L_THREADS) k_gr_rep_l(KBatch a, const i
   }
 }
 __global__ void __launch_bounds__(TB_BLOCK) k_c4_a(KBatch a, C4Cfg cfg, C4Scratch s) {
-  __shared__ uint16_t s_ascii[128];
+  __shared__ uint16_t s_ascii[192];
   load_ascii(s_ascii, a.uc);
   int64_t d = warp_doc();
   if (d >= a.n || !a.alive[d]) return;
   body_c4_a(a, s_ascii, cfg, s, d, threadIdx.x & 31);
 }
 __global__ void __launch_bounds__(TB_BLOCK) k_c4_b(KBatch a, C4Cfg cfg, C4Scratch s) {
-  __shared__ uint16_t s_ascii[128];
+  __shared__ uint16_t s_ascii[192];
   load_ascii(s_ascii, a.uc);
   int64_t d = warp_doc();
   if (d >= a.n || !a.alive[d] || s.docflags[d] || s.nlines[d] == 0) return;
@@ -109,7 +115,7 @@ __global__ void __launch_bounds__(TB_BLOCK) k_c4_c(KBatch a, C4Cfg cfg, C4Scratc
 }
 __global__ void __launch_bounds__(TB_BLOCK) k_c4_d(KBatch a, C4Cfg cfg, C4Scratch s, int step, tb_c4_stats* out,
                                                    uint8_t* rewritten, int64_t* rs_out, int64_t* re_out) {
-  __shared__ uint16_t s_ascii[128];
+  __shared__ uint16_t s_ascii[192];
   load_ascii(s_ascii, a.uc);
   int64_t d = warp_doc();
   if (d >= a.n || !a.alive[d]) return;

@@ -4,6 +4,7 @@
 #pragma once
 #include "tb_common.cuh"
 #include "tb_sentmachine.cuh"
+#include "tb_fastwords.cuh"
 #include "tb_wordmachine.cuh"
 
 #define TB_STRETCH 32
@@ -84,7 +85,7 @@ TB_HD bool gq_line_is_bullet(const Classifier& C, const TextRange& R, int64_t s)
 TB_HD void gq_lane(const Classifier& C, const TextRange& R, const SwTable& sw, int64_t p0, int64_t p1, GqAcc& acc) {
   const uint8_t* t = R.t;
   GqSink sink{&C, t, &sw, &acc};
-  acc.flags |= tb_walk_words<WM_NEED_ALPHA | WM_NEED_LOWKEY>(C, R, p0, p1, sink) & CI_COMPLEX;
+  acc.flags |= tb_walk_words_fast<WM_NEED_ALPHA | WM_NEED_LOWKEY>(C, R, p0, p1, sink) & CI_COMPLEX;
   uint32_t prev = p0 > R.rs ? tb_byte(t, p0 - 1) : 0x100u;
   for (int64_t i = p0; i < p1; i++) {
     uint32_t b = tb_byte(t, i);
@@ -136,7 +137,7 @@ TB_HD void gr_lane(const Classifier& C, const TextRange& R, int64_t p0, int64_t 
   const uint8_t* t = R.t;
   o.nw = 0;
   GrSink sink{&o};
-  o.flags = tb_walk_words<WM_NEED_HASH>(C, R, p0, p1, sink) & CI_COMPLEX;
+  o.flags = tb_walk_words_fast<WM_NEED_HASH>(C, R, p0, p1, sink) & CI_COMPLEX;
   o.has_nl = 0; o.first_nl = 0; o.np = 0; o.nchars = 0;
   o.head.init(); o.head_len = 0;
   Hash2 cur; cur.init(); uint32_t cur_len = 0;
