@@ -81,8 +81,9 @@ TB_HD void sb_sync(const Classifier& C, const TextRange& R, int64_t q, SbState& 
   }
 }
 
-// Number of sentence pieces (non-empty after trim) whose segment starts in [p0, p1).
-TB_HD uint32_t tb_count_sentences(const Classifier& C, const TextRange& R, int64_t p0, int64_t p1) {
+// Number of sentence pieces (non-empty after trim) whose segment starts in [p0, p1)  -- reference walk,
+// one rule evaluation per code point.  Kept as the definition the event-driven version is tested against.
+TB_HD uint32_t tb_count_sentences_walk(const Classifier& C, const TextRange& R, int64_t p0, int64_t p1) {
   const uint8_t* t = R.t;
   int64_t q = p0;
   if (q > R.rs) while (q < R.re && tb_is_cont(tb_byte(t, q))) q++;
@@ -104,6 +105,56 @@ TB_HD uint32_t tb_count_sentences(const Classifier& C, const TextRange& R, int64
     }
     if (open && !(ci & CI_WS)) { count++; open = false; }
     sb_advance(s, cls);
+    i += len;
+  }
+  return count;
+}
+
+// Event-driven count.  A sentence boundary can only arise (a) at the start of text, (b) right after a
+// paragraph separator (SB4) or (c) at the end of a  SATerm Close* Sp*  run (SB11, unless SB6-SB10 veto).
+// So instead of stepping the rule machine over every code point, a lane looks for the terminators and
+// separators that start in its stretch and evaluates the rules only around them, with the same
+// sb_sync / sb_break_before / sb_advance functions.  Every white-space character has class Sp or is a
+// separator, so a segment opened by SB11 always begins with a non-white-space character; one opened
+// by SB4 counts iff a non-white-space character follows before the next separator.
+TB_HD uint32_t tb_count_sentences(const Classifier& C, const TextRange& R, int64_t p0, int64_t p1) {
+  const uint8_t* t = R.t;
+  uint32_t count = 0;
+  int64_t i = p0;
+  if (i > R.rs) while (i < R.re && tb_is_cont(tb_byte(t, i))) i++;
+  if (i == R.rs && i < p1) {  // (a): the text is trimmed, but do not rely on it
+    int64_t j = i;
+    while (j < R.re) { int len; uint32_t cp; uint32_t ci = C.at(t, j, &len, &cp); if (BIT(CI_SB(ci)) & SB_PARASEPMASK) break; if (!(ci & CI_WS)) { count++; break; } j += len; }
+  }
+  while (i < p1) {
+    uint32_t b = tb_byte(t, i);
+    int len = 1; uint32_t cp = b, ci;
+    if (b < 0x80u) {
+      if (b != '.' && b != '!' && b != '?' && b != '\n' && b != '\r') { i++; continue; }  // the only ASCII SATerm / ParaSep
+      ci = C.ascii[b];
+    } else {
+      ci = C.at(t, i, &len, &cp);
+    }
+    const uint32_t cls = CI_SB(ci);
+    if (BIT(cls) & SB_PARASEPMASK) {                                   // (b)
+      int64_t j = i + len;
+      if (!(cls == SB_CR && j < R.re && tb_byte(t, j) == '\n')) {     // SB3: CR x LF
+        while (j < R.re) { int l2; uint32_t c2; uint32_t i2 = C.at(t, j, &l2, &c2); if (BIT(CI_SB(i2)) & SB_PARASEPMASK) break; if (!(i2 & CI_WS)) { count++; break; } j += l2; }
+      }
+    } else if (BIT(cls) & SB_SATERMMASK) {                             // (c)
+      SbState s;
+      sb_sync(C, R, i, s);
+      sb_advance(s, cls);
+      int64_t j = i + len;
+      while (j < R.re && s.st != 0) {
+        int l2; uint32_t c2;
+        uint32_t k2 = CI_SB(C.at(t, j, &l2, &c2));
+        if (sb_break_before(C, R, s, k2, j)) { count++; break; }
+        if (BIT(k2) & SB_SATERMMASK) break;  // the next terminator evaluates what follows it
+        sb_advance(s, k2);
+        j += l2;
+      }
+    }
     i += len;
   }
   return count;
