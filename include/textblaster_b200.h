@@ -273,6 +273,29 @@ int tb_pipeline_kernel_times(tb_pipeline* p, int32_t max_entries, const char** n
                              int64_t* launches);
 void tb_pipeline_reset_kernel_times(tb_pipeline* p);
 
+/* GopherRepetitionFilter for one small batch WITHOUT any allocation -- no counterpart in the reference.
+ *
+ * For embedders that may not enter the CUDA allocator on the calling thread: processes whose device
+ * memory is handed out once by a pool that another component owns (fixed per-tenant quota, a host
+ * runtime that pre-partitions the GPU), or latency-critical sections where cudaMalloc (which can
+ * synchronise the device) is forbidden.  tb_pipeline_run_batch* grow their buffers with cudaMalloc
+ * on demand; this call takes every intermediate from a fixed 16 MiB array inside the library image
+ * (resident on every GPU that loads the library) and therefore accepts at most TB_NOALLOC_MAX_DOCS
+ * documents and TB_NOALLOC_MAX_BYTES bytes of text per call (TB_ERR_INVALID_ARGUMENT beyond that).
+ *
+ * All pointers are DEVICE pointers owned by the caller: utf8_dev / offsets_dev (n_docs + 1 int64,
+ * offsets_dev[n_docs] <= n_bytes) in; stats_dev[n_docs] and keep_dev[n_docs] (1 = passed) out.  Work
+ * is enqueued on cuda_stream (a cudaStream_t, NULL = default stream) and not synchronised.  The first
+ * call on a device performs a blocking set-up (address lookup of the array, table upload): make it at
+ * start-up, before any stream capture.  All calls share the array: calls whose GPU work overlaps race.
+ * Results equal those of a one-step GopherRepetitionFilter pipeline.  err/err_len (optional) receive
+ * the message of a failure. */
+#define TB_NOALLOC_MAX_DOCS 2048
+#define TB_NOALLOC_MAX_BYTES (512 * 1024)
+int tb_gopher_repetition_noalloc(const uint8_t* utf8_dev, const int64_t* offsets_dev, int64_t n_docs, int64_t n_bytes,
+                                 const tb_gr_params* params, tb_gr_stats* stats_dev, uint8_t* keep_dev, void* cuda_stream,
+                                 char* err, size_t err_len);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,169 @@
+// tb_noalloc.cu -- tb_gopher_repetition_noalloc(): the GopherRepetitionFilter pass for a small batch
+// with every byte of working memory taken from one fixed array that is part of the library image.
+//
+// Who needs this.  Some embedders are not allowed to enter the CUDA allocator from the thread that
+// calls us: a worker whose device memory is handed out, once, by a pool owned by another component
+// (a serving process with a fixed per-tenant quota, a host runtime that pre-partitions the GPU), or
+// code on a latency-critical path where a cudaMalloc -- which may synchronise the device and take a
+// driver-wide lock -- is simply forbidden.  The regular entry points (tb_pipeline_run_batch*) grow
+// their buffers with cudaMalloc / cudaMallocHost on demand; this one never does.  The caller brings
+// the inputs and the outputs as device pointers; all intermediates (document ranges, word and line
+// hashes, hash-table work areas, the Unicode tables) live in `tb_noalloc_scratch` below.
+//
+// What it costs.  The array is TB_NOALLOC_SCRATCH_BYTES (16 MiB) of device memory on every GPU that
+// loads the library, for the life of the process.  That bounds the batch: at most
+// TB_NOALLOC_MAX_DOCS documents and TB_NOALLOC_MAX_BYTES bytes of text per call; larger requests are
+// refused with TB_ERR_INVALID_ARGUMENT (split the batch, or use the allocating entry points).
+//
+// Rules of use.
+//  * The first call on a device resolves the array's device address (the name of a __device__ array
+//    is only a host-side handle; kernels must be given the address cudaGetSymbolAddress returns),
+//    uploads the Unicode tables into it with cudaMemcpy and opts one kernel into its shared-memory
+//    size.  That first call blocks; make it during start-up, before any stream capture is begun.
+//  * Every call uses the same array and leaves its contents behind.  The few words that must start
+//    at zero (tier counters and work cursors) are cleared on the caller's stream at the start of
+//    each call; nothing else is assumed clean.
+//  * Two calls whose GPU work overlaps (different streams, or different host threads without an
+//    ordering between their streams) race on the array and produce garbage.  Serialise them.
+//
+// It has no counterpart in the reference and it changes none of the other code paths: it only
+// launches the existing kernels through their launchers with pointers into the static array.
+#include <cuda_runtime.h>
+
+#include <cstring>
+#include <mutex>
+#include <string>
+
+#include "tb_kernels.cuh"
+#include "unicode_tables.inc"
+
+#define TB_NOALLOC_SCRATCH_BYTES (16u << 20)
+
+// The working memory.  In host code this symbol is NOT a device pointer; see setup_device().
+static __device__ __align__(256) unsigned char tb_noalloc_scratch[TB_NOALLOC_SCRATCH_BYTES];
+
+namespace {
+
+constexpr int kMaxDevices = 64;
+struct DeviceState {
+  bool ready = false;
+  unsigned char* base = nullptr;  // device address of tb_noalloc_scratch on this device
+  UcTables uc{};
+  size_t tables_end = 0;          // first free byte after the tables
+  int sm_count = 148;
+};
+DeviceState g_dev[kMaxDevices];
+std::mutex g_mu;
+
+// the message goes to the caller's buffer (this entry point keeps no state of its own besides the scratch)
+struct Err { char* buf; size_t len; };
+thread_local Err g_errbuf{nullptr, 0};
+int fail(int code, const std::string& msg) {
+  if (g_errbuf.buf && g_errbuf.len) { size_t n = msg.size() < g_errbuf.len - 1 ? msg.size() : g_errbuf.len - 1; memcpy(g_errbuf.buf, msg.data(), n); g_errbuf.buf[n] = 0; }
+  return code;
+}
+
+size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+// Once per device, with that device current: resolve the address, place and upload the tables.
+int setup_device(int dev, DeviceState** out) {
+  std::lock_guard<std::mutex> lk(g_mu);
+  DeviceState& st = g_dev[dev];
+  if (!st.ready) {
+    void* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&p, tb_noalloc_scratch);
+    if (e != cudaSuccess || !p) return fail(TB_ERR_CUDA, std::string("cudaGetSymbolAddress(tb_noalloc_scratch): ") + cudaGetErrorString(e));
+    st.base = (unsigned char*)p;
+    size_t off = 0;
+    auto place = [&](const void* src, size_t bytes) -> unsigned char* {
+      unsigned char* d = st.base + off;
+      off = align_up(off + bytes, 256);
+      if (cudaMemcpy(d, src, bytes, cudaMemcpyHostToDevice) != cudaSuccess) return nullptr;
+      return d;
+    };
+    uint64_t pw[TB_POWTAB];
+    { uint32_t a = 1, b = 1; for (int i = 0; i < TB_POWTAB; i++) { pw[i] = ((uint64_t)a << 32) | b; a = tb_mm(a, TB_B1); b = tb_mm(b, TB_B2); } }
+    unsigned char* s1 = place(tb_uc_stage1, sizeof tb_uc_stage1);
+    unsigned char* s2 = place(tb_uc_stage2, sizeof tb_uc_stage2);
+    unsigned char* lo = place(tb_uc_lower, sizeof tb_uc_lower);
+    unsigned char* ca = place(tb_uc_cased, sizeof tb_uc_cased);
+    unsigned char* ci = place(tb_uc_caseign, sizeof tb_uc_caseign);
+    unsigned char* pp = place(pw, sizeof pw);
+    if (!s1 || !s2 || !lo || !ca || !ci || !pp) { cudaGetLastError(); return fail(TB_ERR_CUDA, "uploading the Unicode tables into the static scratch failed"); }
+    st.uc = UcTables{(const uint16_t*)s1, (const uint16_t*)s2, (const uint32_t*)lo, (const uint32_t*)ca, (const uint32_t*)ci,
+                     (const uint64_t*)pp, TB_UC_NLOWER, TB_UC_NCASED, TB_UC_NCASEIGN};
+    st.tables_end = off;
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, dev) == cudaSuccess) st.sm_count = prop.multiProcessorCount;
+    if (tb_kernels_init() != 0) { cudaGetLastError(); return fail(TB_ERR_CUDA, "cudaFuncSetAttribute failed (not an sm_100-class device?)"); }
+    st.ready = true;
+  }
+  *out = &st;
+  return TB_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int tb_gopher_repetition_noalloc(const uint8_t* utf8_dev, const int64_t* offsets_dev, int64_t n_docs, int64_t n_bytes,
+                                 const tb_gr_params* params, tb_gr_stats* stats_dev, uint8_t* keep_dev, void* cuda_stream,
+                                 char* err, size_t err_len) {
+  g_errbuf = Err{err, err_len};
+  if (err && err_len) err[0] = 0;
+  if (n_docs < 0 || n_bytes < 0 || !params || (n_docs > 0 && (!offsets_dev || !stats_dev || !keep_dev)) || (n_bytes > 0 && !utf8_dev))
+    return fail(TB_ERR_INVALID_ARGUMENT, "tb_gopher_repetition_noalloc: NULL or negative argument");
+  if (n_docs > TB_NOALLOC_MAX_DOCS || n_bytes > TB_NOALLOC_MAX_BYTES)
+    return fail(TB_ERR_INVALID_ARGUMENT, "tb_gopher_repetition_noalloc: batch of " + std::to_string(n_docs) + " documents / " +
+                                             std::to_string(n_bytes) + " bytes exceeds the fixed scratch (at most " +
+                                             std::to_string(TB_NOALLOC_MAX_DOCS) + " documents and " + std::to_string(TB_NOALLOC_MAX_BYTES) +
+                                             " bytes per call); split the batch or use tb_pipeline_run_batch");
+  if (params->n_top < 0 || params->n_top > TB_MAX_NGRAMS || params->n_dup < 0 || params->n_dup > TB_MAX_NGRAMS)
+    return fail(TB_ERR_INVALID_ARGUMENT, "tb_gopher_repetition_noalloc: at most " + std::to_string(TB_MAX_NGRAMS) + " entries per n-gram list");
+  for (int k = 0; k < params->n_top; k++) if (params->top_n[k] == 0 || params->top_n[k] > TB_MAX_NGRAM_N) return fail(TB_ERR_INVALID_ARGUMENT, "tb_gopher_repetition_noalloc: n-gram order out of range");
+  for (int k = 0; k < params->n_dup; k++) if (params->dup_n[k] == 0 || params->dup_n[k] > TB_MAX_NGRAM_N) return fail(TB_ERR_INVALID_ARGUMENT, "tb_gopher_repetition_noalloc: n-gram order out of range");
+  if (n_docs == 0) return TB_OK;
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDevices) { cudaGetLastError(); return fail(TB_ERR_CUDA, "no current CUDA device"); }
+  DeviceState* st = nullptr;
+  int rc = setup_device(dev, &st);
+  if (rc) return rc;
+  cudaStream_t stream = (cudaStream_t)cuda_stream;
+
+  // carve the per-call arrays out of the static array (nothing here allocates)
+  const size_t n1 = (size_t)n_docs + 1, units = (size_t)n_bytes / 2 + n1 + 1;
+  size_t off = st->tables_end;
+  auto carve = [&](size_t bytes) -> unsigned char* { unsigned char* p = st->base + off; off = align_up(off + bytes, 256); return p; };
+  int64_t* rs = (int64_t*)carve(n1 * 8); int64_t* re = (int64_t*)carve(n1 * 8);
+  int64_t* ts = (int64_t*)carve(n1 * 8); int64_t* te = (int64_t*)carve(n1 * 8);
+  int8_t* failed = (int8_t*)carve(n1);
+  GrScratch g;
+  g.wh = (uint64_t*)carve(units * 8); g.wl = (uint32_t*)carve(units * 4);
+  g.lh = (uint64_t*)carve(units * 8); g.ll = (uint32_t*)carve(units * 4); g.lg = (uint8_t*)carve(units);
+  g.doc = (GrDoc*)carve(n1 * sizeof(GrDoc));
+  g.work = (uint32_t*)carve((units * TB_REP_K + n1 * TB_REP_DOC_EXTRA) * 4);
+  g.lists = (uint32_t*)carve(3 * n1 * 4);
+  g.counters = (uint32_t*)carve(64);
+  g.n = n_docs;
+  if (off > TB_NOALLOC_SCRATCH_BYTES) return fail(TB_ERR_INVALID_ARGUMENT, "tb_gopher_repetition_noalloc: internal scratch budget exceeded");
+
+  GrCfg cfg{};
+  cfg.has = params->has; cfg.n_top = params->n_top; cfg.n_dup = params->n_dup;
+  cfg.dup_line_frac = params->dup_line_frac; cfg.dup_para_frac = params->dup_para_frac;
+  cfg.dup_line_char_frac = params->dup_line_char_frac; cfg.dup_para_char_frac = params->dup_para_char_frac;
+  for (int k = 0; k < TB_MAX_NGRAMS; k++) { cfg.top_n[k] = params->top_n[k]; cfg.top_frac[k] = params->top_frac[k]; cfg.dup_n[k] = params->dup_n[k]; cfg.dup_frac[k] = params->dup_frac[k]; }
+
+  // state that must start at zero: tier list lengths and work cursors (the array keeps the last call's contents)
+  if (cudaMemsetAsync(g.counters, 0, 64, stream) != cudaSuccess) { cudaGetLastError(); return fail(TB_ERR_CUDA, "cudaMemsetAsync failed"); }
+  // keep_dev doubles as the kernels' "alive" flag; init_ranges sets it to 1 for every document
+  tb_launch_init_ranges(stream, offsets_dev, 1, 0, n_docs, 0, rs, re, keep_dev, failed);
+  KBatch b{utf8_dev, rs, re, keep_dev, failed, n_docs, st->uc};
+  tb_launch_trim(stream, b, ts, te);
+  tb_launch_gr_scan(stream, b, ts, te, g);
+  for (int tier = 0; tier < 3; tier++) tb_launch_gr_rep(stream, b, ts, te, g, cfg, 0, stats_dev, st->sm_count, tier);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return fail(TB_ERR_CUDA, std::string("tb_gopher_repetition_noalloc: launch failed: ") + cudaGetErrorString(e));
+  return TB_OK;
+}
+
+}  // extern "C"
