@@ -120,9 +120,9 @@ extern "C" int tbe_run_chain(const tb_step_cfg* steps, size_t n_steps, const uin
       const tb_gq_params& q = sc.u.gq;
       GqCfg cfg{q.has, q.min_doc_words, q.max_doc_words, q.min_stop_words, q.min_avg_word_length, q.max_avg_word_length,
                 q.max_symbol_word_ratio, q.max_bullet_lines_ratio, q.max_ellipsis_lines_ratio, q.max_non_alpha_words_ratio};
-      uint32_t mask, maxlen;
-      std::vector<SwEntry> tab = tb_build_stop_table(tb_stop_words_of(q), &mask, &maxlen);
-      SwTable sw{tab.data(), mask, maxlen};
+      uint32_t mask, maxlen, lenmask, firstmask;
+      std::vector<SwEntry> tab = tb_build_stop_table(tb_stop_words_of(q), &mask, &maxlen, &lenmask, &firstmask);
+      SwTable sw{tab.data(), mask, maxlen, lenmask, firstmask};
       run_warps(n, alive_pred, [&](int64_t d, int lane) { body_gq(b, ascii, sw, cfg, (int)s, (tb_gq_stats*)stats, d, lane); });
     } else if (sc.type == TB_STEP_GOPHER_REPETITION) {
       const tb_gr_params& q = sc.u.gr;

@@ -107,7 +107,7 @@ struct StepHost {
   C4Cfg c4;
   GqCfg gq;
   GrCfg gr;
-  SwTable sw{nullptr, 0, 0};
+  SwTable sw{nullptr, 0, 0, 0, 0};
   DevBuf sw_dev;
 };
 
@@ -250,11 +250,11 @@ int validate_step(const tb_step_cfg& s) {
 }
 
 int build_stop_table(StepHost& sh, const tb_gq_params& p) {
-  uint32_t mask = 0, maxlen = 0;
-  std::vector<SwEntry> tab = tb_build_stop_table(tb_stop_words_of(p), &mask, &maxlen);
+  uint32_t mask = 0, maxlen = 0, lenmask = 0, firstmask = 0;
+  std::vector<SwEntry> tab = tb_build_stop_table(tb_stop_words_of(p), &mask, &maxlen, &lenmask, &firstmask);
   int rc = upload(sh.sw_dev, tab.data(), tab.size() * sizeof(SwEntry));
   if (rc) return rc;
-  sh.sw = SwTable{sh.sw_dev.as<SwEntry>(), mask, maxlen};
+  sh.sw = SwTable{sh.sw_dev.as<SwEntry>(), mask, maxlen, lenmask, firstmask};
   return TB_OK;
 }
 

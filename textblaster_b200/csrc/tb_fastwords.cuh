@@ -60,11 +60,43 @@ TB_HD int tb_ctz64(uint64_t v) {
 #endif
 }
 
+TB_HD int tb_msb64(uint64_t v) {  // index of the highest set bit, v != 0
+#if defined(__CUDA_ARCH__)
+  return 63 - __clzll((long long)v);
+#else
+  return 63 - __builtin_clzll(v);
+#endif
+}
+
+TB_HD int tb_popc64(uint64_t v) {
+#if defined(__CUDA_ARCH__)
+  return __popcll(v);
+#else
+  return __builtin_popcountll(v);
+#endif
+}
+
 struct AsciiWin {
   uint64_t A, WC, brk;
   int64_t base;   // byte position of bit 0
   uint32_t lim;   // boundary bits up to and including `lim` are final
+  uint32_t x[TB_FW_WIN / 4];  // the window bytes (bytes outside the range read as 0)
 };
+// byte j of the window, j a compile-time constant after unrolling
+#define TB_FW_BYTE(w, j) (((w).x[(j) >> 2] >> (8 * ((j) & 3))) & 0xFFu)
+// 48-bit mask of the window bytes equal to c (bytes are < 0x80)
+TB_HD uint64_t tb_fw_eqmask(const AsciiWin& w, uint32_t c) {
+  uint64_t m = 0;
+  const uint32_t cc = c * 0x01010101u;
+#pragma unroll
+  for (int k = 0; k < TB_FW_WIN / 4; k++) {
+    uint32_t z = w.x[k] ^ cc;
+    uint32_t nz = ((z + 0x7F7F7F7Fu) | z) & 0x80808080u;   // high bit set where the byte differs
+    uint32_t eq = (nz ^ 0x80808080u) >> 7;                 // 0x01 per equal byte
+    m |= (uint64_t)((eq * 0x01020408u) >> 24 & 0xFu) << (4 * k);
+  }
+  return m;
+}
 
 // Build the window for the stretch starting at p0.  Returns false when the fast path does not apply.
 TB_HD bool tb_ascii_window(const Classifier& C, const TextRange& R, int64_t p0, AsciiWin& w) {
@@ -90,6 +122,7 @@ TB_HD bool tb_ascii_window(const Classifier& C, const TextRange& R, int64_t p0, 
 #pragma unroll
   for (int k = 0; k < TB_FW_WIN / 4; k++) {
     uint32_t x = mis ? tb_funnel_r(raw[k], raw[k + 1], mis) : raw[k];
+    w.x[k] = x;
     bad |= x & 0x80808080u;
     uint32_t z = x ^ 0x0D0D0D0Du;                               // '\r' (WB3 CR x LF) -> general path
     bad |= ((z + 0x7F7F7F7Fu) | z) ^ 0xFFFFFFFFu;               // nonzero high bit where a byte of z is 0 (bytes < 0x80)

@@ -15,7 +15,12 @@
 // word.  Key = first 16 bytes + byte length (+ FNV-1a of the bytes beyond 16).
 // ---------------------------------------------------------------------------------------------
 struct SwEntry { uint64_t lo, hi, ext; uint32_t len, used; };
-struct SwTable { const SwEntry* e; uint32_t mask, maxlen; };
+struct SwTable {
+  const SwEntry* e; uint32_t mask, maxlen;
+  uint32_t lenmask;    // bit min(len, 31) set for every entry length: cheap reject before building a key
+  uint32_t firstmask;  // bit (first byte | 0x20) - 'a' for letters, bit 26 for anything else
+};
+TB_HD uint32_t sw_first_bit(uint32_t b) { uint32_t f = (b | 0x20u) - 'a'; return f < 26u ? (1u << f) : (1u << 26); }
 
 TB_HD uint64_t sw_slot_hash(uint64_t lo, uint64_t hi, uint64_t ext, uint32_t len) {
   uint32_t h = (uint32_t)lo * 0x9E3779B1u ^ (uint32_t)(lo >> 32) * 0x85EBCA77u ^ (uint32_t)hi * 0xC2B2AE3Du ^
@@ -82,7 +87,68 @@ TB_HD bool gq_line_is_bullet(const Classifier& C, const TextRange& R, int64_t s)
   return false;
 }
 
+// ASCII fast path of gq_lane: words from the window's break mask, '#', "..." runs and line starts /
+// ends from byte-equality masks; the per-word stop-word key is only built for words that pass the
+// length / first-letter filter of the table.
+TB_HD bool gq_lane_fast(const Classifier& C, const TextRange& R, const SwTable& sw, int64_t p0, int64_t p1, GqAcc& acc) {
+  AsciiWin w;
+  if (!tb_ascii_window(C, R, p0, w)) return false;
+  const uint8_t* t = R.t;
+  const uint32_t s0 = TB_FW_LCTX, s1 = (uint32_t)(p1 - w.base);
+  const uint64_t ownrange = ((1ull << s1) - 1ull) & ~((1ull << s0) - 1ull);
+  const uint64_t limmask = (2ull << w.lim) - 1ull;
+  uint64_t own = w.brk & ownrange;
+  {  // every owned segment must close inside the window, otherwise the general path takes the stretch
+    uint64_t o2 = own;
+    while (o2) { uint32_t s = (uint32_t)tb_ctz64(o2); o2 &= o2 - 1; if (!(((w.brk >> (s + 1)) << (s + 1)) & limmask)) return false; }
+  }
+  while (own) {
+    const uint32_t s = (uint32_t)tb_ctz64(own);
+    own &= own - 1;
+    const uint32_t e = (uint32_t)tb_ctz64(((w.brk >> (s + 1)) << (s + 1)) & limmask);
+    const uint64_t seg = ((1ull << e) - 1ull) & ~((1ull << s) - 1ull);
+    if (!(w.WC & seg)) continue;
+    const uint32_t len = e - s;
+    acc.n_words++; acc.sum_chars += len; acc.n_alpha += (w.A & seg) ? 1u : 0u;
+    if (len <= sw.maxlen && ((sw.lenmask >> (len < 31u ? len : 31u)) & 1u)) {
+      const int64_t ws = w.base + s;
+      if (sw.firstmask & sw_first_bit(tb_byte(t, ws))) {
+        LowKey k; k.init();
+        for (uint32_t i = 0; i < len; i++) { uint32_t b = tb_byte(t, ws + i); k.push((b - 'A') < 26u ? b + 32u : b); }
+        if (sw_lookup(sw, k)) acc.n_stop++;
+      }
+    }
+  }
+  acc.n_hash += (uint32_t)tb_popc64(tb_fw_eqmask(w, '#') & ownrange);                  // :104
+  const uint64_t dot = tb_fw_eqmask(w, '.');
+  uint64_t runs = dot & ~(dot << 1) & ownrange;                                                   // :115 matches("...")
+  while (runs) {
+    const uint32_t s = (uint32_t)tb_ctz64(runs);
+    runs &= runs - 1;
+    uint32_t n = (uint32_t)tb_ctz64(~(dot >> s));
+    if (s + n >= TB_FW_WIN) { int64_t j = w.base + s + n; while (j < R.re && tb_byte(t, j) == '.') { j++; n++; } }
+    acc.n_ell += n / 3;
+  }
+  const uint64_t nl = tb_fw_eqmask(w, '\n');
+  uint64_t starts = ((nl << 1) | (p0 == R.rs ? (1ull << s0) : 0ull)) & ownrange;                  // :126
+  while (starts) {
+    const uint32_t s = (uint32_t)tb_ctz64(starts);
+    starts &= starts - 1;
+    acc.n_lines++;
+    if (gq_line_is_bullet(C, R, w.base + s)) acc.n_bullet++;
+  }
+  uint64_t ends = nl & ownrange;
+  while (ends) {
+    const uint32_t s = (uint32_t)tb_ctz64(ends);
+    ends &= ends - 1;
+    if (gq_line_ends_with_ellipsis(C, R, w.base + s)) acc.n_ell_lines++;
+  }
+  if (p1 == R.re && !((nl >> (s1 - 1)) & 1ull)) { if (gq_line_ends_with_ellipsis(C, R, R.re)) acc.n_ell_lines++; }
+  return true;
+}
+
 TB_HD void gq_lane(const Classifier& C, const TextRange& R, const SwTable& sw, int64_t p0, int64_t p1, GqAcc& acc) {
+  if (gq_lane_fast(C, R, sw, p0, p1, acc)) return;
   const uint8_t* t = R.t;
   GqSink sink{&C, t, &sw, &acc};
   acc.flags |= tb_walk_words_fast<WM_NEED_ALPHA | WM_NEED_LOWKEY>(C, R, p0, p1, sink) & CI_COMPLEX;
@@ -133,7 +199,8 @@ struct GrSink {
     o->nw++;
   }
 };
-TB_HD void gr_lane(const Classifier& C, const TextRange& R, int64_t p0, int64_t p1, GrLane& o) {
+TB_HD void gr_lane(const Classifier& C, const TextRange& R, int64_t p0, int64_t p1, GrLane& o);
+TB_HD void gr_lane_general(const Classifier& C, const TextRange& R, int64_t p0, int64_t p1, GrLane& o) {
   const uint8_t* t = R.t;
   o.nw = 0;
   GrSink sink{&o};
@@ -151,6 +218,72 @@ TB_HD void gr_lane(const Classifier& C, const TextRange& R, int64_t p0, int64_t 
     } else { cur.push(b); cur_len++; }
   }
   o.tail = cur; o.tail_len = cur_len;
+}
+// ASCII fast path of gr_lane.  One running polynomial hash R over the bytes of the stretch (never
+// reset) serves both the words and the line pieces: hash(bytes [a, b)) = R_b - R_a * B^(b-a), so a
+// single converged loop over the window replaces the per-word and per-piece hashing loops.
+TB_HD Hash2 gr_hdiff(Hash2 rb, Hash2 ra, uint64_t pw) {  // R_b - R_a * B^len
+  Hash2 r;
+  r.a = tb_am(rb.a, TB_P31 - tb_mm(ra.a, (uint32_t)(pw >> 32)));
+  r.b = tb_am(rb.b, TB_P31 - tb_mm(ra.b, (uint32_t)pw));
+  return r;
+}
+TB_HD bool gr_lane_fast(const Classifier& C, const TextRange& R, int64_t p0, int64_t p1, GrLane& o) {
+  AsciiWin w;
+  if (!tb_ascii_window(C, R, p0, w)) return false;
+  // owned word segments as start / end bit masks (ASCII words are never adjacent: two alphanumeric
+  // segments next to each other would have been joined by WB5/8/9/10)
+  const uint32_t s0 = TB_FW_LCTX, s1 = (uint32_t)(p1 - w.base);
+  uint64_t own = w.brk & ((1ull << s1) - 1ull) & ~((1ull << s0) - 1ull);
+  const uint64_t limmask = (2ull << w.lim) - 1ull;
+  uint64_t ws = 0, we = 0;
+  while (own) {
+    const uint32_t s = (uint32_t)tb_ctz64(own);
+    own &= own - 1;
+    const uint64_t rest = ((w.brk >> (s + 1)) << (s + 1)) & limmask;
+    if (!rest) return false;  // a segment runs out of the window: let the general path handle the stretch
+    const uint32_t e = (uint32_t)tb_ctz64(rest);
+    const uint64_t seg = ((1ull << e) - 1ull) & ~((1ull << s) - 1ull);
+    if (w.WC & seg) { ws |= 1ull << s; we |= 1ull << e; }
+  }
+  const uint32_t jend = we ? (uint32_t)tb_msb64(we) : 0u;  // end of the last owned word
+  const uint32_t jmax = jend > s1 ? jend : s1;
+  o.nw = 0; o.flags = 0; o.has_nl = 0; o.first_nl = 0; o.np = 0; o.nchars = s1 - s0;
+  o.head.init(); o.head_len = 0;
+  Hash2 Rr; Rr.init();
+  Hash2 hw; hw.init(); uint32_t wstart = 0;      // R and position at the start of the open word
+  Hash2 hp; hp.init(); uint32_t pstart = s0;     // R and position at the start of the open line piece
+#pragma unroll
+  for (uint32_t j = TB_FW_LCTX; j < TB_FW_WIN; j++) {
+    if (j >= jmax) break;
+    if ((we >> j) & 1ull) {
+      uint32_t len = j - wstart;
+      if (o.nw < TB_LANE_MAXW) { o.wh[o.nw] = gr_hdiff(Rr, hw, tb_pow_pack(C.u.powtab, len)).pack(); o.wl[o.nw] = len; }
+      o.nw++;
+    }
+    if ((ws >> j) & 1ull) { hw = Rr; wstart = j; }
+    const uint32_t b = TB_FW_BYTE(w, j);
+    if (j < s1 && b == '\n') {
+      uint32_t len = j - pstart;
+      if (!o.has_nl) { o.has_nl = 1; o.first_nl = j - s0; o.head = gr_hdiff(Rr, hp, tb_pow_pack(C.u.powtab, len)); o.head_len = len; }
+      else if (len) { o.ph[o.np] = gr_hdiff(Rr, hp, tb_pow_pack(C.u.powtab, len)).pack(); o.pl[o.np] = len; o.pend[o.np] = j - s0; o.np++; }
+      pstart = j + 1;
+    }
+    if (j == s1) { o.tail = gr_hdiff(Rr, hp, tb_pow_pack(C.u.powtab, j - pstart)); o.tail_len = j - pstart; }  // words may run past p1
+    Rr.push(b);
+    if (b == '\n' && j < s1) hp = Rr;
+  }
+  if (jmax <= s1) { o.tail = gr_hdiff(Rr, hp, tb_pow_pack(C.u.powtab, s1 - pstart)); o.tail_len = s1 - pstart; }
+  if ((we >> jmax) & 1ull) {  // a word that ends exactly at jmax (>= s1)
+    uint32_t len = jmax - wstart;
+    if (o.nw < TB_LANE_MAXW) { o.wh[o.nw] = gr_hdiff(Rr, hw, tb_pow_pack(C.u.powtab, len)).pack(); o.wl[o.nw] = len; }
+    o.nw++;
+  }
+  return true;
+}
+
+TB_HD void gr_lane(const Classifier& C, const TextRange& R, int64_t p0, int64_t p1, GrLane& o) {
+  if (!gr_lane_fast(C, R, p0, p1, o)) gr_lane_general(C, R, p0, p1, o);
 }
 // was the piece starting at s (s > ts) preceded by a run of >= 2 newlines? (paragraph_exp \n{2,})
 TB_HD uint32_t gr_gap2(const TextRange& R, int64_t s) {
@@ -308,7 +441,8 @@ TB_HD uint32_t c4_pattern_flags(const uint8_t* t, int64_t i, int64_t re, uint32_
   uint32_t fb = b | 0x20u;
   // cheap reject: only j / t / p / c / u can start a pattern, and the next two bytes must continue it
   // ("jav", "ter", "pri", "coo", "use"); the exact (Kelvin-sign aware) compare runs on the few survivors
-  if (!(fb == 'j' || fb == 't' || fb == 'p' || fb == 'c' || fb == 'u') || i + 2 >= re) return 0;
+  const uint32_t d = fb - 'c';  // c, j, p, t, u as bits of a small mask
+  if (d > (uint32_t)('u' - 'c') || !((0x62081u >> d) & 1u) || i + 2 >= re) return 0;
   uint32_t b1 = tb_byte(t, i + 1) | 0x20u, b2 = tb_byte(t, i + 2) | 0x20u;
   uint32_t tri = (fb << 16) | (b1 << 8) | b2;
   if (tri != 0x6A6176u && tri != 0x746572u && tri != 0x707269u && tri != 0x636F6Fu && tri != 0x757365u) return 0;

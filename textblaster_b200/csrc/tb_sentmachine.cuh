@@ -126,15 +126,24 @@ TB_HD uint32_t tb_count_sentences(const Classifier& C, const TextRange& R, int64
     int64_t j = i;
     while (j < R.re) { int len; uint32_t cp; uint32_t ci = C.at(t, j, &len, &cp); if (BIT(CI_SB(ci)) & SB_PARASEPMASK) break; if (!(ci & CI_WS)) { count++; break; } j += len; }
   }
-  while (i < p1) {
-    uint32_t b = tb_byte(t, i);
-    int len = 1; uint32_t cp = b, ci;
-    if (b < 0x80u) {
-      if (b != '.' && b != '!' && b != '?' && b != '\n' && b != '\r') { i++; continue; }  // the only ASCII SATerm / ParaSep
-      ci = C.ascii[b];
-    } else {
-      ci = C.at(t, i, &len, &cp);
-    }
+  // phase 1 (converged): which bytes of the stretch can matter -- ASCII terminators / separators and
+  // the lead bytes of non-ASCII characters; phase 2: evaluate the rules at those positions only
+  uint32_t ev = 0;
+  for (int64_t j = i; j < p1; j++) {
+    uint32_t b = tb_byte(t, j);
+    bool hit = (b == '.') | (b == '!') | (b == '?') | (b == '\n') | (b == '\r') | (b >= 0xC0u);
+    ev |= (hit ? 1u : 0u) << (uint32_t)(j - p0);
+  }
+  while (ev) {
+#if defined(__CUDA_ARCH__)
+    const uint32_t bit = (uint32_t)__ffs((int)ev) - 1u;
+#else
+    const uint32_t bit = (uint32_t)__builtin_ctz(ev);
+#endif
+    ev &= ev - 1;
+    i = p0 + bit;
+    int len; uint32_t cp;
+    const uint32_t ci = C.at(t, i, &len, &cp);
     const uint32_t cls = CI_SB(ci);
     if (BIT(cls) & SB_PARASEPMASK) {                                   // (b)
       int64_t j = i + len;
@@ -155,7 +164,6 @@ TB_HD uint32_t tb_count_sentences(const Classifier& C, const TextRange& R, int64
         j += l2;
       }
     }
-    i += len;
   }
   return count;
 }
