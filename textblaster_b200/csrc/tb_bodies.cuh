@@ -59,7 +59,7 @@ TB_D void body_validate_utf8(const uint8_t* t, const int64_t* rs, const int64_t*
 TB_D void body_gq(const KBatch& a, const uint16_t* s_ascii, const SwTable& sw, const GqCfg& cfg, int step,
                   tb_gq_stats* out, int64_t d, int lane) {
   Classifier C{s_ascii, a.uc};
-  C.key_maxlen = sw.maxlen;
+  C.key_maxlen = sw.maxlen; C.key_lenmask = sw.lenmask; C.key_firstmask = sw.firstmask;
   TextRange R{a.text, a.rs[d], a.re[d]};
   GqAcc acc; acc.zero();
   for (int64_t base = R.rs; base < R.re; base += TB_TILE) {

@@ -86,6 +86,7 @@ struct Classifier {
   const uint16_t* ascii;  // [128] cinfo of the ASCII code points, followed by 128 bytes of fast-path class flags
   UcTables u;
   uint32_t key_maxlen = 0xFFFFFFFFu;  // longest stop word: longer words need no lower-cased key
+  uint32_t key_lenmask = 0xFFFFFFFFu, key_firstmask = 0xFFFFFFFFu;  // cheap reject by length / first letter (SwTable)
   TB_HD const uint8_t* aflags() const { return (const uint8_t*)(ascii + 128); }
   TB_HD uint32_t of_cp(uint32_t cp) const { return cp < 128u ? ascii[cp] : tb_cinfo_trie(u, cp); }
   // classify the code point starting at i; returns cinfo, sets *len (and *cp)

@@ -171,8 +171,14 @@ TB_HD uint32_t tb_walk_words_fast(const Classifier& C, const TextRange& R, int64
     if (MODE & WM_NEED_HASH) { wi.hash.init(); for (int64_t i = wi.start; i < wi.end; i++) wi.hash.push(tb_byte(R.t, i)); }
     if (MODE & WM_NEED_LOWKEY) {
       wi.key.init();
-      if (e - s <= C.key_maxlen) { for (int64_t i = wi.start; i < wi.end; i++) { uint32_t b = tb_byte(R.t, i); wi.key.push((b - 'A') < 26u ? b + 32u : b); } }
-      else wi.key.len = e - s;  // longer than every stop word: only the length is ever looked at
+      const uint32_t len = e - s;
+      uint32_t fb = (tb_byte(R.t, wi.start) | 0x20u) - 'a';
+      fb = fb < 26u ? (1u << fb) : (1u << 26);
+      if (len <= C.key_maxlen && ((C.key_lenmask >> (len < 31u ? len : 31u)) & 1u) && (C.key_firstmask & fb)) {
+        for (int64_t i = wi.start; i < wi.end; i++) { uint32_t b = tb_byte(R.t, i); wi.key.push((b - 'A') < 26u ? b + 32u : b); }
+      } else {
+        wi.key.len = 0;  // cannot equal any stop word: an empty key never matches (sw_lookup)
+      }
     }
     sink.on_word(wi);
   }

@@ -31,7 +31,7 @@ __global__ void __launch_bounds__(TB_BLOCK) k_validate_utf8(const uint8_t* t, co
   int64_t d = warp_doc();
   if (d < n) body_validate_utf8(t, rs, re, bad, d, threadIdx.x & 31);
 }
-__global__ void __launch_bounds__(TB_BLOCK, 24) k_gq(KBatch a, SwTable sw, GqCfg cfg, int step, tb_gq_stats* out) {
+__global__ void __launch_bounds__(TB_BLOCK, 16) k_gq(KBatch a, SwTable sw, GqCfg cfg, int step, tb_gq_stats* out) {
   __shared__ uint16_t s_ascii[192];
   load_ascii(s_ascii, a.uc);
   int64_t d = warp_doc();
@@ -44,7 +44,7 @@ __global__ void k_trim(KBatch a, int64_t* ts, int64_t* te) {
   int64_t d = thread_doc();
   if (d < a.n) body_trim(a, s_ascii, ts, te, d);
 }
-__global__ void __launch_bounds__(TB_BLOCK, 24) k_gr_scan(KBatch a, const int64_t* ts, const int64_t* te, GrScratch s) {
+__global__ void __launch_bounds__(TB_BLOCK, 20) k_gr_scan(KBatch a, const int64_t* ts, const int64_t* te, GrScratch s) {
   __shared__ uint16_t s_ascii[192];
   load_ascii(s_ascii, a.uc);
   int64_t d = warp_doc();

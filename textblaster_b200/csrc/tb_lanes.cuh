@@ -87,68 +87,7 @@ TB_HD bool gq_line_is_bullet(const Classifier& C, const TextRange& R, int64_t s)
   return false;
 }
 
-// ASCII fast path of gq_lane: words from the window's break mask, '#', "..." runs and line starts /
-// ends from byte-equality masks; the per-word stop-word key is only built for words that pass the
-// length / first-letter filter of the table.
-TB_HD bool gq_lane_fast(const Classifier& C, const TextRange& R, const SwTable& sw, int64_t p0, int64_t p1, GqAcc& acc) {
-  AsciiWin w;
-  if (!tb_ascii_window(C, R, p0, w)) return false;
-  const uint8_t* t = R.t;
-  const uint32_t s0 = TB_FW_LCTX, s1 = (uint32_t)(p1 - w.base);
-  const uint64_t ownrange = ((1ull << s1) - 1ull) & ~((1ull << s0) - 1ull);
-  const uint64_t limmask = (2ull << w.lim) - 1ull;
-  uint64_t own = w.brk & ownrange;
-  {  // every owned segment must close inside the window, otherwise the general path takes the stretch
-    uint64_t o2 = own;
-    while (o2) { uint32_t s = (uint32_t)tb_ctz64(o2); o2 &= o2 - 1; if (!(((w.brk >> (s + 1)) << (s + 1)) & limmask)) return false; }
-  }
-  while (own) {
-    const uint32_t s = (uint32_t)tb_ctz64(own);
-    own &= own - 1;
-    const uint32_t e = (uint32_t)tb_ctz64(((w.brk >> (s + 1)) << (s + 1)) & limmask);
-    const uint64_t seg = ((1ull << e) - 1ull) & ~((1ull << s) - 1ull);
-    if (!(w.WC & seg)) continue;
-    const uint32_t len = e - s;
-    acc.n_words++; acc.sum_chars += len; acc.n_alpha += (w.A & seg) ? 1u : 0u;
-    if (len <= sw.maxlen && ((sw.lenmask >> (len < 31u ? len : 31u)) & 1u)) {
-      const int64_t ws = w.base + s;
-      if (sw.firstmask & sw_first_bit(tb_byte(t, ws))) {
-        LowKey k; k.init();
-        for (uint32_t i = 0; i < len; i++) { uint32_t b = tb_byte(t, ws + i); k.push((b - 'A') < 26u ? b + 32u : b); }
-        if (sw_lookup(sw, k)) acc.n_stop++;
-      }
-    }
-  }
-  acc.n_hash += (uint32_t)tb_popc64(tb_fw_eqmask(w, '#') & ownrange);                  // :104
-  const uint64_t dot = tb_fw_eqmask(w, '.');
-  uint64_t runs = dot & ~(dot << 1) & ownrange;                                                   // :115 matches("...")
-  while (runs) {
-    const uint32_t s = (uint32_t)tb_ctz64(runs);
-    runs &= runs - 1;
-    uint32_t n = (uint32_t)tb_ctz64(~(dot >> s));
-    if (s + n >= TB_FW_WIN) { int64_t j = w.base + s + n; while (j < R.re && tb_byte(t, j) == '.') { j++; n++; } }
-    acc.n_ell += n / 3;
-  }
-  const uint64_t nl = tb_fw_eqmask(w, '\n');
-  uint64_t starts = ((nl << 1) | (p0 == R.rs ? (1ull << s0) : 0ull)) & ownrange;                  // :126
-  while (starts) {
-    const uint32_t s = (uint32_t)tb_ctz64(starts);
-    starts &= starts - 1;
-    acc.n_lines++;
-    if (gq_line_is_bullet(C, R, w.base + s)) acc.n_bullet++;
-  }
-  uint64_t ends = nl & ownrange;
-  while (ends) {
-    const uint32_t s = (uint32_t)tb_ctz64(ends);
-    ends &= ends - 1;
-    if (gq_line_ends_with_ellipsis(C, R, w.base + s)) acc.n_ell_lines++;
-  }
-  if (p1 == R.re && !((nl >> (s1 - 1)) & 1ull)) { if (gq_line_ends_with_ellipsis(C, R, R.re)) acc.n_ell_lines++; }
-  return true;
-}
-
 TB_HD void gq_lane(const Classifier& C, const TextRange& R, const SwTable& sw, int64_t p0, int64_t p1, GqAcc& acc) {
-  if (gq_lane_fast(C, R, sw, p0, p1, acc)) return;
   const uint8_t* t = R.t;
   GqSink sink{&C, t, &sw, &acc};
   acc.flags |= tb_walk_words_fast<WM_NEED_ALPHA | WM_NEED_LOWKEY>(C, R, p0, p1, sink) & CI_COMPLEX;
@@ -237,15 +176,17 @@ TB_HD bool gr_lane_fast(const Classifier& C, const TextRange& R, int64_t p0, int
   uint64_t own = w.brk & ((1ull << s1) - 1ull) & ~((1ull << s0) - 1ull);
   const uint64_t limmask = (2ull << w.lim) - 1ull;
   uint64_t ws = 0, we = 0;
+  bool closed = true;  // (no return inside the loop: keeps the lanes of a warp converged afterwards)
   while (own) {
     const uint32_t s = (uint32_t)tb_ctz64(own);
     own &= own - 1;
     const uint64_t rest = ((w.brk >> (s + 1)) << (s + 1)) & limmask;
-    if (!rest) return false;  // a segment runs out of the window: let the general path handle the stretch
-    const uint32_t e = (uint32_t)tb_ctz64(rest);
+    const uint32_t e = rest ? (uint32_t)tb_ctz64(rest) : s + 1;
     const uint64_t seg = ((1ull << e) - 1ull) & ~((1ull << s) - 1ull);
+    closed = closed && rest != 0;
     if (w.WC & seg) { ws |= 1ull << s; we |= 1ull << e; }
   }
+  if (!closed) return false;  // a segment runs out of the window: let the general path handle the stretch
   const uint32_t jend = we ? (uint32_t)tb_msb64(we) : 0u;  // end of the last owned word
   const uint32_t jmax = jend > s1 ? jend : s1;
   o.nw = 0; o.flags = 0; o.has_nl = 0; o.first_nl = 0; o.np = 0; o.nchars = s1 - s0;
@@ -253,16 +194,14 @@ TB_HD bool gr_lane_fast(const Classifier& C, const TextRange& R, int64_t p0, int
   Hash2 Rr; Rr.init();
   Hash2 hw; hw.init(); uint32_t wstart = 0;      // R and position at the start of the open word
   Hash2 hp; hp.init(); uint32_t pstart = s0;     // R and position at the start of the open line piece
-#pragma unroll
-  for (uint32_t j = TB_FW_LCTX; j < TB_FW_WIN; j++) {
-    if (j >= jmax) break;
+  for (uint32_t j = TB_FW_LCTX; j < jmax; j++) {  // rolled on purpose: unrolling it blows the instruction cache
     if ((we >> j) & 1ull) {
       uint32_t len = j - wstart;
       if (o.nw < TB_LANE_MAXW) { o.wh[o.nw] = gr_hdiff(Rr, hw, tb_pow_pack(C.u.powtab, len)).pack(); o.wl[o.nw] = len; }
       o.nw++;
     }
     if ((ws >> j) & 1ull) { hw = Rr; wstart = j; }
-    const uint32_t b = TB_FW_BYTE(w, j);
+    const uint32_t b = tb_byte(R.t, w.base + j);
     if (j < s1 && b == '\n') {
       uint32_t len = j - pstart;
       if (!o.has_nl) { o.has_nl = 1; o.first_nl = j - s0; o.head = gr_hdiff(Rr, hp, tb_pow_pack(C.u.powtab, len)); o.head_len = len; }
