@@ -31,6 +31,9 @@ import numpy as np  # noqa: E402
 
 METRIC = "docs/s through C4+Gopher filter chain"
 UNIT = "docs/s"
+WORKLOAD = ("C4QualityFilter+GopherQualityFilter+GopherRepetitionFilter chain, 1M synthetic C4-shaped docs (~2 KB median) "
+            "per GPU (BASELINE.json configs[1])")
+GROUP_DOCS = 65536  # row-group size of the synthetic corpus
 
 
 def shipped_chain():
@@ -169,8 +172,8 @@ def run_reference(args, rank, world):
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "u8", "data": "synthetic",
-            "config": {"workload": "C4QualityFilter+GopherQualityFilter+GopherRepetitionFilter chain, synthetic C4-shaped docs (~2 KB median)",
-                       "docs_per_step": sample, "bytes_per_step": int(off[-1]), "note": "bounded sample of the 1M-doc workload"},
+            "config": {"workload": WORKLOAD, "docs_per_step": sample, "bytes_per_step": int(off[-1]),
+                       "note": "CPU arm: each step is a bounded sample of the workload"},
             "text_gbs": float(off[-1]) / dt / 1e9,
             "cpu_baseline": {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
                              "sample": f"{sample} docs ({off[-1] / 1e6:.1f} MB) per step, C++ restatement of the reference CPU chain (the Rust reference cannot be built here)"},
@@ -216,18 +219,25 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    # ---- synthetic shard of this rank, generated straight into pinned host memory
-    holder = {}
-
-    def alloc(nbytes):
-        holder["t"] = torch.empty(max(nbytes, 1), dtype=torch.uint8, pin_memory=True)
-        return holder["t"].numpy()
+    # ---- this rank's row groups of the synthetic corpus (round-robin, no overlap between ranks), in pinned host memory
+    from textblaster_b200 import shard
 
     t_gen = time.perf_counter()
-    utf8, off = synth.generate(args.docs, seed=synth.BASE_SEED + 2, first_index=rank * args.docs, out=alloc)
-    off_t = torch.from_numpy(off).pin_memory()
+    groups = shard.row_groups(world * args.docs, min(GROUP_DOCS, args.docs))
+    mine = shard.groups_of_rank(len(groups), rank, world)
+    parts = [synth.generate(b - a, seed=synth.BASE_SEED + 2, first_index=a) for a, b in (groups[g] for g in mine)]
+    n_docs = sum(len(o) - 1 for _, o in parts)
+    n_bytes = sum(int(o[-1]) for _, o in parts)
+    holder = {"t": torch.empty(max(n_bytes, 1), dtype=torch.uint8, pin_memory=True)}
+    utf8 = holder["t"].numpy()
+    off_t = torch.empty(n_docs + 1, dtype=torch.int64, pin_memory=True)
     off = off_t.numpy()
-    n_docs, n_bytes = args.docs, int(off[-1])
+    pos = doc = 0
+    for u, o in parts:
+        utf8[pos:pos + int(o[-1])] = u[:int(o[-1])]
+        off[doc:doc + len(o)] = o + pos
+        pos += int(o[-1]); doc += len(o) - 1
+    del parts
     t_gen = time.perf_counter() - t_gen
     steps = shipped_chain()
     pipe = GpuBatchPipeline(steps, device=local_rank)
@@ -242,9 +252,13 @@ def main():
         pipe.release(out)
         return r
 
+    last_keep = {}
+
     def step_host():
         pipe.run_raw(utf8.ctypes.data, off.ctypes.data, True, n_docs, out)
-        r = (out.gpu_launches, out.gpu_ms, int(np.ctypeslib.as_array(out.keep, (n_docs,)).sum()) if n_docs else 0, int(out.content_bytes))
+        keep = np.ctypeslib.as_array(out.keep, (n_docs,)) if n_docs else np.zeros(0, np.uint8)
+        last_keep["k"] = keep.copy()
+        r = (out.gpu_launches, out.gpu_ms, int(keep.sum()), int(out.content_bytes))
         pipe.release(out)
         return r
 
@@ -272,6 +286,15 @@ def main():
 
     dt_dev, launches, gpu_ms, kept, cbytes, clocks, ktimes = timed(step_device)
     dt_e2e, launches_e, gpu_ms_e, _, _, clocks_e, _ = timed(step_host)
+    # host-side gather of the keep masks onto rank 0, ordered by row group (the only cross-rank traffic of the job)
+    t0 = time.perf_counter()
+    local, pos = {}, 0
+    for g in mine:
+        a, b = groups[g]
+        local[g] = last_keep["k"][pos:pos + (b - a)]
+        pos += b - a
+    masks = shard.gather_keep_masks(local, len(groups), rank, world)
+    gather_s = time.perf_counter() - t0
 
     if rank == 0:
         K = max(args.steps, 1)
@@ -291,8 +314,9 @@ def main():
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": dt_dev / K * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "u8", "data": "synthetic",
-            "config": {"workload": "C4QualityFilter+GopherQualityFilter+GopherRepetitionFilter chain, 1M synthetic C4-shaped docs (~2 KB median) per GPU (BASELINE.json configs[1])",
-                       "docs_per_gpu_per_step": n_docs, "bytes_per_gpu_per_step": n_bytes, "sharding": "documents by rank, no collective",
+            "config": {"workload": WORKLOAD, "docs_per_gpu_per_step": n_docs, "bytes_per_gpu_per_step": n_bytes,
+                       "sharding": "row groups of %d docs round-robin over ranks, no data-path collective; keep masks gathered on the host (%.3f s, outside the timed region)" % (min(GROUP_DOCS, args.docs), gather_s),
+                       "kept_total": int(sum(int(m.sum()) for m in masks)),
                        "chunk_mb": args.chunk_mb, "l2": "inputs (%.2f GB per step) larger than the 126 MB L2" % (n_bytes / 1e9),
                        "generator_s": round(t_gen, 2)},
             "text_gbs": world * n_bytes * K / dt_dev / 1e9,
