@@ -296,10 +296,14 @@ def main():
     masks = shard.gather_keep_masks(local, len(groups), rank, world)
     gather_s = time.perf_counter() - t0
 
+    tot = torch.tensor([n_docs, n_bytes], dtype=torch.int64, device="cuda")
+    if world > 1:
+        dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+    total_docs, total_bytes = int(tot[0].item()), int(tot[1].item())
     if rank == 0:
         K = max(args.steps, 1)
-        value = world * n_docs * K / dt_dev
-        e2e = world * n_docs * K / dt_e2e
+        value = total_docs * K / dt_dev
+        e2e = total_docs * K / dt_e2e
         # roofline of the dominant kernel (device-resident run)
         dom = max(ktimes.items(), key=lambda kv: kv[1][0]) if ktimes else ("", (0.0, 0))
         dom_name, (dom_ms, dom_launches) = dom
@@ -319,10 +323,10 @@ def main():
                        "kept_total": int(sum(int(m.sum()) for m in masks)),
                        "chunk_mb": args.chunk_mb, "l2": "inputs (%.2f GB per step) larger than the 126 MB L2" % (n_bytes / 1e9),
                        "generator_s": round(t_gen, 2)},
-            "text_gbs": world * n_bytes * K / dt_dev / 1e9,
+            "text_gbs": total_bytes * K / dt_dev / 1e9, "total_docs_per_step": total_docs,
             "gpu_ms_per_step": gpu_ms / K, "keep_rate": kept / max(n_docs, 1),
             "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": n_bytes + 8 * (n_docs + 1),
-                    "d2h_bytes_per_step": n_docs * (2 + stats_bytes) + cbytes + 8 * (n_docs + 1), "text_gbs": world * n_bytes * K / dt_e2e / 1e9,
+                    "d2h_bytes_per_step": n_docs * (2 + stats_bytes) + cbytes + 8 * (n_docs + 1), "text_gbs": total_bytes * K / dt_e2e / 1e9,
                     "ms_per_step": dt_e2e / K * 1e3},
             "gpu_launches": launches,
             "roofline": {"bound": "hbm", "kernel": dom_name, "achieved": achieved, "peak": peak, "unit": "GB/s",

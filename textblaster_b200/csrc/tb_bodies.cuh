@@ -278,14 +278,19 @@ TB_D void body_c4_a(const KBatch& a, const uint16_t* s_ascii, const C4Cfg& cfg, 
 }
 
 // Pass B: words per processed line (count, longest), terminal punctuation, javascript / policy.
-struct C4bSink {
+struct C4bSink {  // words arrive in text order: aggregate per line in registers, one pair of atomics per line and lane
   uint32_t* lwc; uint32_t* lmax; uint64_t lbase; int64_t p0, p1; uint32_t nlmask;
+  uint64_t cur; uint32_t cnt, mx;
+  TB_D void flush() {
+    if (cnt) { simt_atomic_add(&lwc[cur], cnt); simt_atomic_max(&lmax[cur], mx); }
+    cnt = 0; mx = 0;
+  }
   TB_D void on_word(WordInfo& w) {
     int64_t x = w.start < p1 ? w.start : p1;
     uint32_t below = (x - p0) >= 32 ? nlmask : (nlmask & ((1u << (uint32_t)(x - p0)) - 1u));
     uint64_t li = lbase + simt_popc(below);
-    simt_atomic_add(&lwc[li], 1u);
-    simt_atomic_max(&lmax[li], w.nchars);
+    if (li != cur) { flush(); cur = li; }
+    cnt++; mx = w.nchars > mx ? w.nchars : mx;
   }
 };
 TB_D void body_c4_b(const KBatch& a, const uint16_t* s_ascii, const C4Cfg& cfg, const C4Scratch& s, int64_t d, int lane) {
@@ -302,8 +307,9 @@ TB_D void body_c4_b(const KBatch& a, const uint16_t* s_ascii, const C4Cfg& cfg, 
     uint32_t tot, pre = simt_exscan((uint32_t)simt_popc(nlmask), lane, &tot);
     if (p0 < R.re) {
       uint64_t lbase = lb + nl + pre;
-      C4bSink sink{s.lwc, s.lmax, lbase, p0, p1, nlmask};
+      C4bSink sink{s.lwc, s.lmax, lbase, p0, p1, nlmask, lbase, 0u, 0u};
       tb_walk_words_fast<0>(C, R, p0, p1, sink);
+      sink.flush();
       uint32_t line = 0, fl = 0;
       for (int64_t i = p0; i < p1; i++) {
         uint32_t b = t[i];

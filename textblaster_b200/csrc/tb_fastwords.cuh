@@ -42,7 +42,7 @@ TB_HD bool tb_ascii_class_ok(uint32_t ci) {
          c == WB_MIDNUMLET || c == WB_MIDLETTER || c == WB_MIDNUM || c == WB_NUMERIC || c == WB_EXTENDNUMLET || c == WB_WSEG;
 }
 
-#define TB_FW_WIN 48
+#define TB_FW_WIN 64
 #define TB_FW_LCTX 2
 
 TB_HD uint32_t tb_funnel_r(uint32_t lo, uint32_t hi, uint32_t bytes) {
@@ -59,15 +59,6 @@ TB_HD int tb_ctz64(uint64_t v) {
   return __builtin_ctzll(v);
 #endif
 }
-
-TB_HD int tb_msb64(uint64_t v) {  // index of the highest set bit, v != 0
-#if defined(__CUDA_ARCH__)
-  return 63 - __clzll((long long)v);
-#else
-  return 63 - __builtin_clzll(v);
-#endif
-}
-
 TB_HD int tb_popc64(uint64_t v) {
 #if defined(__CUDA_ARCH__)
   return __popcll(v);
@@ -78,28 +69,14 @@ TB_HD int tb_popc64(uint64_t v) {
 
 struct AsciiWin {
   uint64_t A, WC, brk;
-  int64_t base;   // byte position of bit 0
-  uint32_t lim;   // boundary bits up to and including `lim` are final
-  uint32_t x[TB_FW_WIN / 4];  // the window bytes (bytes outside the range read as 0)
+  uint64_t dirty;  // decisions that involve a non-ASCII byte, a '\r', or bytes beyond the window: not final
+  int64_t base;    // byte position of bit 0
 };
-// byte j of the window, j a compile-time constant after unrolling
-#define TB_FW_BYTE(w, j) (((w).x[(j) >> 2] >> (8 * ((j) & 3))) & 0xFFu)
-// 48-bit mask of the window bytes equal to c (bytes are < 0x80)
-TB_HD uint64_t tb_fw_eqmask(const AsciiWin& w, uint32_t c) {
-  uint64_t m = 0;
-  const uint32_t cc = c * 0x01010101u;
-#pragma unroll
-  for (int k = 0; k < TB_FW_WIN / 4; k++) {
-    uint32_t z = w.x[k] ^ cc;
-    uint32_t nz = ((z + 0x7F7F7F7Fu) | z) & 0x80808080u;   // high bit set where the byte differs
-    uint32_t eq = (nz ^ 0x80808080u) >> 7;                 // 0x01 per equal byte
-    m |= (uint64_t)((eq * 0x01020408u) >> 24 & 0xFu) << (4 * k);
-  }
-  return m;
-}
 
-// Build the window for the stretch starting at p0.  Returns false when the fast path does not apply.
-TB_HD bool tb_ascii_window(const Classifier& C, const TextRange& R, int64_t p0, AsciiWin& w) {
+// Build the window for the stretch starting at p0 (64 bytes: 2 of left context, the 32-byte stretch, 30 of
+// right context).  Bytes outside the range read as 0.  Decisions whose four-byte neighbourhood holds a
+// non-ASCII byte or a '\r' are flagged dirty instead of failing the whole window.
+TB_HD void tb_ascii_window(const Classifier& C, const TextRange& R, int64_t p0, AsciiWin& w) {
   const uint8_t* af = C.aflags();
   const int64_t base = p0 - TB_FW_LCTX;
   const uintptr_t addr = (uintptr_t)(R.t + base);
@@ -112,28 +89,26 @@ TB_HD bool tb_ascii_window(const Classifier& C, const TextRange& R, int64_t p0, 
     int64_t q = q0 + 4 * k;
     uint32_t v = 0;
     if (q >= R.rs && q + 4 <= R.re) v = TB_LDG((const uint32_t*)(a0 + 4 * k));
-    else {
+    else if (q + 4 > R.rs && q < R.re) {
       for (int r = 0; r < 4; r++) { int64_t pos = q + r; if (pos >= R.rs && pos < R.re) v |= tb_byte(R.t, pos) << (8 * r); }
     }
     raw[k] = v;
   }
-  uint32_t bad = 0;
-  uint64_t mA = 0, mN = 0, mMLQ = 0, mMNQ = 0, mE = 0, mS = 0, mWC = 0;
+  uint64_t mA = 0, mN = 0, mMLQ = 0, mMNQ = 0, mE = 0, mS = 0, mWC = 0, mNA = 0;
 #pragma unroll
   for (int k = 0; k < TB_FW_WIN / 4; k++) {
     uint32_t x = mis ? tb_funnel_r(raw[k], raw[k + 1], mis) : raw[k];
-    w.x[k] = x;
-    bad |= x & 0x80808080u;
-    uint32_t z = x ^ 0x0D0D0D0Du;                               // '\r' (WB3 CR x LF) -> general path
-    bad |= ((z + 0x7F7F7F7Fu) | z) ^ 0xFFFFFFFFu;               // nonzero high bit where a byte of z is 0 (bytes < 0x80)
+    uint32_t hi = x & 0x80808080u;                              // non-ASCII bytes
+    uint32_t z = (x & 0x7F7F7F7Fu) ^ 0x0D0D0D0Du;               // '\r' (WB3 CR x LF is left to the general machine)
+    uint32_t cr = (((z + 0x7F7F7F7Fu) | z) & 0x80808080u) ^ 0x80808080u;
+    uint32_t na = (hi | cr) >> 7;
     uint32_t fw = (uint32_t)af[x & 0x7Fu] | ((uint32_t)af[(x >> 8) & 0x7Fu] << 8) | ((uint32_t)af[(x >> 16) & 0x7Fu] << 16) |
                   ((uint32_t)af[(x >> 24) & 0x7Fu] << 24);
-#define TB_FW_GATHER(mask, bit) mask |= (uint64_t)((((fw >> (bit)) & 0x01010101u) * 0x01020408u) >> 24) << (4 * k)
-    TB_FW_GATHER(mA, 0); TB_FW_GATHER(mN, 1); TB_FW_GATHER(mMLQ, 2); TB_FW_GATHER(mMNQ, 3);
-    TB_FW_GATHER(mE, 4); TB_FW_GATHER(mS, 5); TB_FW_GATHER(mWC, 7);
+#define TB_FW_GATHER(mask, v) mask |= (uint64_t)((((v) & 0x01010101u) * 0x01020408u) >> 24) << (4 * k)
+    TB_FW_GATHER(mA, fw); TB_FW_GATHER(mN, fw >> 1); TB_FW_GATHER(mMLQ, fw >> 2); TB_FW_GATHER(mMNQ, fw >> 3);
+    TB_FW_GATHER(mE, fw >> 4); TB_FW_GATHER(mS, fw >> 5); TB_FW_GATHER(mWC, fw >> 7); TB_FW_GATHER(mNA, na);
 #undef TB_FW_GATHER
   }
-  if (bad & 0x80808080u) return false;
   const uint64_t AN = mA | mN, ANE = AN | mE;
   const uint64_t nb = ((AN << 1) & AN)                                                      // WB5, WB8, WB9, WB10
                       | ((mA << 1) & mMLQ & (mA >> 1)) | ((mA << 2) & (mMLQ << 1) & mA)     // WB6, WB7
@@ -141,28 +116,41 @@ TB_HD bool tb_ascii_window(const Classifier& C, const TextRange& R, int64_t p0, 
                       | ((ANE << 1) & mE) | ((mE << 1) & AN)                                // WB13a, WB13b
                       | ((mS << 1) & mS);                                                   // WB3d
   w.A = mA; w.WC = mWC; w.brk = ~nb; w.base = base;
-  // a decision at bit j looks at bytes j-2 .. j+1: final for j <= WIN-2, or up to eot when the text ends in the window
+  // a decision at bit j looks at bytes j-2 .. j+1: it is final only if none of them is non-ASCII / '\r' and
+  // byte j+1 is inside the window (or beyond the end of the text, which ends inside the window)
   const int64_t left = R.re - base;
-  w.lim = left <= TB_FW_WIN ? (uint32_t)left : (uint32_t)(TB_FW_WIN - 2);
-  return true;
+  const uint32_t lim = left < TB_FW_WIN ? (uint32_t)left : (uint32_t)(TB_FW_WIN - 2);
+  w.dirty = mNA | (mNA << 1) | (mNA << 2) | (mNA >> 1) | ~((2ull << lim) - 1ull);
 }
 
-// Walk the stretch [p0, p1): fast path when possible, the general machine otherwise.
+// Walk the stretch [p0, p1): segments whose boundary decisions are all clean come straight from the masks;
+// dirty runs and segments that touch a dirty decision are handed to the general machine (tb_walk_words),
+// always in text order.
 template <int MODE, class Sink>
 TB_HD uint32_t tb_walk_words_fast(const Classifier& C, const TextRange& R, int64_t p0, int64_t p1, Sink& sink) {
   AsciiWin w;
-  if (!tb_ascii_window(C, R, p0, w)) return tb_walk_words<MODE>(C, R, p0, p1, sink);
+  tb_ascii_window(C, R, p0, w);
   const uint32_t s0 = TB_FW_LCTX, s1 = (uint32_t)(p1 - w.base);  // own segment starts: bits [s0, s1)
-  uint64_t own = w.brk & ((1ull << s1) - 1ull) & ~((1ull << s0) - 1ull);
-  while (own) {
-    const uint32_t s = (uint32_t)tb_ctz64(own);
-    own &= own - 1;
-    const uint64_t rest = (w.brk >> (s + 1)) << (s + 1) & ((w.lim >= 63 ? ~0ull : ((2ull << w.lim) - 1ull)));
-    if (!rest) {  // the segment does not close inside the window
-      tb_walk_words<MODE>(C, R, w.base + s, w.base + s + 1, sink);
+  const uint64_t ownrange = ((1ull << s1) - 1ull) & ~((1ull << s0) - 1ull);
+  const uint64_t dm = w.dirty & ownrange;
+  // work items in text order: clean segment starts, and the first bit of every dirty run
+  uint64_t todo = (w.brk & ~w.dirty & ownrange) | (dm & ~(dm << 1));
+  const uint64_t stop = w.brk | w.dirty;
+  uint32_t flags = 0;
+  while (todo) {
+    const uint32_t s = (uint32_t)tb_ctz64(todo);
+    todo &= todo - 1;
+    if ((w.dirty >> s) & 1ull) {  // dirty run [s, hi): the general machine emits the segments that start in it
+      const uint32_t hi = s + (uint32_t)tb_ctz64(~(dm >> s));
+      flags |= tb_walk_words<MODE>(C, R, w.base + s, w.base + hi, sink);
       continue;
     }
+    const uint64_t rest = (stop >> (s + 1)) << (s + 1);  // never empty: the bits beyond the window are dirty
     const uint32_t e = (uint32_t)tb_ctz64(rest);
+    if ((w.dirty >> e) & 1ull) {  // the segment runs into a dirty decision
+      flags |= tb_walk_words<MODE>(C, R, w.base + s, w.base + s + 1, sink);
+      continue;
+    }
     const uint64_t seg = ((1ull << e) - 1ull) & ~((1ull << s) - 1ull);
     if (!(w.WC & seg)) continue;  // no word character: not a word (text.rs:139-157)
     WordInfo wi;
@@ -176,11 +164,9 @@ TB_HD uint32_t tb_walk_words_fast(const Classifier& C, const TextRange& R, int64
       fb = fb < 26u ? (1u << fb) : (1u << 26);
       if (len <= C.key_maxlen && ((C.key_lenmask >> (len < 31u ? len : 31u)) & 1u) && (C.key_firstmask & fb)) {
         for (int64_t i = wi.start; i < wi.end; i++) { uint32_t b = tb_byte(R.t, i); wi.key.push((b - 'A') < 26u ? b + 32u : b); }
-      } else {
-        wi.key.len = 0;  // cannot equal any stop word: an empty key never matches (sw_lookup)
-      }
+      }  // else: cannot equal any stop word; an empty key never matches (sw_lookup)
     }
     sink.on_word(wi);
   }
-  return 0;  // ASCII: no complex-script flag
+  return flags;
 }

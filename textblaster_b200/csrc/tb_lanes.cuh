@@ -138,8 +138,7 @@ struct GrSink {
     o->nw++;
   }
 };
-TB_HD void gr_lane(const Classifier& C, const TextRange& R, int64_t p0, int64_t p1, GrLane& o);
-TB_HD void gr_lane_general(const Classifier& C, const TextRange& R, int64_t p0, int64_t p1, GrLane& o) {
+TB_HD void gr_lane(const Classifier& C, const TextRange& R, int64_t p0, int64_t p1, GrLane& o) {
   const uint8_t* t = R.t;
   o.nw = 0;
   GrSink sink{&o};
@@ -157,72 +156,6 @@ TB_HD void gr_lane_general(const Classifier& C, const TextRange& R, int64_t p0, 
     } else { cur.push(b); cur_len++; }
   }
   o.tail = cur; o.tail_len = cur_len;
-}
-// ASCII fast path of gr_lane.  One running polynomial hash R over the bytes of the stretch (never
-// reset) serves both the words and the line pieces: hash(bytes [a, b)) = R_b - R_a * B^(b-a), so a
-// single converged loop over the window replaces the per-word and per-piece hashing loops.
-TB_HD Hash2 gr_hdiff(Hash2 rb, Hash2 ra, uint64_t pw) {  // R_b - R_a * B^len
-  Hash2 r;
-  r.a = tb_am(rb.a, TB_P31 - tb_mm(ra.a, (uint32_t)(pw >> 32)));
-  r.b = tb_am(rb.b, TB_P31 - tb_mm(ra.b, (uint32_t)pw));
-  return r;
-}
-TB_HD bool gr_lane_fast(const Classifier& C, const TextRange& R, int64_t p0, int64_t p1, GrLane& o) {
-  AsciiWin w;
-  if (!tb_ascii_window(C, R, p0, w)) return false;
-  // owned word segments as start / end bit masks (ASCII words are never adjacent: two alphanumeric
-  // segments next to each other would have been joined by WB5/8/9/10)
-  const uint32_t s0 = TB_FW_LCTX, s1 = (uint32_t)(p1 - w.base);
-  uint64_t own = w.brk & ((1ull << s1) - 1ull) & ~((1ull << s0) - 1ull);
-  const uint64_t limmask = (2ull << w.lim) - 1ull;
-  uint64_t ws = 0, we = 0;
-  bool closed = true;  // (no return inside the loop: keeps the lanes of a warp converged afterwards)
-  while (own) {
-    const uint32_t s = (uint32_t)tb_ctz64(own);
-    own &= own - 1;
-    const uint64_t rest = ((w.brk >> (s + 1)) << (s + 1)) & limmask;
-    const uint32_t e = rest ? (uint32_t)tb_ctz64(rest) : s + 1;
-    const uint64_t seg = ((1ull << e) - 1ull) & ~((1ull << s) - 1ull);
-    closed = closed && rest != 0;
-    if (w.WC & seg) { ws |= 1ull << s; we |= 1ull << e; }
-  }
-  if (!closed) return false;  // a segment runs out of the window: let the general path handle the stretch
-  const uint32_t jend = we ? (uint32_t)tb_msb64(we) : 0u;  // end of the last owned word
-  const uint32_t jmax = jend > s1 ? jend : s1;
-  o.nw = 0; o.flags = 0; o.has_nl = 0; o.first_nl = 0; o.np = 0; o.nchars = s1 - s0;
-  o.head.init(); o.head_len = 0;
-  Hash2 Rr; Rr.init();
-  Hash2 hw; hw.init(); uint32_t wstart = 0;      // R and position at the start of the open word
-  Hash2 hp; hp.init(); uint32_t pstart = s0;     // R and position at the start of the open line piece
-  for (uint32_t j = TB_FW_LCTX; j < jmax; j++) {  // rolled on purpose: unrolling it blows the instruction cache
-    if ((we >> j) & 1ull) {
-      uint32_t len = j - wstart;
-      if (o.nw < TB_LANE_MAXW) { o.wh[o.nw] = gr_hdiff(Rr, hw, tb_pow_pack(C.u.powtab, len)).pack(); o.wl[o.nw] = len; }
-      o.nw++;
-    }
-    if ((ws >> j) & 1ull) { hw = Rr; wstart = j; }
-    const uint32_t b = tb_byte(R.t, w.base + j);
-    if (j < s1 && b == '\n') {
-      uint32_t len = j - pstart;
-      if (!o.has_nl) { o.has_nl = 1; o.first_nl = j - s0; o.head = gr_hdiff(Rr, hp, tb_pow_pack(C.u.powtab, len)); o.head_len = len; }
-      else if (len) { o.ph[o.np] = gr_hdiff(Rr, hp, tb_pow_pack(C.u.powtab, len)).pack(); o.pl[o.np] = len; o.pend[o.np] = j - s0; o.np++; }
-      pstart = j + 1;
-    }
-    if (j == s1) { o.tail = gr_hdiff(Rr, hp, tb_pow_pack(C.u.powtab, j - pstart)); o.tail_len = j - pstart; }  // words may run past p1
-    Rr.push(b);
-    if (b == '\n' && j < s1) hp = Rr;
-  }
-  if (jmax <= s1) { o.tail = gr_hdiff(Rr, hp, tb_pow_pack(C.u.powtab, s1 - pstart)); o.tail_len = s1 - pstart; }
-  if ((we >> jmax) & 1ull) {  // a word that ends exactly at jmax (>= s1)
-    uint32_t len = jmax - wstart;
-    if (o.nw < TB_LANE_MAXW) { o.wh[o.nw] = gr_hdiff(Rr, hw, tb_pow_pack(C.u.powtab, len)).pack(); o.wl[o.nw] = len; }
-    o.nw++;
-  }
-  return true;
-}
-
-TB_HD void gr_lane(const Classifier& C, const TextRange& R, int64_t p0, int64_t p1, GrLane& o) {
-  if (!gr_lane_fast(C, R, p0, p1, o)) gr_lane_general(C, R, p0, p1, o);
 }
 // was the piece starting at s (s > ts) preceded by a run of >= 2 newlines? (paragraph_exp \n{2,})
 TB_HD uint32_t gr_gap2(const TextRange& R, int64_t s) {
