@@ -21,6 +21,8 @@
 thread_local SimtWarp* simt_warp = nullptr;
 thread_local int simt_lane = 0;
 thread_local SimtBlock* simt_block = nullptr;
+uint64_t tbe_stat_tiles = 0, tbe_stat_walk = 0;
+extern "C" void tbe_stats(uint64_t* tiles, uint64_t* walk) { *tiles = tbe_stat_tiles; *walk = tbe_stat_walk; }
 
 namespace {
 
@@ -110,7 +112,10 @@ extern "C" int tbe_run_chain(const tb_step_cfg* steps, size_t n_steps, const uin
   for (int64_t d = 0; d < n; d++) body_init_ranges(offsets, 1, 0, base, rs0, re0, alive, failed, d);
   memcpy(rs, rs0, (size_t)n * 8); memcpy(re, re0, (size_t)n * 8);
   memset(rewritten, 0, (size_t)n);
-  KBatch b{text, rs, re, alive, failed, n, uc};
+  const char* fw = getenv("TBE_FORCE_WALK");
+  KBatch b{text, rs, re, alive, failed, n, uc, 0, nb, (fw && fw[0] == '1') ? TB_DBG_FORCE_WALK : 0u};
+  std::vector<LutEntry> lut(256);
+  auto build_lut = [&](int kind, uint32_t firstmask) { for (uint32_t i = 0; i < 256; i++) lut[i] = tb_lut_entry(kind, i, i < 128 ? ascii[i] : 0u, firstmask); };
   auto alive_pred = [&](int64_t d) { return alive[d] != 0; };
   bool has_c4 = false;
   for (size_t s = 0; s < n_steps; s++) {
@@ -123,7 +128,8 @@ extern "C" int tbe_run_chain(const tb_step_cfg* steps, size_t n_steps, const uin
       uint32_t mask, maxlen, lenmask, firstmask;
       std::vector<SwEntry> tab = tb_build_stop_table(tb_stop_words_of(q), &mask, &maxlen, &lenmask, &firstmask);
       SwTable sw{tab.data(), mask, maxlen, lenmask, firstmask};
-      run_warps(n, alive_pred, [&](int64_t d, int lane) { body_gq(b, ascii, sw, cfg, (int)s, (tb_gq_stats*)stats, d, lane); });
+      build_lut(TB_LUT_GQ, firstmask);
+      run_warps(n, alive_pred, [&](int64_t d, int lane) { body_gq(b, ascii, lut.data(), sw, cfg, (int)s, (tb_gq_stats*)stats, d, lane); });
     } else if (sc.type == TB_STEP_GOPHER_REPETITION) {
       const tb_gr_params& q = sc.u.gr;
       GrCfg g{};
@@ -135,7 +141,8 @@ extern "C" int tbe_run_chain(const tb_step_cfg* steps, size_t n_steps, const uin
                    (GrDoc*)G8(n1 * sizeof(GrDoc)), G32(units * TB_REP_K + n1 * TB_REP_DOC_EXTRA), G32(3 * n1), G32(16), n};
       memset(gs.counters, 0, 32);
       for (int64_t d = 0; d < n; d++) body_trim(b, ascii, ts, te, d);
-      run_warps(n, alive_pred, [&](int64_t d, int lane) { body_gr_scan(b, ascii, ts, te, gs, d, lane); });
+      build_lut(TB_LUT_GR, 0u);
+      run_warps(n, alive_pred, [&](int64_t d, int lane) { body_gr_scan(b, ascii, lut.data(), ts, te, gs, d, lane); });
       uint8_t* smem_s = (uint8_t*)G64(TB_REP_S_SMEM / 8 + 2);
       uint8_t* smem_m = (uint8_t*)G64(TB_REP_M_SMEM / 8 + 2);
       run_warps_list(gs.lists, gs.counters[0], [&](int64_t d, int lane) { body_gr_rep_s(b, smem_s, ts, te, gs, g, (int)s, (tb_gr_stats*)stats, d, lane); });
@@ -147,8 +154,9 @@ extern "C" int tbe_run_chain(const tb_step_cfg* steps, size_t n_steps, const uin
       C4Scratch cs{G8((size_t)nb + 64), G8((size_t)nb + 64), G64(n1), G32(n1), G32(n1), G32(lines), G32(lines), G32(lines),
                    G64(n1), G64(n1), G64(n1), G64(n1), G32(4 * n1)};
       run_warps(n, alive_pred, [&](int64_t d, int lane) { body_c4_a(b, ascii, cfg, cs, d, lane); });
+      build_lut(TB_LUT_C4B, 0u);
       run_warps(n, [&](int64_t d) { return alive[d] && !cs.docflags[d] && cs.nlines[d] != 0; },
-                [&](int64_t d, int lane) { body_c4_b(b, ascii, cfg, cs, d, lane); });
+                [&](int64_t d, int lane) { body_c4_b(b, ascii, lut.data(), cfg, cs, d, lane); });
       run_warps(n, [&](int64_t) { return true; }, [&](int64_t d, int lane) { body_c4_c(b, cfg, cs, d, lane); });
       { KBatch fb = b; fb.text = cs.F; fb.rs = cs.frs; fb.re = cs.fre; for (int64_t d = 0; d < n; d++) body_trim(fb, ascii, cs.frs, cs.fre, d); }
       run_warps(n, alive_pred, [&](int64_t d, int lane) { body_c4_d(b, ascii, cfg, cs, (int)s, (tb_c4_stats*)stats, rewritten, rs, re, d, lane); });

@@ -131,11 +131,11 @@ struct tb_ctx {
 struct tb_pipeline {
   tb_ctx* ctx = nullptr;
   std::vector<StepHost> steps;
-  int64_t opt_return_content = 1, opt_validate = 0, opt_chunk = 256ll << 20;
+  int64_t opt_return_content = 1, opt_validate = 0, opt_chunk = 256ll << 20, opt_debug = 0;
   std::mutex mu;
   // device buffers (grow-only)
   DevBuf text[2], offs[2], packed[2];
-  DevBuf rs0, re0, rs, re, ts, te, alive, failed, rewritten, len, out_off, bad;
+  DevBuf rs0, re0, rs, re, ts, te, alive, failed, rewritten, len, out_off, bad, cursors;
   DevBuf stats[TB_MAX_STEPS];
   // GopherRepetition scratch
   DevBuf g_wh, g_wl, g_lh, g_ll, g_lg, g_doc, g_work, g_lists, g_counters;
@@ -280,7 +280,7 @@ int ensure_chunk_buffers(tb_pipeline* p, int64_t n, int64_t nb, bool host_input)
   if (host_input) { for (int i = 0; i < 2; i++) { ENS(p->text[i], (size_t)nb + 64); ENS(p->offs[i], n1 * 8); } }
   for (int i = 0; i < 2; i++) ENS(p->packed[i], (size_t)nb + 64);
   ENS(p->rs0, n1 * 8); ENS(p->re0, n1 * 8); ENS(p->rs, n1 * 8); ENS(p->re, n1 * 8); ENS(p->ts, n1 * 8); ENS(p->te, n1 * 8);
-  ENS(p->alive, n1); ENS(p->failed, n1); ENS(p->rewritten, n1); ENS(p->len, n1 * 8); ENS(p->out_off, (n1 + 1) * 8); ENS(p->bad, 16);
+  ENS(p->alive, n1); ENS(p->failed, n1); ENS(p->rewritten, n1); ENS(p->len, n1 * 8); ENS(p->out_off, (n1 + 1) * 8); ENS(p->bad, 16); ENS(p->cursors, 256);
   size_t units = (size_t)nb / 2 + n1 + 1;
   for (size_t s = 0; s < p->steps.size(); s++) {
     const StepHost& sh = p->steps[s];
@@ -304,13 +304,16 @@ int ensure_chunk_buffers(tb_pipeline* p, int64_t n, int64_t nb, bool host_input)
 
 // Enqueue every kernel of the chain for one chunk whose text is at `text` (device) with ranges in
 // rs0/re0 (already initialised).  Leaves packed content in p->packed[pb] and offsets in out_off.
-int enqueue_chain(tb_pipeline* p, const uint8_t* text, int64_t n, int pb, bool want_content, bool* has_c4) {
+int enqueue_chain(tb_pipeline* p, const uint8_t* text, int64_t n, int64_t nbytes, int pb, bool want_content, bool* has_c4) {
   tb_ctx* c = p->ctx;
   cudaStream_t st = c->compute;
   CK(cudaMemcpyAsync(p->rs.p, p->rs0.p, (size_t)n * 8, cudaMemcpyDeviceToDevice, st));
   CK(cudaMemcpyAsync(p->re.p, p->re0.p, (size_t)n * 8, cudaMemcpyDeviceToDevice, st));
   CK(cudaMemsetAsync(p->rewritten.p, 0, (size_t)n, st));
-  KBatch b{text, p->rs.as<int64_t>(), p->re.as<int64_t>(), p->alive.as<uint8_t>(), p->failed.as<int8_t>(), n, c->uc};
+  CK(cudaMemsetAsync(p->cursors.p, 0, 256, st));
+  KBatch b{text, p->rs.as<int64_t>(), p->re.as<int64_t>(), p->alive.as<uint8_t>(), p->failed.as<int8_t>(), n, c->uc, 0, nbytes,
+           (uint32_t)p->opt_debug};
+  uint32_t* cursors = p->cursors.as<uint32_t>();
   *has_c4 = false;
   if (p->opt_validate) {
     CK(cudaMemsetAsync(p->bad.p, 0, 4, st));
@@ -320,14 +323,14 @@ int enqueue_chain(tb_pipeline* p, const uint8_t* text, int64_t n, int pb, bool w
     StepHost& sh = p->steps[s];
     if (sh.type == TB_STEP_GOPHER_QUALITY) {
       Timed t(p, "k_gq");
-      tb_launch_gq(st, b, sh.sw, sh.gq, (int)s, p->stats[s].as<tb_gq_stats>());
+      tb_launch_gq(st, b, sh.sw, sh.gq, (int)s, p->stats[s].as<tb_gq_stats>(), c->sm_count, cursors + s);
     } else if (sh.type == TB_STEP_GOPHER_REPETITION) {
       GrScratch g{p->g_wh.as<uint64_t>(), p->g_wl.as<uint32_t>(), p->g_lh.as<uint64_t>(), p->g_ll.as<uint32_t>(),
                   p->g_lg.as<uint8_t>(), p->g_doc.as<GrDoc>(), p->g_work.as<uint32_t>(), p->g_lists.as<uint32_t>(),
                   p->g_counters.as<uint32_t>(), n};
       CK(cudaMemsetAsync(p->g_counters.p, 0, 32, st));
       { Timed t(p, "k_trim"); tb_launch_trim(st, b, p->ts.as<int64_t>(), p->te.as<int64_t>()); }
-      { Timed t(p, "k_gr_scan"); tb_launch_gr_scan(st, b, p->ts.as<int64_t>(), p->te.as<int64_t>(), g); }
+      { Timed t(p, "k_gr_scan"); tb_launch_gr_scan(st, b, p->ts.as<int64_t>(), p->te.as<int64_t>(), g, c->sm_count); }
       { Timed t(p, "k_gr_rep_s"); tb_launch_gr_rep(st, b, p->ts.as<int64_t>(), p->te.as<int64_t>(), g, sh.gr, (int)s, p->stats[s].as<tb_gr_stats>(), c->sm_count, 0); }
       { Timed t(p, "k_gr_rep_m"); tb_launch_gr_rep(st, b, p->ts.as<int64_t>(), p->te.as<int64_t>(), g, sh.gr, (int)s, p->stats[s].as<tb_gr_stats>(), c->sm_count, 1); }
       { Timed t(p, "k_gr_rep_l"); tb_launch_gr_rep(st, b, p->ts.as<int64_t>(), p->te.as<int64_t>(), g, sh.gr, (int)s, p->stats[s].as<tb_gr_stats>(), c->sm_count, 2); }
@@ -336,7 +339,7 @@ int enqueue_chain(tb_pipeline* p, const uint8_t* text, int64_t n, int pb, bool w
                    p->c_docflags.as<uint32_t>(), p->c_lwc.as<uint32_t>(), p->c_lmax.as<uint32_t>(), p->c_lflags.as<uint32_t>(),
                    p->c_prs.as<int64_t>(), p->c_pre.as<int64_t>(), p->c_frs.as<int64_t>(), p->c_fre.as<int64_t>(), p->c_cnt.as<uint32_t>()};
       { Timed t(p, "k_c4_a"); tb_launch_c4_a(st, b, sh.c4, cs); }
-      { Timed t(p, "k_c4_b"); tb_launch_c4_b(st, b, sh.c4, cs); }
+      { Timed t(p, "k_c4_b"); tb_launch_c4_b(st, b, sh.c4, cs, c->sm_count, cursors + s); }
       { Timed t(p, "k_c4_c"); tb_launch_c4_c(st, b, sh.c4, cs); }
       {  // content = kept.join("\n").trim()   (c4_filters.rs:258)
         KBatch fb = b; fb.text = cs.F; fb.rs = cs.frs; fb.re = cs.fre;
@@ -430,7 +433,7 @@ int run_impl(tb_pipeline* p, const uint8_t* utf8, const void* offsets, int is64,
     // packed[buf] may still be read by the D2H of chunk ci-2
     CK(cudaStreamWaitEvent(c->compute, p->ev_d2h[buf], 0));
     bool has_c4 = false;
-    if ((rc = enqueue_chain(p, text, n, buf, want_content, &has_c4))) return rc;
+    if ((rc = enqueue_chain(p, text, n, ch.b1 - ch.b0, buf, want_content, &has_c4))) return rc;
     // small results
     CK(cudaMemcpyAsync(h_keep + ch.d0, p->alive.p, (size_t)n, cudaMemcpyDeviceToHost, c->compute));
     CK(cudaMemcpyAsync(h_failed + ch.d0, p->failed.p, (size_t)n, cudaMemcpyDeviceToHost, c->compute));
@@ -599,6 +602,7 @@ int tb_pipeline_set_option(tb_pipeline* p, int32_t option, int64_t value) {
   switch (option) {
     case TB_OPT_RETURN_CONTENT: p->opt_return_content = value != 0; return TB_OK;
     case TB_OPT_VALIDATE_UTF8: p->opt_validate = value != 0; return TB_OK;
+    case TB_OPT_GENERAL_WORD_PATH: p->opt_debug = value != 0 ? TB_DBG_FORCE_WALK : 0; return TB_OK;
     case TB_OPT_CHUNK_BYTES:
       if (value < (1 << 16)) return fail(TB_ERR_INVALID_ARGUMENT, "chunk size must be at least 64 KiB");
       p->opt_chunk = value; return TB_OK;

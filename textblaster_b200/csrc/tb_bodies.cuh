@@ -9,6 +9,14 @@
 #include "tb_kernels.cuh"
 #include "tb_rep.cuh"
 #include "tb_simt.cuh"
+#include "tb_tile.cuh"
+
+#if defined(TB_HOST_EMUL)
+extern uint64_t tbe_stat_tiles, tbe_stat_walk;  // documents taken by the mask path / by the walking path (lane 0 counts)
+#define TBE_COUNT(var, lane) do { if ((lane) == 0) __atomic_fetch_add(&(var), 1, __ATOMIC_RELAXED); } while (0)
+#else
+#define TBE_COUNT(var, lane) do { } while (0)
+#endif
 
 #define TB_BLOCK 32  // one warp per CTA: a document never waits for a longer neighbour in its CTA
 
@@ -56,16 +64,22 @@ TB_D void body_validate_utf8(const uint8_t* t, const int64_t* rs, const int64_t*
 // ---------------------------------------------------------------------------------------------
 // GopherQualityFilter: one pass, then the threshold checks of gopher_quality.rs:198-295
 // ---------------------------------------------------------------------------------------------
-TB_D void body_gq(const KBatch& a, const uint16_t* s_ascii, const SwTable& sw, const GqCfg& cfg, int step,
+TB_D void gq_doc_walk(const Classifier& C, const TextRange& R, const SwTable& sw, GqAcc& acc, int lane) {
+  for (int64_t base = R.rs; base < R.re; base += TB_TILE) {
+    int64_t p0 = base + lane * TB_STRETCH;
+    if (p0 < R.re) { int64_t p1 = p0 + TB_STRETCH < R.re ? p0 + TB_STRETCH : R.re; gq_lane(C, R, sw, p0, p1, acc); }
+  }
+}
+TB_D bool gq_doc_tiles(const KBatch& a, const LutEntry* lut, const Classifier& C, const SwTable& sw, const TextRange& R,
+                       GqAcc& acc, int lane);
+TB_D void body_gq(const KBatch& a, const uint16_t* s_ascii, const LutEntry* lut, const SwTable& sw, const GqCfg& cfg, int step,
                   tb_gq_stats* out, int64_t d, int lane) {
   Classifier C{s_ascii, a.uc};
   C.key_maxlen = sw.maxlen; C.key_lenmask = sw.lenmask; C.key_firstmask = sw.firstmask;
   TextRange R{a.text, a.rs[d], a.re[d]};
   GqAcc acc; acc.zero();
-  for (int64_t base = R.rs; base < R.re; base += TB_TILE) {
-    int64_t p0 = base + lane * TB_STRETCH;
-    if (p0 < R.re) { int64_t p1 = p0 + TB_STRETCH < R.re ? p0 + TB_STRETCH : R.re; gq_lane(C, R, sw, p0, p1, acc); }
-  }
+  if ((a.dbg & TB_DBG_FORCE_WALK) || !gq_doc_tiles(a, lut, C, sw, R, acc, lane)) { acc.zero(); gq_doc_walk(C, R, sw, acc, lane); TBE_COUNT(tbe_stat_walk, lane); }
+  else TBE_COUNT(tbe_stat_tiles, lane);
   uint32_t n_words = simt_sum(acc.n_words), n_alpha = simt_sum(acc.n_alpha), n_stop = simt_sum(acc.n_stop),
            n_hash = simt_sum(acc.n_hash), n_ell = simt_sum(acc.n_ell), n_lines = simt_sum(acc.n_lines),
            n_bullet = simt_sum(acc.n_bullet), n_ell_lines = simt_sum(acc.n_ell_lines), flags = simt_or(acc.flags);
@@ -122,10 +136,11 @@ TB_D HL hl_shfl_up(HL v, int o) { HL r; r.a = simt_shfl_up(v.a, o); r.b = simt_s
 TB_D HL hl_shfl(HL v, int src) { HL r; r.a = simt_shfl(v.a, src); r.b = simt_shfl(v.b, src); r.len = simt_shfl(v.len, src); return r; }
 TB_D uint64_t hl_pack(HL v) { return ((uint64_t)tb_canon31(v.a) << 32) | tb_canon31(v.b); }
 
-TB_D void body_gr_scan(const KBatch& a, const uint16_t* s_ascii, const int64_t* ts, const int64_t* te, const GrScratch& s,
-                       int64_t d, int lane) {
-  Classifier C{s_ascii, a.uc};
-  TextRange R{a.text, ts[d], te[d]};
+struct GrTotals { uint32_t W, NL, flags; uint64_t nchars; };
+
+// general path: segment-walking lanes (tb_lanes.cuh)
+TB_D void gr_doc_walk(const KBatch& a, const Classifier& C, const TextRange& R, const GrScratch& s, int64_t d, int lane,
+                      GrTotals& out) {
   const uint64_t ub = (uint64_t)(R.rs >> 1) + (uint64_t)d;
   uint64_t* wh = s.wh + ub; uint32_t* wl = s.wl + ub;
   uint64_t* lh = s.lh + ub; uint32_t* ll = s.ll + ub; uint8_t* lg = s.lg + ub;
@@ -182,9 +197,22 @@ TB_D void body_gr_scan(const KBatch& a, const uint16_t* s_ascii, const int64_t* 
     if (lane == 0) { lh[NL] = hl_pack(carry); ll[NL] = carry.len; lg[NL] = (uint8_t)gr_gap2(R, R.re - carry.len); }
     NL++;
   }
-  flags = simt_or(flags);
-  nchars = simt_sum64(nchars);
+  out.W = W; out.NL = NL; out.flags = flags; out.nchars = nchars;
+}
+TB_D bool gr_doc_tiles(const KBatch& a, const LutEntry* lut, const Classifier& C, const TextRange& R, const GrScratch& s,
+                       int64_t d, int lane, GrTotals& out);
+
+TB_D void body_gr_scan(const KBatch& a, const uint16_t* s_ascii, const LutEntry* lut, const int64_t* ts, const int64_t* te,
+                       const GrScratch& s, int64_t d, int lane) {
+  Classifier C{s_ascii, a.uc};
+  TextRange R{a.text, ts[d], te[d]};
+  GrTotals o;
+  if ((a.dbg & TB_DBG_FORCE_WALK) || !gr_doc_tiles(a, lut, C, R, s, d, lane, o)) { gr_doc_walk(a, C, R, s, d, lane, o); TBE_COUNT(tbe_stat_walk, lane); }
+  else TBE_COUNT(tbe_stat_tiles, lane);
+  const uint32_t flags = simt_or(o.flags);
+  const uint64_t nchars = simt_sum64(o.nchars);
   if (lane == 0) {
+    const uint32_t W = o.W, NL = o.NL;
     GrDoc g; g.char_len = nchars; g.W = W; g.NL = NL; g.flags = flags ? TB_DOCFLAG_COMPLEX_SCRIPT : 0; g.empty = (R.re <= R.rs);
     s.doc[d] = g;
     uint32_t big = W > NL ? W : NL;
@@ -293,10 +321,7 @@ struct C4bSink {  // words arrive in text order: aggregate per line in registers
     cnt++; mx = w.nchars > mx ? w.nchars : mx;
   }
 };
-TB_D void body_c4_b(const KBatch& a, const uint16_t* s_ascii, const C4Cfg& cfg, const C4Scratch& s, int64_t d, int lane) {
-  Classifier C{s_ascii, a.uc};
-  TextRange R{s.P, s.prs[d], s.pre[d]};
-  const uint64_t lb = (uint64_t)a.rs[d] + (uint64_t)d;
+TB_D void c4b_doc_walk(const Classifier& C, const C4Cfg& cfg, const C4Scratch& s, const TextRange& R, uint64_t lb, int lane) {
   const uint8_t* t = R.t;
   uint32_t nl = 0;
   for (int64_t base = R.rs; base < R.re; base += TB_TILE) {
@@ -326,6 +351,21 @@ TB_D void body_c4_b(const KBatch& a, const uint16_t* s_ascii, const C4Cfg& cfg, 
     }
     nl += tot;
   }
+}
+TB_D bool c4b_doc_tiles(const KBatch& a, const LutEntry* lut, const Classifier& C, const C4Cfg& cfg, const C4Scratch& s,
+                        const TextRange& R, uint64_t lb, int lane);
+TB_D void body_c4_b(const KBatch& a, const uint16_t* s_ascii, const LutEntry* lut, const C4Cfg& cfg, const C4Scratch& s, int64_t d,
+                    int lane) {
+  Classifier C{s_ascii, a.uc};
+  TextRange R{s.P, s.prs[d], s.pre[d]};
+  const uint64_t lb = (uint64_t)a.rs[d] + (uint64_t)d;
+  if (!(a.dbg & TB_DBG_FORCE_WALK) && c4b_doc_tiles(a, lut, C, cfg, s, R, lb, lane)) { TBE_COUNT(tbe_stat_tiles, lane); return; }
+  TBE_COUNT(tbe_stat_walk, lane);
+  // general path: clear what the mask path may have added, then walk
+  simt_sync();
+  for (uint32_t k = (uint32_t)lane; k <= s.nlines[d]; k += 32) { s.lwc[lb + k] = 0; s.lmax[lb + k] = 0; s.lflags[lb + k] = 0; }
+  simt_sync();
+  c4b_doc_walk(C, cfg, s, R, lb, lane);
 }
 
 // Pass C: drop lines, join the kept ones with '\n' (c4_filters.rs:207-258) -> F; line counters.
@@ -438,3 +478,5 @@ TB_D void body_pack(const uint8_t* orig, const int64_t* rs0, const uint8_t* cur,
   int64_t o = out_off[d], len = out_off[d + 1] - o;
   for (int64_t i = lane; i < len; i += 32) out[o + i] = src[i];
 }
+
+#include "tb_bodies_tile.cuh"

@@ -1,0 +1,362 @@
+// tb_bodies_tile.cuh -- mask-based document loops of the three word passes (tb_tile.cuh).  Each returns false
+// when the document holds a segment the mask form cannot express; the caller then runs the walking loop.
+// Included at the end of tb_bodies.cuh.
+#pragma once
+
+// segmented inclusive scan of open-fragment summaries; `f`: the lane holds a segment start
+TB_D Frag frag_shfl_up(Frag v, int o) { Frag r; r.nbytes = simt_shfl_up(v.nbytes, o); r.meta = simt_shfl_up(v.meta, o); return r; }
+TB_D Frag frag_shfl(Frag v, int src) { Frag r; r.nbytes = simt_shfl(v.nbytes, src); r.meta = simt_shfl(v.meta, src); return r; }
+// returns the fragment open at the start of this lane's stretch; updates carry to the one open after lane 31
+TB_D Frag frag_scan(Frag tail, uint32_t f, int lane, Frag& carry) {
+  Frag v = tail;
+  for (int off = 1; off < 32; off <<= 1) {
+    Frag vu = frag_shfl_up(v, off);
+    uint32_t fu = simt_shfl_up(f, off);
+    if (lane >= off && !f) { v = frag_cat(vu, v); f = fu; }
+  }
+  if (!f) v = frag_cat(carry, v);
+  Frag cin = frag_shfl_up(v, 1);
+  if (lane == 0) cin = carry;
+  carry = frag_shfl(v, 31);
+  return cin;
+}
+
+// ---------------------------------------------------------------------------------------------
+// GopherQualityFilter (gopher_quality.rs:73-187)
+// ---------------------------------------------------------------------------------------------
+// is the word [s, e) a stop word?  (:184-187: stop_words.contains(&word.to_lowercase()))
+TB_D bool gq_is_stop_word(const Classifier& C, const uint8_t* t, const SwTable& sw, int64_t s, int64_t e, bool pure_ascii) {
+  const uint64_t len = (uint64_t)(e - s);
+  if (pure_ascii) {
+    if (len > sw.maxlen || !((sw.lenmask >> (len < 31u ? (uint32_t)len : 31u)) & 1u)) return false;
+  } else if (len > 3ull * sw.maxlen) {  // to_lowercase() shrinks a character by at most a factor of three
+    return false;
+  }
+  LowKey k; k.init();
+  int64_t i = s;
+  while (i < e) { int l; uint32_t cp; uint32_t ci = C.at(t, i, &l, &cp); lowkey_push(C, k, cp, ci); i += l; }
+  if (k.sigma) lowkey_slow(C, t, s, e, k);
+  return sw_lookup(sw, k);
+}
+
+TB_D bool gq_doc_tiles(const KBatch& a, const LutEntry* lut, const Classifier& C, const SwTable& sw, const TextRange& R,
+                       GqAcc& acc, int lane) {
+  const uint8_t* t = R.t;
+  Frag carry{0u, 0u};
+  for (int64_t base = tb_tile_origin(R); base < R.re; base += TB_TILE) {
+    Tile T;
+    tile_classify<true>(lut, R, a.ext_lo, a.ext_hi, base + lane * TB_STRETCH, T);
+    const uint32_t fl = T.dirty ? tile_fix_dirty(C, R, T) : 0u;
+    if (simt_any((fl & TILE_EXOTIC) != 0u)) return false;
+    acc.flags |= fl & CI_COMPLEX;
+    const int64_t p0 = T.p0;
+    const uint32_t V = T.valid, B = T.brk, WC = T.m[TL_WC], LEAD = V & ~T.h[TH_CONT], NAm = T.m[TL_NA], SWF = T.h[TH_SWF];
+    const uint32_t H = tb_spread(WC, B), HA = tb_spread(T.al, B);
+    const int fb = tb_ctz32(B);                // first segment start of the stretch (32: none)
+    const int lb = B ? 31 - tb_clz32(B) : 0;   // last one
+    const uint32_t headm = tb_below(fb), tailm = B ? ~tb_below(lb) : 0xFFFFFFFFu, inner = ~headm & ~tailm;
+    // ---- segments that start and end inside the stretch
+    acc.n_words += (uint32_t)tb_popc32(B & H & inner);
+    acc.sum_chars += (uint32_t)tb_popc32(LEAD & H & inner);
+    acc.n_alpha += (uint32_t)tb_popc32(B & HA & inner);
+    uint32_t cand = B & H & inner & SWF;
+    while (cand) {
+      const int s = tb_ctz32(cand);
+      cand &= cand - 1u;
+      const int e = tb_ctz32(B & ~tb_upto(s));
+      const uint32_t seg = tb_below(e) & ~tb_below(s);
+      if (gq_is_stop_word(C, t, sw, p0 + s, p0 + e, !(NAm & seg))) acc.n_stop++;
+    }
+    // ---- the segment that was open when the stretch began ends at its first segment start
+    Frag tail = frag_of(T, tailm, B ? ((SWF >> lb) & 1u) : 0u);
+    Frag cin = frag_scan(tail, B != 0u, lane, carry);
+    if (B) {
+      Frag first = frag_cat(cin, frag_of(T, headm, 0u));
+      if (first.meta & FR_WC) {
+        acc.n_words++; acc.sum_chars += first.meta & FR_CNT;
+        if (first.meta & FR_AL) acc.n_alpha++;
+        const int64_t e = p0 + fb;
+        if ((first.meta & FR_SWF) && gq_is_stop_word(C, t, sw, e - (int64_t)first.nbytes, e, !(first.meta & FR_NA))) acc.n_stop++;
+      }
+    }
+    // ---- symbols (:104,:115)
+    acc.n_hash += (uint32_t)tb_popc32(T.h[TH_HASH]);
+    {
+      const uint32_t DOT = T.h[TH_DOT];
+      const uint32_t before = (DOT << 1) | ((T.l1hi >> (4 * TH_DOT)) & 1u);
+      uint32_t runs = DOT & ~before & ((DOT >> 1) | 0x80000000u);  // starts of dot runs that may be >= 3 long
+      while (runs) {
+        const int64_t i = p0 + tb_ctz32(runs);
+        runs &= runs - 1u;
+        int64_t j = i + 1;
+        while (j < R.re && tb_byte(t, j) == '.') j++;
+        acc.n_ell += (uint32_t)((j - i) / 3);
+      }
+      uint32_t e2 = T.h[TH_E2];
+      while (e2) {
+        const int64_t i = p0 + tb_ctz32(e2);
+        e2 &= e2 - 1u;
+        if (i + 2 < R.re && tb_byte(t, i + 1) == 0x80 && tb_byte(t, i + 2) == 0xA6) acc.n_ell++;
+      }
+    }
+    // ---- lines (:126-158)
+    {
+      const uint32_t NLm = T.h[TH_NL];
+      uint32_t LS = ((NLm << 1) | ((T.l1hi >> (4 * TH_NL)) & 1u)) & V;
+      if (R.rs >= p0 && R.rs < p0 + 32 && R.rs < R.re) LS |= 1u << (uint32_t)(R.rs - p0);
+      acc.n_lines += (uint32_t)tb_popc32(LS);
+      acc.n_bullet += (uint32_t)tb_popc32(LS & T.h[TH_DASH]);
+      uint32_t bl = LS & ~(WC & ~NAm) & ~T.h[TH_DASH];  // a line that starts with an ASCII word character is no bullet line
+      while (bl) {
+        const int i = tb_ctz32(bl);
+        bl &= bl - 1u;
+        if (gq_line_is_bullet(C, R, p0 + i)) acc.n_bullet++;
+      }
+      const uint32_t WC1 = (WC << 1) | ((T.lctx >> (4 * TL_WC + 1)) & 1u);
+      uint32_t ends = NLm & ~WC1;  // a line whose last byte is an ASCII word character cannot end with an ellipsis
+      while (ends) {
+        const int i = tb_ctz32(ends);
+        ends &= ends - 1u;
+        if (gq_line_ends_with_ellipsis(C, R, p0 + i)) acc.n_ell_lines++;
+      }
+      const int64_t last = R.re - 1;
+      if (last >= p0 && last < p0 + 32 && last >= R.rs) {
+        const uint32_t bit = 1u << (uint32_t)(last - p0);
+        if (!(NLm & bit) && !(WC & bit & ~NAm) && gq_line_ends_with_ellipsis(C, R, R.re)) acc.n_ell_lines++;
+      }
+    }
+  }
+  if (lane == 0 && (carry.meta & FR_WC)) {  // the segment that runs to the end of the text
+    acc.n_words++; acc.sum_chars += carry.meta & FR_CNT;
+    if (carry.meta & FR_AL) acc.n_alpha++;
+    if ((carry.meta & FR_SWF) && gq_is_stop_word(C, t, sw, R.re - (int64_t)carry.nbytes, R.re, !(carry.meta & FR_NA))) acc.n_stop++;
+  }
+  return true;
+}
+
+// ---------------------------------------------------------------------------------------------
+// C4QualityFilter pass B (c4_filters.rs:207-250): words per processed line, longest word, line flags
+// ---------------------------------------------------------------------------------------------
+TB_D bool c4b_doc_tiles(const KBatch& a, const LutEntry* lut, const Classifier& C, const C4Cfg& cfg, const C4Scratch& s,
+                        const TextRange& R, uint64_t lb, int lane) {
+  const uint8_t* t = R.t;
+  const bool check_len = cfg.max_word_length > 0;
+  const bool small = check_len && cfg.max_word_length < 32;  // words inside one stretch can be too long
+  const bool pats = cfg.filter_javascript != 0 || cfg.filter_policy != 0;
+  Frag carry{0u, 0u};
+  uint32_t nl = 0;
+  for (int64_t base = tb_tile_origin(R); base < R.re; base += TB_TILE) {
+    Tile T;
+    tile_classify<true>(lut, R, a.ext_lo, a.ext_hi, base + lane * TB_STRETCH, T);
+    const uint32_t fl = T.dirty ? tile_fix_dirty(C, R, T) : 0u;
+    if (simt_any((fl & TILE_EXOTIC) != 0u)) return false;
+    const int64_t p0 = T.p0;
+    const uint32_t V = T.valid, B = T.brk, WC = T.m[TL_WC], LEAD = V & ~T.h[TH_CONT], NLm = T.h[TH_NL];
+    uint32_t tot, pre = simt_exscan((uint32_t)tb_popc32(NLm), lane, &tot);
+    const uint64_t lbase = lb + nl + pre;  // line of the first byte of the stretch
+    const uint32_t H = tb_spread(WC, B);
+    const int fb = tb_ctz32(B);
+    const int lbk = B ? 31 - tb_clz32(B) : 0;
+    const uint32_t headm = tb_below(fb), tailm = B ? ~tb_below(lbk) : 0xFFFFFFFFu, inner = ~headm & ~tailm;
+    Frag tail = frag_of(T, tailm, 0u);
+    Frag cin = frag_scan(tail, B != 0u, lane, carry);
+    // word ends: bit j = a word ends just before p0 + j (its line: the '\n' count in front of j)
+    uint32_t WE = B & (H << 1) & ~tb_upto(fb);
+    if (B) {
+      Frag first = frag_cat(cin, frag_of(T, headm, 0u));
+      if (first.meta & FR_WC) {
+        WE |= 1u << fb;
+        const uint32_t cnt = first.meta & FR_CNT;
+        if (check_len && (small || cnt > 31u)) simt_atomic_max(&s.lmax[lbase + (uint32_t)tb_popc32(NLm & headm)], cnt);
+      }
+    }
+    {
+      uint32_t rem = WE, nlm = NLm;
+      uint64_t li = lbase;
+      while (rem) {
+        const uint32_t part = rem & tb_upto(tb_ctz32(nlm));
+        if (part) simt_atomic_add(&s.lwc[li], (uint32_t)tb_popc32(part));
+        rem &= ~part;
+        nlm &= nlm - 1u;
+        li++;
+      }
+    }
+    if (small) {
+      uint32_t starts = B & H & inner;
+      while (starts) {
+        const int sb = tb_ctz32(starts);
+        starts &= starts - 1u;
+        const int e = tb_ctz32(B & ~tb_upto(sb));
+        const uint32_t cnt = (uint32_t)tb_popc32(LEAD & tb_below(e) & ~tb_below(sb));
+        simt_atomic_max(&s.lmax[lbase + (uint32_t)tb_popc32(NLm & tb_below(sb))], cnt);
+      }
+    }
+    // line flags: terminal punctuation of the lines that end here, javascript / policy patterns
+    {
+      uint32_t m = NLm, k = 0;
+      while (m) {
+        const int i = tb_ctz32(m);
+        m &= m - 1u;
+        const uint32_t f = c4_line_end_flags(C, R, p0 + i);
+        if (f) simt_atomic_or(&s.lflags[lbase + k], f);
+        k++;
+      }
+      const int64_t last = R.re - 1;
+      if (last >= p0 && last < p0 + 32 && last >= R.rs && !((NLm >> (uint32_t)(last - p0)) & 1u)) {
+        const uint32_t f = c4_line_end_flags(C, R, R.re);
+        if (f) simt_atomic_or(&s.lflags[lbase + k], f);
+      }
+      if (pats) {
+        uint32_t cand = T.h[TH_P1] & ((T.h[TH_P2] >> 1) | 0x80000000u) & ((T.h[TH_P3] >> 2) | 0xC0000000u);
+        while (cand) {
+          const int i = tb_ctz32(cand);
+          cand &= cand - 1u;
+          const uint32_t f = c4_pattern_flags(t, p0 + i, R.re, tb_byte(t, p0 + i), cfg.filter_javascript != 0, cfg.filter_policy != 0);
+          if (f) simt_atomic_or(&s.lflags[lbase + (uint32_t)tb_popc32(NLm & tb_below(i))], f);
+        }
+      }
+    }
+    nl += tot;
+  }
+  if (lane == 0 && (carry.meta & FR_WC)) {  // the word that runs to the end of the text
+    simt_atomic_add(&s.lwc[lb + nl], 1u);
+    if (check_len) simt_atomic_max(&s.lmax[lb + nl], carry.meta & FR_CNT);
+  }
+  return true;
+}
+
+// ---------------------------------------------------------------------------------------------
+// GopherRepetitionFilter, pass 1 (gopher_rep.rs:57-58,80-84,120-124,159): word and line-piece hashes
+// ---------------------------------------------------------------------------------------------
+TB_D HL hl_fold(uint32_t a, uint32_t b, uint32_t len) { HL r; r.a = tb_hfold(a); r.b = tb_hfold(b); r.len = len; return r; }
+
+TB_D bool gr_doc_tiles(const KBatch& a, const LutEntry* lut, const Classifier& C, const TextRange& R, const GrScratch& s,
+                       int64_t d, int lane, GrTotals& out) {
+  const uint64_t ub = (uint64_t)(R.rs >> 1) + (uint64_t)d;
+  uint64_t* wh = s.wh + ub; uint32_t* wl = s.wl + ub;
+  uint64_t* lh = s.lh + ub; uint32_t* ll = s.ll + ub; uint8_t* lg = s.lg + ub;
+  const uint64_t* powtab = a.uc.powtab;
+  const uint32_t below_lane = tb_below(lane);
+  uint32_t W = 0, NLc = 0, flags = 0;
+  uint64_t nchars = 0;
+  HL wcarry{0u, 0u, 0u}, lcarry{0u, 0u, 0u};
+  uint32_t wcarry_wc = 0;
+  for (int64_t base = tb_tile_origin(R); base < R.re; base += TB_TILE) {
+    Tile T;
+    tile_classify<true>(lut, R, a.ext_lo, a.ext_hi, base + lane * TB_STRETCH, T);
+    const uint32_t fl = T.dirty ? tile_fix_dirty(C, R, T) : 0u;
+    if (simt_any((fl & TILE_EXOTIC) != 0u)) return false;
+    flags |= fl & CI_COMPLEX;
+    const int64_t p0 = T.p0;
+    const uint32_t V = T.valid, B = T.brk, WC = T.m[TL_WC];
+    const uint32_t NLx = T.h[TH_NL] | ~V;  // every byte outside the text ends a piece
+    nchars += (uint32_t)tb_popc32(V & ~T.h[TH_CONT]);
+    const uint32_t H = tb_spread(WC, B);
+    const int fb = tb_ctz32(B);
+    const int lbk = B ? 31 - tb_clz32(B) : 0;
+    const uint32_t headm = tb_below(fb), tailm = B ? ~tb_below(lbk) : 0xFFFFFFFFu;
+    // ---- which lanes close a word with their first segment start: "word character seen" of the open fragment
+    const uint32_t brk_lanes = simt_ballot(B != 0u), twc_lanes = simt_ballot((WC & tailm) != 0u);
+    uint32_t in_wc;
+    {
+      const uint32_t lower = brk_lanes & below_lane;
+      if (lower) in_wc = (twc_lanes & below_lane & ~tb_below(31 - tb_clz32(lower))) != 0u;
+      else in_wc = wcarry_wc | ((twc_lanes & below_lane) != 0u);
+    }
+    const uint32_t first_word = (B && (in_wc || (WC & headm))) ? 1u : 0u;
+    const uint32_t WEin = B & (H << 1) & ~tb_upto(fb);  // word ends after the first segment start
+    uint32_t wtot, wpre = simt_exscan((uint32_t)tb_popc32(WEin) + first_word, lane, &wtot);
+    // ---- line pieces: is the piece that is open at the start of the stretch non-empty?
+    const int fn = tb_ctz32(NLx);
+    const int ln_ = NLx ? 31 - tb_clz32(NLx) : -1;
+    const uint32_t nl_lanes = simt_ballot(NLx != 0u), tnz_lanes = simt_ballot(ln_ < 31);
+    uint32_t in_nz;
+    {
+      const uint32_t lower = nl_lanes & below_lane;
+      if (lower) in_nz = (tnz_lanes & below_lane & ~tb_below(31 - tb_clz32(lower))) != 0u;
+      else in_nz = (lcarry.len != 0u) | ((tnz_lanes & below_lane) != 0u);
+    }
+    const uint32_t first_piece = (NLx && (in_nz || fn > 0)) ? 1u : 0u;
+    const uint32_t PEin = NLx & ~(NLx << 1) & ~tb_upto(fn);  // a later '\n' that ends a non-empty piece
+    uint32_t ltot, lpre = simt_exscan((uint32_t)tb_popc32(PEin) + first_piece, lane, &ltot);
+    // ---- one pass over the 32 bytes: running word hash (restarts at segment starts) and piece hash
+    uint32_t wa = 0, wb = 0, wn = 0, la = 0, lb_ = 0, ln = 0;
+    uint32_t hwa = 0, hwb = 0, hwn = 0, hla = 0, hlb = 0, hln = 0;
+    uint32_t widx = W + wpre + first_word, lidx = NLc + lpre + first_piece;
+#pragma unroll
+    for (int i = 0; i < 32; i++) {
+      const uint32_t byte = (T.w[i >> 2] >> (8 * (i & 3))) & 0xFFu;
+      if ((B >> i) & 1u) {
+        if (i == fb) { hwa = wa; hwb = wb; hwn = wn; }
+        else if ((WEin >> i) & 1u) { wh[widx] = hl_pack(hl_fold(wa, wb, wn)); wl[widx] = wn; widx++; }
+        wa = 0; wb = 0; wn = 0;
+      }
+      wa = tb_hpush(wa, TB_B1, byte + 1u); wb = tb_hpush(wb, TB_B2, byte + 1u); wn++;
+      if ((NLx >> i) & 1u) {
+        if (i == fn) { hla = la; hlb = lb_; hln = ln; }
+        else if (ln) { lh[lidx] = hl_pack(hl_fold(la, lb_, ln)); ll[lidx] = ln; lg[lidx] = (uint8_t)gr_gap2(R, p0 + i - (int64_t)ln); lidx++; }
+        la = 0; lb_ = 0; ln = 0;
+      } else {
+        la = tb_hpush(la, TB_B1, byte + 1u); lb_ = tb_hpush(lb_, TB_B2, byte + 1u); ln++;
+      }
+    }
+    // ---- words: hash of the fragment open at the start of the stretch
+    {
+      HL v = hl_fold(wa, wb, wn);
+      HL cin;
+      if (brk_lanes == 0xFFFFFFFFu) {  // every lane restarts: the open fragment is the previous lane's tail
+        cin = hl_shfl_up(v, 1);
+        if (lane == 0) cin = wcarry;
+        wcarry = hl_shfl(v, 31);
+      } else {
+        uint32_t f = B != 0u;
+        for (int off = 1; off < 32; off <<= 1) {
+          HL vu = hl_shfl_up(v, off);
+          uint32_t fu = simt_shfl_up(f, off);
+          if (lane >= off && !f) { v = hl_cat(vu, v, powtab); f = fu; }
+        }
+        if (!f) v = hl_cat(wcarry, v, powtab);
+        cin = hl_shfl_up(v, 1);
+        if (lane == 0) cin = wcarry;
+        wcarry = hl_shfl(v, 31);
+      }
+      if (first_word) {
+        HL first = hl_cat(cin, hl_fold(hwa, hwb, hwn), powtab);
+        wh[W + wpre] = hl_pack(first); wl[W + wpre] = first.len;
+      }
+      // "word character seen" of the fragment open after lane 31
+      if (brk_lanes) wcarry_wc = (twc_lanes & ~tb_below(31 - tb_clz32(brk_lanes))) != 0u;
+      else wcarry_wc |= twc_lanes != 0u;
+    }
+    // ---- line pieces
+    {
+      HL v = hl_fold(la, lb_, ln);
+      uint32_t f = NLx != 0u;
+      for (int off = 1; off < 32; off <<= 1) {
+        HL vu = hl_shfl_up(v, off);
+        uint32_t fu = simt_shfl_up(f, off);
+        if (lane >= off && !f) { v = hl_cat(vu, v, powtab); f = fu; }
+      }
+      if (!f) v = hl_cat(lcarry, v, powtab);
+      HL cin = hl_shfl_up(v, 1);
+      if (lane == 0) cin = lcarry;
+      lcarry = hl_shfl(v, 31);
+      if (first_piece) {
+        HL first = hl_cat(cin, hl_fold(hla, hlb, hln), powtab);
+        const uint32_t k = NLc + lpre;
+        lh[k] = hl_pack(first); ll[k] = first.len; lg[k] = (uint8_t)gr_gap2(R, p0 + fn - (int64_t)first.len);
+      }
+    }
+    W += wtot; NLc += ltot;
+  }
+  if (wcarry_wc && wcarry.len) {  // the word / the piece that runs to the end of the text
+    if (lane == 0) { wh[W] = hl_pack(wcarry); wl[W] = wcarry.len; }
+    W++;
+  }
+  if (lcarry.len) {
+    if (lane == 0) { lh[NLc] = hl_pack(lcarry); ll[NLc] = lcarry.len; lg[NLc] = (uint8_t)gr_gap2(R, R.re - lcarry.len); }
+    NLc++;
+  }
+  out.W = W; out.NL = NLc; out.flags = flags; out.nchars = nchars;
+  return true;
+}

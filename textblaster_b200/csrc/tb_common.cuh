@@ -128,10 +128,10 @@ TB_HD uint32_t tb_simple_lower(const UcTables& u, uint32_t cp) {
 // It composes under concatenation: H(xy) = H(x) * B^|y| + H(y), which is what the concatenated
 // n-gram keys of find_all_duplicate (text.rs:250) need.  Two keys are treated as equal when both
 // 31-bit residues AND the byte length agree; for two distinct strings of length <= L the
-// probability of that over the choice of bases is <= (L / 2^31)^2.
+// probability of that over the choice of bases is <= (L / 2^29)^2.
 #define TB_P31 0x7FFFFFFFu
-#define TB_B1 0x2F0B4A27u  // < p
-#define TB_B2 0x5C4D3A11u  // < p
+#define TB_B1 0x1F0B4A27u  // < 2^29: lets tb_hpush (tb_tile.cuh) skip the reduction between steps
+#define TB_B2 0x0C4D3A11u  // < 2^29
 TB_HD uint32_t tb_mm(uint32_t a, uint32_t b) {  // a, b <= p  ->  result <= p (p itself stands for 0)
   uint64_t x = (uint64_t)a * b;
   x = (x & TB_P31) + (x >> 31);

@@ -18,6 +18,20 @@ __device__ __forceinline__ void load_ascii(uint16_t* s_ascii, const UcTables& uc
   }
   __syncthreads();
 }
+// per-byte class table of the mask-based word passes (tb_tile.cuh), built once per CTA
+__device__ __forceinline__ void load_lut(LutEntry* s_lut, const UcTables& uc, int kind, uint32_t firstmask) {
+  for (uint32_t i = threadIdx.x; i < 256; i += blockDim.x) {
+    uint32_t ci = i < 128 ? uc.stage2[(uint32_t)uc.stage1[0] * 256u + i] : 0u;
+    s_lut[i] = tb_lut_entry(kind, i, ci, firstmask);
+  }
+  __syncthreads();
+}
+// persistent one-warp CTAs pull document indices from a cursor (zeroed by the host before the launch)
+__device__ __forceinline__ int64_t next_doc(uint32_t* cursor) {
+  uint32_t i = 0;
+  if ((threadIdx.x & 31) == 0) i = atomicAdd(cursor, 1u);
+  return (int64_t)__shfl_sync(0xFFFFFFFFu, i, 0);
+}
 __device__ __forceinline__ int64_t warp_doc() { return ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; }
 __device__ __forceinline__ int64_t thread_doc() { return (int64_t)blockIdx.x * blockDim.x + threadIdx.x; }
 
@@ -31,12 +45,16 @@ __global__ void __launch_bounds__(TB_BLOCK) k_validate_utf8(const uint8_t* t, co
   int64_t d = warp_doc();
   if (d < n) body_validate_utf8(t, rs, re, bad, d, threadIdx.x & 31);
 }
-__global__ void __launch_bounds__(TB_BLOCK, 16) k_gq(KBatch a, SwTable sw, GqCfg cfg, int step, tb_gq_stats* out) {
+__global__ void __launch_bounds__(TB_BLOCK, 12) k_gq(KBatch a, SwTable sw, GqCfg cfg, int step, tb_gq_stats* out, uint32_t* cursor) {
   __shared__ uint16_t s_ascii[192];
+  __shared__ LutEntry s_lut[256];
   load_ascii(s_ascii, a.uc);
-  int64_t d = warp_doc();
-  if (d >= a.n || !a.alive[d]) return;
-  body_gq(a, s_ascii, sw, cfg, step, out, d, threadIdx.x & 31);
+  load_lut(s_lut, a.uc, TB_LUT_GQ, sw.firstmask);
+  for (;;) {
+    const int64_t d = next_doc(cursor);
+    if (d >= a.n) break;
+    if (a.alive[d]) body_gq(a, s_ascii, s_lut, sw, cfg, step, out, d, threadIdx.x & 31);
+  }
 }
 __global__ void k_trim(KBatch a, int64_t* ts, int64_t* te) {
   __shared__ uint16_t s_ascii[192];
@@ -44,12 +62,16 @@ __global__ void k_trim(KBatch a, int64_t* ts, int64_t* te) {
   int64_t d = thread_doc();
   if (d < a.n) body_trim(a, s_ascii, ts, te, d);
 }
-__global__ void __launch_bounds__(TB_BLOCK, 20) k_gr_scan(KBatch a, const int64_t* ts, const int64_t* te, GrScratch s) {
+__global__ void __launch_bounds__(TB_BLOCK, 12) k_gr_scan(KBatch a, const int64_t* ts, const int64_t* te, GrScratch s) {
   __shared__ uint16_t s_ascii[192];
+  __shared__ LutEntry s_lut[256];
   load_ascii(s_ascii, a.uc);
-  int64_t d = warp_doc();
-  if (d >= a.n || !a.alive[d]) return;
-  body_gr_scan(a, s_ascii, ts, te, s, d, threadIdx.x & 31);
+  load_lut(s_lut, a.uc, TB_LUT_GR, 0u);
+  for (;;) {
+    const int64_t d = next_doc(&s.counters[7]);
+    if (d >= a.n) break;
+    if (a.alive[d]) body_gr_scan(a, s_ascii, s_lut, ts, te, s, d, threadIdx.x & 31);
+  }
 }
 // Repetition pass 2, persistent CTAs pulling document ids of their tier from the lists the scan pass built.
 __global__ void __launch_bounds__(32) k_gr_rep_s(KBatch a, const int64_t* ts, const int64_t* te, GrScratch s, GrCfg cfg,
@@ -101,12 +123,16 @@ __global__ void __launch_bounds__(TB_BLOCK) k_c4_a(KBatch a, C4Cfg cfg, C4Scratc
   if (d >= a.n || !a.alive[d]) return;
   body_c4_a(a, s_ascii, cfg, s, d, threadIdx.x & 31);
 }
-__global__ void __launch_bounds__(TB_BLOCK, 24) k_c4_b(KBatch a, C4Cfg cfg, C4Scratch s) {
+__global__ void __launch_bounds__(TB_BLOCK, 12) k_c4_b(KBatch a, C4Cfg cfg, C4Scratch s, uint32_t* cursor) {
   __shared__ uint16_t s_ascii[192];
+  __shared__ LutEntry s_lut[256];
   load_ascii(s_ascii, a.uc);
-  int64_t d = warp_doc();
-  if (d >= a.n || !a.alive[d] || s.docflags[d] || s.nlines[d] == 0) return;
-  body_c4_b(a, s_ascii, cfg, s, d, threadIdx.x & 31);
+  load_lut(s_lut, a.uc, TB_LUT_C4B, 0u);
+  for (;;) {
+    const int64_t d = next_doc(cursor);
+    if (d >= a.n) break;
+    if (a.alive[d] && !s.docflags[d] && s.nlines[d] != 0) body_c4_b(a, s_ascii, s_lut, cfg, s, d, threadIdx.x & 31);
+  }
 }
 __global__ void __launch_bounds__(TB_BLOCK) k_c4_c(KBatch a, C4Cfg cfg, C4Scratch s) {
   int64_t d = warp_doc();
@@ -173,14 +199,19 @@ void tb_launch_validate_utf8(cudaStream_t st, const uint8_t* text, const int64_t
                              int32_t* bad) {
   if (n) k_validate_utf8<<<blocks_for_warps(n), TB_BLOCK, 0, st>>>(text, rs, re, n, bad);
 }
-void tb_launch_gq(cudaStream_t st, const KBatch& b, const SwTable& sw, const GqCfg& cfg, int step, tb_gq_stats* out) {
-  if (b.n) k_gq<<<blocks_for_warps(b.n), TB_BLOCK, 0, st>>>(b, sw, cfg, step, out);
+inline int persistent_grid(int64_t n, int sm_count, int per_sm) {
+  int64_t g = (int64_t)sm_count * per_sm;
+  return (int)(n < g ? n : g);
+}
+void tb_launch_gq(cudaStream_t st, const KBatch& b, const SwTable& sw, const GqCfg& cfg, int step, tb_gq_stats* out,
+                  int sm_count, uint32_t* cursor) {
+  if (b.n) k_gq<<<persistent_grid(b.n, sm_count, 12), TB_BLOCK, 0, st>>>(b, sw, cfg, step, out, cursor);
 }
 void tb_launch_trim(cudaStream_t st, const KBatch& b, int64_t* ts, int64_t* te) {
   if (b.n) k_trim<<<blocks_for_threads(b.n), 256, 0, st>>>(b, ts, te);
 }
-void tb_launch_gr_scan(cudaStream_t st, const KBatch& b, const int64_t* ts, const int64_t* te, const GrScratch& s) {
-  if (b.n) k_gr_scan<<<blocks_for_warps(b.n), TB_BLOCK, 0, st>>>(b, ts, te, s);
+void tb_launch_gr_scan(cudaStream_t st, const KBatch& b, const int64_t* ts, const int64_t* te, const GrScratch& s, int sm_count) {
+  if (b.n) k_gr_scan<<<persistent_grid(b.n, sm_count, 12), TB_BLOCK, 0, st>>>(b, ts, te, s);
 }
 void tb_launch_gr_rep(cudaStream_t st, const KBatch& b, const int64_t* ts, const int64_t* te, const GrScratch& s,
                       const GrCfg& cfg, int step, tb_gr_stats* out, int sm_count, int tier) {
@@ -195,8 +226,8 @@ int tb_kernels_init() {
 void tb_launch_c4_a(cudaStream_t st, const KBatch& b, const C4Cfg& cfg, const C4Scratch& s) {
   if (b.n) k_c4_a<<<blocks_for_warps(b.n), TB_BLOCK, 0, st>>>(b, cfg, s);
 }
-void tb_launch_c4_b(cudaStream_t st, const KBatch& b, const C4Cfg& cfg, const C4Scratch& s) {
-  if (b.n) k_c4_b<<<blocks_for_warps(b.n), TB_BLOCK, 0, st>>>(b, cfg, s);
+void tb_launch_c4_b(cudaStream_t st, const KBatch& b, const C4Cfg& cfg, const C4Scratch& s, int sm_count, uint32_t* cursor) {
+  if (b.n) k_c4_b<<<persistent_grid(b.n, sm_count, 12), TB_BLOCK, 0, st>>>(b, cfg, s, cursor);
 }
 void tb_launch_c4_c(cudaStream_t st, const KBatch& b, const C4Cfg& cfg, const C4Scratch& s) {
   if (b.n) k_c4_c<<<blocks_for_warps(b.n), TB_BLOCK, 0, st>>>(b, cfg, s);

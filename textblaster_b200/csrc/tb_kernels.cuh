@@ -9,6 +9,7 @@ typedef void* cudaStream_t;  // host emulation harness (tests/host_emul): no CUD
 
 #include "../../include/textblaster_b200.h"
 #include "tb_lanes.cuh"
+#include "tb_tile.cuh"
 
 // Current view of the batch chunk on the device.
 struct KBatch {
@@ -19,7 +20,10 @@ struct KBatch {
   int8_t* failed;        // [n] index of the step that filtered it, -1
   int64_t n;
   UcTables uc;
+  int64_t ext_lo, ext_hi;  // positions of `text` (and of the C4 work buffers) that 32-byte vector loads may touch
+  uint32_t dbg;            // TB_DBG_*
 };
+#define TB_DBG_FORCE_WALK 1u  // run the segment-walking bodies for every document (tests)
 
 struct GqCfg {
   uint32_t has;
@@ -51,7 +55,7 @@ struct GrScratch {
   GrDoc* doc;                               // [n]
   uint32_t* work;                           // tier-L work area, TB_REP_K words per unit + TB_REP_DOC_EXTRA per doc
   uint32_t* lists;                          // [3][n] document ids per tier (S, M, L), filled by the scan pass
-  uint32_t* counters;                       // [8]: list lengths [0..2], work cursors [4..6]
+  uint32_t* counters;                       // [8]: list lengths [0..2], work cursors [4..6], scan cursor [7]
   int64_t n;
 };
 #define TB_REP_K 6u           // tier-L words per unit: H[2U] woff[U+2] tab[2U+16] cnt[U]
@@ -75,14 +79,16 @@ struct C4Scratch {
 
 void tb_launch_init_ranges(cudaStream_t st, const void* off, int off64, int64_t doc0, int64_t n, int64_t base,
                            int64_t* rs, int64_t* re, uint8_t* alive, int8_t* failed);
-void tb_launch_gq(cudaStream_t st, const KBatch& b, const SwTable& sw, const GqCfg& cfg, int step, tb_gq_stats* out);
+// gq, gr_scan and c4_b run as persistent one-warp CTAs; `cursor` (gr_scan: s.counters[7]) must be zero at launch
+void tb_launch_gq(cudaStream_t st, const KBatch& b, const SwTable& sw, const GqCfg& cfg, int step, tb_gq_stats* out,
+                  int sm_count, uint32_t* cursor);
 void tb_launch_trim(cudaStream_t st, const KBatch& b, int64_t* ts, int64_t* te);
-void tb_launch_gr_scan(cudaStream_t st, const KBatch& b, const int64_t* ts, const int64_t* te, const GrScratch& s);
+void tb_launch_gr_scan(cudaStream_t st, const KBatch& b, const int64_t* ts, const int64_t* te, const GrScratch& s, int sm_count);
 void tb_launch_gr_rep(cudaStream_t st, const KBatch& b, const int64_t* ts, const int64_t* te, const GrScratch& s,
                       const GrCfg& cfg, int step, tb_gr_stats* out, int sm_count, int tier);  // tier 0 S, 1 M, 2 L
 int tb_kernels_init();  // per-process function attributes (dynamic shared memory opt-in)
 void tb_launch_c4_a(cudaStream_t st, const KBatch& b, const C4Cfg& cfg, const C4Scratch& s);
-void tb_launch_c4_b(cudaStream_t st, const KBatch& b, const C4Cfg& cfg, const C4Scratch& s);
+void tb_launch_c4_b(cudaStream_t st, const KBatch& b, const C4Cfg& cfg, const C4Scratch& s, int sm_count, uint32_t* cursor);
 void tb_launch_c4_c(cudaStream_t st, const KBatch& b, const C4Cfg& cfg, const C4Scratch& s);
 void tb_launch_c4_d(cudaStream_t st, const KBatch& b, const C4Cfg& cfg, const C4Scratch& s, int step, tb_c4_stats* out,
                     uint8_t* rewritten);

@@ -157,9 +157,9 @@ int tb_gopher_repetition_noalloc(const uint8_t* utf8_dev, const int64_t* offsets
   if (cudaMemsetAsync(g.counters, 0, 64, stream) != cudaSuccess) { cudaGetLastError(); return fail(TB_ERR_CUDA, "cudaMemsetAsync failed"); }
   // keep_dev doubles as the kernels' "alive" flag; init_ranges sets it to 1 for every document
   tb_launch_init_ranges(stream, offsets_dev, 1, 0, n_docs, 0, rs, re, keep_dev, failed);
-  KBatch b{utf8_dev, rs, re, keep_dev, failed, n_docs, st->uc};
+  KBatch b{utf8_dev, rs, re, keep_dev, failed, n_docs, st->uc, 0, n_bytes, 0u};
   tb_launch_trim(stream, b, ts, te);
-  tb_launch_gr_scan(stream, b, ts, te, g);
+  tb_launch_gr_scan(stream, b, ts, te, g, st->sm_count);
   for (int tier = 0; tier < 3; tier++) tb_launch_gr_rep(stream, b, ts, te, g, cfg, 0, stats_dev, st->sm_count, tier);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return fail(TB_ERR_CUDA, std::string("tb_gopher_repetition_noalloc: launch failed: ") + cudaGetErrorString(e));

@@ -20,6 +20,7 @@ TB_D uint64_t simt_shfl_xor(uint64_t v, int o) { return __shfl_xor_sync(SIMT_FUL
 TB_D uint32_t simt_sum(uint32_t v) { return __reduce_add_sync(SIMT_FULL, v); }
 TB_D uint32_t simt_or(uint32_t v) { return __reduce_or_sync(SIMT_FULL, v); }
 TB_D bool simt_any(bool p) { return __any_sync(SIMT_FULL, p) != 0; }
+TB_D uint32_t simt_ballot(bool p) { return __ballot_sync(SIMT_FULL, p); }
 TB_D void simt_sync() { __syncwarp(); }
 TB_D uint32_t simt_cas(uint32_t* a, uint32_t cmp, uint32_t val) { return atomicCAS(a, cmp, val); }
 TB_D uint32_t simt_atomic_add(uint32_t* a, uint32_t v) { return atomicAdd(a, v); }
@@ -79,6 +80,7 @@ inline uint32_t simt_or(uint32_t v) {
   return s;
 }
 inline bool simt_any(bool p) { return simt_or(p ? 1u : 0u) != 0; }
+inline uint32_t simt_ballot(bool p) { return simt_or(p ? (1u << simt_lane) : 0u); }
 inline void simt_sync() { simt_warp->bar.arrive_and_wait(); }
 inline uint32_t simt_cas(uint32_t* a, uint32_t cmp, uint32_t val) {
   __atomic_compare_exchange_n(a, &cmp, val, false, __ATOMIC_SEQ_CST, __ATOMIC_SEQ_CST);
