@@ -142,7 +142,8 @@ extern "C" int tbe_run_chain(const tb_step_cfg* steps, size_t n_steps, const uin
       memset(gs.counters, 0, 32);
       for (int64_t d = 0; d < n; d++) body_trim(b, ascii, ts, te, d);
       build_lut(TB_LUT_GR, 0u);
-      run_warps(n, alive_pred, [&](int64_t d, int lane) { body_gr_scan(b, ascii, lut.data(), ts, te, gs, d, lane); });
+      uint32_t* stage = G32(3 * TB_GR_STAGE_WORDS);
+      run_warps(n, alive_pred, [&](int64_t d, int lane) { body_gr_scan(b, ascii, lut.data(), stage, ts, te, gs, d, lane); });
       uint8_t* smem_s = (uint8_t*)G64(TB_REP_S_SMEM / 8 + 2);
       uint8_t* smem_m = (uint8_t*)G64(TB_REP_M_SMEM / 8 + 2);
       run_warps_list(gs.lists, gs.counters[0], [&](int64_t d, int lane) { body_gr_rep_s(b, smem_s, ts, te, gs, g, (int)s, (tb_gr_stats*)stats, d, lane); });

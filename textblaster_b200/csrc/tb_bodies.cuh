@@ -199,15 +199,17 @@ TB_D void gr_doc_walk(const KBatch& a, const Classifier& C, const TextRange& R, 
   }
   out.W = W; out.NL = NL; out.flags = flags; out.nchars = nchars;
 }
-TB_D bool gr_doc_tiles(const KBatch& a, const LutEntry* lut, const Classifier& C, const TextRange& R, const GrScratch& s,
-                       int64_t d, int lane, GrTotals& out);
+#define TB_GR_STAGE_WORDS (17 * 32)  // word ends one tile can hold: at most 16 + 1 per stretch
+TB_D bool gr_doc_tiles(const KBatch& a, const LutEntry* lut, uint32_t* stage, const Classifier& C, const TextRange& R,
+                       const GrScratch& s, int64_t d, int lane, GrTotals& out);
 
-TB_D void body_gr_scan(const KBatch& a, const uint16_t* s_ascii, const LutEntry* lut, const int64_t* ts, const int64_t* te,
-                       const GrScratch& s, int64_t d, int lane) {
+// `stage`: 3 * TB_GR_STAGE_WORDS words of per-warp scratch (shared memory)
+TB_D void body_gr_scan(const KBatch& a, const uint16_t* s_ascii, const LutEntry* lut, uint32_t* stage, const int64_t* ts,
+                       const int64_t* te, const GrScratch& s, int64_t d, int lane) {
   Classifier C{s_ascii, a.uc};
   TextRange R{a.text, ts[d], te[d]};
   GrTotals o;
-  if ((a.dbg & TB_DBG_FORCE_WALK) || !gr_doc_tiles(a, lut, C, R, s, d, lane, o)) { gr_doc_walk(a, C, R, s, d, lane, o); TBE_COUNT(tbe_stat_walk, lane); }
+  if ((a.dbg & TB_DBG_FORCE_WALK) || !gr_doc_tiles(a, lut, stage, C, R, s, d, lane, o)) { gr_doc_walk(a, C, R, s, d, lane, o); TBE_COUNT(tbe_stat_walk, lane); }
   else TBE_COUNT(tbe_stat_tiles, lane);
   const uint32_t flags = simt_or(o.flags);
   const uint64_t nchars = simt_sum64(o.nchars);
@@ -475,8 +477,32 @@ TB_D void body_final_len(const int64_t* rs0, const int64_t* re0, const int64_t* 
 TB_D void body_pack(const uint8_t* orig, const int64_t* rs0, const uint8_t* cur, const int64_t* rs, const uint8_t* rewritten,
                     const int64_t* out_off, uint8_t* out, int64_t d, int lane) {
   const uint8_t* src = rewritten[d] ? cur + rs[d] : orig + rs0[d];
-  int64_t o = out_off[d], len = out_off[d + 1] - o;
-  for (int64_t i = lane; i < len; i += 32) out[o + i] = src[i];
+  const int64_t o = out_off[d], len = out_off[d + 1] - o;
+  uint8_t* dst = out + o;
+#if defined(__CUDA_ARCH__)
+  // 16-byte stores on the destination's alignment; the source words are realigned with funnel shifts
+  int64_t head = (int64_t)((16u - (uint32_t)((uintptr_t)dst & 15u)) & 15u);
+  if (head > len) head = len;
+  if (lane < head) dst[lane] = src[lane];
+  const int64_t body = (len - head) & ~(int64_t)15;
+  const uint8_t* s2 = src + head;
+  uint8_t* d2 = dst + head;
+  const uint32_t mis = (uint32_t)((uintptr_t)s2 & 3u);
+  const uint32_t* sw = (const uint32_t*)(s2 - mis);
+  for (int64_t c = (int64_t)lane * 16; c < body; c += 512) {
+    const uint32_t* q = sw + (c >> 2);
+    uint32_t w0 = q[0], w1 = q[1], w2 = q[2], w3 = q[3];
+    uint4 v;
+    if (mis) {
+      const uint32_t w4 = q[4], sh = 8u * mis;  // the fifth word still overlaps byte c + 15 of the source
+      v.x = __funnelshift_r(w0, w1, sh); v.y = __funnelshift_r(w1, w2, sh); v.z = __funnelshift_r(w2, w3, sh); v.w = __funnelshift_r(w3, w4, sh);
+    } else { v.x = w0; v.y = w1; v.z = w2; v.w = w3; }
+    *(uint4*)(d2 + c) = v;
+  }
+  for (int64_t i = head + body + lane; i < len; i += 32) dst[i] = src[i];
+#else
+  for (int64_t i = lane; i < len; i += 32) dst[i] = src[i];
+#endif
 }
 
 #include "tb_bodies_tile.cuh"

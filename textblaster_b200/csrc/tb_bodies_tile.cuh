@@ -33,6 +33,12 @@ TB_D bool gq_is_stop_word(const Classifier& C, const uint8_t* t, const SwTable& 
     return false;
   }
   LowKey k; k.init();
+  if (pure_ascii && len <= 8) {  // the common case: the key is the lower-cased word itself
+    uint64_t lo = 0;
+    for (uint32_t j = 0; j < (uint32_t)len; j++) { uint32_t b = tb_byte(t, s + j); b = (b - 'A') < 26u ? b + 32u : b; lo |= (uint64_t)b << (8u * j); }
+    k.lo = lo; k.len = (uint32_t)len;
+    return sw_lookup(sw, k);
+  }
   int64_t i = s;
   while (i < e) { int l; uint32_t cp; uint32_t ci = C.at(t, i, &l, &cp); lowkey_push(C, k, cp, ci); i += l; }
   if (k.sigma) lowkey_slow(C, t, s, e, k);
@@ -230,8 +236,9 @@ TB_D bool c4b_doc_tiles(const KBatch& a, const LutEntry* lut, const Classifier& 
 // ---------------------------------------------------------------------------------------------
 TB_D HL hl_fold(uint32_t a, uint32_t b, uint32_t len) { HL r; r.a = tb_hfold(a); r.b = tb_hfold(b); r.len = len; return r; }
 
-TB_D bool gr_doc_tiles(const KBatch& a, const LutEntry* lut, const Classifier& C, const TextRange& R, const GrScratch& s,
-                       int64_t d, int lane, GrTotals& out) {
+TB_D bool gr_doc_tiles(const KBatch& a, const LutEntry* lut, uint32_t* stage, const Classifier& C, const TextRange& R,
+                       const GrScratch& s, int64_t d, int lane, GrTotals& out) {
+  uint32_t* st_a = stage; uint32_t* st_b = stage + TB_GR_STAGE_WORDS; uint32_t* st_n = stage + 2 * TB_GR_STAGE_WORDS;
   const uint64_t ub = (uint64_t)(R.rs >> 1) + (uint64_t)d;
   uint64_t* wh = s.wh + ub; uint32_t* wl = s.wl + ub;
   uint64_t* lh = s.lh + ub; uint32_t* ll = s.ll + ub; uint8_t* lg = s.lg + ub;
@@ -282,13 +289,13 @@ TB_D bool gr_doc_tiles(const KBatch& a, const LutEntry* lut, const Classifier& C
     // ---- one pass over the 32 bytes: running word hash (restarts at segment starts) and piece hash
     uint32_t wa = 0, wb = 0, wn = 0, la = 0, lb_ = 0, ln = 0;
     uint32_t hwa = 0, hwb = 0, hwn = 0, hla = 0, hlb = 0, hln = 0;
-    uint32_t widx = W + wpre + first_word, lidx = NLc + lpre + first_piece;
+    uint32_t widx = wpre + first_word, lidx = NLc + lpre + first_piece;  // widx: slot in the tile's staging arrays
 #pragma unroll
     for (int i = 0; i < 32; i++) {
       const uint32_t byte = (T.w[i >> 2] >> (8 * (i & 3))) & 0xFFu;
       if ((B >> i) & 1u) {
         if (i == fb) { hwa = wa; hwb = wb; hwn = wn; }
-        else if ((WEin >> i) & 1u) { wh[widx] = hl_pack(hl_fold(wa, wb, wn)); wl[widx] = wn; widx++; }
+        else if ((WEin >> i) & 1u) { st_a[widx] = wa; st_b[widx] = wb; st_n[widx] = wn; widx++; }
         wa = 0; wb = 0; wn = 0;
       }
       wa = tb_hpush(wa, TB_B1, byte + 1u); wb = tb_hpush(wb, TB_B2, byte + 1u); wn++;
@@ -322,8 +329,12 @@ TB_D bool gr_doc_tiles(const KBatch& a, const LutEntry* lut, const Classifier& C
       }
       if (first_word) {
         HL first = hl_cat(cin, hl_fold(hwa, hwb, hwn), powtab);
-        wh[W + wpre] = hl_pack(first); wl[W + wpre] = first.len;
+        st_a[wpre] = first.a; st_b[wpre] = first.b; st_n[wpre] = first.len;
       }
+      // the tile's words, in order: reduce and store them with all lanes busy
+      simt_sync();
+      for (uint32_t j = (uint32_t)lane; j < wtot; j += 32) { wh[W + j] = hl_pack(hl_fold(st_a[j], st_b[j], st_n[j])); wl[W + j] = st_n[j]; }
+      simt_sync();
       // "word character seen" of the fragment open after lane 31
       if (brk_lanes) wcarry_wc = (twc_lanes & ~tb_below(31 - tb_clz32(brk_lanes))) != 0u;
       else wcarry_wc |= twc_lanes != 0u;

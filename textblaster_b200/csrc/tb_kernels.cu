@@ -50,6 +50,12 @@ __global__ void __launch_bounds__(TB_BLOCK, 12) k_gq(KBatch a, SwTable sw, GqCfg
   __shared__ LutEntry s_lut[256];
   load_ascii(s_ascii, a.uc);
   load_lut(s_lut, a.uc, TB_LUT_GQ, sw.firstmask);
+  __shared__ SwEntry s_sw[64];  // small stop-word tables are probed in shared memory
+  if (sw.mask < 64u) {
+    for (uint32_t i = threadIdx.x; i <= sw.mask; i += blockDim.x) s_sw[i] = sw.e[i];
+    __syncthreads();
+    sw.e = s_sw;
+  }
   for (;;) {
     const int64_t d = next_doc(cursor);
     if (d >= a.n) break;
@@ -67,10 +73,11 @@ __global__ void __launch_bounds__(TB_BLOCK, 12) k_gr_scan(KBatch a, const int64_
   __shared__ LutEntry s_lut[256];
   load_ascii(s_ascii, a.uc);
   load_lut(s_lut, a.uc, TB_LUT_GR, 0u);
+  __shared__ uint32_t s_stage[3 * TB_GR_STAGE_WORDS];
   for (;;) {
     const int64_t d = next_doc(&s.counters[7]);
     if (d >= a.n) break;
-    if (a.alive[d]) body_gr_scan(a, s_ascii, s_lut, ts, te, s, d, threadIdx.x & 31);
+    if (a.alive[d]) body_gr_scan(a, s_ascii, s_lut, s_stage, ts, te, s, d, threadIdx.x & 31);
   }
 }
 // Repetition pass 2, persistent CTAs pulling document ids of their tier from the lists the scan pass built.
