@@ -106,3 +106,21 @@ def ascii_doc(rng, n_tokens=400):
     for _ in range(n_tokens):
         out.append(rng.choice(atoms))
     return "".join(out)
+
+
+def boundary_docs():
+    """Documents whose interesting spots (white space at line ends, citations, multi-byte characters, words
+    joined by MidLetter / MidNum, CR LF) slide across the 32-byte stretch and 1 KiB tile boundaries of the
+    kernels, at several alignments of the document start."""
+    ws = [" ", "\t", "\u00a0", "\u3000", "\u2003 ", " \u202f", "\r", " \r", "\u0085", "\u2028"]
+    mids = ["don't", "3.14", "a_b", "x:y", "1,000", "café", "naïve", "über", "été", "\U0001f600ok"]
+    docs = []
+    for pad in list(range(0, 40)) + list(range(1000, 1040, 3)):
+        lead = "w" * pad
+        k = pad % len(ws)
+        m = mids[pad % len(mids)]
+        docs.append(lead + ws[k] + "\n" + ws[(k + 1) % len(ws)] + "Second line here [12, 3] ends." + ws[(k + 2) % len(ws)]
+                    + "\n\n" + m + " " + m + ". Tail [7] words" + ws[(k + 3) % len(ws)] * 3 + "and more [1, 2] text.\n")
+        docs.append(lead + " " + (m + " ") * 8 + "\r\n" + ws[k] * 2 + m + ".\r\n")
+        docs.append(("ab " * (pad // 3)) + "x" + ws[k] * (1 + pad % 5) + "[1" + "," * (pad % 2) + " 2]" + ws[(k + 1) % len(ws)] + "y z. Done here now.")
+    return docs

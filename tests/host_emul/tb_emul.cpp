@@ -96,7 +96,8 @@ extern "C" int tbe_run_chain(const tb_step_cfg* steps, size_t n_steps, const uin
   std::vector<uint64_t> pw(TB_POWTAB);
   { uint32_t a = 1, b = 1; for (int i = 0; i < TB_POWTAB; i++) { pw[i] = ((uint64_t)a << 32) | b; a = tb_mm(a, TB_B1); b = tb_mm(b, TB_B2); } }
   UcTables uc{tb_uc_stage1, tb_uc_stage2, &tb_uc_lower[0][0], &tb_uc_cased[0][0], &tb_uc_caseign[0][0], pw.data(),
-              TB_UC_NLOWER, TB_UC_NCASED, TB_UC_NCASEIGN};
+              TB_UC_NLOWER, TB_UC_NCASED, TB_UC_NCASEIGN, {0}};
+  tb_compute_wslead(tb_uc_stage1, tb_uc_stage2, uc.wslead);
   uint16_t ascii[192];
   for (int i = 0; i < 128; i++) {
     ascii[i] = tb_uc_stage2[(uint32_t)tb_uc_stage1[0] * 256u + i];
@@ -115,7 +116,9 @@ extern "C" int tbe_run_chain(const tb_step_cfg* steps, size_t n_steps, const uin
   const char* fw = getenv("TBE_FORCE_WALK");
   KBatch b{text, rs, re, alive, failed, n, uc, 0, nb, (fw && fw[0] == '1') ? TB_DBG_FORCE_WALK : 0u};
   std::vector<LutEntry> lut(256);
-  auto build_lut = [&](int kind, uint32_t firstmask) { for (uint32_t i = 0; i < 256; i++) lut[i] = tb_lut_entry(kind, i, i < 128 ? ascii[i] : 0u, firstmask); };
+  auto build_lut = [&](int kind, uint32_t firstmask) {
+    for (uint32_t i = 0; i < 256; i++) lut[i] = tb_lut_entry(kind, i, i < 128 ? ascii[i] : 0u, kind == TB_LUT_C4A ? ((uc.wslead[i >> 5] >> (i & 31)) & 1u) : firstmask);
+  };
   auto alive_pred = [&](int64_t d) { return alive[d] != 0; };
   bool has_c4 = false;
   for (size_t s = 0; s < n_steps; s++) {
@@ -154,7 +157,9 @@ extern "C" int tbe_run_chain(const tb_step_cfg* steps, size_t n_steps, const uin
       C4Cfg cfg = tb_c4cfg_of(sc.u.c4);
       C4Scratch cs{G8((size_t)nb + 64), G8((size_t)nb + 64), G64(n1), G32(n1), G32(n1), G32(lines), G32(lines), G32(lines),
                    G64(n1), G64(n1), G64(n1), G64(n1), G32(4 * n1)};
-      run_warps(n, alive_pred, [&](int64_t d, int lane) { body_c4_a(b, ascii, cfg, cs, d, lane); });
+      build_lut(TB_LUT_C4A, 0u);
+      uint8_t* cstage = (uint8_t*)G64(TB_STAGE_BYTES / 8 + 2);
+      run_warps(n, alive_pred, [&](int64_t d, int lane) { body_c4_a(b, ascii, lut.data(), cstage, cfg, cs, d, lane); });
       build_lut(TB_LUT_C4B, 0u);
       run_warps(n, [&](int64_t d) { return alive[d] && !cs.docflags[d] && cs.nlines[d] != 0; },
                 [&](int64_t d, int lane) { body_c4_b(b, ascii, lut.data(), cfg, cs, d, lane); });

@@ -73,3 +73,17 @@ def test_word_spanning_many_tiles():
     texts = ["start " + "a" * 5000 + " end. Another sentence here. And a third one.", "a" * 3000, "é" * 1500 + " x"]
     for name in ("gq_open", "gr_open", "c4_lax"):
         _check(name, texts)
+
+
+@pytest.mark.parametrize("name", ["c4_lax", "c4_shipped", "gq_open", "gr_open", "baseline_order"])
+def test_boundary_documents(name):
+    _check(name, fuzzgen.boundary_docs())
+
+
+def test_general_word_path_matches(monkeypatch):
+    """The segment-walking bodies (the general path behind the mask-based passes) give the same results."""
+    monkeypatch.setenv("TBE_FORCE_WALK", "1")
+    rng = random.Random(5)
+    texts = fuzzgen.FuzzGen(21).docs(40) + [fuzzgen.english_doc(rng, 2500)] + fuzzgen.boundary_docs()[:30]
+    for name in ("baseline_order", "gq_open", "gr_open"):
+        _check(name, texts)

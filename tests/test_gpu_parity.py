@@ -101,6 +101,29 @@ def test_ascii_fast_path(name):
     check_texts(name, texts)
 
 
+@pytest.mark.parametrize("name", ["c4_lax", "c4_shipped", "gq_open", "gr_open", "baseline_order", "shipped_order"])
+def test_boundary_documents(name):
+    """White space, citations, multi-byte characters and MidLetter joins sliding across the 32-byte stretch and
+    1 KiB tile boundaries of the mask-based passes."""
+    check_texts(name, fuzzgen.boundary_docs())
+
+
+@pytest.mark.parametrize("name", ["baseline_order", "shipped_order", "gq_open", "gr_open", "c4_lax"])
+def test_general_word_path_matches(name):
+    """TB_OPT_GENERAL_WORD_PATH: the segment-walking kernels bodies, which take over for documents the mask form
+    cannot express, give the same results on every document."""
+    rng = random.Random(5)
+    texts = fuzzgen.FuzzGen(21).docs(150) + [fuzzgen.english_doc(rng, sz) for sz in (900, 2500, 9000)] + fuzzgen.boundary_docs()[:60]
+    p = GpuBatchPipeline(CHAINS[name])
+    p.set_option(_abi.TB_OPT_GENERAL_WORD_PATH, 1)
+    steps = CHAINS[name]
+    res = p.run_texts(texts)
+    ores = oracle.OraclePipeline(steps).run_texts(texts, nthreads=NCPU)
+    contents = [res.content_of(i) for i in range(res.n_docs)] if res.content is not None else None
+    compare(ores, res.keep, res.failed_step, res.stats, contents, step_types(steps), texts, label=name + "/general")
+    p.close()
+
+
 def test_int32_offsets_and_chunking():
     """Arrow StringArray offsets are i32 (parquet_reader.rs:108-112); tiny chunks force the
     double-buffered multi-chunk path and must not change any result."""

@@ -66,6 +66,7 @@ TB_DOCFLAG_COMPLEX_SCRIPT = 1 << 0
 TB_OPT_RETURN_CONTENT = 1
 TB_OPT_VALIDATE_UTF8 = 2
 TB_OPT_CHUNK_BYTES = 3
+TB_OPT_GENERAL_WORD_PATH = 4
 
 
 class tb_c4_params(C.Structure):

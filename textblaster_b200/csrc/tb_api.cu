@@ -338,7 +338,7 @@ int enqueue_chain(tb_pipeline* p, const uint8_t* text, int64_t n, int64_t nbytes
       C4Scratch cs{p->c_P.as<uint8_t>(), p->c_F.as<uint8_t>(), p->c_plen.as<int64_t>(), p->c_nlines.as<uint32_t>(),
                    p->c_docflags.as<uint32_t>(), p->c_lwc.as<uint32_t>(), p->c_lmax.as<uint32_t>(), p->c_lflags.as<uint32_t>(),
                    p->c_prs.as<int64_t>(), p->c_pre.as<int64_t>(), p->c_frs.as<int64_t>(), p->c_fre.as<int64_t>(), p->c_cnt.as<uint32_t>()};
-      { Timed t(p, "k_c4_a"); tb_launch_c4_a(st, b, sh.c4, cs); }
+      { Timed t(p, "k_c4_a"); tb_launch_c4_a(st, b, sh.c4, cs, c->sm_count, cursors + TB_MAX_STEPS + s); }
       { Timed t(p, "k_c4_b"); tb_launch_c4_b(st, b, sh.c4, cs, c->sm_count, cursors + s); }
       { Timed t(p, "k_c4_c"); tb_launch_c4_c(st, b, sh.c4, cs); }
       {  // content = kept.join("\n").trim()   (c4_filters.rs:258)
@@ -508,7 +508,8 @@ int tb_ctx_create(int device, tb_ctx** out) {
   for (int i = 0; i < TB_POWTAB; i++) { pw[i] = ((uint64_t)a << 32) | b; a = tb_mm(a, TB_B1); b = tb_mm(b, TB_B2); }
   if ((rc = upload(c->t_pow, pw.data(), pw.size() * 8))) { delete c; return rc; }
   c->uc = UcTables{c->t_stage1.as<uint16_t>(), c->t_stage2.as<uint16_t>(), c->t_lower.as<uint32_t>(), c->t_cased.as<uint32_t>(),
-                   c->t_caseign.as<uint32_t>(), c->t_pow.as<uint64_t>(), TB_UC_NLOWER, TB_UC_NCASED, TB_UC_NCASEIGN};
+                   c->t_caseign.as<uint32_t>(), c->t_pow.as<uint64_t>(), TB_UC_NLOWER, TB_UC_NCASED, TB_UC_NCASEIGN, {0}};
+  tb_compute_wslead(tb_uc_stage1, tb_uc_stage2, c->uc.wslead);
   *out = c;
   return TB_OK;
 }

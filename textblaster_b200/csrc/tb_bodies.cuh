@@ -272,9 +272,18 @@ TB_D void body_gr_rep_l(const KBatch& a, uint64_t* red, const int64_t* ts, const
 // C4QualityFilter
 // ---------------------------------------------------------------------------------------------
 // Pass A: doc-level checks, processed lines P, line count; zeroes the per-line slots.
-TB_D void body_c4_a(const KBatch& a, const uint16_t* s_ascii, const C4Cfg& cfg, const C4Scratch& s, int64_t d, int lane) {
+#define TB_STAGE_BYTES (TB_TILE + 64)  // per-warp staging buffer of the compacting stores (tile_store_kept)
+TB_D void c4a_doc_tiles(const KBatch& a, const LutEntry* lut, uint8_t* stage, const Classifier& C, const C4Cfg& cfg, const C4Scratch& s,
+                        const TextRange& R, int64_t d, int lane);
+TB_D void c4a_doc_walk(const KBatch& a, const Classifier& C, const C4Cfg& cfg, const C4Scratch& s, const TextRange& R, int64_t d, int lane);
+TB_D void body_c4_a(const KBatch& a, const uint16_t* s_ascii, const LutEntry* lut, uint8_t* stage, const C4Cfg& cfg, const C4Scratch& s,
+                    int64_t d, int lane) {
   Classifier C{s_ascii, a.uc};
   TextRange R{a.text, a.rs[d], a.re[d]};
+  if (a.dbg & TB_DBG_FORCE_WALK) { c4a_doc_walk(a, C, cfg, s, R, d, lane); TBE_COUNT(tbe_stat_walk, lane); }
+  else { c4a_doc_tiles(a, lut, stage, C, cfg, s, R, d, lane); TBE_COUNT(tbe_stat_tiles, lane); }
+}
+TB_D void c4a_doc_walk(const KBatch& a, const Classifier& C, const C4Cfg& cfg, const C4Scratch& s, const TextRange& R, int64_t d, int lane) {
   uint8_t* out = s.P + R.rs;
   const uint64_t lb = (uint64_t)R.rs + (uint64_t)d;
   uint32_t flags = 0, nl = 0;

@@ -371,3 +371,181 @@ TB_D bool gr_doc_tiles(const KBatch& a, const LutEntry* lut, uint32_t* stage, co
   out.W = W; out.NL = NLc; out.flags = flags; out.nchars = nchars;
   return true;
 }
+
+// ---------------------------------------------------------------------------------------------
+// Compacting store: the bytes of the tile selected by K, in order, to dst.  They are gathered in a
+// per-warp staging buffer first (whole words when the stretch is kept entirely) and leave it as
+// aligned 16-byte stores.  Returns the number of bytes written.
+// ---------------------------------------------------------------------------------------------
+TB_D void tb_copy16(uint8_t* d, const uint8_t* s) {
+#if defined(__CUDA_ARCH__)
+  *(uint4*)d = *(const uint4*)s;
+#else
+  memcpy(d, s, 16);
+#endif
+}
+TB_D uint32_t tile_store_kept(const uint32_t* w, uint32_t K, uint8_t* stage, uint8_t* dst, int lane) {
+  uint32_t tot;
+  const uint32_t pre = simt_exscan((uint32_t)tb_popc32(K), lane, &tot);
+  const uint32_t sh = (uint32_t)((uintptr_t)dst & 15u);  // stage + sh + k and dst + k are aligned alike
+  uint8_t* sp = stage + sh + pre;
+  if (K == 0xFFFFFFFFu) {
+    const uint32_t m = (uint32_t)((uintptr_t)sp & 3u);
+    if (m == 0u) {
+      uint32_t* q = (uint32_t*)sp;
+#pragma unroll
+      for (int k = 0; k < 8; k++) q[k] = w[k];
+    } else {
+      const uint32_t hb = 4u - m;
+      for (uint32_t j = 0; j < hb; j++) sp[j] = (uint8_t)(w[0] >> (8u * j));
+      uint32_t* q = (uint32_t*)(sp + hb);
+#pragma unroll
+      for (int k = 0; k < 7; k++) q[k] = tb_funnel_r(w[k], w[k + 1], hb);
+      for (uint32_t j = 0; j < m; j++) sp[32u - m + j] = (uint8_t)(w[7] >> (8u * (hb + j)));
+    }
+  } else if (K) {
+#pragma unroll
+    for (int i = 0; i < 32; i++)
+      if ((K >> i) & 1u) *sp++ = (uint8_t)(w[i >> 2] >> (8 * (i & 3)));
+  }
+  simt_sync();
+  const uint8_t* src = stage + sh;
+  uint32_t head = (16u - sh) & 15u;
+  if (head > tot) head = tot;
+  if ((uint32_t)lane < head) dst[lane] = src[lane];
+  const uint32_t body = (tot - head) & ~15u;
+  for (uint32_t c = head + 16u * (uint32_t)lane; c < head + body; c += 512u) tb_copy16(dst + c, src + c);
+  for (uint32_t i = head + body + (uint32_t)lane; i < tot; i += 32u) dst[i] = src[i];
+  simt_sync();
+  return tot;
+}
+
+// ---------------------------------------------------------------------------------------------
+// C4QualityFilter pass A (c4_filters.rs:150-151,175-199): document flags, line count, and the processed
+// lines P: every line trimmed, citations removed, still joined by the original '\n'.
+// ---------------------------------------------------------------------------------------------
+TB_D void c4a_doc_tiles(const KBatch& a, const LutEntry* lut, uint8_t* stage, const Classifier& C, const C4Cfg& cfg, const C4Scratch& s,
+                        const TextRange& R, int64_t d, int lane) {
+  const uint8_t* t = R.t;
+  uint8_t* out = s.P + R.rs;
+  const uint64_t lb = (uint64_t)R.rs + (uint64_t)d;
+  const uint32_t below_lane = tb_below(lane), upto_lane = tb_upto(lane);
+  uint32_t flags = 0, nl = 0;
+  int64_t outpos = 0;
+  uint32_t carry_seen = 0;  // the current line showed a non-white-space character before this tile
+  int64_t carry_cit = -1;   // end of a citation that runs into this tile
+  if (lane == 0) { s.lwc[lb] = 0; s.lmax[lb] = 0; s.lflags[lb] = 0; }
+  for (int64_t base = tb_tile_origin(R); base < R.re; base += TB_TILE) {
+    Tile T;
+    const int64_t p0 = base + lane * TB_STRETCH;
+    tile_gather<true>(lut, R, a.ext_lo, a.ext_hi, p0, T);
+    const uint32_t V = T.valid, NLm = T.m[CA_NL], NAm = T.m[CA_NA];
+    uint32_t WSm = T.m[CA_WS];
+    if (NAm) {  // non-ASCII White_Space: only a few lead bytes can begin one
+      const int fv = tb_ctz32(V);
+      if (((T.m[CA_CONT] >> fv) & 1u) && p0 + fv > R.rs) {  // the stretch begins inside a character
+        const int64_t k = C.prev_lead(t, p0 + fv, R.rs);
+        int len; uint32_t cp;
+        if (C.at(t, k, &len, &cp) & CI_WS) { const int64_t e = k + len - p0; WSm |= tb_below(e > 32 ? 32 : (int)e) & ~tb_below(fv); }
+      }
+      uint32_t cand = T.h[CH_WSLEAD];
+      while (cand) {
+        const int i = tb_ctz32(cand);
+        cand &= cand - 1u;
+        int len; uint32_t cp;
+        if (C.at(t, p0 + i, &len, &cp) & CI_WS) WSm |= tb_below(i + len > 32 ? 32 : i + len) & ~tb_below(i);
+      }
+    }
+    const uint32_t NW = V & ~WSm;
+    if (T.m[CA_CURLY]) flags |= C4F_CURLY;
+    if (cfg.filter_lorem_ipsum) {
+      uint32_t c = T.m[CA_LL] & ((T.m[CA_LO] >> 1) | 0x80000000u);
+      while (c) {
+        const int i = tb_ctz32(c);
+        c &= c - 1u;
+        if (c4_fold_match(t, p0 + i, R.re, "lorem ipsum", 11)) flags |= C4F_LOREM;
+      }
+    }
+    // ---- citations: every '[' is tried on its own (a match holds no '[' after its first byte)
+    uint32_t cit = 0;
+    if (cfg.remove_citations) {
+      int64_t my_end = -1;
+      uint32_t c = T.m[CA_LBR];
+      while (c) {
+        const int i = tb_ctz32(c);
+        c &= c - 1u;
+        const int64_t e = c4_citation_end(C, R, p0 + i);
+        if (e > 0) { cit |= tb_below(e - p0 > 32 ? 32 : (int)(e - p0)) & ~tb_below(i); if (e > my_end) my_end = e; }
+      }
+      if (simt_any(my_end > p0 + 32) || carry_cit > base) {  // a citation runs past its stretch
+        int64_t v = my_end;
+        for (int off = 1; off < 32; off <<= 1) { int64_t u = simt_shfl_up64(v, off); if (lane >= off && u > v) v = u; }
+        int64_t inc = simt_shfl_up64(v, 1);
+        if (lane == 0) inc = -1;
+        if (carry_cit > inc) inc = carry_cit;
+        if (inc > p0) cit |= tb_below(inc - p0 > 32 ? 32 : (int)(inc - p0));
+        const int64_t last = (int64_t)simt_shfl((uint64_t)v, 31);
+        if (last > carry_cit) carry_cit = last;
+      }
+    }
+    // ---- which white space is inside its (trimmed) line: a non-white-space character on both sides
+    const uint32_t LSb = NLm << 1;  // line starts inside the stretch
+    const int fnl = tb_ctz32(NLm);
+    const uint32_t headm = tb_upto(fnl), tailm = NLm ? ~tb_upto(31 - tb_clz32(NLm)) : 0xFFFFFFFFu;
+    uint32_t seenL = tb_spread_up(NW, LSb), seenR = tb_spread_down(NW, LSb);
+    const uint32_t nl_lanes = simt_ballot(NLm != 0u), tnw_lanes = simt_ballot((NW & tailm) != 0u);
+    {
+      const uint32_t lower = nl_lanes & below_lane;
+      uint32_t in_seen;
+      if (lower) in_seen = (tnw_lanes & below_lane & ~tb_below(31 - tb_clz32(lower))) != 0u;
+      else in_seen = carry_seen | ((tnw_lanes & below_lane) != 0u);
+      if (in_seen) seenL |= headm;
+    }
+    {
+      const uint32_t ev = NW | NLm;
+      const uint32_t ev_lanes = simt_ballot(ev != 0u), nwfirst_lanes = simt_ballot((ev & (0u - ev) & NW) != 0u);
+      const uint32_t higher = ev_lanes & ~upto_lane;
+      const uint32_t unres = V & WSm & ~NLm & tailm & ~seenR;
+      uint32_t beyond = 0;
+      if (simt_any(unres != 0u && higher == 0u)) {  // the answer lies beyond the tile: look ahead (white-space runs are short)
+        int64_t j = base + TB_TILE;
+        while (j < R.re && tb_is_cont(tb_byte(t, j))) j++;
+        while (j < R.re) {
+          int len; uint32_t cp;
+          const uint32_t ci = C.at(t, j, &len, &cp);
+          if (cp == '\n') break;
+          if (!(ci & CI_WS)) { beyond = 1; break; }
+          j += len;
+        }
+      }
+      const uint32_t after_nw = higher ? ((nwfirst_lanes >> tb_ctz32(higher)) & 1u) : beyond;
+      if (after_nw) seenR |= tailm;
+    }
+    if (nl_lanes) carry_seen = (tnw_lanes & ~tb_below(31 - tb_clz32(nl_lanes))) != 0u;
+    else carry_seen |= tnw_lanes != 0u;
+    // ---- kept bytes
+    uint32_t K = (NW | (WSm & ~NLm & seenL & seenR)) & ~cit & V;
+    uint32_t nlk = NLm;
+    {
+      const int64_t last = R.re - 1;
+      if (last >= p0 && last < p0 + 32) nlk &= ~(1u << (uint32_t)(last - p0));  // the '\n' that ends the document
+    }
+    K |= nlk;
+    outpos += tile_store_kept(T.w, K, stage, out + outpos, lane);
+    // zero the slot of every line that starts after a '\n' of this stretch
+    const uint32_t cnt = (uint32_t)tb_popc32(NLm);
+    uint32_t ntot, npre = simt_exscan(cnt, lane, &ntot);
+    for (uint32_t k = 0; k < cnt; k++) { const uint64_t li = lb + nl + npre + k + 1; s.lwc[li] = 0; s.lmax[li] = 0; s.lflags[li] = 0; }
+    nl += ntot;
+  }
+  flags = simt_or(flags);
+  if (lane == 0) {
+    const uint32_t lines = nl + ((R.re > R.rs && t[R.re - 1] != '\n') ? 1u : 0u);  // str::lines().count()
+    s.plen[d] = outpos; s.nlines[d] = lines;
+    uint32_t df = 0;
+    if (cfg.filter_lorem_ipsum && (flags & C4F_LOREM)) df |= C4F_LOREM;
+    if (cfg.filter_curly_bracket && (flags & C4F_CURLY)) df |= C4F_CURLY;
+    s.docflags[d] = df;
+    s.prs[d] = R.rs; s.pre[d] = R.rs + outpos;
+  }
+}

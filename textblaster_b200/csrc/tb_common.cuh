@@ -47,6 +47,7 @@ struct UcTables {
   const uint32_t* caseign;  // [n_caseign][2]
   const uint64_t* powtab;   // [TB_POWTAB] packed B^k for both moduli
   int n_lower, n_cased, n_caseign;
+  uint32_t wslead[8];       // bit b: some non-ASCII White_Space character starts with byte b (tb_compute_wslead)
 };
 #define TB_POWTAB 1025
 

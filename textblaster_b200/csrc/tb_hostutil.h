@@ -51,3 +51,14 @@ inline C4Cfg tb_c4cfg_of(const tb_c4_params& q) {
                (uint32_t)q.filter_javascript, (uint32_t)q.filter_curly_bracket, (uint32_t)q.filter_policy,
                q.min_num_sentences, q.min_words_per_line, q.max_word_length};
 }
+
+// UcTables::wslead: the lead bytes of the non-ASCII White_Space characters, from the cinfo trie
+inline void tb_compute_wslead(const uint16_t* stage1, const uint16_t* stage2, uint32_t out[8]) {
+  for (int i = 0; i < 8; i++) out[i] = 0;
+  for (uint32_t cp = 0x80; cp < 0x110000u; cp++) {
+    uint32_t ci = stage2[(uint32_t)stage1[cp >> 8] * 256u + (cp & 255u)];
+    if (!(ci & CI_WS)) continue;
+    uint32_t lead = cp < 0x800u ? (0xC0u | (cp >> 6)) : cp < 0x10000u ? (0xE0u | (cp >> 12)) : (0xF0u | (cp >> 18));
+    out[lead >> 5] |= 1u << (lead & 31u);
+  }
+}

@@ -22,7 +22,7 @@ __device__ __forceinline__ void load_ascii(uint16_t* s_ascii, const UcTables& uc
 __device__ __forceinline__ void load_lut(LutEntry* s_lut, const UcTables& uc, int kind, uint32_t firstmask) {
   for (uint32_t i = threadIdx.x; i < 256; i += blockDim.x) {
     uint32_t ci = i < 128 ? uc.stage2[(uint32_t)uc.stage1[0] * 256u + i] : 0u;
-    s_lut[i] = tb_lut_entry(kind, i, ci, firstmask);
+    s_lut[i] = tb_lut_entry(kind, i, ci, kind == TB_LUT_C4A ? ((uc.wslead[i >> 5] >> (i & 31)) & 1u) : firstmask);
   }
   __syncthreads();
 }
@@ -123,12 +123,17 @@ __global__ void __launch_bounds__(TB_REP_L_THREADS) k_gr_rep_l(KBatch a, const i
     body_gr_rep_l(a, s_red, ts, te, s, cfg, step, out, (int64_t)s.lists[2 * (uint64_t)s.n + i], (int)threadIdx.x);
   }
 }
-__global__ void __launch_bounds__(TB_BLOCK) k_c4_a(KBatch a, C4Cfg cfg, C4Scratch s) {
+__global__ void __launch_bounds__(TB_BLOCK, 12) k_c4_a(KBatch a, C4Cfg cfg, C4Scratch s, uint32_t* cursor) {
   __shared__ uint16_t s_ascii[192];
+  __shared__ LutEntry s_lut[256];
+  __shared__ __align__(16) uint8_t s_stage[TB_STAGE_BYTES];
   load_ascii(s_ascii, a.uc);
-  int64_t d = warp_doc();
-  if (d >= a.n || !a.alive[d]) return;
-  body_c4_a(a, s_ascii, cfg, s, d, threadIdx.x & 31);
+  load_lut(s_lut, a.uc, TB_LUT_C4A, 0u);
+  for (;;) {
+    const int64_t d = next_doc(cursor);
+    if (d >= a.n) break;
+    if (a.alive[d]) body_c4_a(a, s_ascii, s_lut, s_stage, cfg, s, d, threadIdx.x & 31);
+  }
 }
 __global__ void __launch_bounds__(TB_BLOCK, 12) k_c4_b(KBatch a, C4Cfg cfg, C4Scratch s, uint32_t* cursor) {
   __shared__ uint16_t s_ascii[192];
@@ -193,6 +198,10 @@ __global__ void __launch_bounds__(TB_BLOCK) k_pack(int64_t n, const uint8_t* ori
   if (d < n) body_pack(orig, rs0, cur, rs, rewritten, out_off, out, d, threadIdx.x & 31);
 }
 
+inline int persistent_grid(int64_t n, int sm_count, int per_sm) {
+  int64_t g = (int64_t)sm_count * per_sm;
+  return (int)(n < g ? n : g);
+}
 inline int blocks_for_warps(int64_t n) { return (int)((n * 32 + TB_BLOCK - 1) / TB_BLOCK); }
 inline int blocks_for_threads(int64_t n) { return (int)((n + 255) / 256); }
 
@@ -205,10 +214,6 @@ void tb_launch_init_ranges(cudaStream_t st, const void* off, int off64, int64_t 
 void tb_launch_validate_utf8(cudaStream_t st, const uint8_t* text, const int64_t* rs, const int64_t* re, int64_t n,
                              int32_t* bad) {
   if (n) k_validate_utf8<<<blocks_for_warps(n), TB_BLOCK, 0, st>>>(text, rs, re, n, bad);
-}
-inline int persistent_grid(int64_t n, int sm_count, int per_sm) {
-  int64_t g = (int64_t)sm_count * per_sm;
-  return (int)(n < g ? n : g);
 }
 void tb_launch_gq(cudaStream_t st, const KBatch& b, const SwTable& sw, const GqCfg& cfg, int step, tb_gq_stats* out,
                   int sm_count, uint32_t* cursor) {
@@ -230,8 +235,8 @@ void tb_launch_gr_rep(cudaStream_t st, const KBatch& b, const int64_t* ts, const
 int tb_kernels_init() {
   return (int)cudaFuncSetAttribute(k_gr_rep_m, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TB_REP_M_SMEM);
 }
-void tb_launch_c4_a(cudaStream_t st, const KBatch& b, const C4Cfg& cfg, const C4Scratch& s) {
-  if (b.n) k_c4_a<<<blocks_for_warps(b.n), TB_BLOCK, 0, st>>>(b, cfg, s);
+void tb_launch_c4_a(cudaStream_t st, const KBatch& b, const C4Cfg& cfg, const C4Scratch& s, int sm_count, uint32_t* cursor) {
+  if (b.n) k_c4_a<<<persistent_grid(b.n, sm_count, 12), TB_BLOCK, 0, st>>>(b, cfg, s, cursor);
 }
 void tb_launch_c4_b(cudaStream_t st, const KBatch& b, const C4Cfg& cfg, const C4Scratch& s, int sm_count, uint32_t* cursor) {
   if (b.n) k_c4_b<<<persistent_grid(b.n, sm_count, 12), TB_BLOCK, 0, st>>>(b, cfg, s, cursor);

@@ -87,7 +87,7 @@ void tb_launch_gr_scan(cudaStream_t st, const KBatch& b, const int64_t* ts, cons
 void tb_launch_gr_rep(cudaStream_t st, const KBatch& b, const int64_t* ts, const int64_t* te, const GrScratch& s,
                       const GrCfg& cfg, int step, tb_gr_stats* out, int sm_count, int tier);  // tier 0 S, 1 M, 2 L
 int tb_kernels_init();  // per-process function attributes (dynamic shared memory opt-in)
-void tb_launch_c4_a(cudaStream_t st, const KBatch& b, const C4Cfg& cfg, const C4Scratch& s);
+void tb_launch_c4_a(cudaStream_t st, const KBatch& b, const C4Cfg& cfg, const C4Scratch& s, int sm_count, uint32_t* cursor);
 void tb_launch_c4_b(cudaStream_t st, const KBatch& b, const C4Cfg& cfg, const C4Scratch& s, int sm_count, uint32_t* cursor);
 void tb_launch_c4_c(cudaStream_t st, const KBatch& b, const C4Cfg& cfg, const C4Scratch& s);
 void tb_launch_c4_d(cudaStream_t st, const KBatch& b, const C4Cfg& cfg, const C4Scratch& s, int step, tb_c4_stats* out,

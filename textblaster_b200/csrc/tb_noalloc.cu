@@ -34,6 +34,7 @@
 #include <mutex>
 #include <string>
 
+#include "tb_hostutil.h"
 #include "tb_kernels.cuh"
 #include "unicode_tables.inc"
 
@@ -91,7 +92,8 @@ int setup_device(int dev, DeviceState** out) {
     unsigned char* pp = place(pw, sizeof pw);
     if (!s1 || !s2 || !lo || !ca || !ci || !pp) { cudaGetLastError(); return fail(TB_ERR_CUDA, "uploading the Unicode tables into the static scratch failed"); }
     st.uc = UcTables{(const uint16_t*)s1, (const uint16_t*)s2, (const uint32_t*)lo, (const uint32_t*)ca, (const uint32_t*)ci,
-                     (const uint64_t*)pp, TB_UC_NLOWER, TB_UC_NCASED, TB_UC_NCASEIGN};
+                     (const uint64_t*)pp, TB_UC_NLOWER, TB_UC_NCASED, TB_UC_NCASEIGN, {0}};
+    tb_compute_wslead(tb_uc_stage1, tb_uc_stage2, st.uc.wslead);
     st.tables_end = off;
     cudaDeviceProp prop;
     if (cudaGetDeviceProperties(&prop, dev) == cudaSuccess) st.sm_count = prop.multiProcessorCount;

@@ -112,6 +112,10 @@ TB_D uint64_t simt_max64(uint64_t v) {
   for (int o = 16; o; o >>= 1) { uint64_t x = simt_shfl_xor(v, o); v = x > v ? x : v; }
   return v;
 }
+TB_D int64_t simt_shfl_up64(int64_t v, int o) {
+  uint32_t lo = simt_shfl_up((uint32_t)(uint64_t)v, o), hi = simt_shfl_up((uint32_t)((uint64_t)v >> 32), o);
+  return (int64_t)(((uint64_t)hi << 32) | lo);
+}
 // exclusive prefix sum across the warp; *total gets the warp sum
 TB_D uint32_t simt_exscan(uint32_t v, int lane, uint32_t* total) {
   uint32_t x = v;

@@ -43,13 +43,40 @@
 #define TH_P1 2    // C4 pass B: first / second / third letter of a javascript / policy pattern
 #define TH_P2 3
 #define TH_P3 4
-enum { TB_LUT_GQ = 0, TB_LUT_GR = 1, TB_LUT_C4B = 2 };
+// C4 pass A uses its own slot layout (no word rules there)
+#define CA_WS 0     // ASCII White_Space (includes '\n')
+#define CA_NL 1     // '\n'
+#define CA_NA 2     // non-ASCII byte
+#define CA_CONT 3   // UTF-8 continuation byte
+#define CA_LBR 4    // '['
+#define CA_CURLY 5  // '{' or '}'
+#define CA_LL 6     // 'l' or 'L'
+#define CA_LO 7     // 'o' or 'O'
+#define CH_WSLEAD 0 // lead byte of a non-ASCII character that may be White_Space (UcTables::wslead)
+enum { TB_LUT_GQ = 0, TB_LUT_GR = 1, TB_LUT_C4B = 2, TB_LUT_C4A = 3 };
 
 struct __attribute__((aligned(8))) LutEntry { uint32_t lo, hi; };
 
-// table entry of byte value b; ci = cinfo of the code point b (only used for b < 128)
-TB_HD LutEntry tb_lut_entry(int kind, uint32_t b, uint32_t ci, uint32_t firstmask) {
+// table entry of byte value b; ci = cinfo of the code point b (only used for b < 128); aux: SwTable::firstmask
+// (TB_LUT_GQ) or "b is a lead byte that may begin a White_Space character" (TB_LUT_C4A)
+TB_HD LutEntry tb_lut_entry(int kind, uint32_t b, uint32_t ci, uint32_t aux) {
+  const uint32_t firstmask = aux;
   LutEntry e; e.lo = 0; e.hi = 0;
+  if (kind == TB_LUT_C4A) {
+    if (b >= 0x80u) {
+      e.lo |= 1u << (4 * CA_NA);
+      if ((b & 0xC0u) == 0x80u) e.lo |= 1u << (4 * CA_CONT);
+      else if (aux) e.hi |= 1u << (4 * CH_WSLEAD);
+    } else {
+      if (ci & CI_WS) e.lo |= 1u << (4 * CA_WS);
+      if (b == '\n') e.lo |= 1u << (4 * CA_NL);
+      if (b == '[') e.lo |= 1u << (4 * CA_LBR);
+      if (b == '{' || b == '}') e.lo |= 1u << (4 * CA_CURLY);
+      if ((b | 0x20u) == 'l') e.lo |= 1u << (4 * CA_LL);
+      if ((b | 0x20u) == 'o') e.lo |= 1u << (4 * CA_LO);
+    }
+    return e;
+  }
   if (b >= 0x80u) {
     e.lo |= 1u << (4 * TL_NA);
     if ((b & 0xC0u) == 0x80u) e.hi |= 1u << (4 * TH_CONT);
@@ -214,9 +241,10 @@ TB_HD void tb_load32(const uint8_t* p, uint32_t* w) {
 // first tile position of a range: the stretch of lane 0 is the 32-byte aligned block that holds rs
 TB_HD int64_t tb_tile_origin(const TextRange& R) { return R.rs - (int64_t)((uintptr_t)(R.t + R.rs) & 31u); }
 
-// Load and classify.  [ext_lo, ext_hi) is the extent of the buffer that may be read with vector loads.
+// Load the stretch at p0 and look its bytes up: T.w, T.valid, T.m[] (and T.h[] if HI).  Returns false for a
+// stretch without any byte of the range.  [ext_lo, ext_hi): extent of the buffer that vector loads may touch.
 template <bool HI>
-TB_HD void tile_classify(const LutEntry* lut, const TextRange& R, int64_t ext_lo, int64_t ext_hi, int64_t p0, Tile& T) {
+TB_HD bool tile_gather(const LutEntry* lut, const TextRange& R, int64_t ext_lo, int64_t ext_hi, int64_t p0, Tile& T) {
   const uint8_t* t = R.t;
   T.p0 = p0;
   const int64_t a = R.rs - p0, b = R.re - p0;
@@ -228,7 +256,7 @@ TB_HD void tile_classify(const LutEntry* lut, const TextRange& R, int64_t ext_lo
 #pragma unroll
     for (int k = 0; k < 8; k++) { T.w[k] = 0; T.m[k] = 0; T.h[k] = 0; }
     T.lctx = T.rctx = T.l1hi = 0; T.brk = 0xFFFFFFFFu; T.dirty = 0; T.al = 0;
-    return;
+    return false;
   }
   if (p0 >= ext_lo && p0 + 32 <= ext_hi) {
     tb_load32(t + p0, T.w);
@@ -244,15 +272,6 @@ TB_HD void tile_classify(const LutEntry* lut, const TextRange& R, int64_t ext_lo
     for (int k = 0; k < 8; k++) T.w[k] = 0;
     for (int i = 0; i < 32; i++) if ((V >> i) & 1u) T.w[i >> 2] |= tb_byte(t, p0 + i) << (8 * (i & 3));
   }
-  // context bytes
-  {
-    const int64_t q2 = p0 - 2, q1 = p0 - 1, qr = p0 + 32;
-    uint32_t l2 = 0, l1 = 0, l1h = 0, r1 = 0;
-    if (q2 >= R.rs && q2 < R.re) l2 = lut[tb_byte(t, q2)].lo;
-    if (q1 >= R.rs && q1 < R.re) { LutEntry e = lut[tb_byte(t, q1)]; l1 = e.lo; l1h = e.hi; }
-    if (qr >= R.rs && qr < R.re) r1 = lut[tb_byte(t, qr)].lo;
-    T.lctx = l2 | (l1 << 1); T.rctx = r1; T.l1hi = l1h;
-  }
 #pragma unroll
   for (int k = 0; k < 8; k++) {
     const uint32_t x = T.w[k];
@@ -265,6 +284,24 @@ TB_HD void tile_classify(const LutEntry* lut, const TextRange& R, int64_t ext_lo
   if (V != 0xFFFFFFFFu) {
 #pragma unroll
     for (int k = 0; k < 8; k++) { T.m[k] &= V; if (HI) T.h[k] &= V; }
+  }
+  return true;
+}
+
+// Load and classify for the word passes: tile_gather plus the boundary mask.
+template <bool HI>
+TB_HD void tile_classify(const LutEntry* lut, const TextRange& R, int64_t ext_lo, int64_t ext_hi, int64_t p0, Tile& T) {
+  const uint8_t* t = R.t;
+  if (!tile_gather<HI>(lut, R, ext_lo, ext_hi, p0, T)) return;
+  const uint32_t V = T.valid;
+  // context bytes
+  {
+    const int64_t q2 = p0 - 2, q1 = p0 - 1, qr = p0 + 32;
+    uint32_t l2 = 0, l1 = 0, l1h = 0, r1 = 0;
+    if (q2 >= R.rs && q2 < R.re) l2 = lut[tb_byte(t, q2)].lo;
+    if (q1 >= R.rs && q1 < R.re) { LutEntry e = lut[tb_byte(t, q1)]; l1 = e.lo; l1h = e.hi; }
+    if (qr >= R.rs && qr < R.re) r1 = lut[tb_byte(t, qr)].lo;
+    T.lctx = l2 | (l1 << 1); T.rctx = r1; T.l1hi = l1h;
   }
 #define TILE_L(c) (T.lctx << (30 - 4 * (c)))
 #define TILE_SHL1(c) tb_funnel_l(TILE_L(c), T.m[c], 1)
