@@ -123,4 +123,7 @@ def boundary_docs():
                     + "\n\n" + m + " " + m + ". Tail [7] words" + ws[(k + 3) % len(ws)] * 3 + "and more [1, 2] text.\n")
         docs.append(lead + " " + (m + " ") * 8 + "\r\n" + ws[k] * 2 + m + ".\r\n")
         docs.append(("ab " * (pad // 3)) + "x" + ws[k] * (1 + pad % 5) + "[1" + "," * (pad % 2) + " 2]" + ws[(k + 1) % len(ws)] + "y z. Done here now.")
+    # newline runs longer than a stretch, kept lines on both sides
+    docs.append("First kept line here.\n" + "\n" * 70 + "Second kept line here.\n" + "\n" * 33 + "x\n" * 40 + "Third kept line is here.")
+    docs.append("\n" * 100 + "Only line, it ends well." + "\n" * 64)
     return docs

@@ -163,7 +163,7 @@ extern "C" int tbe_run_chain(const tb_step_cfg* steps, size_t n_steps, const uin
       build_lut(TB_LUT_C4B, 0u);
       run_warps(n, [&](int64_t d) { return alive[d] && !cs.docflags[d] && cs.nlines[d] != 0; },
                 [&](int64_t d, int lane) { body_c4_b(b, ascii, lut.data(), cfg, cs, d, lane); });
-      run_warps(n, [&](int64_t) { return true; }, [&](int64_t d, int lane) { body_c4_c(b, cfg, cs, d, lane); });
+      run_warps(n, [&](int64_t) { return true; }, [&](int64_t d, int lane) { body_c4_c(b, cstage, cfg, cs, d, lane); });
       { KBatch fb = b; fb.text = cs.F; fb.rs = cs.frs; fb.re = cs.fre; for (int64_t d = 0; d < n; d++) body_trim(fb, ascii, cs.frs, cs.fre, d); }
       run_warps(n, alive_pred, [&](int64_t d, int lane) { body_c4_d(b, ascii, cfg, cs, (int)s, (tb_c4_stats*)stats, rewritten, rs, re, d, lane); });
       b.text = cs.F;

@@ -340,7 +340,7 @@ int enqueue_chain(tb_pipeline* p, const uint8_t* text, int64_t n, int64_t nbytes
                    p->c_prs.as<int64_t>(), p->c_pre.as<int64_t>(), p->c_frs.as<int64_t>(), p->c_fre.as<int64_t>(), p->c_cnt.as<uint32_t>()};
       { Timed t(p, "k_c4_a"); tb_launch_c4_a(st, b, sh.c4, cs, c->sm_count, cursors + TB_MAX_STEPS + s); }
       { Timed t(p, "k_c4_b"); tb_launch_c4_b(st, b, sh.c4, cs, c->sm_count, cursors + s); }
-      { Timed t(p, "k_c4_c"); tb_launch_c4_c(st, b, sh.c4, cs); }
+      { Timed t(p, "k_c4_c"); tb_launch_c4_c(st, b, sh.c4, cs, c->sm_count, cursors + 2 * TB_MAX_STEPS + s); }
       {  // content = kept.join("\n").trim()   (c4_filters.rs:258)
         KBatch fb = b; fb.text = cs.F; fb.rs = cs.frs; fb.re = cs.fre;
         Timed t(p, "k_trim"); tb_launch_trim(st, fb, cs.frs, cs.fre);

@@ -380,10 +380,10 @@ TB_D void body_c4_b(const KBatch& a, const uint16_t* s_ascii, const LutEntry* lu
 }
 
 // Pass C: drop lines, join the kept ones with '\n' (c4_filters.rs:207-258) -> F; line counters.
-TB_D void body_c4_c(const KBatch& a, const C4Cfg& cfg, const C4Scratch& s, int64_t d, int lane) {
+TB_D uint32_t tile_store_kept(const uint32_t* w, uint32_t K, uint8_t* stage, uint8_t* dst, int lane);
+TB_D void body_c4_c(const KBatch& a, uint8_t* stage, const C4Cfg& cfg, const C4Scratch& s, int64_t d, int lane) {
   if (!a.alive[d] || s.docflags[d]) { if (lane == 0) { s.frs[d] = a.rs[d]; s.fre[d] = a.rs[d]; } return; }
-  const int64_t rs = s.prs[d], re = s.pre[d];
-  const uint8_t* t = s.P;
+  TextRange R{s.P, s.prs[d], s.pre[d]};
   uint8_t* out = s.F + a.rs[d];
   const uint64_t lb = (uint64_t)a.rs[d] + (uint64_t)d;
   const uint32_t m = s.nlines[d];
@@ -391,49 +391,41 @@ TB_D void body_c4_c(const KBatch& a, const C4Cfg& cfg, const C4Scratch& s, int64
   uint32_t nl = 0, kept_run = 0;              // lines terminated / kept before this tile
   int64_t outpos = 0;
   if (m) {
-    for (int64_t base = rs; base < re; base += TB_TILE) {
-      int64_t p0 = base + lane * TB_STRETCH;
-      int64_t p1 = p0 + TB_STRETCH < re ? p0 + TB_STRETCH : re;
-      uint32_t nlmask = 0;
-      if (p0 < re) for (int64_t i = p0; i < p1; i++) if (t[i] == '\n') nlmask |= 1u << (uint32_t)(i - p0);
-      uint32_t tot, pre = simt_exscan((uint32_t)simt_popc(nlmask), lane, &tot);
-      // decisions of the lines terminated in this stretch
-      uint32_t keepmask = 0, nkept_here = 0;
-      const uint64_t l0 = lb + nl + pre;  // line that contains the first byte of the stretch
-      {
-        uint32_t mm = nlmask, j = 0;
-        while (mm) {
-          uint32_t bit = (uint32_t)simt_ffs(mm) - 1; mm &= mm - 1;
-          int dec = c4_line_decision(cfg, s.lwc[l0 + j], s.lmax[l0 + j], s.lflags[l0 + j]);
-          if (dec == 0) { keepmask |= 1u << bit; nkept_here++; kept++; }
-          else if (dec == 1) c1++; else if (dec == 2) c2++; else if (dec == 3) c3++;
-          j++;
+    for (int64_t base = tb_tile_origin(R); base < R.re; base += TB_TILE) {
+      uint32_t w[8];
+      const int64_t p0 = base + lane * TB_STRETCH;
+      const uint32_t V = tile_load(R, a.ext_lo, a.ext_hi, p0, w);
+      const uint32_t NLm = tile_eq_mask(w, '\n') & V;
+      const uint32_t cnt = (uint32_t)tb_popc32(NLm);
+      uint32_t tot, pre = simt_exscan(cnt, lane, &tot);
+      const uint64_t l0 = lb + nl + pre;  // line that holds the first byte of the stretch
+      // decisions of the lines this stretch touches: bit j = line l0 + j is kept
+      uint64_t dec = 0;  // up to 33 lines
+      if (V) {
+        for (uint32_t j = 0; j <= cnt; j++) {
+          const int r = c4_line_decision(cfg, s.lwc[l0 + j], s.lmax[l0 + j], s.lflags[l0 + j]);
+          if (r == 0) dec |= 1ull << j;
+          if (j < cnt) { if (r == 0) kept++; else if (r == 1) c1++; else if (r == 2) c2++; else if (r == 3) c3++; }  // lines that end here
         }
       }
-      uint32_t ktot, kpre = simt_exscan(nkept_here, lane, &ktot);
-      // emit: bytes of kept lines; a '\n' in front of a kept line that follows another kept line
-      uint8_t buf[TB_STRETCH];
-      uint32_t nb = 0;
-      if (p0 < re) {
-        uint32_t j = 0, kept_before = kept_run + kpre;
-        bool keep_cur = c4_line_decision(cfg, s.lwc[l0], s.lmax[l0], s.lflags[l0]) == 0;
-        for (int64_t i = p0; i < p1; i++) {
-          uint32_t b = t[i];
-          if (b == '\n') {
-            if ((keepmask >> (uint32_t)(i - p0)) & 1u) kept_before++;
-            j++;
-            keep_cur = c4_line_decision(cfg, s.lwc[l0 + j], s.lmax[l0 + j], s.lflags[l0 + j]) == 0;
-            if (keep_cur && kept_before) buf[nb++] = '\n';
-          } else if (keep_cur) buf[nb++] = (uint8_t)b;
-        }
+      uint32_t ktot, kpre = simt_exscan((uint32_t)tb_popc64(dec & ((1ull << cnt) - 1ull)), lane, &ktot);
+      // bytes of kept lines; a '\n' goes in front of a kept line that follows another kept line
+      uint32_t K = 0, mm = NLm;
+      int start = 0;
+      for (uint32_t j = 0; j < cnt; j++) {
+        const int bit = tb_ctz32(mm);
+        mm &= mm - 1u;
+        if ((dec >> j) & 1u) K |= tb_below(bit) & ~tb_below(start);
+        if (((dec >> (j + 1)) & 1u) && kept_run + kpre + (uint32_t)tb_popc64(dec & ((2ull << j) - 1ull)) > 0u) K |= 1u << bit;
+        start = bit + 1;
       }
-      uint32_t btot, bpre = simt_exscan(nb, lane, &btot);
-      for (uint32_t k = 0; k < nb; k++) out[outpos + bpre + k] = buf[k];
-      outpos += btot; nl += tot; kept_run += ktot;
+      if ((dec >> cnt) & 1u) K |= ~tb_below(start);
+      outpos += tile_store_kept(w, K & V, stage, out + outpos, lane);
+      nl += tot; kept_run += ktot;
     }
     if (lane == 0) {  // the last line has no terminator
-      int dec = c4_line_decision(cfg, s.lwc[lb + m - 1], s.lmax[lb + m - 1], s.lflags[lb + m - 1]);
-      if (dec == 0) kept++; else if (dec == 1) c1++; else if (dec == 2) c2++; else if (dec == 3) c3++;
+      int r = c4_line_decision(cfg, s.lwc[lb + m - 1], s.lmax[lb + m - 1], s.lflags[lb + m - 1]);
+      if (r == 0) kept++; else if (r == 1) c1++; else if (r == 2) c2++; else if (r == 3) c3++;
     }
   }
   c1 = simt_sum(c1); c2 = simt_sum(c2); c3 = simt_sum(c3); kept = simt_sum(kept);

@@ -146,10 +146,13 @@ __global__ void __launch_bounds__(TB_BLOCK, 12) k_c4_b(KBatch a, C4Cfg cfg, C4Sc
     if (a.alive[d] && !s.docflags[d] && s.nlines[d] != 0) body_c4_b(a, s_ascii, s_lut, cfg, s, d, threadIdx.x & 31);
   }
 }
-__global__ void __launch_bounds__(TB_BLOCK) k_c4_c(KBatch a, C4Cfg cfg, C4Scratch s) {
-  int64_t d = warp_doc();
-  if (d >= a.n) return;
-  body_c4_c(a, cfg, s, d, threadIdx.x & 31);
+__global__ void __launch_bounds__(TB_BLOCK, 16) k_c4_c(KBatch a, C4Cfg cfg, C4Scratch s, uint32_t* cursor) {
+  __shared__ __align__(16) uint8_t s_stage[TB_STAGE_BYTES];
+  for (;;) {
+    const int64_t d = next_doc(cursor);
+    if (d >= a.n) break;
+    body_c4_c(a, s_stage, cfg, s, d, threadIdx.x & 31);
+  }
 }
 __global__ void __launch_bounds__(TB_BLOCK) k_c4_d(KBatch a, C4Cfg cfg, C4Scratch s, int step, tb_c4_stats* out,
                                                    uint8_t* rewritten, int64_t* rs_out, int64_t* re_out) {
@@ -241,8 +244,8 @@ void tb_launch_c4_a(cudaStream_t st, const KBatch& b, const C4Cfg& cfg, const C4
 void tb_launch_c4_b(cudaStream_t st, const KBatch& b, const C4Cfg& cfg, const C4Scratch& s, int sm_count, uint32_t* cursor) {
   if (b.n) k_c4_b<<<persistent_grid(b.n, sm_count, 12), TB_BLOCK, 0, st>>>(b, cfg, s, cursor);
 }
-void tb_launch_c4_c(cudaStream_t st, const KBatch& b, const C4Cfg& cfg, const C4Scratch& s) {
-  if (b.n) k_c4_c<<<blocks_for_warps(b.n), TB_BLOCK, 0, st>>>(b, cfg, s);
+void tb_launch_c4_c(cudaStream_t st, const KBatch& b, const C4Cfg& cfg, const C4Scratch& s, int sm_count, uint32_t* cursor) {
+  if (b.n) k_c4_c<<<persistent_grid(b.n, sm_count, 16), TB_BLOCK, 0, st>>>(b, cfg, s, cursor);
 }
 void tb_launch_c4_d(cudaStream_t st, const KBatch& b, const C4Cfg& cfg, const C4Scratch& s, int step, tb_c4_stats* out,
                     uint8_t* rewritten) {

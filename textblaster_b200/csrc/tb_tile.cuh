@@ -243,34 +243,57 @@ TB_HD int64_t tb_tile_origin(const TextRange& R) { return R.rs - (int64_t)((uint
 
 // Load the stretch at p0 and look its bytes up: T.w, T.valid, T.m[] (and T.h[] if HI).  Returns false for a
 // stretch without any byte of the range.  [ext_lo, ext_hi): extent of the buffer that vector loads may touch.
-template <bool HI>
-TB_HD bool tile_gather(const LutEntry* lut, const TextRange& R, int64_t ext_lo, int64_t ext_hi, int64_t p0, Tile& T) {
+// the 32 bytes at p0 (0 outside [rs, re)); returns the mask of bytes inside the range
+TB_HD uint32_t tile_load(const TextRange& R, int64_t ext_lo, int64_t ext_hi, int64_t p0, uint32_t* w) {
   const uint8_t* t = R.t;
-  T.p0 = p0;
   const int64_t a = R.rs - p0, b = R.re - p0;
   const uint32_t vlo = a <= 0 ? 0xFFFFFFFFu : (a >= 32 ? 0u : ~((1u << (uint32_t)a) - 1u));
   const uint32_t vhi = b >= 32 ? 0xFFFFFFFFu : (b <= 0 ? 0u : ((1u << (uint32_t)b) - 1u));
   const uint32_t V = vlo & vhi;
-  T.valid = V;
   if (V == 0u) {
 #pragma unroll
-    for (int k = 0; k < 8; k++) { T.w[k] = 0; T.m[k] = 0; T.h[k] = 0; }
-    T.lctx = T.rctx = T.l1hi = 0; T.brk = 0xFFFFFFFFu; T.dirty = 0; T.al = 0;
-    return false;
-  }
-  if (p0 >= ext_lo && p0 + 32 <= ext_hi) {
-    tb_load32(t + p0, T.w);
+    for (int k = 0; k < 8; k++) w[k] = 0;
+  } else if (p0 >= ext_lo && p0 + 32 <= ext_hi) {
+    tb_load32(t + p0, w);
     if (V != 0xFFFFFFFFu) {
 #pragma unroll
       for (int k = 0; k < 8; k++) {
         uint32_t nib = (V >> (4 * k)) & 15u;
-        T.w[k] &= ((nib * 0x00204081u) & 0x01010101u) * 0xFFu;
+        w[k] &= ((nib * 0x00204081u) & 0x01010101u) * 0xFFu;
       }
     }
   } else {
 #pragma unroll
-    for (int k = 0; k < 8; k++) T.w[k] = 0;
-    for (int i = 0; i < 32; i++) if ((V >> i) & 1u) T.w[i >> 2] |= tb_byte(t, p0 + i) << (8 * (i & 3));
+    for (int k = 0; k < 8; k++) w[k] = 0;
+    for (int i = 0; i < 32; i++) if ((V >> i) & 1u) w[i >> 2] |= tb_byte(t, p0 + i) << (8 * (i & 3));
+  }
+  return V;
+}
+// mask of the bytes equal to c (SWAR compare, no table)
+TB_HD uint32_t tile_eq_mask(const uint32_t* w, uint32_t c) {
+  const uint32_t cc = c * 0x01010101u;
+  uint32_t m = 0;
+#pragma unroll
+  for (int k = 0; k < 8; k++) {
+    const uint32_t z = w[k] ^ cc;
+    const uint32_t t = ~(((z & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | z | 0x7F7F7F7Fu);  // 0x80 where the byte of z is zero
+    m |= ((((t >> 7) * 0x00204081u) >> 21) & 15u) << (4 * k);
+  }
+  return m;
+}
+
+// Load the stretch at p0 and look its bytes up: T.w, T.valid, T.m[] (and T.h[] if HI).  Returns false for a
+// stretch without any byte of the range.  [ext_lo, ext_hi): extent of the buffer that vector loads may touch.
+template <bool HI>
+TB_HD bool tile_gather(const LutEntry* lut, const TextRange& R, int64_t ext_lo, int64_t ext_hi, int64_t p0, Tile& T) {
+  T.p0 = p0;
+  const uint32_t V = tile_load(R, ext_lo, ext_hi, p0, T.w);
+  T.valid = V;
+  if (V == 0u) {
+#pragma unroll
+    for (int k = 0; k < 8; k++) { T.m[k] = 0; T.h[k] = 0; }
+    T.lctx = T.rctx = T.l1hi = 0; T.brk = 0xFFFFFFFFu; T.dirty = 0; T.al = 0;
+    return false;
   }
 #pragma unroll
   for (int k = 0; k < 8; k++) {
