@@ -87,3 +87,21 @@ def test_general_word_path_matches(monkeypatch):
     texts = fuzzgen.FuzzGen(21).docs(40) + [fuzzgen.english_doc(rng, 2500)] + fuzzgen.boundary_docs()[:30]
     for name in ("baseline_order", "gq_open", "gr_open"):
         _check(name, texts)
+
+
+def split_ambiguity_docs():
+    """find_all_duplicate keys are bare concatenations (text.rs:250): "no where" and "now here" give the same
+    key although the word sequences differ, and such a pair need not share any shorter repeated n-gram.
+    Tiny alphabets make these collisions frequent."""
+    rng = random.Random(12)
+    toks = ["a", "b", "ab", "ba", "aa", "aba", "bab", "no", "now", "where", "here", "w", "he", "re"]
+    docs = ["is no where to be seen today but is now here to be seen today ok",
+            "a ba b ab a ba b ab x a ba", "ab a ab a a ba a ba ab a"]
+    for _ in range(40):
+        docs.append(" ".join(rng.choice(toks) for _ in range(rng.choice([8, 30, 120, 700]))))
+    return docs
+
+
+def test_ngram_split_ambiguity():
+    _check("gr_open", split_ambiguity_docs())
+    _check("gr_shipped", split_ambiguity_docs())

@@ -14,7 +14,7 @@ import multilingual
 import oracle
 from parity_cases import CHAINS, GQ_OPEN, GR_OPEN, step_types
 from parity_util import compare
-from test_emul_parity import GOLDEN_DOCS
+from test_emul_parity import GOLDEN_DOCS, split_ambiguity_docs
 from test_oracle_golden import C4_LINE_CASES, c4_default
 from textblaster_b200 import _abi, synth
 from textblaster_b200.config import GopherRepetitionParams
@@ -122,6 +122,12 @@ def test_general_word_path_matches(name):
     contents = [res.content_of(i) for i in range(res.n_docs)] if res.content is not None else None
     compare(ores, res.keep, res.failed_step, res.stats, contents, step_types(steps), texts, label=name + "/general")
     p.close()
+
+
+def test_ngram_split_ambiguity():
+    """Concatenated n-gram keys that agree although the word sequences differ ("no where" / "now here")."""
+    check_texts("gr_open", split_ambiguity_docs())
+    check_texts("gr_shipped", split_ambiguity_docs())
 
 
 def test_int32_offsets_and_chunking():

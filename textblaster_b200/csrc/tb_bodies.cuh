@@ -227,45 +227,53 @@ TB_D void body_gr_scan(const KBatch& a, const uint16_t* s_ascii, const LutEntry*
 // ---------------------------------------------------------------------------------------------
 // GopherRepetitionFilter, pass 2 (tb_rep.cuh): three tiers by document size
 // ---------------------------------------------------------------------------------------------
-#define TB_REP_S_SMEM (TB_REP_S_CAP * 8 + (TB_REP_S_CAP + 2) * 4 + 2 * TB_REP_S_CAP * 4 + TB_REP_S_CAP * 2)
-#define TB_REP_M_SMEM (TB_REP_M_CAP * 8 + (TB_REP_M_CAP + 2) * 4 + 2 * TB_REP_M_CAP * 4 + TB_REP_M_CAP * 2 + 64 * 8)
+// shared-memory layout of one document's working arrays for capacity CAP (8-byte aligned pieces first)
+#define TB_REP_SMEM(CAP) ((CAP) * 8 + ((CAP) + 2) * 4 + 2 * (CAP) * 4 + ((CAP) / 32 + 2) * 4 + (CAP) * 2 + (CAP) * 2)
+#define TB_REP_S_SMEM TB_REP_SMEM(TB_REP_S_CAP)
+#define TB_REP_M_SMEM (TB_REP_SMEM(TB_REP_M_CAP) + 64 * 8)
+struct RepCarve { RepArrays A; uint32_t* tab; uint16_t* cnt; uint16_t* list; uint8_t* end; };
+TB_D RepCarve rep_carve(uint8_t* smem, uint32_t cap) {
+  RepCarve c;
+  c.A.H = (uint64_t*)smem;
+  c.A.woff = (uint32_t*)(c.A.H + cap);
+  c.tab = c.A.woff + cap + 2;
+  c.A.flag = c.tab + 2 * cap;
+  c.cnt = (uint16_t*)(c.A.flag + cap / 32 + 2);
+  c.list = c.cnt + cap;
+  c.end = (uint8_t*)(c.list + cap);
+  return c;
+}
 
 // tier S: one warp, working arrays carved from `smem` (TB_REP_S_SMEM bytes, 8-byte aligned)
 TB_D void body_gr_rep_s(const KBatch& a, uint8_t* smem, const int64_t* ts, const int64_t* te, const GrScratch& s,
                         const GrCfg& cfg, int step, tb_gr_stats* out, int64_t d, int lane) {
-  RepArrays A;
-  A.H = (uint64_t*)smem;
-  A.woff = (uint32_t*)(A.H + TB_REP_S_CAP);
-  uint32_t* tab = A.woff + TB_REP_S_CAP + 2;
-  uint16_t* cnt = (uint16_t*)(tab + 2 * TB_REP_S_CAP);
+  RepCarve c = rep_carve(smem, TB_REP_S_CAP);
   WarpGroup g{lane};
-  rep_body<WarpGroup, uint16_t>(g, a, ts, te, s, cfg, step, out, d, A, tab, cnt);
+  rep_body<WarpGroup, uint16_t>(g, a, ts, te, s, cfg, step, out, d, c.A, c.tab, c.cnt, c.list);
 }
 // tier M: one CTA, working arrays carved from `smem` (TB_REP_M_SMEM bytes)
 TB_D void body_gr_rep_m(const KBatch& a, uint8_t* smem, const int64_t* ts, const int64_t* te, const GrScratch& s,
                         const GrCfg& cfg, int step, tb_gr_stats* out, int64_t d, int tid) {
-  RepArrays A;
-  A.H = (uint64_t*)smem;
-  A.woff = (uint32_t*)(A.H + TB_REP_M_CAP);
-  uint32_t* tab = A.woff + TB_REP_M_CAP + 2;
-  uint16_t* cnt = (uint16_t*)(tab + 2 * TB_REP_M_CAP);
-  BlockGroup g{tid, (uint64_t*)(cnt + TB_REP_M_CAP)};
-  rep_body<BlockGroup, uint16_t>(g, a, ts, te, s, cfg, step, out, d, A, tab, cnt);
+  RepCarve c = rep_carve(smem, TB_REP_M_CAP);
+  BlockGroup g{tid, (uint64_t*)(((uintptr_t)c.end + 7) & ~(uintptr_t)7)};
+  rep_body<BlockGroup, uint16_t>(g, a, ts, te, s, cfg, step, out, d, c.A, c.tab, c.cnt, c.list);
 }
 // tier L: one CTA, working arrays in the document's region of the global work area; `red` = 64 u64 of shared scratch
 TB_D void body_gr_rep_l(const KBatch& a, uint64_t* red, const int64_t* ts, const int64_t* te, const GrScratch& s,
                         const GrCfg& cfg, int step, tb_gr_stats* out, int64_t d, int tid) {
   const int64_t rs = ts[d], re = te[d];
   const uint64_t ub = (uint64_t)(rs >> 1) + (uint64_t)d;
-  const uint32_t U = (uint32_t)((re - rs) >> 1) + 1u;
+  const uint32_t U = (uint32_t)((re - rs) >> 1) + 1u;  // >= number of words, >= number of line pieces
   uint32_t* work = s.work + ub * TB_REP_K + (uint64_t)d * TB_REP_DOC_EXTRA;
   RepArrays A;
-  A.H = (uint64_t*)work;
-  A.woff = (uint32_t*)(A.H + U);
-  uint32_t* tab = A.woff + U + 2;
+  A.H = (uint64_t*)work;                   // U entries
+  A.woff = (uint32_t*)(A.H + U);           // U + 2
+  uint32_t* tab = A.woff + U + 2;          // 2 U + TB_REP_MIN_TABLE
   uint32_t* cnt = tab + 2u * U + TB_REP_MIN_TABLE;
+  uint32_t* list = cnt + U;
+  A.flag = list + U;                       // U / 32 + 1
   BlockGroup g{tid, red};
-  rep_body<BlockGroup, uint32_t>(g, a, ts, te, s, cfg, step, out, d, A, tab, cnt);
+  rep_body<BlockGroup, uint32_t>(g, a, ts, te, s, cfg, step, out, d, A, tab, cnt, list);
 }
 
 // ---------------------------------------------------------------------------------------------

@@ -58,8 +58,8 @@ struct GrScratch {
   uint32_t* counters;                       // [8]: list lengths [0..2], work cursors [4..6], scan cursor [7]
   int64_t n;
 };
-#define TB_REP_K 6u           // tier-L words per unit: H[2U] woff[U+2] tab[2U+16] cnt[U]
-#define TB_REP_DOC_EXTRA 20u  // words: 16 (minimum table) + 1 (woff tail) + pad
+#define TB_REP_K 8u           // tier-L words per unit: H[2U] woff[U+2] tab[2U+16] cnt[U] list[U] flag[U/32+1]
+#define TB_REP_DOC_EXTRA 24u  // words: the constant parts of the above, padded to keep 8-byte alignment
 #define TB_REP_MIN_TABLE 16u
 
 // scratch of the C4 filter

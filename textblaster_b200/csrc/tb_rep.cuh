@@ -127,9 +127,9 @@ TB_D void idx_inc(uint16_t* a) {
 
 // table size: load factor 0.5; any size works because slots are picked by multiply-high
 TB_D uint32_t rep_tab_size(uint32_t count) { return 2u * count < TB_REP_MIN_TABLE ? TB_REP_MIN_TABLE : 2u * count; }
-TB_D uint32_t rep_slot(uint64_t key, uint32_t len, uint32_t T) {
-  uint32_t h = ((uint32_t)(key >> 32) * 0x9E3779B1u) ^ ((uint32_t)key * 0x85EBCA77u) ^ (len * 0xC2B2AE3Du);
-  h ^= h >> 15; h *= 0x2C1B3C6Du; h ^= h >> 13;
+TB_D uint32_t rep_slot(uint64_t key, uint32_t T) {  // the two residues are already well mixed
+  uint32_t h = ((uint32_t)(key >> 32) * 0x9E3779B1u) ^ (uint32_t)key;
+  h ^= h >> 15;
   return (uint32_t)(((uint64_t)h * T) >> 32);
 }
 TB_D uint32_t rep_next(uint32_t sl, uint32_t T) { return sl + 1 == T ? 0u : sl + 1; }
@@ -149,12 +149,12 @@ TB_D void rep_dedup(const G& g, uint32_t* tab, const uint64_t* h, const uint32_t
   uint32_t distinct = 0; uint64_t dbytes = 0, total = 0;
   for (uint32_t i = g.tid; i < n; i += g.size()) {
     uint64_t hi = h[i]; uint32_t li = len[i];
-    uint32_t sl = rep_slot(hi, li, T);
+    uint32_t sl = rep_slot(hi, T);
     total += li;
     for (;;) {
       uint32_t old = idx_cas(&tab[sl], EMPTY, i);
       if (old == EMPTY) { distinct++; dbytes += li; break; }
-      if (h[old] == hi && len[old] == li) break;
+      if (h[old] == hi) break;  // both residues agree: equal strings (the byte offset +1 makes lengths agree too)
       sl = rep_next(sl, T);
     }
   }
@@ -205,11 +205,12 @@ struct RepArrays {
   // per-document working arrays (shared memory for tiers S/M, global work area for tier L)
   uint64_t* H;     // [cap] current n-gram key hash / paragraph hashes
   uint32_t* woff;  // [cap + 1] byte offsets of the words in their concatenation / paragraph lengths
+  uint32_t* flag;  // [cap / 32 + 1] top n-grams: positions whose n-gram repeats (the next level's candidates)
 };
 
 template <class G, class IdxT>
 TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t* te, const GrScratch& s, const GrCfg& cfg,
-                   int step, tb_gr_stats* out, int64_t d, RepArrays A, uint32_t* tab, IdxT* cnt) {
+                   int step, tb_gr_stats* out, int64_t d, RepArrays A, uint32_t* tab, IdxT* cnt, IdxT* list) {
   (void)te;
   const uint32_t EMPTY = 0xFFFFFFFFu;
   const GrDoc gd = s.doc[d];
@@ -281,45 +282,82 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
   }
   const uint64_t* wh = wh_g;  // read in place (coalesced, once per pass)
   const uint32_t* woff = A.woff;
-  // -- top n-grams: keys are the " "-joined strings (find_top_duplicate, text.rs:211-238)
-  for (uint32_t n = 1; n <= ntop_max; n++) {
-    const uint32_t cn = W - n + 1;
-    for (uint32_t i = g.tid; i < cn; i += g.size()) {
-      if (n == 1) { A.H[i] = wh[i]; continue; }
-      uint32_t j = i + n - 1;
-      Hash2 jj = tb_unpack(A.H[i]); jj.push(' ');
-      A.H[i] = tb_hcat(jj, tb_unpack(wh[j]), tb_pow_pack(a.uc.powtab, woff[j + 1] - woff[j])).pack();
-    }
-    g.sync();
-    for (int k = 0; k < cfg.n_top; k++) {
-      if (cfg.top_n[k] != n) continue;
-      const uint32_t T = rep_tab_size(cn);
+  // -- top n-grams: keys are the " "-joined strings (find_top_duplicate, text.rs:211-238).  A joined key
+  // determines its word sequence, so an n-gram that occurs twice has an (n-1)-gram prefix that occurs twice:
+  // after the first counted level only the positions whose n-gram repeated are extended and counted again.
+  {
+    const uint32_t fw = W / 32 + 1;
+    uint32_t count = W;     // positions still in play: all, or list[0 .. count)
+    bool pruned = false;
+    for (uint32_t n = 1; n <= ntop_max && count; n++) {
+      const uint32_t cn = W - n + 1;
+      for (uint32_t k = g.tid; k < count; k += g.size()) {
+        const uint32_t i = pruned ? (uint32_t)list[k] : k;
+        if (i >= cn) continue;
+        if (n == 1) { A.H[i] = wh[i]; continue; }
+        const uint32_t j = i + n - 1;
+        Hash2 jj = tb_unpack(A.H[i]); jj.push(' ');
+        A.H[i] = tb_hcat(jj, tb_unpack(wh[j]), tb_pow_pack(a.uc.powtab, woff[j + 1] - woff[j])).pack();
+      }
+      bool wanted = false;
+      for (int k = 0; k < cfg.n_top; k++) wanted |= cfg.top_n[k] == n;
+      if (!wanted) { g.sync(); continue; }
+      const uint32_t T = rep_tab_size(count);
       for (uint32_t i = g.tid; i < T; i += g.size()) tab[i] = EMPTY;
-      for (uint32_t i = g.tid; i < cn; i += g.size()) cnt[i] = 0;
+      for (uint32_t i = g.tid; i < fw; i += g.size()) A.flag[i] = 0;
+      for (uint32_t k = g.tid; k < count; k += g.size()) cnt[pruned ? (uint32_t)list[k] : k] = 0;
       g.sync();
-      for (uint32_t i = g.tid; i < cn; i += g.size()) {
-        // key length = concatenated bytes + (n - 1) spaces; equal joined strings <=> equal hash + length
-        uint32_t len = woff[i + n] - woff[i] + n - 1;
-        uint64_t key = A.H[i];
-        uint32_t sl = rep_slot(key, len, T);
+      bool hit = false;
+      for (uint32_t k = g.tid; k < count; k += g.size()) {
+        const uint32_t i = pruned ? (uint32_t)list[k] : k;
+        if (i >= cn) continue;
+        const uint64_t key = A.H[i];
+        uint32_t sl = rep_slot(key, T);
         for (;;) {
           uint32_t old = idx_cas(&tab[sl], EMPTY, i);
           if (old == EMPTY) { idx_inc(&cnt[i]); break; }
-          if (A.H[old] == key && woff[old + n] - woff[old] + n - 1 == len) { idx_inc(&cnt[old]); break; }
+          if (A.H[old] == key) {
+            idx_inc(&cnt[old]); hit = true;
+            simt_atomic_or(&A.flag[i >> 5], 1u << (i & 31)); simt_atomic_or(&A.flag[old >> 5], 1u << (old & 31));
+            break;
+          }
           sl = rep_next(sl, T);
         }
       }
       g.sync();
       uint64_t best = 0;
-      for (uint32_t i = g.tid; i < cn; i += g.size()) {
-        uint32_t c = cnt[i];
-        if (c) { uint64_t v = ((uint64_t)c << 32) | (woff[i + n] - woff[i] + n - 1); best = v > best ? v : best; }
+      const bool any_hit = g.any(hit);
+      if (any_hit) {
+        for (uint32_t k = g.tid; k < count; k += g.size()) {
+          const uint32_t i = pruned ? (uint32_t)list[k] : k;
+          if (i >= cn) continue;
+          const uint32_t c = cnt[i];
+          // key length = concatenated bytes + (n - 1) spaces
+          if (c > 1) { uint64_t v = ((uint64_t)c << 32) | (woff[i + n] - woff[i] + n - 1); best = v > best ? v : best; }
+        }
+        best = g.max64(best);
       }
-      best = g.max64(best);
-      uint32_t c = (uint32_t)(best >> 32), len = (uint32_t)best;
-      uint64_t v = c > 1 ? (uint64_t)len * c : 0;
-      st.top_bytes[k] = v;
-      if ((double)v / text_char_len > cfg.top_frac[k]) reasons |= 1u << (TB_GR_REASON_TOP_SHIFT + k);
+      {
+        const uint32_t c = (uint32_t)(best >> 32), len = (uint32_t)best;
+        const uint64_t v = c > 1 ? (uint64_t)len * c : 0;
+        for (int k = 0; k < cfg.n_top; k++) {
+          if (cfg.top_n[k] != n) continue;
+          st.top_bytes[k] = v;
+          if ((double)v / text_char_len > cfg.top_frac[k]) reasons |= 1u << (TB_GR_REASON_TOP_SHIFT + k);
+        }
+      }
+      // survivors: positions whose n-gram occurred at least twice, in order
+      uint32_t ncount = 0;
+      if (any_hit && n < ntop_max) {
+        for (uint32_t b0 = 0; b0 < cn; b0 += g.size()) {
+          const uint32_t i = b0 + g.tid;
+          const uint32_t is = (i < cn && ((A.flag[i >> 5] >> (i & 31)) & 1u)) ? 1u : 0u;
+          uint32_t tot, pre = g.exscan(is, &tot);
+          if (is) list[ncount + pre] = (IdxT)i;
+          ncount += tot;
+        }
+      }
+      count = ncount; pruned = true;
       g.sync();
     }
   }
@@ -338,30 +376,21 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
       rep_fill(g, tab, T, EMPTY);
       bool dup = false;
       for (uint32_t i = g.tid; i < cn; i += g.size()) {
-        uint32_t len = woff[i + n] - woff[i];
-        uint64_t key = A.H[i];
-        uint32_t sl = rep_slot(key, len, T);
+        const uint64_t key = A.H[i];
+        uint32_t sl = rep_slot(key, T);
         for (;;) {
           uint32_t old = idx_cas(&tab[sl], EMPTY, i);
           if (old == EMPTY) break;
-          if (A.H[old] == key && woff[old + n] - woff[old] == len) { idx_min(&tab[sl], i); dup = true; break; }
+          if (A.H[old] == key) { idx_min(&tab[sl], i); dup = true; break; }
           sl = rep_next(sl, T);
         }
+        cnt[i] = (IdxT)sl;  // the slot of this key; resolved to its first position below
       }
       g.sync();
       uint64_t v = 0;
       if (g.any(dup)) {
-        // fo[i] = smallest position carrying the same key (re-probe: the slot of an existing key is stable)
-        for (uint32_t i = g.tid; i < cn; i += g.size()) {
-          uint32_t len = woff[i + n] - woff[i];
-          uint64_t key = A.H[i];
-          uint32_t sl = rep_slot(key, len, T);
-          for (;;) {
-            uint32_t old = tab[sl];
-            if (A.H[old] == key && woff[old + n] - woff[old] == len) { cnt[i] = (IdxT)old; break; }
-            sl = rep_next(sl, T);
-          }
-        }
+        // fo[i] = smallest position carrying the same key
+        for (uint32_t i = g.tid; i < cn; i += g.size()) cnt[i] = (IdxT)tab[cnt[i]];
         g.sync();
         v = rep_dup_walk(g, cnt, tab, woff, cn, n);  // the table is dead now: reuse it for the candidate list
       }
