@@ -64,7 +64,7 @@ TB_D void body_validate_utf8(const uint8_t* t, const int64_t* rs, const int64_t*
 // ---------------------------------------------------------------------------------------------
 // GopherQualityFilter: one pass, then the threshold checks of gopher_quality.rs:198-295
 // ---------------------------------------------------------------------------------------------
-TB_D void gq_doc_walk(const Classifier& C, const TextRange& R, const SwTable& sw, GqAcc& acc, int lane) {
+TB_D_NOINLINE void gq_doc_walk(const Classifier& C, const TextRange& R, const SwTable& sw, GqAcc& acc, int lane) {
   for (int64_t base = R.rs; base < R.re; base += TB_TILE) {
     int64_t p0 = base + lane * TB_STRETCH;
     if (p0 < R.re) { int64_t p1 = p0 + TB_STRETCH < R.re ? p0 + TB_STRETCH : R.re; gq_lane(C, R, sw, p0, p1, acc); }
@@ -139,7 +139,7 @@ TB_D uint64_t hl_pack(HL v) { return ((uint64_t)tb_canon31(v.a) << 32) | tb_cano
 struct GrTotals { uint32_t W, NL, flags; uint64_t nchars; };
 
 // general path: segment-walking lanes (tb_lanes.cuh)
-TB_D void gr_doc_walk(const KBatch& a, const Classifier& C, const TextRange& R, const GrScratch& s, int64_t d, int lane,
+TB_D_NOINLINE void gr_doc_walk(const KBatch& a, const Classifier& C, const TextRange& R, const GrScratch& s, int64_t d, int lane,
                       GrTotals& out) {
   const uint64_t ub = (uint64_t)(R.rs >> 1) + (uint64_t)d;
   uint64_t* wh = s.wh + ub; uint32_t* wl = s.wl + ub;
@@ -283,7 +283,7 @@ TB_D void body_gr_rep_l(const KBatch& a, uint64_t* red, const int64_t* ts, const
 #define TB_STAGE_BYTES (TB_TILE + 64)  // per-warp staging buffer of the compacting stores (tile_store_kept)
 TB_D void c4a_doc_tiles(const KBatch& a, const LutEntry* lut, uint8_t* stage, const Classifier& C, const C4Cfg& cfg, const C4Scratch& s,
                         const TextRange& R, int64_t d, int lane);
-TB_D void c4a_doc_walk(const KBatch& a, const Classifier& C, const C4Cfg& cfg, const C4Scratch& s, const TextRange& R, int64_t d, int lane);
+TB_D_NOINLINE void c4a_doc_walk(const KBatch& a, const Classifier& C, const C4Cfg& cfg, const C4Scratch& s, const TextRange& R, int64_t d, int lane);
 TB_D void body_c4_a(const KBatch& a, const uint16_t* s_ascii, const LutEntry* lut, uint8_t* stage, const C4Cfg& cfg, const C4Scratch& s,
                     int64_t d, int lane) {
   Classifier C{s_ascii, a.uc};
@@ -291,7 +291,7 @@ TB_D void body_c4_a(const KBatch& a, const uint16_t* s_ascii, const LutEntry* lu
   if (a.dbg & TB_DBG_FORCE_WALK) { c4a_doc_walk(a, C, cfg, s, R, d, lane); TBE_COUNT(tbe_stat_walk, lane); }
   else { c4a_doc_tiles(a, lut, stage, C, cfg, s, R, d, lane); TBE_COUNT(tbe_stat_tiles, lane); }
 }
-TB_D void c4a_doc_walk(const KBatch& a, const Classifier& C, const C4Cfg& cfg, const C4Scratch& s, const TextRange& R, int64_t d, int lane) {
+TB_D_NOINLINE void c4a_doc_walk(const KBatch& a, const Classifier& C, const C4Cfg& cfg, const C4Scratch& s, const TextRange& R, int64_t d, int lane) {
   uint8_t* out = s.P + R.rs;
   const uint64_t lb = (uint64_t)R.rs + (uint64_t)d;
   uint32_t flags = 0, nl = 0;
@@ -340,7 +340,7 @@ struct C4bSink {  // words arrive in text order: aggregate per line in registers
     cnt++; mx = w.nchars > mx ? w.nchars : mx;
   }
 };
-TB_D void c4b_doc_walk(const Classifier& C, const C4Cfg& cfg, const C4Scratch& s, const TextRange& R, uint64_t lb, int lane) {
+TB_D_NOINLINE void c4b_doc_walk(const Classifier& C, const C4Cfg& cfg, const C4Scratch& s, const TextRange& R, uint64_t lb, int lane) {
   const uint8_t* t = R.t;
   uint32_t nl = 0;
   for (int64_t base = R.rs; base < R.re; base += TB_TILE) {

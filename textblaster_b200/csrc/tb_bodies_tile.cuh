@@ -25,7 +25,7 @@ TB_D Frag frag_scan(Frag tail, uint32_t f, int lane, Frag& carry) {
 // GopherQualityFilter (gopher_quality.rs:73-187)
 // ---------------------------------------------------------------------------------------------
 // is the word [s, e) a stop word?  (:184-187: stop_words.contains(&word.to_lowercase()))
-TB_D bool gq_is_stop_word(const Classifier& C, const uint8_t* t, const SwTable& sw, int64_t s, int64_t e, bool pure_ascii) {
+TB_D_NOINLINE bool gq_is_stop_word(const Classifier& C, const uint8_t* t, const SwTable& sw, int64_t s, int64_t e, bool pure_ascii) {
   const uint64_t len = (uint64_t)(e - s);
   if (pure_ascii) {
     if (len > sw.maxlen || !((sw.lenmask >> (len < 31u ? (uint32_t)len : 31u)) & 1u)) return false;
@@ -290,21 +290,39 @@ TB_D bool gr_doc_tiles(const KBatch& a, const LutEntry* lut, uint32_t* stage, co
     uint32_t wa = 0, wb = 0, wn = 0, la = 0, lb_ = 0, ln = 0;
     uint32_t hwa = 0, hwb = 0, hwn = 0, hla = 0, hlb = 0, hln = 0;
     uint32_t widx = wpre + first_word, lidx = NLc + lpre + first_piece;  // widx: slot in the tile's staging arrays
+    // (eight rounds of four bytes; the words and masks rotate so that the round body is one piece of code)
+    {
+      uint32_t wq[8];
 #pragma unroll
-    for (int i = 0; i < 32; i++) {
-      const uint32_t byte = (T.w[i >> 2] >> (8 * (i & 3))) & 0xFFu;
-      if ((B >> i) & 1u) {
-        if (i == fb) { hwa = wa; hwb = wb; hwn = wn; }
-        else if ((WEin >> i) & 1u) { st_a[widx] = wa; st_b[widx] = wb; st_n[widx] = wn; widx++; }
-        wa = 0; wb = 0; wn = 0;
-      }
-      wa = tb_hpush(wa, TB_B1, byte + 1u); wb = tb_hpush(wb, TB_B2, byte + 1u); wn++;
-      if ((NLx >> i) & 1u) {
-        if (i == fn) { hla = la; hlb = lb_; hln = ln; }
-        else if (ln) { lh[lidx] = hl_pack(hl_fold(la, lb_, ln)); ll[lidx] = ln; lg[lidx] = (uint8_t)gr_gap2(R, p0 + i - (int64_t)ln); lidx++; }
-        la = 0; lb_ = 0; ln = 0;
-      } else {
-        la = tb_hpush(la, TB_B1, byte + 1u); lb_ = tb_hpush(lb_, TB_B2, byte + 1u); ln++;
+      for (int k = 0; k < 8; k++) wq[k] = T.w[k];
+      uint32_t Bq = B, WEq = WEin, NLq = NLx;
+      int fbq = fb, fnq = fn;
+#pragma unroll 1
+      for (int k = 0; k < 8; k++) {
+        const uint32_t x = wq[0];
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+          const uint32_t byte = (x >> (8 * j)) & 0xFFu;
+          if ((Bq >> j) & 1u) {
+            if (j == fbq) { hwa = wa; hwb = wb; hwn = wn; }
+            else if ((WEq >> j) & 1u) { st_a[widx] = wa; st_b[widx] = wb; st_n[widx] = wn; widx++; }
+            wa = 0; wb = 0; wn = 0;
+          }
+          wa = tb_hpush(wa, TB_B1, byte + 1u); wb = tb_hpush(wb, TB_B2, byte + 1u); wn++;
+          if ((NLq >> j) & 1u) {
+            if (j == fnq) { hla = la; hlb = lb_; hln = ln; }
+            else if (ln) {
+              lh[lidx] = hl_pack(hl_fold(la, lb_, ln)); ll[lidx] = ln; lg[lidx] = (uint8_t)gr_gap2(R, p0 + 4 * k + j - (int64_t)ln);
+              lidx++;
+            }
+            la = 0; lb_ = 0; ln = 0;
+          } else {
+            la = tb_hpush(la, TB_B1, byte + 1u); lb_ = tb_hpush(lb_, TB_B2, byte + 1u); ln++;
+          }
+        }
+#pragma unroll
+        for (int q = 0; q < 7; q++) wq[q] = wq[q + 1];
+        Bq >>= 4; WEq >>= 4; NLq >>= 4; fbq -= 4; fnq -= 4;
       }
     }
     // ---- words: hash of the fragment open at the start of the stretch

@@ -8,9 +8,13 @@
 #if defined(__CUDACC__)
 #define TB_HD __host__ __device__ __forceinline__
 #define TB_D __device__ __forceinline__
+#define TB_HD_NOINLINE static __host__ __device__ __noinline__
+#define TB_D_NOINLINE static __device__ __noinline__
 #else
 #define TB_HD inline
 #define TB_D inline
+#define TB_HD_NOINLINE inline
+#define TB_D_NOINLINE inline
 #endif
 
 // ---- cinfo bit layout (tools/gen_unicode_tables.py) ------------------------------------------

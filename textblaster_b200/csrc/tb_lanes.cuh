@@ -58,7 +58,7 @@ struct GqSink {
 
 // line.trim_end().ends_with("...") || ends_with("…") for the line that ends at e (position of its
 // '\n', or re).  gopher_quality.rs:152-158
-TB_HD bool gq_line_ends_with_ellipsis(const Classifier& C, const TextRange& R, int64_t e) {
+TB_HD_NOINLINE bool gq_line_ends_with_ellipsis(const Classifier& C, const TextRange& R, int64_t e) {
   const uint8_t* t = R.t;
   int64_t j = e;
   while (j > R.rs) {
@@ -74,7 +74,7 @@ TB_HD bool gq_line_ends_with_ellipsis(const Classifier& C, const TextRange& R, i
   return (a == '.' && b == '.' && c == '.') || (a == 0xE2 && b == 0x80 && c == 0xA6);
 }
 // line.trim_start().starts_with('•') || starts_with('-') for the line starting at s.  :134-141
-TB_HD bool gq_line_is_bullet(const Classifier& C, const TextRange& R, int64_t s) {
+TB_HD_NOINLINE bool gq_line_is_bullet(const Classifier& C, const TextRange& R, int64_t s) {
   const uint8_t* t = R.t;
   int64_t j = s;
   while (j < R.re) {
@@ -168,7 +168,7 @@ TB_HD uint32_t gr_gap2(const TextRange& R, int64_t s) {
 // case-folded compare against an ASCII lower-case pattern, as `s.to_lowercase().contains(pat)`
 // sees it: A-Z fold to a-z and U+212A KELVIN SIGN lower-cases to 'k'; no other character
 // lower-cases to an ASCII letter (U+0130 gives "i" + U+0307, which can never complete a pattern).
-TB_HD bool c4_fold_match(const uint8_t* t, int64_t i, int64_t re, const char* pat, int n) {
+TB_HD_NOINLINE bool c4_fold_match(const uint8_t* t, int64_t i, int64_t re, const char* pat, int n) {
   int64_t j = i;
   for (int k = 0; k < n; k++) {
     if (j >= re) return false;
@@ -183,7 +183,7 @@ TB_HD bool c4_fold_match(const uint8_t* t, int64_t i, int64_t re, const char* pa
 
 // CITATION_REGEX \[\d+(?:,\s*\d+)*\] anchored at the '[' at i; returns the end or -1.  The
 // reference applies it per line, so '\n' never matches \s here.  c4_filters.rs:33,195-199
-TB_HD int64_t c4_citation_end(const Classifier& C, const TextRange& R, int64_t i) {
+TB_HD_NOINLINE int64_t c4_citation_end(const Classifier& C, const TextRange& R, int64_t i) {
   const uint8_t* t = R.t;
   int64_t j = i + 1;
   int len; uint32_t cp;
@@ -297,7 +297,7 @@ TB_HD void c4a_lane(const Classifier& C, const TextRange& R, int64_t p0, int64_t
 #define C4L_POLICY 8u   // contains a POLICY_SUBSTRINGS entry (:24-31,248)
 
 // flags for the line that ends at e (exclusive), looking only at its last bytes
-TB_HD uint32_t c4_line_end_flags(const Classifier& C, const TextRange& R, int64_t e) {
+TB_HD_NOINLINE uint32_t c4_line_end_flags(const Classifier& C, const TextRange& R, int64_t e) {
   const uint8_t* t = R.t;
   if (e <= R.rs || tb_byte(t, e - 1) == '\n') return 0;  // empty line
   int64_t k = C.prev_lead(t, e, R.rs);
@@ -309,7 +309,7 @@ TB_HD uint32_t c4_line_end_flags(const Classifier& C, const TextRange& R, int64_
   return f;
 }
 // javascript / policy substrings starting at byte i (lower-cased compare)
-TB_HD uint32_t c4_pattern_flags(const uint8_t* t, int64_t i, int64_t re, uint32_t b, bool js, bool policy) {
+TB_HD_NOINLINE uint32_t c4_pattern_flags(const uint8_t* t, int64_t i, int64_t re, uint32_t b, bool js, bool policy) {
   uint32_t fb = b | 0x20u;
   // cheap reject: only j / t / p / c / u can start a pattern, and the next two bytes must continue it
   // ("jav", "ter", "pri", "coo", "use"); the exact (Kelvin-sign aware) compare runs on the few survivors

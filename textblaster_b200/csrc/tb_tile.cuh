@@ -349,48 +349,52 @@ TB_HD void tile_classify(const LutEntry* lut, const TextRange& R, int64_t ext_lo
 #undef TILE_SHR1
 }
 
-// Decisions and character classes of the dirty positions, from the rule machine.  Returns TILE_EXOTIC and/or
-// CI_COMPLEX (a character of a dictionary-segmented script was seen).
-TB_HD uint32_t tile_fix_dirty(const Classifier& C, const TextRange& R, Tile& T) {
+// Decisions and character classes of the dirty positions, from the rule machine (out of line: the rule
+// machine is large and most stretches never need it).  fl: TILE_EXOTIC and/or CI_COMPLEX (a character of a
+// dictionary-segmented script was seen).
+struct DirtyFix { uint32_t span, brk, wc, al, fl; };  // span: positions decided; brk / wc / al: their bits
+TB_HD_NOINLINE void tile_dirty_bits(const Classifier& C, const TextRange& R, int64_t p0, uint32_t dirty, DirtyFix& o) {
   const uint8_t* t = R.t;
-  uint32_t dm = T.dirty, fl = 0;
+  uint32_t dm = dirty;
+  o.span = dirty; o.brk = 0; o.wc = 0; o.al = 0; o.fl = 0;
   while (dm) {
     const int s = tb_ctz32(dm);
     int hi = s + tb_ctz32(~(dm >> s));
     if (hi > 32) hi = 32;
-    const uint32_t span = tb_below(hi) & ~tb_below(s);
-    dm &= ~span;
-    int64_t q = T.p0 + s;
-    const int64_t q1 = T.p0 + hi;
+    dm &= ~(tb_below(hi) & ~tb_below(s));
+    int64_t q = p0 + s;
+    const int64_t q1 = p0 + hi;
     while (q < q1 && q > R.rs && tb_is_cont(tb_byte(t, q))) q++;
-    uint32_t bb = 0, wc = 0, al = 0;
-    if (q < q1) {
-      WbState st;
-      wb_sync(C, R, q, st);
-      uint32_t prev_ws = 0;
-      if (q > R.rs) { int64_t k = C.prev_lead(t, q, R.rs); int l0; uint32_t c0; prev_ws = C.at(t, k, &l0, &c0) & CI_WS; }
-      int64_t i = q;
-      while (i < q1) {
-        int len; uint32_t cp;
-        const uint32_t ci = C.at(t, i, &len, &cp), cls = CI_WB(ci);
-        const uint32_t bit = 1u << (uint32_t)(i - T.p0);
-        if (wb_break_before(C, R, st, cls, ci, i, len)) bb |= bit;
-        else if ((ci & CI_WS) != prev_ws) fl |= TILE_EXOTIC;
-        if (cp >= 0x80u) {
-          if (!(ci & (CI_PUNCT | CI_WS))) wc |= bit;
-          if (ci & CI_ALPHA) al |= bit;
-          fl |= ci & CI_COMPLEX;
-        }
-        prev_ws = ci & CI_WS;
-        wb_advance(st, cls);
-        i += len;
+    if (q >= q1) continue;
+    WbState st;
+    wb_sync(C, R, q, st);
+    uint32_t prev_ws = 0;
+    if (q > R.rs) { int64_t k = C.prev_lead(t, q, R.rs); int l0; uint32_t c0; prev_ws = C.at(t, k, &l0, &c0) & CI_WS; }
+    int64_t i = q;
+    while (i < q1) {
+      int len; uint32_t cp;
+      const uint32_t ci = C.at(t, i, &len, &cp), cls = CI_WB(ci);
+      const uint32_t bit = 1u << (uint32_t)(i - p0);
+      if (wb_break_before(C, R, st, cls, ci, i, len)) o.brk |= bit;
+      else if ((ci & CI_WS) != prev_ws) o.fl |= TILE_EXOTIC;
+      if (cp >= 0x80u) {
+        if (!(ci & (CI_PUNCT | CI_WS))) o.wc |= bit;
+        if (ci & CI_ALPHA) o.al |= bit;
+        o.fl |= ci & CI_COMPLEX;
       }
+      prev_ws = ci & CI_WS;
+      wb_advance(st, cls);
+      i += len;
     }
-    T.brk = (T.brk & ~span) | bb;
-    T.m[TL_WC] |= wc;
-    T.al |= al;
   }
-  return fl;
+}
+TB_HD uint32_t tile_fix_dirty(const Classifier& C, const TextRange& R, Tile& T) {
+  DirtyFix f;
+  tile_dirty_bits(C, R, T.p0, T.dirty, f);
+  T.brk = (T.brk & ~f.span) | f.brk;
+  T.m[TL_WC] |= f.wc;
+  T.al |= f.al;
+  return f.fl;
 }
 
 // ---- open-fragment summaries (segments that cross stretch boundaries) ------------------------------

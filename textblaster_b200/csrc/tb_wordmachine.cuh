@@ -146,7 +146,7 @@ TB_HD void lowkey_push(const Classifier& C, LowKey& k, uint32_t cp, uint32_t ci)
 
 // Exact to_lowercase() of the word [start, end) including the Final_Sigma condition
 // (alloc::str::to_lowercase / map_uppercase_sigma).  Slow path: only words containing U+03A3.
-TB_HD void lowkey_slow(const Classifier& C, const uint8_t* t, int64_t start, int64_t end, LowKey& k) {
+TB_HD_NOINLINE void lowkey_slow(const Classifier& C, const uint8_t* t, int64_t start, int64_t end, LowKey& k) {
   k.init();
   int64_t i = start;
   while (i < end) {
