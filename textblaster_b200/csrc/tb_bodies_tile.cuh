@@ -34,9 +34,18 @@ TB_D_NOINLINE bool gq_is_stop_word(const Classifier& C, const uint8_t* t, const 
   }
   LowKey k; k.init();
   if (pure_ascii && len <= 8) {  // the common case: the key is the lower-cased word itself
-    uint64_t lo = 0;
-    for (uint32_t j = 0; j < (uint32_t)len; j++) { uint32_t b = tb_byte(t, s + j); b = (b - 'A') < 26u ? b + 32u : b; lo |= (uint64_t)b << (8u * j); }
-    k.lo = lo; k.len = (uint32_t)len;
+    // eight bytes from the word's start (three aligned loads, realigned), cut to its length, A-Z folded in place
+    const uintptr_t addr = (uintptr_t)(t + s);
+    const uint32_t* q = (const uint32_t*)(addr & ~(uintptr_t)3);
+    const uint32_t mis = (uint32_t)(addr & 3u), l = (uint32_t)len;
+    uint32_t w0 = TB_LDG(q), w1 = l + mis > 4u ? TB_LDG(q + 1) : 0u, w2 = l + mis > 8u ? TB_LDG(q + 2) : 0u;
+    uint32_t lo = mis ? tb_funnel_r(w0, w1, mis) : w0, hi = mis ? tb_funnel_r(w1, w2, mis) : w1;
+    if (l < 4u) { lo &= (1u << (8u * l)) - 1u; hi = 0u; }
+    else if (l == 4u) hi = 0u;
+    else if (l < 8u) hi &= (1u << (8u * (l - 4u))) - 1u;
+    lo |= (((lo + 0x3F3F3F3Fu) & ~(lo + 0x25252525u)) & 0x80808080u) >> 2;  // bytes are ASCII: no carries between them
+    hi |= (((hi + 0x3F3F3F3Fu) & ~(hi + 0x25252525u)) & 0x80808080u) >> 2;
+    k.lo = ((uint64_t)hi << 32) | lo; k.len = l;
     return sw_lookup(sw, k);
   }
   int64_t i = s;

@@ -23,10 +23,9 @@ struct SwTable {
 TB_HD uint32_t sw_first_bit(uint32_t b) { uint32_t f = (b | 0x20u) - 'a'; return f < 26u ? (1u << f) : (1u << 26); }
 
 TB_HD uint64_t sw_slot_hash(uint64_t lo, uint64_t hi, uint64_t ext, uint32_t len) {
-  uint32_t h = (uint32_t)lo * 0x9E3779B1u ^ (uint32_t)(lo >> 32) * 0x85EBCA77u ^ (uint32_t)hi * 0xC2B2AE3Du ^
-               (uint32_t)(hi >> 32) * 0x27D4EB2Fu ^ (uint32_t)ext ^ (len * 0x165667B1u);
-  h ^= h >> 15; h *= 0x2C1B3C6Du; h ^= h >> 13;
-  return h;
+  uint64_t x = lo ^ (hi * 0x9E3779B97F4A7C15ull) ^ (ext * 0xC2B2AE3D27D4EB4Full) ^ len;
+  uint32_t h = ((uint32_t)x ^ (uint32_t)(x >> 32)) * 0x9E3779B1u;
+  return h ^ (h >> 15);
 }
 TB_HD bool sw_lookup(const SwTable& sw, const LowKey& k) {
   if (k.len == 0 || k.len > sw.maxlen) return false;
