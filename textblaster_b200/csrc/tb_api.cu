@@ -123,7 +123,8 @@ struct KTime { const char* name; double ms; int64_t launches; };
 
 struct tb_ctx {
   int device = 0, sm_count = 148;
-  cudaStream_t compute = nullptr, copy = nullptr, d2h = nullptr;
+  cudaStream_t compute = nullptr, copy = nullptr, d2h = nullptr, side = nullptr;
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   UcTables uc{};
   DevBuf t_stage1, t_stage2, t_lower, t_cased, t_caseign, t_pow;
 };
@@ -289,7 +290,7 @@ int ensure_chunk_buffers(tb_pipeline* p, int64_t n, int64_t nb, bool host_input)
       ENS(p->g_wh, units * 8); ENS(p->g_wl, units * 4); ENS(p->g_lh, units * 8); ENS(p->g_ll, units * 4); ENS(p->g_lg, units);
       ENS(p->g_doc, n1 * sizeof(GrDoc));
       ENS(p->g_work, (units * TB_REP_K + n1 * TB_REP_DOC_EXTRA) * 4);
-      ENS(p->g_lists, 3 * n1 * 4); ENS(p->g_counters, 64);
+      ENS(p->g_lists, 4 * n1 * 4); ENS(p->g_counters, 64);
     } else if (sh.type == TB_STEP_C4_QUALITY) {
       size_t lines = (size_t)nb + n1 + 1;
       ENS(p->c_P, (size_t)nb + 64); ENS(p->c_F, (size_t)nb + 64);
@@ -328,12 +329,19 @@ int enqueue_chain(tb_pipeline* p, const uint8_t* text, int64_t n, int64_t nbytes
       GrScratch g{p->g_wh.as<uint64_t>(), p->g_wl.as<uint32_t>(), p->g_lh.as<uint64_t>(), p->g_ll.as<uint32_t>(),
                   p->g_lg.as<uint8_t>(), p->g_doc.as<GrDoc>(), p->g_work.as<uint32_t>(), p->g_lists.as<uint32_t>(),
                   p->g_counters.as<uint32_t>(), n};
-      CK(cudaMemsetAsync(p->g_counters.p, 0, 32, st));
+      CK(cudaMemsetAsync(p->g_counters.p, 0, 64, st));
       { Timed t(p, "k_trim"); tb_launch_trim(st, b, p->ts.as<int64_t>(), p->te.as<int64_t>()); }
       { Timed t(p, "k_gr_scan"); tb_launch_gr_scan(st, b, p->ts.as<int64_t>(), p->te.as<int64_t>(), g, c->sm_count); }
+      // the few documents of tier X (each a long chain of passes on one CTA) run beside the other tiers
+      CK(cudaEventRecord(c->ev_fork, st));
+      CK(cudaStreamWaitEvent(c->side, c->ev_fork, 0));
+      tb_launch_gr_rep(c->side, b, p->ts.as<int64_t>(), p->te.as<int64_t>(), g, sh.gr, (int)s, p->stats[s].as<tb_gr_stats>(), c->sm_count, 3);
+      CK(cudaEventRecord(c->ev_join, c->side));
+      p->launches_this_run++;
       { Timed t(p, "k_gr_rep_s"); tb_launch_gr_rep(st, b, p->ts.as<int64_t>(), p->te.as<int64_t>(), g, sh.gr, (int)s, p->stats[s].as<tb_gr_stats>(), c->sm_count, 0); }
       { Timed t(p, "k_gr_rep_m"); tb_launch_gr_rep(st, b, p->ts.as<int64_t>(), p->te.as<int64_t>(), g, sh.gr, (int)s, p->stats[s].as<tb_gr_stats>(), c->sm_count, 1); }
       { Timed t(p, "k_gr_rep_l"); tb_launch_gr_rep(st, b, p->ts.as<int64_t>(), p->te.as<int64_t>(), g, sh.gr, (int)s, p->stats[s].as<tb_gr_stats>(), c->sm_count, 2); }
+      { Timed t(p, "k_gr_rep_x(join)"); CK(cudaStreamWaitEvent(st, c->ev_join, 0)); }
     } else {
       C4Scratch cs{p->c_P.as<uint8_t>(), p->c_F.as<uint8_t>(), p->c_plen.as<int64_t>(), p->c_nlines.as<uint32_t>(),
                    p->c_docflags.as<uint32_t>(), p->c_lwc.as<uint32_t>(), p->c_lmax.as<uint32_t>(), p->c_lflags.as<uint32_t>(),
@@ -499,6 +507,9 @@ int tb_ctx_create(int device, tb_ctx** out) {
   CK(cudaStreamCreateWithFlags(&c->compute, cudaStreamNonBlocking));
   CK(cudaStreamCreateWithFlags(&c->copy, cudaStreamNonBlocking));
   CK(cudaStreamCreateWithFlags(&c->d2h, cudaStreamNonBlocking));
+  CK(cudaStreamCreateWithFlags(&c->side, cudaStreamNonBlocking));
+  CK(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
+  CK(cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming));
   int rc;
   if ((rc = upload(c->t_stage1, tb_uc_stage1, sizeof tb_uc_stage1)) || (rc = upload(c->t_stage2, tb_uc_stage2, sizeof tb_uc_stage2)) ||
       (rc = upload(c->t_lower, tb_uc_lower, sizeof tb_uc_lower)) || (rc = upload(c->t_cased, tb_uc_cased, sizeof tb_uc_cased)) ||
@@ -521,6 +532,9 @@ void tb_ctx_destroy(tb_ctx* c) {
   if (c->compute) cudaStreamDestroy(c->compute);
   if (c->copy) cudaStreamDestroy(c->copy);
   if (c->d2h) cudaStreamDestroy(c->d2h);
+  if (c->side) cudaStreamDestroy(c->side);
+  if (c->ev_fork) cudaEventDestroy(c->ev_fork);
+  if (c->ev_join) cudaEventDestroy(c->ev_join);
   delete c;
 }
 

@@ -218,7 +218,7 @@ TB_D void body_gr_scan(const KBatch& a, const uint16_t* s_ascii, const LutEntry*
     GrDoc g; g.char_len = nchars; g.W = W; g.NL = NL; g.flags = flags ? TB_DOCFLAG_COMPLEX_SCRIPT : 0; g.empty = (R.re <= R.rs);
     s.doc[d] = g;
     uint32_t big = W > NL ? W : NL;
-    uint32_t tier = big <= TB_REP_S_CAP ? 0u : big <= TB_REP_M_CAP ? 1u : 2u;
+    uint32_t tier = big <= TB_REP_S_CAP ? 0u : big <= TB_REP_M_CAP ? 1u : big <= TB_REP_L_CAP ? 2u : 3u;
     uint32_t k = simt_atomic_add(&s.counters[tier], 1u);
     s.lists[(uint64_t)tier * (uint64_t)s.n + k] = (uint32_t)d;
   }
@@ -231,6 +231,7 @@ TB_D void body_gr_scan(const KBatch& a, const uint16_t* s_ascii, const LutEntry*
 #define TB_REP_SMEM(CAP) ((CAP) * 8 + ((CAP) + 2) * 4 + 2 * (CAP) * 4 + ((CAP) / 32 + 2) * 4 + (CAP) * 2 + (CAP) * 2)
 #define TB_REP_S_SMEM TB_REP_SMEM(TB_REP_S_CAP)
 #define TB_REP_M_SMEM (TB_REP_SMEM(TB_REP_M_CAP) + 64 * 8)
+#define TB_REP_L_SMEM (TB_REP_SMEM(TB_REP_L_CAP) + 64 * 8)
 struct RepCarve { RepArrays A; uint32_t* tab; uint16_t* cnt; uint16_t* list; uint8_t* end; };
 TB_D RepCarve rep_carve(uint8_t* smem, uint32_t cap) {
   RepCarve c;
@@ -258,8 +259,15 @@ TB_D void body_gr_rep_m(const KBatch& a, uint8_t* smem, const int64_t* ts, const
   BlockGroup g{tid, (uint64_t*)(((uintptr_t)c.end + 7) & ~(uintptr_t)7)};
   rep_body<BlockGroup, uint16_t>(g, a, ts, te, s, cfg, step, out, d, c.A, c.tab, c.cnt, c.list);
 }
-// tier L: one CTA, working arrays in the document's region of the global work area; `red` = 64 u64 of shared scratch
-TB_D void body_gr_rep_l(const KBatch& a, uint64_t* red, const int64_t* ts, const int64_t* te, const GrScratch& s,
+// tier L: one large CTA, working arrays carved from `smem` (TB_REP_L_SMEM bytes: one CTA per SM)
+TB_D void body_gr_rep_l(const KBatch& a, uint8_t* smem, const int64_t* ts, const int64_t* te, const GrScratch& s,
+                        const GrCfg& cfg, int step, tb_gr_stats* out, int64_t d, int tid) {
+  RepCarve c = rep_carve(smem, TB_REP_L_CAP);
+  BlockGroup g{tid, (uint64_t*)(((uintptr_t)c.end + 7) & ~(uintptr_t)7)};
+  rep_body<BlockGroup, uint16_t>(g, a, ts, te, s, cfg, step, out, d, c.A, c.tab, c.cnt, c.list);
+}
+// tier X: one CTA, working arrays in the document's region of the global work area; `red` = 64 u64 of shared scratch
+TB_D void body_gr_rep_x(const KBatch& a, uint64_t* red, const int64_t* ts, const int64_t* te, const GrScratch& s,
                         const GrCfg& cfg, int step, tb_gr_stats* out, int64_t d, int tid) {
   const int64_t rs = ts[d], re = te[d];
   const uint64_t ub = (uint64_t)(rs >> 1) + (uint64_t)d;

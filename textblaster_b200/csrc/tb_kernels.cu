@@ -75,7 +75,7 @@ __global__ void __launch_bounds__(TB_BLOCK, 12) k_gr_scan(KBatch a, const int64_
   load_lut(s_lut, a.uc, TB_LUT_GR, 0u);
   __shared__ uint32_t s_stage[3 * TB_GR_STAGE_WORDS];
   for (;;) {
-    const int64_t d = next_doc(&s.counters[7]);
+    const int64_t d = next_doc(&s.counters[8]);
     if (d >= a.n) break;
     if (a.alive[d]) body_gr_scan(a, s_ascii, s_lut, s_stage, ts, te, s, d, threadIdx.x & 31);
   }
@@ -111,7 +111,7 @@ __global__ void __launch_bounds__(TB_REP_M_THREADS) k_gr_rep_m(KBatch a, const i
 }
 __global__ void __launch_bounds__(TB_REP_L_THREADS) k_gr_rep_l(KBatch a, const int64_t* ts, const int64_t* te, GrScratch s,
                                                                GrCfg cfg, int step, tb_gr_stats* out) {
-  __shared__ uint64_t s_red[64];
+  extern __shared__ __align__(16) uint8_t dsmem[];
   __shared__ uint32_t s_i;
   const uint32_t count = s.counters[2];
   for (;;) {
@@ -120,7 +120,21 @@ __global__ void __launch_bounds__(TB_REP_L_THREADS) k_gr_rep_l(KBatch a, const i
     __syncthreads();
     uint32_t i = s_i;
     if (i >= count) break;
-    body_gr_rep_l(a, s_red, ts, te, s, cfg, step, out, (int64_t)s.lists[2 * (uint64_t)s.n + i], (int)threadIdx.x);
+    body_gr_rep_l(a, dsmem, ts, te, s, cfg, step, out, (int64_t)s.lists[2 * (uint64_t)s.n + i], (int)threadIdx.x);
+  }
+}
+__global__ void __launch_bounds__(TB_REP_X_THREADS) k_gr_rep_x(KBatch a, const int64_t* ts, const int64_t* te, GrScratch s,
+                                                               GrCfg cfg, int step, tb_gr_stats* out) {
+  __shared__ uint64_t s_red[64];
+  __shared__ uint32_t s_i;
+  const uint32_t count = s.counters[3];
+  for (;;) {
+    __syncthreads();
+    if (threadIdx.x == 0) s_i = atomicAdd(&s.counters[7], 1u);
+    __syncthreads();
+    uint32_t i = s_i;
+    if (i >= count) break;
+    body_gr_rep_x(a, s_red, ts, te, s, cfg, step, out, (int64_t)s.lists[3 * (uint64_t)s.n + i], (int)threadIdx.x);
   }
 }
 __global__ void __launch_bounds__(TB_BLOCK, 12) k_c4_a(KBatch a, C4Cfg cfg, C4Scratch s, uint32_t* cursor) {
@@ -233,10 +247,13 @@ void tb_launch_gr_rep(cudaStream_t st, const KBatch& b, const int64_t* ts, const
   if (!b.n) return;
   if (tier == 0) k_gr_rep_s<<<sm_count * 20, 32, 0, st>>>(b, ts, te, s, cfg, step, out);
   else if (tier == 1) k_gr_rep_m<<<sm_count * 5, TB_REP_M_THREADS, TB_REP_M_SMEM, st>>>(b, ts, te, s, cfg, step, out);
-  else k_gr_rep_l<<<sm_count * 2, TB_REP_L_THREADS, 0, st>>>(b, ts, te, s, cfg, step, out);
+  else if (tier == 2) k_gr_rep_l<<<sm_count, TB_REP_L_THREADS, TB_REP_L_SMEM, st>>>(b, ts, te, s, cfg, step, out);
+  else k_gr_rep_x<<<sm_count, TB_REP_X_THREADS, 0, st>>>(b, ts, te, s, cfg, step, out);
 }
 int tb_kernels_init() {
-  return (int)cudaFuncSetAttribute(k_gr_rep_m, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TB_REP_M_SMEM);
+  cudaError_t e = cudaFuncSetAttribute(k_gr_rep_m, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TB_REP_M_SMEM);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(k_gr_rep_l, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TB_REP_L_SMEM);
+  return (int)e;
 }
 void tb_launch_c4_a(cudaStream_t st, const KBatch& b, const C4Cfg& cfg, const C4Scratch& s, int sm_count, uint32_t* cursor) {
   if (b.n) k_c4_a<<<persistent_grid(b.n, sm_count, 12), TB_BLOCK, 0, st>>>(b, cfg, s, cursor);

@@ -54,8 +54,8 @@ struct GrScratch {
   uint64_t* lh; uint32_t* ll; uint8_t* lg;  // line pieces: hash, byte length, "preceded by >= 2 newlines"
   GrDoc* doc;                               // [n]
   uint32_t* work;                           // tier-L work area, TB_REP_K words per unit + TB_REP_DOC_EXTRA per doc
-  uint32_t* lists;                          // [3][n] document ids per tier (S, M, L), filled by the scan pass
-  uint32_t* counters;                       // [8]: list lengths [0..2], work cursors [4..6], scan cursor [7]
+  uint32_t* lists;                          // [4][n] document ids per tier (S, M, L, X), filled by the scan pass
+  uint32_t* counters;                       // [16]: list lengths [0..3], work cursors [4..7], scan cursor [8]
   int64_t n;
 };
 #define TB_REP_K 8u           // tier-L words per unit: H[2U] woff[U+2] tab[2U+16] cnt[U] list[U] flag[U/32+1]
@@ -79,13 +79,13 @@ struct C4Scratch {
 
 void tb_launch_init_ranges(cudaStream_t st, const void* off, int off64, int64_t doc0, int64_t n, int64_t base,
                            int64_t* rs, int64_t* re, uint8_t* alive, int8_t* failed);
-// gq, gr_scan and c4_b run as persistent one-warp CTAs; `cursor` (gr_scan: s.counters[7]) must be zero at launch
+// gq, gr_scan and c4_b run as persistent one-warp CTAs; `cursor` (gr_scan: s.counters[8]) must be zero at launch
 void tb_launch_gq(cudaStream_t st, const KBatch& b, const SwTable& sw, const GqCfg& cfg, int step, tb_gq_stats* out,
                   int sm_count, uint32_t* cursor);
 void tb_launch_trim(cudaStream_t st, const KBatch& b, int64_t* ts, int64_t* te);
 void tb_launch_gr_scan(cudaStream_t st, const KBatch& b, const int64_t* ts, const int64_t* te, const GrScratch& s, int sm_count);
 void tb_launch_gr_rep(cudaStream_t st, const KBatch& b, const int64_t* ts, const int64_t* te, const GrScratch& s,
-                      const GrCfg& cfg, int step, tb_gr_stats* out, int sm_count, int tier);  // tier 0 S, 1 M, 2 L
+                      const GrCfg& cfg, int step, tb_gr_stats* out, int sm_count, int tier);  // tier 0 S, 1 M, 2 L, 3 X
 int tb_kernels_init();  // per-process function attributes (dynamic shared memory opt-in)
 void tb_launch_c4_a(cudaStream_t st, const KBatch& b, const C4Cfg& cfg, const C4Scratch& s, int sm_count, uint32_t* cursor);
 void tb_launch_c4_b(cudaStream_t st, const KBatch& b, const C4Cfg& cfg, const C4Scratch& s, int sm_count, uint32_t* cursor);

@@ -144,7 +144,7 @@ int tb_gopher_repetition_noalloc(const uint8_t* utf8_dev, const int64_t* offsets
   g.lh = (uint64_t*)carve(units * 8); g.ll = (uint32_t*)carve(units * 4); g.lg = (uint8_t*)carve(units);
   g.doc = (GrDoc*)carve(n1 * sizeof(GrDoc));
   g.work = (uint32_t*)carve((units * TB_REP_K + n1 * TB_REP_DOC_EXTRA) * 4);
-  g.lists = (uint32_t*)carve(3 * n1 * 4);
+  g.lists = (uint32_t*)carve(4 * n1 * 4);
   g.counters = (uint32_t*)carve(64);
   g.n = n_docs;
   if (off > TB_NOALLOC_SCRATCH_BYTES) return fail(TB_ERR_INVALID_ARGUMENT, "tb_gopher_repetition_noalloc: internal scratch budget exceeded");
@@ -162,7 +162,7 @@ int tb_gopher_repetition_noalloc(const uint8_t* utf8_dev, const int64_t* offsets
   KBatch b{utf8_dev, rs, re, keep_dev, failed, n_docs, st->uc, 0, n_bytes, 0u};
   tb_launch_trim(stream, b, ts, te);
   tb_launch_gr_scan(stream, b, ts, te, g, st->sm_count);
-  for (int tier = 0; tier < 3; tier++) tb_launch_gr_rep(stream, b, ts, te, g, cfg, 0, stats_dev, st->sm_count, tier);
+  for (int tier = 0; tier < 4; tier++) tb_launch_gr_rep(stream, b, ts, te, g, cfg, 0, stats_dev, st->sm_count, tier);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return fail(TB_ERR_CUDA, std::string("tb_gopher_repetition_noalloc: launch failed: ") + cudaGetErrorString(e));
   return TB_OK;

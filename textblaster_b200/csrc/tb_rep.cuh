@@ -2,7 +2,8 @@
 // duplicate n-grams of one document, written once against a "group" of cooperating threads:
 //   tier S  one warp  per document, working arrays in shared memory        (W, NL <= 512)
 //   tier M  one CTA   per document, working arrays in shared memory        (W, NL <= 2048)
-//   tier L  one CTA   per document, working arrays in the global work area (anything larger; L2 resident)
+//   tier L  one CTA   per document (one per SM), arrays in shared memory   (W, NL <= 8192)
+//   tier X  one CTA   per document, working arrays in the global work area (anything larger; L2 resident)
 // Replaces text.rs:197-259 as called from gopher_rep.rs:86-196.
 //
 // Open-addressing tables hold element indices; the keys live in the arrays (equality = 62-bit
@@ -15,8 +16,10 @@
 
 #define TB_REP_S_CAP 512u
 #define TB_REP_M_CAP 2048u
+#define TB_REP_L_CAP 8192u
 #define TB_REP_M_THREADS 256
-#define TB_REP_L_THREADS 512
+#define TB_REP_L_THREADS 1024
+#define TB_REP_X_THREADS 512
 
 // ---- thread groups ---------------------------------------------------------------------------
 struct WarpGroup {
@@ -33,50 +36,48 @@ struct WarpGroup {
 };
 
 #if !defined(TB_HOST_EMUL)
-// One CTA; `red` is shared scratch of at least (blockDim/32 + 2) u64.
+// One CTA; `red` is 64 u64 of shared scratch, used as two alternating halves so that a collective needs a
+// single barrier: a half is rewritten only after every thread has passed the barrier of the collective
+// that used the other half.
 struct BlockGroup {
   int tid;
   uint64_t* red;
+  mutable int phase = 0;
   TB_D int size() const { return (int)blockDim.x; }
   TB_D void sync() const { __syncthreads(); }
+  TB_D uint64_t* publish(uint64_t v) const {  // lane 0 of every warp posts v; returns the half holding the posts
+    uint64_t* r = red + 32 * phase;
+    phase ^= 1;
+    if ((tid & 31) == 0) r[tid >> 5] = v;
+    __syncthreads();
+    return r;
+  }
   TB_D uint64_t sum64(uint64_t v) const {
-    v = simt_sum64(v);
-    int w = tid >> 5, nw = (int)blockDim.x >> 5;
-    __syncthreads();
-    if ((tid & 31) == 0) red[w] = v;
-    __syncthreads();
-    uint64_t s = 0;
-    for (int i = 0; i < nw; i++) s += red[i];
-    return s;
+    const uint64_t* r = publish(simt_sum64(v));
+    const int lane = tid & 31, nw = (int)blockDim.x >> 5;
+    return simt_sum64(lane < nw ? r[lane] : 0ull);
   }
   TB_D uint32_t sum(uint32_t v) const { return (uint32_t)sum64(v); }
   TB_D uint64_t max64(uint64_t v) const {
-    v = simt_max64(v);
-    int w = tid >> 5, nw = (int)blockDim.x >> 5;
-    __syncthreads();
-    if ((tid & 31) == 0) red[w] = v;
-    __syncthreads();
-    uint64_t s = 0;
-    for (int i = 0; i < nw; i++) s = red[i] > s ? red[i] : s;
-    return s;
+    const uint64_t* r = publish(simt_max64(v));
+    const int lane = tid & 31, nw = (int)blockDim.x >> 5;
+    return simt_max64(lane < nw ? r[lane] : 0ull);
   }
   TB_D bool any(bool p) const { return __syncthreads_or(p ? 1 : 0) != 0; }
   TB_D uint32_t exscan(uint32_t v, uint32_t* total) const {
     uint32_t wt, pre = simt_exscan(v, tid & 31, &wt);
-    int w = tid >> 5, nw = (int)blockDim.x >> 5;
-    __syncthreads();
-    if ((tid & 31) == 0) red[w] = wt;
-    __syncthreads();
-    uint32_t base = 0, tot = 0;
-    for (int i = 0; i < nw; i++) { uint32_t x = (uint32_t)red[i]; if (i < w) base += x; tot += x; }
+    const uint64_t* r = publish(wt);
+    const int lane = tid & 31, w = tid >> 5, nw = (int)blockDim.x >> 5;
+    uint32_t tot, wpre = simt_exscan(lane < nw ? (uint32_t)r[lane] : 0u, lane, &tot);
     *total = tot;
-    return base + pre;
+    return simt_shfl(wpre, w) + pre;
   }
   TB_D uint32_t bcast(uint32_t v) const {
+    uint64_t* r = red + 32 * phase;
+    phase ^= 1;
+    if (tid == 0) r[0] = v;
     __syncthreads();
-    if (tid == 0) red[0] = v;
-    __syncthreads();
-    return (uint32_t)red[0];
+    return (uint32_t)r[0];
   }
 };
 #else
@@ -84,6 +85,7 @@ struct BlockGroup {
 struct BlockGroup {
   int tid;
   uint64_t* red;  // unused
+  mutable int phase = 0;
   TB_D int size() const { return simt_block->n; }
   TB_D void sync() const { simt_block->bar.arrive_and_wait(); }
   TB_D uint64_t sum64(uint64_t v) const {
@@ -265,8 +267,9 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
 
   // ---- n-grams (gopher_rep.rs:159-196)
   uint32_t ntop_max = 0, ndup_max = 0;
-  for (int k = 0; k < cfg.n_top; k++) ntop_max = cfg.top_n[k] > ntop_max ? cfg.top_n[k] : ntop_max;
-  for (int k = 0; k < cfg.n_dup; k++) ndup_max = cfg.dup_n[k] > ndup_max ? cfg.dup_n[k] : ndup_max;
+  uint64_t top_levels = 0, dup_levels = 0;  // bit n: some entry of the list asks for n-grams of n words (n <= TB_MAX_NGRAM_N)
+  for (int k = 0; k < cfg.n_top; k++) { ntop_max = cfg.top_n[k] > ntop_max ? cfg.top_n[k] : ntop_max; top_levels |= 1ull << cfg.top_n[k]; }
+  for (int k = 0; k < cfg.n_dup; k++) { ndup_max = cfg.dup_n[k] > ndup_max ? cfg.dup_n[k] : ndup_max; dup_levels |= 1ull << cfg.dup_n[k]; }
   if (ntop_max > W) ntop_max = W;
   if (ndup_max > W) ndup_max = W;
   if (ntop_max || ndup_max) {
@@ -299,9 +302,7 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
         Hash2 jj = tb_unpack(A.H[i]); jj.push(' ');
         A.H[i] = tb_hcat(jj, tb_unpack(wh[j]), tb_pow_pack(a.uc.powtab, woff[j + 1] - woff[j])).pack();
       }
-      bool wanted = false;
-      for (int k = 0; k < cfg.n_top; k++) wanted |= cfg.top_n[k] == n;
-      if (!wanted) { g.sync(); continue; }
+      if (!((top_levels >> n) & 1ull)) { g.sync(); continue; }
       const uint32_t T = rep_tab_size(count);
       for (uint32_t i = g.tid; i < T; i += g.size()) tab[i] = EMPTY;
       for (uint32_t i = g.tid; i < fw; i += g.size()) A.flag[i] = 0;
@@ -370,8 +371,7 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
       A.H[i] = tb_hcat(tb_unpack(A.H[i]), tb_unpack(wh[j]), tb_pow_pack(a.uc.powtab, woff[j + 1] - woff[j])).pack();
     }
     g.sync();
-    for (int k = 0; k < cfg.n_dup; k++) {
-      if (cfg.dup_n[k] != n) continue;
+    if ((dup_levels >> n) & 1ull) {
       const uint32_t T = rep_tab_size(cn);
       rep_fill(g, tab, T, EMPTY);
       bool dup = false;
@@ -395,8 +395,11 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
         v = rep_dup_walk(g, cnt, tab, woff, cn, n);  // the table is dead now: reuse it for the candidate list
       }
       if (g.tid == 0) {
-        st.dup_bytes[k] = v;
-        if ((double)v / text_char_len > cfg.dup_frac[k]) reasons |= 1u << (TB_GR_REASON_DUP_SHIFT + k);
+        for (int k = 0; k < cfg.n_dup; k++) {
+          if (cfg.dup_n[k] != n) continue;
+          st.dup_bytes[k] = v;
+          if ((double)v / text_char_len > cfg.dup_frac[k]) reasons |= 1u << (TB_GR_REASON_DUP_SHIFT + k);
+        }
       }
       g.sync();
     }
