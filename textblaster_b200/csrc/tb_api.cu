@@ -136,13 +136,14 @@ struct tb_pipeline {
   std::mutex mu;
   // device buffers (grow-only)
   DevBuf text[2], offs[2], packed[2];
-  DevBuf rs0, re0, rs, re, ts, te, alive, failed, rewritten, len, out_off, bad, cursors;
-  DevBuf stats[TB_MAX_STEPS];
+  DevBuf rs0, re0, rs, re, ts, te, rewritten, len, bad, cursors;
+  // per-chunk results, double-buffered: the copies to the host run beside the next chunk's kernels
+  DevBuf alive[2], failed[2], out_off[2], stats[TB_MAX_STEPS][2];
   // GopherRepetition scratch
   DevBuf g_wh, g_wl, g_lh, g_ll, g_lg, g_doc, g_work, g_lists, g_counters;
   // C4 scratch
   DevBuf c_P, c_F, c_plen, c_nlines, c_docflags, c_lwc, c_lmax, c_lflags, c_prs, c_pre, c_frs, c_fre, c_cnt;
-  cudaEvent_t ev_h2d[2] = {nullptr, nullptr}, ev_done[2] = {nullptr, nullptr}, ev_d2h[2] = {nullptr, nullptr};
+  cudaEvent_t ev_h2d[2] = {nullptr, nullptr}, ev_done[2] = {nullptr, nullptr}, ev_d2h[2] = {nullptr, nullptr}, ev_small[2] = {nullptr, nullptr};
   std::vector<ResultSet*> results;
   // kernel timing
   std::vector<cudaEvent_t> ev_pool;
@@ -281,11 +282,12 @@ int ensure_chunk_buffers(tb_pipeline* p, int64_t n, int64_t nb, bool host_input)
   if (host_input) { for (int i = 0; i < 2; i++) { ENS(p->text[i], (size_t)nb + 64); ENS(p->offs[i], n1 * 8); } }
   for (int i = 0; i < 2; i++) ENS(p->packed[i], (size_t)nb + 64);
   ENS(p->rs0, n1 * 8); ENS(p->re0, n1 * 8); ENS(p->rs, n1 * 8); ENS(p->re, n1 * 8); ENS(p->ts, n1 * 8); ENS(p->te, n1 * 8);
-  ENS(p->alive, n1); ENS(p->failed, n1); ENS(p->rewritten, n1); ENS(p->len, n1 * 8); ENS(p->out_off, (n1 + 1) * 8); ENS(p->bad, 16); ENS(p->cursors, 256);
+  for (int i = 0; i < 2; i++) { ENS(p->alive[i], n1); ENS(p->failed[i], n1); ENS(p->out_off[i], (n1 + 1) * 8); }
+  ENS(p->rewritten, n1); ENS(p->len, n1 * 8); ENS(p->bad, 16); ENS(p->cursors, 256);
   size_t units = (size_t)nb / 2 + n1 + 1;
   for (size_t s = 0; s < p->steps.size(); s++) {
     const StepHost& sh = p->steps[s];
-    ENS(p->stats[s], n1 * stat_size(sh.type));
+    for (int i = 0; i < 2; i++) ENS(p->stats[s][i], n1 * stat_size(sh.type));
     if (sh.type == TB_STEP_GOPHER_REPETITION) {
       ENS(p->g_wh, units * 8); ENS(p->g_wl, units * 4); ENS(p->g_lh, units * 8); ENS(p->g_ll, units * 4); ENS(p->g_lg, units);
       ENS(p->g_doc, n1 * sizeof(GrDoc));
@@ -312,19 +314,18 @@ int enqueue_chain(tb_pipeline* p, const uint8_t* text, int64_t n, int64_t nbytes
   CK(cudaMemcpyAsync(p->re.p, p->re0.p, (size_t)n * 8, cudaMemcpyDeviceToDevice, st));
   CK(cudaMemsetAsync(p->rewritten.p, 0, (size_t)n, st));
   CK(cudaMemsetAsync(p->cursors.p, 0, 256, st));
-  KBatch b{text, p->rs.as<int64_t>(), p->re.as<int64_t>(), p->alive.as<uint8_t>(), p->failed.as<int8_t>(), n, c->uc, 0, nbytes,
+  KBatch b{text, p->rs.as<int64_t>(), p->re.as<int64_t>(), p->alive[pb].as<uint8_t>(), p->failed[pb].as<int8_t>(), n, c->uc, 0, nbytes,
            (uint32_t)p->opt_debug};
   uint32_t* cursors = p->cursors.as<uint32_t>();
   *has_c4 = false;
-  if (p->opt_validate) {
-    CK(cudaMemsetAsync(p->bad.p, 0, 4, st));
+  if (p->opt_validate) {  // p->bad counts over the whole run (cleared by run_impl)
     { Timed t(p, "k_validate_utf8"); tb_launch_validate_utf8(st, text, b.rs, b.re, n, p->bad.as<int32_t>()); }
   }
   for (size_t s = 0; s < p->steps.size(); s++) {
     StepHost& sh = p->steps[s];
     if (sh.type == TB_STEP_GOPHER_QUALITY) {
       Timed t(p, "k_gq");
-      tb_launch_gq(st, b, sh.sw, sh.gq, (int)s, p->stats[s].as<tb_gq_stats>(), c->sm_count, cursors + s);
+      tb_launch_gq(st, b, sh.sw, sh.gq, (int)s, p->stats[s][pb].as<tb_gq_stats>(), c->sm_count, cursors + s);
     } else if (sh.type == TB_STEP_GOPHER_REPETITION) {
       GrScratch g{p->g_wh.as<uint64_t>(), p->g_wl.as<uint32_t>(), p->g_lh.as<uint64_t>(), p->g_ll.as<uint32_t>(),
                   p->g_lg.as<uint8_t>(), p->g_doc.as<GrDoc>(), p->g_work.as<uint32_t>(), p->g_lists.as<uint32_t>(),
@@ -335,12 +336,12 @@ int enqueue_chain(tb_pipeline* p, const uint8_t* text, int64_t n, int64_t nbytes
       // the few documents of tier X (each a long chain of passes on one CTA) run beside the other tiers
       CK(cudaEventRecord(c->ev_fork, st));
       CK(cudaStreamWaitEvent(c->side, c->ev_fork, 0));
-      tb_launch_gr_rep(c->side, b, p->ts.as<int64_t>(), p->te.as<int64_t>(), g, sh.gr, (int)s, p->stats[s].as<tb_gr_stats>(), c->sm_count, 3);
+      tb_launch_gr_rep(c->side, b, p->ts.as<int64_t>(), p->te.as<int64_t>(), g, sh.gr, (int)s, p->stats[s][pb].as<tb_gr_stats>(), c->sm_count, 3);
       CK(cudaEventRecord(c->ev_join, c->side));
       p->launches_this_run++;
-      { Timed t(p, "k_gr_rep_s"); tb_launch_gr_rep(st, b, p->ts.as<int64_t>(), p->te.as<int64_t>(), g, sh.gr, (int)s, p->stats[s].as<tb_gr_stats>(), c->sm_count, 0); }
-      { Timed t(p, "k_gr_rep_m"); tb_launch_gr_rep(st, b, p->ts.as<int64_t>(), p->te.as<int64_t>(), g, sh.gr, (int)s, p->stats[s].as<tb_gr_stats>(), c->sm_count, 1); }
-      { Timed t(p, "k_gr_rep_l"); tb_launch_gr_rep(st, b, p->ts.as<int64_t>(), p->te.as<int64_t>(), g, sh.gr, (int)s, p->stats[s].as<tb_gr_stats>(), c->sm_count, 2); }
+      { Timed t(p, "k_gr_rep_s"); tb_launch_gr_rep(st, b, p->ts.as<int64_t>(), p->te.as<int64_t>(), g, sh.gr, (int)s, p->stats[s][pb].as<tb_gr_stats>(), c->sm_count, 0); }
+      { Timed t(p, "k_gr_rep_m"); tb_launch_gr_rep(st, b, p->ts.as<int64_t>(), p->te.as<int64_t>(), g, sh.gr, (int)s, p->stats[s][pb].as<tb_gr_stats>(), c->sm_count, 1); }
+      { Timed t(p, "k_gr_rep_l"); tb_launch_gr_rep(st, b, p->ts.as<int64_t>(), p->te.as<int64_t>(), g, sh.gr, (int)s, p->stats[s][pb].as<tb_gr_stats>(), c->sm_count, 2); }
       { Timed t(p, "k_gr_rep_x(join)"); CK(cudaStreamWaitEvent(st, c->ev_join, 0)); }
     } else {
       C4Scratch cs{p->c_P.as<uint8_t>(), p->c_F.as<uint8_t>(), p->c_plen.as<int64_t>(), p->c_nlines.as<uint32_t>(),
@@ -353,15 +354,15 @@ int enqueue_chain(tb_pipeline* p, const uint8_t* text, int64_t n, int64_t nbytes
         KBatch fb = b; fb.text = cs.F; fb.rs = cs.frs; fb.re = cs.fre;
         Timed t(p, "k_trim"); tb_launch_trim(st, fb, cs.frs, cs.fre);
       }
-      { Timed t(p, "k_c4_d"); tb_launch_c4_d(st, b, sh.c4, cs, (int)s, p->stats[s].as<tb_c4_stats>(), p->rewritten.as<uint8_t>()); }
+      { Timed t(p, "k_c4_d"); tb_launch_c4_d(st, b, sh.c4, cs, (int)s, p->stats[s][pb].as<tb_c4_stats>(), p->rewritten.as<uint8_t>()); }
       b.text = cs.F;  // every document still alive now lives in F
       *has_c4 = true;
     }
   }
   if (*has_c4 && want_content) {
     { Timed t(p, "k_final_len"); tb_launch_final_len(st, n, p->rs0.as<int64_t>(), p->re0.as<int64_t>(), b.rs, b.re, p->rewritten.as<uint8_t>(), p->len.as<int64_t>()); }
-    { Timed t(p, "k_scan_i64"); tb_launch_scan_i64(st, p->len.as<int64_t>(), p->out_off.as<int64_t>(), n); }
-    { Timed t(p, "k_pack"); tb_launch_pack(st, n, text, p->rs0.as<int64_t>(), b.text, b.rs, p->rewritten.as<uint8_t>(), p->out_off.as<int64_t>(), p->packed[pb].as<uint8_t>()); }
+    { Timed t(p, "k_scan_i64"); tb_launch_scan_i64(st, p->len.as<int64_t>(), p->out_off[pb].as<int64_t>(), n); }
+    { Timed t(p, "k_pack"); tb_launch_pack(st, n, text, p->rs0.as<int64_t>(), b.text, b.rs, p->rewritten.as<uint8_t>(), p->out_off[pb].as<int64_t>(), p->packed[pb].as<uint8_t>()); }
   }
   CK(cudaGetLastError());
   return TB_OK;
@@ -422,48 +423,63 @@ int run_impl(tb_pipeline* p, const uint8_t* utf8, const void* offsets, int is64,
     return TB_OK;
   };
 
+  // Results of a chunk leave on the d2h stream while the compute stream already runs the next chunk; the
+  // host only waits (for the content size) one chunk behind.
+  auto finish = [&](size_t ci) -> int {
+    const Chunk& ch = chunks[ci];
+    const int buf = (int)(ci & 1);
+    const int64_t n = ch.d1 - ch.d0;
+    CK(cudaEventSynchronize(p->ev_small[buf]));
+    if (p->opt_validate && h_bad) return fail(TB_ERR_INVALID_UTF8, "input contains " + std::to_string(h_bad) + " document(s) with invalid UTF-8 (first chunk doc " + std::to_string(ch.d0) + ")");
+    if (want_content) {
+      int64_t tot = h_coff[ch.d0 + n];
+      for (int64_t i = 0; i <= n; i++) h_coff[ch.d0 + i] += content_base;  // chunk-relative -> absolute
+      if (tot) CK(cudaMemcpyAsync(h_content + content_base, p->packed[buf].p, (size_t)tot, cudaMemcpyDeviceToHost, c->d2h));
+      content_base += tot;
+    }
+    CK(cudaEventRecord(p->ev_d2h[buf], c->d2h));
+    return TB_OK;
+  };
+
+  if (p->opt_validate) CK(cudaMemsetAsync(p->bad.p, 0, 4, c->compute));
   if (!chunks.empty()) if ((rc = enqueue_h2d(0))) return rc;
   for (size_t ci = 0; ci < chunks.size(); ci++) {
     const Chunk& ch = chunks[ci];
     int buf = (int)(ci & 1);
     int64_t n = ch.d1 - ch.d0;
     if (ci + 1 < chunks.size()) if ((rc = enqueue_h2d(ci + 1))) return rc;
+    // result buffers and packed[buf] may still be read by the copies of chunk ci-2
+    CK(cudaStreamWaitEvent(c->compute, p->ev_d2h[buf], 0));
     const uint8_t* text;
     if (device_input) {
       text = utf8 + ch.b0;
-      tb_launch_init_ranges(c->compute, offsets_dev, 1, ch.d0, n, ch.b0, p->rs0.as<int64_t>(), p->re0.as<int64_t>(), p->alive.as<uint8_t>(), p->failed.as<int8_t>());
+      tb_launch_init_ranges(c->compute, offsets_dev, 1, ch.d0, n, ch.b0, p->rs0.as<int64_t>(), p->re0.as<int64_t>(), p->alive[buf].as<uint8_t>(), p->failed[buf].as<int8_t>());
     } else {
       CK(cudaStreamWaitEvent(c->compute, p->ev_h2d[buf], 0));
       text = p->text[buf].as<uint8_t>();
-      tb_launch_init_ranges(c->compute, p->offs[buf].p, is64, 0, n, ch.b0, p->rs0.as<int64_t>(), p->re0.as<int64_t>(), p->alive.as<uint8_t>(), p->failed.as<int8_t>());
+      tb_launch_init_ranges(c->compute, p->offs[buf].p, is64, 0, n, ch.b0, p->rs0.as<int64_t>(), p->re0.as<int64_t>(), p->alive[buf].as<uint8_t>(), p->failed[buf].as<int8_t>());
     }
     p->launches_this_run++;
-    // packed[buf] may still be read by the D2H of chunk ci-2
-    CK(cudaStreamWaitEvent(c->compute, p->ev_d2h[buf], 0));
     bool has_c4 = false;
     if ((rc = enqueue_chain(p, text, n, ch.b1 - ch.b0, buf, want_content, &has_c4))) return rc;
+    CK(cudaEventRecord(p->ev_done[buf], c->compute));
+    // the previous chunk's content goes out first (its copy must not queue behind this chunk's kernels)
+    if (ci > 0) if ((rc = finish(ci - 1))) return rc;
     // small results
-    CK(cudaMemcpyAsync(h_keep + ch.d0, p->alive.p, (size_t)n, cudaMemcpyDeviceToHost, c->compute));
-    CK(cudaMemcpyAsync(h_failed + ch.d0, p->failed.p, (size_t)n, cudaMemcpyDeviceToHost, c->compute));
+    CK(cudaStreamWaitEvent(c->d2h, p->ev_done[buf], 0));
+    CK(cudaMemcpyAsync(h_keep + ch.d0, p->alive[buf].p, (size_t)n, cudaMemcpyDeviceToHost, c->d2h));
+    CK(cudaMemcpyAsync(h_failed + ch.d0, p->failed[buf].p, (size_t)n, cudaMemcpyDeviceToHost, c->d2h));
     for (size_t s = 0; s < p->steps.size(); s++) {
       size_t sz = stat_size(p->steps[s].type);
-      CK(cudaMemcpyAsync(rsx->stats[s].as<uint8_t>() + (size_t)ch.d0 * sz, p->stats[s].p, (size_t)n * sz, cudaMemcpyDeviceToHost, c->compute));
+      CK(cudaMemcpyAsync(rsx->stats[s].as<uint8_t>() + (size_t)ch.d0 * sz, p->stats[s][buf].p, (size_t)n * sz, cudaMemcpyDeviceToHost, c->d2h));
     }
-    if (want_content) CK(cudaMemcpyAsync(h_coff + ch.d0, p->out_off.p, (size_t)(n + 1) * 8, cudaMemcpyDeviceToHost, c->compute));
-    if (p->opt_validate) CK(cudaMemcpyAsync(&h_bad, p->bad.p, 4, cudaMemcpyDeviceToHost, c->compute));
-    CK(cudaEventRecord(p->ev_done[buf], c->compute));
-    CK(cudaStreamSynchronize(c->compute));
-    resolve_times(p);
-    if (p->opt_validate && h_bad) return fail(TB_ERR_INVALID_UTF8, "input contains " + std::to_string(h_bad) + " document(s) with invalid UTF-8 (first chunk doc " + std::to_string(ch.d0) + ")");
-    if (want_content) {
-      int64_t tot = h_coff[ch.d0 + n];
-      for (int64_t i = 0; i <= n; i++) h_coff[ch.d0 + i] += content_base;  // chunk-relative -> absolute
-      CK(cudaStreamWaitEvent(c->d2h, p->ev_done[buf], 0));
-      if (tot) CK(cudaMemcpyAsync(h_content + content_base, p->packed[buf].p, (size_t)tot, cudaMemcpyDeviceToHost, c->d2h));
-      CK(cudaEventRecord(p->ev_d2h[buf], c->d2h));
-      content_base += tot;
-    }
+    if (want_content) CK(cudaMemcpyAsync(h_coff + ch.d0, p->out_off[buf].p, (size_t)(n + 1) * 8, cudaMemcpyDeviceToHost, c->d2h));
+    if (p->opt_validate) CK(cudaMemcpyAsync(&h_bad, p->bad.p, 4, cudaMemcpyDeviceToHost, c->d2h));
+    CK(cudaEventRecord(p->ev_small[buf], c->d2h));
   }
+  if (!chunks.empty()) if ((rc = finish(chunks.size() - 1))) return rc;
+  CK(cudaStreamSynchronize(c->compute));
+  resolve_times(p);
   CK(cudaStreamSynchronize(c->d2h));
   CK(cudaStreamSynchronize(c->copy));
   out->keep = h_keep;
@@ -581,6 +597,7 @@ int tb_pipeline_create(tb_ctx* ctx, const tb_step_cfg* steps, size_t n_steps, tb
     CK(cudaEventCreateWithFlags(&p->ev_h2d[i], cudaEventDisableTiming));
     CK(cudaEventCreateWithFlags(&p->ev_done[i], cudaEventDisableTiming));
     CK(cudaEventCreateWithFlags(&p->ev_d2h[i], cudaEventDisableTiming));
+    CK(cudaEventCreateWithFlags(&p->ev_small[i], cudaEventDisableTiming));
   }
   *out = p;
   return TB_OK;
@@ -591,11 +608,11 @@ void tb_pipeline_destroy(tb_pipeline* p) {
   cudaSetDevice(p->ctx->device);
   cudaDeviceSynchronize();
   for (DevBuf* b : {&p->text[0], &p->text[1], &p->offs[0], &p->offs[1], &p->packed[0], &p->packed[1], &p->rs0, &p->re0, &p->rs,
-                    &p->re, &p->ts, &p->te, &p->alive, &p->failed, &p->rewritten, &p->len, &p->out_off, &p->bad, &p->g_wh,
+                    &p->re, &p->ts, &p->te, &p->alive[0], &p->alive[1], &p->failed[0], &p->failed[1], &p->rewritten, &p->len, &p->out_off[0], &p->out_off[1], &p->bad, &p->cursors, &p->g_wh,
                     &p->g_wl, &p->g_lh, &p->g_ll, &p->g_lg, &p->g_doc, &p->g_work, &p->g_lists, &p->g_counters, &p->c_P, &p->c_F, &p->c_plen, &p->c_nlines,
                     &p->c_docflags, &p->c_lwc, &p->c_lmax, &p->c_lflags, &p->c_prs, &p->c_pre, &p->c_frs, &p->c_fre, &p->c_cnt})
     b->release();
-  for (auto& b : p->stats) b.release();
+  for (auto& b : p->stats) { b[0].release(); b[1].release(); }
   for (auto& s : p->steps) s.sw_dev.release();
   for (auto* r : p->results) {
     r->keep.release(); r->failed.release(); r->content.release(); r->content_off.release();
@@ -606,6 +623,7 @@ void tb_pipeline_destroy(tb_pipeline* p) {
     if (p->ev_h2d[i]) cudaEventDestroy(p->ev_h2d[i]);
     if (p->ev_done[i]) cudaEventDestroy(p->ev_done[i]);
     if (p->ev_d2h[i]) cudaEventDestroy(p->ev_d2h[i]);
+    if (p->ev_small[i]) cudaEventDestroy(p->ev_small[i]);
   }
   for (auto e : p->ev_pool) cudaEventDestroy(e);
   delete p;
