@@ -136,7 +136,7 @@ struct tb_pipeline {
   std::mutex mu;
   // device buffers (grow-only)
   DevBuf text[2], offs[2], packed[2];
-  DevBuf rs0, re0, rs, re, ts, te, rewritten, len, bad, cursors;
+  DevBuf rs0, re0, rs, re, ts, te, rewritten, len, bad, cursors, order, sizecls;
   // per-chunk results, double-buffered: the copies to the host run beside the next chunk's kernels
   DevBuf alive[2], failed[2], out_off[2], stats[TB_MAX_STEPS][2];
   // GopherRepetition scratch
@@ -283,7 +283,7 @@ int ensure_chunk_buffers(tb_pipeline* p, int64_t n, int64_t nb, bool host_input)
   for (int i = 0; i < 2; i++) ENS(p->packed[i], (size_t)nb + 64);
   ENS(p->rs0, n1 * 8); ENS(p->re0, n1 * 8); ENS(p->rs, n1 * 8); ENS(p->re, n1 * 8); ENS(p->ts, n1 * 8); ENS(p->te, n1 * 8);
   for (int i = 0; i < 2; i++) { ENS(p->alive[i], n1); ENS(p->failed[i], n1); ENS(p->out_off[i], (n1 + 1) * 8); }
-  ENS(p->rewritten, n1); ENS(p->len, n1 * 8); ENS(p->bad, 16); ENS(p->cursors, 256);
+  ENS(p->rewritten, n1); ENS(p->len, n1 * 8); ENS(p->bad, 16); ENS(p->cursors, 256); ENS(p->order, n1 * 4); ENS(p->sizecls, n1);
   size_t units = (size_t)nb / 2 + n1 + 1;
   for (size_t s = 0; s < p->steps.size(); s++) {
     const StepHost& sh = p->steps[s];
@@ -314,9 +314,10 @@ int enqueue_chain(tb_pipeline* p, const uint8_t* text, int64_t n, int64_t nbytes
   CK(cudaMemcpyAsync(p->re.p, p->re0.p, (size_t)n * 8, cudaMemcpyDeviceToDevice, st));
   CK(cudaMemsetAsync(p->rewritten.p, 0, (size_t)n, st));
   CK(cudaMemsetAsync(p->cursors.p, 0, 256, st));
+  uint32_t* cursors = p->cursors.as<uint32_t>();  // [0, 3 * TB_MAX_STEPS): kernel cursors; [48], [49]: counts of the work order
   KBatch b{text, p->rs.as<int64_t>(), p->re.as<int64_t>(), p->alive[pb].as<uint8_t>(), p->failed[pb].as<int8_t>(), n, c->uc, 0, nbytes,
-           (uint32_t)p->opt_debug};
-  uint32_t* cursors = p->cursors.as<uint32_t>();
+           (uint32_t)p->opt_debug, p->order.as<uint32_t>(), cursors + 48, p->sizecls.as<uint8_t>()};
+  { Timed t(p, "k_order"); tb_launch_order(st, p->rs0.as<int64_t>(), p->re0.as<int64_t>(), n, p->order.as<uint32_t>(), cursors + 48, p->sizecls.as<uint8_t>()); }
   *has_c4 = false;
   if (p->opt_validate) {  // p->bad counts over the whole run (cleared by run_impl)
     { Timed t(p, "k_validate_utf8"); tb_launch_validate_utf8(st, text, b.rs, b.re, n, p->bad.as<int32_t>()); }
@@ -608,7 +609,7 @@ void tb_pipeline_destroy(tb_pipeline* p) {
   cudaSetDevice(p->ctx->device);
   cudaDeviceSynchronize();
   for (DevBuf* b : {&p->text[0], &p->text[1], &p->offs[0], &p->offs[1], &p->packed[0], &p->packed[1], &p->rs0, &p->re0, &p->rs,
-                    &p->re, &p->ts, &p->te, &p->alive[0], &p->alive[1], &p->failed[0], &p->failed[1], &p->rewritten, &p->len, &p->out_off[0], &p->out_off[1], &p->bad, &p->cursors, &p->g_wh,
+                    &p->re, &p->ts, &p->te, &p->alive[0], &p->alive[1], &p->failed[0], &p->failed[1], &p->rewritten, &p->len, &p->out_off[0], &p->out_off[1], &p->bad, &p->cursors, &p->order, &p->sizecls, &p->g_wh,
                     &p->g_wl, &p->g_lh, &p->g_ll, &p->g_lg, &p->g_doc, &p->g_work, &p->g_lists, &p->g_counters, &p->c_P, &p->c_F, &p->c_plen, &p->c_nlines,
                     &p->c_docflags, &p->c_lwc, &p->c_lmax, &p->c_lflags, &p->c_prs, &p->c_pre, &p->c_frs, &p->c_fre, &p->c_cnt})
     b->release();

@@ -26,11 +26,28 @@ __device__ __forceinline__ void load_lut(LutEntry* s_lut, const UcTables& uc, in
   }
   __syncthreads();
 }
-// persistent one-warp CTAs pull document indices from a cursor (zeroed by the host before the launch)
-__device__ __forceinline__ int64_t next_doc(uint32_t* cursor) {
+// persistent one-warp CTAs pull work items from a cursor (zeroed by the host before the launch): first the
+// listed long documents, then all documents in index order (listed ones are skipped there).
+// Returns -1 when the work is exhausted, -2 for an item to skip.
+__device__ __forceinline__ int64_t next_doc(uint32_t* cursor, const KBatch& a) {
   uint32_t i = 0;
   if ((threadIdx.x & 31) == 0) i = atomicAdd(cursor, 1u);
-  return (int64_t)__shfl_sync(0xFFFFFFFFu, i, 0);
+  i = __shfl_sync(0xFFFFFFFFu, i, 0);
+  const uint32_t nx = a.order_counts[0], nl = a.order_counts[1];
+  if (i < nx) return (int64_t)a.order[i];
+  if (i < nx + nl) return (int64_t)a.order[a.n - 1 - (i - nx)];
+  const int64_t d = (int64_t)i - nx - nl;
+  if (d >= a.n) return -1;
+  return a.sizecls[d] ? -2 : d;
+}
+__global__ void k_order(const int64_t* rs, const int64_t* re, int64_t n, uint32_t* order, uint32_t* counts, uint8_t* sizecls) {
+  int64_t d = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (d >= n) return;
+  const int64_t len = re[d] - rs[d];
+  uint8_t c = len > TB_XLONG_DOC_BYTES ? 2 : len > TB_LONG_DOC_BYTES ? 1 : 0;
+  sizecls[d] = c;
+  if (c == 2) order[atomicAdd(&counts[0], 1u)] = (uint32_t)d;
+  else if (c == 1) order[n - 1 - atomicAdd(&counts[1], 1u)] = (uint32_t)d;
 }
 __device__ __forceinline__ int64_t warp_doc() { return ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; }
 __device__ __forceinline__ int64_t thread_doc() { return (int64_t)blockIdx.x * blockDim.x + threadIdx.x; }
@@ -57,8 +74,9 @@ __global__ void __launch_bounds__(TB_BLOCK, 12) k_gq(KBatch a, SwTable sw, GqCfg
     sw.e = s_sw;
   }
   for (;;) {
-    const int64_t d = next_doc(cursor);
-    if (d >= a.n) break;
+    const int64_t d = next_doc(cursor, a);
+    if (d == -1) break;
+    if (d < 0) continue;
     if (a.alive[d]) body_gq(a, s_ascii, s_lut, sw, cfg, step, out, d, threadIdx.x & 31);
   }
 }
@@ -75,8 +93,9 @@ __global__ void __launch_bounds__(TB_BLOCK, 12) k_gr_scan(KBatch a, const int64_
   load_lut(s_lut, a.uc, TB_LUT_GR, 0u);
   __shared__ uint32_t s_stage[3 * TB_GR_STAGE_WORDS];
   for (;;) {
-    const int64_t d = next_doc(&s.counters[8]);
-    if (d >= a.n) break;
+    const int64_t d = next_doc(&s.counters[8], a);
+    if (d == -1) break;
+    if (d < 0) continue;
     if (a.alive[d]) body_gr_scan(a, s_ascii, s_lut, s_stage, ts, te, s, d, threadIdx.x & 31);
   }
 }
@@ -144,8 +163,9 @@ __global__ void __launch_bounds__(TB_BLOCK, 12) k_c4_a(KBatch a, C4Cfg cfg, C4Sc
   load_ascii(s_ascii, a.uc);
   load_lut(s_lut, a.uc, TB_LUT_C4A, 0u);
   for (;;) {
-    const int64_t d = next_doc(cursor);
-    if (d >= a.n) break;
+    const int64_t d = next_doc(cursor, a);
+    if (d == -1) break;
+    if (d < 0) continue;
     if (a.alive[d]) body_c4_a(a, s_ascii, s_lut, s_stage, cfg, s, d, threadIdx.x & 31);
   }
 }
@@ -155,16 +175,18 @@ __global__ void __launch_bounds__(TB_BLOCK, 12) k_c4_b(KBatch a, C4Cfg cfg, C4Sc
   load_ascii(s_ascii, a.uc);
   load_lut(s_lut, a.uc, TB_LUT_C4B, 0u);
   for (;;) {
-    const int64_t d = next_doc(cursor);
-    if (d >= a.n) break;
+    const int64_t d = next_doc(cursor, a);
+    if (d == -1) break;
+    if (d < 0) continue;
     if (a.alive[d] && !s.docflags[d] && s.nlines[d] != 0) body_c4_b(a, s_ascii, s_lut, cfg, s, d, threadIdx.x & 31);
   }
 }
 __global__ void __launch_bounds__(TB_BLOCK, 16) k_c4_c(KBatch a, C4Cfg cfg, C4Scratch s, uint32_t* cursor) {
   __shared__ __align__(16) uint8_t s_stage[TB_STAGE_BYTES];
   for (;;) {
-    const int64_t d = next_doc(cursor);
-    if (d >= a.n) break;
+    const int64_t d = next_doc(cursor, a);
+    if (d == -1) break;
+    if (d < 0) continue;
     body_c4_c(a, s_stage, cfg, s, d, threadIdx.x & 31);
   }
 }
@@ -224,6 +246,9 @@ inline int blocks_for_threads(int64_t n) { return (int)((n + 255) / 256); }
 
 }  // namespace
 
+void tb_launch_order(cudaStream_t st, const int64_t* rs, const int64_t* re, int64_t n, uint32_t* order, uint32_t* counts, uint8_t* sizecls) {
+  if (n) k_order<<<(int)((n + 255) / 256), 256, 0, st>>>(rs, re, n, order, counts, sizecls);
+}
 void tb_launch_init_ranges(cudaStream_t st, const void* off, int off64, int64_t doc0, int64_t n, int64_t base,
                            int64_t* rs, int64_t* re, uint8_t* alive, int8_t* failed) {
   if (n) k_init_ranges<<<blocks_for_threads(n), 256, 0, st>>>(off, off64, doc0, n, base, rs, re, alive, failed);

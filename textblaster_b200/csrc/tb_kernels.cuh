@@ -22,7 +22,13 @@ struct KBatch {
   UcTables uc;
   int64_t ext_lo, ext_hi;  // positions of `text` (and of the C4 work buffers) that 32-byte vector loads may touch
   uint32_t dbg;            // TB_DBG_*
+  // Work order of the persistent kernels (built by tb_launch_order): long documents go first so that none of
+  // them is started when everything else is already done.  order[0 .. n): very long ones from the front, long
+  // ones from the back; counts[0], counts[1] their numbers; sizecls[d] != 0 marks a listed document.
+  const uint32_t* order; const uint32_t* order_counts; const uint8_t* sizecls;
 };
+#define TB_LONG_DOC_BYTES (8 << 10)
+#define TB_XLONG_DOC_BYTES (32 << 10)
 #define TB_DBG_FORCE_WALK 1u  // run the segment-walking bodies for every document (tests)
 
 struct GqCfg {
@@ -80,6 +86,8 @@ struct C4Scratch {
 void tb_launch_init_ranges(cudaStream_t st, const void* off, int off64, int64_t doc0, int64_t n, int64_t base,
                            int64_t* rs, int64_t* re, uint8_t* alive, int8_t* failed);
 // gq, gr_scan and c4_b run as persistent one-warp CTAs; `cursor` (gr_scan: s.counters[8]) must be zero at launch
+// order / counts (zeroed by the caller) / sizecls for KBatch, from the original ranges
+void tb_launch_order(cudaStream_t st, const int64_t* rs, const int64_t* re, int64_t n, uint32_t* order, uint32_t* counts, uint8_t* sizecls);
 void tb_launch_gq(cudaStream_t st, const KBatch& b, const SwTable& sw, const GqCfg& cfg, int step, tb_gq_stats* out,
                   int sm_count, uint32_t* cursor);
 void tb_launch_trim(cudaStream_t st, const KBatch& b, int64_t* ts, int64_t* te);

@@ -145,7 +145,9 @@ int tb_gopher_repetition_noalloc(const uint8_t* utf8_dev, const int64_t* offsets
   g.doc = (GrDoc*)carve(n1 * sizeof(GrDoc));
   g.work = (uint32_t*)carve((units * TB_REP_K + n1 * TB_REP_DOC_EXTRA) * 4);
   g.lists = (uint32_t*)carve(4 * n1 * 4);
-  g.counters = (uint32_t*)carve(64);
+  g.counters = (uint32_t*)carve(64);  // [12], [13] double as the counts of the work order
+  uint32_t* order = (uint32_t*)carve(n1 * 4);
+  uint8_t* sizecls = (uint8_t*)carve(n1);
   g.n = n_docs;
   if (off > TB_NOALLOC_SCRATCH_BYTES) return fail(TB_ERR_INVALID_ARGUMENT, "tb_gopher_repetition_noalloc: internal scratch budget exceeded");
 
@@ -159,7 +161,8 @@ int tb_gopher_repetition_noalloc(const uint8_t* utf8_dev, const int64_t* offsets
   if (cudaMemsetAsync(g.counters, 0, 64, stream) != cudaSuccess) { cudaGetLastError(); return fail(TB_ERR_CUDA, "cudaMemsetAsync failed"); }
   // keep_dev doubles as the kernels' "alive" flag; init_ranges sets it to 1 for every document
   tb_launch_init_ranges(stream, offsets_dev, 1, 0, n_docs, 0, rs, re, keep_dev, failed);
-  KBatch b{utf8_dev, rs, re, keep_dev, failed, n_docs, st->uc, 0, n_bytes, 0u};
+  tb_launch_order(stream, rs, re, n_docs, order, g.counters + 12, sizecls);
+  KBatch b{utf8_dev, rs, re, keep_dev, failed, n_docs, st->uc, 0, n_bytes, 0u, order, g.counters + 12, sizecls};
   tb_launch_trim(stream, b, ts, te);
   tb_launch_gr_scan(stream, b, ts, te, g, st->sm_count);
   for (int tier = 0; tier < 4; tier++) tb_launch_gr_rep(stream, b, ts, te, g, cfg, 0, stats_dev, st->sm_count, tier);
