@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define TB_ABI_VERSION 1
+#define TB_ABI_VERSION 2
 #define TB_MAX_STEPS 8
 #define TB_MAX_NGRAMS 12 /* entries per top_n_grams / dup_n_grams list */
 #define TB_MAX_NGRAM_N 32 /* largest n-gram order accepted */
@@ -51,7 +51,8 @@ enum {
 typedef enum {
   TB_STEP_C4_QUALITY = 1,        /* StepConfig::C4QualityFilter        */
   TB_STEP_GOPHER_QUALITY = 2,    /* StepConfig::GopherQualityFilter    */
-  TB_STEP_GOPHER_REPETITION = 3  /* StepConfig::GopherRepetitionFilter */
+  TB_STEP_GOPHER_REPETITION = 3, /* StepConfig::GopherRepetitionFilter */
+  TB_STEP_FINEWEB_QUALITY = 4    /* StepConfig::FineWebQualityFilter */
 } tb_step_type;
 
 /* C4QualityParams, src/config/pipeline.rs:66-79; field meaning src/pipeline/filters/c4_filters.rs:98-139 */
@@ -120,6 +121,19 @@ typedef struct tb_gr_params {
   double dup_frac[TB_MAX_NGRAMS];
 } tb_gr_params;
 
+/* FineWebQualityFilterParams, src/config/pipeline.rs:311-322; use src/pipeline/filters/fineweb_quality.rs:41-62 */
+#define TB_FW_MAX_STOP_CHARS 32
+typedef struct tb_fw_params {
+  double line_punct_thr;
+  int32_t line_punct_exclude_zero;
+  int32_t n_stop_chars; /* < 0: stop_chars = None -> END_PUNCTUATION . ! ? " ' U+201D (fineweb_quality.rs:26,51) */
+  uint32_t stop_chars[TB_FW_MAX_STOP_CHARS]; /* code points */
+  double short_line_thr;
+  uint64_t short_line_length;
+  double char_duplicates_ratio;
+  double new_line_ratio;
+} tb_fw_params;
+
 typedef struct tb_step_cfg {
   int32_t type; /* tb_step_type */
   int32_t _pad;
@@ -127,6 +141,7 @@ typedef struct tb_step_cfg {
     tb_c4_params c4;
     tb_gq_params gq;
     tb_gr_params gr;
+    tb_fw_params fw;
   } u;
 } tb_step_cfg;
 
@@ -202,6 +217,28 @@ typedef struct tb_gr_stats {
   uint64_t top_bytes[TB_MAX_NGRAMS];  /* find_top_duplicate, text.rs:211-238 */
   uint64_t dup_bytes[TB_MAX_NGRAMS];  /* find_all_duplicate, text.rs:241-259 */
 } tb_gr_stats;
+
+/* fineweb_quality.rs:79-222: the checks return at the first failure, so exactly one bit is set */
+enum {
+  TB_FW_REASON_EMPTY = 1 << 0,          /* no non-blank line, :79-90 (reason "empty") */
+  TB_FW_REASON_LINE_PUNCT = 1 << 1,     /* :106-123 */
+  TB_FW_REASON_SHORT_LINE = 1 << 2,     /* :126-146 */
+  TB_FW_REASON_CHAR_DUP = 1 << 3,       /* :148-185 */
+  TB_FW_REASON_LIST_NO_WORDS = 1 << 4,  /* :191-204 */
+  TB_FW_REASON_LIST_RATIO = 1 << 5      /* :205-222 */
+};
+typedef struct tb_fw_stats {
+  uint32_t reason_bits;
+  uint32_t flags;               /* TB_DOCFLAG_* */
+  uint32_t n_lines;             /* non-blank lines of content.lines(), :74-77 */
+  uint32_t n_stop_lines;        /* :93-104 */
+  uint32_t n_short_lines;       /* :126-129 */
+  uint32_t n_words;             /* split_into_words(content).len(), :188 */
+  uint32_t n_newlines;          /* content.matches('\n').count(), :189 */
+  uint32_t _pad;
+  uint64_t dup_line_bytes;      /* find_duplicates(non-blank lines).1, :162 */
+  uint64_t n_chars_no_newline;  /* :158-159 */
+} tb_fw_stats;
 
 /* Document flags (information, never affects decisions) */
 enum {

@@ -757,9 +757,94 @@ struct GR {
 };
 
 // ---------------------------------------------------------------------------------------------
+// FineWebQualityFilter  (fineweb_quality.rs:71-226)
+// ---------------------------------------------------------------------------------------------
+std::string fmt4(double v) { char b[64]; snprintf(b, sizeof b, "%.4f", v); return b; }
+struct FW {
+  tb_fw_params p;
+  bool is_stop_char(uint32_t cp) const {
+    if (p.n_stop_chars < 0) return cp == '.' || cp == '!' || cp == '?' || cp == '"' || cp == '\'' || cp == 0x201D;   // :26
+    for (int i = 0; i < p.n_stop_chars; i++) if (p.stop_chars[i] == cp) return true;
+    return false;
+  }
+  StepResult fail(Doc& doc, const std::string& reason, const std::string& md_reason) const {
+    doc.metadata["fineweb_filter_status"] = "filtered";
+    doc.metadata["fineweb_filter_reason"] = md_reason;
+    return {false, reason};
+  }
+  StepResult process(Doc& doc, tb_fw_stats* st) const {
+    memset(st, 0, sizeof *st);
+    Str text{doc.content.data(), doc.content.size()};
+    for (size_t i = 0; i < text.n;) { int l; uint32_t cp = decode_at(text.p, text.n, i, &l); if (is_complex(cp)) st->flags |= TB_DOCFLAG_COMPLEX_SCRIPT; i += l; }
+    std::vector<Str> lns;                                                     // :74-77
+    for (Str l : lines(text)) if (trim(l).n) lns.push_back(l);
+    st->n_lines = (uint32_t)lns.size();
+    if (lns.empty()) { st->reason_bits = TB_FW_REASON_EMPTY; return fail(doc, "empty", "empty document"); }   // :79-90
+    size_t stop_lines = 0;                                                    // :93-104
+    for (Str l : lns) {
+      Str t = trim_end(l);
+      if (!t.n) continue;
+      size_t k = t.n - 1;
+      while (k > 0 && ((unsigned char)t.p[k] & 0xC0) == 0x80) k--;
+      int len; uint32_t cp = decode_at(t.p, t.n, k, &len);
+      if (is_stop_char(cp)) stop_lines++;
+    }
+    st->n_stop_lines = (uint32_t)stop_lines;
+    double punct_ratio = (double)stop_lines / (double)lns.size();
+    if (punct_ratio < p.line_punct_thr && !(punct_ratio == 0.0 && p.line_punct_exclude_zero)) {   // :106-123
+      st->reason_bits = TB_FW_REASON_LINE_PUNCT;
+      std::string r = "line_punct_ratio: " + fmt4(punct_ratio) + " < threshold " + fmt4(p.line_punct_thr) + " (exclude_zero: " +
+                      (p.line_punct_exclude_zero ? "true" : "false") + ")";
+      return fail(doc, r, r);
+    }
+    size_t short_lines = 0;                                                   // :126-129
+    for (Str l : lns) { size_t nc = 0; for (size_t i = 0; i < l.n; i++) if (((unsigned char)l.p[i] & 0xC0) != 0x80) nc++; if (nc <= p.short_line_length) short_lines++; }
+    st->n_short_lines = (uint32_t)short_lines;
+    double short_ratio = (double)short_lines / (double)lns.size();
+    if (short_ratio > p.short_line_thr) {                                     // :131-146
+      st->reason_bits = TB_FW_REASON_SHORT_LINE;
+      std::string r = "short_line_ratio: " + fmt4(short_ratio) + " > threshold " + fmt4(p.short_line_thr);
+      return fail(doc, r, r);
+    }
+    std::vector<std::string> ne;                                              // :150-154
+    for (Str l : lns) ne.emplace_back(l.p, l.n);
+    size_t total_chars = 0;                                                   // :158-159
+    for (size_t i = 0; i < text.n; i++) { unsigned char c = (unsigned char)text.p[i]; if ((c & 0xC0) != 0x80 && c != '\n') total_chars++; }
+    size_t de, dc;
+    find_duplicates(ne, &de, &dc);                                            // :162
+    st->dup_line_bytes = dc; st->n_chars_no_newline = total_chars;
+    double dup_ratio = total_chars > 0 ? (double)dc / (double)total_chars : 0.0;   // :165-169
+    if (dup_ratio > p.char_duplicates_ratio) {                                // :171-185
+      st->reason_bits = TB_FW_REASON_CHAR_DUP;
+      std::string r = "char_dup_ratio: " + fmt4(dup_ratio) + " > threshold " + fmt4(p.char_duplicates_ratio);
+      return fail(doc, r, r);
+    }
+    std::vector<Str> words = split_into_words(text);                          // :188-189
+    size_t nl = 0;
+    for (size_t i = 0; i < text.n; i++) if (text.p[i] == '\n') nl++;
+    st->n_words = (uint32_t)words.size(); st->n_newlines = (uint32_t)nl;
+    if (words.empty()) {                                                      // :191-204
+      if (nl > 0) {
+        st->reason_bits = TB_FW_REASON_LIST_NO_WORDS;
+        std::string r = "list_ratio_no_words (newlines present but no words)";
+        return fail(doc, r, r);
+      }
+    } else {
+      double list_ratio = (double)nl / (double)words.size();                  // :206
+      if (list_ratio > p.new_line_ratio) {                                    // :207-222
+        st->reason_bits = TB_FW_REASON_LIST_RATIO;
+        std::string r = "list_ratio: " + fmt4(list_ratio) + " > threshold " + fmt4(p.new_line_ratio);
+        return fail(doc, r, r);
+      }
+    }
+    return {true, ""};                                                        // :225 (no metadata on pass)
+  }
+};
+
+// ---------------------------------------------------------------------------------------------
 // Pipeline = PipelineExecutor::run_single_async (executor.rs:30-57)
 // ---------------------------------------------------------------------------------------------
-struct Step { int type; C4 c4; GQ gq; GR gr; };
+struct Step { int type; C4 c4; GQ gq; GR gr; FW fw; };
 struct Pipeline { std::vector<Step> steps; };
 
 struct BatchResult {
@@ -773,7 +858,8 @@ struct BatchResult {
 };
 
 size_t stat_size(int type) {
-  return type == TB_STEP_C4_QUALITY ? sizeof(tb_c4_stats) : type == TB_STEP_GOPHER_QUALITY ? sizeof(tb_gq_stats) : sizeof(tb_gr_stats);
+  return type == TB_STEP_C4_QUALITY ? sizeof(tb_c4_stats) : type == TB_STEP_GOPHER_QUALITY ? sizeof(tb_gq_stats)
+         : type == TB_STEP_FINEWEB_QUALITY ? sizeof(tb_fw_stats) : sizeof(tb_gr_stats);
 }
 
 void run_one(const Pipeline& pl, const char* text, size_t len, int64_t i, BatchResult& br) {
@@ -787,6 +873,7 @@ void run_one(const Pipeline& pl, const char* text, size_t len, int64_t i, BatchR
     StepResult r;
     if (st.type == TB_STEP_C4_QUALITY) r = st.c4.process(doc, (tb_c4_stats*)slot);
     else if (st.type == TB_STEP_GOPHER_QUALITY) r = st.gq.process(doc, (tb_gq_stats*)slot);
+    else if (st.type == TB_STEP_FINEWEB_QUALITY) r = st.fw.process(doc, (tb_fw_stats*)slot);
     else r = st.gr.process(doc, (tb_gr_stats*)slot);
     if (!r.ok) { failed = (int8_t)s; reason = r.reason; break; }
   }
@@ -823,6 +910,7 @@ void* tbo_pipeline_create(const tb_step_cfg* steps, size_t n) {
       }
       s.gq.p.stop_words_utf8 = nullptr; s.gq.p.stop_words_offsets = nullptr;
     } else if (s.type == TB_STEP_GOPHER_REPETITION) s.gr.p = steps[i].u.gr;
+    else if (s.type == TB_STEP_FINEWEB_QUALITY) s.fw.p = steps[i].u.fw;
     else { delete pl; return nullptr; }
     pl->steps.push_back(std::move(s));
   }

@@ -77,7 +77,8 @@ template <class T> T* garbage(size_t n) {
 }
 
 size_t stat_size(int type) {
-  return type == TB_STEP_C4_QUALITY ? sizeof(tb_c4_stats) : type == TB_STEP_GOPHER_QUALITY ? sizeof(tb_gq_stats) : sizeof(tb_gr_stats);
+  return type == TB_STEP_C4_QUALITY ? sizeof(tb_c4_stats) : type == TB_STEP_GOPHER_QUALITY ? sizeof(tb_gq_stats)
+         : type == TB_STEP_FINEWEB_QUALITY ? sizeof(tb_fw_stats) : sizeof(tb_gr_stats);
 }
 
 }  // namespace
@@ -117,7 +118,7 @@ extern "C" int tbe_run_chain(const tb_step_cfg* steps, size_t n_steps, const uin
   KBatch b{text, rs, re, alive, failed, n, uc, 0, nb, (fw && fw[0] == '1') ? TB_DBG_FORCE_WALK : 0u};
   std::vector<LutEntry> lut(256);
   auto build_lut = [&](int kind, uint32_t firstmask) {
-    for (uint32_t i = 0; i < 256; i++) lut[i] = tb_lut_entry(kind, i, i < 128 ? ascii[i] : 0u, kind == TB_LUT_C4A ? ((uc.wslead[i >> 5] >> (i & 31)) & 1u) : firstmask);
+    for (uint32_t i = 0; i < 256; i++) lut[i] = tb_lut_entry(kind, i, i < 128 ? ascii[i] : 0u, (kind == TB_LUT_C4A || kind == TB_LUT_FW) ? ((uc.wslead[i >> 5] >> (i & 31)) & 1u) : firstmask);
   };
   auto alive_pred = [&](int64_t d) { return alive[d] != 0; };
   bool has_c4 = false;
@@ -154,6 +155,18 @@ extern "C" int tbe_run_chain(const tb_step_cfg* steps, size_t n_steps, const uin
       uint8_t* smem_l = (uint8_t*)G64(TB_REP_L_SMEM / 8 + 2);
       run_blocks(gs.lists + 2 * n, gs.counters[2], TB_REP_L_THREADS, [&](int64_t d, int tid) { body_gr_rep_l(b, smem_l, ts, te, gs, g, (int)s, (tb_gr_stats*)stats, d, tid); });
       run_blocks(gs.lists + 3 * n, gs.counters[3], TB_REP_X_THREADS, [&](int64_t d, int tid) { body_gr_rep_x(b, nullptr, ts, te, gs, g, (int)s, (tb_gr_stats*)stats, d, tid); });
+    } else if (sc.type == TB_STEP_FINEWEB_QUALITY) {
+      const tb_fw_params& q = sc.u.fw;
+      FwCfg f{};
+      f.line_punct_thr = q.line_punct_thr; f.short_line_thr = q.short_line_thr; f.char_duplicates_ratio = q.char_duplicates_ratio;
+      f.new_line_ratio = q.new_line_ratio; f.short_line_length = q.short_line_length;
+      f.line_punct_exclude_zero = q.line_punct_exclude_zero != 0; f.n_stop_chars = q.n_stop_chars;
+      for (int k = 0; k < TB_FW_MAX_STOP_CHARS; k++) f.stop_chars[k] = q.stop_chars[k];
+      FwScratch fs{(uint64_t*)G64(units), G32(units), (FwDoc*)G8(n1 * sizeof(FwDoc)), G32(units * 2 + n1 * 16)};
+      build_lut(TB_LUT_FW, 0u);
+      run_warps(n, alive_pred, [&](int64_t d, int lane) { body_fw_scan(b, ascii, lut.data(), f, fs, d, lane); });
+      uint32_t* ftab = G32(2 * TB_FW_SMEM_LINES);
+      run_warps(n, alive_pred, [&](int64_t d, int lane) { body_fw_fin(b, ftab, f, fs, (int)s, (tb_fw_stats*)stats, d, lane); });
     } else if (sc.type == TB_STEP_C4_QUALITY) {
       if (!sc.u.c4.split_paragraph || has_c4) return 5;
       C4Cfg cfg = tb_c4cfg_of(sc.u.c4);

@@ -1,5 +1,5 @@
 """Step configurations shared by the emulation (CPU) and CUDA (GPU) parity tests."""
-from textblaster_b200.config import C4QualityParams, GopherQualityParams, GopherRepetitionParams
+from textblaster_b200.config import C4QualityParams, FineWebQualityParams, GopherQualityParams, GopherRepetitionParams
 
 # permissive: (almost) nothing is filtered, so every statistic of every step is compared
 GQ_OPEN = GopherQualityParams(min_doc_words=1, max_doc_words=1000000, min_avg_word_length=0.01, max_avg_word_length=5000.0,
@@ -25,7 +25,16 @@ C4_ONE_SENT = C4QualityParams(True, True, True, 1, 3, 1000, True, True, True, Tr
 C4_LAX = C4QualityParams(True, False, False, 1, 1, 50, False, False, False, False)
 C4_NOPUNCT = C4QualityParams(True, True, False, 1, 2, 1000, False, True, False, True)
 
+# FineWebQualityFilter: shipped thresholds (config/pipeline_config.yaml:74-80), a permissive
+# variant that lets every counter be compared, and a custom stop-character set with non-ASCII members
+FW_SHIPPED = FineWebQualityParams(0.12, False, 0.67, 30, 0.01, 0.3)
+FW_OPEN = FineWebQualityParams(0.0, False, 1.0, 30, 1.0, 1.0)
+FW_CUSTOM = FineWebQualityParams(0.5, True, 0.9, 12, 0.5, 0.8, stop_chars=["\u3002", "a", "\u2026", ".", "\U0001f600"])
 CHAINS = {
+    "fw_shipped": [FW_SHIPPED],
+    "fw_open": [FW_OPEN],
+    "fw_custom": [FW_CUSTOM],
+    "shipped_with_fineweb": [GR_SHIPPED, GQ_SHIPPED, C4_SHIPPED, FW_SHIPPED],  # the accelerated steps of pipeline_config.yaml, in its order
     "gq_open": [GQ_OPEN],
     "gq_shipped": [GQ_SHIPPED],
     "gr_open": [GR_OPEN],

@@ -180,7 +180,7 @@ pipeline:
     cfg = load_pipeline_config(_write(tmp_path, text))
     assert [s.name() for s in cfg.pipeline] == ["LanguageDetectionFilter", "GopherRepetitionFilter", "GopherQualityFilter",
                                                 "C4QualityFilter", "FineWebQualityFilter", "TokenCounter"]
-    assert [s.in_scope for s in cfg.pipeline] == [False, True, True, True, False, False]
+    assert [s.in_scope for s in cfg.pipeline] == [False, True, True, True, True, False]
     gq = cfg.pipeline[2].params
     assert gq.stop_words == ["ad", "af", "på", "fordi", "fordi"] and gq.min_stop_words == 2
     assert cfg.pipeline[1].params.dup_n_grams == [(5, 0.15), (10, 0.10)]
@@ -199,3 +199,20 @@ def test_rust_f64_display():
     assert rust_f64_display(1.0) == "1" and rust_f64_display(1.5) == "1.5" and rust_f64_display(-0.1) == "-0.1"
     assert rust_f64_display(0.30000000000000004) == "0.30000000000000004" and rust_f64_display(1e21) == "1000000000000000000000"
     assert rust_f64_display(1e-7) == "0.0000001"
+
+
+def test_fineweb_params_validate_and_marshal():  # src/config/pipeline.rs:311-348
+    from textblaster_b200 import _abi
+    from textblaster_b200.config import FineWebQualityParams
+    from textblaster_b200.error import ConfigValidationError
+    ok = FineWebQualityParams.from_dict(dict(line_punct_thr=0.12, line_punct_exclude_zero=False, short_line_thr=0.67,
+                                             short_line_length=30, char_duplicates_ratio=0.01, new_line_ratio=0.3))
+    ok.validate()
+    c = ok.to_c([])
+    assert c.type == _abi.TB_STEP_FINEWEB_QUALITY and c.u.fw.n_stop_chars == -1 and c.u.fw.short_line_length == 30
+    with pytest.raises(ConfigValidationError, match="FineWebQualityFilterParams: new_line_ratio must be between 0.0 and 1.0, got 1.5"):
+        FineWebQualityParams(0.1, False, 0.5, 30, 0.1, 1.5).validate()
+    with pytest.raises(ConfigValidationError, match="short_line_length must be greater than 0"):
+        FineWebQualityParams(0.1, False, 0.5, 0, 0.1, 0.5).validate()
+    custom = FineWebQualityParams(0.1, True, 0.5, 10, 0.1, 0.5, stop_chars=["\u3002", ".", "."]).to_c([])
+    assert custom.u.fw.n_stop_chars == 2 and sorted(custom.u.fw.stop_chars[:2]) == [ord("."), 0x3002]

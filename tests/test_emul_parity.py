@@ -41,7 +41,7 @@ def test_fuzzed_documents(name):
     _check(name, fuzzgen.FuzzGen(11).docs(120))
 
 
-@pytest.mark.parametrize("name", ["baseline_order", "shipped_order", "c4_then_open", "gr_open", "gq_open"])
+@pytest.mark.parametrize("name", ["baseline_order", "shipped_order", "c4_then_open", "gr_open", "gq_open", "fw_open", "fw_custom"])
 def test_multi_tile_documents(name):
     rng = random.Random(3)
     texts = [fuzzgen.english_doc(rng, sz) for sz in (200, 900, 1023, 1024, 1025, 1100, 3000, 8000, 20000)]
@@ -75,7 +75,7 @@ def test_word_spanning_many_tiles():
         _check(name, texts)
 
 
-@pytest.mark.parametrize("name", ["c4_lax", "c4_shipped", "gq_open", "gr_open", "baseline_order"])
+@pytest.mark.parametrize("name", ["c4_lax", "c4_shipped", "gq_open", "gr_open", "baseline_order", "fw_open", "fw_custom", "fw_shipped"])
 def test_boundary_documents(name):
     _check(name, fuzzgen.boundary_docs())
 
@@ -85,7 +85,7 @@ def test_general_word_path_matches(monkeypatch):
     monkeypatch.setenv("TBE_FORCE_WALK", "1")
     rng = random.Random(5)
     texts = fuzzgen.FuzzGen(21).docs(40) + [fuzzgen.english_doc(rng, 2500)] + fuzzgen.boundary_docs()[:30]
-    for name in ("baseline_order", "gq_open", "gr_open"):
+    for name in ("baseline_order", "gq_open", "gr_open", "fw_open"):
         _check(name, texts)
 
 
@@ -105,3 +105,24 @@ def split_ambiguity_docs():
 def test_ngram_split_ambiguity():
     _check("gr_open", split_ambiguity_docs())
     _check("gr_shipped", split_ambiguity_docs())
+
+
+def fineweb_docs():
+    """Line shapes FineWebQualityFilter is sensitive to: CR LF and bare CR, blank lines of odd white space,
+    repeated lines (more than the 512 the shared-memory table of pass 2 holds), lines around the short-line
+    length, stop characters behind trailing white space, very long lines, no final newline / only newlines."""
+    rng = random.Random(23)
+    docs = ["a\r\nb\r\na\r\n", "a\rb\n\r\n \u00a0\n\u3000 \nlast\r", "x" * 30 + ".\n" + "y" * 31 + ".  \n" + "z" * 29 + "\u201d \t\n",
+            "same line here.\n" * 700 + "other.\n" * 3, ("l" * 5000 + ". \n") * 3, "\n\n\n", "word", "\u3002\n\u3002\n!!!\n",
+            "Ends with an emoji \U0001f600\nEnds with a dot.\u2003\nEnds with an a\nEnds with ellipsis\u2026\n"]
+    for _ in range(30):
+        n = rng.choice([3, 20, 200])
+        pool = [fuzzgen.english_doc(rng, rng.choice([10, 40, 120])).replace("\n", " ") for _ in range(max(2, n // 3))]
+        eol = rng.choice(["\n", "\r\n", "\n\n", " \n"])
+        docs.append(eol.join(rng.choice(pool) for _ in range(n)) + rng.choice(["", "\n", "\r"]))
+    return docs
+
+
+@pytest.mark.parametrize("name", ["fw_open", "fw_shipped", "fw_custom", "shipped_with_fineweb"])
+def test_fineweb_documents(name):
+    _check(name, fineweb_docs())

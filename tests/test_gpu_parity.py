@@ -14,7 +14,7 @@ import multilingual
 import oracle
 from parity_cases import CHAINS, GQ_OPEN, GR_OPEN, step_types
 from parity_util import compare
-from test_emul_parity import GOLDEN_DOCS, split_ambiguity_docs
+from test_emul_parity import GOLDEN_DOCS, fineweb_docs, split_ambiguity_docs
 from test_oracle_golden import C4_LINE_CASES, c4_default
 from textblaster_b200 import _abi, synth
 from textblaster_b200.config import GopherRepetitionParams
@@ -101,7 +101,7 @@ def test_ascii_fast_path(name):
     check_texts(name, texts)
 
 
-@pytest.mark.parametrize("name", ["c4_lax", "c4_shipped", "gq_open", "gr_open", "baseline_order", "shipped_order"])
+@pytest.mark.parametrize("name", ["c4_lax", "c4_shipped", "gq_open", "gr_open", "baseline_order", "shipped_order", "fw_open", "fw_custom"])
 def test_boundary_documents(name):
     """White space, citations, multi-byte characters and MidLetter joins sliding across the 32-byte stretch and
     1 KiB tile boundaries of the mask-based passes."""
@@ -122,6 +122,12 @@ def test_general_word_path_matches(name):
     contents = [res.content_of(i) for i in range(res.n_docs)] if res.content is not None else None
     compare(ores, res.keep, res.failed_step, res.stats, contents, step_types(steps), texts, label=name + "/general")
     p.close()
+
+
+@pytest.mark.parametrize("name", ["fw_open", "fw_shipped", "fw_custom", "shipped_with_fineweb"])
+def test_fineweb_documents(name):
+    rng = random.Random(9)
+    check_texts(name, fineweb_docs() + [fuzzgen.english_doc(rng, sz) for sz in (300, 2000, 9000, 40000)] + multilingual.corpus(5, 200))
 
 
 def test_ngram_split_ambiguity():

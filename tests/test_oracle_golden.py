@@ -4,7 +4,7 @@ repo).  Inputs and expected values are the reference's own golden vectors."""
 import pytest
 
 import oracle
-from textblaster_b200.config import C4QualityParams, GopherQualityParams, GopherRepetitionParams
+from textblaster_b200.config import C4QualityParams, FineWebQualityParams, GopherQualityParams, GopherRepetitionParams
 
 
 # ---------------------------------------------------------------------------------------------
@@ -369,6 +369,81 @@ def test_gr_empty():  # gopher_rep.rs:60-74
     ok, reason, _, md, _ = run1(gr(), "  \n ")
     assert not ok and reason == "skipping empty content"
     assert md == {"gopher_repetition_filter_status": "filtered", "gopher_repetition_filter_reason": "skipping empty content"}
+
+
+# ---------------------------------------------------------------------------------------------
+# FineWebQualityFilter: src/pipeline/filters/fineweb_quality.rs:230-604
+# ---------------------------------------------------------------------------------------------
+def fw(**kw):  # default_filter(), fineweb_quality.rs:240-250
+    d = dict(line_punct_thr=0.12, line_punct_exclude_zero=False, short_line_thr=0.67, short_line_length=30,
+             char_duplicates_ratio=0.95, new_line_ratio=0.3, stop_chars=None)
+    d.update(kw)
+    return FineWebQualityParams(**d)
+
+
+def test_fw_empty_and_whitespace():  # :263-285, :475-488
+    for t in ("", "   \n\t   \n ", "\n\n\n"):
+        ok, reason, _, md, _ = run1(fw(), t)
+        assert not ok and reason == "empty"
+        assert md == {"fineweb_filter_status": "filtered", "fineweb_filter_reason": "empty document"}
+
+
+def test_fw_line_punct_ratio():  # :288-344
+    t = "Line one\nLine two\nLine three\nLine four\nLine five\nLine six\nLine seven\nLine eight\nLine nine\nLine ten."
+    ok, reason, *_ = run1(fw(), t)
+    assert not ok and reason.startswith("line_punct_ratio: 0.1000 < threshold 0.1200") and reason.endswith("(exclude_zero: false)")
+    t = ("Line one is long enough and ends with a period.\nLine two is also long enough and ends with a question mark?\n"
+         "Line three is also very long indeed and ends with an exclamation mark!")
+    assert run1(fw(short_line_thr=1.0), t)[0]
+    t = ("Looooooooong line one, no punctuation here\nLooooooooong line two, also no punctuation\n"
+         "Looooooooong line three, definitely no punctuation")
+    assert run1(fw(line_punct_exclude_zero=True, short_line_thr=1.0), t)[0]
+    ok, reason, *_ = run1(fw(), "Line one\nLine two\nLine three")
+    assert not ok and reason.startswith("line_punct_ratio: 0.0000 < threshold 0.1200")
+
+
+def test_fw_short_line_ratio():  # :347-369
+    t = ("Short line.\nThis is another short one.\nWay too short.\n"
+         "This line is definitely longer than thirty characters to provide some balance.")
+    ok, reason, *_ = run1(fw(), t)
+    assert not ok and reason.startswith("short_line_ratio: 0.7500 > threshold 0.6700")
+    t = ("This line is adequately long and should pass.\nSo is this one, it meets the criteria perfectly.\n"
+         "And another one just to be sure it's fine.")
+    assert run1(fw(), t)[0]
+
+
+def test_fw_char_dup_ratio():  # :374-425
+    assert run1(fw(line_punct_thr=0.0, short_line_thr=1.0, new_line_ratio=1.0), "abcdefghijklmnopqrstuvwxyz.\n1234567890.")[0]
+    assert run1(fw(line_punct_thr=0.0, short_line_thr=1.0), "abcde fghij klmno pqrst uvwxyz.")[0]
+    ok, reason, _, _, r = run1(fw(line_punct_thr=0.0, short_line_thr=1.0, new_line_ratio=1.0, char_duplicates_ratio=0.66),
+                               "Hello World\nHello World\nHello World")
+    assert not ok and reason.startswith("char_dup_ratio: 0.6667 > threshold 0.6600")
+    assert r.stats[0]["dup_line_bytes"][0] == 22 and r.stats[0]["n_chars_no_newline"][0] == 33
+
+
+def test_fw_new_line_ratio():  # :430-472, :491-508
+    ok, reason, *_ = run1(fw(line_punct_thr=0.0, short_line_thr=1.0), "word.\nword.\nword.\nword.\nword.")
+    assert not ok and reason.startswith("list_ratio: 0.8000 > threshold 0.3000")
+    assert run1(fw(), "Many words on a single line with no newlines effectively. This should pass easily.")[0]
+    t = ("Word one is long enough and ends with a period.\nWord two is also quite long and ends with a period.\n"
+         "Word three is suitably lengthy and ends with a period.\nWord four and five and six are here and it ends with a period.")
+    assert run1(fw(), t)[0]
+    ok, reason, *_ = run1(fw(), "... --- !!!")
+    assert not ok and reason.startswith("short_line_ratio: 1.0000 > threshold 0.6700")
+
+
+def test_fw_passing_document():  # :511-527 (no metadata is written on pass, :225)
+    t = ("This is a good line that ends with a period.\nAnother good line also ends with a question mark?\n"
+         "Short lines are not too frequent here, which is great!\n"
+         "Character duplication is hopefully not too high in this example text.\n"
+         "And the ratio of newlines to words should be reasonable as well.")
+    ok, reason, _, md, _ = run1(fw(), t)
+    assert ok and reason == "" and md == {}
+
+
+def test_fw_no_words_but_newlines():  # fineweb_quality.rs:191-204 (no reference test reaches it)
+    ok, reason, *_ = run1(fw(line_punct_thr=0.0, short_line_thr=1.0), "!!!\n???")
+    assert not ok and reason == "list_ratio_no_words (newlines present but no words)"
 
 
 # ---------------------------------------------------------------------------------------------

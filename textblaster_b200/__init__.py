@@ -20,7 +20,7 @@ __all__ = [
 
 def __getattr__(name):  # executor pulls in numpy + the native library lazily
     if name in ("ProcessingStep", "PipelineExecutor", "GpuBatchPipeline", "C4QualityFilter", "GopherQualityFilter",
-                "GopherRepetitionFilter", "build_pipeline_from_config", "BatchResult"):
+                "GopherRepetitionFilter", "FineWebQualityFilter", "build_pipeline_from_config", "BatchResult"):
         from . import executor
         return getattr(executor, name)
     raise AttributeError(name)

@@ -5,7 +5,7 @@ oracle's loader can describe the same C structs.
 """
 import ctypes as C
 
-TB_ABI_VERSION = 1
+TB_ABI_VERSION = 2
 TB_MAX_STEPS = 8
 TB_MAX_NGRAMS = 12
 TB_MAX_NGRAM_N = 32
@@ -21,6 +21,8 @@ TB_ERR_INVALID_UTF8 = 6
 TB_STEP_C4_QUALITY = 1
 TB_STEP_GOPHER_QUALITY = 2
 TB_STEP_GOPHER_REPETITION = 3
+TB_STEP_FINEWEB_QUALITY = 4
+TB_FW_MAX_STOP_CHARS = 32
 
 TB_GQ_HAS_MIN_DOC_WORDS = 1 << 0
 TB_GQ_HAS_MAX_DOC_WORDS = 1 << 1
@@ -60,6 +62,13 @@ TB_GR_REASON_DUP_LINE_CHAR_FRAC = 1 << 3
 TB_GR_REASON_TOP_SHIFT = 4
 TB_GR_REASON_DUP_SHIFT = 4 + TB_MAX_NGRAMS
 TB_GR_REASON_EMPTY = 1 << 31
+
+TB_FW_REASON_EMPTY = 1 << 0
+TB_FW_REASON_LINE_PUNCT = 1 << 1
+TB_FW_REASON_SHORT_LINE = 1 << 2
+TB_FW_REASON_CHAR_DUP = 1 << 3
+TB_FW_REASON_LIST_NO_WORDS = 1 << 4
+TB_FW_REASON_LIST_RATIO = 1 << 5
 
 TB_DOCFLAG_COMPLEX_SCRIPT = 1 << 0
 
@@ -120,8 +129,21 @@ class tb_gr_params(C.Structure):
     ]
 
 
+class tb_fw_params(C.Structure):
+    _fields_ = [
+        ("line_punct_thr", C.c_double),
+        ("line_punct_exclude_zero", C.c_int32),
+        ("n_stop_chars", C.c_int32),
+        ("stop_chars", C.c_uint32 * TB_FW_MAX_STOP_CHARS),
+        ("short_line_thr", C.c_double),
+        ("short_line_length", C.c_uint64),
+        ("char_duplicates_ratio", C.c_double),
+        ("new_line_ratio", C.c_double),
+    ]
+
+
 class _tb_step_union(C.Union):
-    _fields_ = [("c4", tb_c4_params), ("gq", tb_gq_params), ("gr", tb_gr_params)]
+    _fields_ = [("c4", tb_c4_params), ("gq", tb_gq_params), ("gr", tb_gr_params), ("fw", tb_fw_params)]
 
 
 class tb_step_cfg(C.Structure):
@@ -174,6 +196,21 @@ class tb_gr_stats(C.Structure):
     ]
 
 
+class tb_fw_stats(C.Structure):
+    _fields_ = [
+        ("reason_bits", C.c_uint32),
+        ("flags", C.c_uint32),
+        ("n_lines", C.c_uint32),
+        ("n_stop_lines", C.c_uint32),
+        ("n_short_lines", C.c_uint32),
+        ("n_words", C.c_uint32),
+        ("n_newlines", C.c_uint32),
+        ("_pad", C.c_uint32),
+        ("dup_line_bytes", C.c_uint64),
+        ("n_chars_no_newline", C.c_uint64),
+    ]
+
+
 class tb_batch_out(C.Structure):
     _fields_ = [
         ("n_docs", C.c_int64),
@@ -196,12 +233,14 @@ STATS_STRUCT = {
     TB_STEP_C4_QUALITY: tb_c4_stats,
     TB_STEP_GOPHER_QUALITY: tb_gq_stats,
     TB_STEP_GOPHER_REPETITION: tb_gr_stats,
+    TB_STEP_FINEWEB_QUALITY: tb_fw_stats,
 }
 
 STEP_NAMES = {
     TB_STEP_C4_QUALITY: "C4QualityFilter",
     TB_STEP_GOPHER_QUALITY: "GopherQualityFilter",
     TB_STEP_GOPHER_REPETITION: "GopherRepetitionFilter",
+    TB_STEP_FINEWEB_QUALITY: "FineWebQualityFilter",
 }
 
 

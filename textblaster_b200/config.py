@@ -8,7 +8,7 @@ Mirrors ``src/config/pipeline.rs`` of the reference:
   * ``load_pipeline_config``                                               (:372-393)
 
 The four step types outside the accelerated path (LanguageDetectionFilter, C4BadWordsFilter,
-FineWebQualityFilter, TokenCounter) still parse and validate with the reference's rules so the
+TokenCounter) still parse and validate with the reference's rules so the
 shipped ``config/pipeline_config.yaml`` loads; building a GPU pipeline from them is refused
 unless the caller asks to skip them.
 """
@@ -293,9 +293,68 @@ class GopherQualityParams:
 
 
 @dataclass
+class FineWebQualityParams:
+    """FineWebQualityFilterParams, src/config/pipeline.rs:311-322 (stop_chars: Option<HashSet<char>>)"""
+
+    line_punct_thr: float
+    line_punct_exclude_zero: bool
+    short_line_thr: float
+    short_line_length: int
+    char_duplicates_ratio: float
+    new_line_ratio: float
+    stop_chars: Optional[List[str]] = None
+
+    TYPE = "FineWebQualityFilter"
+    CTYPE = _abi.TB_STEP_FINEWEB_QUALITY
+
+    @classmethod
+    def from_dict(cls, d: dict) -> "FineWebQualityParams":
+        ctx = cls.TYPE
+        sc = d.get("stop_chars")
+        if sc is not None:
+            if not isinstance(sc, (list, tuple)) or any(not isinstance(c, str) or len(c) != 1 for c in sc):
+                raise ConfigError(f"{ctx}: invalid type for `stop_chars`: expected a sequence of single characters")
+            sc = list(sc)
+        return cls(_req(d, "line_punct_thr", float, ctx), _req(d, "line_punct_exclude_zero", bool, ctx),
+                   _req(d, "short_line_thr", float, ctx), _req(d, "short_line_length", int, ctx),
+                   _req(d, "char_duplicates_ratio", float, ctx), _req(d, "new_line_ratio", float, ctx), sc)
+
+    def validate(self) -> None:
+        """src/config/pipeline.rs:324-348"""
+        for name in ("line_punct_thr", "short_line_thr", "char_duplicates_ratio", "new_line_ratio"):
+            v = getattr(self, name)
+            if not (0.0 <= v <= 1.0):
+                raise ConfigValidationError(
+                    f"FineWebQualityFilterParams: {name} must be between 0.0 and 1.0, got {rust_f64_display(v)}")
+        if self.short_line_length == 0:
+            raise ConfigValidationError("FineWebQualityFilterParams: short_line_length must be greater than 0")
+
+    def to_c(self, keepalive: list) -> _abi.tb_step_cfg:
+        s = _abi.tb_step_cfg()
+        s.type = _abi.TB_STEP_FINEWEB_QUALITY
+        p = s.u.fw
+        p.line_punct_thr = self.line_punct_thr
+        p.line_punct_exclude_zero = 1 if self.line_punct_exclude_zero else 0
+        if self.stop_chars is None:
+            p.n_stop_chars = -1
+        else:
+            chars = sorted(set(self.stop_chars))
+            if len(chars) > _abi.TB_FW_MAX_STOP_CHARS:
+                raise ConfigError(f"FineWebQualityFilter: at most {_abi.TB_FW_MAX_STOP_CHARS} stop_chars are supported")
+            p.n_stop_chars = len(chars)
+            for i, c in enumerate(chars):
+                p.stop_chars[i] = ord(c)
+        p.short_line_thr = self.short_line_thr
+        p.short_line_length = self.short_line_length
+        p.char_duplicates_ratio = self.char_duplicates_ratio
+        p.new_line_ratio = self.new_line_ratio
+        return s
+
+
+@dataclass
 class OutOfScopeParams:
     """A reference step type that parses and validates but has no GPU implementation here
-    (LanguageDetectionFilter, C4BadWordsFilter, FineWebQualityFilter, TokenCounter)."""
+    (LanguageDetectionFilter, C4BadWordsFilter, TokenCounter)."""
 
     type_name: str
     params: dict
@@ -316,14 +375,6 @@ class OutOfScopeParams:
                     f"C4BadWordsParams: keep_fraction must be between 0.0 and 1.0, got {rust_f64_display(kf)}")
             if not d.get("default_language"):
                 raise ConfigValidationError("C4BadWordsParams: default_language cannot be empty")
-        elif t == "FineWebQualityFilter":  # :324-348
-            for name in ("line_punct_thr", "short_line_thr", "char_duplicates_ratio", "new_line_ratio"):
-                v = d.get(name)
-                if not (0.0 <= v <= 1.0):
-                    raise ConfigValidationError(
-                        f"FineWebQualityFilterParams: {name} must be between 0.0 and 1.0, got {rust_f64_display(v)}")
-            if d.get("short_line_length") == 0:
-                raise ConfigValidationError("FineWebQualityFilterParams: short_line_length must be greater than 0")
         elif t == "TokenCounter":  # :357-367
             if not d.get("tokenizer_name"):
                 raise ConfigValidationError("TokenCounterParams: tokenizer_name cannot be empty")
@@ -332,11 +383,9 @@ class OutOfScopeParams:
 _OUT_OF_SCOPE_REQUIRED = {
     "LanguageDetectionFilter": ("min_confidence", "allowed_languages"),
     "C4BadWordsFilter": ("keep_fraction", "fail_on_missing_language", "default_language"),
-    "FineWebQualityFilter": ("line_punct_thr", "line_punct_exclude_zero", "short_line_thr", "short_line_length",
-                             "char_duplicates_ratio", "new_line_ratio"),
     "TokenCounter": ("tokenizer_name",),
 }
-_IN_SCOPE = {c.TYPE: c for c in (C4QualityParams, GopherRepetitionParams, GopherQualityParams)}
+_IN_SCOPE = {c.TYPE: c for c in (C4QualityParams, GopherRepetitionParams, GopherQualityParams, FineWebQualityParams)}
 _VARIANTS = ["C4QualityFilter", "GopherRepetitionFilter", "GopherQualityFilter", "C4BadWordsFilter",
              "LanguageDetectionFilter", "FineWebQualityFilter", "TokenCounter"]
 

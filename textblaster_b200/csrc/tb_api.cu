@@ -99,7 +99,8 @@ struct HostBuf {  // grow-only pinned host allocation
 };
 
 size_t stat_size(int type) {
-  return type == TB_STEP_C4_QUALITY ? sizeof(tb_c4_stats) : type == TB_STEP_GOPHER_QUALITY ? sizeof(tb_gq_stats) : sizeof(tb_gr_stats);
+  return type == TB_STEP_C4_QUALITY ? sizeof(tb_c4_stats) : type == TB_STEP_GOPHER_QUALITY ? sizeof(tb_gq_stats)
+         : type == TB_STEP_FINEWEB_QUALITY ? sizeof(tb_fw_stats) : sizeof(tb_gr_stats);
 }
 
 struct StepHost {
@@ -107,6 +108,7 @@ struct StepHost {
   C4Cfg c4;
   GqCfg gq;
   GrCfg gr;
+  FwCfg fw;
   SwTable sw{nullptr, 0, 0, 0, 0};
   DevBuf sw_dev;
 };
@@ -141,6 +143,8 @@ struct tb_pipeline {
   DevBuf alive[2], failed[2], out_off[2], stats[TB_MAX_STEPS][2];
   // GopherRepetition scratch
   DevBuf g_wh, g_wl, g_lh, g_ll, g_lg, g_doc, g_work, g_lists, g_counters;
+  // FineWeb scratch
+  DevBuf f_lh, f_ll, f_doc, f_tab;
   // C4 scratch
   DevBuf c_P, c_F, c_plen, c_nlines, c_docflags, c_lwc, c_lmax, c_lflags, c_prs, c_pre, c_frs, c_fre, c_cnt;
   cudaEvent_t ev_h2d[2] = {nullptr, nullptr}, ev_done[2] = {nullptr, nullptr}, ev_d2h[2] = {nullptr, nullptr}, ev_small[2] = {nullptr, nullptr};
@@ -248,6 +252,17 @@ int validate_step(const tb_step_cfg& s) {
       return fail(TB_ERR_INVALID_ARGUMENT, "GopherQualityFilter: stop word list pointers missing");
     return TB_OK;
   }
+  if (s.type == TB_STEP_FINEWEB_QUALITY) {  // src/config/pipeline.rs:324-348
+    const tb_fw_params& p = s.u.fw;
+    struct { const char* name; double v; } rr[4] = {{"line_punct_thr", p.line_punct_thr}, {"short_line_thr", p.short_line_thr},
+                                                    {"char_duplicates_ratio", p.char_duplicates_ratio}, {"new_line_ratio", p.new_line_ratio}};
+    for (auto& r : rr)
+      if (!(r.v >= 0.0 && r.v <= 1.0))
+        return fail(TB_ERR_CONFIG_VALIDATION, std::string("FineWebQualityFilterParams: ") + r.name + " must be between 0.0 and 1.0, got " + rust_f64(r.v));
+    if (p.short_line_length == 0) return fail(TB_ERR_CONFIG_VALIDATION, "FineWebQualityFilterParams: short_line_length must be greater than 0");
+    if (p.n_stop_chars > TB_FW_MAX_STOP_CHARS) return fail(TB_ERR_INVALID_ARGUMENT, "FineWebQualityFilter: at most " + std::to_string(TB_FW_MAX_STOP_CHARS) + " stop_chars");
+    return TB_OK;
+  }
   return fail(TB_ERR_INVALID_ARGUMENT, "unknown step type " + std::to_string(s.type));
 }
 
@@ -293,6 +308,8 @@ int ensure_chunk_buffers(tb_pipeline* p, int64_t n, int64_t nb, bool host_input)
       ENS(p->g_doc, n1 * sizeof(GrDoc));
       ENS(p->g_work, (units * TB_REP_K + n1 * TB_REP_DOC_EXTRA) * 4);
       ENS(p->g_lists, 4 * n1 * 4); ENS(p->g_counters, 64);
+    } else if (sh.type == TB_STEP_FINEWEB_QUALITY) {
+      ENS(p->f_lh, units * 8); ENS(p->f_ll, units * 4); ENS(p->f_doc, n1 * sizeof(FwDoc)); ENS(p->f_tab, (units * 2 + n1 * 16) * 4);
     } else if (sh.type == TB_STEP_C4_QUALITY) {
       size_t lines = (size_t)nb + n1 + 1;
       ENS(p->c_P, (size_t)nb + 64); ENS(p->c_F, (size_t)nb + 64);
@@ -344,6 +361,10 @@ int enqueue_chain(tb_pipeline* p, const uint8_t* text, int64_t n, int64_t nbytes
       { Timed t(p, "k_gr_rep_m"); tb_launch_gr_rep(st, b, p->ts.as<int64_t>(), p->te.as<int64_t>(), g, sh.gr, (int)s, p->stats[s][pb].as<tb_gr_stats>(), c->sm_count, 1); }
       { Timed t(p, "k_gr_rep_l"); tb_launch_gr_rep(st, b, p->ts.as<int64_t>(), p->te.as<int64_t>(), g, sh.gr, (int)s, p->stats[s][pb].as<tb_gr_stats>(), c->sm_count, 2); }
       { Timed t(p, "k_gr_rep_x(join)"); CK(cudaStreamWaitEvent(st, c->ev_join, 0)); }
+    } else if (sh.type == TB_STEP_FINEWEB_QUALITY) {
+      FwScratch fs{p->f_lh.as<uint64_t>(), p->f_ll.as<uint32_t>(), p->f_doc.as<FwDoc>(), p->f_tab.as<uint32_t>()};
+      { Timed t(p, "k_fw_scan"); tb_launch_fw_scan(st, b, sh.fw, fs, c->sm_count, cursors + s); }
+      { Timed t(p, "k_fw_fin"); tb_launch_fw_fin(st, b, sh.fw, fs, (int)s, p->stats[s][pb].as<tb_fw_stats>(), c->sm_count, cursors + TB_MAX_STEPS + s); }
     } else {
       C4Scratch cs{p->c_P.as<uint8_t>(), p->c_F.as<uint8_t>(), p->c_plen.as<int64_t>(), p->c_nlines.as<uint32_t>(),
                    p->c_docflags.as<uint32_t>(), p->c_lwc.as<uint32_t>(), p->c_lmax.as<uint32_t>(), p->c_lflags.as<uint32_t>(),
@@ -506,6 +527,7 @@ const char* tb_step_name(int32_t t) {
     case TB_STEP_C4_QUALITY: return "C4QualityFilter";
     case TB_STEP_GOPHER_QUALITY: return "GopherQualityFilter";
     case TB_STEP_GOPHER_REPETITION: return "GopherRepetitionFilter";
+    case TB_STEP_FINEWEB_QUALITY: return "FineWebQualityFilter";
     default: return "";
   }
 }
@@ -584,6 +606,14 @@ int tb_pipeline_create(tb_ctx* ctx, const tb_step_cfg* steps, size_t n_steps, tb
                     q.max_symbol_word_ratio, q.max_bullet_lines_ratio, q.max_ellipsis_lines_ratio, q.max_non_alpha_words_ratio};
       int rc = build_stop_table(sh, q);
       if (rc) { tb_pipeline_destroy(p); return rc; }
+    } else if (sh.type == TB_STEP_FINEWEB_QUALITY) {
+      const tb_fw_params& q = steps[i].u.fw;
+      FwCfg f{};
+      f.line_punct_thr = q.line_punct_thr; f.short_line_thr = q.short_line_thr; f.char_duplicates_ratio = q.char_duplicates_ratio;
+      f.new_line_ratio = q.new_line_ratio; f.short_line_length = q.short_line_length;
+      f.line_punct_exclude_zero = q.line_punct_exclude_zero != 0; f.n_stop_chars = q.n_stop_chars;
+      for (int k = 0; k < TB_FW_MAX_STOP_CHARS; k++) f.stop_chars[k] = q.stop_chars[k];
+      sh.fw = f;
     } else {
       const tb_gr_params& q = steps[i].u.gr;
       GrCfg g{};
@@ -610,7 +640,7 @@ void tb_pipeline_destroy(tb_pipeline* p) {
   cudaDeviceSynchronize();
   for (DevBuf* b : {&p->text[0], &p->text[1], &p->offs[0], &p->offs[1], &p->packed[0], &p->packed[1], &p->rs0, &p->re0, &p->rs,
                     &p->re, &p->ts, &p->te, &p->alive[0], &p->alive[1], &p->failed[0], &p->failed[1], &p->rewritten, &p->len, &p->out_off[0], &p->out_off[1], &p->bad, &p->cursors, &p->order, &p->sizecls, &p->g_wh,
-                    &p->g_wl, &p->g_lh, &p->g_ll, &p->g_lg, &p->g_doc, &p->g_work, &p->g_lists, &p->g_counters, &p->c_P, &p->c_F, &p->c_plen, &p->c_nlines,
+                    &p->g_wl, &p->g_lh, &p->g_ll, &p->g_lg, &p->g_doc, &p->g_work, &p->g_lists, &p->g_counters, &p->f_lh, &p->f_ll, &p->f_doc, &p->f_tab, &p->c_P, &p->c_F, &p->c_plen, &p->c_nlines,
                     &p->c_docflags, &p->c_lwc, &p->c_lmax, &p->c_lflags, &p->c_prs, &p->c_pre, &p->c_frs, &p->c_fre, &p->c_cnt})
     b->release();
   for (auto& b : p->stats) { b[0].release(); b[1].release(); }

@@ -523,3 +523,4 @@ TB_D void body_pack(const uint8_t* orig, const int64_t* rs0, const uint8_t* cur,
 }
 
 #include "tb_bodies_tile.cuh"
+#include "tb_bodies_fw.cuh"

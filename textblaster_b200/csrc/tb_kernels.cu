@@ -22,7 +22,7 @@ __device__ __forceinline__ void load_ascii(uint16_t* s_ascii, const UcTables& uc
 __device__ __forceinline__ void load_lut(LutEntry* s_lut, const UcTables& uc, int kind, uint32_t firstmask) {
   for (uint32_t i = threadIdx.x; i < 256; i += blockDim.x) {
     uint32_t ci = i < 128 ? uc.stage2[(uint32_t)uc.stage1[0] * 256u + i] : 0u;
-    s_lut[i] = tb_lut_entry(kind, i, ci, kind == TB_LUT_C4A ? ((uc.wslead[i >> 5] >> (i & 31)) & 1u) : firstmask);
+    s_lut[i] = tb_lut_entry(kind, i, ci, (kind == TB_LUT_C4A || kind == TB_LUT_FW) ? ((uc.wslead[i >> 5] >> (i & 31)) & 1u) : firstmask);
   }
   __syncthreads();
 }
@@ -198,6 +198,28 @@ __global__ void __launch_bounds__(TB_BLOCK) k_c4_d(KBatch a, C4Cfg cfg, C4Scratc
   if (d >= a.n || !a.alive[d]) return;
   body_c4_d(a, s_ascii, cfg, s, step, out, rewritten, rs_out, re_out, d, threadIdx.x & 31);
 }
+__global__ void __launch_bounds__(TB_BLOCK, 12) k_fw_scan(KBatch a, FwCfg cfg, FwScratch s, uint32_t* cursor) {
+  __shared__ uint16_t s_ascii[192];
+  __shared__ LutEntry s_lut[256];
+  load_ascii(s_ascii, a.uc);
+  load_lut(s_lut, a.uc, TB_LUT_FW, 0u);
+  for (;;) {
+    const int64_t d = next_doc(cursor, a);
+    if (d == -1) break;
+    if (d < 0) continue;
+    if (a.alive[d]) body_fw_scan(a, s_ascii, s_lut, cfg, s, d, threadIdx.x & 31);
+  }
+}
+__global__ void __launch_bounds__(TB_BLOCK, 16) k_fw_fin(KBatch a, FwCfg cfg, FwScratch s, int step, tb_fw_stats* out, uint32_t* cursor) {
+  __shared__ uint32_t s_tab[2 * TB_FW_SMEM_LINES];
+  for (;;) {
+    const int64_t d = next_doc(cursor, a);
+    if (d == -1) break;
+    if (d < 0) continue;
+    if (a.alive[d]) body_fw_fin(a, s_tab, cfg, s, step, out, d, threadIdx.x & 31);
+    __syncwarp();
+  }
+}
 __global__ void k_final_len(int64_t n, const int64_t* rs0, const int64_t* re0, const int64_t* rs, const int64_t* re,
                             const uint8_t* rewritten, int64_t* len) {
   int64_t d = thread_doc();
@@ -274,6 +296,13 @@ void tb_launch_gr_rep(cudaStream_t st, const KBatch& b, const int64_t* ts, const
   else if (tier == 1) k_gr_rep_m<<<sm_count * 5, TB_REP_M_THREADS, TB_REP_M_SMEM, st>>>(b, ts, te, s, cfg, step, out);
   else if (tier == 2) k_gr_rep_l<<<sm_count, TB_REP_L_THREADS, TB_REP_L_SMEM, st>>>(b, ts, te, s, cfg, step, out);
   else k_gr_rep_x<<<sm_count, TB_REP_X_THREADS, 0, st>>>(b, ts, te, s, cfg, step, out);
+}
+void tb_launch_fw_scan(cudaStream_t st, const KBatch& b, const FwCfg& cfg, const FwScratch& s, int sm_count, uint32_t* cursor) {
+  if (b.n) k_fw_scan<<<persistent_grid(b.n, sm_count, 12), TB_BLOCK, 0, st>>>(b, cfg, s, cursor);
+}
+void tb_launch_fw_fin(cudaStream_t st, const KBatch& b, const FwCfg& cfg, const FwScratch& s, int step, tb_fw_stats* out, int sm_count,
+                      uint32_t* cursor) {
+  if (b.n) k_fw_fin<<<persistent_grid(b.n, sm_count, 16), TB_BLOCK, 0, st>>>(b, cfg, s, step, out, cursor);
 }
 int tb_kernels_init() {
   cudaError_t e = cudaFuncSetAttribute(k_gr_rep_m, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TB_REP_M_SMEM);

@@ -68,6 +68,26 @@ struct GrScratch {
 #define TB_REP_DOC_EXTRA 24u  // words: the constant parts of the above, padded to keep 8-byte alignment
 #define TB_REP_MIN_TABLE 16u
 
+// FineWebQualityFilter
+struct FwCfg {
+  double line_punct_thr, short_line_thr, char_duplicates_ratio, new_line_ratio;
+  uint64_t short_line_length;
+  uint32_t line_punct_exclude_zero;
+  int32_t n_stop_chars;  // < 0: default set
+  uint32_t stop_chars[TB_FW_MAX_STOP_CHARS];
+};
+// per-document result of the scan pass
+struct FwDoc {
+  uint64_t n_chars;  // chars other than '\n'
+  uint32_t n_lines, n_stop, n_short, n_words, n_newlines, flags;
+};
+// non-blank lines of document d: hash / byte length at unit (rs[d] >> 1) + d; tab: 2 words per unit + 16 per document
+struct FwScratch {
+  uint64_t* lh; uint32_t* ll;
+  FwDoc* doc;
+  uint32_t* tab;
+};
+
 // scratch of the C4 filter
 struct C4Scratch {
   uint8_t* P;          // processed lines, doc d at [rs0[d], rs0[d] + plen[d])
@@ -94,6 +114,9 @@ void tb_launch_trim(cudaStream_t st, const KBatch& b, int64_t* ts, int64_t* te);
 void tb_launch_gr_scan(cudaStream_t st, const KBatch& b, const int64_t* ts, const int64_t* te, const GrScratch& s, int sm_count);
 void tb_launch_gr_rep(cudaStream_t st, const KBatch& b, const int64_t* ts, const int64_t* te, const GrScratch& s,
                       const GrCfg& cfg, int step, tb_gr_stats* out, int sm_count, int tier);  // tier 0 S, 1 M, 2 L, 3 X
+void tb_launch_fw_scan(cudaStream_t st, const KBatch& b, const FwCfg& cfg, const FwScratch& s, int sm_count, uint32_t* cursor);
+void tb_launch_fw_fin(cudaStream_t st, const KBatch& b, const FwCfg& cfg, const FwScratch& s, int step, tb_fw_stats* out, int sm_count,
+                      uint32_t* cursor);
 int tb_kernels_init();  // per-process function attributes (dynamic shared memory opt-in)
 void tb_launch_c4_a(cudaStream_t st, const KBatch& b, const C4Cfg& cfg, const C4Scratch& s, int sm_count, uint32_t* cursor);
 void tb_launch_c4_b(cudaStream_t st, const KBatch& b, const C4Cfg& cfg, const C4Scratch& s, int sm_count, uint32_t* cursor);

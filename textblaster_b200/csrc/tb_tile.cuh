@@ -53,12 +53,15 @@
 #define CA_LL 6     // 'l' or 'L'
 #define CA_LO 7     // 'o' or 'O'
 #define CH_WSLEAD 0 // lead byte of a non-ASCII character that may be White_Space (UcTables::wslead)
-enum { TB_LUT_GQ = 0, TB_LUT_GR = 1, TB_LUT_C4B = 2, TB_LUT_C4A = 3 };
+#define FH_WS 2      // FineWeb: ASCII White_Space
+#define FH_WSLEAD 3  //          lead byte of a non-ASCII character that may be White_Space
+#define FH_CR 4      //          '\r'
+enum { TB_LUT_GQ = 0, TB_LUT_GR = 1, TB_LUT_C4B = 2, TB_LUT_C4A = 3, TB_LUT_FW = 4 };
 
 struct __attribute__((aligned(8))) LutEntry { uint32_t lo, hi; };
 
 // table entry of byte value b; ci = cinfo of the code point b (only used for b < 128); aux: SwTable::firstmask
-// (TB_LUT_GQ) or "b is a lead byte that may begin a White_Space character" (TB_LUT_C4A)
+// (TB_LUT_GQ) or "b is a lead byte that may begin a White_Space character" (TB_LUT_C4A, TB_LUT_FW)
 TB_HD LutEntry tb_lut_entry(int kind, uint32_t b, uint32_t ci, uint32_t aux) {
   const uint32_t firstmask = aux;
   LutEntry e; e.lo = 0; e.hi = 0;
@@ -101,6 +104,13 @@ TB_HD LutEntry tb_lut_entry(int kind, uint32_t b, uint32_t ci, uint32_t aux) {
     // a non-ASCII first byte may change under to_lowercase(): always a candidate
     uint32_t fl = (b | 0x20u) - 'a';
     if (b >= 0x80u || (firstmask & (fl < 26u ? (1u << fl) : (1u << 26)))) e.hi |= 1u << (4 * TH_SWF);
+  } else if (kind == TB_LUT_FW) {
+    if (b < 0x80u) {
+      if (ci & CI_WS) e.hi |= 1u << (4 * FH_WS);
+      if (b == '\r') e.hi |= 1u << (4 * FH_CR);
+    } else if ((b & 0xC0u) != 0x80u && aux) {
+      e.hi |= 1u << (4 * FH_WSLEAD);
+    }
   } else if (kind == TB_LUT_C4B) {
     if (b < 0x80u) {
       uint32_t l = b | 0x20u;

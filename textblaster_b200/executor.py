@@ -20,7 +20,8 @@ from typing import List, Optional, Sequence, Union
 import numpy as np
 
 from . import _abi, _native
-from .config import (C4QualityParams, GopherQualityParams, GopherRepetitionParams, PipelineConfig, StepConfig)
+from .config import (C4QualityParams, FineWebQualityParams, GopherQualityParams, GopherRepetitionParams, PipelineConfig,
+                     StepConfig)
 from .data_model import ProcessingOutcome, TextDocument
 from .error import ConfigError, DocumentFiltered, PipelineError, StepError, Unexpected
 from .reasons import step_metadata
@@ -91,7 +92,7 @@ class GpuBatchPipeline:
     def __init__(self, params: Sequence[object], device: int = 0, validate: bool = True):
         self.params = list(params)
         for p in self.params:
-            if not isinstance(p, (C4QualityParams, GopherQualityParams, GopherRepetitionParams)):
+            if not isinstance(p, (C4QualityParams, GopherQualityParams, GopherRepetitionParams, FineWebQualityParams)):
                 raise ConfigError(f"step type {getattr(p, 'type_name', type(p).__name__)} has no GPU implementation")
             if validate:
                 p.validate()
@@ -230,6 +231,17 @@ class GopherRepetitionFilter(_GpuStep):
                                                 list(top_n_grams), list(dup_n_grams)), device)
 
 
+class FineWebQualityFilter(_GpuStep):
+    """FineWebQualityFilter::new, fineweb_quality.rs:41-62 (same argument order)."""
+    NAME = "FineWebQualityFilter"
+
+    def __init__(self, line_punct_thr, line_punct_exclude_zero, short_line_thr, short_line_length, char_duplicates_ratio,
+                 new_line_ratio, stop_chars=None, device: int = 0):
+        super().__init__(FineWebQualityParams(line_punct_thr, line_punct_exclude_zero, short_line_thr, short_line_length,
+                                              char_duplicates_ratio, new_line_ratio,
+                                              None if stop_chars is None else list(stop_chars)), device)
+
+
 def _apply_result(doc: TextDocument, res: BatchResult, i: int, raise_step_error: bool, names: List[str]) -> TextDocument:
     """Turn row i of a batch result into the Rust ``Result<TextDocument>``: returns the document
     (content + metadata updated) or raises DocumentFiltered / StepError{DocumentFiltered}."""
@@ -321,11 +333,13 @@ def build_pipeline_from_config(config: PipelineConfig, device: int = 0, skip_out
             st = GopherQualityFilter.__new__(GopherQualityFilter)
         elif isinstance(p, GopherRepetitionParams):
             st = GopherRepetitionFilter.__new__(GopherRepetitionFilter)
+        elif isinstance(p, FineWebQualityParams):
+            st = FineWebQualityFilter.__new__(FineWebQualityFilter)
         else:
             if skip_out_of_scope:
                 continue
             raise ConfigError(f"step type {sc.name()} is outside the GPU hot path (C4QualityFilter, GopherQualityFilter, "
-                              "GopherRepetitionFilter)")
+                              "GopherRepetitionFilter, FineWebQualityFilter)")
         _GpuStep.__init__(st, p, device)
         steps.append(st)
     return steps

@@ -9,7 +9,7 @@ from __future__ import annotations
 from typing import Dict, List, Tuple
 
 from . import _abi
-from .config import C4QualityParams, GopherQualityParams, GopherRepetitionParams
+from .config import C4QualityParams, FineWebQualityParams, GopherQualityParams, GopherRepetitionParams
 
 
 def _f2(v: float) -> str:
@@ -116,6 +116,33 @@ def gr_metadata(p: GopherRepetitionParams, st) -> Tuple[Dict[str, str], str]:
     return {"gopher_repetition_filter_status": "filtered", "gopher_repetition_filter_reasons": rs}, rs
 
 
+def _f4(v: float) -> str:
+    return "%.4f" % v
+
+
+def fw_metadata(p: FineWebQualityParams, st) -> Tuple[Dict[str, str], str]:
+    """fineweb_quality.rs:79-225: the first failing check returns; nothing is written on pass.
+    (metadata, reason): the metadata value of the empty case differs from its reason (:82-89)."""
+    bits = int(st["reason_bits"])
+    if not bits:
+        return {}, ""
+    nl = float(int(st["n_lines"]))
+    if bits & _abi.TB_FW_REASON_EMPTY:
+        return {"fineweb_filter_status": "filtered", "fineweb_filter_reason": "empty document"}, "empty"
+    if bits & _abi.TB_FW_REASON_LINE_PUNCT:
+        r = (f"line_punct_ratio: {_f4(float(int(st['n_stop_lines'])) / nl)} < threshold {_f4(p.line_punct_thr)} "
+             f"(exclude_zero: {'true' if p.line_punct_exclude_zero else 'false'})")
+    elif bits & _abi.TB_FW_REASON_SHORT_LINE:
+        r = f"short_line_ratio: {_f4(float(int(st['n_short_lines'])) / nl)} > threshold {_f4(p.short_line_thr)}"
+    elif bits & _abi.TB_FW_REASON_CHAR_DUP:
+        r = f"char_dup_ratio: {_f4(float(int(st['dup_line_bytes'])) / float(int(st['n_chars_no_newline'])))} > threshold {_f4(p.char_duplicates_ratio)}"
+    elif bits & _abi.TB_FW_REASON_LIST_NO_WORDS:
+        r = "list_ratio_no_words (newlines present but no words)"
+    else:
+        r = f"list_ratio: {_f4(float(int(st['n_newlines'])) / float(int(st['n_words'])))} > threshold {_f4(p.new_line_ratio)}"
+    return {"fineweb_filter_status": "filtered", "fineweb_filter_reason": r}, r
+
+
 def step_metadata(params, st) -> Tuple[Dict[str, str], str]:
     if isinstance(params, C4QualityParams):
         return c4_metadata(params, st)
@@ -123,4 +150,6 @@ def step_metadata(params, st) -> Tuple[Dict[str, str], str]:
         return gq_metadata(params, st)
     if isinstance(params, GopherRepetitionParams):
         return gr_metadata(params, st)
+    if isinstance(params, FineWebQualityParams):
+        return fw_metadata(params, st)
     raise TypeError(type(params))
