@@ -86,7 +86,7 @@ __global__ void k_trim(KBatch a, int64_t* ts, int64_t* te) {
   int64_t d = thread_doc();
   if (d < a.n) body_trim(a, s_ascii, ts, te, d);
 }
-__global__ void __launch_bounds__(TB_BLOCK, 12) k_gr_scan(KBatch a, const int64_t* ts, const int64_t* te, GrScratch s) {
+__global__ void __launch_bounds__(TB_BLOCK, 16) k_gr_scan(KBatch a, const int64_t* ts, const int64_t* te, GrScratch s) {
   __shared__ uint16_t s_ascii[192];
   __shared__ LutEntry s_lut[256];
   load_ascii(s_ascii, a.uc);
@@ -156,7 +156,7 @@ __global__ void __launch_bounds__(TB_REP_X_THREADS) k_gr_rep_x(KBatch a, const i
     body_gr_rep_x(a, s_red, ts, te, s, cfg, step, out, (int64_t)s.lists[3 * (uint64_t)s.n + i], (int)threadIdx.x);
   }
 }
-__global__ void __launch_bounds__(TB_BLOCK, 12) k_c4_a(KBatch a, C4Cfg cfg, C4Scratch s, uint32_t* cursor) {
+__global__ void __launch_bounds__(TB_BLOCK, 24) k_c4_a(KBatch a, C4Cfg cfg, C4Scratch s, uint32_t* cursor) {
   __shared__ uint16_t s_ascii[192];
   __shared__ LutEntry s_lut[256];
   __shared__ __align__(16) uint8_t s_stage[TB_STAGE_BYTES];
@@ -169,7 +169,7 @@ __global__ void __launch_bounds__(TB_BLOCK, 12) k_c4_a(KBatch a, C4Cfg cfg, C4Sc
     if (a.alive[d]) body_c4_a(a, s_ascii, s_lut, s_stage, cfg, s, d, threadIdx.x & 31);
   }
 }
-__global__ void __launch_bounds__(TB_BLOCK, 12) k_c4_b(KBatch a, C4Cfg cfg, C4Scratch s, uint32_t* cursor) {
+__global__ void __launch_bounds__(TB_BLOCK, 20) k_c4_b(KBatch a, C4Cfg cfg, C4Scratch s, uint32_t* cursor) {
   __shared__ uint16_t s_ascii[192];
   __shared__ LutEntry s_lut[256];
   load_ascii(s_ascii, a.uc);
@@ -181,7 +181,7 @@ __global__ void __launch_bounds__(TB_BLOCK, 12) k_c4_b(KBatch a, C4Cfg cfg, C4Sc
     if (a.alive[d] && !s.docflags[d] && s.nlines[d] != 0) body_c4_b(a, s_ascii, s_lut, cfg, s, d, threadIdx.x & 31);
   }
 }
-__global__ void __launch_bounds__(TB_BLOCK, 16) k_c4_c(KBatch a, C4Cfg cfg, C4Scratch s, uint32_t* cursor) {
+__global__ void __launch_bounds__(TB_BLOCK, 32) k_c4_c(KBatch a, C4Cfg cfg, C4Scratch s, uint32_t* cursor) {
   __shared__ __align__(16) uint8_t s_stage[TB_STAGE_BYTES];
   for (;;) {
     const int64_t d = next_doc(cursor, a);
@@ -198,7 +198,7 @@ __global__ void __launch_bounds__(TB_BLOCK) k_c4_d(KBatch a, C4Cfg cfg, C4Scratc
   if (d >= a.n || !a.alive[d]) return;
   body_c4_d(a, s_ascii, cfg, s, step, out, rewritten, rs_out, re_out, d, threadIdx.x & 31);
 }
-__global__ void __launch_bounds__(TB_BLOCK, 12) k_fw_scan(KBatch a, FwCfg cfg, FwScratch s, uint32_t* cursor) {
+__global__ void __launch_bounds__(TB_BLOCK, 24) k_fw_scan(KBatch a, FwCfg cfg, FwScratch s, uint32_t* cursor) {
   __shared__ uint16_t s_ascii[192];
   __shared__ LutEntry s_lut[256];
   load_ascii(s_ascii, a.uc);
@@ -287,7 +287,7 @@ void tb_launch_trim(cudaStream_t st, const KBatch& b, int64_t* ts, int64_t* te) 
   if (b.n) k_trim<<<blocks_for_threads(b.n), 256, 0, st>>>(b, ts, te);
 }
 void tb_launch_gr_scan(cudaStream_t st, const KBatch& b, const int64_t* ts, const int64_t* te, const GrScratch& s, int sm_count) {
-  if (b.n) k_gr_scan<<<persistent_grid(b.n, sm_count, 12), TB_BLOCK, 0, st>>>(b, ts, te, s);
+  if (b.n) k_gr_scan<<<persistent_grid(b.n, sm_count, 16), TB_BLOCK, 0, st>>>(b, ts, te, s);
 }
 void tb_launch_gr_rep(cudaStream_t st, const KBatch& b, const int64_t* ts, const int64_t* te, const GrScratch& s,
                       const GrCfg& cfg, int step, tb_gr_stats* out, int sm_count, int tier) {
@@ -298,7 +298,7 @@ void tb_launch_gr_rep(cudaStream_t st, const KBatch& b, const int64_t* ts, const
   else k_gr_rep_x<<<sm_count, TB_REP_X_THREADS, 0, st>>>(b, ts, te, s, cfg, step, out);
 }
 void tb_launch_fw_scan(cudaStream_t st, const KBatch& b, const FwCfg& cfg, const FwScratch& s, int sm_count, uint32_t* cursor) {
-  if (b.n) k_fw_scan<<<persistent_grid(b.n, sm_count, 12), TB_BLOCK, 0, st>>>(b, cfg, s, cursor);
+  if (b.n) k_fw_scan<<<persistent_grid(b.n, sm_count, 24), TB_BLOCK, 0, st>>>(b, cfg, s, cursor);
 }
 void tb_launch_fw_fin(cudaStream_t st, const KBatch& b, const FwCfg& cfg, const FwScratch& s, int step, tb_fw_stats* out, int sm_count,
                       uint32_t* cursor) {
@@ -310,13 +310,13 @@ int tb_kernels_init() {
   return (int)e;
 }
 void tb_launch_c4_a(cudaStream_t st, const KBatch& b, const C4Cfg& cfg, const C4Scratch& s, int sm_count, uint32_t* cursor) {
-  if (b.n) k_c4_a<<<persistent_grid(b.n, sm_count, 12), TB_BLOCK, 0, st>>>(b, cfg, s, cursor);
+  if (b.n) k_c4_a<<<persistent_grid(b.n, sm_count, 24), TB_BLOCK, 0, st>>>(b, cfg, s, cursor);
 }
 void tb_launch_c4_b(cudaStream_t st, const KBatch& b, const C4Cfg& cfg, const C4Scratch& s, int sm_count, uint32_t* cursor) {
-  if (b.n) k_c4_b<<<persistent_grid(b.n, sm_count, 12), TB_BLOCK, 0, st>>>(b, cfg, s, cursor);
+  if (b.n) k_c4_b<<<persistent_grid(b.n, sm_count, 20), TB_BLOCK, 0, st>>>(b, cfg, s, cursor);
 }
 void tb_launch_c4_c(cudaStream_t st, const KBatch& b, const C4Cfg& cfg, const C4Scratch& s, int sm_count, uint32_t* cursor) {
-  if (b.n) k_c4_c<<<persistent_grid(b.n, sm_count, 16), TB_BLOCK, 0, st>>>(b, cfg, s, cursor);
+  if (b.n) k_c4_c<<<persistent_grid(b.n, sm_count, 32), TB_BLOCK, 0, st>>>(b, cfg, s, cursor);
 }
 void tb_launch_c4_d(cudaStream_t st, const KBatch& b, const C4Cfg& cfg, const C4Scratch& s, int step, tb_c4_stats* out,
                     uint8_t* rewritten) {
