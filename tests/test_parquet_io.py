@@ -50,6 +50,7 @@ def _write_input(path, large=False, with_null=False):
 
 
 def _run(tmp_path, pipeline, **kw):
+    tmp_path.mkdir(parents=True, exist_ok=True)
     src = str(tmp_path / "in.parquet")
     _write_input(src, **kw)
     kept, exc = str(tmp_path / "out" / "kept.parquet"), str(tmp_path / "out" / "excluded.parquet")
