@@ -469,9 +469,19 @@ TB_D void body_c4_d(const KBatch& a, const uint16_t* s_ascii, const C4Cfg& cfg, 
   Classifier C{s_ascii, a.uc};
   TextRange R{s.F, s.frs[d], s.fre[d]};  // already trimmed by body_trim
   uint32_t ns = 0;
-  for (int64_t base = R.rs; base < R.re; base += TB_TILE) {
-    int64_t p0 = base + lane * TB_STRETCH;
-    if (p0 < R.re) { int64_t p1 = p0 + TB_STRETCH < R.re ? p0 + TB_STRETCH : R.re; ns += tb_count_sentences(C, R, p0, p1); }
+  if (lane == 0 && R.rs < R.re) ns = tb_count_sentences_start(C, R);
+  for (int64_t base = tb_tile_origin(R); base < R.re; base += TB_TILE) {
+    // events of the stretch: ASCII terminators / separators and lead bytes of non-ASCII characters (SWAR masks)
+    uint32_t w[8];
+    const int64_t p0 = base + lane * TB_STRETCH;
+    const uint32_t V = tile_load(R, a.ext_lo, a.ext_hi, p0, w);
+    if (!V) continue;
+    uint32_t hi = 0;
+#pragma unroll
+    for (int k = 0; k < 8; k++) hi |= (((((w[k] & (w[k] << 1)) & 0x80808080u) >> 7) * 0x00204081u >> 21) & 15u) << (4 * k);
+    const uint32_t ev = (tile_eq_mask(w, '.') | tile_eq_mask(w, '!') | tile_eq_mask(w, '?') | tile_eq_mask(w, '\n') |
+                         tile_eq_mask(w, '\r') | hi) & V;
+    ns += tb_count_sentences_events(C, R, p0, ev);
   }
   ns = simt_sum(ns);
   if (lane) return;

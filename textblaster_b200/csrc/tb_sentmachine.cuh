@@ -117,23 +117,10 @@ TB_HD uint32_t tb_count_sentences_walk(const Classifier& C, const TextRange& R, 
 // sb_sync / sb_break_before / sb_advance functions.  Every white-space character has class Sp or is a
 // separator, so a segment opened by SB11 always begins with a non-white-space character; one opened
 // by SB4 counts iff a non-white-space character follows before the next separator.
-TB_HD uint32_t tb_count_sentences(const Classifier& C, const TextRange& R, int64_t p0, int64_t p1) {
+// phase 2: evaluate the rules at the event positions of the stretch that starts at p0 (bit k = byte p0 + k)
+TB_HD uint32_t tb_count_sentences_events(const Classifier& C, const TextRange& R, int64_t p0, uint32_t ev) {
   const uint8_t* t = R.t;
   uint32_t count = 0;
-  int64_t i = p0;
-  if (i > R.rs) while (i < R.re && tb_is_cont(tb_byte(t, i))) i++;
-  if (i == R.rs && i < p1) {  // (a): the text is trimmed, but do not rely on it
-    int64_t j = i;
-    while (j < R.re) { int len; uint32_t cp; uint32_t ci = C.at(t, j, &len, &cp); if (BIT(CI_SB(ci)) & SB_PARASEPMASK) break; if (!(ci & CI_WS)) { count++; break; } j += len; }
-  }
-  // phase 1 (converged): which bytes of the stretch can matter -- ASCII terminators / separators and
-  // the lead bytes of non-ASCII characters; phase 2: evaluate the rules at those positions only
-  uint32_t ev = 0;
-  for (int64_t j = i; j < p1; j++) {
-    uint32_t b = tb_byte(t, j);
-    bool hit = (b == '.') | (b == '!') | (b == '?') | (b == '\n') | (b == '\r') | (b >= 0xC0u);
-    ev |= (hit ? 1u : 0u) << (uint32_t)(j - p0);
-  }
   while (ev) {
 #if defined(__CUDA_ARCH__)
     const uint32_t bit = (uint32_t)__ffs((int)ev) - 1u;
@@ -141,7 +128,7 @@ TB_HD uint32_t tb_count_sentences(const Classifier& C, const TextRange& R, int64
     const uint32_t bit = (uint32_t)__builtin_ctz(ev);
 #endif
     ev &= ev - 1;
-    i = p0 + bit;
+    const int64_t i = p0 + bit;
     int len; uint32_t cp;
     const uint32_t ci = C.at(t, i, &len, &cp);
     const uint32_t cls = CI_SB(ci);
@@ -166,4 +153,25 @@ TB_HD uint32_t tb_count_sentences(const Classifier& C, const TextRange& R, int64
     }
   }
   return count;
+}
+// (a): the segment that starts the text counts iff a non-white-space character comes before the first separator
+TB_HD uint32_t tb_count_sentences_start(const Classifier& C, const TextRange& R) {
+  const uint8_t* t = R.t;
+  int64_t j = R.rs;
+  while (j < R.re) { int len; uint32_t cp; uint32_t ci = C.at(t, j, &len, &cp); if (BIT(CI_SB(ci)) & SB_PARASEPMASK) break; if (!(ci & CI_WS)) return 1u; j += len; }
+  return 0u;
+}
+TB_HD uint32_t tb_count_sentences(const Classifier& C, const TextRange& R, int64_t p0, int64_t p1) {
+  const uint8_t* t = R.t;
+  uint32_t count = 0;
+  if (p0 <= R.rs && R.rs < p1) count += tb_count_sentences_start(C, R);
+  // phase 1 (converged): which bytes of the stretch can matter -- ASCII terminators / separators and
+  // the lead bytes of non-ASCII characters; phase 2: evaluate the rules at those positions only
+  uint32_t ev = 0;
+  for (int64_t j = p0 < R.rs ? R.rs : p0; j < p1; j++) {
+    uint32_t b = tb_byte(t, j);
+    bool hit = (b == '.') | (b == '!') | (b == '?') | (b == '\n') | (b == '\r') | (b >= 0xC0u);
+    ev |= (hit ? 1u : 0u) << (uint32_t)(j - p0);
+  }
+  return count + tb_count_sentences_events(C, R, p0, ev);
 }
