@@ -376,7 +376,7 @@ int enqueue_chain(tb_pipeline* p, const uint8_t* text, int64_t n, int64_t nbytes
         KBatch fb = b; fb.text = cs.F; fb.rs = cs.frs; fb.re = cs.fre;
         Timed t(p, "k_trim"); tb_launch_trim(st, fb, cs.frs, cs.fre);
       }
-      { Timed t(p, "k_c4_d"); tb_launch_c4_d(st, b, sh.c4, cs, (int)s, p->stats[s][pb].as<tb_c4_stats>(), p->rewritten.as<uint8_t>()); }
+      { Timed t(p, "k_c4_d"); tb_launch_c4_d(st, b, sh.c4, cs, (int)s, p->stats[s][pb].as<tb_c4_stats>(), p->rewritten.as<uint8_t>(), c->sm_count, cursors + 3 * TB_MAX_STEPS + s); }
       b.text = cs.F;  // every document still alive now lives in F
       *has_c4 = true;
     }

@@ -190,13 +190,16 @@ __global__ void __launch_bounds__(TB_BLOCK, 32) k_c4_c(KBatch a, C4Cfg cfg, C4Sc
     body_c4_c(a, s_stage, cfg, s, d, threadIdx.x & 31);
   }
 }
-__global__ void __launch_bounds__(TB_BLOCK) k_c4_d(KBatch a, C4Cfg cfg, C4Scratch s, int step, tb_c4_stats* out,
-                                                   uint8_t* rewritten, int64_t* rs_out, int64_t* re_out) {
+__global__ void __launch_bounds__(TB_BLOCK, 24) k_c4_d(KBatch a, C4Cfg cfg, C4Scratch s, int step, tb_c4_stats* out,
+                                                       uint8_t* rewritten, int64_t* rs_out, int64_t* re_out, uint32_t* cursor) {
   __shared__ uint16_t s_ascii[192];
   load_ascii(s_ascii, a.uc);
-  int64_t d = warp_doc();
-  if (d >= a.n || !a.alive[d]) return;
-  body_c4_d(a, s_ascii, cfg, s, step, out, rewritten, rs_out, re_out, d, threadIdx.x & 31);
+  for (;;) {
+    const int64_t d = next_doc(cursor, a);
+    if (d == -1) break;
+    if (d < 0) continue;
+    if (a.alive[d]) body_c4_d(a, s_ascii, cfg, s, step, out, rewritten, rs_out, re_out, d, threadIdx.x & 31);
+  }
 }
 __global__ void __launch_bounds__(TB_BLOCK, 24) k_fw_scan(KBatch a, FwCfg cfg, FwScratch s, uint32_t* cursor) {
   __shared__ uint16_t s_ascii[192];
@@ -319,9 +322,9 @@ void tb_launch_c4_c(cudaStream_t st, const KBatch& b, const C4Cfg& cfg, const C4
   if (b.n) k_c4_c<<<persistent_grid(b.n, sm_count, 32), TB_BLOCK, 0, st>>>(b, cfg, s, cursor);
 }
 void tb_launch_c4_d(cudaStream_t st, const KBatch& b, const C4Cfg& cfg, const C4Scratch& s, int step, tb_c4_stats* out,
-                    uint8_t* rewritten) {
+                    uint8_t* rewritten, int sm_count, uint32_t* cursor) {
   // the new ranges are written over the batch's own rs/re (only for documents that were rewritten)
-  if (b.n) k_c4_d<<<blocks_for_warps(b.n), TB_BLOCK, 0, st>>>(b, cfg, s, step, out, rewritten, (int64_t*)b.rs, (int64_t*)b.re);
+  if (b.n) k_c4_d<<<persistent_grid(b.n, sm_count, 24), TB_BLOCK, 0, st>>>(b, cfg, s, step, out, rewritten, (int64_t*)b.rs, (int64_t*)b.re, cursor);
 }
 void tb_launch_final_len(cudaStream_t st, int64_t n, const int64_t* rs0, const int64_t* re0, const int64_t* rs,
                          const int64_t* re, const uint8_t* rewritten, int64_t* len) {
