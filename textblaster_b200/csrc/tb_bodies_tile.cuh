@@ -312,10 +312,12 @@ TB_D bool gr_doc_tiles(const KBatch& a, const LutEntry* lut, uint32_t* stage, co
 #pragma unroll
         for (int j = 0; j < 4; j++) {
           const uint32_t byte = (x >> (8 * j)) & 0xFFu;
-          if ((Bq >> j) & 1u) {
-            if (j == fbq) { hwa = wa; hwb = wb; hwn = wn; }
-            else if ((WEq >> j) & 1u) { st_a[widx] = wa; st_b[widx] = wb; st_n[widx] = wn; widx++; }
-            wa = 0; wb = 0; wn = 0;
+          {  // segment start: written as selects and predicated stores so that the lanes stay together
+            const bool brk = (Bq >> j) & 1u, emit = (WEq >> j) & 1u, head = brk && j == fbq;  // WEq is a subset of Bq without fb
+            if (emit) { st_a[widx] = wa; st_b[widx] = wb; st_n[widx] = wn; }
+            widx += emit ? 1u : 0u;
+            hwa = head ? wa : hwa; hwb = head ? wb : hwb; hwn = head ? wn : hwn;
+            wa = brk ? 0u : wa; wb = brk ? 0u : wb; wn = brk ? 0u : wn;
           }
           wa = tb_hpush(wa, TB_B1, byte + 1u); wb = tb_hpush(wb, TB_B2, byte + 1u); wn++;
           if ((NLq >> j) & 1u) {
