@@ -133,7 +133,8 @@ extern "C" int tbe_run_chain(const tb_step_cfg* steps, size_t n_steps, const uin
       std::vector<SwEntry> tab = tb_build_stop_table(tb_stop_words_of(q), &mask, &maxlen, &lenmask, &firstmask);
       SwTable sw{tab.data(), mask, maxlen, lenmask, firstmask};
       build_lut(TB_LUT_GQ, firstmask);
-      run_warps(n, alive_pred, [&](int64_t d, int lane) { body_gq(b, ascii, lut.data(), sw, cfg, (int)s, (tb_gq_stats*)stats, d, lane); });
+      uint32_t* gstage = G32(2 * TB_GQ_STAGE);
+      run_warps(n, alive_pred, [&](int64_t d, int lane) { body_gq(b, ascii, lut.data(), gstage, sw, cfg, (int)s, (tb_gq_stats*)stats, d, lane); });
     } else if (sc.type == TB_STEP_GOPHER_REPETITION) {
       const tb_gr_params& q = sc.u.gr;
       GrCfg g{};

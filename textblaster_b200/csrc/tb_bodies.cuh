@@ -70,15 +70,17 @@ TB_D_NOINLINE void gq_doc_walk(const Classifier& C, const TextRange& R, const Sw
     if (p0 < R.re) { int64_t p1 = p0 + TB_STRETCH < R.re ? p0 + TB_STRETCH : R.re; gq_lane(C, R, sw, p0, p1, acc); }
   }
 }
-TB_D bool gq_doc_tiles(const KBatch& a, const LutEntry* lut, const Classifier& C, const SwTable& sw, const TextRange& R,
-                       GqAcc& acc, int lane);
-TB_D void body_gq(const KBatch& a, const uint16_t* s_ascii, const LutEntry* lut, const SwTable& sw, const GqCfg& cfg, int step,
-                  tb_gq_stats* out, int64_t d, int lane) {
+#define TB_GQ_STAGE (17 * 32)  // stop-word candidates one tile can hold
+TB_D bool gq_doc_tiles(const KBatch& a, const LutEntry* lut, uint32_t* stage, const Classifier& C, const SwTable& sw,
+                       const TextRange& R, GqAcc& acc, int lane);
+// `stage`: 2 * TB_GQ_STAGE words of per-warp scratch (shared memory)
+TB_D void body_gq(const KBatch& a, const uint16_t* s_ascii, const LutEntry* lut, uint32_t* stage, const SwTable& sw, const GqCfg& cfg,
+                  int step, tb_gq_stats* out, int64_t d, int lane) {
   Classifier C{s_ascii, a.uc};
   C.key_maxlen = sw.maxlen; C.key_lenmask = sw.lenmask; C.key_firstmask = sw.firstmask;
   TextRange R{a.text, a.rs[d], a.re[d]};
   GqAcc acc; acc.zero();
-  if ((a.dbg & TB_DBG_FORCE_WALK) || !gq_doc_tiles(a, lut, C, sw, R, acc, lane)) { acc.zero(); gq_doc_walk(C, R, sw, acc, lane); TBE_COUNT(tbe_stat_walk, lane); }
+  if ((a.dbg & TB_DBG_FORCE_WALK) || !gq_doc_tiles(a, lut, stage, C, sw, R, acc, lane)) { acc.zero(); gq_doc_walk(C, R, sw, acc, lane); TBE_COUNT(tbe_stat_walk, lane); }
   else TBE_COUNT(tbe_stat_tiles, lane);
   uint32_t n_words = simt_sum(acc.n_words), n_alpha = simt_sum(acc.n_alpha), n_stop = simt_sum(acc.n_stop),
            n_hash = simt_sum(acc.n_hash), n_ell = simt_sum(acc.n_ell), n_lines = simt_sum(acc.n_lines),

@@ -54,9 +54,16 @@ TB_D_NOINLINE bool gq_is_stop_word(const Classifier& C, const uint8_t* t, const 
   return sw_lookup(sw, k);
 }
 
-TB_D bool gq_doc_tiles(const KBatch& a, const LutEntry* lut, const Classifier& C, const SwTable& sw, const TextRange& R,
+// cheap reject by byte length (exact for pure-ASCII words; to_lowercase() shrinks a character at most threefold)
+TB_D bool gq_len_may_match(const SwTable& sw, uint32_t len, bool pure_ascii) {
+  if (pure_ascii) return len <= sw.maxlen && ((sw.lenmask >> (len < 31u ? len : 31u)) & 1u);
+  return (uint64_t)len <= 3ull * sw.maxlen;
+}
+// `stage`: 2 * TB_GQ_STAGE words of per-warp scratch (shared memory)
+TB_D bool gq_doc_tiles(const KBatch& a, const LutEntry* lut, uint32_t* stage, const Classifier& C, const SwTable& sw, const TextRange& R,
                        GqAcc& acc, int lane) {
   const uint8_t* t = R.t;
+  uint32_t* st_pos = stage; uint32_t* st_len = stage + TB_GQ_STAGE;
   Frag carry{0u, 0u};
   for (int64_t base = tb_tile_origin(R); base < R.re; base += TB_TILE) {
     Tile T;
@@ -74,25 +81,47 @@ TB_D bool gq_doc_tiles(const KBatch& a, const LutEntry* lut, const Classifier& C
     acc.n_words += (uint32_t)tb_popc32(B & H & inner);
     acc.sum_chars += (uint32_t)tb_popc32(LEAD & H & inner);
     acc.n_alpha += (uint32_t)tb_popc32(B & HA & inner);
-    uint32_t cand = B & H & inner & SWF;
-    while (cand) {
-      const int s = tb_ctz32(cand);
-      cand &= cand - 1u;
-      const int e = tb_ctz32(B & ~tb_upto(s));
-      const uint32_t seg = tb_below(e) & ~tb_below(s);
-      if (gq_is_stop_word(C, t, sw, p0 + s, p0 + e, !(NAm & seg))) acc.n_stop++;
-    }
     // ---- the segment that was open when the stretch began ends at its first segment start
     Frag tail = frag_of(T, tailm, B ? ((SWF >> lb) & 1u) : 0u);
     Frag cin = frag_scan(tail, B != 0u, lane, carry);
+    Frag first{0u, 0u};
+    bool first_cand = false;
     if (B) {
-      Frag first = frag_cat(cin, frag_of(T, headm, 0u));
+      first = frag_cat(cin, frag_of(T, headm, 0u));
       if (first.meta & FR_WC) {
         acc.n_words++; acc.sum_chars += first.meta & FR_CNT;
         if (first.meta & FR_AL) acc.n_alpha++;
-        const int64_t e = p0 + fb;
-        if ((first.meta & FR_SWF) && gq_is_stop_word(C, t, sw, e - (int64_t)first.nbytes, e, !(first.meta & FR_NA))) acc.n_stop++;
+        first_cand = (first.meta & FR_SWF) && gq_len_may_match(sw, first.nbytes, !(first.meta & FR_NA));
       }
+    }
+    // ---- stop-word candidates (first letter and length fit): collected per tile, then tested with all lanes busy
+    {
+      uint32_t cand = B & H & inner & SWF, keepc = 0;
+      for (uint32_t c = cand; c; c &= c - 1u) {
+        const int sb = tb_ctz32(c);
+        const int e = tb_ctz32(B & ~tb_upto(sb));
+        if (gq_len_may_match(sw, (uint32_t)(e - sb), !(NAm & tb_below(e) & ~tb_below(sb)))) keepc |= 1u << sb;
+      }
+      uint32_t ctot, k = simt_exscan((uint32_t)tb_popc32(keepc) + (first_cand ? 1u : 0u), lane, &ctot);
+      if (first_cand) {
+        st_pos[k] = (uint32_t)(p0 + fb - (int64_t)first.nbytes - R.rs);
+        st_len[k] = first.nbytes | ((first.meta & FR_NA) ? 0u : 0x80000000u);
+        k++;
+      }
+      for (uint32_t c = keepc; c; c &= c - 1u) {
+        const int sb = tb_ctz32(c);
+        const int e = tb_ctz32(B & ~tb_upto(sb));
+        st_pos[k] = (uint32_t)(p0 + sb - R.rs);
+        st_len[k] = (uint32_t)(e - sb) | ((NAm & tb_below(e) & ~tb_below(sb)) ? 0u : 0x80000000u);
+        k++;
+      }
+      simt_sync();
+      for (uint32_t j = (uint32_t)lane; j < ctot; j += 32) {
+        const int64_t sp = R.rs + (int64_t)st_pos[j];
+        const uint32_t l = st_len[j];
+        if (gq_is_stop_word(C, t, sw, sp, sp + (int64_t)(l & 0x7FFFFFFFu), (l >> 31) != 0u)) acc.n_stop++;
+      }
+      simt_sync();
     }
     // ---- symbols (:104,:115)
     acc.n_hash += (uint32_t)tb_popc32(T.h[TH_HASH]);

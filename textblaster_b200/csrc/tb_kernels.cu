@@ -67,6 +67,7 @@ __global__ void __launch_bounds__(TB_BLOCK, 12) k_gq(KBatch a, SwTable sw, GqCfg
   __shared__ LutEntry s_lut[256];
   load_ascii(s_ascii, a.uc);
   load_lut(s_lut, a.uc, TB_LUT_GQ, sw.firstmask);
+  __shared__ uint32_t s_cand[2 * TB_GQ_STAGE];
   __shared__ SwEntry s_sw[64];  // small stop-word tables are probed in shared memory
   if (sw.mask < 64u) {
     for (uint32_t i = threadIdx.x; i <= sw.mask; i += blockDim.x) s_sw[i] = sw.e[i];
@@ -77,7 +78,7 @@ __global__ void __launch_bounds__(TB_BLOCK, 12) k_gq(KBatch a, SwTable sw, GqCfg
     const int64_t d = next_doc(cursor, a);
     if (d == -1) break;
     if (d < 0) continue;
-    if (a.alive[d]) body_gq(a, s_ascii, s_lut, sw, cfg, step, out, d, threadIdx.x & 31);
+    if (a.alive[d]) body_gq(a, s_ascii, s_lut, s_cand, sw, cfg, step, out, d, threadIdx.x & 31);
   }
 }
 __global__ void k_trim(KBatch a, int64_t* ts, int64_t* te) {
