@@ -413,15 +413,27 @@ int run_impl(tb_pipeline* p, const uint8_t* utf8, const void* offsets, int is64,
   if (want_content) { if ((rc = rsx->content.ensure((size_t)total_bytes + 64)) || (rc = rsx->content_off.ensure(n1 * 8))) return rc; }
   for (int64_t i = 0; i < n_docs; i++) if (off_at(offsets, is64, i + 1) < off_at(offsets, is64, i)) return fail(TB_ERR_INVALID_ARGUMENT, "offsets must be non-decreasing");
 
-  // chunk plan
+  // chunk plan.  Large chunks cost the least device time (every launch ends with a tail), but the first copy
+  // to the device and the last copy back are not hidden behind kernels: from host memory the first chunk is a
+  // quarter of the target, and a short remainder is split so that the last chunk is a quarter as well.
   std::vector<Chunk> chunks;
   int64_t max_n = 0, max_b = 0;
-  for (int64_t d = 0; d < n_docs;) {
-    int64_t b0 = off_at(offsets, is64, d), e = d;
-    while (e < n_docs && (e == d || off_at(offsets, is64, e + 1) - b0 <= p->opt_chunk)) e++;
-    chunks.push_back({d, e, b0, off_at(offsets, is64, e)});
-    max_n = std::max(max_n, e - d); max_b = std::max(max_b, off_at(offsets, is64, e) - b0);
-    d = e;
+  {
+    const int64_t C = p->opt_chunk, end_b = n_docs ? off_at(offsets, is64, n_docs) : 0;
+    bool first = true;
+    for (int64_t d = 0; d < n_docs;) {
+      const int64_t b0 = off_at(offsets, is64, d), remaining = end_b - b0;
+      int64_t target = C;
+      if (first && !device_input && remaining > C) target = C / 4;
+      else if (!device_input && remaining > C && remaining <= C + C / 4) target = remaining - C / 4;
+      if (target < 1) target = 1;
+      int64_t e = d;
+      while (e < n_docs && (e == d || off_at(offsets, is64, e + 1) - b0 <= target)) e++;
+      chunks.push_back({d, e, b0, off_at(offsets, is64, e)});
+      max_n = std::max(max_n, e - d); max_b = std::max(max_b, off_at(offsets, is64, e) - b0);
+      d = e;
+      first = false;
+    }
   }
   if ((rc = ensure_chunk_buffers(p, max_n, max_b, !device_input))) return rc;
 
