@@ -292,21 +292,25 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
     const uint32_t fw = W / 32 + 1;
     uint32_t count = W;     // positions still in play: all, or list[0 .. count)
     bool pruned = false;
+    uint32_t cur = 0;       // level of the keys in A.H (0: none yet)
     for (uint32_t n = 1; n <= ntop_max && count; n++) {
+      if (!((top_levels >> n) & 1ull)) continue;  // only configured levels run a pass; the keys jump levels in registers
       const uint32_t cn = W - n + 1;
-      for (uint32_t k = g.tid; k < count; k += g.size()) {
-        const uint32_t i = pruned ? (uint32_t)list[k] : k;
-        if (i >= cn) continue;
-        if (n == 1) { A.H[i] = wh[i]; continue; }
-        const uint32_t j = i + n - 1;
-        Hash2 jj = tb_unpack(A.H[i]); jj.push(' ');
-        A.H[i] = tb_hcat(jj, tb_unpack(wh[j]), tb_pow_pack(a.uc.powtab, woff[j + 1] - woff[j])).pack();
-      }
-      if (!((top_levels >> n) & 1ull)) { g.sync(); continue; }
       const uint32_t T = rep_tab_size(count);
       for (uint32_t i = g.tid; i < T; i += g.size()) tab[i] = EMPTY;
       for (uint32_t i = g.tid; i < fw; i += g.size()) A.flag[i] = 0;
-      for (uint32_t k = g.tid; k < count; k += g.size()) cnt[pruned ? (uint32_t)list[k] : k] = 0;
+      for (uint32_t k = g.tid; k < count; k += g.size()) {
+        const uint32_t i = pruned ? (uint32_t)list[k] : k;
+        cnt[i] = 0;
+        if (i >= cn) continue;
+        Hash2 h = tb_unpack(cur ? A.H[i] : wh[i]);
+        for (uint32_t j = i + (cur ? cur : 1u); j < i + n; j++) {
+          h.push(' ');
+          h = tb_hcat(h, tb_unpack(wh[j]), tb_pow_pack(a.uc.powtab, woff[j + 1] - woff[j]));
+        }
+        A.H[i] = h.pack();
+      }
+      cur = n;
       g.sync();
       bool hit = false;
       for (uint32_t k = g.tid; k < count; k += g.size()) {
@@ -363,17 +367,23 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
     }
   }
   // -- duplicate n-grams: keys are the concatenated strings (find_all_duplicate, text.rs:241-259)
+  uint32_t dcur = 0;  // level of the keys in A.H (0: none yet)
   for (uint32_t n = 1; n <= ndup_max; n++) {
+    if (!((dup_levels >> n) & 1ull)) continue;  // only configured levels run a pass; the keys jump levels in registers
     const uint32_t cn = W - n + 1;
-    for (uint32_t i = g.tid; i < cn; i += g.size()) {
-      if (n == 1) { A.H[i] = wh[i]; continue; }
-      uint32_t j = i + n - 1;
-      A.H[i] = tb_hcat(tb_unpack(A.H[i]), tb_unpack(wh[j]), tb_pow_pack(a.uc.powtab, woff[j + 1] - woff[j])).pack();
-    }
-    g.sync();
-    if ((dup_levels >> n) & 1ull) {
+    {
       const uint32_t T = rep_tab_size(cn);
-      rep_fill(g, tab, T, EMPTY);
+      // one sweep: clear the table, bring the keys from level dcur to level n
+      for (uint32_t i = g.tid; i < T; i += g.size()) {
+        tab[i] = EMPTY;
+        if (i >= cn) continue;
+        Hash2 h = tb_unpack(dcur ? A.H[i] : wh[i]);
+        for (uint32_t j = i + (dcur ? dcur : 1u); j < i + n; j++)
+          h = tb_hcat(h, tb_unpack(wh[j]), tb_pow_pack(a.uc.powtab, woff[j + 1] - woff[j]));
+        A.H[i] = h.pack();
+      }
+      dcur = n;
+      g.sync();
       bool dup = false;
       for (uint32_t i = g.tid; i < cn; i += g.size()) {
         const uint64_t key = A.H[i];
