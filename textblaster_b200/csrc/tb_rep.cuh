@@ -303,10 +303,10 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
         const uint32_t i = pruned ? (uint32_t)list[k] : k;
         cnt[i] = 0;
         if (i >= cn) continue;
-        Hash2 h = tb_unpack(cur ? A.H[i] : wh[i]);
+        Hash2 h = tb_unpack(cur ? A.H[i] : TB_LDG(wh + i));
         for (uint32_t j = i + (cur ? cur : 1u); j < i + n; j++) {
           h.push(' ');
-          h = tb_hcat(h, tb_unpack(wh[j]), tb_pow_pack(a.uc.powtab, woff[j + 1] - woff[j]));
+          h = tb_hcat(h, tb_unpack(TB_LDG(wh + j)), tb_pow_pack(a.uc.powtab, woff[j + 1] - woff[j]));
         }
         A.H[i] = h.pack();
       }
@@ -374,12 +374,13 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
     {
       const uint32_t T = rep_tab_size(cn);
       // one sweep: clear the table, bring the keys from level dcur to level n
+#pragma unroll 2
       for (uint32_t i = g.tid; i < T; i += g.size()) {
         tab[i] = EMPTY;
         if (i >= cn) continue;
-        Hash2 h = tb_unpack(dcur ? A.H[i] : wh[i]);
+        Hash2 h = tb_unpack(dcur ? A.H[i] : TB_LDG(wh + i));
         for (uint32_t j = i + (dcur ? dcur : 1u); j < i + n; j++)
-          h = tb_hcat(h, tb_unpack(wh[j]), tb_pow_pack(a.uc.powtab, woff[j + 1] - woff[j]));
+          h = tb_hcat(h, tb_unpack(TB_LDG(wh + j)), tb_pow_pack(a.uc.powtab, woff[j + 1] - woff[j]));
         A.H[i] = h.pack();
       }
       dcur = n;
