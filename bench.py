@@ -23,8 +23,21 @@ import sys
 import threading
 import time
 
-# stdout carries exactly one JSON line: whatever NCCL has to say (e.g. its version banner) goes to stderr
+# stdout carries exactly one JSON line: anything libraries print there (NCCL's version banner, for one) is
+# sent to stderr by pointing fd 1 at fd 2 for the duration of the run; emit() writes to the real stdout
 os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+_REAL_STDOUT = None
+
+
+def guard_stdout():
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
+
+
+def emit(line: dict):
+    os.write(_REAL_STDOUT if _REAL_STDOUT is not None else 1, (json.dumps(line) + "\n").encode())
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
@@ -184,7 +197,7 @@ def run_reference(args, rank, world):
                              "sample": f"{sample} docs ({off[-1] / 1e6:.1f} MB) per step, C++ restatement of the reference CPU chain (the Rust reference cannot be built here)"},
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "keep_rate": float(r.keep.mean())}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def main():
@@ -199,6 +212,7 @@ def main():
     ap.add_argument("--with-fineweb", action="store_true",
                     help="append FineWebQualityFilter (SURVEY 8(f) row 3) to the chain; not the headline workload")
     args = ap.parse_args()
+    guard_stdout()
     args.warmup = max(args.warmup, 0)
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -345,7 +359,7 @@ def main():
         }
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(utf8, off, steps)
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
