@@ -30,7 +30,7 @@ struct WarpGroup {
   TB_D uint32_t sum(uint32_t v) const { return simt_sum(v); }
   TB_D uint64_t sum64(uint64_t v) const { return simt_sum64(v); }
   TB_D uint64_t max64(uint64_t v) const { return simt_max64(v); }
-  TB_D bool any(bool p) const { return simt_any(p); }
+  TB_D bool any(bool p) const { simt_sync(); return simt_any(p); }  // also a barrier with memory ordering, like the CTA's
   TB_D uint32_t exscan(uint32_t v, uint32_t* total) const { return simt_exscan(v, tid, total); }
   TB_D uint32_t bcast(uint32_t v) const { return simt_shfl(v, 0); }
 };
@@ -329,9 +329,8 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
           sl = rep_next(sl, T);
         }
       }
-      g.sync();
       uint64_t best = 0;
-      const bool any_hit = g.any(hit);
+      const bool any_hit = g.any(hit);  // (a barrier: the counts are complete)
       if (any_hit) {
         for (uint32_t k = g.tid; k < count; k += g.size()) {
           const uint32_t i = pruned ? (uint32_t)list[k] : k;
@@ -397,9 +396,8 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
         }
         cnt[i] = (IdxT)sl;  // the slot of this key; resolved to its first position below
       }
-      g.sync();
       uint64_t v = 0;
-      if (g.any(dup)) {
+      if (g.any(dup)) {  // (a barrier: the table is complete)
         // fo[i] = smallest position carrying the same key
         for (uint32_t i = g.tid; i < cn; i += g.size()) cnt[i] = (IdxT)tab[cnt[i]];
         g.sync();
@@ -412,7 +410,7 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
           if ((double)v / text_char_len > cfg.dup_frac[k]) reasons |= 1u << (TB_GR_REASON_DUP_SHIFT + k);
         }
       }
-      g.sync();
+      // no barrier here: the next level's sweep only follows g.any() above or the one that ends rep_dup_walk
     }
   }
   if (g.tid == 0) {
