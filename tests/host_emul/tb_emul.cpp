@@ -1,7 +1,7 @@
 // tb_emul.cpp -- TEST INFRASTRUCTURE ONLY (never linked into or loaded by the product).
 //
 // Runs the exact warp bodies of the CUDA kernels (textblaster_b200/csrc/tb_bodies.cuh) on the host:
-// 32 threads play the lanes of a warp, warp collectives become barriers (tb_simt.cuh, TB_HOST_EMUL).
+// 32 fibers play the lanes of a warp, warp collectives become barriers (tb_simt.cuh, TB_HOST_EMUL).
 // It exists so that the kernel logic can be checked against the oracle on a machine with no GPU
 // (`pytest -m "not gpu"`); the GPU tests check the real kernels through the C ABI.  Scratch memory
 // is filled with garbage first, like cudaMalloc'd memory, to expose reads of unwritten slots.
@@ -11,7 +11,6 @@
 #include <cstring>
 #include <functional>
 #include <string>
-#include <thread>
 #include <vector>
 
 #include "../../textblaster_b200/csrc/tb_bodies.cuh"
@@ -26,48 +25,97 @@ extern "C" void tbe_stats(uint64_t* tiles, uint64_t* walk) { *tiles = tbe_stat_t
 
 namespace {
 
-// Launch `fn(d, lane)` for every document as one emulated warp (32 threads in lock step at the
+// ---- fibers: the lanes of a group share one host thread and run round-robin between barriers ------------
+#if defined(__x86_64__)
+extern "C" void tbe_switch(void** save_sp, void* load_sp);
+asm(".text\n.globl tbe_switch\n.type tbe_switch,@function\ntbe_switch:\n"
+    "  pushq %rbp\n  pushq %rbx\n  pushq %r12\n  pushq %r13\n  pushq %r14\n  pushq %r15\n"
+    "  movq %rsp, (%rdi)\n  movq %rsi, %rsp\n"
+    "  popq %r15\n  popq %r14\n  popq %r13\n  popq %r12\n  popq %rbx\n  popq %rbp\n  ret\n"
+    ".size tbe_switch,.-tbe_switch\n");
+#else
+#error "the host emulation harness switches fibers with x86-64 code"
+#endif
+struct FiberGroup {
+  int n = 0, cur = 0, done = 0;
+  std::vector<void*> sp;
+  std::vector<char*> stacks;
+  void* main_sp = nullptr;
+  const std::function<void(int)>* body = nullptr;
+};
+FiberGroup* g_fibers = nullptr;  // one group at a time (the harness is single-threaded)
+constexpr size_t kFiberStack = 256 << 10;
+void fiber_entry() {
+  FiberGroup* g = g_fibers;
+  const int me = g->cur;
+  (*g->body)(me);
+  g->done++;
+  void* dummy;
+  if (g->done == g->n) tbe_switch(&dummy, g->main_sp);
+  const int nx = (me + 1) % g->n;
+  g->cur = nx; simt_lane = nx;
+  tbe_switch(&dummy, g->sp[nx]);
+  abort();
+}
+// run body(0) .. body(n - 1) as fibers; a barrier inside hands over to the next one
+void run_fibers(int n, const std::function<void(int)>& body) {
+  FiberGroup g;
+  g.n = n; g.body = &body; g.sp.resize(n); g.stacks.resize(n);
+  for (int i = 0; i < n; i++) {
+    char* st = (char*)malloc(kFiberStack);
+    g.stacks[i] = st;
+    uintptr_t top = ((uintptr_t)st + kFiberStack) & ~(uintptr_t)15;
+    void** q = (void**)top;
+    *--q = nullptr;                 // return address of fiber_entry (never used)
+    *--q = (void*)&fiber_entry;     // `ret` of the first switch lands here
+    for (int k = 0; k < 6; k++) *--q = nullptr;
+    g.sp[i] = q;
+  }
+  g_fibers = &g;
+  g.cur = 0; simt_lane = 0;
+  tbe_switch(&g.main_sp, g.sp[0]);
+  g_fibers = nullptr;
+  for (char* st : g.stacks) free(st);
+}
+}  // namespace
+void simt_fiber_yield() {
+  FiberGroup* g = g_fibers;
+  const int me = g->cur, nx = (me + 1) % g->n;
+  g->cur = nx; simt_lane = nx;
+  tbe_switch(&g->sp[me], g->sp[nx]);
+}
+namespace {
+
+// Launch `fn(d, lane)` for every document as one emulated warp (32 lanes in lock step at the
 // collectives).  `pred(d)` is the warp-uniform early-exit test of the __global__ wrapper.
 void run_warps(int64_t n, const std::function<bool(int64_t)>& pred, const std::function<void(int64_t, int)>& fn) {
   SimtWarp warp;
-  std::vector<std::thread> th;
-  for (int lane = 0; lane < 32; lane++) {
-    th.emplace_back([&, lane]() {
-      simt_warp = &warp; simt_lane = lane;
-      for (int64_t d = 0; d < n; d++) {
-        bool go = pred(d);
-        warp.bar.arrive_and_wait();  // every lane has sampled the predicate before anyone runs
-        if (!go) continue;
-        fn(d, lane);
-        warp.bar.arrive_and_wait();  // kernels never share state between warps mid-flight
-      }
-    });
-  }
-  for (auto& t : th) t.join();
+  simt_warp = &warp;
+  run_fibers(32, [&](int lane) {
+    for (int64_t d = 0; d < n; d++) {
+      bool go = pred(d);
+      warp.bar.arrive_and_wait();  // every lane has sampled the predicate before anyone runs
+      if (!go) continue;
+      fn(d, lane);
+      warp.bar.arrive_and_wait();  // kernels never share state between warps mid-flight
+    }
+  });
 }
 
 // One emulated CTA of `nthreads` threads per listed document (block-level collectives only).
 void run_blocks(const uint32_t* list, uint32_t count, int nthreads, const std::function<void(int64_t, int)>& fn) {
   SimtBlock blk(nthreads);
-  std::vector<std::thread> th;
-  for (int t = 0; t < nthreads; t++) {
-    th.emplace_back([&, t]() {
-      simt_block = &blk;
-      for (uint32_t i = 0; i < count; i++) { fn((int64_t)list[i], t); blk.bar.arrive_and_wait(); }
-    });
-  }
-  for (auto& t : th) t.join();
+  simt_block = &blk;
+  run_fibers(nthreads, [&](int t) {
+    for (uint32_t i = 0; i < count; i++) { fn((int64_t)list[i], t); blk.bar.arrive_and_wait(); }
+  });
 }
 void run_warps_list(const uint32_t* list, uint32_t count, const std::function<void(int64_t, int)>& fn) {
   SimtWarp warp;
-  std::vector<std::thread> th;
-  for (int lane = 0; lane < 32; lane++) {
-    th.emplace_back([&, lane]() {
-      simt_warp = &warp; simt_lane = lane;
-      for (uint32_t i = 0; i < count; i++) { fn((int64_t)list[i], lane); warp.bar.arrive_and_wait(); }
-    });
-  }
-  for (auto& t : th) t.join();
+  simt_warp = &warp;
+  run_fibers(32, [&](int lane) {
+    for (uint32_t i = 0; i < count; i++) { fn((int64_t)list[i], lane); warp.bar.arrive_and_wait(); }
+  });
 }
 
 template <class T> T* garbage(size_t n) {

@@ -2,9 +2,9 @@
 //
 // Device build: thin wrappers over the CUDA intrinsics (full-warp masks only).
 // TB_HOST_EMUL build (tests/host_emul, test infrastructure only, never linked into the shipped
-// library): 32 host threads play the lanes of one warp; every collective is a barrier plus an
-// exchange through a small per-warp mailbox, atomics are GCC builtins.  This lets the exact kernel
-// bodies run against the oracle on a machine without a GPU.
+// library): the lanes of one warp (or the threads of one CTA) are fibers of one host thread, run round-robin;
+// every collective is a barrier (= a switch to the next lane) plus an exchange through a small mailbox,
+// atomics are GCC builtins.  This lets the exact kernel bodies run against the oracle on a machine without a GPU.
 #pragma once
 #include <stdint.h>
 
@@ -32,20 +32,23 @@ TB_D int simt_ffs(uint32_t v) { return __ffs(v); }
 
 #else  // ---------------------------------------------------------------- host emulation
 
-#include <barrier>
 #include <cstring>
 
+// Defined by the harness: suspends the calling lane and runs every other lane of the group up to its next
+// barrier.  All lanes execute the same sequence of barriers (full-mask collectives only), so this is a barrier.
+void simt_fiber_yield();
+struct SimtBar { void arrive_and_wait() { simt_fiber_yield(); } };
 struct SimtWarp {
-  std::barrier<> bar{32};
+  SimtBar bar;
   uint64_t box[32];
 };
 extern thread_local SimtWarp* simt_warp;
 extern thread_local int simt_lane;
 struct SimtBlock {  // one emulated CTA of n threads (block-level collectives only)
   int n;
-  std::barrier<> bar;
+  SimtBar bar;
   uint64_t box[1024];
-  explicit SimtBlock(int n_) : n(n_), bar(n_) {}
+  explicit SimtBlock(int n_) : n(n_) {}
 };
 extern thread_local SimtBlock* simt_block;
 
