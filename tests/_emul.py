@@ -1,6 +1,6 @@
 """Loader for the host emulation harness (tests/host_emul/tb_emul.cpp) -- test infrastructure.
 
-It runs the kernel bodies with 32 host threads standing in for the lanes of a warp, so the kernel
+It runs the kernel bodies with 32 fibers of one host thread standing in for the lanes of a warp, so the kernel
 logic can be compared with the oracle without a GPU.  Never imported by the product package."""
 import ctypes as C
 import os
@@ -53,7 +53,7 @@ def run_chain(steps, texts):
     failed = np.zeros(n + 1, np.int8)
     stats = [np.zeros(n + 1, _abi.stats_dtype(t)) for t in types]
     sp = (C.c_void_p * max(len(steps), 1))(*[s.ctypes.data for s in stats])
-    content = np.zeros(len(blob) + 64, np.uint8)
+    content = np.zeros(len(blob) + len(blob) // 2 + 2 * n + 128, np.uint8)  # sentence-wise lines can outgrow the input
     coff = np.zeros(n + 2, np.int64)
     rc = lib().tbe_run_chain(C.addressof(arr), len(steps), blob.ctypes.data, off.ctypes.data, n, keep.ctypes.data,
                              failed.ctypes.data, C.addressof(sp), content.ctypes.data, coff.ctypes.data)

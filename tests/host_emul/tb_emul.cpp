@@ -140,7 +140,9 @@ extern "C" int tbe_run_chain(const tb_step_cfg* steps, size_t n_steps, const uin
   auto G64 = [&](size_t c) { auto* p = garbage<int64_t>(c); frees.push_back(p); return p; };
   const int64_t base = n ? offsets[0] : 0;
   const int64_t nb = n ? offsets[n] - base : 0;
-  const size_t n1 = (size_t)n + 1, units = (size_t)nb / 2 + n1 + 1, lines = (size_t)nb + n1 + 1;
+  bool any_sent = false;
+  for (size_t s = 0; s < n_steps; s++) any_sent |= steps[s].type == TB_STEP_C4_QUALITY && !steps[s].u.c4.split_paragraph;
+  const size_t n1 = (size_t)n + 1, units = (any_sent ? tb_grown_bytes(nb, n) : (size_t)nb) / 2 + n1 + 1;
   // tables
   std::vector<uint64_t> pw(TB_POWTAB);
   { uint32_t a = 1, b = 1; for (int i = 0; i < TB_POWTAB; i++) { pw[i] = ((uint64_t)a << 32) | b; a = tb_mm(a, TB_B1); b = tb_mm(b, TB_B2); } }
@@ -217,10 +219,24 @@ extern "C" int tbe_run_chain(const tb_step_cfg* steps, size_t n_steps, const uin
       uint32_t* ftab = G32(2 * TB_FW_SMEM_LINES);
       run_warps(n, alive_pred, [&](int64_t d, int lane) { body_fw_fin(b, ftab, f, fs, (int)s, (tb_fw_stats*)stats, d, lane); });
     } else if (sc.type == TB_STEP_C4_QUALITY) {
-      if (!sc.u.c4.split_paragraph || has_c4) return 5;
+      if (has_c4) return 5;
       C4Cfg cfg = tb_c4cfg_of(sc.u.c4);
-      C4Scratch cs{G8((size_t)nb + 64), G8((size_t)nb + 64), G64(n1), G32(n1), G32(n1), G32(lines), G32(lines), G32(lines),
+      const bool sent = !sc.u.c4.split_paragraph;
+      const size_t cb = sent ? tb_grown_bytes(nb, n) : (size_t)nb, clines = cb + n1 + 1;
+      C4Scratch cs{G8(cb + 64), G8(cb + 64), G64(n1), G32(n1), G32(n1), G32(clines), G32(clines), G32(clines),
                    G64(n1), G64(n1), G64(n1), G64(n1), G32(4 * n1)};
+      const KBatch b_in = b;
+      if (sent) {  // one sentence per line into S (the launch sequence of enqueue_chain)
+        uint32_t* bits = G32((size_t)nb / 32 + 4);
+        memset(bits, 0, ((size_t)nb / 32 + 4) * 4);
+        uint8_t* S = G8(cb + 64);
+        int64_t *srs = G64(n1), *sre = G64(n1);
+        for (int64_t d = 0; d < n; d++) body_trim(b, ascii, ts, te, d);
+        uint8_t* sstage = (uint8_t*)G64(TB_SENT_STAGE_BYTES / 8 + 2);
+        for (int64_t d = 0; d < n; d++) if (!alive[d]) { srs[d] = tb_sent_off(rs[d], d); sre[d] = srs[d]; }
+        run_warps(n, alive_pred, [&](int64_t d, int lane) { body_c4_sent(b, ascii, sstage, ts, te, bits, S, srs, sre, d, lane); });
+        b.text = S; b.rs = srs; b.re = sre; b.ext_hi = (int64_t)cb;
+      }
       build_lut(TB_LUT_C4A, 0u);
       uint8_t* cstage = (uint8_t*)G64(TB_STAGE_BYTES / 8 + 2);
       run_warps(n, alive_pred, [&](int64_t d, int lane) { body_c4_a(b, ascii, lut.data(), cstage, cfg, cs, d, lane); });
@@ -230,6 +246,7 @@ extern "C" int tbe_run_chain(const tb_step_cfg* steps, size_t n_steps, const uin
       run_warps(n, [&](int64_t) { return true; }, [&](int64_t d, int lane) { body_c4_c(b, cstage, cfg, cs, d, lane); });
       { KBatch fb = b; fb.text = cs.F; fb.rs = cs.frs; fb.re = cs.fre; for (int64_t d = 0; d < n; d++) body_trim(fb, ascii, cs.frs, cs.fre, d); }
       run_warps(n, alive_pred, [&](int64_t d, int lane) { body_c4_d(b, ascii, cfg, cs, (int)s, (tb_c4_stats*)stats, rewritten, rs, re, d, lane); });
+      b.rs = b_in.rs; b.re = b_in.re;
       b.text = cs.F;
       has_c4 = true;
     } else {

@@ -24,6 +24,9 @@ C4_SHIPPED = C4QualityParams(True, True, True, 5, 3, 1000, True, True, True, Tru
 C4_ONE_SENT = C4QualityParams(True, True, True, 1, 3, 1000, True, True, True, True)
 C4_LAX = C4QualityParams(True, False, False, 1, 1, 50, False, False, False, False)
 C4_NOPUNCT = C4QualityParams(True, True, False, 1, 2, 1000, False, True, False, True)
+# split_paragraph = false: lines are the pieces of split_into_sentences (c4_filters.rs:152-155)
+C4_SENT = C4QualityParams(False, True, True, 2, 3, 1000, True, True, True, True)
+C4_SENT_LAX = C4QualityParams(False, False, False, 1, 1, 50, False, False, False, False)
 
 # FineWebQualityFilter: shipped thresholds (config/pipeline_config.yaml:74-80), a permissive
 # variant that lets every counter be compared, and a custom stop-character set with non-ASCII members
@@ -43,6 +46,9 @@ CHAINS = {
     "c4_lax": [C4_LAX],
     "c4_nopunct": [C4_NOPUNCT],
     "c4_shipped": [C4_SHIPPED],
+    "c4_sentences": [C4_SENT],
+    "c4_sentences_lax": [C4_SENT_LAX],
+    "sentences_then_open": [C4_SENT_LAX, GQ_OPEN, GR_OPEN],
     "baseline_order": [C4_SHIPPED, GQ_DEFAULT_SW, GR_SHIPPED],      # BASELINE.json config 2 order
     "shipped_order": [GR_SHIPPED, GQ_SHIPPED, C4_SHIPPED],          # config/pipeline_config.yaml order
     "c4_then_open": [C4_ONE_SENT, GQ_OPEN, GR_OPEN],

@@ -89,6 +89,34 @@ def test_general_word_path_matches(monkeypatch):
         _check(name, texts)
 
 
+SENTENCE_LINE_DOCS = [
+    "a?b?c?d", "?a?a?a", "Hello.World and more", "Stop! Go now? Yes.", "foo.\n\nbar.", "x one two.\r\ny three four.", "  \n  ",
+    "One two three.  Four five six.\nSeven eight nine!\n\n\n  Ten eleven twelve?  ", "a.\rb c d.\r\re f g.",
+    "He said \"stop.\" Then left (quickly.) And more words here.", "e.g. this is not a break. But this one is.",
+    "Dr. Smith went home. 3.5 apples fell.", "Line\u2028sep here now.\u2029Para sep here now.\u0085Next line here now.",
+    "Wait...really? Yes!!! No?! Sure.", "\u3053\u308c\u306f\u6587\u3067\u3059\u3002\u6b21\u306e\u6587\u3067\u3059\u3002final one here.",
+    "ends with spaces and newline.   \n", "\n\n  leading newlines here. And more text.", "no terminator at all",
+    "This has a citation [1]. And another [2, 3] one here. Please enable javascript now. We use cookies here.",
+    "a.\u00a0b c d. e f g.\u3000h i j.", "x" * 40 + "? " + "y" * 1100 + ". z z z.",
+    " ".join("Sentence number %d is here." % i for i in range(120)),
+    "\n".join("w%d? next%d" % (i, i) for i in range(300)),
+]
+
+
+def boundary_sentence_docs():
+    """terminators and separators around the 32-byte stretch and 1 KiB tile edges"""
+    out = []
+    for pad in (28, 29, 30, 31, 32, 33, 1020, 1021, 1022, 1023, 1024, 1025):
+        for sep in ("? ", "?", ".\n", ". \n ", "!\r\n", ".\u2029", "?\u00a0", ".) "):
+            out.append("a" * pad + sep + "Bcd efg hij." + sep + "k l m.")
+    return out
+
+
+@pytest.mark.parametrize("name", ["c4_sentences", "c4_sentences_lax", "sentences_then_open"])
+def test_sentence_wise_lines(name):  # split_paragraph = false, c4_filters.rs:152-155
+    _check(name, SENTENCE_LINE_DOCS + boundary_sentence_docs())
+
+
 def split_ambiguity_docs():
     """find_all_duplicate keys are bare concatenations (text.rs:250): "no where" and "now here" give the same
     key although the word sequences differ, and such a pair need not share any shorter repeated n-gram.

@@ -14,7 +14,7 @@ import multilingual
 import oracle
 from parity_cases import CHAINS, GQ_OPEN, GR_OPEN, step_types
 from parity_util import compare
-from test_emul_parity import GOLDEN_DOCS, fineweb_docs, split_ambiguity_docs
+from test_emul_parity import GOLDEN_DOCS, SENTENCE_LINE_DOCS, boundary_sentence_docs, fineweb_docs, split_ambiguity_docs
 from test_oracle_golden import C4_LINE_CASES, c4_default
 from textblaster_b200 import _abi, synth
 from textblaster_b200.config import GopherRepetitionParams
@@ -128,6 +128,30 @@ def test_general_word_path_matches(name):
 def test_fineweb_documents(name):
     rng = random.Random(9)
     check_texts(name, fineweb_docs() + [fuzzgen.english_doc(rng, sz) for sz in (300, 2000, 9000, 40000)] + multilingual.corpus(5, 200))
+
+
+@pytest.mark.parametrize("name", ["c4_sentences", "c4_sentences_lax", "sentences_then_open"])
+def test_sentence_wise_lines(name):  # split_paragraph = false, c4_filters.rs:152-155
+    rng = random.Random(23)
+    texts = SENTENCE_LINE_DOCS + boundary_sentence_docs() + fuzzgen.boundary_docs()[:80]
+    texts += [fuzzgen.english_doc(rng, sz) for sz in (300, 1024, 2500, 9000, 40000, 150000)] + multilingual.corpus(7, 150)
+    check_texts(name, texts)
+
+
+def test_sentence_wise_lines_corpus_and_chunks():
+    """BASELINE config 2 shape with sentences as lines; the rewritten text can outgrow a chunk's input."""
+    utf8, off = synth.generate(8000, seed=synth.BASE_SEED + 6)
+    p = GpuBatchPipeline(CHAINS["sentences_then_open"])
+    ref, _ = check_packed("sentences_then_open", utf8, off, p)
+    p.set_option(_abi.TB_OPT_CHUNK_BYTES, 1 << 18)
+    r = p.run_packed(utf8, off)
+    assert np.array_equal(r.keep, ref.keep) and np.array_equal(r.failed_step, ref.failed_step)
+    _same_stats(r, ref)
+    assert np.array_equal(r.content, ref.content) and np.array_equal(r.content_offsets, ref.content_offsets)
+    grow = ["?".join("ab" for _ in range(4000))] * 50  # every break adds a byte
+    rg = p.run_texts(grow)
+    assert rg.content_of(0) == grow[0].replace("?", "?\n") and int(rg.content_offsets[-1]) > sum(len(t) for t in grow)
+    p.close()
 
 
 def test_ngram_split_ambiguity():

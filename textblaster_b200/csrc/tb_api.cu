@@ -106,6 +106,7 @@ size_t stat_size(int type) {
 struct StepHost {
   int type;
   C4Cfg c4;
+  bool c4_sentences = false;  // split_paragraph = false: lines are sentences (c4_filters.rs:152-155)
   GqCfg gq;
   GrCfg gr;
   FwCfg fw;
@@ -146,6 +147,7 @@ struct tb_pipeline {
   // FineWeb scratch
   DevBuf f_lh, f_ll, f_doc, f_tab;
   // C4 scratch
+  DevBuf c_S, c_bits, c_srs, c_sre;  // sentence-wise lines
   DevBuf c_P, c_F, c_plen, c_nlines, c_docflags, c_lwc, c_lmax, c_lflags, c_prs, c_pre, c_frs, c_fre, c_cnt;
   cudaEvent_t ev_h2d[2] = {nullptr, nullptr}, ev_done[2] = {nullptr, nullptr}, ev_d2h[2] = {nullptr, nullptr}, ev_small[2] = {nullptr, nullptr};
   std::vector<ResultSet*> results;
@@ -295,11 +297,15 @@ int ensure_chunk_buffers(tb_pipeline* p, int64_t n, int64_t nb, bool host_input)
   size_t n1 = (size_t)n + 1;
 #define ENS(buf, bytes) if ((rc = (buf).ensure(bytes))) return rc
   if (host_input) { for (int i = 0; i < 2; i++) { ENS(p->text[i], (size_t)nb + 64); ENS(p->offs[i], n1 * 8); } }
-  for (int i = 0; i < 2; i++) ENS(p->packed[i], (size_t)nb + 64);
+  // with sentence-wise lines the rewritten text can outgrow the input (tb_sent_off)
+  bool sent = false;
+  for (auto& sh : p->steps) sent |= sh.type == TB_STEP_C4_QUALITY && sh.c4_sentences;
+  const size_t cb = sent ? tb_grown_bytes(nb, n) : (size_t)nb;
+  for (int i = 0; i < 2; i++) ENS(p->packed[i], cb + 64);
   ENS(p->rs0, n1 * 8); ENS(p->re0, n1 * 8); ENS(p->rs, n1 * 8); ENS(p->re, n1 * 8); ENS(p->ts, n1 * 8); ENS(p->te, n1 * 8);
   for (int i = 0; i < 2; i++) { ENS(p->alive[i], n1); ENS(p->failed[i], n1); ENS(p->out_off[i], (n1 + 1) * 8); }
   ENS(p->rewritten, n1); ENS(p->len, n1 * 8); ENS(p->bad, 16); ENS(p->cursors, 256); ENS(p->order, n1 * 4); ENS(p->sizecls, n1);
-  size_t units = (size_t)nb / 2 + n1 + 1;
+  size_t units = cb / 2 + n1 + 1;  // word / line slots are indexed by the position of the document in its buffer
   for (size_t s = 0; s < p->steps.size(); s++) {
     const StepHost& sh = p->steps[s];
     for (int i = 0; i < 2; i++) ENS(p->stats[s][i], n1 * stat_size(sh.type));
@@ -311,8 +317,9 @@ int ensure_chunk_buffers(tb_pipeline* p, int64_t n, int64_t nb, bool host_input)
     } else if (sh.type == TB_STEP_FINEWEB_QUALITY) {
       ENS(p->f_lh, units * 8); ENS(p->f_ll, units * 4); ENS(p->f_doc, n1 * sizeof(FwDoc)); ENS(p->f_tab, (units * 2 + n1 * 16) * 4);
     } else if (sh.type == TB_STEP_C4_QUALITY) {
-      size_t lines = (size_t)nb + n1 + 1;
-      ENS(p->c_P, (size_t)nb + 64); ENS(p->c_F, (size_t)nb + 64);
+      size_t lines = cb + n1 + 1;
+      ENS(p->c_P, cb + 64); ENS(p->c_F, cb + 64);
+      if (sh.c4_sentences) { ENS(p->c_S, cb + 64); ENS(p->c_bits, ((size_t)nb / 32 + 4) * 4); ENS(p->c_srs, n1 * 8); ENS(p->c_sre, n1 * 8); }
       ENS(p->c_plen, n1 * 8); ENS(p->c_nlines, n1 * 4); ENS(p->c_docflags, n1 * 4);
       ENS(p->c_lwc, lines * 4); ENS(p->c_lmax, lines * 4); ENS(p->c_lflags, lines * 4);
       ENS(p->c_prs, n1 * 8); ENS(p->c_pre, n1 * 8); ENS(p->c_frs, n1 * 8); ENS(p->c_fre, n1 * 8); ENS(p->c_cnt, n1 * 16);
@@ -369,6 +376,15 @@ int enqueue_chain(tb_pipeline* p, const uint8_t* text, int64_t n, int64_t nbytes
       C4Scratch cs{p->c_P.as<uint8_t>(), p->c_F.as<uint8_t>(), p->c_plen.as<int64_t>(), p->c_nlines.as<uint32_t>(),
                    p->c_docflags.as<uint32_t>(), p->c_lwc.as<uint32_t>(), p->c_lmax.as<uint32_t>(), p->c_lflags.as<uint32_t>(),
                    p->c_prs.as<int64_t>(), p->c_pre.as<int64_t>(), p->c_frs.as<int64_t>(), p->c_fre.as<int64_t>(), p->c_cnt.as<uint32_t>()};
+      const KBatch b_in = b;  // rs / re of the chain: pass D writes the ranges of the rewritten documents there
+      if (sh.c4_sentences) {  // one sentence per line into S; the line passes then run on S
+        CK(cudaMemsetAsync(p->c_bits.p, 0, ((size_t)nbytes / 32 + 4) * 4, st));
+        { Timed t(p, "k_trim"); tb_launch_trim(st, b, p->ts.as<int64_t>(), p->te.as<int64_t>()); }
+        { Timed t(p, "k_c4_sent"); tb_launch_c4_sent(st, b, p->ts.as<int64_t>(), p->te.as<int64_t>(), p->c_bits.as<uint32_t>(), p->c_S.as<uint8_t>(),
+                                                     p->c_srs.as<int64_t>(), p->c_sre.as<int64_t>(), c->sm_count, cursors + 50); }
+        b.text = p->c_S.as<uint8_t>(); b.rs = p->c_srs.as<int64_t>(); b.re = p->c_sre.as<int64_t>();
+        b.ext_hi = (int64_t)tb_grown_bytes(nbytes, n);
+      }
       { Timed t(p, "k_c4_a"); tb_launch_c4_a(st, b, sh.c4, cs, c->sm_count, cursors + TB_MAX_STEPS + s); }
       { Timed t(p, "k_c4_b"); tb_launch_c4_b(st, b, sh.c4, cs, c->sm_count, cursors + s); }
       { Timed t(p, "k_c4_c"); tb_launch_c4_c(st, b, sh.c4, cs, c->sm_count, cursors + 2 * TB_MAX_STEPS + s); }
@@ -376,7 +392,8 @@ int enqueue_chain(tb_pipeline* p, const uint8_t* text, int64_t n, int64_t nbytes
         KBatch fb = b; fb.text = cs.F; fb.rs = cs.frs; fb.re = cs.fre;
         Timed t(p, "k_trim"); tb_launch_trim(st, fb, cs.frs, cs.fre);
       }
-      { Timed t(p, "k_c4_d"); tb_launch_c4_d(st, b, sh.c4, cs, (int)s, p->stats[s][pb].as<tb_c4_stats>(), p->rewritten.as<uint8_t>(), c->sm_count, cursors + 3 * TB_MAX_STEPS + s); }
+      { Timed t(p, "k_c4_d"); tb_launch_c4_d(st, b, sh.c4, cs, (int)s, p->stats[s][pb].as<tb_c4_stats>(), p->rewritten.as<uint8_t>(), (int64_t*)b_in.rs, (int64_t*)b_in.re, c->sm_count, cursors + 3 * TB_MAX_STEPS + s); }
+      b.rs = b_in.rs; b.re = b_in.re;
       b.text = cs.F;  // every document still alive now lives in F
       *has_c4 = true;
     }
@@ -401,6 +418,8 @@ int run_impl(tb_pipeline* p, const uint8_t* utf8, const void* offsets, int is64,
   bool any_c4 = false;
   for (auto& s : p->steps) any_c4 |= s.type == TB_STEP_C4_QUALITY;
   const bool want_content = any_c4 && p->opt_return_content;
+  bool sent_mode = false;
+  for (auto& s : p->steps) sent_mode |= s.type == TB_STEP_C4_QUALITY && s.c4_sentences;
 
   ResultSet* rsx = acquire_results(p);
   out->_owner = rsx;
@@ -410,7 +429,7 @@ int run_impl(tb_pipeline* p, const uint8_t* utf8, const void* offsets, int is64,
   for (size_t s = 0; s < p->steps.size(); s++) if ((rc = rsx->stats[s].ensure(n1 * stat_size(p->steps[s].type)))) return rc;
   const int64_t base0 = n_docs ? off_at(offsets, is64, 0) : 0;
   const int64_t total_bytes = n_docs ? off_at(offsets, is64, n_docs) - base0 : 0;
-  if (want_content) { if ((rc = rsx->content.ensure((size_t)total_bytes + 64)) || (rc = rsx->content_off.ensure(n1 * 8))) return rc; }
+  if (want_content) { if ((rc = rsx->content.ensure((sent_mode ? tb_grown_bytes(total_bytes, n_docs) : (size_t)total_bytes) + 64)) || (rc = rsx->content_off.ensure(n1 * 8))) return rc; }
   for (int64_t i = 0; i < n_docs; i++) if (off_at(offsets, is64, i + 1) < off_at(offsets, is64, i)) return fail(TB_ERR_INVALID_ARGUMENT, "offsets must be non-decreasing");
 
   // chunk plan.  Large chunks cost the least device time (every launch ends with a tail), but the first copy
@@ -598,8 +617,6 @@ int tb_pipeline_create(tb_ctx* ctx, const tb_step_cfg* steps, size_t n_steps, tb
     int rc = validate_step(steps[i]);
     if (rc) return rc;
     n_c4 += steps[i].type == TB_STEP_C4_QUALITY;
-    if (steps[i].type == TB_STEP_C4_QUALITY && !steps[i].u.c4.split_paragraph)
-      return fail(TB_ERR_UNSUPPORTED, "C4QualityFilter: split_paragraph = false (sentence-wise lines) is not implemented on the GPU path");
   }
   if (n_c4 > 1) return fail(TB_ERR_UNSUPPORTED, "at most one C4QualityFilter step per pipeline");
   CK(cudaSetDevice(ctx->device));
@@ -612,6 +629,7 @@ int tb_pipeline_create(tb_ctx* ctx, const tb_step_cfg* steps, size_t n_steps, tb
     if (sh.type == TB_STEP_C4_QUALITY) {
       const tb_c4_params& q = steps[i].u.c4;
       sh.c4 = tb_c4cfg_of(q);
+      sh.c4_sentences = !q.split_paragraph;
     } else if (sh.type == TB_STEP_GOPHER_QUALITY) {
       const tb_gq_params& q = steps[i].u.gq;
       sh.gq = GqCfg{q.has, q.min_doc_words, q.max_doc_words, q.min_stop_words, q.min_avg_word_length, q.max_avg_word_length,
@@ -652,7 +670,7 @@ void tb_pipeline_destroy(tb_pipeline* p) {
   cudaDeviceSynchronize();
   for (DevBuf* b : {&p->text[0], &p->text[1], &p->offs[0], &p->offs[1], &p->packed[0], &p->packed[1], &p->rs0, &p->re0, &p->rs,
                     &p->re, &p->ts, &p->te, &p->alive[0], &p->alive[1], &p->failed[0], &p->failed[1], &p->rewritten, &p->len, &p->out_off[0], &p->out_off[1], &p->bad, &p->cursors, &p->order, &p->sizecls, &p->g_wh,
-                    &p->g_wl, &p->g_lh, &p->g_ll, &p->g_lg, &p->g_doc, &p->g_work, &p->g_lists, &p->g_counters, &p->f_lh, &p->f_ll, &p->f_doc, &p->f_tab, &p->c_P, &p->c_F, &p->c_plen, &p->c_nlines,
+                    &p->g_wl, &p->g_lh, &p->g_ll, &p->g_lg, &p->g_doc, &p->g_work, &p->g_lists, &p->g_counters, &p->f_lh, &p->f_ll, &p->f_doc, &p->f_tab, &p->c_S, &p->c_bits, &p->c_srs, &p->c_sre, &p->c_P, &p->c_F, &p->c_plen, &p->c_nlines,
                     &p->c_docflags, &p->c_lwc, &p->c_lmax, &p->c_lflags, &p->c_prs, &p->c_pre, &p->c_frs, &p->c_fre, &p->c_cnt})
     b->release();
   for (auto& b : p->stats) { b[0].release(); b[1].release(); }

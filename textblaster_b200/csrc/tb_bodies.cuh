@@ -496,6 +496,68 @@ TB_D void body_c4_d(const KBatch& a, const uint16_t* s_ascii, const C4Cfg& cfg, 
   if (st.reason_bits) { a.alive[d] = 0; a.failed[d] = (int8_t)step; }
 }
 
+// Sentence-wise lines (split_paragraph = false: `lines = split_into_sentences(content)`, c4_filters.rs:152-155).
+// The document is rewritten into S so that str::lines() of the result yields exactly the reference's pieces
+// (up to outer white space, which pass A trims per line like the reference does, :193), and the line passes
+// above then run on S unchanged:
+//   * only the trimmed text is copied (text.rs:60);
+//   * every '\n' is dropped -- a piece always ends right after one (SB4), so none is interior to a piece;
+//   * a '\n' goes in front of the first non-white-space character of every piece but the first; pieces that
+//     are white space only (dropped by text.rs:80-86) thereby melt into the end of the line before them.
+// S can be longer than the text: a break that follows no white space ("a?b") adds a byte.  Such a break
+// closes a piece of at least two bytes, so doc d fits into [soff(d), soff(d + 1)), soff(d) = rs + rs / 2 + 2 d.
+#define TB_SENT_STAGE_BYTES (TB_TILE + TB_TILE / 2 + 32)
+TB_HD int64_t tb_sent_off(int64_t rs, int64_t d) { return rs + (rs >> 1) + 2 * d; }
+struct SentMark {
+  uint32_t* bits; uint32_t mis;
+  TB_D void operator()(int64_t q) { const uint64_t k = (uint64_t)q + mis; simt_atomic_or(&bits[k >> 5], 1u << (uint32_t)(k & 31u)); }
+};
+TB_D void body_c4_sent(const KBatch& a, const uint16_t* s_ascii, uint8_t* stage, const int64_t* ts, const int64_t* te,
+                       uint32_t* bits, uint8_t* S, int64_t* srs, int64_t* sre, int64_t d, int lane) {
+  Classifier C{s_ascii, a.uc};
+  TextRange R{a.text, ts[d], te[d]};
+  const int64_t o0 = tb_sent_off(a.rs[d], d);
+  if (R.rs >= R.re) { if (lane == 0) { srs[d] = o0; sre[d] = o0; } return; }
+  SentMark mark{bits, (uint32_t)((uintptr_t)a.text & 31u)};
+  // pass 1: where the pieces begin (bit per byte; a mark can land in a later stretch or tile)
+  for (int64_t base = tb_tile_origin(R); base < R.re; base += TB_TILE) {
+    uint32_t w[8];
+    const int64_t p0 = base + lane * TB_STRETCH;
+    const uint32_t V = tile_load(R, a.ext_lo, a.ext_hi, p0, w);
+    if (!V) continue;
+    uint32_t hi = 0;
+#pragma unroll
+    for (int k = 0; k < 8; k++) hi |= (((((w[k] & (w[k] << 1)) & 0x80808080u) >> 7) * 0x00204081u >> 21) & 15u) << (4 * k);
+    const uint32_t ev = (tile_eq_mask(w, '.') | tile_eq_mask(w, '!') | tile_eq_mask(w, '?') | tile_eq_mask(w, '\n') |
+                         tile_eq_mask(w, '\r') | hi) & V;
+    tb_sentence_starts_events(C, R, p0, ev, mark);
+  }
+  simt_sync();
+  // pass 2: copy without the '\n' bytes, a '\n' in front of every marked byte
+  uint8_t* out = S + o0;
+  int64_t outpos = 0;
+  for (int64_t base = tb_tile_origin(R); base < R.re; base += TB_TILE) {
+    uint32_t w[8];
+    const int64_t p0 = base + lane * TB_STRETCH;
+    const uint32_t V = tile_load(R, a.ext_lo, a.ext_hi, p0, w);
+    uint32_t INS = 0;
+    if (V) INS = simt_load_fresh(&bits[((uint64_t)p0 + mark.mis) >> 5]) & V;
+    const uint32_t KEEP = V & ~tile_eq_mask(w, '\n');
+    uint32_t tot, pre = simt_exscan((uint32_t)(tb_popc32(KEEP) + tb_popc32(INS)), lane, &tot);
+    uint32_t o = pre;
+#pragma unroll
+    for (int k = 0; k < 32; k++) {
+      if ((INS >> k) & 1u) stage[o++] = '\n';
+      if ((KEEP >> k) & 1u) stage[o++] = (uint8_t)(w[k >> 2] >> (8 * (k & 3)));
+    }
+    simt_sync();
+    for (uint32_t k = (uint32_t)lane; k < tot; k += 32) out[outpos + k] = stage[k];
+    simt_sync();
+    outpos += tot;
+  }
+  if (lane == 0) { srs[d] = o0; sre[d] = o0 + outpos; }
+}
+
 // ---------------------------------------------------------------------------------------------
 // final content
 // ---------------------------------------------------------------------------------------------

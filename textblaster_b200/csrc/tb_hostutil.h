@@ -52,6 +52,9 @@ inline C4Cfg tb_c4cfg_of(const tb_c4_params& q) {
                q.min_num_sentences, q.min_words_per_line, q.max_word_length};
 }
 
+// bytes the sentence-per-line copy of a chunk (nb bytes, n documents) can take: see tb_sent_off (tb_bodies.cuh)
+inline size_t tb_grown_bytes(int64_t nb, int64_t n) { return (size_t)nb + (size_t)nb / 2 + 2 * (size_t)n + 64; }
+
 // UcTables::wslead: the lead bytes of the non-ASCII White_Space characters, from the cinfo trie
 inline void tb_compute_wslead(const uint16_t* stage1, const uint16_t* stage2, uint32_t out[8]) {
   for (int i = 0; i < 8; i++) out[i] = 0;

@@ -170,6 +170,19 @@ __global__ void __launch_bounds__(TB_BLOCK, 24) k_c4_a(KBatch a, C4Cfg cfg, C4Sc
     if (a.alive[d]) body_c4_a(a, s_ascii, s_lut, s_stage, cfg, s, d, threadIdx.x & 31);
   }
 }
+__global__ void __launch_bounds__(TB_BLOCK, 16) k_c4_sent(KBatch a, const int64_t* ts, const int64_t* te, uint32_t* bits, uint8_t* S,
+                                                          int64_t* srs, int64_t* sre, uint32_t* cursor) {
+  __shared__ uint16_t s_ascii[192];
+  __shared__ __align__(16) uint8_t s_stage[TB_SENT_STAGE_BYTES];
+  load_ascii(s_ascii, a.uc);
+  for (;;) {
+    const int64_t d = next_doc(cursor, a);
+    if (d == -1) break;
+    if (d < 0) continue;
+    if (a.alive[d]) body_c4_sent(a, s_ascii, s_stage, ts, te, bits, S, srs, sre, d, threadIdx.x & 31);
+    else if ((threadIdx.x & 31) == 0) { srs[d] = tb_sent_off(a.rs[d], d); sre[d] = srs[d]; }
+  }
+}
 __global__ void __launch_bounds__(TB_BLOCK, 20) k_c4_b(KBatch a, C4Cfg cfg, C4Scratch s, uint32_t* cursor) {
   __shared__ uint16_t s_ascii[192];
   __shared__ LutEntry s_lut[256];
@@ -316,6 +329,10 @@ int tb_kernels_init() {
 void tb_launch_c4_a(cudaStream_t st, const KBatch& b, const C4Cfg& cfg, const C4Scratch& s, int sm_count, uint32_t* cursor) {
   if (b.n) k_c4_a<<<persistent_grid(b.n, sm_count, 24), TB_BLOCK, 0, st>>>(b, cfg, s, cursor);
 }
+void tb_launch_c4_sent(cudaStream_t st, const KBatch& b, const int64_t* ts, const int64_t* te, uint32_t* bits, uint8_t* S,
+                       int64_t* srs, int64_t* sre, int sm_count, uint32_t* cursor) {
+  if (b.n) k_c4_sent<<<persistent_grid(b.n, sm_count, 16), TB_BLOCK, 0, st>>>(b, ts, te, bits, S, srs, sre, cursor);
+}
 void tb_launch_c4_b(cudaStream_t st, const KBatch& b, const C4Cfg& cfg, const C4Scratch& s, int sm_count, uint32_t* cursor) {
   if (b.n) k_c4_b<<<persistent_grid(b.n, sm_count, 20), TB_BLOCK, 0, st>>>(b, cfg, s, cursor);
 }
@@ -323,9 +340,9 @@ void tb_launch_c4_c(cudaStream_t st, const KBatch& b, const C4Cfg& cfg, const C4
   if (b.n) k_c4_c<<<persistent_grid(b.n, sm_count, 32), TB_BLOCK, 0, st>>>(b, cfg, s, cursor);
 }
 void tb_launch_c4_d(cudaStream_t st, const KBatch& b, const C4Cfg& cfg, const C4Scratch& s, int step, tb_c4_stats* out,
-                    uint8_t* rewritten, int sm_count, uint32_t* cursor) {
-  // the new ranges are written over the batch's own rs/re (only for documents that were rewritten)
-  if (b.n) k_c4_d<<<persistent_grid(b.n, sm_count, 24), TB_BLOCK, 0, st>>>(b, cfg, s, step, out, rewritten, (int64_t*)b.rs, (int64_t*)b.re, cursor);
+                    uint8_t* rewritten, int64_t* rs_out, int64_t* re_out, int sm_count, uint32_t* cursor) {
+  // the new ranges go to rs_out / re_out (the chain's rs / re), only for documents that were rewritten
+  if (b.n) k_c4_d<<<persistent_grid(b.n, sm_count, 24), TB_BLOCK, 0, st>>>(b, cfg, s, step, out, rewritten, rs_out, re_out, cursor);
 }
 void tb_launch_final_len(cudaStream_t st, int64_t n, const int64_t* rs0, const int64_t* re0, const int64_t* rs,
                          const int64_t* re, const uint8_t* rewritten, int64_t* len) {

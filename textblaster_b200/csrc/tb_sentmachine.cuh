@@ -154,6 +154,45 @@ TB_HD uint32_t tb_count_sentences_events(const Classifier& C, const TextRange& R
   }
   return count;
 }
+// Same events, but reporting WHERE each non-empty piece after the first begins: the position of its first
+// non-white-space character (for SB11 breaks that is the break position itself).  Used by the
+// sentence-wise line mode of C4 (split_paragraph = false, c4_filters.rs:152-155).  `mark(q)` is called once
+// per piece; R is the trimmed text (text.rs:60).
+template <class Mark>
+TB_HD void tb_sentence_starts_events(const Classifier& C, const TextRange& R, int64_t p0, uint32_t ev, Mark& mark) {
+  const uint8_t* t = R.t;
+  while (ev) {
+#if defined(__CUDA_ARCH__)
+    const uint32_t bit = (uint32_t)__ffs((int)ev) - 1u;
+#else
+    const uint32_t bit = (uint32_t)__builtin_ctz(ev);
+#endif
+    ev &= ev - 1;
+    const int64_t i = p0 + bit;
+    int len; uint32_t cp;
+    const uint32_t ci = C.at(t, i, &len, &cp);
+    const uint32_t cls = CI_SB(ci);
+    if (BIT(cls) & SB_PARASEPMASK) {                                   // SB4
+      int64_t j = i + len;
+      if (!(cls == SB_CR && j < R.re && tb_byte(t, j) == '\n')) {     // SB3: CR x LF
+        while (j < R.re) { int l2; uint32_t c2; uint32_t i2 = C.at(t, j, &l2, &c2); if (BIT(CI_SB(i2)) & SB_PARASEPMASK) break; if (!(i2 & CI_WS)) { mark(j); break; } j += l2; }
+      }
+    } else if (BIT(cls) & SB_SATERMMASK) {                             // SB11
+      SbState s;
+      sb_sync(C, R, i, s);
+      sb_advance(s, cls);
+      int64_t j = i + len;
+      while (j < R.re && s.st != 0) {
+        int l2; uint32_t c2;
+        uint32_t k2 = CI_SB(C.at(t, j, &l2, &c2));
+        if (sb_break_before(C, R, s, k2, j)) { mark(j); break; }
+        if (BIT(k2) & SB_SATERMMASK) break;
+        sb_advance(s, k2);
+        j += l2;
+      }
+    }
+  }
+}
 // (a): the segment that starts the text counts iff a non-white-space character comes before the first separator
 TB_HD uint32_t tb_count_sentences_start(const Classifier& C, const TextRange& R) {
   const uint8_t* t = R.t;

@@ -27,6 +27,8 @@ TB_D uint32_t simt_atomic_add(uint32_t* a, uint32_t v) { return atomicAdd(a, v);
 TB_D uint32_t simt_atomic_min(uint32_t* a, uint32_t v) { return atomicMin(a, v); }
 TB_D uint32_t simt_atomic_max(uint32_t* a, uint32_t v) { return atomicMax(a, v); }
 TB_D uint32_t simt_atomic_or(uint32_t* a, uint32_t v) { return atomicOr(a, v); }
+// a word other lanes of this warp have updated with simt_atomic_or since the last simt_sync
+TB_D uint32_t simt_load_fresh(const uint32_t* a) { return __ldcg(a); }
 TB_D int simt_popc(uint32_t v) { return __popc(v); }
 TB_D int simt_ffs(uint32_t v) { return __ffs(v); }
 
@@ -101,6 +103,7 @@ inline uint32_t simt_atomic_max(uint32_t* a, uint32_t v) {
   while (v > old && !__atomic_compare_exchange_n(a, &old, v, false, __ATOMIC_SEQ_CST, __ATOMIC_SEQ_CST)) {}
   return old;
 }
+inline uint32_t simt_load_fresh(const uint32_t* a) { return __atomic_load_n(a, __ATOMIC_SEQ_CST); }
 inline int simt_popc(uint32_t v) { return __builtin_popcount(v); }
 inline int simt_ffs(uint32_t v) { return __builtin_ffs((int)v); }
 
