@@ -57,7 +57,7 @@ typedef enum {
 
 /* C4QualityParams, src/config/pipeline.rs:66-79; field meaning src/pipeline/filters/c4_filters.rs:98-139 */
 typedef struct tb_c4_params {
-  int32_t split_paragraph;
+  int32_t split_paragraph;          /* 1: lines = str::lines(); 0: lines = split_into_sentences() (c4_filters.rs:150-155) */
   int32_t remove_citations;
   int32_t filter_no_terminal_punct;
   int32_t filter_lorem_ipsum;

@@ -60,6 +60,10 @@ static void test_c4() {  // c4_filters.rs:594-790
   C4QualityFilter g(true, true, true, 1, 3, 1000, true, true, true, true);
   out = g.process(doc("rewrite", "This line is kept[1] as it is.\nPlease enable javascript to view this.\nWe use cookies on this site.\nShort one."));
   CHECK(out.content == "This line is kept as it is.");
+  // split_paragraph = false: the lines are the sentences (c4_filters.rs:152-155); "Yes." has too few words
+  C4QualityFilter h(false, true, true, 1, 3, 1000, true, true, true, true);
+  out = h.process(doc("sentences", "Stop right now please! Go there now? Yes."));
+  CHECK(out.content == "Stop right now please!\nGo there now?");
 }
 
 static void test_gopher_quality() {  // gopher_quality.rs:360-829
