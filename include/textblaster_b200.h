@@ -267,7 +267,12 @@ typedef struct tb_ctx tb_ctx;
 typedef struct tb_pipeline tb_pipeline;
 
 /* Creates the per-device context (streams, Unicode tables in HBM).  Replaces nothing in the
- * reference (it has no device); lifetime = the worker's `Arc<PipelineExecutor>` (src/bin/worker.rs:149). */
+ * reference (it has no device); lifetime = the worker's `Arc<PipelineExecutor>` (src/bin/worker.rs:149).
+ * Threads: the reference shares one executor between all worker tasks (ProcessingStep: Send + Sync,
+ * src/bin/worker.rs:149, src/worker_logic.rs:260-264).  Here every entry point may be called from any host thread;
+ * calls on one tb_pipeline are serialised by the pipeline (it owns one set of device buffers), pipelines of one
+ * context may run at the same time (their kernels share the context's streams), and results do not depend on
+ * either. */
 int tb_ctx_create(int device, tb_ctx** out);
 void tb_ctx_destroy(tb_ctx* ctx);
 /* Thread-local text of the last failure on this thread (ctx may be NULL). */

@@ -200,6 +200,36 @@ def test_device_resident_entry_point():
     p.close()
 
 
+def test_concurrent_callers():
+    """ProcessingStep is Send + Sync and one executor is shared by all worker tasks (bin/worker.rs:149,
+    worker_logic.rs:260-264): calls on one pipeline from several host threads, and on several pipelines of one
+    context at once, give the results of the same calls made one after the other."""
+    import threading
+    utf8, off = synth.generate(4000, seed=77, median_bytes=1500)
+    shared = GpuBatchPipeline(CHAINS["baseline_order"])
+    own = [GpuBatchPipeline(CHAINS[name]) for name in ("shipped_order", "c4_then_open", "gr_shipped")]
+    jobs = [(shared, 0, 1500), (shared, 1000, 3000), (shared, 2500, 4000)] + [(p, 500 * k, 500 * k + 2500) for k, p in enumerate(own)]
+    serial = [p.run_packed(utf8, off[a:b + 1]) for p, a, b in jobs]
+    got = [None] * len(jobs)
+
+    def work(k):
+        p, a, b = jobs[k]
+        for _ in range(3):
+            got[k] = p.run_packed(utf8, off[a:b + 1])
+
+    th = [threading.Thread(target=work, args=(k,)) for k in range(len(jobs))]
+    for t in th:
+        t.start()
+    for t in th:
+        t.join()
+    for r, ref in zip(got, serial):
+        assert r is not None and np.array_equal(r.keep, ref.keep) and np.array_equal(r.failed_step, ref.failed_step)
+        _same_stats(r, ref)
+        assert np.array_equal(r.content, ref.content) and np.array_equal(r.content_offsets, ref.content_offsets)
+    for p in [shared] + own:
+        p.close()
+
+
 def test_empty_and_degenerate_batches():
     p = pipe("baseline_order")
     r = p.run_packed(np.zeros(0, np.uint8), np.zeros(1, np.int64))
