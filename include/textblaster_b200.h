@@ -305,7 +305,7 @@ void tb_batch_out_release(tb_pipeline* p, tb_batch_out* out);
 enum {
   TB_OPT_RETURN_CONTENT = 1, /* [1] copy rewritten content back to the host */
   TB_OPT_VALIDATE_UTF8 = 2,  /* [0] check inputs on the device, TB_ERR_INVALID_UTF8 on failure */
-  TB_OPT_CHUNK_BYTES = 3,    /* [256 MiB] H2D staging chunk */
+  TB_OPT_CHUNK_BYTES = 3,    /* [1 GiB] largest chunk the batch is processed in (device scratch: ~45 bytes per byte of it) */
   TB_OPT_GENERAL_WORD_PATH = 4 /* [0] testing: run the segment-walking word passes for every document (same results, slower) */
 };
 int tb_pipeline_set_option(tb_pipeline* p, int32_t option, int64_t value);

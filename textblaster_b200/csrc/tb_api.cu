@@ -8,6 +8,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <chrono>
 #include <mutex>
 #include <string>
 #include <vector>
@@ -135,7 +136,7 @@ struct tb_ctx {
 struct tb_pipeline {
   tb_ctx* ctx = nullptr;
   std::vector<StepHost> steps;
-  int64_t opt_return_content = 1, opt_validate = 0, opt_chunk = 256ll << 20, opt_debug = 0;
+  int64_t opt_return_content = 1, opt_validate = 0, opt_chunk = 1024ll << 20, opt_debug = 0;
   std::mutex mu;
   // device buffers (grow-only)
   DevBuf text[2], offs[2], packed[2];
@@ -411,6 +412,9 @@ int run_impl(tb_pipeline* p, const uint8_t* utf8, const void* offsets, int is64,
              const int64_t* offsets_dev, tb_batch_out* out) {
   tb_ctx* c = p->ctx;
   CK(cudaSetDevice(c->device));
+  static const bool trace = getenv("TB_TRACE") != nullptr;  // host-side timeline of one call on stderr
+  const auto t_entry = std::chrono::steady_clock::now();
+  auto since = [&]() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_entry).count(); };
   memset(out, 0, sizeof *out);
   out->n_docs = n_docs;
   out->n_steps = (int32_t)p->steps.size();
@@ -432,29 +436,49 @@ int run_impl(tb_pipeline* p, const uint8_t* utf8, const void* offsets, int is64,
   if (want_content) { if ((rc = rsx->content.ensure((sent_mode ? tb_grown_bytes(total_bytes, n_docs) : (size_t)total_bytes) + 64)) || (rc = rsx->content_off.ensure(n1 * 8))) return rc; }
   for (int64_t i = 0; i < n_docs; i++) if (off_at(offsets, is64, i + 1) < off_at(offsets, is64, i)) return fail(TB_ERR_INVALID_ARGUMENT, "offsets must be non-decreasing");
 
-  // chunk plan.  Large chunks cost the least device time (every launch ends with a tail), but the first copy
-  // to the device and the last copy back are not hidden behind kernels: from host memory the first chunk is a
-  // quarter of the target, and a short remainder is split so that the last chunk is a quarter as well.
+  // chunk plan.  Large chunks cost the least device time (every launch of the chain ends with a tail: about
+  // 90 us per launch, measured), but the copy of the first chunk to the device and the copy of the last
+  // chunk's results back are not hidden behind kernels.  So the sizes ramp: from host memory they start small
+  // and double (the copy engine moves text ~2.5x faster than the kernels consume it, so the next chunk is
+  // always there in time), they stay at the configured size, and they shrink by thirds at the end (the
+  // results of a chunk leave while the next, smaller one is computed).
   std::vector<Chunk> chunks;
   int64_t max_n = 0, max_b = 0;
   {
-    const int64_t C = p->opt_chunk, end_b = n_docs ? off_at(offsets, is64, n_docs) : 0;
-    bool first = true;
+    const int64_t C = std::max<int64_t>(p->opt_chunk, 1), B = total_bytes;
+    const int64_t lo_up = std::min<int64_t>(C, 64ll << 20), lo_down = std::min<int64_t>(C, 48ll << 20);
+    std::vector<int64_t> up, down;  // ramp sizes, smallest first
+    if (!device_input) for (int64_t v = lo_up; v < C; v *= 2) up.push_back(v);
+    for (int64_t v = lo_down; v < C; v *= 3) down.push_back(v);
+    // take ramp steps from both ends, smallest first, while they fit; what is left is the plateau
+    std::vector<int64_t> head, tail;
+    int64_t used = 0;
+    for (size_t k = 0; k < std::max(up.size(), down.size()); k++) {
+      if (k < up.size() && used + up[k] <= B) { head.push_back(up[k]); used += up[k]; }
+      if (k < down.size() && used + down[k] <= B) { tail.push_back(down[k]); used += down[k]; }
+    }
+    std::vector<int64_t> targets = head;
+    const int64_t mid = B - used;
+    if (mid > 0) { const int64_t k = (mid + C - 1) / C; for (int64_t i = 0; i < k; i++) targets.push_back((mid + k - 1) / k); }
+    for (size_t k = tail.size(); k-- > 0;) targets.push_back(tail[k]);
+    if (targets.empty()) targets.push_back(C);
+    size_t ti = 0;
     for (int64_t d = 0; d < n_docs;) {
-      const int64_t b0 = off_at(offsets, is64, d), remaining = end_b - b0;
-      int64_t target = C;
-      if (first && !device_input && remaining > C) target = C / 4;
-      else if (!device_input && remaining > C && remaining <= C + C / 4) target = remaining - C / 4;
-      if (target < 1) target = 1;
+      const int64_t b0 = off_at(offsets, is64, d);
+      const int64_t target = targets[std::min(ti, targets.size() - 1)];
+      ti++;
       int64_t e = d;
       while (e < n_docs && (e == d || off_at(offsets, is64, e + 1) - b0 <= target)) e++;
+      if (ti >= targets.size()) {  // rounding left a few documents over: they join the last chunk if that keeps it <= C
+        if (off_at(offsets, is64, n_docs) - b0 <= C) e = n_docs;
+      }
       chunks.push_back({d, e, b0, off_at(offsets, is64, e)});
       max_n = std::max(max_n, e - d); max_b = std::max(max_b, off_at(offsets, is64, e) - b0);
       d = e;
-      first = false;
     }
   }
   if ((rc = ensure_chunk_buffers(p, max_n, max_b, !device_input))) return rc;
+  if (trace) fprintf(stderr, "[tb] %.2f ms: planned %zu chunks, buffers ready\n", since(), chunks.size());
 
   uint8_t* h_keep = rsx->keep.as<uint8_t>();
   int8_t* h_failed = rsx->failed.as<int8_t>();
@@ -483,6 +507,7 @@ int run_impl(tb_pipeline* p, const uint8_t* utf8, const void* offsets, int is64,
     const int buf = (int)(ci & 1);
     const int64_t n = ch.d1 - ch.d0;
     CK(cudaEventSynchronize(p->ev_small[buf]));
+    if (trace) fprintf(stderr, "[tb] %.2f ms: chunk %zu (%lld docs, %.0f MB) results on the host\n", since(), ci, (long long)n, (ch.b1 - ch.b0) / 1048576.0);
     if (p->opt_validate && h_bad) return fail(TB_ERR_INVALID_UTF8, "input contains " + std::to_string(h_bad) + " document(s) with invalid UTF-8 (first chunk doc " + std::to_string(ch.d0) + ")");
     if (want_content) {
       int64_t tot = h_coff[ch.d0 + n];
@@ -530,7 +555,9 @@ int run_impl(tb_pipeline* p, const uint8_t* utf8, const void* offsets, int is64,
     if (p->opt_validate) CK(cudaMemcpyAsync(&h_bad, p->bad.p, 4, cudaMemcpyDeviceToHost, c->d2h));
     CK(cudaEventRecord(p->ev_small[buf], c->d2h));
   }
+  if (trace) fprintf(stderr, "[tb] %.2f ms: all chunks enqueued\n", since());
   if (!chunks.empty()) if ((rc = finish(chunks.size() - 1))) return rc;
+  if (trace) fprintf(stderr, "[tb] %.2f ms: last chunk's kernels done\n", since());
   CK(cudaStreamSynchronize(c->compute));
   resolve_times(p);
   CK(cudaStreamSynchronize(c->d2h));
@@ -544,6 +571,7 @@ int run_impl(tb_pipeline* p, const uint8_t* utf8, const void* offsets, int is64,
   }
   out->gpu_ms = p->ms_this_run;
   out->gpu_launches = p->launches_this_run;
+  if (trace) fprintf(stderr, "[tb] %.2f ms: done (kernels %.2f ms)\n", since(), p->ms_this_run);
   return TB_OK;
 }
 
