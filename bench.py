@@ -305,6 +305,20 @@ def main():
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item()), launches, gpu_ms, kept, cbytes, clocks, pipe.kernel_times()
 
+    def h2d_probe():
+        """Pinned host -> device copy rate of this box (the step's own text buffer, CUDA events, best of 3)."""
+        best = 0.0
+        for _ in range(3):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            torch.cuda.synchronize()
+            e0.record()
+            d_text.copy_(holder["t"], non_blocking=True)
+            e1.record()
+            torch.cuda.synchronize()
+            best = max(best, holder["t"].numel() / (e0.elapsed_time(e1) * 1e-3) / 1e9)
+        return best
+
+    h2d_peak = h2d_probe() if holder["t"].is_pinned() else None
     dt_dev, launches, gpu_ms, kept, cbytes, clocks, ktimes = timed(step_device)
     dt_e2e, launches_e, gpu_ms_e, _, _, clocks_e, _ = timed(step_host)
     # host-side gather of the keep masks onto rank 0, ordered by row group (the only cross-rank traffic of the job)
@@ -354,6 +368,14 @@ def main():
                          "frac": achieved / peak if peak else None, "traffic": ncu_traffic(dom_name), "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": alg_bytes_launch, "avg_launch_ms": avg_ms,
                          "share_of_gpu_time": dom_ms / max(sum(v[0] for v in ktimes.values()), 1e-9)},
+            # the whole chain against HBM (algorithmic bytes / sum of kernel time) and the end-to-end
+            # run against the host-to-device link (bytes sent / wall time of the copy-overlapped pipeline)
+            "chain_hbm": {"achieved": alg_bytes_step * K / max(gpu_ms * 1e-3, 1e-12) / 1e9, "peak": peak, "unit": "GB/s",
+                          "frac": (alg_bytes_step * K / max(gpu_ms * 1e-3, 1e-12) / 1e9) / peak if peak else None},
+            "h2d_roofline": {"achieved": (n_bytes + 8 * (n_docs + 1)) * K / dt_e2e / 1e9, "peak": h2d_peak, "unit": "GB/s",
+                             "frac": ((n_bytes + 8 * (n_docs + 1)) * K / dt_e2e / 1e9) / h2d_peak if h2d_peak else None,
+                             "peak_source": "pinned host->device copy of this step's text buffer, measured in this run (best of 3)",
+                             "per_gpu": True},
             "kernels_ms_per_step": {k: round(v[0] / K, 3) for k, v in sorted(ktimes.items(), key=lambda kv: -kv[1][0])},
             "clocks": clocks,
         }
