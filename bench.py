@@ -128,12 +128,18 @@ def measured_peaks():
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
-def ncu_traffic(kernel):
-    """dram bytes per launch of the dominant kernel from the committed ncu capture, if any."""
+def ncu_traffic(kernel, alg_bytes_per_launch):
+    """dram bytes per launch of the dominant kernel from the committed ncu capture, if any.  The capture is of ONE
+    launch (whose algorithmic bytes the file records); launches differ in size, so the figure is scaled to the
+    average launch that `achieved` is quoted on."""
     p = os.path.join(ROOT, "profiles", "roofline_traffic.json")
     if os.path.exists(p):
         try:
-            return json.load(open(p)).get(kernel)
+            d = json.load(open(p))
+            t, cap = d.get(kernel), d.get("_captured_launch_algorithmic_bytes")
+            if t is None:
+                return None
+            return t * alg_bytes_per_launch / cap if cap else t
         except Exception:
             return None
     return None
@@ -365,7 +371,7 @@ def main():
                     "ms_per_step": dt_e2e / K * 1e3},
             "gpu_launches": launches,
             "roofline": {"bound": "hbm", "kernel": dom_name, "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak if peak else None, "traffic": ncu_traffic(dom_name), "peak_source": peak_src,
+                         "frac": achieved / peak if peak else None, "traffic": ncu_traffic(dom_name, alg_bytes_launch), "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": alg_bytes_launch, "avg_launch_ms": avg_ms,
                          "share_of_gpu_time": dom_ms / max(sum(v[0] for v in ktimes.values()), 1e-9)},
             # the whole chain against HBM (algorithmic bytes / sum of kernel time) and the end-to-end
