@@ -306,7 +306,12 @@ enum {
   TB_OPT_RETURN_CONTENT = 1, /* [1] copy rewritten content back to the host */
   TB_OPT_VALIDATE_UTF8 = 2,  /* [0] check inputs on the device, TB_ERR_INVALID_UTF8 on failure */
   TB_OPT_CHUNK_BYTES = 3,    /* [1 GiB] largest chunk the batch is processed in (device scratch: ~45 bytes per byte of it) */
-  TB_OPT_GENERAL_WORD_PATH = 4 /* [0] testing: run the segment-walking word passes for every document (same results, slower) */
+  TB_OPT_GENERAL_WORD_PATH = 4, /* [0] testing: run the segment-walking word passes for every document (same results, slower) */
+  TB_OPT_DECODE_HTML_ENTITIES = 5 /* [0] decode HTML entities before the first step, as the reference's reader does with
+                                     html_escape::decode_html_entities (src/pipeline/readers/parquet_reader.rs:178-179): pass the
+                                     Arrow buffers of the text column as they are.  The decoded text is the document's content
+                                     (content / content_offsets are then returned even without a C4 step).  Parity with the
+                                     html-escape crate is unpinned, see textblaster_b200/csrc/tb_entities.cuh */
 };
 int tb_pipeline_set_option(tb_pipeline* p, int32_t option, int64_t value);
 

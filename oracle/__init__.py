@@ -65,7 +65,7 @@ def lib():
         L.tbo_punctuation_contains.argtypes = [C.c_uint32]
         L.tbo_cinfo.restype = C.c_uint32
         L.tbo_cinfo.argtypes = [C.c_uint32]
-        for f in ("tbo_to_lowercase", "tbo_remove_citations"):
+        for f in ("tbo_to_lowercase", "tbo_remove_citations", "tbo_decode_html_entities"):
             getattr(L, f).restype = C.c_int64
             getattr(L, f).argtypes = [C.c_char_p, C.c_int64, C.c_char_p, C.c_int64]
         _lib = L
@@ -148,6 +148,14 @@ def to_lowercase(text: str) -> str:
     b = text.encode("utf-8")
     out = C.create_string_buffer(3 * len(b) + 8)
     n = lib().tbo_to_lowercase(b, len(b), out, len(out))
+    return out.raw[:n].decode("utf-8")
+
+
+def decode_html_entities(text: str) -> str:
+    """html_escape::decode_html_entities as restated in tb_oracle.cpp (parity unpinned)"""
+    b = text.encode("utf-8")
+    out = C.create_string_buffer(2 * len(b) + 8)
+    n = lib().tbo_decode_html_entities(b, len(b), out, len(out))
     return out.raw[:n].decode("utf-8")
 
 

@@ -19,6 +19,9 @@
 //        ICU4X's dictionary (Han/Kana) and LSTM (Thai/Lao/Khmer/Burmese) re-segmentation is NOT
 //        reproduced: documents containing those scripts are a declared divergence class.
 //   regex 1.11.1: \[\d+(?:,\s*\d+)*\] (Unicode \d = Nd, \s = White_Space), \n{2,}, \n+ as hand DFAs.
+//   html-escape 0.2.13: decode_html_entities (src/pipeline/readers/parquet_reader.rs:178-179, the reader row of
+//        SURVEY 8f) -> named references of the WHATWG list with their ';', "&#D;", "&#xH;"; PARITY UNPINNED (the
+//        reference has no test with an entity; the choices made are listed at decode_html_entities below).
 //   Rust std: char::is_whitespace / is_alphabetic, str::to_lowercase (incl. final sigma, U+0130),
 //        str::lines, str::trim*, str::matches.
 //
@@ -41,6 +44,8 @@
 
 #include "../include/textblaster_b200.h"
 #include "../textblaster_b200/csrc/unicode_tables.inc"
+struct EntEntry { char name[32]; uint8_t nlen, rlen; uint8_t repl[6]; };  // layout of the generated table
+#include "../textblaster_b200/csrc/entity_table.inc"
 
 namespace {
 
@@ -891,6 +896,65 @@ void run_one(const Pipeline& pl, const char* text, size_t len, int64_t i, BatchR
 // ---------------------------------------------------------------------------------------------
 // C API (ctypes)
 // ---------------------------------------------------------------------------------------------
+// ---- html-escape 0.2.13 decode_html_entities, restated (see the header: parity unpinned) -------------------------
+// One left-to-right scan.  After '&': "#" opens a numeric reference (an 'x' / 'X' makes it hexadecimal), anything
+// else a named one.  The reference ends at ';'.  A byte that cannot belong to it (names: ASCII letters and digits;
+// numbers: digits of the base) abandons the candidate and is looked at again as ordinary text, so a second '&'
+// starts a new candidate.  Numbers are parsed like str::parse::<u32> / u32::from_str_radix (overflow = error) and
+// mapped with char::from_u32 (surrogates and values above 0x10FFFF are errors; 0 is a character).  On any error
+// the text stays as it is.  A candidate of more than 40 bytes is not looked at (20+ leading zeros).
+static std::string decode_html_entities(const std::string& in) {
+  static const std::unordered_map<std::string, std::string> named = [] {
+    std::unordered_map<std::string, std::string> m;
+    for (int i = 0; i < TB_ENT_COUNT; i++) m.emplace(std::string(tb_ent_table[i].name, tb_ent_table[i].nlen), std::string((const char*)tb_ent_table[i].repl, tb_ent_table[i].rlen));
+    return m;
+  }();
+  std::string out;
+  out.reserve(in.size());
+  size_t i = 0;
+  const size_t n = in.size();
+  while (i < n) {
+    if (in[i] != '&') { out.push_back(in[i++]); continue; }
+    // candidate: find its end within 40 bytes
+    size_t j = i + 1;
+    bool ok = false;
+    std::string rep;
+    if (j < n && in[j] == '#') {
+      j++;
+      int base = 10;
+      if (j < n && (in[j] == 'x' || in[j] == 'X')) { base = 16; j++; }
+      const size_t d0 = j;
+      unsigned long long v = 0;
+      bool overflow = false;
+      while (j < n && j < i + 40) {
+        const unsigned char c = (unsigned char)in[j];
+        int dv = -1;
+        if (c >= '0' && c <= '9') dv = c - '0';
+        else if (base == 16 && c >= 'a' && c <= 'f') dv = c - 'a' + 10;
+        else if (base == 16 && c >= 'A' && c <= 'F') dv = c - 'A' + 10;
+        if (dv < 0) break;
+        v = v * (unsigned)base + (unsigned)dv;
+        if (v > 0xFFFFFFFFull) overflow = true, v = 0x100000000ull;
+        j++;
+      }
+      if (j < n && j < i + 40 && in[j] == ';' && j > d0 && !overflow && v <= 0x10FFFF && !(v >= 0xD800 && v <= 0xDFFF)) {
+        push_utf8(rep, (uint32_t)v);
+        ok = true;
+      }
+    } else {
+      const size_t n0 = j;
+      while (j < n && j < i + 40 && isalnum((unsigned char)in[j]) && (unsigned char)in[j] < 0x80) j++;
+      if (j < n && j < i + 40 && in[j] == ';' && j > n0) {
+        auto it = named.find(in.substr(n0, j - n0));
+        if (it != named.end()) { rep = it->second; ok = true; }
+      }
+    }
+    if (ok) { out += rep; i = j + 1; }
+    else out.push_back(in[i++]);  // the '&' is text; what follows is scanned again
+  }
+  return out;
+}
+
 extern "C" {
 
 void* tbo_pipeline_create(const tb_step_cfg* steps, size_t n) {
@@ -1006,6 +1070,11 @@ int tbo_punctuation_contains(uint32_t cp) { return is_punct(cp) ? 1 : 0; }
 uint32_t tbo_cinfo(uint32_t cp) { return cinfo(cp); }
 int64_t tbo_to_lowercase(const char* text, int64_t len, char* out, int64_t cap) {
   std::string s = to_lowercase(Str{text, (size_t)len});
+  if ((int64_t)s.size() <= cap) memcpy(out, s.data(), s.size());
+  return (int64_t)s.size();
+}
+int64_t tbo_decode_html_entities(const char* text, int64_t len, char* out, int64_t cap) {
+  std::string s = decode_html_entities(std::string(text, (size_t)len));
   if ((int64_t)s.size() <= cap) memcpy(out, s.data(), s.size());
   return (int64_t)s.size();
 }

@@ -26,7 +26,7 @@ def lib():
         L = C.CDLL(_SO)
         L.tbe_run_chain.restype = C.c_int
         L.tbe_run_chain.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p,
-                                    C.c_void_p, C.c_void_p, C.c_void_p]
+                                    C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
         _lib = L
     return _lib
 
@@ -35,7 +35,7 @@ class EmulResult:
     pass
 
 
-def run_chain(steps, texts):
+def run_chain(steps, texts, decode_entities=False):
     """steps: config param objects; texts: list[str].  Returns keep, failed_step, stats[], contents."""
     keepalive = []
     arr = (_abi.tb_step_cfg * max(len(steps), 1))()
@@ -53,10 +53,10 @@ def run_chain(steps, texts):
     failed = np.zeros(n + 1, np.int8)
     stats = [np.zeros(n + 1, _abi.stats_dtype(t)) for t in types]
     sp = (C.c_void_p * max(len(steps), 1))(*[s.ctypes.data for s in stats])
-    content = np.zeros(len(blob) + len(blob) // 2 + 2 * n + 128, np.uint8)  # sentence-wise lines can outgrow the input
+    content = np.zeros(3 * len(blob) + 8 * n + 512, np.uint8)  # sentence-wise lines can outgrow the input
     coff = np.zeros(n + 2, np.int64)
     rc = lib().tbe_run_chain(C.addressof(arr), len(steps), blob.ctypes.data, off.ctypes.data, n, keep.ctypes.data,
-                             failed.ctypes.data, C.addressof(sp), content.ctypes.data, coff.ctypes.data)
+                             failed.ctypes.data, C.addressof(sp), content.ctypes.data, coff.ctypes.data, 1 if decode_entities else 0)
     if rc not in (0, 100):
         raise RuntimeError(f"emulation failed rc={rc}")
     r = EmulResult()

@@ -16,6 +16,7 @@
 #include "../../textblaster_b200/csrc/tb_bodies.cuh"
 #include "../../textblaster_b200/csrc/tb_hostutil.h"
 #include "../../textblaster_b200/csrc/unicode_tables.inc"
+#include "../../textblaster_b200/csrc/entity_table.inc"
 
 thread_local SimtWarp* simt_warp = nullptr;
 thread_local int simt_lane = 0;
@@ -133,13 +134,14 @@ size_t stat_size(int type) {
 
 extern "C" int tbe_run_chain(const tb_step_cfg* steps, size_t n_steps, const uint8_t* utf8, const int64_t* offsets,
                              int64_t n, uint8_t* keep, int8_t* failed_out, void** stats_out, uint8_t* content_out,
-                             int64_t* content_off_out) {
+                             int64_t* content_off_out, int decode_entities) {
   std::vector<void*> frees;
   auto G8 = [&](size_t c) { auto* p = garbage<uint8_t>(c); frees.push_back(p); return p; };
   auto G32 = [&](size_t c) { auto* p = garbage<uint32_t>(c); frees.push_back(p); return p; };
   auto G64 = [&](size_t c) { auto* p = garbage<int64_t>(c); frees.push_back(p); return p; };
   const int64_t base = n ? offsets[0] : 0;
-  const int64_t nb = n ? offsets[n] - base : 0;
+  const int64_t nb_in = n ? offsets[n] - base : 0;
+  const int64_t nb = decode_entities ? (int64_t)tb_grown_bytes(nb_in, n) : nb_in;  // extent of the text the chain sees
   bool any_sent = false;
   for (size_t s = 0; s < n_steps; s++) any_sent |= steps[s].type == TB_STEP_C4_QUALITY && !steps[s].u.c4.split_paragraph;
   const size_t n1 = (size_t)n + 1, units = (any_sent ? tb_grown_bytes(nb, n) : (size_t)nb) / 2 + n1 + 1;
@@ -156,12 +158,24 @@ extern "C" int tbe_run_chain(const tb_step_cfg* steps, size_t n_steps, const uin
     if (!tb_ascii_class_ok(ascii[i])) return 7;  // the ASCII fast path would not be exact
   }
 
-  uint8_t* text = G8((size_t)nb + 64);
-  if (nb) memcpy(text, utf8 + base, (size_t)nb);
+  uint8_t* text = G8((size_t)nb_in + 64);
+  if (nb_in) memcpy(text, utf8 + base, (size_t)nb_in);
   int64_t *rs0 = G64(n1), *re0 = G64(n1), *rs = G64(n1), *re = G64(n1), *ts = G64(n1), *te = G64(n1), *len = G64(n1), *out_off = G64(n1 + 1);
   uint8_t *alive = G8(n1), *rewritten = G8(n1);
   int8_t* failed = (int8_t*)G8(n1);
   for (int64_t d = 0; d < n; d++) body_init_ranges(offsets, 1, 0, base, rs0, re0, alive, failed, d);
+  if (decode_entities) {  // the pre-pass of TB_OPT_DECODE_HTML_ENTITIES (run_impl): the decoded copy becomes the text
+    const size_t bw = (size_t)nb_in / 32 + 4;
+    uint32_t *amp = G32(bw), *drop = G32(bw);
+    memset(amp, 0, bw * 4); memset(drop, 0, bw * 4);
+    uint8_t* D = G8((size_t)nb + 64);
+    int64_t *drs = G64(n1), *dre = G64(n1);
+    uint8_t* estage = (uint8_t*)G64(TB_SENT_STAGE_BYTES / 8 + 2);
+    KBatch eb{text, rs0, re0, alive, failed, n, uc, 0, nb_in, 0u};
+    run_warps(n, [&](int64_t) { return true; }, [&](int64_t d, int lane) { body_entities(eb, estage, tb_ent_table, TB_ENT_COUNT, amp, drop, D, drs, dre, d, lane); });
+    memcpy(rs0, drs, (size_t)n * 8); memcpy(re0, dre, (size_t)n * 8);
+    text = D;
+  }
   memcpy(rs, rs0, (size_t)n * 8); memcpy(re, re0, (size_t)n * 8);
   memset(rewritten, 0, (size_t)n);
   const char* fw = getenv("TBE_FORCE_WALK");
@@ -256,7 +270,7 @@ extern "C" int tbe_run_chain(const tb_step_cfg* steps, size_t n_steps, const uin
   }
   memcpy(keep, alive, (size_t)n);
   memcpy(failed_out, failed, (size_t)n);
-  if (has_c4 && content_out) {
+  if ((has_c4 || decode_entities) && content_out) {
     for (int64_t d = 0; d < n; d++) body_final_len(rs0, re0, rs, re, rewritten, len, d);
     int64_t acc = 0;
     for (int64_t d = 0; d < n; d++) { out_off[d] = acc; acc += len[d]; }
@@ -266,5 +280,5 @@ extern "C" int tbe_run_chain(const tb_step_cfg* steps, size_t n_steps, const uin
     memcpy(content_off_out, out_off, n1 * 8);
   }
   for (void* p : frees) free(p);
-  return has_c4 ? 100 : 0;
+  return (has_c4 || decode_entities) ? 100 : 0;
 }

@@ -117,6 +117,44 @@ def test_sentence_wise_lines(name):  # split_paragraph = false, c4_filters.rs:15
     _check(name, SENTENCE_LINE_DOCS + boundary_sentence_docs())
 
 
+def entity_docs():
+    """HTML entities of every kind, well-formed and not, also sliding across the 32-byte stretch and 1 KiB tile edges"""
+    import html.entities
+    rng = random.Random(41)
+    names = sorted(k for k in html.entities.html5 if k.endswith(";"))
+    docs = [
+        "AT&T said &amp; co. Fish &amp; chips &lt;b&gt;bold&lt;/b&gt; &quot;quoted&quot; &apos;x&apos; &nbsp;done.",
+        "&#65;&#x41;&#X1F600; &nLt;&nGt; &bogus; &amp &#; &#x; &#xD800; &#1114112; &#0;x &#00000000000000000065; &#99999999999; &;&&amp;&CounterClockwiseContourIntegral;",
+        "&", "&&&&", "&amp", "&amp;", "x&amp;", "&amp;&amp;&amp;&amp;&amp;&amp;&amp;&amp;&amp;&amp;", "&nLt;&nGt;&nLt;&nGt;&nLt;&nGt;&nLt;",
+        "&#x000000000000000000000000000000000041;", "&#x0000000000000000000000000000000041;", "&AMP;&aMp;&Amp;", "&lt;&#10;&gt;\n&#13;&#10;line two.&#x2028;three",
+        "Caf&eacute; na&iuml;ve &euro;5 &mdash; &hellip; &ldquo;So it goes.&rdquo; He said &#8220;stop.&#8221; Then left. And more words here now.",
+        "", "no entities at all. Just text. And more text.",
+    ]
+    for pad in (26, 27, 28, 29, 30, 31, 32, 33, 1015, 1018, 1020, 1022, 1023, 1024, 1025):
+        for e in ("&amp;", "&nLt;", "&#x1F600;", "&CounterClockwiseContourIntegral;", "&bogus;", "&#12"):
+            docs.append("a" * pad + e + " Bcd efg hij." + e + e + " k l m.")
+    for _ in range(60):  # fuzzed documents with entities sprinkled in
+        words = fuzzgen.FuzzGen(rng.randrange(1 << 30)).doc(max_lines=10).split(" ")
+        for _ in range(rng.randrange(1, 12)):
+            k = rng.randrange(len(words) + 1)
+            kind = rng.randrange(6)
+            e = ("&" + rng.choice(names) if kind < 2 else "&#%d;" % rng.choice([38, 60, 233, 8212, 128512, 55296, 1114112, 0]) if kind == 2
+                 else "&#x%X;" % rng.randrange(0x30000) if kind == 3 else "&" + rng.choice(names)[:-1] if kind == 4 else "&" + rng.choice(["", "#", "#x", "zz;", " amp;"]))
+            words.insert(k, e)
+        docs.append(" ".join(words))
+    return docs
+
+
+@pytest.mark.parametrize("name", ["baseline_order", "gq_open", "gr_open", "c4_lax", "sentences_then_open", "fw_open"])
+def test_html_entities_decoded_first(name):  # parquet_reader.rs:178-179 (SURVEY 8f row 1), parity with html-escape unpinned
+    steps = CHAINS[name]
+    texts = entity_docs()
+    decoded = [oracle.decode_html_entities(t) for t in texts]
+    o = oracle.OraclePipeline(steps).run_texts(decoded)
+    e = _emul.run_chain(steps, texts, decode_entities=True)
+    compare(o, e.keep, e.failed_step, e.stats, e.contents, step_types(steps), texts, label=name + "/entities")
+
+
 def split_ambiguity_docs():
     """find_all_duplicate keys are bare concatenations (text.rs:250): "no where" and "now here" give the same
     key although the word sequences differ, and such a pair need not share any shorter repeated n-gram.

@@ -14,7 +14,7 @@ import multilingual
 import oracle
 from parity_cases import CHAINS, GQ_OPEN, GR_OPEN, step_types
 from parity_util import compare
-from test_emul_parity import GOLDEN_DOCS, SENTENCE_LINE_DOCS, boundary_sentence_docs, fineweb_docs, split_ambiguity_docs
+from test_emul_parity import GOLDEN_DOCS, SENTENCE_LINE_DOCS, boundary_sentence_docs, entity_docs, fineweb_docs, split_ambiguity_docs
 from test_oracle_golden import C4_LINE_CASES, c4_default
 from textblaster_b200 import _abi, synth
 from textblaster_b200.config import GopherRepetitionParams
@@ -151,6 +151,29 @@ def test_sentence_wise_lines_corpus_and_chunks():
     grow = ["?".join("ab" for _ in range(4000))] * 50  # every break adds a byte
     rg = p.run_texts(grow)
     assert rg.content_of(0) == grow[0].replace("?", "?\n") and int(rg.content_offsets[-1]) > sum(len(t) for t in grow)
+    p.close()
+
+
+@pytest.mark.parametrize("name", ["baseline_order", "shipped_order", "gq_open", "gr_open", "c4_lax", "sentences_then_open", "fw_open"])
+def test_html_entities_decoded_first(name):  # parquet_reader.rs:178-179; parity with html-escape unpinned
+    rng = random.Random(29)
+    texts = entity_docs() + [fuzzgen.english_doc(rng, sz).replace(" and ", " &amp; ").replace("the ", "the&nbsp;") for sz in (500, 3000, 20000, 90000)]
+    steps = CHAINS[name]
+    decoded = [oracle.decode_html_entities(t) for t in texts]
+    p = GpuBatchPipeline(steps, decode_html_entities=True)
+    for chunk in (None, 1 << 16):  # one chunk, then many
+        if chunk:
+            p.set_option(_abi.TB_OPT_CHUNK_BYTES, chunk)
+        res = p.run_texts(texts)
+        ores = oracle.OraclePipeline(steps).run_texts(decoded, nthreads=NCPU)
+        assert res.content is not None  # the decoded text is the content, with or without a C4 step
+        contents = [res.content_of(i) for i in range(res.n_docs)]
+        compare(ores, res.keep, res.failed_step, res.stats, contents, step_types(steps), texts, label=name + "/entities")
+    # without entities the pre-pass is the identity
+    plain = [t for t in GOLDEN_DOCS if "&" not in t]
+    r1, r0 = p.run_texts(plain), pipe(name).run_texts(plain)
+    assert np.array_equal(r1.keep, r0.keep) and np.array_equal(r1.failed_step, r0.failed_step)
+    _same_stats(r1, r0)
     p.close()
 
 

@@ -460,3 +460,27 @@ def test_chain_short_circuit():
     assert "gopher_quality_filter_status" not in r.metadata(0)  # later steps never ran
     md = r.metadata(2)
     assert md["c4_filter_status"] == md["gopher_quality_filter_status"] == md["gopher_repetition_filter_status"] == "passed"
+
+
+# ---------------------------------------------------------------------------------------------
+# html_escape::decode_html_entities (parquet_reader.rs:178-179), SURVEY 8(f) row 1.  The crate is not in the
+# reference tree and the reference has no test with an entity: these pin the restatement to the published
+# meaning of the references (WHATWG named list, decimal, hexadecimal), not to the crate -- parity unpinned.
+# ---------------------------------------------------------------------------------------------
+def test_decode_html_entities_published_forms():
+    d = oracle.decode_html_entities
+    assert d("Tom &amp; Jerry &lt;3 &gt; &quot;x&quot; &apos;y&apos;") == "Tom & Jerry <3 > \"x\" 'y'"
+    assert d("&#72;i&#x21; &#X41; &eacute;&Eacute; &nbsp;|&euro;") == "Hi! A \u00e9\u00c9 \u00a0|\u20ac"
+    assert d("&nLt;&#128512;&CounterClockwiseContourIntegral;") == "\u226a\u20d2\U0001f600\u2233"
+    # not references: no semicolon, unknown or wrongly cased name, no digits, not a scalar value, does not fit u32
+    for t in ("&amp", "&bogus;", "&AMp;", "&#;", "&#x;", "&#xD800;", "&#1114112;", "&#99999999999;", "&;", "& amp;", "AT&T"):
+        assert d(t) == t
+    assert d("AT&T &amp; co") == "AT&T & co" and d("&&amp;;") == "&&;" and d("&amp;amp;") == "&amp;"
+
+
+def test_decode_html_entities_agrees_with_python_on_well_formed_input():
+    import html
+    import html.entities
+    names = sorted(k for k in html.entities.html5 if k.endswith(";"))
+    text = " ".join("&%s x" % n for n in names) + " " + " ".join("&#%d; &#x%X;" % (c, c) for c in (9, 10, 38, 65, 233, 0x20AC, 0x1F600, 0x10000))
+    assert oracle.decode_html_entities(text) == html.unescape(text)

@@ -26,9 +26,20 @@ class OracleAsPipeline:
 
     def __init__(self, steps):
         self.pl = oracle.OraclePipeline(steps)
+        self.decode = False
+
+    def set_option(self, option, value):
+        from textblaster_b200 import _abi
+        if option == _abi.TB_OPT_DECODE_HTML_ENTITIES:
+            self.decode = bool(value)
 
     def run_packed(self, values, off):
-        r = self.pl.run_packed(np.asarray(values), np.asarray(off, dtype=np.int64))
+        values, off = np.asarray(values), np.asarray(off, dtype=np.int64)
+        if self.decode:  # what the device pre-pass does, by the oracle's restatement of the crate
+            texts = [oracle.decode_html_entities(bytes(values[off[i]:off[i + 1]]).decode("utf-8")) for i in range(len(off) - 1)]
+            r = self.pl.run_texts(texts)
+        else:
+            r = self.pl.run_packed(values, off)
 
         class R:
             keep = r.keep
@@ -63,8 +74,7 @@ def test_outcome_files_schema_and_routing(tmp_path):
     assert counts == (4, kept.num_rows, exc.num_rows) and kept.num_rows + exc.num_rows == 4
     assert kept.schema.equals(parquet_io.output_schema()) and exc.schema.equals(parquet_io.output_schema())
     k, e = kept.to_pydict(), exc.to_pydict()
-    import html
-    ref = oracle.OraclePipeline(CHAINS["baseline_order"]).run_texts([html.unescape(d) for d in DOCS])
+    ref = oracle.OraclePipeline(CHAINS["baseline_order"]).run_texts([oracle.decode_html_entities(d) for d in DOCS])
     assert list(ref.keep) == [1, 0, 1, 0], [ref.reason(i) for i in range(4)]
     assert k["id"] == ["d0", "d2"] and e["id"] == ["d1", "d3"]
     assert "&amp;" not in k["text"][1] and "Tom & Jerry said Hi! and that was it." in k["text"][1]   # entities decoded before the filters
@@ -80,10 +90,10 @@ def test_large_utf8_and_buffers_zero_copy(tmp_path):
     src = str(tmp_path / "l.parquet")
     _write_input(src, large=True)
     batch = next(parquet_io.read_batches(parquet_io.ParquetInputConfig(src)))
-    values, off = parquet_io.text_buffers(batch.column("text"), decode_entities=False)
+    values, off = parquet_io.text_buffers(batch.column("text"))
     assert off.dtype == np.int64 and bytes(values[off[3]:off[4]]) == b"short"
     sliced = batch.column("text").slice(2, 2)
-    v2, o2 = parquet_io.text_buffers(sliced, decode_entities=False)
+    v2, o2 = parquet_io.text_buffers(sliced)
     assert len(o2) == 3 and bytes(v2[o2[1]:o2[2]]) == b"short"
 
 

@@ -76,6 +76,7 @@ TB_OPT_RETURN_CONTENT = 1
 TB_OPT_VALIDATE_UTF8 = 2
 TB_OPT_CHUNK_BYTES = 3
 TB_OPT_GENERAL_WORD_PATH = 4
+TB_OPT_DECODE_HTML_ENTITIES = 5
 
 
 class tb_c4_params(C.Structure):

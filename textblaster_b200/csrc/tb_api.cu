@@ -16,6 +16,8 @@
 #include "tb_hostutil.h"
 #include "tb_kernels.cuh"
 #include "unicode_tables.inc"
+#include "tb_entities.cuh"
+#include "entity_table.inc"
 
 static_assert(TB_WB_OTHER == WB_OTHER && TB_WB_CR == WB_CR && TB_WB_LF == WB_LF && TB_WB_NEWLINE == WB_NEWLINE &&
               TB_WB_EXTEND == WB_EXTEND && TB_WB_ZWJ == WB_ZWJ && TB_WB_REGIONAL_INDICATOR == WB_RI &&
@@ -130,13 +132,13 @@ struct tb_ctx {
   cudaStream_t compute = nullptr, copy = nullptr, d2h = nullptr, side = nullptr;
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   UcTables uc{};
-  DevBuf t_stage1, t_stage2, t_lower, t_cased, t_caseign, t_pow;
+  DevBuf t_stage1, t_stage2, t_lower, t_cased, t_caseign, t_pow, t_ent;
 };
 
 struct tb_pipeline {
   tb_ctx* ctx = nullptr;
   std::vector<StepHost> steps;
-  int64_t opt_return_content = 1, opt_validate = 0, opt_chunk = 1024ll << 20, opt_debug = 0;
+  int64_t opt_return_content = 1, opt_validate = 0, opt_chunk = 1024ll << 20, opt_debug = 0, opt_decode = 0;
   std::mutex mu;
   // device buffers (grow-only)
   DevBuf text[2], offs[2], packed[2];
@@ -148,6 +150,7 @@ struct tb_pipeline {
   // FineWeb scratch
   DevBuf f_lh, f_ll, f_doc, f_tab;
   // C4 scratch
+  DevBuf e_D, e_amp, e_drop, e_drs, e_dre;  // HTML entity pre-pass
   DevBuf c_S, c_bits, c_srs, c_sre;  // sentence-wise lines
   DevBuf c_P, c_F, c_plen, c_nlines, c_docflags, c_lwc, c_lmax, c_lflags, c_prs, c_pre, c_frs, c_fre, c_cnt;
   cudaEvent_t ev_h2d[2] = {nullptr, nullptr}, ev_done[2] = {nullptr, nullptr}, ev_d2h[2] = {nullptr, nullptr}, ev_small[2] = {nullptr, nullptr};
@@ -301,7 +304,13 @@ int ensure_chunk_buffers(tb_pipeline* p, int64_t n, int64_t nb, bool host_input)
   // with sentence-wise lines the rewritten text can outgrow the input (tb_sent_off)
   bool sent = false;
   for (auto& sh : p->steps) sent |= sh.type == TB_STEP_C4_QUALITY && sh.c4_sentences;
-  const size_t cb = sent ? tb_grown_bytes(nb, n) : (size_t)nb;
+  size_t cb = (size_t)nb;  // extent of the buffers the chain works in
+  if (p->opt_decode) {
+    cb = tb_grown_bytes((int64_t)cb, n);
+    ENS(p->e_D, cb + 64); ENS(p->e_amp, ((size_t)nb / 32 + 4) * 4); ENS(p->e_drop, ((size_t)nb / 32 + 4) * 4); ENS(p->e_drs, n1 * 8); ENS(p->e_dre, n1 * 8);
+  }
+  const size_t cb_in = cb;  // what the sentence-wise pre-pass of C4 reads
+  if (sent) cb = tb_grown_bytes((int64_t)cb, n);
   for (int i = 0; i < 2; i++) ENS(p->packed[i], cb + 64);
   ENS(p->rs0, n1 * 8); ENS(p->re0, n1 * 8); ENS(p->rs, n1 * 8); ENS(p->re, n1 * 8); ENS(p->ts, n1 * 8); ENS(p->te, n1 * 8);
   for (int i = 0; i < 2; i++) { ENS(p->alive[i], n1); ENS(p->failed[i], n1); ENS(p->out_off[i], (n1 + 1) * 8); }
@@ -320,7 +329,7 @@ int ensure_chunk_buffers(tb_pipeline* p, int64_t n, int64_t nb, bool host_input)
     } else if (sh.type == TB_STEP_C4_QUALITY) {
       size_t lines = cb + n1 + 1;
       ENS(p->c_P, cb + 64); ENS(p->c_F, cb + 64);
-      if (sh.c4_sentences) { ENS(p->c_S, cb + 64); ENS(p->c_bits, ((size_t)nb / 32 + 4) * 4); ENS(p->c_srs, n1 * 8); ENS(p->c_sre, n1 * 8); }
+      if (sh.c4_sentences) { ENS(p->c_S, cb + 64); ENS(p->c_bits, (cb_in / 32 + 4) * 4); ENS(p->c_srs, n1 * 8); ENS(p->c_sre, n1 * 8); }
       ENS(p->c_plen, n1 * 8); ENS(p->c_nlines, n1 * 4); ENS(p->c_docflags, n1 * 4);
       ENS(p->c_lwc, lines * 4); ENS(p->c_lmax, lines * 4); ENS(p->c_lflags, lines * 4);
       ENS(p->c_prs, n1 * 8); ENS(p->c_pre, n1 * 8); ENS(p->c_frs, n1 * 8); ENS(p->c_fre, n1 * 8); ENS(p->c_cnt, n1 * 16);
@@ -399,7 +408,7 @@ int enqueue_chain(tb_pipeline* p, const uint8_t* text, int64_t n, int64_t nbytes
       *has_c4 = true;
     }
   }
-  if (*has_c4 && want_content) {
+  if (want_content) {  // a C4 step rewrote documents, or the entity pre-pass made `text` a copy of its own
     { Timed t(p, "k_final_len"); tb_launch_final_len(st, n, p->rs0.as<int64_t>(), p->re0.as<int64_t>(), b.rs, b.re, p->rewritten.as<uint8_t>(), p->len.as<int64_t>()); }
     { Timed t(p, "k_scan_i64"); tb_launch_scan_i64(st, p->len.as<int64_t>(), p->out_off[pb].as<int64_t>(), n); }
     { Timed t(p, "k_pack"); tb_launch_pack(st, n, text, p->rs0.as<int64_t>(), b.text, b.rs, p->rewritten.as<uint8_t>(), p->out_off[pb].as<int64_t>(), p->packed[pb].as<uint8_t>()); }
@@ -421,10 +430,11 @@ int run_impl(tb_pipeline* p, const uint8_t* utf8, const void* offsets, int is64,
   p->launches_this_run = 0; p->ms_this_run = 0;
   bool any_c4 = false;
   for (auto& s : p->steps) any_c4 |= s.type == TB_STEP_C4_QUALITY;
-  const bool want_content = any_c4 && p->opt_return_content;
+  const bool want_content = (any_c4 || p->opt_decode) && p->opt_return_content;
   bool sent_mode = false;
   for (auto& s : p->steps) sent_mode |= s.type == TB_STEP_C4_QUALITY && s.c4_sentences;
 
+  size_t content_cap = (size_t)0;
   ResultSet* rsx = acquire_results(p);
   out->_owner = rsx;
   int rc;
@@ -433,7 +443,10 @@ int run_impl(tb_pipeline* p, const uint8_t* utf8, const void* offsets, int is64,
   for (size_t s = 0; s < p->steps.size(); s++) if ((rc = rsx->stats[s].ensure(n1 * stat_size(p->steps[s].type)))) return rc;
   const int64_t base0 = n_docs ? off_at(offsets, is64, 0) : 0;
   const int64_t total_bytes = n_docs ? off_at(offsets, is64, n_docs) - base0 : 0;
-  if (want_content) { if ((rc = rsx->content.ensure((sent_mode ? tb_grown_bytes(total_bytes, n_docs) : (size_t)total_bytes) + 64)) || (rc = rsx->content_off.ensure(n1 * 8))) return rc; }
+  content_cap = (size_t)total_bytes;
+  if (p->opt_decode) content_cap = tb_grown_bytes((int64_t)content_cap, n_docs);
+  if (sent_mode) content_cap = tb_grown_bytes((int64_t)content_cap, n_docs);
+  if (want_content) { if ((rc = rsx->content.ensure(content_cap + 64)) || (rc = rsx->content_off.ensure(n1 * 8))) return rc; }
   for (int64_t i = 0; i < n_docs; i++) if (off_at(offsets, is64, i + 1) < off_at(offsets, is64, i)) return fail(TB_ERR_INVALID_ARGUMENT, "offsets must be non-decreasing");
 
   // chunk plan.  Large chunks cost the least device time (every launch of the chain ends with a tail: about
@@ -538,8 +551,24 @@ int run_impl(tb_pipeline* p, const uint8_t* utf8, const void* offsets, int is64,
       tb_launch_init_ranges(c->compute, p->offs[buf].p, is64, 0, n, ch.b0, p->rs0.as<int64_t>(), p->re0.as<int64_t>(), p->alive[buf].as<uint8_t>(), p->failed[buf].as<int8_t>());
     }
     p->launches_this_run++;
+    int64_t text_extent = ch.b1 - ch.b0;
+    if (p->opt_decode) {  // the decoded copy becomes the text, and its ranges the documents' original ranges
+      const size_t bw = ((size_t)text_extent / 32 + 4) * 4;
+      CK(cudaMemsetAsync(p->e_amp.p, 0, bw, c->compute));
+      CK(cudaMemsetAsync(p->e_drop.p, 0, bw, c->compute));
+      CK(cudaMemsetAsync(p->cursors.p, 0, 256, c->compute));
+      KBatch eb{text, p->rs0.as<int64_t>(), p->re0.as<int64_t>(), p->alive[buf].as<uint8_t>(), p->failed[buf].as<int8_t>(), n, c->uc, 0, text_extent,
+                0u, nullptr, nullptr, nullptr};
+      { Timed t(p, "k_entities");
+        tb_launch_entities(c->compute, eb, c->t_ent.as<EntEntry>(), TB_ENT_COUNT, p->e_amp.as<uint32_t>(), p->e_drop.as<uint32_t>(), p->e_D.as<uint8_t>(),
+                           p->e_drs.as<int64_t>(), p->e_dre.as<int64_t>(), c->sm_count, p->cursors.as<uint32_t>() + 51); }
+      CK(cudaMemcpyAsync(p->rs0.p, p->e_drs.p, (size_t)n * 8, cudaMemcpyDeviceToDevice, c->compute));
+      CK(cudaMemcpyAsync(p->re0.p, p->e_dre.p, (size_t)n * 8, cudaMemcpyDeviceToDevice, c->compute));
+      text = p->e_D.as<uint8_t>();
+      text_extent = (int64_t)tb_grown_bytes(text_extent, n);
+    }
     bool has_c4 = false;
-    if ((rc = enqueue_chain(p, text, n, ch.b1 - ch.b0, buf, want_content, &has_c4))) return rc;
+    if ((rc = enqueue_chain(p, text, n, text_extent, buf, want_content, &has_c4))) return rc;
     CK(cudaEventRecord(p->ev_done[buf], c->compute));
     // the previous chunk's content goes out first (its copy must not queue behind this chunk's kernels)
     if (ci > 0) if ((rc = finish(ci - 1))) return rc;
@@ -616,6 +645,7 @@ int tb_ctx_create(int device, tb_ctx** out) {
   uint32_t a = 1, b = 1;
   for (int i = 0; i < TB_POWTAB; i++) { pw[i] = ((uint64_t)a << 32) | b; a = tb_mm(a, TB_B1); b = tb_mm(b, TB_B2); }
   if ((rc = upload(c->t_pow, pw.data(), pw.size() * 8))) { delete c; return rc; }
+  if ((rc = upload(c->t_ent, tb_ent_table, sizeof tb_ent_table))) { delete c; return rc; }
   c->uc = UcTables{c->t_stage1.as<uint16_t>(), c->t_stage2.as<uint16_t>(), c->t_lower.as<uint32_t>(), c->t_cased.as<uint32_t>(),
                    c->t_caseign.as<uint32_t>(), c->t_pow.as<uint64_t>(), TB_UC_NLOWER, TB_UC_NCASED, TB_UC_NCASEIGN, {0}};
   tb_compute_wslead(tb_uc_stage1, tb_uc_stage2, c->uc.wslead);
@@ -626,7 +656,7 @@ int tb_ctx_create(int device, tb_ctx** out) {
 void tb_ctx_destroy(tb_ctx* c) {
   if (!c) return;
   cudaSetDevice(c->device);
-  for (DevBuf* b : {&c->t_stage1, &c->t_stage2, &c->t_lower, &c->t_cased, &c->t_caseign, &c->t_pow}) b->release();
+  for (DevBuf* b : {&c->t_stage1, &c->t_stage2, &c->t_lower, &c->t_cased, &c->t_caseign, &c->t_pow, &c->t_ent}) b->release();
   if (c->compute) cudaStreamDestroy(c->compute);
   if (c->copy) cudaStreamDestroy(c->copy);
   if (c->d2h) cudaStreamDestroy(c->d2h);
@@ -698,7 +728,7 @@ void tb_pipeline_destroy(tb_pipeline* p) {
   cudaDeviceSynchronize();
   for (DevBuf* b : {&p->text[0], &p->text[1], &p->offs[0], &p->offs[1], &p->packed[0], &p->packed[1], &p->rs0, &p->re0, &p->rs,
                     &p->re, &p->ts, &p->te, &p->alive[0], &p->alive[1], &p->failed[0], &p->failed[1], &p->rewritten, &p->len, &p->out_off[0], &p->out_off[1], &p->bad, &p->cursors, &p->order, &p->sizecls, &p->g_wh,
-                    &p->g_wl, &p->g_lh, &p->g_ll, &p->g_lg, &p->g_doc, &p->g_work, &p->g_lists, &p->g_counters, &p->f_lh, &p->f_ll, &p->f_doc, &p->f_tab, &p->c_S, &p->c_bits, &p->c_srs, &p->c_sre, &p->c_P, &p->c_F, &p->c_plen, &p->c_nlines,
+                    &p->g_wl, &p->g_lh, &p->g_ll, &p->g_lg, &p->g_doc, &p->g_work, &p->g_lists, &p->g_counters, &p->f_lh, &p->f_ll, &p->f_doc, &p->f_tab, &p->e_D, &p->e_amp, &p->e_drop, &p->e_drs, &p->e_dre, &p->c_S, &p->c_bits, &p->c_srs, &p->c_sre, &p->c_P, &p->c_F, &p->c_plen, &p->c_nlines,
                     &p->c_docflags, &p->c_lwc, &p->c_lmax, &p->c_lflags, &p->c_prs, &p->c_pre, &p->c_frs, &p->c_fre, &p->c_cnt})
     b->release();
   for (auto& b : p->stats) { b[0].release(); b[1].release(); }
@@ -725,6 +755,7 @@ int tb_pipeline_set_option(tb_pipeline* p, int32_t option, int64_t value) {
     case TB_OPT_RETURN_CONTENT: p->opt_return_content = value != 0; return TB_OK;
     case TB_OPT_VALIDATE_UTF8: p->opt_validate = value != 0; return TB_OK;
     case TB_OPT_GENERAL_WORD_PATH: p->opt_debug = value != 0 ? TB_DBG_FORCE_WALK : 0; return TB_OK;
+    case TB_OPT_DECODE_HTML_ENTITIES: p->opt_decode = value != 0; return TB_OK;
     case TB_OPT_CHUNK_BYTES:
       if (value < (1 << 16)) return fail(TB_ERR_INVALID_ARGUMENT, "chunk size must be at least 64 KiB");
       p->opt_chunk = value; return TB_OK;

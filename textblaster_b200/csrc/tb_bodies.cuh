@@ -10,6 +10,7 @@
 #include "tb_rep.cuh"
 #include "tb_simt.cuh"
 #include "tb_tile.cuh"
+#include "tb_entities.cuh"
 
 #if defined(TB_HOST_EMUL)
 extern uint64_t tbe_stat_tiles, tbe_stat_walk;  // documents taken by the mask path / by the walking path (lane 0 counts)
@@ -556,6 +557,70 @@ TB_D void body_c4_sent(const KBatch& a, const uint16_t* s_ascii, uint8_t* stage,
     outpos += tot;
   }
   if (lane == 0) { srs[d] = o0; sre[d] = o0 + outpos; }
+}
+
+// ---------------------------------------------------------------------------------------------
+// HTML entities (tb_entities.cuh): the decoded copy of a document, the text every step then sees
+// ---------------------------------------------------------------------------------------------
+// Pass 1: every '&' is a candidate, parsed by the lane that owns it; for an entity the '&' is marked in `amp`
+// and the rest of its span in `drop` (bit per byte of the text buffer; a span can reach into later stretches).
+// Pass 2: copy, with the replacement in place of a marked '&' and without the dropped bytes.  Only "&nLt;" and
+// "&nGt;" have a replacement longer than the entity (by one byte); tb_sent_off leaves room for far more.
+TB_D_NOINLINE uint32_t ent_parse_at(const TextRange& R, int64_t a, const EntEntry* tab, uint32_t ntab, uint32_t* span, uint64_t* repl) {
+  return ent_parse(R.t, a, R.re, tab, ntab, span, repl);
+}
+TB_D void body_entities(const KBatch& a, uint8_t* stage, const EntEntry* tab, uint32_t ntab, uint32_t* amp, uint32_t* drop,
+                        uint8_t* D, int64_t* drs, int64_t* dre, int64_t d, int lane) {
+  TextRange R{a.text, a.rs[d], a.re[d]};
+  const int64_t o0 = tb_sent_off(a.rs[d], d);
+  const uint32_t mis = (uint32_t)((uintptr_t)a.text & 31u);
+  for (int64_t base = tb_tile_origin(R); base < R.re; base += TB_TILE) {
+    uint32_t w[8];
+    const int64_t p0 = base + lane * TB_STRETCH;
+    const uint32_t V = tile_load(R, a.ext_lo, a.ext_hi, p0, w);
+    uint32_t cand = tile_eq_mask(w, '&') & V;
+    while (cand) {
+      const int i = tb_ctz32(cand);
+      cand &= cand - 1u;
+      uint32_t span; uint64_t repl;
+      if (!ent_parse_at(R, p0 + i, tab, ntab, &span, &repl)) continue;
+      const uint64_t k0 = (uint64_t)(p0 + i) + mis;
+      simt_atomic_or(&amp[k0 >> 5], 1u << (uint32_t)(k0 & 31u));
+      for (uint64_t k = k0 + 1; k < k0 + span; k++) simt_atomic_or(&drop[k >> 5], 1u << (uint32_t)(k & 31u));
+    }
+  }
+  simt_sync();
+  uint8_t* out = D + o0;
+  int64_t outpos = 0;
+  for (int64_t base = tb_tile_origin(R); base < R.re; base += TB_TILE) {
+    uint32_t w[8];
+    const int64_t p0 = base + lane * TB_STRETCH;
+    const uint32_t V = tile_load(R, a.ext_lo, a.ext_hi, p0, w);
+    uint32_t AMP = 0, DROP = 0;
+    if (V) { const uint64_t wi = ((uint64_t)p0 + mis) >> 5; AMP = simt_load_fresh(&amp[wi]) & V; DROP = simt_load_fresh(&drop[wi]) & V; }
+    const uint32_t KEEP = V & ~DROP & ~AMP;
+    uint32_t n = (uint32_t)tb_popc32(KEEP);
+    for (uint32_t m = AMP; m; m &= m - 1u) { uint32_t span; uint64_t repl; n += ent_parse_at(R, p0 + tb_ctz32(m), tab, ntab, &span, &repl); }
+    uint32_t tot, pre = simt_exscan(n, lane, &tot);
+    uint32_t o = pre;
+    if (AMP == 0u) {
+#pragma unroll
+      for (int k = 0; k < 32; k++) if ((KEEP >> k) & 1u) stage[o++] = (uint8_t)(w[k >> 2] >> (8 * (k & 3)));
+    } else {  // rare: a stretch with an entity in it
+      for (int k = 0; k < 32; k++) {
+        if ((AMP >> k) & 1u) {
+          uint32_t span; uint64_t repl;
+          const uint32_t rl = ent_parse_at(R, p0 + k, tab, ntab, &span, &repl);
+          for (uint32_t q = 0; q < rl; q++) stage[o++] = (uint8_t)(repl >> (8 * q));
+        } else if ((KEEP >> k) & 1u) stage[o++] = (uint8_t)tb_byte(R.t, p0 + k);
+      }
+    }
+    simt_sync();
+    for (uint32_t k = (uint32_t)lane; k < tot; k += 32) out[outpos + k] = stage[k];
+    simt_sync();
+    outpos += tot;
+  }
+  if (lane == 0) { drs[d] = o0; dre[d] = o0 + outpos; }
 }
 
 // ---------------------------------------------------------------------------------------------

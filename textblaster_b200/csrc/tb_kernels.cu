@@ -170,6 +170,17 @@ __global__ void __launch_bounds__(TB_BLOCK, 24) k_c4_a(KBatch a, C4Cfg cfg, C4Sc
     if (a.alive[d]) body_c4_a(a, s_ascii, s_lut, s_stage, cfg, s, d, threadIdx.x & 31);
   }
 }
+__global__ void __launch_bounds__(TB_BLOCK, 16) k_entities(KBatch a, const EntEntry* tab, uint32_t ntab, uint32_t* amp, uint32_t* drop,
+                                                           uint8_t* D, int64_t* drs, int64_t* dre, uint32_t* cursor) {
+  __shared__ __align__(16) uint8_t s_stage[TB_SENT_STAGE_BYTES];
+  for (;;) {  // runs before the work order of the chain exists: documents in index order
+    uint32_t i = 0;
+    if ((threadIdx.x & 31) == 0) i = atomicAdd(cursor, 1u);
+    i = __shfl_sync(0xFFFFFFFFu, i, 0);
+    if ((int64_t)i >= a.n) break;
+    body_entities(a, s_stage, tab, ntab, amp, drop, D, drs, dre, (int64_t)i, threadIdx.x & 31);
+  }
+}
 __global__ void __launch_bounds__(TB_BLOCK, 16) k_c4_sent(KBatch a, const int64_t* ts, const int64_t* te, uint32_t* bits, uint8_t* S,
                                                           int64_t* srs, int64_t* sre, uint32_t* cursor) {
   __shared__ uint16_t s_ascii[192];
@@ -328,6 +339,10 @@ int tb_kernels_init() {
 }
 void tb_launch_c4_a(cudaStream_t st, const KBatch& b, const C4Cfg& cfg, const C4Scratch& s, int sm_count, uint32_t* cursor) {
   if (b.n) k_c4_a<<<persistent_grid(b.n, sm_count, 24), TB_BLOCK, 0, st>>>(b, cfg, s, cursor);
+}
+void tb_launch_entities(cudaStream_t st, const KBatch& b, const EntEntry* tab, uint32_t ntab, uint32_t* amp, uint32_t* drop,
+                        uint8_t* D, int64_t* drs, int64_t* dre, int sm_count, uint32_t* cursor) {
+  if (b.n) k_entities<<<persistent_grid(b.n, sm_count, 16), TB_BLOCK, 0, st>>>(b, tab, ntab, amp, drop, D, drs, dre, cursor);
 }
 void tb_launch_c4_sent(cudaStream_t st, const KBatch& b, const int64_t* ts, const int64_t* te, uint32_t* bits, uint8_t* S,
                        int64_t* srs, int64_t* sre, int sm_count, uint32_t* cursor) {

@@ -123,6 +123,10 @@ void tb_launch_c4_b(cudaStream_t st, const KBatch& b, const C4Cfg& cfg, const C4
 void tb_launch_c4_c(cudaStream_t st, const KBatch& b, const C4Cfg& cfg, const C4Scratch& s, int sm_count, uint32_t* cursor);
 void tb_launch_c4_d(cudaStream_t st, const KBatch& b, const C4Cfg& cfg, const C4Scratch& s, int step, tb_c4_stats* out,
                     uint8_t* rewritten, int64_t* rs_out, int64_t* re_out, int sm_count, uint32_t* cursor);
+// HTML entities decoded into D (ranges drs / dre): the pre-pass of TB_OPT_DECODE_HTML_ENTITIES
+struct EntEntry;
+void tb_launch_entities(cudaStream_t st, const KBatch& b, const EntEntry* tab, uint32_t ntab, uint32_t* amp, uint32_t* drop,
+                        uint8_t* D, int64_t* drs, int64_t* dre, int sm_count, uint32_t* cursor);
 // split_paragraph = false: the document rewritten with one sentence per line (S, ranges srs / sre)
 void tb_launch_c4_sent(cudaStream_t st, const KBatch& b, const int64_t* ts, const int64_t* te, uint32_t* bits, uint8_t* S,
                        int64_t* srs, int64_t* sre, int sm_count, uint32_t* cursor);

@@ -89,7 +89,9 @@ class BatchResult:
 class GpuBatchPipeline:
     """An immutable chain of C4 / Gopher steps on one GPU (tb_pipeline).  Thread-safe."""
 
-    def __init__(self, params: Sequence[object], device: int = 0, validate: bool = True):
+    def __init__(self, params: Sequence[object], device: int = 0, validate: bool = True, decode_html_entities: bool = False):
+        """decode_html_entities: decode entities on the device before the first step, as the reference's reader does
+        (parquet_reader.rs:178-179); the decoded text is then the content of every document."""
         self.params = list(params)
         for p in self.params:
             if not isinstance(p, (C4QualityParams, GopherQualityParams, GopherRepetitionParams, FineWebQualityParams)):
@@ -106,6 +108,8 @@ class GpuBatchPipeline:
         _native.check(self._lib.tb_pipeline_create(_ctx(device), C.addressof(arr), len(self.params), C.byref(h)))
         self._h = h.value
         self.device = device
+        if decode_html_entities:
+            self.set_option(_abi.TB_OPT_DECODE_HTML_ENTITIES, 1)
 
     def set_option(self, option: int, value: int):
         _native.check(self._lib.tb_pipeline_set_option(self._h, option, value))

@@ -9,13 +9,12 @@
     (src/pipeline/writers/parquet_writer.rs:17-44): id, source, text, added, created{start,end}, metadata (JSON).
 
 HTML entities: the reference decodes them in the reader with the `html-escape 0.2.13` crate
-(parquet_reader.rs:178-179), which is not part of the reference tree.  ``decode_entities=True`` uses
-Python's ``html.unescape`` as a stand-in (same named / decimal / hexadecimal forms; it additionally accepts
-a few legacy names without ';') -- parity of this one step is unpinned; batches without '&' are untouched.
+(parquet_reader.rs:178-179).  Here the Arrow buffers go to the device as they are and the pipeline decodes
+them in a pre-pass (TB_OPT_DECODE_HTML_ENTITIES, csrc/tb_entities.cuh); the crate is not part of the
+reference tree, so parity of this one step is unpinned.
 """
 from __future__ import annotations
 
-import html
 import json
 from dataclasses import dataclass
 from typing import Iterator, List, Optional, Sequence, Tuple
@@ -65,8 +64,8 @@ def read_batches(cfg: ParquetInputConfig) -> Iterator["object"]:
         yield batch
 
 
-def text_buffers(arr, decode_entities: bool = True) -> Tuple[np.ndarray, np.ndarray]:
-    """(values u8, offsets i32/i64 starting anywhere) of a string array; zero-copy unless entities are decoded."""
+def text_buffers(arr) -> Tuple[np.ndarray, np.ndarray]:
+    """(values u8, offsets i32/i64 starting anywhere) of a string array, zero-copy."""
     import pyarrow as pa
 
     if isinstance(arr, pa.ChunkedArray):
@@ -76,12 +75,6 @@ def text_buffers(arr, decode_entities: bool = True) -> Tuple[np.ndarray, np.ndar
     odt = np.int64 if large else np.int32
     off = np.frombuffer(bufs[1], dtype=odt, count=len(arr) + 1, offset=arr.offset * odt().itemsize)
     values = np.frombuffer(bufs[2], dtype=np.uint8) if bufs[2] is not None else np.zeros(0, np.uint8)
-    if decode_entities and len(arr) and (values[int(off[0]):int(off[-1])] == ord("&")).any():
-        texts = [html.unescape(s) for s in arr.to_pylist()]
-        enc = [s.encode("utf-8") for s in texts]
-        values = np.frombuffer(b"".join(enc) + b"\0", dtype=np.uint8)
-        off = np.zeros(len(enc) + 1, np.int64)
-        off[1:] = np.cumsum([len(e) for e in enc])
     return values, off
 
 
@@ -149,9 +142,13 @@ class OutcomeWriter:
 
 def run_parquet(pipeline, cfg: ParquetInputConfig, kept_path: str, excluded_path: str, decode_entities: bool = True):
     """Read -> filter on the GPU -> write.  ``pipeline``: a GpuBatchPipeline.  Returns (received, kept, excluded),
-    the triple aggregate_results_from_stream returns (producer_logic.rs:195)."""
+    the triple aggregate_results_from_stream returns (producer_logic.rs:195).  ``decode_entities`` switches the
+    pipeline's entity pre-pass on or off (the reference always decodes)."""
     import pyarrow as pa
 
+    from . import _abi
+
+    pipeline.set_option(_abi.TB_OPT_DECODE_HTML_ENTITIES, 1 if decode_entities else 0)
     out = OutcomeWriter(kept_path, excluded_path)
     received = 0
     for batch in read_batches(cfg):
@@ -163,7 +160,7 @@ def run_parquet(pipeline, cfg: ParquetInputConfig, kept_path: str, excluded_path
                 i = int(np.flatnonzero(~np.asarray(arr.is_valid()))[0])
                 kind = "text" if nm == cfg.text_column else "id"
                 raise Unexpected(f"Row {i} has null {kind} column '{nm}'")
-        values, off = text_buffers(text_arr, decode_entities)
+        values, off = text_buffers(text_arr)
         res = pipeline.run_packed(values, off)
         ids = id_arr.to_pylist()
         sources = batch.column("source").to_pylist() if "source" in names else [None] * n
