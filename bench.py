@@ -215,6 +215,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--chunk-mb", type=int, default=1024)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--decode-entities", action="store_true", help="also run the HTML-entity pre-pass of the reader (SURVEY 8f row 1); not part of the headline workload")
     ap.add_argument("--with-fineweb", action="store_true",
                     help="append FineWebQualityFilter (SURVEY 8(f) row 3) to the chain; not the headline workload")
     args = ap.parse_args()
@@ -269,6 +270,8 @@ def main():
     steps = shipped_chain(args.with_fineweb)
     pipe = GpuBatchPipeline(steps, device=local_rank)
     pipe.set_option(_abi.TB_OPT_CHUNK_BYTES, args.chunk_mb << 20)
+    if args.decode_entities:
+        pipe.set_option(_abi.TB_OPT_DECODE_HTML_ENTITIES, 1)
     d_text = holder["t"].cuda(non_blocking=False)
     d_off = off_t.cuda()
     out = _abi.tb_batch_out()
@@ -359,7 +362,7 @@ def main():
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": dt_dev / K * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "u8", "data": "synthetic",
-            "config": {"workload": WORKLOAD + (" + FineWebQualityFilter" if args.with_fineweb else ""), "docs_per_gpu_per_step": n_docs, "bytes_per_gpu_per_step": n_bytes,
+            "config": {"workload": WORKLOAD + (" + FineWebQualityFilter" if args.with_fineweb else "") + (" + HTML entity pre-pass" if args.decode_entities else ""), "docs_per_gpu_per_step": n_docs, "bytes_per_gpu_per_step": n_bytes,
                        "sharding": "row groups of %d docs round-robin over ranks, no data-path collective; keep masks gathered on the host (%.3f s, outside the timed region)" % (min(GROUP_DOCS, args.docs), gather_s),
                        "kept_total": int(sum(int(m.sum()) for m in masks)),
                        "chunk_mb": args.chunk_mb, "l2": "inputs (%.2f GB per step) larger than the 126 MB L2" % (n_bytes / 1e9),
