@@ -572,32 +572,50 @@ TB_D_NOINLINE uint32_t ent_parse_at(const TextRange& R, int64_t a, const EntEntr
 TB_D void body_entities(const KBatch& a, uint8_t* stage, const EntEntry* tab, uint32_t ntab, uint32_t* amp, uint32_t* drop,
                         uint8_t* D, int64_t* drs, int64_t* dre, int64_t d, int lane) {
   TextRange R{a.text, a.rs[d], a.re[d]};
-  const int64_t o0 = tb_sent_off(a.rs[d], d);
+  int64_t o0 = tb_sent_off(a.rs[d], d);
+  // The copy starts at the same address modulo 32 as the text (a document of 128 bytes or more has the room):
+  // as long as no entity has been met, a stretch is then copied with two aligned 16-byte stores.
+  const bool same_phase = R.re - R.rs >= 128;
+  if (same_phase) o0 += (int64_t)(((uintptr_t)(R.t + R.rs) - (uintptr_t)(D + o0)) & 31u);
   const uint32_t mis = (uint32_t)((uintptr_t)a.text & 31u);
-  for (int64_t base = tb_tile_origin(R); base < R.re; base += TB_TILE) {
-    uint32_t w[8];
-    const int64_t p0 = base + lane * TB_STRETCH;
-    const uint32_t V = tile_load(R, a.ext_lo, a.ext_hi, p0, w);
-    uint32_t cand = tile_eq_mask(w, '&') & V;
-    while (cand) {
-      const int i = tb_ctz32(cand);
-      cand &= cand - 1u;
-      uint32_t span; uint64_t repl;
-      if (!ent_parse_at(R, p0 + i, tab, ntab, &span, &repl)) continue;
-      const uint64_t k0 = (uint64_t)(p0 + i) + mis;
-      simt_atomic_or(&amp[k0 >> 5], 1u << (uint32_t)(k0 & 31u));
-      for (uint64_t k = k0 + 1; k < k0 + span; k++) simt_atomic_or(&drop[k >> 5], 1u << (uint32_t)(k & 31u));
-    }
-  }
-  simt_sync();
   uint8_t* out = D + o0;
   int64_t outpos = 0;
   for (int64_t base = tb_tile_origin(R); base < R.re; base += TB_TILE) {
     uint32_t w[8];
     const int64_t p0 = base + lane * TB_STRETCH;
     const uint32_t V = tile_load(R, a.ext_lo, a.ext_hi, p0, w);
+    // marks: a span only reaches forward (into this tile or the next), so the marks of a tile are complete once
+    // the candidates of the tiles up to it have been parsed
+    uint32_t cand = tile_eq_mask(w, '&') & V;
+    if (simt_any(cand != 0u)) {
+      while (cand) {
+        const int i = tb_ctz32(cand);
+        cand &= cand - 1u;
+        uint32_t span; uint64_t repl;
+        if (!ent_parse_at(R, p0 + i, tab, ntab, &span, &repl)) continue;
+        const uint64_t k0 = (uint64_t)(p0 + i) + mis;
+        simt_atomic_or(&amp[k0 >> 5], 1u << (uint32_t)(k0 & 31u));
+        for (uint64_t k = k0 + 1; k < k0 + span; k++) simt_atomic_or(&drop[k >> 5], 1u << (uint32_t)(k & 31u));
+      }
+      simt_sync();
+    }
     uint32_t AMP = 0, DROP = 0;
     if (V) { const uint64_t wi = ((uint64_t)p0 + mis) >> 5; AMP = simt_load_fresh(&amp[wi]) & V; DROP = simt_load_fresh(&drop[wi]) & V; }
+    if (same_phase && outpos == (base < R.rs ? 0 : base - R.rs) && !simt_any((AMP | DROP) != 0u)) {
+      // nothing decoded up to the end of this tile: the copy is in phase with the text
+      uint8_t* q = out + (p0 - R.rs);
+      if (V == 0xFFFFFFFFu) {
+#if defined(__CUDA_ARCH__)
+        ((uint4*)q)[0] = make_uint4(w[0], w[1], w[2], w[3]); ((uint4*)q)[1] = make_uint4(w[4], w[5], w[6], w[7]);
+#else
+        memcpy(q, w, 32);
+#endif
+      } else {
+        for (uint32_t m = V; m; m &= m - 1u) { const int k = tb_ctz32(m); q[k] = (uint8_t)tb_byte(R.t, p0 + k); }
+      }
+      outpos += (int64_t)simt_sum((uint32_t)tb_popc32(V));
+      continue;
+    }
     const uint32_t KEEP = V & ~DROP & ~AMP;
     uint32_t n = (uint32_t)tb_popc32(KEEP);
     for (uint32_t m = AMP; m; m &= m - 1u) { uint32_t span; uint64_t repl; n += ent_parse_at(R, p0 + tb_ctz32(m), tab, ntab, &span, &repl); }
