@@ -69,6 +69,28 @@ def shipped_chain(with_fineweb=False):
     return [c4, gq, gr]
 
 
+def pin_to_gpu_socket(torch, index):
+    """Run this process (and so place its pinned host buffers, by first touch) on the CPU socket the GPU hangs off
+    (one reader per GPU, NUMA-pinned).  Returns a short description for the config line."""
+    try:
+        pr = torch.cuda.get_device_properties(index)
+        bdf = "%04x:%02x:%02x.0" % (pr.pci_domain_id, pr.pci_bus_id, pr.pci_device_id)
+        base = "/sys/bus/pci/devices/" + bdf
+        node = int(open(base + "/numa_node").read().strip())
+        cpus = set()
+        for part in open(base + "/local_cpulist").read().strip().split(","):
+            if part:
+                a, _, b = part.partition("-")
+                cpus.update(range(int(a), int(b or a) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if node < 0 or not cpus:
+            return "not pinned (no NUMA information for %s)" % bdf
+        os.sched_setaffinity(0, cpus)
+        return "pinned to NUMA node %d (%d cpus)" % (node, len(cpus))
+    except Exception as e:  # no sysfs, odd device properties: run unpinned
+        return "not pinned (%s)" % type(e).__name__
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
 
@@ -238,6 +260,7 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device (no CPU fallback); use --impl reference for the CPU arm")
     torch.cuda.set_device(local_rank)
+    numa = pin_to_gpu_socket(torch, local_rank) if world > 1 else "single process, not pinned"
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
@@ -298,7 +321,8 @@ def main():
         pipe.reset_kernel_times()
         barrier()
         sampler = ClockSampler(local_rank)
-        sampler.start()
+        if rank == 0:  # one poller for the job: concurrent nvidia-smi queries on every rank disturb the launches
+            sampler.start()
         launches = 0
         gpu_ms = 0.0
         t0 = time.perf_counter()
@@ -314,20 +338,38 @@ def main():
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item()), launches, gpu_ms, kept, cbytes, clocks, pipe.kernel_times()
 
-    def h2d_probe():
-        """Pinned host -> device copy rate of this box (the step's own text buffer, CUDA events, best of 3)."""
+    def h2d_probe(back=False):
+        """Pinned host -> device copy rate of this box (the step's own text buffer, CUDA events, best of 3);
+        back=True: device -> pinned host, the way the results leave."""
         best = 0.0
         for _ in range(3):
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             torch.cuda.synchronize()
             e0.record()
-            d_text.copy_(holder["t"], non_blocking=True)
+            if back:
+                holder["t"].copy_(d_text, non_blocking=True)
+            else:
+                d_text.copy_(holder["t"], non_blocking=True)
             e1.record()
             torch.cuda.synchronize()
             best = max(best, holder["t"].numel() / (e0.elapsed_time(e1) * 1e-3) / 1e9)
         return best
 
     h2d_peak = h2d_probe() if holder["t"].is_pinned() else None
+    # the same probe on every rank at once: what the host can feed to all GPUs of the job together
+    h2d_all = None
+    if world > 1 and h2d_peak is not None:
+        barrier()
+        t = torch.tensor([h2d_probe()], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        h2d_all = float(t.item())
+    d2h_peak = h2d_probe(back=True) if holder["t"].is_pinned() else None
+    d2h_all = None
+    if world > 1 and d2h_peak is not None:
+        barrier()
+        t = torch.tensor([h2d_probe(back=True)], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        d2h_all = float(t.item())
     dt_dev, launches, gpu_ms, kept, cbytes, clocks, ktimes = timed(step_device)
     dt_e2e, launches_e, gpu_ms_e, _, _, clocks_e, _ = timed(step_host)
     # host-side gather of the keep masks onto rank 0, ordered by row group (the only cross-rank traffic of the job)
@@ -365,7 +407,7 @@ def main():
             "config": {"workload": WORKLOAD + (" + FineWebQualityFilter" if args.with_fineweb else "") + (" + HTML entity pre-pass" if args.decode_entities else ""), "docs_per_gpu_per_step": n_docs, "bytes_per_gpu_per_step": n_bytes,
                        "sharding": "row groups of %d docs round-robin over ranks, no data-path collective; keep masks gathered on the host (%.3f s, outside the timed region)" % (min(GROUP_DOCS, args.docs), gather_s),
                        "kept_total": int(sum(int(m.sum()) for m in masks)),
-                       "chunk_mb": args.chunk_mb, "l2": "inputs (%.2f GB per step) larger than the 126 MB L2" % (n_bytes / 1e9),
+                       "chunk_mb": args.chunk_mb, "host": numa, "l2": "inputs (%.2f GB per step) larger than the 126 MB L2" % (n_bytes / 1e9),
                        "generator_s": round(t_gen, 2)},
             "text_gbs": total_bytes * K / dt_dev / 1e9, "total_docs_per_step": total_docs,
             "gpu_ms_per_step": gpu_ms / K, "keep_rate": kept / max(n_docs, 1),
@@ -384,7 +426,19 @@ def main():
             "h2d_roofline": {"achieved": (n_bytes + 8 * (n_docs + 1)) * K / dt_e2e / 1e9, "peak": h2d_peak, "unit": "GB/s",
                              "frac": ((n_bytes + 8 * (n_docs + 1)) * K / dt_e2e / 1e9) / h2d_peak if h2d_peak else None,
                              "peak_source": "pinned host->device copy of this step's text buffer, measured in this run (best of 3)",
-                             "per_gpu": True},
+                             "per_gpu": True,
+                             # whole job: bytes all ranks sent per second against the sum of the per-rank rates of the
+                             # probe run on all ranks at once (N > 1)
+                             "job_achieved": (total_bytes + 8 * (total_docs + world)) * K / dt_e2e / 1e9,
+                             "job_peak_concurrent": h2d_all,
+                             "job_frac": ((total_bytes + 8 * (total_docs + world)) * K / dt_e2e / 1e9) / h2d_all if h2d_all else None},
+            # the results (keep, statistics, content) go back over the same link in the other direction; on a box whose
+            # host cannot take the results of all its GPUs at once this, not the kernels, bounds the job (N = 8)
+            "d2h_roofline": {"achieved": (n_docs * (2 + stats_bytes) + cbytes + 8 * (n_docs + 1)) * K / dt_dev / 1e9, "peak": d2h_peak, "unit": "GB/s",
+                             "frac": ((n_docs * (2 + stats_bytes) + cbytes + 8 * (n_docs + 1)) * K / dt_dev / 1e9) / d2h_peak if d2h_peak else None,
+                             "per_gpu": True, "measured_on": "the device-resident run (value)",
+                             "job_peak_concurrent": d2h_all,
+                             "job_frac_per_gpu": ((n_docs * (2 + stats_bytes) + cbytes + 8 * (n_docs + 1)) * K / dt_dev / 1e9) / (d2h_all / world) if d2h_all else None},
             "kernels_ms_per_step": {k: round(v[0] / K, 3) for k, v in sorted(ktimes.items(), key=lambda kv: -kv[1][0])},
             "clocks": clocks,
         }

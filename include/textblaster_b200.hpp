@@ -215,6 +215,9 @@ class GpuPipeline {
   ~GpuPipeline() { if (h_) tb_pipeline_destroy(h_); }
   GpuPipeline(const GpuPipeline&) = delete;
   GpuPipeline& operator=(const GpuPipeline&) = delete;
+  // TB_OPT_*; e.g. TB_OPT_DECODE_HTML_ENTITIES = 1 for callers whose reader does not decode entities itself
+  // (the reference's does, src/pipeline/readers/parquet_reader.rs:178-179)
+  void set_option(int32_t option, int64_t value) { detail::check(tb_pipeline_set_option(h_, option, value)); }
 
   // One result per input document, in input order (run_batch_parallel_async, executor.rs:60-70).  `names`:
   // the step names used in StepError.
@@ -412,6 +415,7 @@ class PipelineExecutor {
     if (auto* ok = std::get_if<TextDocument>(&r[0])) return std::move(*ok);
     throw *std::get<std::shared_ptr<StepError>>(r[0]);
   }
+  void set_option(int32_t option, int64_t value) { pipe_->set_option(option, value); }
   // run_batch_parallel_async: one Result per input, input order
   std::vector<StepResult> run_batch(const std::vector<TextDocument>& documents) const { return pipe_->run(documents, names_); }
 

@@ -155,6 +155,12 @@ static void test_executor() {  // executor.rs:30-70
   CHECK(ex.run_single(doc("2", good)).metadata.at("gopher_repetition_filter_status") == "passed");
   try { ex.run_single(doc("0", "Some code block {}.")); CHECK(!"run_single has to throw"); }
   catch (const StepError& e) { CHECK(e.step_name == "C4QualityFilter" && has(e.source->reason, "curly_bracket")); }
+  // a reader that hands the raw column over lets the pipeline decode the entities first (parquet_reader.rs:178-179)
+  ex.set_option(TB_OPT_DECODE_HTML_ENTITIES, 1);
+  const std::string raw = "Tom &amp; Jerry wrote the first sentence. This is the second &#115;entence. This is the third sentence. "
+                          "This is the fourth sentence. This is the fifth sentence.";
+  TextDocument dec = ex.run_single(doc("3", raw));
+  CHECK(dec.content.rfind("Tom & Jerry wrote", 0) == 0 && has(dec.content, "second sentence."));
 }
 
 static void test_config_errors() {  // src/config/pipeline.rs validate(): rejected before any document runs
