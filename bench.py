@@ -338,38 +338,39 @@ def main():
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item()), launches, gpu_ms, kept, cbytes, clocks, pipe.kernel_times()
 
+    def copy_rate(back):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        e0.record()
+        if back:
+            holder["t"].copy_(d_text, non_blocking=True)
+        else:
+            d_text.copy_(holder["t"], non_blocking=True)
+        e1.record()
+        torch.cuda.synchronize()
+        return holder["t"].numel() / (e0.elapsed_time(e1) * 1e-3) / 1e9
+
     def h2d_probe(back=False):
         """Pinned host -> device copy rate of this box (the step's own text buffer, CUDA events, best of 3);
         back=True: device -> pinned host, the way the results leave."""
-        best = 0.0
-        for _ in range(3):
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            torch.cuda.synchronize()
-            e0.record()
-            if back:
-                holder["t"].copy_(d_text, non_blocking=True)
-            else:
-                d_text.copy_(holder["t"], non_blocking=True)
-            e1.record()
-            torch.cuda.synchronize()
-            best = max(best, holder["t"].numel() / (e0.elapsed_time(e1) * 1e-3) / 1e9)
-        return best
+        return max(copy_rate(back) for _ in range(3))
 
-    h2d_peak = h2d_probe() if holder["t"].is_pinned() else None
-    # the same probe on every rank at once: what the host can feed to all GPUs of the job together
-    h2d_all = None
-    if world > 1 and h2d_peak is not None:
-        barrier()
-        t = torch.tensor([h2d_probe()], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.SUM)
-        h2d_all = float(t.item())
-    d2h_peak = h2d_probe(back=True) if holder["t"].is_pinned() else None
-    d2h_all = None
-    if world > 1 and d2h_peak is not None:
-        barrier()
-        t = torch.tensor([h2d_probe(back=True)], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.SUM)
-        d2h_all = float(t.item())
+    def concurrent_probe(back=False):
+        """The same copy on every rank at once (a barrier before each of 3 rounds): the sum of the ranks' rates,
+        median over the rounds = what the host can move for all GPUs of the job together."""
+        sums = []
+        for _ in range(3):
+            barrier()
+            t = torch.tensor([copy_rate(back)], dtype=torch.float64, device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.SUM)
+            sums.append(float(t.item()))
+        return sorted(sums)[1]
+
+    pinned = holder["t"].is_pinned()
+    h2d_peak = h2d_probe() if pinned else None
+    d2h_peak = h2d_probe(back=True) if pinned else None
+    h2d_all = concurrent_probe() if world > 1 and pinned else None
+    d2h_all = concurrent_probe(back=True) if world > 1 and pinned else None
     dt_dev, launches, gpu_ms, kept, cbytes, clocks, ktimes = timed(step_device)
     dt_e2e, launches_e, gpu_ms_e, _, _, clocks_e, _ = timed(step_host)
     # host-side gather of the keep masks onto rank 0, ordered by row group (the only cross-rank traffic of the job)

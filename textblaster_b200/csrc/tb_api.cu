@@ -451,7 +451,7 @@ int run_impl(tb_pipeline* p, const uint8_t* utf8, const void* offsets, int is64,
 
   // chunk plan.  Large chunks cost the least device time (every launch of the chain ends with a tail: about
   // 90 us per launch, measured), but the copy of the first chunk to the device and the copy of the last
-  // chunk's results back are not hidden behind kernels.  So the sizes ramp: from host memory they start small
+  // chunk's results back are not hidden behind kernels.  So the sizes ramp: they start small
   // and double (the copy engine moves text ~2.5x faster than the kernels consume it, so the next chunk is
   // always there in time), they stay at the configured size, and they shrink by thirds at the end (the
   // results of a chunk leave while the next, smaller one is computed).
@@ -459,9 +459,13 @@ int run_impl(tb_pipeline* p, const uint8_t* utf8, const void* offsets, int is64,
   int64_t max_n = 0, max_b = 0;
   {
     const int64_t C = std::max<int64_t>(p->opt_chunk, 1), B = total_bytes;
-    const int64_t lo_up = std::min<int64_t>(C, 64ll << 20), lo_down = std::min<int64_t>(C, 48ll << 20);
+    // first size: 64 MiB from host memory (its copy is exposed), 256 MiB for text on the device (nothing to wait for,
+    // small chunks only cost kernel efficiency there)
+    const int64_t lo_up = std::min<int64_t>(C, (device_input ? 256ll : 64ll) << 20), lo_down = std::min<int64_t>(C, 48ll << 20);
     std::vector<int64_t> up, down;  // ramp sizes, smallest first
-    if (!device_input) for (int64_t v = lo_up; v < C; v *= 2) up.push_back(v);
+    // (also for text that is already on the device: the sooner the first results are computed, the sooner they
+    // start to leave, which is what counts when the link back to the host is the bottleneck)
+    for (int64_t v = lo_up; v < C; v *= 2) up.push_back(v);
     for (int64_t v = lo_down; v < C; v *= 3) down.push_back(v);
     // take ramp steps from both ends, smallest first, while they fit; what is left is the plateau
     std::vector<int64_t> head, tail;
