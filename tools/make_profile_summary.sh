@@ -11,14 +11,14 @@ for r in rows[2:]:
     def val(m):
         i=hdr.index(m); v=float(r[i].replace(',','')); return v*{'byte':1,'Kbyte':1e3,'Mbyte':1e6,'Gbyte':1e9}[units[i]]
     out[name]=val('dram__bytes_read.sum')+val('dram__bytes_write.sum')
-# the captured launch is the first chunk of the device-resident run: with the default plan (1 GiB, shrinking by
-# thirds at the end: 48 + 144 + 432 MiB) that is a third of the rest, ~960.07 MB of text and ~271.6k documents
-out['_captured_launch_algorithmic_bytes']=float(sys.argv[1]) if len(sys.argv)>1 else 966.59e6
+# the captured launch is the first chunk of the device-resident run: with the default plan that is 256 MiB of text
+# (268.4 MB) and ~75.9k documents of 24 bytes of offsets / results each
+out['_captured_launch_algorithmic_bytes']=float(sys.argv[1]) if len(sys.argv)>1 else 270.26e6
 json.dump(out, open('profiles/roofline_traffic.json','w'), indent=1)
 "
 {
 echo "# Round 1 -- ncu evidence for the bench command (python bench.py, 1M docs per step, chunks ramping up to 1 GiB)"
-echo "# capture: ncu --set full --clock-control none --import-source on, first launch of each listed kernel (the 893 MB chunk, ~265k docs)"
+echo "# capture: ncu --set full --clock-control none --import-source on, first launch of each listed kernel (the first chunk of the device-resident run: 256 MiB, ~76k docs)"
 echo "# launch list: profiles/r01_launches.csv (ncu --metrics gpu__time_duration.sum --clock-control none, serialised, cold caches)"
 echo
 echo "## kernel share of the step: ncu launch list vs CUDA events inside bench.py (profiles/r01_bench_n1_1Mdocs.json)"
