@@ -27,8 +27,17 @@ def lib():
         L.tbe_run_chain.restype = C.c_int
         L.tbe_run_chain.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p,
                                     C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
+        L.tbe_chunk_targets.restype = C.c_int64
+        L.tbe_chunk_targets.argtypes = [C.c_int64, C.c_int64, C.c_int, C.c_void_p, C.c_int64]
         _lib = L
     return _lib
+
+
+def chunk_targets(total_bytes, chunk_bytes, device_input=False):
+    """tb_chunk_targets (csrc/tb_hostutil.h): the sizes the host executor cuts a batch into"""
+    out = np.zeros(4096, np.int64)
+    n = lib().tbe_chunk_targets(total_bytes, chunk_bytes, 1 if device_input else 0, out.ctypes.data, len(out))
+    return [int(x) for x in out[:n]]
 
 
 class EmulResult:

@@ -23,6 +23,12 @@ thread_local int simt_lane = 0;
 thread_local SimtBlock* simt_block = nullptr;
 uint64_t tbe_stat_tiles = 0, tbe_stat_walk = 0;
 extern "C" void tbe_stats(uint64_t* tiles, uint64_t* walk) { *tiles = tbe_stat_tiles; *walk = tbe_stat_walk; }
+// the chunk plan of the host executor (tb_hostutil.h): sizes into out[0 .. cap), returns their number
+extern "C" int64_t tbe_chunk_targets(int64_t total_bytes, int64_t chunk_bytes, int device_input, int64_t* out, int64_t cap) {
+  std::vector<int64_t> t = tb_chunk_targets(total_bytes, chunk_bytes, device_input != 0);
+  for (size_t i = 0; i < t.size() && (int64_t)i < cap; i++) out[i] = t[i];
+  return (int64_t)t.size();
+}
 
 namespace {
 

@@ -86,3 +86,28 @@ def test_outcome_mapping():  # worker_tests.rs:60-160 / worker_logic.rs:155-180
     fl = PipelineExecutor([MockStep("FilteringStep", filt)]).run_outcomes([doc("1", "x")])[0]
     assert fl.kind == "Filtered" and fl.reason == "Filtered by FilteringStep" and fl.document.metadata == {"k": "v"}
     assert PipelineExecutor([MockStep("FailingStep", fail)]).run_outcomes([doc("1", "x")])[0] is None
+
+
+def test_chunk_plan_ramps():
+    """Chunk sizes of the host executor (tb_chunk_targets): they cover the batch exactly, never exceed the configured
+    size, about double on the way up (the next chunk's copy fits behind the current chunk's kernels), shrink by about
+    thirds on the way down, and a small batch is one chunk."""
+    import _emul
+    MiB = 1 << 20
+    for total in (0, 1, 5 * MiB, 64 * MiB, 200 * MiB, 1000 * MiB, 3534533291, 40 * 1024 * MiB):
+        for C in (1 << 16, 64 * MiB, 256 * MiB, 1024 * MiB):
+            for dev in (False, True):
+                if total // C > 3000:
+                    continue
+                t = _emul.chunk_targets(total, C, dev)
+                assert (sum(t) == total or total == 0) and all(0 < x <= C for x in t), (total, C, dev, t)
+                peak = t.index(max(t))
+                for a, b in zip(t[:peak], t[1:peak + 1]):
+                    assert b <= 3 * a or a >= C // 2, (total, C, dev, t)   # up: doubling (a remainder may stretch one step)
+                last = len(t) - 1 - t[::-1].index(max(t))
+                for a, b in zip(t[last:], t[last + 1:]):
+                    assert 4 * b >= a or b >= C // 3, (total, C, dev, t)   # down: thirds (a remainder may stretch one step)
+    assert _emul.chunk_targets(5 * MiB, 1024 * MiB) == [5 * MiB]
+    t = _emul.chunk_targets(3534533291, 1024 * MiB)
+    assert t[0] == 64 * MiB and t[-1] == 48 * MiB and max(t) <= 1024 * MiB and len(t) == 9
+    assert _emul.chunk_targets(3534533291, 1024 * MiB, True)[0] == 256 * MiB

@@ -458,27 +458,8 @@ int run_impl(tb_pipeline* p, const uint8_t* utf8, const void* offsets, int is64,
   std::vector<Chunk> chunks;
   int64_t max_n = 0, max_b = 0;
   {
-    const int64_t C = std::max<int64_t>(p->opt_chunk, 1), B = total_bytes;
-    // first size: 64 MiB from host memory (its copy is exposed), 256 MiB for text on the device (nothing to wait for,
-    // small chunks only cost kernel efficiency there)
-    const int64_t lo_up = std::min<int64_t>(C, (device_input ? 256ll : 64ll) << 20), lo_down = std::min<int64_t>(C, 48ll << 20);
-    std::vector<int64_t> up, down;  // ramp sizes, smallest first
-    // (also for text that is already on the device: the sooner the first results are computed, the sooner they
-    // start to leave, which is what counts when the link back to the host is the bottleneck)
-    for (int64_t v = lo_up; v < C; v *= 2) up.push_back(v);
-    for (int64_t v = lo_down; v < C; v *= 3) down.push_back(v);
-    // take ramp steps from both ends, smallest first, while they fit; what is left is the plateau
-    std::vector<int64_t> head, tail;
-    int64_t used = 0;
-    for (size_t k = 0; k < std::max(up.size(), down.size()); k++) {
-      if (k < up.size() && used + up[k] <= B) { head.push_back(up[k]); used += up[k]; }
-      if (k < down.size() && used + down[k] <= B) { tail.push_back(down[k]); used += down[k]; }
-    }
-    std::vector<int64_t> targets = head;
-    const int64_t mid = B - used;
-    if (mid > 0) { const int64_t k = (mid + C - 1) / C; for (int64_t i = 0; i < k; i++) targets.push_back((mid + k - 1) / k); }
-    for (size_t k = tail.size(); k-- > 0;) targets.push_back(tail[k]);
-    if (targets.empty()) targets.push_back(C);
+    const int64_t C = std::max<int64_t>(p->opt_chunk, 1);
+    const std::vector<int64_t> targets = tb_chunk_targets(total_bytes, C, device_input);
     size_t ti = 0;
     for (int64_t d = 0; d < n_docs;) {
       const int64_t b0 = off_at(offsets, is64, d);

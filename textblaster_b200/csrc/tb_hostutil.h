@@ -1,6 +1,7 @@
 // tb_hostutil.h -- host-side helpers shared by the C ABI (tb_api.cu) and the host emulation
 // harness (tests/host_emul): building the stop-word table the kernels probe.
 #pragma once
+#include <algorithm>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -54,6 +55,38 @@ inline C4Cfg tb_c4cfg_of(const tb_c4_params& q) {
 
 // bytes the sentence-per-line copy of a chunk (nb bytes, n documents) can take: see tb_sent_off (tb_bodies.cuh)
 inline size_t tb_grown_bytes(int64_t nb, int64_t n) { return (size_t)nb + (size_t)nb / 2 + 2 * (size_t)n + 64; }
+
+// Sizes of the chunks a batch of B bytes is cut into (tb_api.cu run_impl; the documents are dealt to them in order,
+// so a chunk ends up a little under its target).  Ramp up by doubling from 64 MiB (host input: the first copy to the
+// device is exposed) or 256 MiB (text already on the device), plateau at C, ramp down by thirds to 48 MiB (the
+// results of a chunk leave while the next, smaller one is computed).  The sizes sum to B.
+inline std::vector<int64_t> tb_chunk_targets(int64_t B, int64_t C, bool device_input) {
+  if (C < 1) C = 1;
+  const int64_t lo_up = std::min<int64_t>(C, (device_input ? 256ll : 64ll) << 20), lo_down = std::min<int64_t>(C, 48ll << 20);
+  std::vector<int64_t> up, down;  // ramp sizes, smallest first
+  for (int64_t v = lo_up; v < C; v *= 2) up.push_back(v);
+  for (int64_t v = lo_down; v < C; v *= 3) down.push_back(v);
+  // take ramp steps from both ends, smallest first, while they fit; what is left is the plateau
+  std::vector<int64_t> head, tail;
+  int64_t used = 0;
+  for (size_t k = 0; k < std::max(up.size(), down.size()); k++) {
+    if (k < up.size() && used + up[k] <= B) { head.push_back(up[k]); used += up[k]; }
+    if (k < down.size() && used + down[k] <= B) { tail.push_back(down[k]); used += down[k]; }
+  }
+  int64_t mid = B - used;
+  // a remainder smaller than its neighbours would break the ramp: it joins the largest ramp step that stays <= C
+  if (mid > 0 && !(head.empty() && tail.empty())) {
+    int64_t* big = nullptr;
+    for (auto& v : head) if (!big || v > *big) big = &v;
+    for (auto& v : tail) if (!big || v > *big) big = &v;
+    if (mid < *big && *big + mid <= C) { *big += mid; mid = 0; }
+  }
+  std::vector<int64_t> targets = head;
+  if (mid > 0) { const int64_t k = (mid + C - 1) / C; for (int64_t i = 0; i < k; i++) targets.push_back(mid / k + (i < mid % k ? 1 : 0)); }
+  for (size_t k = tail.size(); k-- > 0;) targets.push_back(tail[k]);
+  if (targets.empty()) targets.push_back(C);
+  return targets;
+}
 
 // UcTables::wslead: the lead bytes of the non-ASCII White_Space characters, from the cinfo trie
 inline void tb_compute_wslead(const uint16_t* stage1, const uint16_t* stage2, uint32_t out[8]) {
