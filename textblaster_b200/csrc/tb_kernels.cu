@@ -323,7 +323,7 @@ void tb_launch_gr_rep(cudaStream_t st, const KBatch& b, const int64_t* ts, const
   if (tier == 0) k_gr_rep_s<<<sm_count * 20, 32, 0, st>>>(b, ts, te, s, cfg, step, out);
   else if (tier == 1) k_gr_rep_m<<<sm_count * 5, TB_REP_M_THREADS, TB_REP_M_SMEM, st>>>(b, ts, te, s, cfg, step, out);
   else if (tier == 2) k_gr_rep_l<<<sm_count, TB_REP_L_THREADS, TB_REP_L_SMEM, st>>>(b, ts, te, s, cfg, step, out);
-  else k_gr_rep_x<<<sm_count, TB_REP_X_THREADS, 0, st>>>(b, ts, te, s, cfg, step, out);
+  else k_gr_rep_x<<<sm_count * 3, TB_REP_X_THREADS, 0, st>>>(b, ts, te, s, cfg, step, out);  // global-memory tables: several CTAs per SM hide the latency
 }
 void tb_launch_fw_scan(cudaStream_t st, const KBatch& b, const FwCfg& cfg, const FwScratch& s, int sm_count, uint32_t* cursor) {
   if (b.n) k_fw_scan<<<persistent_grid(b.n, sm_count, 24), TB_BLOCK, 0, st>>>(b, cfg, s, cursor);
