@@ -52,7 +52,7 @@ WORKLOAD = ("C4QualityFilter+GopherQualityFilter+GopherRepetitionFilter chain, 1
 GROUP_DOCS = 65536  # row-group size of the synthetic corpus
 
 
-def shipped_chain(with_fineweb=False):
+def shipped_chain(with_fineweb=False, order="baseline"):
     """BASELINE.json configs[1] order (C4 -> GopherQuality -> GopherRepetition), parameters of the
     reference's config/pipeline_config.yaml:6-32,56-66 with the default English stop words."""
     from textblaster_b200.config import C4QualityParams, FineWebQualityParams, GopherQualityParams, GopherRepetitionParams
@@ -64,9 +64,11 @@ def shipped_chain(with_fineweb=False):
     gr = GopherRepetitionParams(dup_line_frac=0.3, dup_para_frac=0.3, dup_line_char_frac=0.2, dup_para_char_frac=0.2,
                                 top_n_grams=[(2, 0.2), (3, 0.18), (4, 0.16)],
                                 dup_n_grams=[(5, 0.15), (6, 0.14), (7, 0.13), (8, 0.12), (9, 0.11), (10, 0.10)])
+    # order="shipped": the order of config/pipeline_config.yaml (GopherRepetition -> GopherQuality -> C4), SURVEY 8d config 4
+    chain = [gr, gq, c4] if order == "shipped" else [c4, gq, gr]
     if with_fineweb:  # SURVEY 8(f) row 3, pipeline_config.yaml:74-80; not part of the headline workload
-        return [c4, gq, gr, FineWebQualityParams(0.12, False, 0.67, 30, 0.01, 0.3)]
-    return [c4, gq, gr]
+        chain.append(FineWebQualityParams(0.12, False, 0.67, 30, 0.01, 0.3))
+    return chain
 
 
 def pin_to_gpu_socket(torch, index):
@@ -196,7 +198,7 @@ def run_reference(args, rank, world):
         return
     from textblaster_b200 import synth
 
-    steps = shipped_chain(args.with_fineweb)
+    steps = shipped_chain(args.with_fineweb, args.order)
     threads = os.cpu_count() or 1
     import oracle
 
@@ -218,7 +220,7 @@ def run_reference(args, rank, world):
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "u8", "data": "synthetic",
-            "config": {"workload": WORKLOAD + (" + FineWebQualityFilter" if args.with_fineweb else ""), "docs_per_step": sample, "bytes_per_step": int(off[-1]),
+            "config": {"workload": WORKLOAD + (" + FineWebQualityFilter" if args.with_fineweb else "") + (" [shipped step order]" if args.order == "shipped" else ""), "docs_per_step": sample, "bytes_per_step": int(off[-1]),
                        "note": "CPU arm: each step is a bounded sample of the workload"},
             "text_gbs": float(off[-1]) / dt / 1e9,
             "cpu_baseline": {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
@@ -238,6 +240,7 @@ def main():
     ap.add_argument("--chunk-mb", type=int, default=1024)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--decode-entities", action="store_true", help="also run the HTML-entity pre-pass of the reader (SURVEY 8f row 1); not part of the headline workload")
+    ap.add_argument("--order", default="baseline", choices=["baseline", "shipped"], help="step order: BASELINE.json configs[1] (C4, GopherQuality, GopherRepetition; the headline) or the shipped pipeline_config.yaml (GopherRepetition, GopherQuality, C4)")
     ap.add_argument("--with-fineweb", action="store_true",
                     help="append FineWebQualityFilter (SURVEY 8(f) row 3) to the chain; not the headline workload")
     args = ap.parse_args()
@@ -290,7 +293,7 @@ def main():
         pos += int(o[-1]); doc += len(o) - 1
     del parts
     t_gen = time.perf_counter() - t_gen
-    steps = shipped_chain(args.with_fineweb)
+    steps = shipped_chain(args.with_fineweb, args.order)
     pipe = GpuBatchPipeline(steps, device=local_rank)
     pipe.set_option(_abi.TB_OPT_CHUNK_BYTES, args.chunk_mb << 20)
     if args.decode_entities:
@@ -405,7 +408,7 @@ def main():
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": dt_dev / K * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "u8", "data": "synthetic",
-            "config": {"workload": WORKLOAD + (" + FineWebQualityFilter" if args.with_fineweb else "") + (" + HTML entity pre-pass" if args.decode_entities else ""), "docs_per_gpu_per_step": n_docs, "bytes_per_gpu_per_step": n_bytes,
+            "config": {"workload": WORKLOAD + (" + FineWebQualityFilter" if args.with_fineweb else "") + (" [shipped step order]" if args.order == "shipped" else "") + (" + HTML entity pre-pass" if args.decode_entities else ""), "docs_per_gpu_per_step": n_docs, "bytes_per_gpu_per_step": n_bytes,
                        "sharding": "row groups of %d docs round-robin over ranks, no data-path collective; keep masks gathered on the host (%.3f s, outside the timed region)" % (min(GROUP_DOCS, args.docs), gather_s),
                        "kept_total": int(sum(int(m.sum()) for m in masks)),
                        "chunk_mb": args.chunk_mb, "host": numa, "l2": "inputs (%.2f GB per step) larger than the 126 MB L2" % (n_bytes / 1e9),
