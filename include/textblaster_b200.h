@@ -242,9 +242,11 @@ typedef struct tb_fw_stats {
 
 /* Document flags (information, never affects decisions) */
 enum {
-  TB_DOCFLAG_COMPLEX_SCRIPT = 1 << 0 /* has Han/Kana/Thai/Lao/Khmer/Burmese text: ICU4X new_auto()
-                                        (text.rs:107) would re-segment it with dictionary/LSTM data;
-                                        we apply plain UAX #29 -- parity unpinned for such documents */
+  TB_DOCFLAG_COMPLEX_SCRIPT = 1 << 0, /* has Han/Kana/Thai/Lao/Khmer/Burmese text: ICU4X new_auto()
+                                         (text.rs:107) would re-segment it with dictionary/LSTM data;
+                                         we apply plain UAX #29 -- parity unpinned for such documents */
+  TB_DOCFLAG_BAD_OFFSETS = 1 << 1     /* tb_gopher_repetition_noalloc only: the document's offsets were decreasing
+                                         or outside [0, n_bytes]; it was not processed (keep = 0, counters zero) */
 };
 
 typedef struct tb_batch_out {
@@ -332,7 +334,9 @@ void tb_pipeline_reset_kernel_times(tb_pipeline* p);
  * documents and TB_NOALLOC_MAX_BYTES bytes of text per call (TB_ERR_INVALID_ARGUMENT beyond that).
  *
  * All pointers are DEVICE pointers owned by the caller: utf8_dev / offsets_dev (n_docs + 1 int64,
- * offsets_dev[n_docs] <= n_bytes) in; stats_dev[n_docs] and keep_dev[n_docs] (1 = passed) out.  Work
+ * non-decreasing, 0 <= offsets <= n_bytes; the offsets cannot be checked on the host without a
+ * synchronisation, so a document whose offsets break this is skipped on the device: keep = 0 and
+ * flags = TB_DOCFLAG_BAD_OFFSETS) in; stats_dev[n_docs] and keep_dev[n_docs] (1 = passed) out.  Work
  * is enqueued on cuda_stream (a cudaStream_t, NULL = default stream) and not synchronised.  The first
  * call on a device performs a blocking set-up (address lookup of the array, table upload): make it at
  * start-up, before any stream capture.  All calls share the array: calls whose GPU work overlaps race.

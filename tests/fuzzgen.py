@@ -127,3 +127,19 @@ def boundary_docs():
     docs.append("First kept line here.\n" + "\n" * 70 + "Second kept line here.\n" + "\n" * 33 + "x\n" * 40 + "Third kept line is here.")
     docs.append("\n" * 100 + "Only line, it ends well." + "\n" * 64)
     return docs
+
+
+def dense_word_docs():
+    """Documents with the most words a text can hold per byte: a one-byte letter or digit alternating with a
+    two-byte symbol that is a word of its own (not in PUNCTUATION, Word_Break = Other) gives two words per
+    three bytes.  Each is followed by an ordinary document so that a write past the first one's word slots shows
+    up in its neighbour."""
+    docs = []
+    for sym, k in (("\u00a9", 4), ("\u00a9", 40), ("\u00d7", 300), ("\u00a7", 700), ("\u00b0", 3000), ("\u00a9", 11)):
+        for lead in ("", "zz ", "\n"):
+            docs.append(lead + ("a" + sym) * k + "a")
+            docs.append("An ordinary line of text follows here. It has two sentences.\nAnd a second line that repeats a b c d e f a b c d e f.")
+    docs.append("".join("x\u00a9"[i % 2] for i in range(5000)) + "\n" + "7\u00d7" * 100)
+    docs.append("\u00a9" * 600)
+    docs.append("a\u00a9 " * 400)
+    return docs

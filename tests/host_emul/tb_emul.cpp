@@ -150,7 +150,8 @@ extern "C" int tbe_run_chain(const tb_step_cfg* steps, size_t n_steps, const uin
   const int64_t nb = decode_entities ? (int64_t)tb_grown_bytes(nb_in, n) : nb_in;  // extent of the text the chain sees
   bool any_sent = false;
   for (size_t s = 0; s < n_steps; s++) any_sent |= steps[s].type == TB_STEP_C4_QUALITY && !steps[s].u.c4.split_paragraph;
-  const size_t n1 = (size_t)n + 1, units = (any_sent ? tb_grown_bytes(nb, n) : (size_t)nb) / 2 + n1 + 1;
+  const size_t n1 = (size_t)n + 1, cbx = any_sent ? tb_grown_bytes(nb, n) : (size_t)nb;
+  const size_t wunits = tb_word_units(cbx, (size_t)n), units = tb_line_units(cbx, (size_t)n);
   // tables
   std::vector<uint64_t> pw(TB_POWTAB);
   { uint32_t a = 1, b = 1; for (int i = 0; i < TB_POWTAB; i++) { pw[i] = ((uint64_t)a << 32) | b; a = tb_mm(a, TB_B1); b = tb_mm(b, TB_B2); } }
@@ -212,8 +213,8 @@ extern "C" int tbe_run_chain(const tb_step_cfg* steps, size_t n_steps, const uin
       g.dup_line_frac = q.dup_line_frac; g.dup_para_frac = q.dup_para_frac;
       g.dup_line_char_frac = q.dup_line_char_frac; g.dup_para_char_frac = q.dup_para_char_frac;
       for (int k = 0; k < TB_MAX_NGRAMS; k++) { g.top_n[k] = q.top_n[k]; g.top_frac[k] = q.top_frac[k]; g.dup_n[k] = q.dup_n[k]; g.dup_frac[k] = q.dup_frac[k]; }
-      GrScratch gs{(uint64_t*)G64(units), G32(units), (uint64_t*)G64(units), G32(units), G8(units),
-                   (GrDoc*)G8(n1 * sizeof(GrDoc)), G32(units * TB_REP_K + n1 * TB_REP_DOC_EXTRA), G32(4 * n1), G32(16), n};
+      GrScratch gs{(uint64_t*)G64(wunits), G32(wunits), (uint64_t*)G64(units), G32(units), G8(units),
+                   (GrDoc*)G8(n1 * sizeof(GrDoc)), G32(wunits * TB_REP_K + n1 * TB_REP_DOC_EXTRA), G32(4 * n1), G32(16), n};
       memset(gs.counters, 0, 64);
       for (int64_t d = 0; d < n; d++) body_trim(b, ascii, ts, te, d);
       build_lut(TB_LUT_GR, 0u);

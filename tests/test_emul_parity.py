@@ -57,6 +57,11 @@ def test_ascii_fast_path(name):
     _check(name, texts)
 
 
+@pytest.mark.parametrize("name", ["gr_shipped", "gr_open", "gq_shipped", "gq_open", "baseline_order", "shipped_order", "fw_open"])
+def test_dense_word_documents(name):  # two words per three bytes: the bound the word slots are sized by
+    _check(name, fuzzgen.dense_word_docs())
+
+
 def test_repetition_tiers():
     """tb_rep.cuh picks shared-memory (warp / CTA) or global work areas by document size; a document
     with many repeated n-grams exercises the candidate walk in each tier."""

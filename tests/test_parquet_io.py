@@ -56,7 +56,7 @@ def _write_input(path, large=False, with_null=False):
         texts[1] = None
     tab = pa.table({"id": pa.array([f"d{i}" for i in range(len(DOCS))]), "text": pa.array(texts, t),
                     "source": pa.array(["s0", None, "s2", "s3"]), "added": pa.array([738000, None, 738002, 738003], pa.int32()).cast(pa.date32()),
-                    "metadata": pa.array(['{"lang":"en"}', None, "not json", None])})
+                    "metadata": pa.array(['{"lang":"en"}', None, "not json", '{"a": 1, "b": "x"}'])})
     pq.write_table(tab, path)
 
 
@@ -83,6 +83,10 @@ def test_outcome_files_schema_and_routing(tmp_path):
     assert md0["lang"] == "en" and md0["c4_filter_status"] == "passed" and md0["gopher_repetition_filter_status"] == "passed"
     md1 = json.loads(e["metadata"][0])
     assert md1 == {"c4_filter_status": "filtered", "c4_filter_reasons": "curly_bracket"}   # later steps never ran
+    # a metadata object with a non-string value does not deserialise into HashMap<String, String>: the reader
+    # falls back to an empty map (parquet_reader.rs:224-229), so only the step's keys are written
+    md3 = json.loads(e["metadata"][1])
+    assert "a" not in md3 and "b" not in md3 and md3["c4_filter_status"] == "filtered"
     assert kept.column("added").cast(pa.int32()).to_pylist() == [738000, 738002]          # days pass through unchanged
 
 

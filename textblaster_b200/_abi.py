@@ -71,6 +71,7 @@ TB_FW_REASON_LIST_NO_WORDS = 1 << 4
 TB_FW_REASON_LIST_RATIO = 1 << 5
 
 TB_DOCFLAG_COMPLEX_SCRIPT = 1 << 0
+TB_DOCFLAG_BAD_OFFSETS = 1 << 1
 
 TB_OPT_RETURN_CONTENT = 1
 TB_OPT_VALIDATE_UTF8 = 2

@@ -315,14 +315,15 @@ int ensure_chunk_buffers(tb_pipeline* p, int64_t n, int64_t nb, bool host_input)
   ENS(p->rs0, n1 * 8); ENS(p->re0, n1 * 8); ENS(p->rs, n1 * 8); ENS(p->re, n1 * 8); ENS(p->ts, n1 * 8); ENS(p->te, n1 * 8);
   for (int i = 0; i < 2; i++) { ENS(p->alive[i], n1); ENS(p->failed[i], n1); ENS(p->out_off[i], (n1 + 1) * 8); }
   ENS(p->rewritten, n1); ENS(p->len, n1 * 8); ENS(p->bad, 16); ENS(p->cursors, 256); ENS(p->order, n1 * 4); ENS(p->sizecls, n1);
-  size_t units = cb / 2 + n1 + 1;  // word / line slots are indexed by the position of the document in its buffer
+  // word / line slots are indexed by the position of the document in its buffer (tb_wunit / tb_lunit)
+  const size_t wunits = tb_word_units(cb, (size_t)n), units = tb_line_units(cb, (size_t)n);
   for (size_t s = 0; s < p->steps.size(); s++) {
     const StepHost& sh = p->steps[s];
     for (int i = 0; i < 2; i++) ENS(p->stats[s][i], n1 * stat_size(sh.type));
     if (sh.type == TB_STEP_GOPHER_REPETITION) {
-      ENS(p->g_wh, units * 8); ENS(p->g_wl, units * 4); ENS(p->g_lh, units * 8); ENS(p->g_ll, units * 4); ENS(p->g_lg, units);
+      ENS(p->g_wh, wunits * 8); ENS(p->g_wl, wunits * 4); ENS(p->g_lh, units * 8); ENS(p->g_ll, units * 4); ENS(p->g_lg, units);
       ENS(p->g_doc, n1 * sizeof(GrDoc));
-      ENS(p->g_work, (units * TB_REP_K + n1 * TB_REP_DOC_EXTRA) * 4);
+      ENS(p->g_work, (wunits * TB_REP_K + n1 * TB_REP_DOC_EXTRA) * 4);
       ENS(p->g_lists, 4 * n1 * 4); ENS(p->g_counters, 64);
     } else if (sh.type == TB_STEP_FINEWEB_QUALITY) {
       ENS(p->f_lh, units * 8); ENS(p->f_ll, units * 4); ENS(p->f_doc, n1 * sizeof(FwDoc)); ENS(p->f_tab, (units * 2 + n1 * 16) * 4);

@@ -71,7 +71,7 @@ TB_D_NOINLINE void gq_doc_walk(const Classifier& C, const TextRange& R, const Sw
     if (p0 < R.re) { int64_t p1 = p0 + TB_STRETCH < R.re ? p0 + TB_STRETCH : R.re; gq_lane(C, R, sw, p0, p1, acc); }
   }
 }
-#define TB_GQ_STAGE (17 * 32)  // stop-word candidates one tile can hold
+#define TB_GQ_STAGE (23 * 32)  // stop-word candidates one tile can hold: a stretch ends at most 22 words (two per three bytes) + 1
 TB_D bool gq_doc_tiles(const KBatch& a, const LutEntry* lut, uint32_t* stage, const Classifier& C, const SwTable& sw,
                        const TextRange& R, GqAcc& acc, int lane);
 // `stage`: 2 * TB_GQ_STAGE words of per-warp scratch (shared memory)
@@ -144,9 +144,9 @@ struct GrTotals { uint32_t W, NL, flags; uint64_t nchars; };
 // general path: segment-walking lanes (tb_lanes.cuh)
 TB_D_NOINLINE void gr_doc_walk(const KBatch& a, const Classifier& C, const TextRange& R, const GrScratch& s, int64_t d, int lane,
                       GrTotals& out) {
-  const uint64_t ub = (uint64_t)(R.rs >> 1) + (uint64_t)d;
-  uint64_t* wh = s.wh + ub; uint32_t* wl = s.wl + ub;
-  uint64_t* lh = s.lh + ub; uint32_t* ll = s.ll + ub; uint8_t* lg = s.lg + ub;
+  const uint64_t uw = tb_wunit(R.rs, d), ul = tb_lunit(R.rs, d);
+  uint64_t* wh = s.wh + uw; uint32_t* wl = s.wl + uw;
+  uint64_t* lh = s.lh + ul; uint32_t* ll = s.ll + ul; uint8_t* lg = s.lg + ul;
   uint32_t W = 0, NL = 0, flags = 0;
   uint64_t nchars = 0;
   HL carry{0, 0, 0};  // open line piece entering the tile
@@ -202,7 +202,7 @@ TB_D_NOINLINE void gr_doc_walk(const KBatch& a, const Classifier& C, const TextR
   }
   out.W = W; out.NL = NL; out.flags = flags; out.nchars = nchars;
 }
-#define TB_GR_STAGE_WORDS (17 * 32)  // word ends one tile can hold: at most 16 + 1 per stretch
+#define TB_GR_STAGE_WORDS (23 * 32)  // word ends one tile can hold: at most 22 + 1 per stretch (two words per three bytes)
 TB_D bool gr_doc_tiles(const KBatch& a, const LutEntry* lut, uint32_t* stage, const Classifier& C, const TextRange& R,
                        const GrScratch& s, int64_t d, int lane, GrTotals& out);
 
@@ -273,8 +273,8 @@ TB_D void body_gr_rep_l(const KBatch& a, uint8_t* smem, const int64_t* ts, const
 TB_D void body_gr_rep_x(const KBatch& a, uint64_t* red, const int64_t* ts, const int64_t* te, const GrScratch& s,
                         const GrCfg& cfg, int step, tb_gr_stats* out, int64_t d, int tid) {
   const int64_t rs = ts[d], re = te[d];
-  const uint64_t ub = (uint64_t)(rs >> 1) + (uint64_t)d;
-  const uint32_t U = (uint32_t)((re - rs) >> 1) + 1u;  // >= number of words, >= number of line pieces
+  const uint64_t ub = tb_wunit(rs, d);
+  const uint32_t U = tb_wunits_of(re - rs);  // >= number of words, >= number of line pieces
   uint32_t* work = s.work + ub * TB_REP_K + (uint64_t)d * TB_REP_DOC_EXTRA;
   RepArrays A;
   A.H = (uint64_t*)work;                   // U entries

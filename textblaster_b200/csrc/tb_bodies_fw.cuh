@@ -62,7 +62,7 @@ TB_D void body_fw_scan(const KBatch& a, const uint16_t* s_ascii, const LutEntry*
   Classifier C{s_ascii, a.uc};
   TextRange R{a.text, a.rs[d], a.re[d]};
   const uint8_t* t = R.t;
-  const uint64_t ub = (uint64_t)(R.rs >> 1) + (uint64_t)d;
+  const uint64_t ub = tb_lunit(R.rs, d);
   uint64_t* lh = s.lh + ub; uint32_t* ll = s.ll + ub;
   const uint64_t* powtab = a.uc.powtab;
   const uint32_t below_lane = tb_below(lane);
@@ -209,7 +209,7 @@ TB_D void body_fw_scan(const KBatch& a, const uint16_t* s_ascii, const LutEntry*
 TB_D void body_fw_fin(const KBatch& a, uint32_t* smem_tab, const FwCfg& cfg, const FwScratch& s, int step, tb_fw_stats* out,
                       int64_t d, int lane) {
   const FwDoc fd = s.doc[d];
-  const uint64_t ub = (uint64_t)(a.rs[d] >> 1) + (uint64_t)d;
+  const uint64_t ub = tb_lunit(a.rs[d], d);
   const uint32_t NL = fd.n_lines;
   uint32_t de = 0; uint64_t db = 0;
   if (NL) {

@@ -277,9 +277,9 @@ TB_D HL hl_fold(uint32_t a, uint32_t b, uint32_t len) { HL r; r.a = tb_hfold(a);
 TB_D bool gr_doc_tiles(const KBatch& a, const LutEntry* lut, uint32_t* stage, const Classifier& C, const TextRange& R,
                        const GrScratch& s, int64_t d, int lane, GrTotals& out) {
   uint32_t* st_a = stage; uint32_t* st_b = stage + TB_GR_STAGE_WORDS; uint32_t* st_n = stage + 2 * TB_GR_STAGE_WORDS;
-  const uint64_t ub = (uint64_t)(R.rs >> 1) + (uint64_t)d;
-  uint64_t* wh = s.wh + ub; uint32_t* wl = s.wl + ub;
-  uint64_t* lh = s.lh + ub; uint32_t* ll = s.ll + ub; uint8_t* lg = s.lg + ub;
+  const uint64_t uw = tb_wunit(R.rs, d), ul = tb_lunit(R.rs, d);
+  uint64_t* wh = s.wh + uw; uint32_t* wl = s.wl + uw;
+  uint64_t* lh = s.lh + ul; uint32_t* ll = s.ll + ul; uint8_t* lg = s.lg + ul;
   const uint64_t* powtab = a.uc.powtab;
   const uint32_t below_lane = tb_below(lane);
   uint32_t W = 0, NLc = 0, flags = 0;

@@ -53,6 +53,11 @@ inline C4Cfg tb_c4cfg_of(const tb_c4_params& q) {
                q.min_num_sentences, q.min_words_per_line, q.max_word_length};
 }
 
+// units of the per-document scratch of a chunk whose content buffer spans cb bytes and holds n documents
+// (tb_wunit / tb_lunit in tb_kernels.cuh: the last document ends at most at unit f(cb) + n)
+inline size_t tb_word_units(size_t cb, size_t n) { return 2 * cb / 3 + n + 2; }
+inline size_t tb_line_units(size_t cb, size_t n) { return cb / 2 + n + 2; }
+
 // bytes the sentence-per-line copy of a chunk (nb bytes, n documents) can take: see tb_sent_off (tb_bodies.cuh)
 inline size_t tb_grown_bytes(int64_t nb, int64_t n) { return (size_t)nb + (size_t)nb / 2 + 2 * (size_t)n + 64; }
 

@@ -54,12 +54,22 @@ struct GrDoc {
   uint32_t W, NL, flags, empty;
 };
 
-// scratch of the repetition filter; all arrays are indexed from ubase(d) = (rs[d] >> 1) + d units
+// Per-document scratch is addressed from the document's byte offset, without a prefix sum over the batch.
+//   words: a text of L bytes holds at most (2L + 1) / 3 of them -- only the letters and digits are one-byte
+//   word characters and two of those never break apart (WB5, WB8-10), so two adjacent words take at least
+//   three bytes ("a\u00a9a\u00a9a": 5 words in 7 bytes).  Document d owns the units [tb_wunit(rs, d), tb_wunit(rs', d + 1)),
+//   at least floor(2L / 3) + 1 of them.
+//   line pieces: non-empty and separated by '\n', at most (L + 1) / 2: units from tb_lunit.
+TB_HD uint64_t tb_wunit(int64_t rs, int64_t d) { return (uint64_t)((2 * rs) / 3) + (uint64_t)d; }
+TB_HD uint64_t tb_lunit(int64_t rs, int64_t d) { return (uint64_t)(rs >> 1) + (uint64_t)d; }
+TB_HD uint32_t tb_wunits_of(int64_t len) { return (uint32_t)((2 * len) / 3) + 1u; }  // word slots a text of len bytes needs at most
+
+// scratch of the repetition filter; word arrays are indexed from tb_wunit(rs[d], d), line arrays from tb_lunit(rs[d], d)
 struct GrScratch {
   uint64_t* wh; uint32_t* wl;               // words: hash, byte length
   uint64_t* lh; uint32_t* ll; uint8_t* lg;  // line pieces: hash, byte length, "preceded by >= 2 newlines"
   GrDoc* doc;                               // [n]
-  uint32_t* work;                           // tier-L work area, TB_REP_K words per unit + TB_REP_DOC_EXTRA per doc
+  uint32_t* work;                           // tier-X work area, TB_REP_K words per word unit + TB_REP_DOC_EXTRA per doc
   uint32_t* lists;                          // [4][n] document ids per tier (S, M, L, X), filled by the scan pass
   uint32_t* counters;                       // [16]: list lengths [0..3], work cursors [4..7], scan cursor [8]
   int64_t n;
@@ -81,7 +91,7 @@ struct FwDoc {
   uint64_t n_chars;  // chars other than '\n'
   uint32_t n_lines, n_stop, n_short, n_words, n_newlines, flags;
 };
-// non-blank lines of document d: hash / byte length at unit (rs[d] >> 1) + d; tab: 2 words per unit + 16 per document
+// non-blank lines of document d: hash / byte length at unit tb_lunit(rs[d], d); tab: 2 words per unit + 16 per document
 struct FwScratch {
   uint64_t* lh; uint32_t* ll;
   FwDoc* doc;

@@ -116,7 +116,7 @@ TB_HD void gq_lane(const Classifier& C, const TextRange& R, const SwTable& sw, i
 // ---------------------------------------------------------------------------------------------
 // GopherRepetitionFilter scan pass (gopher_rep.rs:57-58,80-84,120-124,159)
 // ---------------------------------------------------------------------------------------------
-#define TB_LANE_MAXW 17  // a 32-byte stretch starts at most 16 words (+1 slack)
+#define TB_LANE_MAXW 23  // a 32-byte stretch starts at most 22 words (two per three bytes; +1 slack)
 struct GrLane {
   uint32_t nw;
   uint64_t wh[TB_LANE_MAXW];

@@ -98,10 +98,45 @@ int setup_device(int dev, DeviceState** out) {
     cudaDeviceProp prop;
     if (cudaGetDeviceProperties(&prop, dev) == cudaSuccess) st.sm_count = prop.multiProcessorCount;
     if (tb_kernels_init() != 0) { cudaGetLastError(); return fail(TB_ERR_CUDA, "cudaFuncSetAttribute failed (not an sm_100-class device?)"); }
+    // The table uploads come from pageable memory: cudaMemcpy may return once the data is staged, with the DMA still
+    // ordered on the NULL stream only.  The caller's stream may be a non-blocking one, so wait for the device here
+    // (the first call is documented as blocking) before any kernel can read the tables.
+    if (cudaDeviceSynchronize() != cudaSuccess) { cudaGetLastError(); return fail(TB_ERR_CUDA, "cudaDeviceSynchronize after the table upload failed"); }
     st.ready = true;
   }
   *out = &st;
   return TB_OK;
+}
+
+// Document ranges from the caller's offsets, which are device memory this entry point cannot inspect on the host
+// (it must not synchronise).  The scratch is carved for n_bytes of text, so an offset outside [0, n_bytes] or a
+// decreasing pair would index outside the static array: such a document is not processed.  It gets an empty range,
+// keep = 0 and statistics that are all zero except flags = TB_DOCFLAG_BAD_OFFSETS.  A document [a, b) is accepted
+// when hi <= a <= b <= n_bytes, hi being the end of the last accepted document before it (0 at the start): accepted
+// documents are then disjoint and in order, which is what the per-document scratch layout relies on.  One CTA
+// (n <= 2048); the walk over the offsets is sequential and short.
+__global__ void k_noalloc_ranges(const int64_t* off, int64_t n, int64_t n_bytes, int64_t* rs, int64_t* re, uint8_t* keep,
+                                 int8_t* failed, tb_gr_stats* stats) {
+  __shared__ int64_t s_pos[TB_NOALLOC_MAX_DOCS];  // rejected document d: where its empty range goes (-1: accepted)
+  if (threadIdx.x == 0) {
+    int64_t hi = 0;
+    for (int64_t d = 0; d < n; d++) {
+      const int64_t a = off[d], b = off[d + 1];
+      if (hi <= a && a <= b && b <= n_bytes) { s_pos[d] = -1; hi = b; }
+      else s_pos[d] = hi;
+    }
+  }
+  __syncthreads();
+  for (int64_t d = threadIdx.x; d < n; d += blockDim.x) {
+    if (s_pos[d] < 0) { rs[d] = off[d]; re[d] = off[d + 1]; keep[d] = 1; failed[d] = -1; }
+    else {
+      rs[d] = s_pos[d]; re[d] = s_pos[d]; keep[d] = 0; failed[d] = 0;
+      tb_gr_stats z;
+      memset(&z, 0, sizeof z);
+      z.flags = TB_DOCFLAG_BAD_OFFSETS;
+      stats[d] = z;
+    }
+  }
 }
 
 }  // namespace
@@ -133,17 +168,17 @@ int tb_gopher_repetition_noalloc(const uint8_t* utf8_dev, const int64_t* offsets
   cudaStream_t stream = (cudaStream_t)cuda_stream;
 
   // carve the per-call arrays out of the static array (nothing here allocates)
-  const size_t n1 = (size_t)n_docs + 1, units = (size_t)n_bytes / 2 + n1 + 1;
+  const size_t n1 = (size_t)n_docs + 1, wunits = tb_word_units((size_t)n_bytes, (size_t)n_docs), units = tb_line_units((size_t)n_bytes, (size_t)n_docs);
   size_t off = st->tables_end;
   auto carve = [&](size_t bytes) -> unsigned char* { unsigned char* p = st->base + off; off = align_up(off + bytes, 256); return p; };
   int64_t* rs = (int64_t*)carve(n1 * 8); int64_t* re = (int64_t*)carve(n1 * 8);
   int64_t* ts = (int64_t*)carve(n1 * 8); int64_t* te = (int64_t*)carve(n1 * 8);
   int8_t* failed = (int8_t*)carve(n1);
   GrScratch g;
-  g.wh = (uint64_t*)carve(units * 8); g.wl = (uint32_t*)carve(units * 4);
+  g.wh = (uint64_t*)carve(wunits * 8); g.wl = (uint32_t*)carve(wunits * 4);
   g.lh = (uint64_t*)carve(units * 8); g.ll = (uint32_t*)carve(units * 4); g.lg = (uint8_t*)carve(units);
   g.doc = (GrDoc*)carve(n1 * sizeof(GrDoc));
-  g.work = (uint32_t*)carve((units * TB_REP_K + n1 * TB_REP_DOC_EXTRA) * 4);
+  g.work = (uint32_t*)carve((wunits * TB_REP_K + n1 * TB_REP_DOC_EXTRA) * 4);
   g.lists = (uint32_t*)carve(4 * n1 * 4);
   g.counters = (uint32_t*)carve(64);  // [12], [13] double as the counts of the work order
   uint32_t* order = (uint32_t*)carve(n1 * 4);
@@ -159,8 +194,8 @@ int tb_gopher_repetition_noalloc(const uint8_t* utf8_dev, const int64_t* offsets
 
   // state that must start at zero: tier list lengths and work cursors (the array keeps the last call's contents)
   if (cudaMemsetAsync(g.counters, 0, 64, stream) != cudaSuccess) { cudaGetLastError(); return fail(TB_ERR_CUDA, "cudaMemsetAsync failed"); }
-  // keep_dev doubles as the kernels' "alive" flag; init_ranges sets it to 1 for every document
-  tb_launch_init_ranges(stream, offsets_dev, 1, 0, n_docs, 0, rs, re, keep_dev, failed);
+  // keep_dev doubles as the kernels' "alive" flag: 1 for every document whose offsets are usable
+  k_noalloc_ranges<<<1, 1024, 0, stream>>>(offsets_dev, n_docs, n_bytes, rs, re, keep_dev, failed, stats_dev);
   tb_launch_order(stream, rs, re, n_docs, order, g.counters + 12, sizecls);
   KBatch b{utf8_dev, rs, re, keep_dev, failed, n_docs, st->uc, 0, n_bytes, 0u, order, g.counters + 12, sizecls};
   tb_launch_trim(stream, b, ts, te);

@@ -225,9 +225,9 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
     return;
   }
   const int64_t rs = ts[d];
-  const uint64_t ub = (uint64_t)(rs >> 1) + (uint64_t)d;
-  const uint64_t* wh_g = s.wh + ub; const uint32_t* wl_g = s.wl + ub;
-  const uint64_t* lh = s.lh + ub; const uint32_t* ll = s.ll + ub; const uint8_t* lg = s.lg + ub;
+  const uint64_t uw = tb_wunit(rs, d), ul = tb_lunit(rs, d);
+  const uint64_t* wh_g = s.wh + uw; const uint32_t* wl_g = s.wl + uw;
+  const uint64_t* lh = s.lh + ul; const uint32_t* ll = s.ll + ul; const uint8_t* lg = s.lg + ul;
   const uint32_t W = gd.W, NL = gd.NL;
   const double text_char_len = (double)(gd.char_len ? gd.char_len : 1);
   uint32_t reasons = 0;

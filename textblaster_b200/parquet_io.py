@@ -176,9 +176,12 @@ def run_parquet(pipeline, cfg: ParquetInputConfig, kept_path: str, excluded_path
         for i in range(n):
             md = {}
             if in_md[i]:
+                # serde_json::from_str::<HashMap<String, String>>: anything but an object whose values are all
+                # strings fails to parse, and the reader then falls back to an empty map (parquet_reader.rs:224-229)
                 try:
-                    md = {str(k): str(v) for k, v in json.loads(in_md[i]).items()}
-                except (ValueError, AttributeError):
+                    obj = json.loads(in_md[i])
+                    md = dict(obj) if isinstance(obj, dict) and all(isinstance(v, str) for v in obj.values()) else {}
+                except ValueError:
                     md = {}
             step_md, _reason = res.metadata_and_reason(i)
             md.update(step_md)
