@@ -188,7 +188,54 @@ def cpu_baseline(utf8, off, steps, budget_s=12.0, threads=None):
     nbytes = int(off[sample] - off[0])
     return {"value": sample / dt, "unit": UNIT, "cores": threads, "kind": "port",
             "sample": f"first {sample} docs ({nbytes / 1e6:.1f} MB) of the workload, {dt:.2f} s, oracle/tb_oracle.cpp with {threads} threads",
-            "text_gbs": nbytes / dt / 1e9, "keep_rate": float(r.keep.mean()) if sample else None}
+            "text_gbs": nbytes / dt / 1e9, "keep_rate": float(r.keep.mean()) if sample else None}, r, sample
+
+
+def parity_check(pipe, steps, utf8, off, sample, ores):
+    """The benchmarked run, checked: the GPU's results for the documents of the cpu_baseline sample against the
+    oracle's for the same documents -- keep, failing step, every statistics field of every step that ran, and the
+    rewritten content byte for byte.  Tolerance 0.  Returns {"docs", "values", "mismatches", ...}."""
+    from parity_util import executed
+
+    sub_off = (off[:sample + 1] - off[0]).astype(np.int64)
+    res = pipe.run_packed(utf8[off[0]:off[sample]], sub_off)
+    mism, values, first = 0, 0, None
+
+    def note(what, idx):
+        nonlocal first
+        if first is None and len(idx):
+            first = f"{what} at doc {int(idx[0])}"
+
+    bad = np.flatnonzero((res.keep != ores.keep) | (res.failed_step != ores.failed_step))
+    mism += len(bad); values += 2 * sample
+    note("keep/failed_step", bad)
+    for s in range(len(steps)):
+        ran = executed(ores.failed_step, s)
+        a, b = res.stats[s], ores.stats[s]
+        for name in a.dtype.names:
+            x, y = a[name][ran], b[name][ran]
+            ne = x != y
+            if ne.ndim > 1:
+                ne = ne.any(axis=1)
+            bad = np.flatnonzero(ran)[ne]
+            mism += len(bad); values += int(ran.sum())
+            note(f"step {s} field {name}", bad)
+    content = None
+    if res.content is not None:
+        ob, oo = ores.content_packed()
+        same = np.array_equal(res.content_offsets, oo) and np.array_equal(res.content, ob)
+        content = bool(same)
+        values += sample
+        if not same:
+            lens_a, lens_b = np.diff(res.content_offsets), np.diff(oo)
+            bad = np.flatnonzero(lens_a != lens_b)
+            mism += max(len(bad), 1)
+            note("content", bad if len(bad) else np.array([0]))
+    out = {"docs": int(sample), "values": int(values), "mismatches": int(mism), "content_identical": content,
+           "checked": "GPU (tb_pipeline_run_batch) vs oracle on the cpu_baseline sample: keep, failed_step, all statistics of executed steps, rewritten content; tolerance 0"}
+    if first:
+        out["first_mismatch"] = first
+    return out
 
 
 def run_reference(args, rank, world):
@@ -446,9 +493,16 @@ def main():
             "kernels_ms_per_step": {k: round(v[0] / K, 3) for k, v in sorted(ktimes.items(), key=lambda kv: -kv[1][0])},
             "clocks": clocks,
         }
+        parity_failed = False
         if world == 1 and not args.no_cpu_baseline:
-            line["cpu_baseline"] = cpu_baseline(utf8, off, steps)
+            line["cpu_baseline"], ores, sample = cpu_baseline(utf8, off, steps)
+            if not args.decode_entities:  # (the oracle arm sees the text as generated; the entity pre-pass has its own tests)
+                line["parity"] = parity_check(pipe, steps, utf8, off, sample, ores)
+                parity_failed = line["parity"]["mismatches"] != 0
         emit(line)
+        if parity_failed:
+            sys.stderr.write("bench.py: the GPU results differ from the oracle on the checked sample: %s\n" % json.dumps(line["parity"]))
+            sys.exit(1)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
