@@ -329,7 +329,7 @@ void tb_pipeline_reset_kernel_times(tb_pipeline* p);
  * memory is handed out once by a pool that another component owns (fixed per-tenant quota, a host
  * runtime that pre-partitions the GPU), or latency-critical sections where cudaMalloc (which can
  * synchronise the device) is forbidden.  tb_pipeline_run_batch* grow their buffers with cudaMalloc
- * on demand; this call takes every intermediate from a fixed 16 MiB array inside the library image
+ * on demand; this call takes every intermediate from a fixed 24 MiB array inside the library image
  * (resident on every GPU that loads the library) and therefore accepts at most TB_NOALLOC_MAX_DOCS
  * documents and TB_NOALLOC_MAX_BYTES bytes of text per call (TB_ERR_INVALID_ARGUMENT beyond that).
  *

@@ -33,6 +33,13 @@ def lib():
     return _lib
 
 
+def rep_stats(reset=True):
+    """(word ends seen, candidates kept, documents) of the signature-pruned duplicate n-gram levels since the last reset"""
+    w, i, p = C.c_uint64(), C.c_uint64(), C.c_uint64()
+    lib().tbe_rep_stats(C.byref(w), C.byref(i), C.byref(p), 1 if reset else 0)
+    return w.value, i.value, p.value
+
+
 def chunk_targets(total_bytes, chunk_bytes, device_input=False):
     """tb_chunk_targets (csrc/tb_hostutil.h): the sizes the host executor cuts a batch into"""
     out = np.zeros(4096, np.int64)

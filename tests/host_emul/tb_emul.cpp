@@ -22,6 +22,11 @@ thread_local SimtWarp* simt_warp = nullptr;
 thread_local int simt_lane = 0;
 thread_local SimtBlock* simt_block = nullptr;
 uint64_t tbe_stat_tiles = 0, tbe_stat_walk = 0;
+uint64_t tbe_stat_rep_words = 0, tbe_stat_rep_items = 0, tbe_stat_rep_pruned = 0;
+extern "C" void tbe_rep_stats(uint64_t* words, uint64_t* items, uint64_t* pruned, int reset) {
+  *words = tbe_stat_rep_words; *items = tbe_stat_rep_items; *pruned = tbe_stat_rep_pruned;
+  if (reset) tbe_stat_rep_words = tbe_stat_rep_items = tbe_stat_rep_pruned = 0;
+}
 extern "C" void tbe_stats(uint64_t* tiles, uint64_t* walk) { *tiles = tbe_stat_tiles; *walk = tbe_stat_walk; }
 // the chunk plan of the host executor (tb_hostutil.h): sizes into out[0 .. cap), returns their number
 extern "C" int64_t tbe_chunk_targets(int64_t total_bytes, int64_t chunk_bytes, int device_input, int64_t* out, int64_t cap) {
@@ -213,12 +218,12 @@ extern "C" int tbe_run_chain(const tb_step_cfg* steps, size_t n_steps, const uin
       g.dup_line_frac = q.dup_line_frac; g.dup_para_frac = q.dup_para_frac;
       g.dup_line_char_frac = q.dup_line_char_frac; g.dup_para_char_frac = q.dup_para_char_frac;
       for (int k = 0; k < TB_MAX_NGRAMS; k++) { g.top_n[k] = q.top_n[k]; g.top_frac[k] = q.top_frac[k]; g.dup_n[k] = q.dup_n[k]; g.dup_frac[k] = q.dup_frac[k]; }
-      GrScratch gs{(uint64_t*)G64(wunits), G32(wunits), (uint64_t*)G64(units), G32(units), G8(units),
+      GrScratch gs{(uint64_t*)G64(wunits), G32(wunits), (uint64_t*)G64(wunits), (uint64_t*)G64(units), G32(units), G8(units),
                    (GrDoc*)G8(n1 * sizeof(GrDoc)), G32(wunits * TB_REP_K + n1 * TB_REP_DOC_EXTRA), G32(4 * n1), G32(16), n};
       memset(gs.counters, 0, 64);
       for (int64_t d = 0; d < n; d++) body_trim(b, ascii, ts, te, d);
       build_lut(TB_LUT_GR, 0u);
-      uint32_t* stage = G32(3 * TB_GR_STAGE_WORDS);
+      uint32_t* stage = (uint32_t*)G64(5 * TB_GR_STAGE_WORDS / 2 + 1);
       run_warps(n, alive_pred, [&](int64_t d, int lane) { body_gr_scan(b, ascii, lut.data(), stage, ts, te, gs, d, lane); });
       uint8_t* smem_s = (uint8_t*)G64(TB_REP_S_SMEM / 8 + 2);
       uint8_t* smem_m = (uint8_t*)G64(TB_REP_M_SMEM / 8 + 2);

@@ -173,6 +173,50 @@ def split_ambiguity_docs():
     return docs
 
 
+def signature_pruning_docs():
+    """The duplicate n-gram levels only visit word ends whose suffix signature (last k key bytes, four bits of each)
+    repeats (tb_rep.cuh).  Documents that stress the filter: characters that differ only in the bits the signature
+    drops, shortest 5-grams around the switch-over lengths (k < 6: no pruning; 6..16; > 16), words longer than the
+    16 bytes a signature holds, repeats that overlap themselves, equal concatenations with different word splits at
+    the pruned levels, and every repeat pattern at each tier size."""
+    rng = random.Random(31)
+    docs = []
+    same_low = ["a", "q", "1", "A", "Q", "\u00e1", "b", "r", "2", "B"]  # 0x61 0x71 0x31 0x41 0x51 ... : equal low nibbles
+    for nw in (9, 40, 300, 700, 2500, 9000):
+        docs.append(" ".join(rng.choice(same_low) * rng.randint(1, 3) for _ in range(nw)))
+    for wl in (1, 2, 3, 4, 7, 17, 40):  # word length sets the shortest 5-gram: 5, 10, 15, 20, 35, 85, 200 bytes
+        vocab = ["".join(rng.choice("abcdefgh") for _ in range(wl)) for _ in range(12)]
+        for nw in (30, 600, 3000):
+            docs.append(" ".join(rng.choice(vocab) for _ in range(nw)))
+    phrase = "one two three four five six seven eight nine ten eleven twelve"
+    filler = lambda n: " ".join("".join(rng.choice("klmnopqrstuvwxyz") for _ in range(rng.randint(2, 9))) for _ in range(n))
+    for reps, gap in ((2, 3), (2, 40), (5, 7), (30, 1), (3, 400), (12, 90)):
+        docs.append(" ".join(phrase + " " + filler(gap) for _ in range(reps)))
+    docs.append(("x y z " * 4 + "no where to be seen at all today ") + filler(20) + (" x y z " * 2 + "now here to be seen at all today"))
+    docs.append("ab c d e f g h i j k " + filler(15) + " a bc d e f g h i j k " + filler(5) + " a b cd e f g h i j k")
+    docs.append("the end of the story is the end of the story is the end of the story " * 3)
+    docs.append(" ".join(["w" * 40, "v" * 18] * 30 + ["u" * 16] * 12))
+    docs.append("a b c d e f " * 200 + filler(50) + " a b c d e f" * 7)
+    docs.append("\u00e9t\u00e9 \u00fcber na\u00efve caf\u00e9 \u4e2d\u6587 " * 25 + filler(30))
+    for _ in range(12):
+        toks = ["no", "now", "where", "here", "w", "he", "re", "to", "be", "seen", "a", "ll", "all", "al", "l"]
+        docs.append(" ".join(rng.choice(toks) for _ in range(rng.choice([40, 400, 2400]))))
+    return docs
+
+
+def test_signature_pruning():
+    for name in ("gr_open", "gr_shipped"):
+        _check(name, signature_pruning_docs())
+    # and it does prune: on C4-shaped prose only a few percent of the word ends stay in play
+    from textblaster_b200 import synth
+    utf8, off = synth.generate(300, seed=9)
+    texts = [bytes(utf8[off[i]:off[i + 1]]).decode("utf-8") for i in range(300)]
+    _emul.rep_stats()
+    _check("gr_shipped", texts)
+    words, items, docs = _emul.rep_stats()
+    assert docs > 250 and items < 0.1 * words, (words, items, docs)
+
+
 def test_ngram_split_ambiguity():
     _check("gr_open", split_ambiguity_docs())
     _check("gr_shipped", split_ambiguity_docs())

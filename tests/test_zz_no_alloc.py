@@ -2,7 +2,7 @@
 
 Some embedders cannot let this library call cudaMalloc on their thread -- their device memory is
 parcelled out once by a pool somebody else owns, or they sit on a path where the CUDA allocator
-(which may synchronise the whole device) is off limits.  For them the library carries a fixed 16 MiB
+(which may synchronise the whole device) is off limits.  For them the library carries a fixed 24 MiB
 work array inside its own image; this entry point runs the GopherRepetitionFilter kernels out of that
 array on caller-provided device buffers.  The price is a hard batch limit (2048 documents, 512 KiB).
 

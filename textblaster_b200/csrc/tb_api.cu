@@ -146,7 +146,7 @@ struct tb_pipeline {
   // per-chunk results, double-buffered: the copies to the host run beside the next chunk's kernels
   DevBuf alive[2], failed[2], out_off[2], stats[TB_MAX_STEPS][2];
   // GopherRepetition scratch
-  DevBuf g_wh, g_wl, g_lh, g_ll, g_lg, g_doc, g_work, g_lists, g_counters;
+  DevBuf g_wh, g_wl, g_ws, g_lh, g_ll, g_lg, g_doc, g_work, g_lists, g_counters;
   // FineWeb scratch
   DevBuf f_lh, f_ll, f_doc, f_tab;
   // C4 scratch
@@ -321,7 +321,7 @@ int ensure_chunk_buffers(tb_pipeline* p, int64_t n, int64_t nb, bool host_input)
     const StepHost& sh = p->steps[s];
     for (int i = 0; i < 2; i++) ENS(p->stats[s][i], n1 * stat_size(sh.type));
     if (sh.type == TB_STEP_GOPHER_REPETITION) {
-      ENS(p->g_wh, wunits * 8); ENS(p->g_wl, wunits * 4); ENS(p->g_lh, units * 8); ENS(p->g_ll, units * 4); ENS(p->g_lg, units);
+      ENS(p->g_wh, wunits * 8); ENS(p->g_wl, wunits * 4); ENS(p->g_ws, wunits * 8); ENS(p->g_lh, units * 8); ENS(p->g_ll, units * 4); ENS(p->g_lg, units);
       ENS(p->g_doc, n1 * sizeof(GrDoc));
       ENS(p->g_work, (wunits * TB_REP_K + n1 * TB_REP_DOC_EXTRA) * 4);
       ENS(p->g_lists, 4 * n1 * 4); ENS(p->g_counters, 64);
@@ -363,7 +363,7 @@ int enqueue_chain(tb_pipeline* p, const uint8_t* text, int64_t n, int64_t nbytes
       Timed t(p, "k_gq");
       tb_launch_gq(st, b, sh.sw, sh.gq, (int)s, p->stats[s][pb].as<tb_gq_stats>(), c->sm_count, cursors + s);
     } else if (sh.type == TB_STEP_GOPHER_REPETITION) {
-      GrScratch g{p->g_wh.as<uint64_t>(), p->g_wl.as<uint32_t>(), p->g_lh.as<uint64_t>(), p->g_ll.as<uint32_t>(),
+      GrScratch g{p->g_wh.as<uint64_t>(), p->g_wl.as<uint32_t>(), p->g_ws.as<uint64_t>(), p->g_lh.as<uint64_t>(), p->g_ll.as<uint32_t>(),
                   p->g_lg.as<uint8_t>(), p->g_doc.as<GrDoc>(), p->g_work.as<uint32_t>(), p->g_lists.as<uint32_t>(),
                   p->g_counters.as<uint32_t>(), n};
       CK(cudaMemsetAsync(p->g_counters.p, 0, 64, st));
@@ -714,7 +714,7 @@ void tb_pipeline_destroy(tb_pipeline* p) {
   cudaDeviceSynchronize();
   for (DevBuf* b : {&p->text[0], &p->text[1], &p->offs[0], &p->offs[1], &p->packed[0], &p->packed[1], &p->rs0, &p->re0, &p->rs,
                     &p->re, &p->ts, &p->te, &p->alive[0], &p->alive[1], &p->failed[0], &p->failed[1], &p->rewritten, &p->len, &p->out_off[0], &p->out_off[1], &p->bad, &p->cursors, &p->order, &p->sizecls, &p->g_wh,
-                    &p->g_wl, &p->g_lh, &p->g_ll, &p->g_lg, &p->g_doc, &p->g_work, &p->g_lists, &p->g_counters, &p->f_lh, &p->f_ll, &p->f_doc, &p->f_tab, &p->e_D, &p->e_amp, &p->e_drop, &p->e_drs, &p->e_dre, &p->c_S, &p->c_bits, &p->c_srs, &p->c_sre, &p->c_P, &p->c_F, &p->c_plen, &p->c_nlines,
+                    &p->g_wl, &p->g_ws, &p->g_lh, &p->g_ll, &p->g_lg, &p->g_doc, &p->g_work, &p->g_lists, &p->g_counters, &p->f_lh, &p->f_ll, &p->f_doc, &p->f_tab, &p->e_D, &p->e_amp, &p->e_drop, &p->e_drs, &p->e_dre, &p->c_S, &p->c_bits, &p->c_srs, &p->c_sre, &p->c_P, &p->c_F, &p->c_plen, &p->c_nlines,
                     &p->c_docflags, &p->c_lwc, &p->c_lmax, &p->c_lflags, &p->c_prs, &p->c_pre, &p->c_frs, &p->c_fre, &p->c_cnt})
     b->release();
   for (auto& b : p->stats) { b[0].release(); b[1].release(); }

@@ -145,7 +145,7 @@ struct GrTotals { uint32_t W, NL, flags; uint64_t nchars; };
 TB_D_NOINLINE void gr_doc_walk(const KBatch& a, const Classifier& C, const TextRange& R, const GrScratch& s, int64_t d, int lane,
                       GrTotals& out) {
   const uint64_t uw = tb_wunit(R.rs, d), ul = tb_lunit(R.rs, d);
-  uint64_t* wh = s.wh + uw; uint32_t* wl = s.wl + uw;
+  uint64_t* wh = s.wh + uw; uint32_t* wl = s.wl + uw; uint64_t* wsg = s.ws + uw;
   uint64_t* lh = s.lh + ul; uint32_t* ll = s.ll + ul; uint8_t* lg = s.lg + ul;
   uint32_t W = 0, NL = 0, flags = 0;
   uint64_t nchars = 0;
@@ -160,7 +160,7 @@ TB_D_NOINLINE void gr_doc_walk(const KBatch& a, const Classifier& C, const TextR
     flags |= o.flags; nchars += o.nchars;
     // ---- words: dense, ordered
     uint32_t tot, pre = simt_exscan(o.nw, lane, &tot);
-    for (uint32_t k = 0; k < o.nw; k++) { wh[W + pre + k] = o.wh[k]; wl[W + pre + k] = o.wl[k]; }
+    for (uint32_t k = 0; k < o.nw; k++) { wh[W + pre + k] = o.wh[k]; wl[W + pre + k] = o.wl[k]; wsg[W + pre + k] = o.ws[k]; }
     W += tot;
     // ---- line pieces: segmented scan of the open-piece value; a lane with a '\n' restarts it
     HL v{o.tail.a, o.tail.b, o.tail_len};
@@ -202,11 +202,14 @@ TB_D_NOINLINE void gr_doc_walk(const KBatch& a, const Classifier& C, const TextR
   }
   out.W = W; out.NL = NL; out.flags = flags; out.nchars = nchars;
 }
-#define TB_GR_STAGE_WORDS (23 * 32)  // word ends one tile can hold: at most 22 + 1 per stretch (two words per three bytes)
+// Words one tile can stage (five 32-bit words each).  A tile can end up to 23 * 32 words (two words per three
+// bytes, "a\u00a9a\u00a9..."); a tile with more than this many -- twelve per stretch, under three bytes per word and
+// separator -- hands the document to the walking path instead of tripling every warp's shared memory.
+#define TB_GR_STAGE_WORDS (12 * 32)
 TB_D bool gr_doc_tiles(const KBatch& a, const LutEntry* lut, uint32_t* stage, const Classifier& C, const TextRange& R,
                        const GrScratch& s, int64_t d, int lane, GrTotals& out);
 
-// `stage`: 3 * TB_GR_STAGE_WORDS words of per-warp scratch (shared memory)
+// `stage`: 5 * TB_GR_STAGE_WORDS words of per-warp scratch (shared memory, 8-byte aligned)
 TB_D void body_gr_scan(const KBatch& a, const uint16_t* s_ascii, const LutEntry* lut, uint32_t* stage, const int64_t* ts,
                        const int64_t* te, const GrScratch& s, int64_t d, int lane) {
   Classifier C{s_ascii, a.uc};

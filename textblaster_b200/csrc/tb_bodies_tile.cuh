@@ -273,18 +273,25 @@ TB_D bool c4b_doc_tiles(const KBatch& a, const LutEntry* lut, const Classifier& 
 // GopherRepetitionFilter, pass 1 (gopher_rep.rs:57-58,80-84,120-124,159): word and line-piece hashes
 // ---------------------------------------------------------------------------------------------
 TB_D HL hl_fold(uint32_t a, uint32_t b, uint32_t len) { HL r; r.a = tb_hfold(a); r.b = tb_hfold(b); r.len = len; return r; }
+// word fragments also carry their suffix signature (tb_sig_push)
+struct HLS { HL h; uint64_t sig; };
+TB_D HLS hls_cat(HLS x, HLS y, const uint64_t* powtab) { HLS r; r.sig = tb_sig_cat(x.sig, y.sig, y.h.len); r.h = hl_cat(x.h, y.h, powtab); return r; }
+TB_D HLS hls_shfl_up(HLS v, int o) { HLS r; r.h = hl_shfl_up(v.h, o); r.sig = (uint64_t)simt_shfl_up64((int64_t)v.sig, o); return r; }
+TB_D HLS hls_shfl(HLS v, int src) { HLS r; r.h = hl_shfl(v.h, src); r.sig = simt_shfl(v.sig, src); return r; }
 
 TB_D bool gr_doc_tiles(const KBatch& a, const LutEntry* lut, uint32_t* stage, const Classifier& C, const TextRange& R,
                        const GrScratch& s, int64_t d, int lane, GrTotals& out) {
-  uint32_t* st_a = stage; uint32_t* st_b = stage + TB_GR_STAGE_WORDS; uint32_t* st_n = stage + 2 * TB_GR_STAGE_WORDS;
+  uint64_t* st_s = (uint64_t*)stage;
+  uint32_t* st_a = stage + 2 * TB_GR_STAGE_WORDS; uint32_t* st_b = stage + 3 * TB_GR_STAGE_WORDS; uint32_t* st_n = stage + 4 * TB_GR_STAGE_WORDS;
   const uint64_t uw = tb_wunit(R.rs, d), ul = tb_lunit(R.rs, d);
-  uint64_t* wh = s.wh + uw; uint32_t* wl = s.wl + uw;
+  uint64_t* wh = s.wh + uw; uint32_t* wl = s.wl + uw; uint64_t* wsg = s.ws + uw;
   uint64_t* lh = s.lh + ul; uint32_t* ll = s.ll + ul; uint8_t* lg = s.lg + ul;
   const uint64_t* powtab = a.uc.powtab;
   const uint32_t below_lane = tb_below(lane);
   uint32_t W = 0, NLc = 0, flags = 0;
   uint64_t nchars = 0;
-  HL wcarry{0u, 0u, 0u}, lcarry{0u, 0u, 0u};
+  HLS wcarry{{0u, 0u, 0u}, 0ull};
+  HL lcarry{0u, 0u, 0u};
   uint32_t wcarry_wc = 0;
   for (int64_t base = tb_tile_origin(R); base < R.re; base += TB_TILE) {
     Tile T;
@@ -311,6 +318,7 @@ TB_D bool gr_doc_tiles(const KBatch& a, const LutEntry* lut, uint32_t* stage, co
     const uint32_t first_word = (B && (in_wc || (WC & headm))) ? 1u : 0u;
     const uint32_t WEin = B & (H << 1) & ~tb_upto(fb);  // word ends after the first segment start
     uint32_t wtot, wpre = simt_exscan((uint32_t)tb_popc32(WEin) + first_word, lane, &wtot);
+    if (wtot > TB_GR_STAGE_WORDS) return false;  // more words than the staging arrays hold: the walking path takes the document
     // ---- line pieces: is the piece that is open at the start of the stretch non-empty?
     const int fn = tb_ctz32(NLx);
     const int ln_ = NLx ? 31 - tb_clz32(NLx) : -1;
@@ -327,6 +335,7 @@ TB_D bool gr_doc_tiles(const KBatch& a, const LutEntry* lut, uint32_t* stage, co
     // ---- one pass over the 32 bytes: running word hash (restarts at segment starts) and piece hash
     uint32_t wa = 0, wb = 0, wn = 0, la = 0, lb_ = 0, ln = 0;
     uint32_t hwa = 0, hwb = 0, hwn = 0, hla = 0, hlb = 0, hln = 0;
+    uint64_t wsig = 0, hwsig = 0;  // suffix signature of the running word fragment / of the one before the first segment start
     uint32_t widx = wpre + first_word, lidx = NLc + lpre + first_piece;  // widx: slot in the tile's staging arrays
     // (eight rounds of four bytes; the words and masks rotate so that the round body is one piece of code)
     {
@@ -343,12 +352,12 @@ TB_D bool gr_doc_tiles(const KBatch& a, const LutEntry* lut, uint32_t* stage, co
           const uint32_t byte = (x >> (8 * j)) & 0xFFu;
           {  // segment start: written as selects and predicated stores so that the lanes stay together
             const bool brk = (Bq >> j) & 1u, emit = (WEq >> j) & 1u, head = brk && j == fbq;  // WEq is a subset of Bq without fb
-            if (emit) { st_a[widx] = wa; st_b[widx] = wb; st_n[widx] = wn; }
+            if (emit) { st_a[widx] = wa; st_b[widx] = wb; st_n[widx] = wn; st_s[widx] = wsig; }
             widx += emit ? 1u : 0u;
-            hwa = head ? wa : hwa; hwb = head ? wb : hwb; hwn = head ? wn : hwn;
-            wa = brk ? 0u : wa; wb = brk ? 0u : wb; wn = brk ? 0u : wn;
+            hwa = head ? wa : hwa; hwb = head ? wb : hwb; hwn = head ? wn : hwn; hwsig = head ? wsig : hwsig;
+            wa = brk ? 0u : wa; wb = brk ? 0u : wb; wn = brk ? 0u : wn; wsig = brk ? 0ull : wsig;
           }
-          wa = tb_hpush(wa, TB_B1, byte + 1u); wb = tb_hpush(wb, TB_B2, byte + 1u); wn++;
+          wa = tb_hpush(wa, TB_B1, byte + 1u); wb = tb_hpush(wb, TB_B2, byte + 1u); wn++; wsig = tb_sig_push(wsig, byte);
           if ((NLq >> j) & 1u) {
             if (j == fnq) { hla = la; hlb = lb_; hln = ln; }
             else if (ln) {
@@ -367,31 +376,31 @@ TB_D bool gr_doc_tiles(const KBatch& a, const LutEntry* lut, uint32_t* stage, co
     }
     // ---- words: hash of the fragment open at the start of the stretch
     {
-      HL v = hl_fold(wa, wb, wn);
-      HL cin;
+      HLS v{hl_fold(wa, wb, wn), wsig};
+      HLS cin;
       if (brk_lanes == 0xFFFFFFFFu) {  // every lane restarts: the open fragment is the previous lane's tail
-        cin = hl_shfl_up(v, 1);
+        cin = hls_shfl_up(v, 1);
         if (lane == 0) cin = wcarry;
-        wcarry = hl_shfl(v, 31);
+        wcarry = hls_shfl(v, 31);
       } else {
         uint32_t f = B != 0u;
         for (int off = 1; off < 32; off <<= 1) {
-          HL vu = hl_shfl_up(v, off);
+          HLS vu = hls_shfl_up(v, off);
           uint32_t fu = simt_shfl_up(f, off);
-          if (lane >= off && !f) { v = hl_cat(vu, v, powtab); f = fu; }
+          if (lane >= off && !f) { v = hls_cat(vu, v, powtab); f = fu; }
         }
-        if (!f) v = hl_cat(wcarry, v, powtab);
-        cin = hl_shfl_up(v, 1);
+        if (!f) v = hls_cat(wcarry, v, powtab);
+        cin = hls_shfl_up(v, 1);
         if (lane == 0) cin = wcarry;
-        wcarry = hl_shfl(v, 31);
+        wcarry = hls_shfl(v, 31);
       }
       if (first_word) {
-        HL first = hl_cat(cin, hl_fold(hwa, hwb, hwn), powtab);
-        st_a[wpre] = first.a; st_b[wpre] = first.b; st_n[wpre] = first.len;
+        HLS first = hls_cat(cin, HLS{hl_fold(hwa, hwb, hwn), hwsig}, powtab);
+        st_a[wpre] = first.h.a; st_b[wpre] = first.h.b; st_n[wpre] = first.h.len; st_s[wpre] = first.sig;
       }
       // the tile's words, in order: reduce and store them with all lanes busy
       simt_sync();
-      for (uint32_t j = (uint32_t)lane; j < wtot; j += 32) { wh[W + j] = hl_pack(hl_fold(st_a[j], st_b[j], st_n[j])); wl[W + j] = st_n[j]; }
+      for (uint32_t j = (uint32_t)lane; j < wtot; j += 32) { wh[W + j] = hl_pack(hl_fold(st_a[j], st_b[j], st_n[j])); wl[W + j] = st_n[j]; wsg[W + j] = st_s[j]; }
       simt_sync();
       // "word character seen" of the fragment open after lane 31
       if (brk_lanes) wcarry_wc = (twc_lanes & ~tb_below(31 - tb_clz32(brk_lanes))) != 0u;
@@ -418,8 +427,8 @@ TB_D bool gr_doc_tiles(const KBatch& a, const LutEntry* lut, uint32_t* stage, co
     }
     W += wtot; NLc += ltot;
   }
-  if (wcarry_wc && wcarry.len) {  // the word / the piece that runs to the end of the text
-    if (lane == 0) { wh[W] = hl_pack(wcarry); wl[W] = wcarry.len; }
+  if (wcarry_wc && wcarry.h.len) {  // the word / the piece that runs to the end of the text
+    if (lane == 0) { wh[W] = hl_pack(wcarry.h); wl[W] = wcarry.h.len; wsg[W] = wcarry.sig; }
     W++;
   }
   if (lcarry.len) {

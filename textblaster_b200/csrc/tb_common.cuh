@@ -175,6 +175,14 @@ TB_HD uint64_t tb_pow_pack(const uint64_t* powtab, uint64_t len) {
   }
   return ((uint64_t)ra << 32) | rb;
 }
+// ---- suffix signature of a byte string: its last 16 bytes, four bits of each, the last byte in the low nibble
+// (a string shorter than 16 bytes leaves the upper nibbles zero).  Equal strings have equal signatures, and so
+// do their suffixes of any common length k <= 16 (mask with tb_sig_mask(k)): the repetition pass uses that as a
+// cheap necessary condition for two concatenated n-gram keys to be equal (tb_rep.cuh).
+TB_HD uint64_t tb_sig_push(uint64_t s, uint32_t byte) { return (s << 4) | (uint64_t)(byte & 15u); }
+TB_HD uint64_t tb_sig_cat(uint64_t x, uint64_t y, uint32_t ylen) { return ylen >= 16u ? y : (y | (x << (4u * ylen))); }  // x followed by y
+TB_HD uint64_t tb_sig_mask(uint32_t k) { return k >= 16u ? ~0ull : ((1ull << (4u * k)) - 1ull); }
+
 TB_HD uint64_t tb_mix64(uint64_t x) {  // splitmix64 finaliser, for table slot selection only
   x ^= x >> 30; x *= 0xBF58476D1CE4E5B9ull; x ^= x >> 27; x *= 0x94D049BB133111EBull; x ^= x >> 31;
   return x;

@@ -92,7 +92,7 @@ __global__ void __launch_bounds__(TB_BLOCK, 16) k_gr_scan(KBatch a, const int64_
   __shared__ LutEntry s_lut[256];
   load_ascii(s_ascii, a.uc);
   load_lut(s_lut, a.uc, TB_LUT_GR, 0u);
-  __shared__ uint32_t s_stage[3 * TB_GR_STAGE_WORDS];
+  __shared__ __align__(8) uint32_t s_stage[5 * TB_GR_STAGE_WORDS];
   for (;;) {
     const int64_t d = next_doc(&s.counters[8], a);
     if (d == -1) break;

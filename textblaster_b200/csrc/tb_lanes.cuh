@@ -121,6 +121,7 @@ struct GrLane {
   uint32_t nw;
   uint64_t wh[TB_LANE_MAXW];
   uint32_t wl[TB_LANE_MAXW];
+  uint64_t ws[TB_LANE_MAXW];
   // '\n'-delimited pieces of the stretch: head (before the first '\n'), complete inner pieces,
   // tail (after the last '\n').  Without any '\n' the whole stretch is `tail`.
   uint32_t has_nl, first_nl;     // first_nl: offset of the first '\n'
@@ -132,15 +133,21 @@ struct GrLane {
 };
 struct GrSink {
   GrLane* o;
+  const uint8_t* t;
   TB_HD void on_word(WordInfo& w) {
-    if (o->nw < TB_LANE_MAXW) { o->wh[o->nw] = w.hash.pack(); o->wl[o->nw] = (uint32_t)(w.end - w.start); }
+    if (o->nw < TB_LANE_MAXW) {
+      o->wh[o->nw] = w.hash.pack(); o->wl[o->nw] = (uint32_t)(w.end - w.start);
+      uint64_t sig = 0;
+      for (int64_t i = w.end - w.start > 16 ? w.end - 16 : w.start; i < w.end; i++) sig = tb_sig_push(sig, tb_byte(t, i));
+      o->ws[o->nw] = sig;
+    }
     o->nw++;
   }
 };
 TB_HD void gr_lane(const Classifier& C, const TextRange& R, int64_t p0, int64_t p1, GrLane& o) {
   const uint8_t* t = R.t;
   o.nw = 0;
-  GrSink sink{&o};
+  GrSink sink{&o, t};
   o.flags = tb_walk_words_fast<WM_NEED_HASH>(C, R, p0, p1, sink) & CI_COMPLEX;
   o.has_nl = 0; o.first_nl = 0; o.np = 0; o.nchars = 0;
   o.head.init(); o.head_len = 0;

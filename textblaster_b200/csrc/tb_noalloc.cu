@@ -10,7 +10,7 @@
 // the inputs and the outputs as device pointers; all intermediates (document ranges, word and line
 // hashes, hash-table work areas, the Unicode tables) live in `tb_noalloc_scratch` below.
 //
-// What it costs.  The array is TB_NOALLOC_SCRATCH_BYTES (16 MiB) of device memory on every GPU that
+// What it costs.  The array is TB_NOALLOC_SCRATCH_BYTES (24 MiB) of device memory on every GPU that
 // loads the library, for the life of the process.  That bounds the batch: at most
 // TB_NOALLOC_MAX_DOCS documents and TB_NOALLOC_MAX_BYTES bytes of text per call; larger requests are
 // refused with TB_ERR_INVALID_ARGUMENT (split the batch, or use the allocating entry points).
@@ -38,7 +38,7 @@
 #include "tb_kernels.cuh"
 #include "unicode_tables.inc"
 
-#define TB_NOALLOC_SCRATCH_BYTES (16u << 20)
+#define TB_NOALLOC_SCRATCH_BYTES (24u << 20)
 
 // The working memory.  In host code this symbol is NOT a device pointer; see setup_device().
 static __device__ __align__(256) unsigned char tb_noalloc_scratch[TB_NOALLOC_SCRATCH_BYTES];
@@ -175,7 +175,7 @@ int tb_gopher_repetition_noalloc(const uint8_t* utf8_dev, const int64_t* offsets
   int64_t* ts = (int64_t*)carve(n1 * 8); int64_t* te = (int64_t*)carve(n1 * 8);
   int8_t* failed = (int8_t*)carve(n1);
   GrScratch g;
-  g.wh = (uint64_t*)carve(wunits * 8); g.wl = (uint32_t*)carve(wunits * 4);
+  g.wh = (uint64_t*)carve(wunits * 8); g.wl = (uint32_t*)carve(wunits * 4); g.ws = (uint64_t*)carve(wunits * 8);
   g.lh = (uint64_t*)carve(units * 8); g.ll = (uint32_t*)carve(units * 4); g.lg = (uint8_t*)carve(units);
   g.doc = (GrDoc*)carve(n1 * sizeof(GrDoc));
   g.work = (uint32_t*)carve((wunits * TB_REP_K + n1 * TB_REP_DOC_EXTRA) * 4);

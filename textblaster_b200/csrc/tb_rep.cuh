@@ -10,9 +10,22 @@
 // polynomial hash + byte length).  find_all_duplicate's greedy scan is order dependent; it is
 // reduced to a short sequential pass over the *candidate* positions only (those whose key already
 // occurred earlier), see rep_dup_walk.
+//
+// Duplicate n-grams, pruned.  Their keys are bare concatenations, so levels cannot be pruned by one
+// another ("no where" == "now here" without any shared shorter n-gram).  But two equal keys are equal
+// byte strings, so they end in the same k bytes for every k up to their length.  With m = the shortest
+// n-gram of the smallest pruned level (in bytes) and k = min(16, m), every n-gram of every pruned level is
+// at least k bytes long: a position whose last k key bytes (4 bits of each: the suffix signatures the scan
+// pass stores per word, tb_sig_push) occur nowhere else in the document can neither repeat nor be repeated
+// at any of those levels.  One cheap table pass over the signatures finds the word ends that can; the
+// levels then hash, insert and walk those only -- a few percent of the positions of ordinary prose.
 #pragma once
 #include "tb_kernels.cuh"
 #include "tb_simt.cuh"
+
+#if defined(TB_HOST_EMUL)
+extern uint64_t tbe_stat_rep_words, tbe_stat_rep_items, tbe_stat_rep_pruned;  // word ends / candidates among them / documents pruned
+#endif
 
 #define TB_REP_S_CAP 512u
 #define TB_REP_M_CAP 2048u
@@ -20,6 +33,8 @@
 #define TB_REP_M_THREADS 256
 #define TB_REP_L_THREADS 1024
 #define TB_REP_X_THREADS 512
+#define TB_REP_PRUNE_FROM 4u  // duplicate n-gram levels from this order on run over the signature candidates only
+#define TB_REP_SIG_MIN 6u     // ... if the shortest n-gram of the first such level has at least this many bytes
 
 // ---- thread groups ---------------------------------------------------------------------------
 struct WarpGroup {
@@ -33,6 +48,7 @@ struct WarpGroup {
   TB_D bool any(bool p) const { simt_sync(); return simt_any(p); }  // also a barrier with memory ordering, like the CTA's
   TB_D uint32_t exscan(uint32_t v, uint32_t* total) const { return simt_exscan(v, tid, total); }
   TB_D uint32_t bcast(uint32_t v) const { return simt_shfl(v, 0); }
+  TB_D uint32_t warp_ballot(bool p) const { return simt_ballot(p); }
 };
 
 #if !defined(TB_HOST_EMUL)
@@ -79,6 +95,7 @@ struct BlockGroup {
     __syncthreads();
     return (uint32_t)r[0];
   }
+  TB_D uint32_t warp_ballot(bool p) const { return __ballot_sync(0xFFFFFFFFu, p); }  // over the 32 threads tid & ~31 .. | 31
 };
 #else
 // host emulation: N threads share one barrier + mailbox (tb_simt.cuh SimtBlock)
@@ -109,6 +126,12 @@ struct BlockGroup {
   TB_D uint32_t bcast(uint32_t v) const {
     SimtBlock* b = simt_block; if (tid == 0) b->box[0] = v; b->bar.arrive_and_wait();
     uint32_t r = (uint32_t)b->box[0]; b->bar.arrive_and_wait(); return r;
+  }
+  TB_D uint32_t warp_ballot(bool p) const {
+    SimtBlock* b = simt_block; b->box[tid] = p ? 1 : 0; b->bar.arrive_and_wait();
+    uint32_t r = 0; const int w0 = tid & ~31;
+    for (int i = 0; i < 32 && w0 + i < b->n; i++) r |= (uint32_t)b->box[w0 + i] << i;
+    b->bar.arrive_and_wait(); return r;
   }
 };
 #endif
@@ -165,34 +188,47 @@ TB_D void rep_dedup(const G& g, uint32_t* tab, const uint64_t* h, const uint32_t
   *dup_elems = n - distinct; *dup_bytes = total - dbytes;
 }
 
-// The greedy scan of find_all_duplicate (text.rs:241-259) given fo[i] = first position with the same
-// key.  Positions whose key is new (fo[i] == i) only ever insert; they are pre-marked "seen".  A hit at
-// q skips q+1..q+n-1: first occurrences inside that window were never visited, so their mark is
-// removed; a later occurrence of such a key then inserts instead of hitting.  Only candidates
-// (fo[q] < q), in increasing order, need the sequential pass.
+// Ordered list of the set bits of a bitmap: out[0 .. count) = indices i < nbits with bit i set, increasing.
+// One prefix sum over the bitmap's words (a thread per word), then every thread expands its own word.
 template <class G, class IdxT>
-TB_D uint64_t rep_dup_walk(const G& g, IdxT* fo, uint32_t* cand, const uint32_t* woff, uint32_t cn, uint32_t n) {
-  const uint32_t EMPTY = IdxTraits<IdxT>::kEmpty;
-  // ordered compaction of the candidates
-  uint32_t ncand = 0;
-  for (uint32_t b0 = 0; b0 < cn; b0 += g.size()) {
-    uint32_t i = b0 + g.tid;
-    uint32_t is = (i < cn && fo[i] != i) ? 1u : 0u, tot, pre = g.exscan(is, &tot);
-    if (is) cand[ncand + pre] = i;
-    ncand += tot;
+TB_D uint32_t rep_compact_bits(const G& g, const uint32_t* bits, uint32_t nbits, IdxT* out) {
+  const uint32_t nwords = (nbits + 31u) >> 5;
+  uint32_t run = 0;
+  for (uint32_t b0 = 0; b0 < nwords; b0 += (uint32_t)g.size()) {
+    const uint32_t wi = b0 + (uint32_t)g.tid;
+    uint32_t w = wi < nwords ? bits[wi] : 0u;
+    if (wi == nwords - 1u && (nbits & 31u)) w &= (1u << (nbits & 31u)) - 1u;
+    uint32_t tot, o = run + g.exscan((uint32_t)simt_popc(w), &tot);
+    while (w) { out[o++] = (IdxT)(wi * 32u + (uint32_t)(simt_ffs(w) - 1)); w &= w - 1u; }
+    run += tot;
   }
   g.sync();
+  return run;
+}
+
+// The greedy scan of find_all_duplicate (text.rs:241-259) over `items` n-grams given in increasing position:
+// item k is the n-gram that ENDS with word E(k) (E(k) = elist[k], or k itself without a list), i.e. starts at
+// q = E(k) - (n - 1); fo[k] = first item with the same key.  Items whose key is new (fo[k] == k) only ever insert;
+// they are pre-marked "seen".  A hit at q skips q+1..q+n-1: first occurrences inside that window were never
+// visited, so their mark is removed; a later occurrence of such a key then inserts instead of hitting.  Only
+// the candidates (fo[k] != k; bitmap `cbits`), in increasing order, need the sequential pass.  n-grams that are
+// not among the items are unique in the document: nothing ever refers to them.
+template <class G, class IdxT>
+TB_D uint64_t rep_dup_walk(const G& g, IdxT* fo, IdxT* cand, const uint32_t* cbits, const uint32_t* woff, const IdxT* elist,
+                           uint32_t items, uint32_t n) {
+  const uint32_t EMPTY = IdxTraits<IdxT>::kEmpty;
+  const uint32_t ncand = rep_compact_bits(g, cbits, items, cand);
   uint64_t rep = 0;
   if (g.tid == 0) {
     uint32_t skip_until = 0;
-    for (uint32_t k = 0; k < ncand; k++) {
-      uint32_t q = cand[k];
+    for (uint32_t kk = 0; kk < ncand; kk++) {
+      const uint32_t k = cand[kk];
+      const uint32_t e = elist ? (uint32_t)elist[k] : k, q = e + 1u - n;
       if (q < skip_until) continue;
-      uint32_t c = fo[q];
+      const uint32_t c = fo[k];
       if (fo[c] == c) {  // key seen: hit
-        rep += woff[q + n] - woff[q];
-        uint32_t e = q + n < cn ? q + n : cn;
-        for (uint32_t p = q + 1; p < e; p++) if (fo[p] == p) fo[p] = (IdxT)EMPTY;
+        rep += woff[e + 1] - woff[q];
+        for (uint32_t p = k + 1; p < items && (elist ? (uint32_t)elist[p] : p) < e + n; p++) if (fo[p] == p) fo[p] = (IdxT)EMPTY;
         skip_until = q + n;
       } else {
         fo[c] = (IdxT)c;  // its first occurrence was skipped: this one inserts
@@ -226,7 +262,7 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
   }
   const int64_t rs = ts[d];
   const uint64_t uw = tb_wunit(rs, d), ul = tb_lunit(rs, d);
-  const uint64_t* wh_g = s.wh + uw; const uint32_t* wl_g = s.wl + uw;
+  const uint64_t* wh_g = s.wh + uw; const uint32_t* wl_g = s.wl + uw; const uint64_t* wsg = s.ws + uw;
   const uint64_t* lh = s.lh + ul; const uint32_t* ll = s.ll + ul; const uint8_t* lg = s.lg + ul;
   const uint32_t W = gd.W, NL = gd.NL;
   const double text_char_len = (double)(gd.char_len ? gd.char_len : 1);
@@ -273,14 +309,15 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
   if (ntop_max > W) ntop_max = W;
   if (ndup_max > W) ndup_max = W;
   if (ntop_max || ndup_max) {
-    // byte offsets of the words in the concatenation; word hashes into the working array
-    uint32_t run = 0;
-    for (uint32_t b0 = 0; b0 < W; b0 += g.size()) {
-      uint32_t i = b0 + g.tid, v = i < W ? wl_g[i] : 0, tot, pre = g.exscan(v, &tot);
-      if (i < W) A.woff[i] = run + pre;
-      run += tot;
-    }
-    if (g.tid == 0) A.woff[W] = run;
+    // byte offsets of the words in the concatenation: every thread sums a run of consecutive words, one prefix
+    // sum over the threads, then the run is written out
+    const uint32_t per = (W + (uint32_t)g.size() - 1u) / (uint32_t)g.size();
+    const uint32_t i0 = (uint32_t)g.tid * per < W ? (uint32_t)g.tid * per : W, i1 = i0 + per < W ? i0 + per : W;
+    uint32_t sum = 0;
+    for (uint32_t i = i0; i < i1; i++) sum += TB_LDG(wl_g + i);
+    uint32_t tot, run = g.exscan(sum, &tot);
+    for (uint32_t i = i0; i < i1; i++) { A.woff[i] = run; run += TB_LDG(wl_g + i); }
+    if (g.tid == 0) A.woff[W] = tot;
     g.sync();
   }
   const uint64_t* wh = wh_g;  // read in place (coalesced, once per pass)
@@ -352,40 +389,82 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
       }
       // survivors: positions whose n-gram occurred at least twice, in order
       uint32_t ncount = 0;
-      if (any_hit && n < ntop_max) {
-        for (uint32_t b0 = 0; b0 < cn; b0 += g.size()) {
-          const uint32_t i = b0 + g.tid;
-          const uint32_t is = (i < cn && ((A.flag[i >> 5] >> (i & 31)) & 1u)) ? 1u : 0u;
-          uint32_t tot, pre = g.exscan(is, &tot);
-          if (is) list[ncount + pre] = (IdxT)i;
-          ncount += tot;
-        }
-      }
+      if (any_hit && n < ntop_max) ncount = rep_compact_bits(g, A.flag, cn, list);
       count = ncount; pruned = true;
       g.sync();
     }
   }
-  // -- duplicate n-grams: keys are the concatenated strings (find_all_duplicate, text.rs:241-259)
-  uint32_t dcur = 0;  // level of the keys in A.H (0: none yet)
-  for (uint32_t n = 1; n <= ndup_max; n++) {
-    if (!((dup_levels >> n) & 1ull)) continue;  // only configured levels run a pass; the keys jump levels in registers
-    const uint32_t cn = W - n + 1;
-    {
-      const uint32_t T = rep_tab_size(cn);
-      // one sweep: clear the table, bring the keys from level dcur to level n
+  // -- duplicate n-grams: keys are the concatenated strings (find_all_duplicate, text.rs:241-259).
+  // An item is the n-gram that ends with word e; its key grows to the left from level to level.  Levels below
+  // TB_REP_PRUNE_FROM run over every word end; from there on only over the ends whose suffix signature repeats.
+  {
+    const uint32_t fw = W / 32 + 1;
+    uint32_t n_p = 0;  // first pruned level
+    for (uint32_t n = TB_REP_PRUNE_FROM; n <= ndup_max && !n_p; n++) if ((dup_levels >> n) & 1ull) n_p = n;
+    bool pruned = false;   // the items are list[0 .. items)
+    uint32_t items = W;
+    uint32_t dcur = 0;     // level of the keys in A.H (0: none yet)
+    for (uint32_t n = 1; n <= ndup_max; n++) {
+      if (!((dup_levels >> n) & 1ull)) continue;  // only configured levels run a pass; the keys jump levels in registers
+      if (n == n_p) {
+        // shortest n-gram of this level, in bytes
+        uint32_t m = 0xFFFFFFFFu;
+        for (uint32_t i = g.tid; i + n <= W; i += g.size()) { const uint32_t v = woff[i + n] - woff[i]; m = v < m ? v : m; }
+        m = 0xFFFFFFFFu - (uint32_t)g.max64((uint64_t)(0xFFFFFFFFu - m));
+        const uint32_t k = m < 16u ? m : 16u;
+        if (k >= TB_REP_SIG_MIN) {
+          // word ends whose last k key bytes occur at another word end too (signature in A.H, first end per value in the table)
+          const uint64_t mask = tb_sig_mask(k);
+          const uint32_t T = rep_tab_size(W - n + 1);
+          for (uint32_t i = g.tid; i < T; i += g.size()) tab[i] = EMPTY;
+          for (uint32_t i = g.tid; i < fw; i += g.size()) A.flag[i] = 0;
+          for (uint32_t e = n - 1 + g.tid; e < W; e += g.size()) {
+            uint64_t sig = TB_LDG(wsg + e);
+            uint32_t filled = woff[e + 1] - woff[e];
+            for (uint32_t j = e; filled < k; ) { j--; sig |= TB_LDG(wsg + j) << (4u * filled); filled += woff[j + 1] - woff[j]; }
+            A.H[e] = sig & mask;
+          }
+          g.sync();
+          for (uint32_t e = n - 1 + g.tid; e < W; e += g.size()) {
+            const uint64_t key = A.H[e];
+            uint32_t sl = rep_slot(tb_mix64(key), T);
+            for (;;) {
+              uint32_t old = idx_cas(&tab[sl], EMPTY, e);
+              if (old == EMPTY) break;
+              if (A.H[old] == key) { simt_atomic_or(&A.flag[e >> 5], 1u << (e & 31)); simt_atomic_or(&A.flag[old >> 5], 1u << (old & 31)); break; }
+              sl = rep_next(sl, T);
+            }
+          }
+          g.sync();
+          items = rep_compact_bits(g, A.flag, W, list);
+          pruned = true; dcur = 0;
+#if defined(TB_HOST_EMUL)
+          if (g.tid == 0) { tbe_stat_rep_words += W; tbe_stat_rep_items += items; tbe_stat_rep_pruned++; }
+#endif
+        }
+      }
+      if (items == 0) continue;  // nothing can repeat at this level: dup_bytes stays 0
+      const uint32_t T = rep_tab_size(items);
+      // one sweep: clear the table, bring the keys from level dcur to level n (new words go in front)
 #pragma unroll 2
       for (uint32_t i = g.tid; i < T; i += g.size()) {
         tab[i] = EMPTY;
-        if (i >= cn) continue;
-        Hash2 h = tb_unpack(dcur ? A.H[i] : TB_LDG(wh + i));
-        for (uint32_t j = i + (dcur ? dcur : 1u); j < i + n; j++)
-          h = tb_hcat(h, tb_unpack(TB_LDG(wh + j)), tb_pow_pack(a.uc.powtab, woff[j + 1] - woff[j]));
+        if (i >= items) continue;
+        const uint32_t e = pruned ? (uint32_t)list[i] : i;
+        if (e + 1u < n) continue;
+        const uint32_t q = e + 1u - n;  // first word of the n-gram
+        Hash2 h = tb_unpack(TB_LDG(wh + q));
+        const uint32_t stop = dcur ? e + 1u - dcur : e + 1u;  // the words [stop, e] are in the stored key already
+        for (uint32_t j = q + 1; j < stop; j++) h = tb_hcat(h, tb_unpack(TB_LDG(wh + j)), tb_pow_pack(a.uc.powtab, woff[j + 1] - woff[j]));
+        if (dcur) h = tb_hcat(h, tb_unpack(A.H[i]), tb_pow_pack(a.uc.powtab, woff[e + 1] - woff[stop]));
         A.H[i] = h.pack();
       }
       dcur = n;
       g.sync();
       bool dup = false;
-      for (uint32_t i = g.tid; i < cn; i += g.size()) {
+      for (uint32_t i = g.tid; i < items; i += g.size()) {
+        const uint32_t e = pruned ? (uint32_t)list[i] : i;
+        if (e + 1u < n) { cnt[i] = (IdxT)EMPTY; continue; }
         const uint64_t key = A.H[i];
         uint32_t sl = rep_slot(key, T);
         for (;;) {
@@ -394,14 +473,23 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
           if (A.H[old] == key) { idx_min(&tab[sl], i); dup = true; break; }
           sl = rep_next(sl, T);
         }
-        cnt[i] = (IdxT)sl;  // the slot of this key; resolved to its first position below
+        cnt[i] = (IdxT)sl;  // the slot of this key; resolved to its first item below
       }
       uint64_t v = 0;
       if (g.any(dup)) {  // (a barrier: the table is complete)
-        // fo[i] = smallest position carrying the same key
-        for (uint32_t i = g.tid; i < cn; i += g.size()) cnt[i] = (IdxT)tab[cnt[i]];
+        // fo[i] = first item carrying the same key; the items that are not the first of their key form the bitmap
+        // of candidates (assembled a word per warp from ballots: no atomics)
+        const uint32_t rounds = (items + (uint32_t)g.size() - 1u) / (uint32_t)g.size();
+        for (uint32_t r = 0; r < rounds; r++) {
+          const uint32_t i = r * (uint32_t)g.size() + (uint32_t)g.tid;
+          uint32_t f = i;
+          if (i < items && cnt[i] != (IdxT)EMPTY) f = tab[cnt[i]];
+          const uint32_t bits = g.warp_ballot(f != i);
+          if (i < items) cnt[i] = (IdxT)f;
+          if ((g.tid & 31) == 0 && i < items) A.flag[i >> 5] = bits;
+        }
         g.sync();
-        v = rep_dup_walk(g, cnt, tab, woff, cn, n);  // the table is dead now: reuse it for the candidate list
+        v = rep_dup_walk(g, cnt, (IdxT*)tab, A.flag, woff, pruned ? list : (const IdxT*)nullptr, items, n);  // the table is dead now: it holds the candidate list
       }
       if (g.tid == 0) {
         for (int k = 0; k < cfg.n_dup; k++) {
