@@ -316,8 +316,17 @@ TB_D_NOINLINE void c4a_doc_walk(const KBatch& a, const Classifier& C, const C4Cf
     int64_t p0 = base + lane * TB_STRETCH;
     int64_t p1 = p0 + TB_STRETCH < R.re ? p0 + TB_STRETCH : R.re;
     if (p0 < R.re) c4a_lane(C, R, p0, p1, cfg.remove_citations != 0, cfg.filter_lorem_ipsum != 0, o);
-    else { o.nkept = 0; o.n_nl = 0; o.flags = 0; }
+    else { o.nkept = 0; o.n_nl = 0; o.flags = 0; o.kmask = 0; }
     flags |= o.flags;
+    if (o.kmask) {  // the kept bytes into the bitmap of pass A (the stretches of this path are not aligned: always OR)
+      const uint64_t k0 = (uint64_t)p0 + (uint32_t)((uintptr_t)a.text & 31u);
+      const uint32_t sh = (uint32_t)(k0 & 31u);
+      const uint64_t lo = o.kmask << sh;                       // bits of the words k0 >> 5 and + 1 ...
+      const uint64_t hi = sh ? (o.kmask >> (64u - sh)) : 0ull;  // ... and + 2
+      if ((uint32_t)lo) simt_atomic_or(&s.ka[k0 >> 5], (uint32_t)lo);
+      if ((uint32_t)(lo >> 32)) simt_atomic_or(&s.ka[(k0 >> 5) + 1], (uint32_t)(lo >> 32));
+      if ((uint32_t)hi) simt_atomic_or(&s.ka[(k0 >> 5) + 2], (uint32_t)hi);
+    }
     uint32_t tot, pre = simt_exscan(o.nkept, lane, &tot);
     for (uint32_t k = 0; k < o.nkept; k++) out[outpos + pre + k] = o.bytes[k];
     outpos += tot;

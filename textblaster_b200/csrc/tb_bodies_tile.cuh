@@ -598,6 +598,7 @@ TB_D void c4a_doc_tiles(const KBatch& a, const LutEntry* lut, uint8_t* stage, co
       if (last >= p0 && last < p0 + 32) nlk &= ~(1u << (uint32_t)(last - p0));  // the '\n' that ends the document
     }
     K |= nlk;
+    tb_bits_store(s.ka, p0, (uint32_t)((uintptr_t)t & 31u), V, K);
     outpos += tile_store_kept(T.w, K, stage, out + outpos, lane);
     // zero the slot of every line that starts after a '\n' of this stretch
     const uint32_t cnt = (uint32_t)tb_popc32(NLm);

@@ -10,6 +10,7 @@ typedef void* cudaStream_t;  // host emulation harness (tests/host_emul): no CUD
 #include "../../include/textblaster_b200.h"
 #include "tb_lanes.cuh"
 #include "tb_tile.cuh"
+#include "tb_simt.cuh"
 
 // Current view of the batch chunk on the device.
 struct KBatch {
@@ -112,7 +113,18 @@ struct C4Scratch {
   int64_t* prs; int64_t* pre;   // [n] ranges of P
   int64_t* frs; int64_t* fre;   // [n] ranges of F (untrimmed), then trimmed in place
   uint32_t* cnt;       // [n][4] too_long_word, no_terminal_punc, too_few_words, kept
+  // One bit per byte of the text C4 reads (bit (pos + mis) of the bitmap, mis = address of the text buffer & 31, so
+  // that a 32-byte stretch is one word): ka = the byte is part of its processed line (pass A: line trimmed,
+  // citations cut, '\n' kept except the document's last); kf = the byte is part of the joined kept lines (pass C,
+  // before the final trim; only written when kf != NULL).  Words shared by two documents are OR-ed: zero them first.
+  uint32_t* ka; uint32_t* kf;
 };
+// store the word of a stretch into such a bitmap (V: the bytes of the stretch that belong to this document)
+TB_D void tb_bits_store(uint32_t* bits, int64_t p0, uint32_t mis, uint32_t V, uint32_t K) {
+  if (!V) return;
+  uint32_t* w = bits + (((uint64_t)p0 + mis) >> 5);
+  if (V == 0xFFFFFFFFu) *w = K; else if (K) simt_atomic_or(w, K);
+}
 
 void tb_launch_init_ranges(cudaStream_t st, const void* off, int off64, int64_t doc0, int64_t n, int64_t base,
                            int64_t* rs, int64_t* re, uint8_t* alive, int8_t* failed);

@@ -217,13 +217,14 @@ struct C4aLane {
   uint8_t bytes[TB_STRETCH + 4];
   uint32_t n_nl;    // '\n' bytes in [p0, p1)
   uint32_t flags;   // C4F_*
+  uint64_t kmask;   // kept bytes: bit i = byte p0 + i (a character that begins in the stretch can end up to 3 bytes behind it)
 };
 // Pass A: original text -> "processed lines" (each line trimmed, citations removed), still joined
 // by the original '\n' (the one that ends the document is dropped).  c4_filters.rs:150-151,193-199
 TB_HD void c4a_lane(const Classifier& C, const TextRange& R, int64_t p0, int64_t p1, bool remove_citations,
                     bool want_lorem, C4aLane& o) {
   const uint8_t* t = R.t;
-  o.nkept = 0; o.n_nl = 0; o.flags = 0;
+  o.nkept = 0; o.n_nl = 0; o.flags = 0; o.kmask = 0;
   for (int64_t i = p0; i < p1; i++) {
     uint32_t b = tb_byte(t, i);
     if (b == '\n') o.n_nl++;
@@ -291,7 +292,7 @@ TB_HD void c4a_lane(const Classifier& C, const TextRange& R, int64_t p0, int64_t
         if (e > 0) { cit_end = e; keep = false; } else keep = true;
       } else keep = true;
     }
-    if (keep) for (int k = 0; k < len; k++) o.bytes[o.nkept++] = (uint8_t)tb_byte(t, i + k);
+    if (keep) for (int k = 0; k < len; k++) { o.bytes[o.nkept++] = (uint8_t)tb_byte(t, i + k); o.kmask |= 1ull << (uint32_t)(i + k - p0); }
     i += len;
   }
 }
