@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define TB_ABI_VERSION 2
+#define TB_ABI_VERSION 3
 #define TB_MAX_STEPS 8
 #define TB_MAX_NGRAMS 12 /* entries per top_n_grams / dup_n_grams list */
 #define TB_MAX_NGRAM_N 32 /* largest n-gram order accepted */
@@ -249,10 +249,15 @@ enum {
                                          or outside [0, n_bytes]; it was not processed (keep = 0, counters zero) */
 };
 
+/* One run of a document's content: the bytes [begin, end) of the document's own input text (TB_OPT_RETURN_CONTENT = 2) */
+typedef struct tb_run {
+  uint32_t begin, end;
+} tb_run;
+
 typedef struct tb_batch_out {
   int64_t n_docs;
   int32_t n_steps;
-  int32_t content_rewritten;       /* 1 if a C4 step ran: content/content_offsets are valid */
+  int32_t content_rewritten;       /* 1 if content/content_offsets are valid (a C4 step or the entity pre-pass ran, content returned as bytes) */
   uint8_t* keep;                   /* [n_docs] 1 = passed every step */
   int8_t* failed_step;             /* [n_docs] index into the pipeline, -1 = passed */
   void* step_stats[TB_MAX_STEPS];  /* [n_docs] of tb_c4_stats / tb_gq_stats / tb_gr_stats */
@@ -261,8 +266,13 @@ typedef struct tb_batch_out {
   int64_t content_bytes;
   double gpu_ms;                   /* device time of the kernels of this call (CUDA events) */
   int32_t gpu_launches;            /* kernels launched by this call */
-  int32_t _pad;
+  int32_t content_kind;            /* 0: no content returned, 1: content / content_offsets, 2: runs / run_offsets */
   void* _owner;                    /* internal */
+  /* TB_OPT_RETURN_CONTENT = 2: the content of document d is the concatenation of the runs
+   * runs[run_offsets[d] .. run_offsets[d + 1]) of its input text (tb_gather_content copies them out) */
+  const tb_run* runs;
+  const int64_t* run_offsets;      /* [n_docs + 1] */
+  int64_t n_runs;
 } tb_batch_out;
 
 typedef struct tb_ctx tb_ctx;
@@ -303,9 +313,24 @@ int tb_pipeline_run_batch_device(tb_pipeline* p, const uint8_t* utf8_dev, const 
 
 void tb_batch_out_release(tb_pipeline* p, tb_batch_out* out);
 
+/* The content of the selected documents of a batch, gathered on the host from the runs of a TB_OPT_RETURN_CONTENT = 2
+ * result and the caller's input column (the same utf8 / offsets that went into tb_pipeline_run_batch): what the
+ * reference's aggregator does when it pushes `document.content` into the output batch (src/producer_logic.rs:157-167,
+ * src/pipeline/writers/parquet_writer.rs:69-157).  select[d] != 0 picks document d (NULL: every document); the
+ * picked documents' contents go to dst back to back, dst_offsets gets their n_selected + 1 offsets.  dst may be
+ * NULL to learn the sizes only (*dst_bytes, dst_offsets).  nthreads <= 0: one thread per 64 MiB, at most 8.
+ * Pure host code: no CUDA call, any thread. */
+int tb_gather_content(const tb_batch_out* out, const uint8_t* utf8, const void* offsets, int offsets_are_i64, const uint8_t* select,
+                      uint8_t* dst, int64_t dst_capacity, int64_t* dst_offsets, int64_t* dst_bytes, int nthreads);
+
 /* Options (set before running; default in brackets) */
 enum {
-  TB_OPT_RETURN_CONTENT = 1, /* [1] copy rewritten content back to the host */
+  TB_OPT_RETURN_CONTENT = 1, /* [1] how the content after the chain comes back.  1: as bytes (content / content_offsets).  0: not at all.
+                                2: as runs of the caller's own text (runs / run_offsets) -- C4's output is a subsequence of its input
+                                (c4_filters.rs:192-258: lines trimmed, citations cut, kept lines joined by the '\n' in front of them), so
+                                a few (begin, end) pairs per document replace the bytes on the device->host link, and the caller (or
+                                tb_gather_content) copies the runs of the documents it writes out straight from its input column.  Falls
+                                back to 1 where the text C4 reads is not the caller's (entity pre-pass, split_paragraph = false) */
   TB_OPT_VALIDATE_UTF8 = 2,  /* [0] check inputs on the device, TB_ERR_INVALID_UTF8 on failure */
   TB_OPT_CHUNK_BYTES = 3,    /* [1 GiB] largest chunk the batch is processed in (device scratch: ~45 bytes per byte of it) */
   TB_OPT_GENERAL_WORD_PATH = 4, /* [0] testing: run the segment-walking word passes for every document (same results, slower) */

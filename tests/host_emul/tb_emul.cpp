@@ -198,6 +198,7 @@ extern "C" int tbe_run_chain(const tb_step_cfg* steps, size_t n_steps, const uin
   };
   auto alive_pred = [&](int64_t d) { return alive[d] != 0; };
   bool has_c4 = false;
+  const uint32_t* runs_kf = nullptr; const int64_t* runs_frs = nullptr; const int64_t* runs_fre = nullptr;  // for the runs check below
   for (size_t s = 0; s < n_steps; s++) {
     const tb_step_cfg& sc = steps[s];
     uint8_t* stats = G8(n1 * stat_size(sc.type));
@@ -249,8 +250,10 @@ extern "C" int tbe_run_chain(const tb_step_cfg* steps, size_t n_steps, const uin
       C4Cfg cfg = tb_c4cfg_of(sc.u.c4);
       const bool sent = !sc.u.c4.split_paragraph;
       const size_t cb = sent ? tb_grown_bytes(nb, n) : (size_t)nb, clines = cb + n1 + 1;
+      const size_t bw = cb / 32 + 4;
       C4Scratch cs{G8(cb + 64), G8(cb + 64), G64(n1), G32(n1), G32(n1), G32(clines), G32(clines), G32(clines),
-                   G64(n1), G64(n1), G64(n1), G64(n1), G32(4 * n1)};
+                   G64(n1), G64(n1), G64(n1), G64(n1), G32(4 * n1), G32(bw), G32(bw)};
+      memset(cs.ka, 0, bw * 4); memset(cs.kf, 0, bw * 4);
       const KBatch b_in = b;
       if (sent) {  // one sentence per line into S (the launch sequence of enqueue_chain)
         uint32_t* bits = G32((size_t)nb / 32 + 4);
@@ -275,6 +278,7 @@ extern "C" int tbe_run_chain(const tb_step_cfg* steps, size_t n_steps, const uin
       b.rs = b_in.rs; b.re = b_in.re;
       b.text = cs.F;
       has_c4 = true;
+      if (!sent && !decode_entities) { runs_kf = cs.kf; runs_frs = cs.frs; runs_fre = cs.fre; }
     } else {
       return 1;
     }
@@ -290,6 +294,31 @@ extern "C" int tbe_run_chain(const tb_step_cfg* steps, size_t n_steps, const uin
     run_warps(n, [&](int64_t) { return true; },
               [&](int64_t d, int lane) { body_pack(text, rs0, b.text, rs, rewritten, out_off, content_out, d, lane); });
     memcpy(content_off_out, out_off, n1 * 8);
+    if (runs_kf) {
+      // TB_OPT_RETURN_CONTENT = 2: the runs of the input text (count, offsets, write, as enqueue_chain does) must
+      // reproduce the packed content byte for byte
+      const uint32_t mis = (uint32_t)((uintptr_t)text & 31u);
+      int64_t *nruns = G64(n1), *roff = G64(n1 + 1);
+      run_warps(n, [&](int64_t) { return true; }, [&](int64_t d, int lane) {
+        body_c4_runs(rs0, re0, rewritten, runs_kf, mis, runs_frs, runs_fre, nruns, nullptr, nullptr, 0, false, d, lane); });
+      int64_t tot = 0;
+      for (int64_t d = 0; d < n; d++) { roff[d] = tot; tot += nruns[d]; }
+      roff[n] = tot;
+      tb_run_dev* runs = (tb_run_dev*)G64((size_t)tot + 1);
+      run_warps(n, [&](int64_t) { return true; }, [&](int64_t d, int lane) {
+        body_c4_runs(rs0, re0, rewritten, runs_kf, mis, runs_frs, runs_fre, nullptr, roff, runs, tot, true, d, lane); });
+      for (int64_t d = 0; d < n; d++) {
+        int64_t o = out_off[d];
+        for (int64_t k = roff[d]; k < roff[d + 1]; k++) {
+          if (runs[k].end <= runs[k].begin || (int64_t)runs[k].end > re0[d] - rs0[d]) return 9;
+          if (k > roff[d] && runs[k].begin <= runs[k - 1].end) return 9;  // runs are maximal and in order
+          const int64_t len = (int64_t)runs[k].end - runs[k].begin;
+          if (o + len > out_off[d + 1] || memcmp(content_out + o, text + rs0[d] + runs[k].begin, (size_t)len) != 0) return 9;
+          o += len;
+        }
+        if (o != out_off[d + 1]) return 9;
+      }
+    }
   }
   for (void* p : frees) free(p);
   return (has_c4 || decode_entities) ? 100 : 0;

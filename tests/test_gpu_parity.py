@@ -404,3 +404,72 @@ def test_size_independent_properties_at_scale():
     assert np.array_equal(second.content, buf2) and np.array_equal(second.content_offsets, off2)
     p.close()
     c4.close()
+
+
+@pytest.mark.parametrize("name", ["baseline_order", "shipped_order", "c4_shipped", "c4_lax", "c4_nopunct", "c4_then_open"])
+def test_content_as_runs(name):
+    """TB_OPT_RETURN_CONTENT = 2: the content comes back as runs of the caller's own text (C4's output is a subsequence of
+    its input, c4_filters.rs:192-258).  Gathered from the input column (tb_gather_content) it must equal the oracle's
+    content byte for byte; statistics and decisions are those of the byte mode.  Fuzzed, boundary-sliding, multi-tile
+    and synthetic documents; one chunk and many."""
+    steps = CHAINS[name]
+    rng = random.Random(41)
+    texts = (GOLDEN_DOCS + fuzzgen.FuzzGen(77).docs(400) + fuzzgen.boundary_docs() +
+             [fuzzgen.english_doc(rng, sz) for sz in (900, 1024, 3000, 20000, 70000)] + multilingual.corpus(4, 60))
+    p = GpuBatchPipeline(steps)
+    p.set_option(_abi.TB_OPT_RETURN_CONTENT, 2)
+    for chunk in (1 << 30, 1 << 16):
+        p.set_option(_abi.TB_OPT_CHUNK_BYTES, chunk)
+        res = p.run_texts(texts)
+        assert res.runs is not None and res.content is not None
+        ores = oracle.OraclePipeline(steps).run_texts(texts, nthreads=NCPU)
+        contents = [res.content_of(i) for i in range(res.n_docs)]
+        compare(ores, res.keep, res.failed_step, res.stats, contents, step_types(steps), texts, label=name + "/runs")
+        # runs are maximal, ordered and inside their document
+        lens = np.array([len(t.encode("utf-8")) for t in texts], np.int64)
+        for d in range(res.n_docs):
+            r = res.runs[int(res.run_offsets[d]):int(res.run_offsets[d + 1])].astype(np.int64)
+            assert (r[:, 1] > r[:, 0]).all() and (r[:, 1] <= lens[d]).all() and (r[1:, 0] > r[:-1, 1]).all()
+    utf8, off = synth.generate(20000, seed=synth.BASE_SEED + 5)
+    p.set_option(_abi.TB_OPT_CHUNK_BYTES, 8 << 20)
+    res = p.run_packed(utf8, off)
+    ores = oracle.OraclePipeline(steps).run_packed(utf8, off.astype(np.int64), nthreads=NCPU)
+    compare(ores, res.keep, res.failed_step, res.stats, None, step_types(steps), None, label=name + "/runs/synthetic")
+    ob, oo = ores.content_packed()
+    assert np.array_equal(res.content_offsets, oo) and np.array_equal(res.content, ob)
+    # far fewer bytes cross the link than the content holds
+    assert res.runs.nbytes < 0.2 * max(len(ob), 1)
+    p.close()
+
+
+def test_content_as_runs_select_and_fallback():
+    """tb_gather_content with a selection (the kept documents, as the writer of the output file wants them), and the
+    fall-back to bytes where the text C4 reads is not the caller's (sentences as lines, entity pre-pass)."""
+    from textblaster_b200.executor import gather_content
+    from textblaster_b200 import _native
+    steps = CHAINS["baseline_order"]
+    utf8, off = synth.generate(3000, seed=synth.BASE_SEED + 6)
+    p = GpuBatchPipeline(steps)
+    p.set_option(_abi.TB_OPT_RETURN_CONTENT, 2)
+    out = _abi.tb_batch_out()
+    p.run_raw(utf8.ctypes.data, off.ctypes.data, True, len(off) - 1, out)
+    assert out.content_kind == 2 and not out.content
+    keep = np.ctypeslib.as_array(out.keep, (len(off) - 1,)).copy()
+    got, goff = gather_content(out, utf8, off, select=keep, nthreads=3)
+    p.release(out)
+    ores = oracle.OraclePipeline(steps).run_packed(utf8, off.astype(np.int64), nthreads=NCPU)
+    assert np.array_equal(keep, ores.keep)
+    want = [ores.content(i) for i in np.flatnonzero(keep)]
+    assert len(goff) == len(want) + 1
+    for k, w in enumerate(want[:400]):
+        assert bytes(got[goff[k]:goff[k + 1]]).decode("utf-8") == w
+    assert int(goff[-1]) == sum(len(w.encode("utf-8")) for w in want)
+    p.close()
+    for chain, opt in (("c4_sentences", None), ("c4_shipped", _abi.TB_OPT_DECODE_HTML_ENTITIES)):
+        q = GpuBatchPipeline(CHAINS[chain])
+        q.set_option(_abi.TB_OPT_RETURN_CONTENT, 2)
+        if opt:
+            q.set_option(opt, 1)
+        r = q.run_texts(["One sentence here. And a second one follows it. A third &amp; last one ends it. Four. Five is it."])
+        assert r.runs is None and r.content is not None
+        q.close()

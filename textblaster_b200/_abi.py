@@ -5,7 +5,7 @@ oracle's loader can describe the same C structs.
 """
 import ctypes as C
 
-TB_ABI_VERSION = 2
+TB_ABI_VERSION = 3
 TB_MAX_STEPS = 8
 TB_MAX_NGRAMS = 12
 TB_MAX_NGRAM_N = 32
@@ -213,6 +213,10 @@ class tb_fw_stats(C.Structure):
     ]
 
 
+class tb_run(C.Structure):
+    _fields_ = [("begin", C.c_uint32), ("end", C.c_uint32)]
+
+
 class tb_batch_out(C.Structure):
     _fields_ = [
         ("n_docs", C.c_int64),
@@ -226,8 +230,11 @@ class tb_batch_out(C.Structure):
         ("content_bytes", C.c_int64),
         ("gpu_ms", C.c_double),
         ("gpu_launches", C.c_int32),
-        ("_pad", C.c_int32),
+        ("content_kind", C.c_int32),
         ("_owner", C.c_void_p),
+        ("runs", C.POINTER(tb_run)),
+        ("run_offsets", C.POINTER(C.c_int64)),
+        ("n_runs", C.c_int64),
     ]
 
 

@@ -16,7 +16,7 @@ _lib = None
 EXPORTS = [
     "tb_abi_version", "tb_last_error", "tb_step_name", "tb_ctx_create", "tb_ctx_destroy", "tb_pipeline_create",
     "tb_pipeline_destroy", "tb_pipeline_run_batch", "tb_pipeline_run_batch_device", "tb_batch_out_release",
-    "tb_pipeline_set_option", "tb_pipeline_kernel_times", "tb_pipeline_reset_kernel_times",
+    "tb_pipeline_set_option", "tb_pipeline_kernel_times", "tb_pipeline_reset_kernel_times", "tb_gather_content",
 ]
 
 
@@ -50,6 +50,9 @@ def lib():
     L.tb_pipeline_kernel_times.restype = C.c_int
     L.tb_pipeline_kernel_times.argtypes = [C.c_void_p, C.c_int32, C.POINTER(C.c_char_p), C.POINTER(C.c_double), C.POINTER(C.c_int64)]
     L.tb_pipeline_reset_kernel_times.argtypes = [C.c_void_p]
+    L.tb_gather_content.restype = C.c_int
+    L.tb_gather_content.argtypes = [C.POINTER(_abi.tb_batch_out), C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int64,
+                                    C.c_void_p, C.POINTER(C.c_int64), C.c_int]
     if L.tb_abi_version() != _abi.TB_ABI_VERSION:
         raise Unexpected(f"ABI mismatch: library {L.tb_abi_version()} vs binding {_abi.TB_ABI_VERSION}")
     _lib = L

@@ -11,6 +11,7 @@
 #include <chrono>
 #include <mutex>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "tb_hostutil.h"
@@ -152,6 +153,7 @@ struct tb_pipeline {
   // C4 scratch
   DevBuf e_D, e_amp, e_drop, e_drs, e_dre;  // HTML entity pre-pass
   DevBuf c_S, c_bits, c_srs, c_sre;  // sentence-wise lines
+  DevBuf c_ka, c_kf;                 // kept-byte bitmaps of passes A and C (tb_kernels.cuh C4Scratch)
   DevBuf c_P, c_F, c_plen, c_nlines, c_docflags, c_lwc, c_lmax, c_lflags, c_prs, c_pre, c_frs, c_fre, c_cnt;
   cudaEvent_t ev_h2d[2] = {nullptr, nullptr}, ev_done[2] = {nullptr, nullptr}, ev_d2h[2] = {nullptr, nullptr}, ev_small[2] = {nullptr, nullptr};
   std::vector<ResultSet*> results;
@@ -311,7 +313,7 @@ int ensure_chunk_buffers(tb_pipeline* p, int64_t n, int64_t nb, bool host_input)
   }
   const size_t cb_in = cb;  // what the sentence-wise pre-pass of C4 reads
   if (sent) cb = tb_grown_bytes((int64_t)cb, n);
-  for (int i = 0; i < 2; i++) ENS(p->packed[i], cb + 64);
+  for (int i = 0; i < 2; i++) ENS(p->packed[i], cb + 8 * n1 + 64);  // the content, or its runs: at most one per 8 bytes of text + one per document
   ENS(p->rs0, n1 * 8); ENS(p->re0, n1 * 8); ENS(p->rs, n1 * 8); ENS(p->re, n1 * 8); ENS(p->ts, n1 * 8); ENS(p->te, n1 * 8);
   for (int i = 0; i < 2; i++) { ENS(p->alive[i], n1); ENS(p->failed[i], n1); ENS(p->out_off[i], (n1 + 1) * 8); }
   ENS(p->rewritten, n1); ENS(p->len, n1 * 8); ENS(p->bad, 16); ENS(p->cursors, 256); ENS(p->order, n1 * 4); ENS(p->sizecls, n1);
@@ -330,6 +332,7 @@ int ensure_chunk_buffers(tb_pipeline* p, int64_t n, int64_t nb, bool host_input)
     } else if (sh.type == TB_STEP_C4_QUALITY) {
       size_t lines = cb + n1 + 1;
       ENS(p->c_P, cb + 64); ENS(p->c_F, cb + 64);
+      ENS(p->c_ka, (cb / 32 + 4) * 4); ENS(p->c_kf, (cb / 32 + 4) * 4);
       if (sh.c4_sentences) { ENS(p->c_S, cb + 64); ENS(p->c_bits, (cb_in / 32 + 4) * 4); ENS(p->c_srs, n1 * 8); ENS(p->c_sre, n1 * 8); }
       ENS(p->c_plen, n1 * 8); ENS(p->c_nlines, n1 * 4); ENS(p->c_docflags, n1 * 4);
       ENS(p->c_lwc, lines * 4); ENS(p->c_lmax, lines * 4); ENS(p->c_lflags, lines * 4);
@@ -342,7 +345,9 @@ int ensure_chunk_buffers(tb_pipeline* p, int64_t n, int64_t nb, bool host_input)
 
 // Enqueue every kernel of the chain for one chunk whose text is at `text` (device) with ranges in
 // rs0/re0 (already initialised).  Leaves packed content in p->packed[pb] and offsets in out_off.
-int enqueue_chain(tb_pipeline* p, const uint8_t* text, int64_t n, int64_t nbytes, int pb, bool want_content, bool* has_c4) {
+// content_mode: 0 nothing is returned, 1 the packed content, 2 runs of the input text (one C4 step, lines = str::lines)
+int enqueue_chain(tb_pipeline* p, const uint8_t* text, int64_t n, int64_t nbytes, int pb, int content_mode, bool* has_c4) {
+  const bool want_content = content_mode != 0;
   tb_ctx* c = p->ctx;
   cudaStream_t st = c->compute;
   CK(cudaMemcpyAsync(p->rs.p, p->rs0.p, (size_t)n * 8, cudaMemcpyDeviceToDevice, st));
@@ -386,7 +391,13 @@ int enqueue_chain(tb_pipeline* p, const uint8_t* text, int64_t n, int64_t nbytes
     } else {
       C4Scratch cs{p->c_P.as<uint8_t>(), p->c_F.as<uint8_t>(), p->c_plen.as<int64_t>(), p->c_nlines.as<uint32_t>(),
                    p->c_docflags.as<uint32_t>(), p->c_lwc.as<uint32_t>(), p->c_lmax.as<uint32_t>(), p->c_lflags.as<uint32_t>(),
-                   p->c_prs.as<int64_t>(), p->c_pre.as<int64_t>(), p->c_frs.as<int64_t>(), p->c_fre.as<int64_t>(), p->c_cnt.as<uint32_t>()};
+                   p->c_prs.as<int64_t>(), p->c_pre.as<int64_t>(), p->c_frs.as<int64_t>(), p->c_fre.as<int64_t>(), p->c_cnt.as<uint32_t>(),
+                   p->c_ka.as<uint32_t>(), content_mode == 2 ? p->c_kf.as<uint32_t>() : nullptr};
+      {  // the bitmaps are OR-ed into where two documents share a word
+        const size_t bw = ((size_t)(sh.c4_sentences ? tb_grown_bytes(nbytes, n) : (size_t)nbytes) / 32 + 4) * 4;
+        CK(cudaMemsetAsync(p->c_ka.p, 0, bw, st));
+        if (cs.kf) CK(cudaMemsetAsync(p->c_kf.p, 0, bw, st));
+      }
       const KBatch b_in = b;  // rs / re of the chain: pass D writes the ranges of the rewritten documents there
       if (sh.c4_sentences) {  // one sentence per line into S; the line passes then run on S
         CK(cudaMemsetAsync(p->c_bits.p, 0, ((size_t)nbytes / 32 + 4) * 4, st));
@@ -409,7 +420,15 @@ int enqueue_chain(tb_pipeline* p, const uint8_t* text, int64_t n, int64_t nbytes
       *has_c4 = true;
     }
   }
-  if (want_content) {  // a C4 step rewrote documents, or the entity pre-pass made `text` a copy of its own
+  if (content_mode == 2) {  // runs of the caller's text: count, offsets, write (the text of the chain's first step is the caller's)
+    const uint32_t mis = (uint32_t)((uintptr_t)text & 31u);
+    const int64_t cap = nbytes / 8 + n;  // runs packed[pb] holds
+    { Timed t(p, "k_c4_runs"); tb_launch_c4_runs(st, n, p->rs0.as<int64_t>(), p->re0.as<int64_t>(), p->rewritten.as<uint8_t>(), p->c_kf.as<uint32_t>(), mis,
+                                                 p->c_frs.as<int64_t>(), p->c_fre.as<int64_t>(), p->len.as<int64_t>(), nullptr, nullptr, cap, 0); }
+    { Timed t(p, "k_scan_i64"); tb_launch_scan_i64(st, p->len.as<int64_t>(), p->out_off[pb].as<int64_t>(), n); }
+    { Timed t(p, "k_c4_runs"); tb_launch_c4_runs(st, n, p->rs0.as<int64_t>(), p->re0.as<int64_t>(), p->rewritten.as<uint8_t>(), p->c_kf.as<uint32_t>(), mis,
+                                                 p->c_frs.as<int64_t>(), p->c_fre.as<int64_t>(), nullptr, p->out_off[pb].as<int64_t>(), p->packed[pb].p, cap, 1); }
+  } else if (want_content) {  // a C4 step rewrote documents, or the entity pre-pass made `text` a copy of its own
     { Timed t(p, "k_final_len"); tb_launch_final_len(st, n, p->rs0.as<int64_t>(), p->re0.as<int64_t>(), b.rs, b.re, p->rewritten.as<uint8_t>(), p->len.as<int64_t>()); }
     { Timed t(p, "k_scan_i64"); tb_launch_scan_i64(st, p->len.as<int64_t>(), p->out_off[pb].as<int64_t>(), n); }
     { Timed t(p, "k_pack"); tb_launch_pack(st, n, text, p->rs0.as<int64_t>(), b.text, b.rs, p->rewritten.as<uint8_t>(), p->out_off[pb].as<int64_t>(), p->packed[pb].as<uint8_t>()); }
@@ -431,9 +450,14 @@ int run_impl(tb_pipeline* p, const uint8_t* utf8, const void* offsets, int is64,
   p->launches_this_run = 0; p->ms_this_run = 0;
   bool any_c4 = false;
   for (auto& s : p->steps) any_c4 |= s.type == TB_STEP_C4_QUALITY;
-  const bool want_content = (any_c4 || p->opt_decode) && p->opt_return_content;
   bool sent_mode = false;
   for (auto& s : p->steps) sent_mode |= s.type == TB_STEP_C4_QUALITY && s.c4_sentences;
+  // what comes back as the content: nothing, the bytes, or runs of the caller's own text.  Runs need the text C4 reads to
+  // be the caller's (no entity pre-pass, lines = str::lines); otherwise the bytes are returned.
+  int content_mode = (any_c4 || p->opt_decode) ? (int)p->opt_return_content : 0;
+  if (content_mode == 2 && (p->opt_decode || sent_mode || !any_c4)) content_mode = 1;
+  const bool want_content = content_mode != 0;
+  const size_t esz = content_mode == 2 ? sizeof(tb_run) : 1;  // bytes per element of the content buffer
 
   size_t content_cap = (size_t)0;
   ResultSet* rsx = acquire_results(p);
@@ -447,7 +471,7 @@ int run_impl(tb_pipeline* p, const uint8_t* utf8, const void* offsets, int is64,
   content_cap = (size_t)total_bytes;
   if (p->opt_decode) content_cap = tb_grown_bytes((int64_t)content_cap, n_docs);
   if (sent_mode) content_cap = tb_grown_bytes((int64_t)content_cap, n_docs);
-  if (want_content) { if ((rc = rsx->content.ensure(content_cap + 64)) || (rc = rsx->content_off.ensure(n1 * 8))) return rc; }
+  if (want_content) { if ((rc = rsx->content.ensure(content_cap + 8 * n1 + 64)) || (rc = rsx->content_off.ensure(n1 * 8))) return rc; }
   for (int64_t i = 0; i < n_docs; i++) if (off_at(offsets, is64, i + 1) < off_at(offsets, is64, i)) return fail(TB_ERR_INVALID_ARGUMENT, "offsets must be non-decreasing");
 
   // chunk plan.  Large chunks cost the least device time (every launch of the chain ends with a tail: about
@@ -510,8 +534,10 @@ int run_impl(tb_pipeline* p, const uint8_t* utf8, const void* offsets, int is64,
     if (p->opt_validate && h_bad) return fail(TB_ERR_INVALID_UTF8, "input contains " + std::to_string(h_bad) + " document(s) with invalid UTF-8 (first chunk doc " + std::to_string(ch.d0) + ")");
     if (want_content) {
       int64_t tot = h_coff[ch.d0 + n];
+      if (content_mode == 2 && tot > (ch.b1 - ch.b0) / 8 + n)
+        return fail(TB_ERR_UNSUPPORTED, "content too fragmented for TB_OPT_RETURN_CONTENT = 2 (more than one run per 8 bytes of text in a chunk): use 1");
       for (int64_t i = 0; i <= n; i++) h_coff[ch.d0 + i] += content_base;  // chunk-relative -> absolute
-      if (tot) CK(cudaMemcpyAsync(h_content + content_base, p->packed[buf].p, (size_t)tot, cudaMemcpyDeviceToHost, c->d2h));
+      if (tot) CK(cudaMemcpyAsync(h_content + (size_t)content_base * esz, p->packed[buf].p, (size_t)tot * esz, cudaMemcpyDeviceToHost, c->d2h));
       content_base += tot;
     }
     CK(cudaEventRecord(p->ev_d2h[buf], c->d2h));
@@ -554,7 +580,7 @@ int run_impl(tb_pipeline* p, const uint8_t* utf8, const void* offsets, int is64,
       text_extent = (int64_t)tb_grown_bytes(text_extent, n);
     }
     bool has_c4 = false;
-    if ((rc = enqueue_chain(p, text, n, text_extent, buf, want_content, &has_c4))) return rc;
+    if ((rc = enqueue_chain(p, text, n, text_extent, buf, content_mode, &has_c4))) return rc;
     CK(cudaEventRecord(p->ev_done[buf], c->compute));
     // the previous chunk's content goes out first (its copy must not queue behind this chunk's kernels)
     if (ci > 0) if ((rc = finish(ci - 1))) return rc;
@@ -582,7 +608,9 @@ int run_impl(tb_pipeline* p, const uint8_t* utf8, const void* offsets, int is64,
   for (size_t s = 0; s < p->steps.size(); s++) out->step_stats[s] = rsx->stats[s].p;
   if (want_content) {
     if (n_docs == 0) h_coff[0] = 0;
-    out->content_rewritten = 1; out->content = h_content; out->content_offsets = h_coff; out->content_bytes = content_base;
+    out->content_kind = content_mode;
+    if (content_mode == 2) { out->runs = (const tb_run*)h_content; out->run_offsets = h_coff; out->n_runs = content_base; }
+    else { out->content_rewritten = 1; out->content = h_content; out->content_offsets = h_coff; out->content_bytes = content_base; }
   }
   out->gpu_ms = p->ms_this_run;
   out->gpu_launches = p->launches_this_run;
@@ -714,7 +742,7 @@ void tb_pipeline_destroy(tb_pipeline* p) {
   cudaDeviceSynchronize();
   for (DevBuf* b : {&p->text[0], &p->text[1], &p->offs[0], &p->offs[1], &p->packed[0], &p->packed[1], &p->rs0, &p->re0, &p->rs,
                     &p->re, &p->ts, &p->te, &p->alive[0], &p->alive[1], &p->failed[0], &p->failed[1], &p->rewritten, &p->len, &p->out_off[0], &p->out_off[1], &p->bad, &p->cursors, &p->order, &p->sizecls, &p->g_wh,
-                    &p->g_wl, &p->g_ws, &p->g_lh, &p->g_ll, &p->g_lg, &p->g_doc, &p->g_work, &p->g_lists, &p->g_counters, &p->f_lh, &p->f_ll, &p->f_doc, &p->f_tab, &p->e_D, &p->e_amp, &p->e_drop, &p->e_drs, &p->e_dre, &p->c_S, &p->c_bits, &p->c_srs, &p->c_sre, &p->c_P, &p->c_F, &p->c_plen, &p->c_nlines,
+                    &p->g_wl, &p->g_ws, &p->g_lh, &p->g_ll, &p->g_lg, &p->g_doc, &p->g_work, &p->g_lists, &p->g_counters, &p->f_lh, &p->f_ll, &p->f_doc, &p->f_tab, &p->e_D, &p->e_amp, &p->e_drop, &p->e_drs, &p->e_dre, &p->c_S, &p->c_bits, &p->c_srs, &p->c_sre, &p->c_ka, &p->c_kf, &p->c_P, &p->c_F, &p->c_plen, &p->c_nlines,
                     &p->c_docflags, &p->c_lwc, &p->c_lmax, &p->c_lflags, &p->c_prs, &p->c_pre, &p->c_frs, &p->c_fre, &p->c_cnt})
     b->release();
   for (auto& b : p->stats) { b[0].release(); b[1].release(); }
@@ -738,7 +766,9 @@ int tb_pipeline_set_option(tb_pipeline* p, int32_t option, int64_t value) {
   if (!p) return fail(TB_ERR_INVALID_ARGUMENT, "NULL pipeline");
   std::lock_guard<std::mutex> lk(p->mu);
   switch (option) {
-    case TB_OPT_RETURN_CONTENT: p->opt_return_content = value != 0; return TB_OK;
+    case TB_OPT_RETURN_CONTENT:
+      if (value < 0 || value > 2) return fail(TB_ERR_INVALID_ARGUMENT, "TB_OPT_RETURN_CONTENT: 0 (nothing), 1 (content) or 2 (runs of the input text)");
+      p->opt_return_content = value; return TB_OK;
     case TB_OPT_VALIDATE_UTF8: p->opt_validate = value != 0; return TB_OK;
     case TB_OPT_GENERAL_WORD_PATH: p->opt_debug = value != 0 ? TB_DBG_FORCE_WALK : 0; return TB_OK;
     case TB_OPT_DECODE_HTML_ENTITIES: p->opt_decode = value != 0; return TB_OK;
@@ -776,6 +806,57 @@ void tb_batch_out_release(tb_pipeline* p, tb_batch_out* out) {
   std::lock_guard<std::mutex> lk(p->mu);
   ((ResultSet*)out->_owner)->in_use = false;
   memset(out, 0, sizeof *out);
+}
+
+int tb_gather_content(const tb_batch_out* out, const uint8_t* utf8, const void* offsets, int offsets_are_i64, const uint8_t* select,
+                      uint8_t* dst, int64_t dst_capacity, int64_t* dst_offsets, int64_t* dst_bytes, int nthreads) {
+  if (!out || !dst_offsets || (out->n_docs > 0 && !offsets)) return fail(TB_ERR_INVALID_ARGUMENT, "tb_gather_content: NULL argument");
+  if (out->content_kind != 2 || !out->run_offsets) return fail(TB_ERR_INVALID_ARGUMENT, "tb_gather_content: the batch holds no runs (TB_OPT_RETURN_CONTENT = 2)");
+  const int64_t n = out->n_docs;
+  const tb_run* runs = out->runs;
+  const int64_t* ro = out->run_offsets;
+  // the documents are dealt to the threads in contiguous shares; pass 1 sizes every share, pass 2 writes offsets and bytes
+  int T = nthreads > 0 ? nthreads : (int)std::min<int64_t>(8, n / 32768 + 1);
+  T = std::max(1, std::min(T, 64));
+  std::vector<int64_t> share_docs(T + 1, 0), share_bytes(T + 1, 0);
+  auto each = [&](auto&& fn) {
+    if (T == 1) { fn(0); return; }
+    std::vector<std::thread> th;
+    for (int t = 1; t < T; t++) th.emplace_back(fn, t);
+    fn(0);
+    for (auto& x : th) x.join();
+  };
+  each([&](int t) {
+    int64_t nd = 0, nb = 0;
+    for (int64_t d = n * t / T, e = n * (t + 1) / T; d < e; d++) {
+      if (select && !select[d]) continue;
+      nd++;
+      for (int64_t k = ro[d]; k < ro[d + 1]; k++) nb += (int64_t)runs[k].end - (int64_t)runs[k].begin;
+    }
+    share_docs[t + 1] = nd; share_bytes[t + 1] = nb;
+  });
+  for (int t = 0; t < T; t++) { share_docs[t + 1] += share_docs[t]; share_bytes[t + 1] += share_bytes[t]; }
+  const int64_t acc = share_bytes[T];
+  if (dst_bytes) *dst_bytes = acc;
+  if (dst) {
+    if (acc > dst_capacity) return fail(TB_ERR_INVALID_ARGUMENT, "tb_gather_content: dst holds " + std::to_string(dst_capacity) + " bytes, " + std::to_string(acc) + " needed");
+    if (acc > 0 && !utf8) return fail(TB_ERR_INVALID_ARGUMENT, "tb_gather_content: utf8 is NULL");
+  }
+  dst_offsets[0] = 0;
+  each([&](int t) {
+    int64_t k = share_docs[t], o = share_bytes[t];
+    for (int64_t d = n * t / T, e = n * (t + 1) / T; d < e; d++) {
+      if (select && !select[d]) continue;
+      const uint8_t* src = utf8 + off_at(offsets, offsets_are_i64, d);
+      for (int64_t r = ro[d]; r < ro[d + 1]; r++) {
+        const size_t len = (size_t)runs[r].end - runs[r].begin;
+        if (dst) memcpy(dst + o, src + runs[r].begin, len);
+        o += (int64_t)len;
+      }
+      dst_offsets[++k] = o;
+    }
+  });
+  return TB_OK;
 }
 
 int tb_pipeline_kernel_times(tb_pipeline* p, int32_t max_entries, const char** names, double* ms, int64_t* launches) {

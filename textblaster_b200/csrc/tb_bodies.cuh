@@ -411,10 +411,15 @@ TB_D void body_c4_b(const KBatch& a, const uint16_t* s_ascii, const LutEntry* lu
 }
 
 // Pass C: drop lines, join the kept ones with '\n' (c4_filters.rs:207-258) -> F; line counters.
+// It walks the text pass A read, not P: the processed lines are the bytes pass A marked in `ka`, and the '\n' bytes
+// (all of them marked but the document's last) sit where they sat.  So every byte of F is a byte of that text, and
+// the bitmap `kf` of the bytes that went into F is all a caller needs to rebuild the content from its own copy
+// of the text (TB_OPT_RETURN_CONTENT = 2, k_c4_runs).
 TB_D uint32_t tile_store_kept(const uint32_t* w, uint32_t K, uint8_t* stage, uint8_t* dst, int lane);
 TB_D void body_c4_c(const KBatch& a, uint8_t* stage, const C4Cfg& cfg, const C4Scratch& s, int64_t d, int lane) {
   if (!a.alive[d] || s.docflags[d]) { if (lane == 0) { s.frs[d] = a.rs[d]; s.fre[d] = a.rs[d]; } return; }
-  TextRange R{s.P, s.prs[d], s.pre[d]};
+  TextRange R{a.text, a.rs[d], a.re[d]};
+  const uint32_t mis = (uint32_t)((uintptr_t)a.text & 31u);
   uint8_t* out = s.F + a.rs[d];
   const uint64_t lb = (uint64_t)a.rs[d] + (uint64_t)d;
   const uint32_t m = s.nlines[d];
@@ -426,7 +431,12 @@ TB_D void body_c4_c(const KBatch& a, uint8_t* stage, const C4Cfg& cfg, const C4S
       uint32_t w[8];
       const int64_t p0 = base + lane * TB_STRETCH;
       const uint32_t V = tile_load(R, a.ext_lo, a.ext_hi, p0, w);
-      const uint32_t NLm = tile_eq_mask(w, '\n') & V;
+      uint32_t NLm = tile_eq_mask(w, '\n') & V;
+      {
+        const int64_t last = R.re - 1;  // the '\n' that ends the document ends no line of P (pass A dropped it)
+        if (last >= p0 && last < p0 + 32) NLm &= ~(1u << (uint32_t)(last - p0));
+      }
+      const uint32_t KA = V ? (s.ka[((uint64_t)p0 + mis) >> 5] & V) : 0u;
       const uint32_t cnt = (uint32_t)tb_popc32(NLm);
       uint32_t tot, pre = simt_exscan(cnt, lane, &tot);
       const uint64_t l0 = lb + nl + pre;  // line that holds the first byte of the stretch
@@ -451,7 +461,9 @@ TB_D void body_c4_c(const KBatch& a, uint8_t* stage, const C4Cfg& cfg, const C4S
         start = bit + 1;
       }
       if ((dec >> cnt) & 1u) K |= ~tb_below(start);
-      outpos += tile_store_kept(w, K & V, stage, out + outpos, lane);
+      K &= KA;  // (the '\n' bytes between lines are marked in ka)
+      if (s.kf) tb_bits_store(s.kf, p0, mis, V, K);
+      outpos += tile_store_kept(w, K, stage, out + outpos, lane);
       nl += tot; kept_run += ktot;
     }
     if (lane == 0) {  // the last line has no terminator
@@ -651,6 +663,72 @@ TB_D void body_entities(const KBatch& a, uint8_t* stage, const EntEntry* tab, ui
     outpos += tot;
   }
   if (lane == 0) { drs[d] = o0; dre[d] = o0 + outpos; }
+}
+
+// ---------------------------------------------------------------------------------------------
+// final content as runs of the caller's own text (TB_OPT_RETURN_CONTENT = 2)
+// ---------------------------------------------------------------------------------------------
+// C4's output is a subsequence of its input (c4_filters.rs:192-258: lines trimmed, citations cut, kept lines joined by
+// the '\n' that stood in front of them).  Instead of the rewritten bytes the host gets, per document, the maximal runs
+// [begin, end) of input bytes (relative to the document's start) whose concatenation is the content.  A document C4
+// did not rewrite is one run, its whole text.  For a rewritten one the runs are read off the bitmap `kf` of pass C,
+// cut to the bytes that survive the final trim (c4_filters.rs:258): F holds `total` bytes, the trimmed content is
+// its bytes [lo, hi).  One warp per document, a bitmap word per lane; emit = false only counts (nruns[d]).
+struct tb_run_dev { uint32_t begin, end; };
+TB_D void body_c4_runs(const int64_t* rs0, const int64_t* re0, const uint8_t* rewritten, const uint32_t* kf, uint32_t mis,
+                       const int64_t* frs, const int64_t* fre, int64_t* nruns, const int64_t* run_off, tb_run_dev* runs,
+                       int64_t cap, bool emit, int64_t d, int lane) {
+  const int64_t rs = rs0[d], re = re0[d];
+  if (!rewritten[d]) {
+    if (lane == 0) {
+      if (!emit) nruns[d] = re > rs ? 1 : 0;
+      else if (re > rs && run_off[d] < cap) runs[run_off[d]] = tb_run_dev{0u, (uint32_t)(re - rs)};
+    }
+    return;
+  }
+  const int64_t lo = frs[d] - rs, hi = lo + (fre[d] - frs[d]);  // ranks (in F) of the bytes that stay
+  const uint64_t w0 = ((uint64_t)rs + mis) >> 5, w1 = ((uint64_t)re + mis) >> 5;  // one word past the text closes a run that reaches its end
+  int64_t rank = 0, nb = 0, ne = 0;  // kept bytes / run begins / run ends before this round of 32 words
+  uint32_t carry = 0;                // the bit in front of this round's first word
+  const int64_t base = run_off ? run_off[d] : 0;
+  for (uint64_t wb = w0; wb <= w1; wb += 32) {
+    const uint64_t wi = wb + (uint64_t)lane;
+    uint32_t w = 0;
+    if (wi <= w1 && rs < re) {
+      w = kf[wi];
+      const int64_t p0 = (int64_t)(wi << 5) - mis;  // position of bit 0
+      if (p0 < rs) w &= ~tb_below((int)(rs - p0 > 32 ? 32 : rs - p0));
+      if (p0 + 32 > re) w &= tb_below((int)(re - p0 < 0 ? 0 : re - p0));
+    }
+    // keep the bits whose rank lies in [lo, hi)
+    const uint32_t c = (uint32_t)tb_popc32(w);
+    uint32_t tot, pre = simt_exscan(c, lane, &tot);
+    const int64_t r0 = rank + pre;
+    if (c) {
+      if (r0 + c <= lo || r0 >= hi) w = 0;
+      else {
+        for (int64_t k = r0; k < lo; k++) w &= w - 1u;                     // drop the lowest bits below lo
+        int64_t over = r0 + c - hi;                                         // ... and the highest beyond hi
+        while (over-- > 0) w &= ~(0x80000000u >> tb_clz32(w));
+      }
+    }
+    rank += tot;
+    uint32_t prev_top = simt_shfl_up(w >> 31, 1);
+    if (lane == 0) prev_top = carry;
+    carry = simt_shfl(w >> 31, 31);
+    const uint32_t before = (w << 1) | prev_top;
+    uint32_t begins = w & ~before, ends = ~w & before;  // a run begins at a set bit after a clear one, and ends in front of a clear bit after a set one
+    uint32_t tb_, te_, pb = simt_exscan((uint32_t)tb_popc32(begins), lane, &tb_), pe = simt_exscan((uint32_t)tb_popc32(ends), lane, &te_);
+    if (emit) {
+      const int64_t p0 = (int64_t)(wi << 5) - mis - rs;
+      int64_t k = base + nb + pb;
+      for (; begins; begins &= begins - 1u, k++) if (k < cap) runs[k].begin = (uint32_t)(p0 + tb_ctz32(begins));
+      k = base + ne + pe;
+      for (; ends; ends &= ends - 1u, k++) if (k < cap) runs[k].end = (uint32_t)(p0 + tb_ctz32(ends));
+    }
+    nb += tb_; ne += te_;
+  }
+  if (!emit && lane == 0) nruns[d] = nb;
 }
 
 // ---------------------------------------------------------------------------------------------

@@ -248,6 +248,12 @@ __global__ void __launch_bounds__(TB_BLOCK, 16) k_fw_fin(KBatch a, FwCfg cfg, Fw
     __syncwarp();
   }
 }
+__global__ void __launch_bounds__(TB_BLOCK) k_c4_runs(int64_t n, const int64_t* rs0, const int64_t* re0, const uint8_t* rewritten, const uint32_t* kf,
+                                                      uint32_t mis, const int64_t* frs, const int64_t* fre, int64_t* nruns, const int64_t* run_off,
+                                                      tb_run_dev* runs, int64_t cap, int emit) {
+  int64_t d = warp_doc();
+  if (d < n) body_c4_runs(rs0, re0, rewritten, kf, mis, frs, fre, nruns, run_off, runs, cap, emit != 0, d, threadIdx.x & 31);
+}
 __global__ void k_final_len(int64_t n, const int64_t* rs0, const int64_t* re0, const int64_t* rs, const int64_t* re,
                             const uint8_t* rewritten, int64_t* len) {
   int64_t d = thread_doc();
@@ -358,6 +364,10 @@ void tb_launch_c4_d(cudaStream_t st, const KBatch& b, const C4Cfg& cfg, const C4
                     uint8_t* rewritten, int64_t* rs_out, int64_t* re_out, int sm_count, uint32_t* cursor) {
   // the new ranges go to rs_out / re_out (the chain's rs / re), only for documents that were rewritten
   if (b.n) k_c4_d<<<persistent_grid(b.n, sm_count, 24), TB_BLOCK, 0, st>>>(b, cfg, s, step, out, rewritten, rs_out, re_out, cursor);
+}
+void tb_launch_c4_runs(cudaStream_t st, int64_t n, const int64_t* rs0, const int64_t* re0, const uint8_t* rewritten, const uint32_t* kf,
+                       uint32_t mis, const int64_t* frs, const int64_t* fre, int64_t* nruns, const int64_t* run_off, void* runs, int64_t cap, int emit) {
+  if (n) k_c4_runs<<<blocks_for_warps(n), TB_BLOCK, 0, st>>>(n, rs0, re0, rewritten, kf, mis, frs, fre, nruns, run_off, (tb_run_dev*)runs, cap, emit);
 }
 void tb_launch_final_len(cudaStream_t st, int64_t n, const int64_t* rs0, const int64_t* re0, const int64_t* rs,
                          const int64_t* re, const uint8_t* rewritten, int64_t* len) {

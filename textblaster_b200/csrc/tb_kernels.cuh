@@ -155,6 +155,10 @@ void tb_launch_c4_sent(cudaStream_t st, const KBatch& b, const int64_t* ts, cons
                        int64_t* srs, int64_t* sre, int sm_count, uint32_t* cursor);
 void tb_launch_validate_utf8(cudaStream_t st, const uint8_t* text, const int64_t* rs, const int64_t* re, int64_t n,
                              int32_t* bad);
+// final content as runs of the input text (TB_OPT_RETURN_CONTENT = 2): emit = 0 counts the runs of every document into
+// nruns, emit = 1 writes them (8 bytes each: begin, end) at run_off[d]; at most cap runs are written
+void tb_launch_c4_runs(cudaStream_t st, int64_t n, const int64_t* rs0, const int64_t* re0, const uint8_t* rewritten, const uint32_t* kf,
+                       uint32_t mis, const int64_t* frs, const int64_t* fre, int64_t* nruns, const int64_t* run_off, void* runs, int64_t cap, int emit);
 // final content: lengths -> exclusive scan -> packed copy
 void tb_launch_final_len(cudaStream_t st, int64_t n, const int64_t* rs0, const int64_t* re0, const int64_t* rs,
                          const int64_t* re, const uint8_t* rewritten, int64_t* len);

@@ -43,7 +43,8 @@ def _ctx(device: int):
 class BatchResult:
     """Results of one batch, copied out of the library's pinned buffers."""
 
-    def __init__(self, params, out: _abi.tb_batch_out, copy_content: bool = True):
+    def __init__(self, params, out: _abi.tb_batch_out, copy_content: bool = True, source=None):
+        """source: (utf8, offsets) of the input column; with TB_OPT_RETURN_CONTENT = 2 the content is gathered from it"""
         n = out.n_docs
         self.n_docs = n
         self.params = list(params)
@@ -63,6 +64,17 @@ class BatchResult:
             self.content_offsets = np.ctypeslib.as_array(out.content_offsets, (n + 1,)).copy()
             nb = int(out.content_bytes)
             self.content = np.ctypeslib.as_array(out.content, (nb,)).copy() if nb else np.zeros(0, np.uint8)
+        self.runs = None
+        self.run_offsets = None
+        if out.content_kind == 2:
+            # runs of the input text: kept as they came, and (unless copy_content is off) gathered into the same
+            # content / content_offsets a TB_OPT_RETURN_CONTENT = 1 call returns
+            self.run_offsets = np.ctypeslib.as_array(out.run_offsets, (n + 1,)).copy()
+            nr = int(out.n_runs)
+            self.runs = (np.frombuffer(C.string_at(out.runs, nr * 8), dtype=np.uint32).reshape(nr, 2).copy() if nr
+                         else np.zeros((0, 2), np.uint32))
+            if copy_content and source is not None:
+                self.content, self.content_offsets = gather_content(out, source[0], source[1])
         self.gpu_ms = out.gpu_ms
         self.gpu_launches = out.gpu_launches
 
@@ -84,6 +96,24 @@ class BatchResult:
             if s == fs:
                 reason = r
         return md, reason
+
+
+def gather_content(out: _abi.tb_batch_out, utf8: np.ndarray, offsets: np.ndarray, select: Optional[np.ndarray] = None,
+                   nthreads: int = 0):
+    """tb_gather_content: the contents of the selected documents (all if ``select`` is None) of a TB_OPT_RETURN_CONTENT = 2
+    result, copied out of the input column.  Returns (content u8, offsets i64)."""
+    lib = _native.lib()
+    n = int(out.n_docs)
+    sel = None if select is None else np.ascontiguousarray(select, dtype=np.uint8)
+    nsel = n if sel is None else int(np.count_nonzero(sel))
+    doff = np.zeros(nsel + 1, np.int64)
+    total = C.c_int64()
+    args = (C.byref(out), utf8.ctypes.data if utf8.size else None, offsets.ctypes.data, 1 if offsets.dtype == np.int64 else 0,
+            None if sel is None else sel.ctypes.data)
+    _native.check(lib.tb_gather_content(*args, None, 0, doff.ctypes.data, C.byref(total), nthreads))
+    dst = np.empty(max(int(total.value), 1), np.uint8)
+    _native.check(lib.tb_gather_content(*args, dst.ctypes.data, int(total.value), doff.ctypes.data, C.byref(total), nthreads))
+    return dst[: int(total.value)], doff
 
 
 class GpuBatchPipeline:
@@ -125,7 +155,7 @@ class GpuBatchPipeline:
         _native.check(self._lib.tb_pipeline_run_batch(self._h, utf8.ctypes.data if utf8.size else None, offsets.ctypes.data,
                                                       1 if offsets.dtype == np.int64 else 0, n, C.byref(out)))
         try:
-            return BatchResult(self.params, out, copy_content)
+            return BatchResult(self.params, out, copy_content, source=(utf8, offsets))
         finally:
             self._lib.tb_batch_out_release(self._h, C.byref(out))
 
