@@ -350,12 +350,11 @@ def main():
         pipe.set_option(_abi.TB_OPT_DECODE_HTML_ENTITIES, 1)
     runs_mode = args.content == "runs" and not args.decode_entities
     pipe.set_option(_abi.TB_OPT_RETURN_CONTENT, 2 if runs_mode else 1)
+    # runs mode: the end-to-end call also rebuilds the content of the kept documents (what the writer of the output
+    # file takes) on host threads inside the library, chunk by chunk behind the device
     gather_threads = max(1, min(8, (os.cpu_count() or 1) // world))
-    lib = pipe._lib
-    # where the kept documents' content is gathered (runs mode): what the writer of the output file would fill
-    kept_buf = np.empty(n_bytes + 64, np.uint8) if runs_mode else None
-    kept_off = np.empty(n_docs + 2, np.int64) if runs_mode else None
-    gather_s = [0.0]
+    if runs_mode:
+        pipe.set_option(_abi.TB_OPT_GATHER_KEPT, gather_threads)
     d_text = holder["t"].cuda(non_blocking=False)
     d_off = off_t.cuda()
     out = _abi.tb_batch_out()
@@ -375,14 +374,10 @@ def main():
         pipe.run_raw(utf8.ctypes.data, off.ctypes.data, True, n_docs, out)
         keep = np.ctypeslib.as_array(out.keep, (n_docs,)) if n_docs else np.zeros(0, np.uint8)
         last_keep["k"] = keep.copy()
-        if out.content_kind == 2:  # the content of the documents that are written out, rebuilt from the input column
-            t0 = time.perf_counter()
-            total = C.c_int64()
-            rc = lib.tb_gather_content(C.byref(out), utf8.ctypes.data, off.ctypes.data, 1, out.keep, kept_buf.ctypes.data, kept_buf.size,
-                                       kept_off.ctypes.data, C.byref(total), gather_threads)
-            assert rc == 0
-            last_keep["kept_bytes"] = int(total.value)
-            gather_s[0] += time.perf_counter() - t0
+        if out.content_kind == 2:  # the content of the documents that are written out was rebuilt from the input column
+            nk = int(out.n_kept)
+            assert nk == int(keep.sum()) and out.kept_offsets[0] == 0
+            last_keep["kept_bytes"] = int(out.kept_offsets[nk])
         r = (out.gpu_launches, out.gpu_ms, int(keep.sum()), content_bytes_back())
         pipe.release(out)
         return r
@@ -391,7 +386,6 @@ def main():
         for _ in range(args.warmup):
             fn()
         pipe.reset_kernel_times()
-        gather_s[0] = 0.0
         barrier()
         sampler = ClockSampler(local_rank)
         if rank == 0:  # one poller for the job: concurrent nvidia-smi queries on every rank disturb the launches
@@ -445,9 +439,7 @@ def main():
     h2d_all = concurrent_probe() if world > 1 and pinned else None
     d2h_all = concurrent_probe(back=True) if world > 1 and pinned else None
     dt_dev, launches, gpu_ms, kept, cbytes, clocks, ktimes = timed(step_device)
-    gather_s[0] = 0.0
     dt_e2e, launches_e, gpu_ms_e, _, cbytes_e, clocks_e, _ = timed(step_host)
-    gather_ms = gather_s[0] / max(args.steps, 1) * 1e3
     # host-side gather of the keep masks onto rank 0, ordered by row group (the only cross-rank traffic of the job)
     t0 = time.perf_counter()
     local, pos = {}, 0
@@ -483,8 +475,9 @@ def main():
             "config": {"workload": WORKLOAD + (" + FineWebQualityFilter" if args.with_fineweb else "") + (" [shipped step order]" if args.order == "shipped" else "") + (" + HTML entity pre-pass" if args.decode_entities else ""), "docs_per_gpu_per_step": n_docs, "bytes_per_gpu_per_step": n_bytes,
                        "sharding": "row groups of %d docs round-robin over ranks, no data-path collective; keep masks gathered on the host (%.3f s, outside the timed region)" % (min(GROUP_DOCS, args.docs), gather_s),
                        "kept_total": int(sum(int(m.sum()) for m in masks)),
-                       "content": ("runs of the input text (TB_OPT_RETURN_CONTENT = 2); e2e gathers the content of the kept documents on the host "
-                                   "inside the timed region (%d threads, %.1f ms per step, %.2f GB)" % (gather_threads, gather_ms, last_keep.get("kept_bytes", 0) / 1e9))
+                       "content": ("runs of the input text (TB_OPT_RETURN_CONTENT = 2); the e2e call also rebuilds the content of the kept documents "
+                                   "on the host from the runs and the input column (TB_OPT_GATHER_KEPT, %d threads, %.2f GB per step), "
+                                   "inside the timed region" % (gather_threads, last_keep.get("kept_bytes", 0) / 1e9))
                                   if runs_mode else "bytes (TB_OPT_RETURN_CONTENT = 1)",
                        "chunk_mb": args.chunk_mb, "host": numa, "l2": "inputs (%.2f GB per step) larger than the 126 MB L2" % (n_bytes / 1e9),
                        "generator_s": round(t_gen, 2)},
@@ -492,7 +485,8 @@ def main():
             "gpu_ms_per_step": gpu_ms / K, "keep_rate": kept / max(n_docs, 1),
             "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": n_bytes + 8 * (n_docs + 1),
                     "d2h_bytes_per_step": n_docs * (2 + stats_bytes) + cbytes_e + 8 * (n_docs + 1), "text_gbs": total_bytes * K / dt_e2e / 1e9,
-                    "ms_per_step": dt_e2e / K * 1e3, "host_gather_ms_per_step": gather_ms if runs_mode else None},
+                    "ms_per_step": dt_e2e / K * 1e3,
+                    "host_gathered_bytes_per_step": last_keep.get("kept_bytes") if runs_mode else None},
             "gpu_launches": launches,
             "roofline": {"bound": "hbm", "kernel": dom_name, "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak if peak else None, "traffic": ncu_traffic(dom_name, alg_bytes_launch), "peak_source": peak_src,

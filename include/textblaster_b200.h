@@ -273,6 +273,12 @@ typedef struct tb_batch_out {
   const tb_run* runs;
   const int64_t* run_offsets;      /* [n_docs + 1] */
   int64_t n_runs;
+  /* TB_OPT_GATHER_KEPT: the content of the documents that passed every step, back to back in input order, and its
+   * n_kept + 1 offsets -- the text column of the output file (src/producer_logic.rs:157-167), built by host threads
+   * from the runs and the caller's input while the device works on the following chunks */
+  const uint8_t* kept_content;
+  const int64_t* kept_offsets;
+  int64_t n_kept;
 } tb_batch_out;
 
 typedef struct tb_ctx tb_ctx;
@@ -334,11 +340,14 @@ enum {
   TB_OPT_VALIDATE_UTF8 = 2,  /* [0] check inputs on the device, TB_ERR_INVALID_UTF8 on failure */
   TB_OPT_CHUNK_BYTES = 3,    /* [1 GiB] largest chunk the batch is processed in (device scratch: ~45 bytes per byte of it) */
   TB_OPT_GENERAL_WORD_PATH = 4, /* [0] testing: run the segment-walking word passes for every document (same results, slower) */
-  TB_OPT_DECODE_HTML_ENTITIES = 5 /* [0] decode HTML entities before the first step, as the reference's reader does with
+  TB_OPT_DECODE_HTML_ENTITIES = 5, /* [0] decode HTML entities before the first step, as the reference's reader does with
                                      html_escape::decode_html_entities (src/pipeline/readers/parquet_reader.rs:178-179): pass the
                                      Arrow buffers of the text column as they are.  The decoded text is the document's content
                                      (content / content_offsets are then returned even without a C4 step).  Parity with the
                                      html-escape crate is unpinned, see textblaster_b200/csrc/tb_entities.cuh */
+  TB_OPT_GATHER_KEPT = 6        /* [0] with TB_OPT_RETURN_CONTENT = 2 and host input: number of host threads that copy the content of the
+                                     kept documents out of the caller's input column (kept_content / kept_offsets of tb_batch_out), chunk
+                                     by chunk behind the device; 0: the caller gathers what it needs itself (tb_gather_content) */
 };
 int tb_pipeline_set_option(tb_pipeline* p, int32_t option, int64_t value);
 

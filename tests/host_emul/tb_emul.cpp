@@ -52,27 +52,39 @@ struct FiberGroup {
   int n = 0, cur = 0, done = 0;
   std::vector<void*> sp;
   std::vector<char*> stacks;
+  std::vector<char> finished;
   void* main_sp = nullptr;
   const std::function<void(int)>* body = nullptr;
+  SimtWarp* warps = nullptr;  // block mode: the warp-level state of fibers 32 w .. 32 w + 31
 };
 FiberGroup* g_fibers = nullptr;  // one group at a time (the harness is single-threaded)
 constexpr size_t kFiberStack = 256 << 10;
+// make fiber `nx` the current one (its warp-level context with it) -- called right before switching to it
+void fiber_select(FiberGroup* g, int nx) {
+  g->cur = nx; simt_lane = nx & 31;
+  if (g->warps) simt_warp = &g->warps[nx >> 5];
+}
+int fiber_next(FiberGroup* g, int me) {
+  int nx = me;
+  do { nx = (nx + 1) % g->n; } while (g->finished[nx] && nx != me);
+  return nx;
+}
 void fiber_entry() {
   FiberGroup* g = g_fibers;
   const int me = g->cur;
   (*g->body)(me);
-  g->done++;
+  g->done++; g->finished[me] = 1;
   void* dummy;
   if (g->done == g->n) tbe_switch(&dummy, g->main_sp);
-  const int nx = (me + 1) % g->n;
-  g->cur = nx; simt_lane = nx;
+  const int nx = fiber_next(g, me);
+  fiber_select(g, nx);
   tbe_switch(&dummy, g->sp[nx]);
   abort();
 }
-// run body(0) .. body(n - 1) as fibers; a barrier inside hands over to the next one
-void run_fibers(int n, const std::function<void(int)>& body) {
+// run body(0) .. body(n - 1) as fibers; a barrier inside hands over to the other fibers until all have arrived
+void run_fibers(int n, const std::function<void(int)>& body, SimtWarp* warps = nullptr) {
   FiberGroup g;
-  g.n = n; g.body = &body; g.sp.resize(n); g.stacks.resize(n);
+  g.n = n; g.body = &body; g.sp.resize(n); g.stacks.resize(n); g.finished.assign(n, 0); g.warps = warps;
   for (int i = 0; i < n; i++) {
     char* st = (char*)malloc(kFiberStack);
     g.stacks[i] = st;
@@ -84,7 +96,7 @@ void run_fibers(int n, const std::function<void(int)>& body) {
     g.sp[i] = q;
   }
   g_fibers = &g;
-  g.cur = 0; simt_lane = 0;
+  fiber_select(&g, 0);
   tbe_switch(&g.main_sp, g.sp[0]);
   g_fibers = nullptr;
   for (char* st : g.stacks) free(st);
@@ -92,8 +104,9 @@ void run_fibers(int n, const std::function<void(int)>& body) {
 }  // namespace
 void simt_fiber_yield() {
   FiberGroup* g = g_fibers;
-  const int me = g->cur, nx = (me + 1) % g->n;
-  g->cur = nx; simt_lane = nx;
+  const int me = g->cur, nx = fiber_next(g, me);
+  if (nx == me) return;
+  fiber_select(g, nx);
   tbe_switch(&g->sp[me], g->sp[nx]);
 }
 namespace {
@@ -118,9 +131,10 @@ void run_warps(int64_t n, const std::function<bool(int64_t)>& pred, const std::f
 void run_blocks(const uint32_t* list, uint32_t count, int nthreads, const std::function<void(int64_t, int)>& fn) {
   SimtBlock blk(nthreads);
   simt_block = &blk;
+  std::vector<SimtWarp> warps((size_t)(nthreads + 31) / 32);  // warp-level collectives inside the CTA (full warps only)
   run_fibers(nthreads, [&](int t) {
     for (uint32_t i = 0; i < count; i++) { fn((int64_t)list[i], t); blk.bar.arrive_and_wait(); }
-  });
+  }, warps.data());
 }
 void run_warps_list(const uint32_t* list, uint32_t count, const std::function<void(int64_t, int)>& fn) {
   SimtWarp warp;

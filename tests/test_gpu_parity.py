@@ -464,6 +464,17 @@ def test_content_as_runs_select_and_fallback():
     for k, w in enumerate(want[:400]):
         assert bytes(got[goff[k]:goff[k + 1]]).decode("utf-8") == w
     assert int(goff[-1]) == sum(len(w.encode("utf-8")) for w in want)
+    # TB_OPT_GATHER_KEPT: the library gathers the kept documents itself, chunk by chunk behind the device
+    p.set_option(_abi.TB_OPT_GATHER_KEPT, 3)
+    for chunk in (1 << 30, 1 << 20):
+        p.set_option(_abi.TB_OPT_CHUNK_BYTES, chunk)
+        p.run_raw(utf8.ctypes.data, off.ctypes.data, True, len(off) - 1, out)
+        nk = int(out.n_kept)
+        assert nk == int(keep.sum())
+        koff = np.ctypeslib.as_array(out.kept_offsets, (nk + 1,)).copy()
+        kbytes = np.ctypeslib.as_array(out.kept_content, (int(koff[-1]),)).copy() if koff[-1] else np.zeros(0, np.uint8)
+        p.release(out)
+        assert np.array_equal(koff, goff) and np.array_equal(kbytes, got)
     p.close()
     for chain, opt in (("c4_sentences", None), ("c4_shipped", _abi.TB_OPT_DECODE_HTML_ENTITIES)):
         q = GpuBatchPipeline(CHAINS[chain])

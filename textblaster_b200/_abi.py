@@ -78,6 +78,7 @@ TB_OPT_VALIDATE_UTF8 = 2
 TB_OPT_CHUNK_BYTES = 3
 TB_OPT_GENERAL_WORD_PATH = 4
 TB_OPT_DECODE_HTML_ENTITIES = 5
+TB_OPT_GATHER_KEPT = 6
 
 
 class tb_c4_params(C.Structure):
@@ -235,6 +236,9 @@ class tb_batch_out(C.Structure):
         ("runs", C.POINTER(tb_run)),
         ("run_offsets", C.POINTER(C.c_int64)),
         ("n_runs", C.c_int64),
+        ("kept_content", C.POINTER(C.c_uint8)),
+        ("kept_offsets", C.POINTER(C.c_int64)),
+        ("n_kept", C.c_int64),
     ]
 
 

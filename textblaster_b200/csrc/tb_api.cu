@@ -9,6 +9,8 @@
 #include <cstdlib>
 #include <cstring>
 #include <chrono>
+#include <condition_variable>
+#include <deque>
 #include <mutex>
 #include <string>
 #include <thread>
@@ -118,8 +120,21 @@ struct StepHost {
   DevBuf sw_dev;
 };
 
+struct PlainBuf {  // grow-only pageable host allocation (not initialised)
+  void* p = nullptr; size_t cap = 0;
+  int ensure(size_t bytes) {
+    if (bytes <= cap) return TB_OK;
+    free(p);
+    p = malloc(bytes + bytes / 8 + 256); cap = p ? bytes + bytes / 8 + 256 : 0;
+    return p ? TB_OK : fail(TB_ERR_OUT_OF_MEMORY, "malloc of " + std::to_string(bytes) + " bytes failed");
+  }
+  void release() { free(p); p = nullptr; cap = 0; }
+  template <class T> T* as() const { return (T*)p; }
+};
+
 struct ResultSet {  // host-side results of one run
   HostBuf keep, failed, content, content_off;
+  PlainBuf kept, kept_off;  // TB_OPT_GATHER_KEPT
   HostBuf stats[TB_MAX_STEPS];
   bool in_use = false;
 };
@@ -139,7 +154,8 @@ struct tb_ctx {
 struct tb_pipeline {
   tb_ctx* ctx = nullptr;
   std::vector<StepHost> steps;
-  int64_t opt_return_content = 1, opt_validate = 0, opt_chunk = 1024ll << 20, opt_debug = 0, opt_decode = 0;
+  int64_t opt_return_content = 1, opt_validate = 0, opt_chunk = 1024ll << 20, opt_debug = 0, opt_decode = 0, opt_gather = 0;
+  std::vector<cudaEvent_t> ev_gather;  // one per chunk of a call (TB_OPT_GATHER_KEPT)
   std::mutex mu;
   // device buffers (grow-only)
   DevBuf text[2], offs[2], packed[2];
@@ -288,6 +304,82 @@ struct Chunk { int64_t d0, d1, b0, b1; };
 inline int64_t off_at(const void* offsets, int is64, int64_t i) {
   return is64 ? ((const int64_t*)offsets)[i] : (int64_t)((const int32_t*)offsets)[i];
 }
+
+// The content of the documents d in [d0, d1) with select[d] != 0 (NULL: all), rebuilt from their runs and the input
+// column: bytes to dst + byte_base (dst may be NULL: sizes only), offsets to dst_off[k_base + 1 ...].  The documents
+// are dealt to T threads in contiguous shares; pass 1 sizes every share, pass 2 writes.  `last_end`: run_offsets[d1]
+// (passed by value: the entry is shared with the next chunk's results, which may be arriving).  Returns through nk / nb
+// the number of documents and bytes written.
+struct GatherSrc { const tb_run* runs; const int64_t* ro; const uint8_t* utf8; const void* offsets; int is64; const uint8_t* select; };
+void gather_range(const GatherSrc& g, int64_t d0, int64_t d1, int64_t last_end, uint8_t* dst, int64_t* dst_off, int64_t k_base,
+                  int64_t byte_base, int T, int64_t* nk, int64_t* nb) {
+  const int64_t n = d1 - d0;
+  T = (int)std::max<int64_t>(1, std::min<int64_t>(T, n / 1024 + 1));
+  std::vector<int64_t> share_docs(T + 1, 0), share_bytes(T + 1, 0);
+  auto ro_end = [&](int64_t d) { return d + 1 == d1 ? last_end : g.ro[d + 1]; };
+  auto each = [&](auto&& fn) {
+    if (T == 1) { fn(0); return; }
+    std::vector<std::thread> th;
+    for (int t = 1; t < T; t++) th.emplace_back(fn, t);
+    fn(0);
+    for (auto& x : th) x.join();
+  };
+  each([&](int t) {
+    int64_t cd = 0, cb = 0;
+    for (int64_t d = d0 + n * t / T, e = d0 + n * (t + 1) / T; d < e; d++) {
+      if (g.select && !g.select[d]) continue;
+      cd++;
+      for (int64_t k = g.ro[d], ke = ro_end(d); k < ke; k++) cb += (int64_t)g.runs[k].end - (int64_t)g.runs[k].begin;
+    }
+    share_docs[t + 1] = cd; share_bytes[t + 1] = cb;
+  });
+  for (int t = 0; t < T; t++) { share_docs[t + 1] += share_docs[t]; share_bytes[t + 1] += share_bytes[t]; }
+  *nk = share_docs[T]; *nb = share_bytes[T];
+  each([&](int t) {
+    int64_t k = k_base + share_docs[t], o = byte_base + share_bytes[t];
+    for (int64_t d = d0 + n * t / T, e = d0 + n * (t + 1) / T; d < e; d++) {
+      if (g.select && !g.select[d]) continue;
+      const uint8_t* src = g.utf8 + off_at(g.offsets, g.is64, d);
+      for (int64_t r = g.ro[d], re = ro_end(d); r < re; r++) {
+        const size_t len = (size_t)g.runs[r].end - g.runs[r].begin;
+        if (dst) {
+          // the next run starts somewhere else in the input: ask for its first lines while this one is copied
+          if (r + 1 < re) { const uint8_t* nx = src + g.runs[r + 1].begin; __builtin_prefetch(nx); __builtin_prefetch(nx + 64); __builtin_prefetch(nx + 128); }
+          memcpy(dst + o, src + g.runs[r].begin, len);
+        }
+        o += (int64_t)len;
+      }
+      dst_off[++k] = o;
+    }
+  });
+}
+
+// TB_OPT_GATHER_KEPT: one thread per call that takes the chunks in order as their runs reach the host (an event per
+// chunk on the d2h stream) and gathers the kept documents' content with T workers, behind the device.
+struct Gatherer {
+  struct Item { int64_t d0, d1, last_end; cudaEvent_t ev; };
+  std::mutex mu; std::condition_variable cv; std::deque<Item> q; bool closed = false;
+  std::thread th;
+  GatherSrc src{}; uint8_t* dst = nullptr; int64_t* dst_off = nullptr; int T = 1, device = 0;
+  int64_t nk = 0, nb = 0; cudaError_t err = cudaSuccess;
+  void start() {
+    th = std::thread([this] {
+      cudaSetDevice(device);
+      for (;;) {
+        Item it;
+        { std::unique_lock<std::mutex> lk(mu); cv.wait(lk, [&] { return closed || !q.empty(); }); if (q.empty()) return; it = q.front(); q.pop_front(); }
+        cudaError_t e = cudaEventSynchronize(it.ev);
+        if (e != cudaSuccess) { err = e; continue; }
+        int64_t k = 0, b = 0;
+        gather_range(src, it.d0, it.d1, it.last_end, dst, dst_off, nk, nb, T, &k, &b);
+        nk += k; nb += b;
+      }
+    });
+  }
+  void push(const Item& it) { { std::lock_guard<std::mutex> lk(mu); q.push_back(it); } cv.notify_one(); }
+  void finish() { if (!th.joinable()) return; { std::lock_guard<std::mutex> lk(mu); closed = true; } cv.notify_one(); th.join(); }
+  ~Gatherer() { finish(); }
+};
 
 ResultSet* acquire_results(tb_pipeline* p) {
   for (auto* r : p->results) if (!r->in_use) { r->in_use = true; return r; }
@@ -473,6 +565,9 @@ int run_impl(tb_pipeline* p, const uint8_t* utf8, const void* offsets, int is64,
   if (sent_mode) content_cap = tb_grown_bytes((int64_t)content_cap, n_docs);
   if (want_content) { if ((rc = rsx->content.ensure(content_cap + 8 * n1 + 64)) || (rc = rsx->content_off.ensure(n1 * 8))) return rc; }
   for (int64_t i = 0; i < n_docs; i++) if (off_at(offsets, is64, i + 1) < off_at(offsets, is64, i)) return fail(TB_ERR_INVALID_ARGUMENT, "offsets must be non-decreasing");
+  const int gather_T = (content_mode == 2 && !device_input) ? (int)std::min<int64_t>(p->opt_gather, 64) : 0;
+  Gatherer gth;  // (joins its thread when this frame is left, whichever way)
+  if (gather_T > 0) { if ((rc = rsx->kept.ensure((size_t)total_bytes + 64)) || (rc = rsx->kept_off.ensure((n1 + 1) * 8))) return rc; }
 
   // chunk plan.  Large chunks cost the least device time (every launch of the chain ends with a tail: about
   // 90 us per launch, measured), but the copy of the first chunk to the device and the copy of the last
@@ -539,11 +634,22 @@ int run_impl(tb_pipeline* p, const uint8_t* utf8, const void* offsets, int is64,
       for (int64_t i = 0; i <= n; i++) h_coff[ch.d0 + i] += content_base;  // chunk-relative -> absolute
       if (tot) CK(cudaMemcpyAsync(h_content + (size_t)content_base * esz, p->packed[buf].p, (size_t)tot * esz, cudaMemcpyDeviceToHost, c->d2h));
       content_base += tot;
+      if (gather_T > 0) {  // the chunk's runs are on their way: its kept documents can be gathered once they have landed
+        while (p->ev_gather.size() <= ci) { cudaEvent_t e; CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); p->ev_gather.push_back(e); }
+        CK(cudaEventRecord(p->ev_gather[ci], c->d2h));
+        gth.push({ch.d0, ch.d1, content_base, p->ev_gather[ci]});
+      }
     }
     CK(cudaEventRecord(p->ev_d2h[buf], c->d2h));
     return TB_OK;
   };
 
+  if (gather_T > 0) {
+    gth.src = GatherSrc{(const tb_run*)h_content, h_coff, utf8 + 0, offsets, is64, h_keep};
+    gth.dst = rsx->kept.as<uint8_t>(); gth.dst_off = rsx->kept_off.as<int64_t>(); gth.dst_off[0] = 0;
+    gth.T = gather_T; gth.device = c->device;
+    gth.start();
+  }
   if (p->opt_validate) CK(cudaMemsetAsync(p->bad.p, 0, 4, c->compute));
   if (!chunks.empty()) if ((rc = enqueue_h2d(0))) return rc;
   for (size_t ci = 0; ci < chunks.size(); ci++) {
@@ -610,6 +716,11 @@ int run_impl(tb_pipeline* p, const uint8_t* utf8, const void* offsets, int is64,
     if (n_docs == 0) h_coff[0] = 0;
     out->content_kind = content_mode;
     if (content_mode == 2) { out->runs = (const tb_run*)h_content; out->run_offsets = h_coff; out->n_runs = content_base; }
+    if (gather_T > 0) {
+      gth.finish();
+      if (gth.err != cudaSuccess) return fail(TB_ERR_CUDA, std::string("gather thread: ") + cudaGetErrorString(gth.err));
+      out->kept_content = rsx->kept.as<uint8_t>(); out->kept_offsets = rsx->kept_off.as<int64_t>(); out->n_kept = gth.nk;
+    }
     else { out->content_rewritten = 1; out->content = h_content; out->content_offsets = h_coff; out->content_bytes = content_base; }
   }
   out->gpu_ms = p->ms_this_run;
@@ -748,7 +859,7 @@ void tb_pipeline_destroy(tb_pipeline* p) {
   for (auto& b : p->stats) { b[0].release(); b[1].release(); }
   for (auto& s : p->steps) s.sw_dev.release();
   for (auto* r : p->results) {
-    r->keep.release(); r->failed.release(); r->content.release(); r->content_off.release();
+    r->keep.release(); r->failed.release(); r->content.release(); r->content_off.release(); r->kept.release(); r->kept_off.release();
     for (auto& s : r->stats) s.release();
     delete r;
   }
@@ -759,6 +870,7 @@ void tb_pipeline_destroy(tb_pipeline* p) {
     if (p->ev_small[i]) cudaEventDestroy(p->ev_small[i]);
   }
   for (auto e : p->ev_pool) cudaEventDestroy(e);
+  for (auto e : p->ev_gather) cudaEventDestroy(e);
   delete p;
 }
 
@@ -772,6 +884,9 @@ int tb_pipeline_set_option(tb_pipeline* p, int32_t option, int64_t value) {
     case TB_OPT_VALIDATE_UTF8: p->opt_validate = value != 0; return TB_OK;
     case TB_OPT_GENERAL_WORD_PATH: p->opt_debug = value != 0 ? TB_DBG_FORCE_WALK : 0; return TB_OK;
     case TB_OPT_DECODE_HTML_ENTITIES: p->opt_decode = value != 0; return TB_OK;
+    case TB_OPT_GATHER_KEPT:
+      if (value < 0) return fail(TB_ERR_INVALID_ARGUMENT, "TB_OPT_GATHER_KEPT: number of host threads, 0 = off");
+      p->opt_gather = value; return TB_OK;
     case TB_OPT_CHUNK_BYTES:
       if (value < (1 << 16)) return fail(TB_ERR_INVALID_ARGUMENT, "chunk size must be at least 64 KiB");
       p->opt_chunk = value; return TB_OK;
@@ -815,47 +930,18 @@ int tb_gather_content(const tb_batch_out* out, const uint8_t* utf8, const void* 
   const int64_t n = out->n_docs;
   const tb_run* runs = out->runs;
   const int64_t* ro = out->run_offsets;
-  // the documents are dealt to the threads in contiguous shares; pass 1 sizes every share, pass 2 writes offsets and bytes
-  int T = nthreads > 0 ? nthreads : (int)std::min<int64_t>(8, n / 32768 + 1);
-  T = std::max(1, std::min(T, 64));
-  std::vector<int64_t> share_docs(T + 1, 0), share_bytes(T + 1, 0);
-  auto each = [&](auto&& fn) {
-    if (T == 1) { fn(0); return; }
-    std::vector<std::thread> th;
-    for (int t = 1; t < T; t++) th.emplace_back(fn, t);
-    fn(0);
-    for (auto& x : th) x.join();
-  };
-  each([&](int t) {
-    int64_t nd = 0, nb = 0;
-    for (int64_t d = n * t / T, e = n * (t + 1) / T; d < e; d++) {
-      if (select && !select[d]) continue;
-      nd++;
-      for (int64_t k = ro[d]; k < ro[d + 1]; k++) nb += (int64_t)runs[k].end - (int64_t)runs[k].begin;
-    }
-    share_docs[t + 1] = nd; share_bytes[t + 1] = nb;
-  });
-  for (int t = 0; t < T; t++) { share_docs[t + 1] += share_docs[t]; share_bytes[t + 1] += share_bytes[t]; }
-  const int64_t acc = share_bytes[T];
-  if (dst_bytes) *dst_bytes = acc;
-  if (dst) {
+  const int T = nthreads > 0 ? std::min(nthreads, 64) : (int)std::min<int64_t>(8, n / 32768 + 1);
+  GatherSrc src{runs, ro, utf8, offsets, offsets_are_i64, select};
+  int64_t nk = 0, acc = 0;
+  dst_offsets[0] = 0;
+  if (dst) {  // sizes first: the destination must hold them
+    std::vector<int64_t> tmp((size_t)n + 2);
+    gather_range(src, 0, n, n ? ro[n] : 0, nullptr, tmp.data(), 0, 0, T, &nk, &acc);
     if (acc > dst_capacity) return fail(TB_ERR_INVALID_ARGUMENT, "tb_gather_content: dst holds " + std::to_string(dst_capacity) + " bytes, " + std::to_string(acc) + " needed");
     if (acc > 0 && !utf8) return fail(TB_ERR_INVALID_ARGUMENT, "tb_gather_content: utf8 is NULL");
   }
-  dst_offsets[0] = 0;
-  each([&](int t) {
-    int64_t k = share_docs[t], o = share_bytes[t];
-    for (int64_t d = n * t / T, e = n * (t + 1) / T; d < e; d++) {
-      if (select && !select[d]) continue;
-      const uint8_t* src = utf8 + off_at(offsets, offsets_are_i64, d);
-      for (int64_t r = ro[d]; r < ro[d + 1]; r++) {
-        const size_t len = (size_t)runs[r].end - runs[r].begin;
-        if (dst) memcpy(dst + o, src + runs[r].begin, len);
-        o += (int64_t)len;
-      }
-      dst_offsets[++k] = o;
-    }
-  });
+  gather_range(src, 0, n, n ? ro[n] : 0, dst, dst_offsets, 0, 0, T, &nk, &acc);
+  if (dst_bytes) *dst_bytes = acc;
   return TB_OK;
 }
 

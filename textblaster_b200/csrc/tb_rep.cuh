@@ -239,6 +239,119 @@ TB_D uint64_t rep_dup_walk(const G& g, IdxT* fo, IdxT* cand, const uint32_t* cbi
   return rep;  // valid on tid 0
 }
 
+// ---- sets of at most 32 elements, one per lane of a warp, compared in registers (no table) --------------------
+// lowest lane holding the same key; lanes that hold no element (holder = false) match nobody.  Keys are packed
+// pairs of 31-bit residues: bits 63 and 31 are clear, so the stand-in of a non-holder equals no key.
+TB_D uint32_t rep_small_first(uint64_t key, bool holder, int lane) {
+  const uint32_t m = simt_match_any64(holder ? key : (0x8000000000000000ull | (uint64_t)(uint32_t)lane));
+  return (uint32_t)(simt_ffs(m) - 1);
+}
+// find_duplicates (text.rs:197-208) over n <= 32 pieces, piece `lane` on lane `lane`
+TB_D void rep_dedup_small(uint64_t h, uint32_t len, uint32_t n, int lane, uint32_t* dup_elems, uint64_t* dup_bytes) {
+  const bool holder = (uint32_t)lane < n;
+  const uint32_t first = rep_small_first(h, holder, lane);  // (every lane takes part in the match)
+  const bool dup = holder && first != (uint32_t)lane;
+  *dup_elems = (uint32_t)simt_popc(simt_ballot(dup));
+  const uint32_t l = dup ? len : 0u;  // 32 lengths below 2^32: two 32-bit sums of 16-bit halves cannot overflow
+  *dup_bytes = (uint64_t)simt_sum(l & 0xFFFFu) + ((uint64_t)simt_sum(l >> 16) << 16);
+}
+// Lines and paragraphs of a document with NL <= 32 line pieces (gopher_rep.rs:80-156), by one warp.  The fold of the
+// pieces into paragraphs runs on every lane alike (uniform loads); lane p keeps paragraph p.
+TB_D void rep_lines_small(const uint64_t* lh, const uint32_t* ll, const uint8_t* lg, uint32_t NL, const uint64_t* powtab, int lane,
+                          uint32_t* line_de, uint64_t* line_db, uint32_t* NPo, uint32_t* para_de, uint64_t* para_db) {
+  rep_dedup_small((uint32_t)lane < NL ? lh[lane] : 0ull, (uint32_t)lane < NL ? ll[lane] : 0u, NL, lane, line_de, line_db);
+  uint32_t NP = 0;
+  uint64_t myh = 0; uint32_t mylen = 0;
+  Hash2 cur; cur.init(); uint32_t curlen = 0;
+  for (uint32_t k = 0; k < NL; k++) {
+    const Hash2 hk = tb_unpack(lh[k]);
+    const uint32_t lk = ll[k];
+    if (k == 0) { cur = hk; curlen = lk; continue; }
+    if (lg[k]) { if (NP == (uint32_t)lane) { myh = cur.pack(); mylen = curlen; } NP++; cur = hk; curlen = lk; }
+    else { cur.push('\n'); cur = tb_hcat(cur, hk, tb_pow_pack(powtab, lk)); curlen += 1 + lk; }
+  }
+  if (NL) { if (NP == (uint32_t)lane) { myh = cur.pack(); mylen = curlen; } NP++; }
+  *NPo = NP;
+  rep_dedup_small(myh, mylen, NP, lane, para_de, para_db);
+}
+// Duplicate n-grams of every configured level from n_from on (text.rs:241-259) when at most 32 word ends are in play:
+// item `lane` is the n-gram that ends with word e (valid: lane < items).  Keys grow to the left in registers; equal
+// keys are found with one match per level; the order-dependent walk over the candidates runs on all lanes alike,
+// the "first item with my key" values staying in the lanes' registers (see rep_dup_walk for the rules).
+// Writes st.dup_bytes / reason bits through `sink(level, bytes)`; returns nothing (valid on every lane).
+template <class Sink>
+TB_D void rep_dup_small(const uint64_t* wh, const uint32_t* woff, const uint64_t* powtab, uint32_t e, uint32_t items, uint32_t n_from,
+                        uint32_t ndup_max, uint64_t dup_levels, int lane, Sink sink) {
+  const uint32_t NONE = 0xFFFFFFFFu;
+  const bool holder = (uint32_t)lane < items;
+  uint32_t dcur = 0;
+  Hash2 h; h.init();
+  for (uint32_t n = n_from; n <= ndup_max; n++) {
+    if (!((dup_levels >> n) & 1ull)) continue;
+    const bool valid = holder && e + 1u >= n;
+    const uint32_t q = valid ? e + 1u - n : 0u;
+    if (valid) {
+      const uint32_t stop = dcur ? e + 1u - dcur : e + 1u;  // the words [stop, e] are in h already
+      Hash2 p = tb_unpack(TB_LDG(wh + q));
+      for (uint32_t j = q + 1; j < stop; j++) p = tb_hcat(p, tb_unpack(TB_LDG(wh + j)), tb_pow_pack(powtab, woff[j + 1] - woff[j]));
+      h = dcur ? tb_hcat(p, h, tb_pow_pack(powtab, woff[e + 1] - woff[stop])) : p;
+    }
+    dcur = n;
+    uint32_t fo = rep_small_first(h.pack(), valid, lane);  // first item with my key
+    uint32_t cm = simt_ballot(valid && fo != (uint32_t)lane);  // candidates, in position order
+    uint64_t rep = 0;
+    if (cm) {
+      const uint32_t len = valid ? woff[e + 1] - woff[q] : 0u;
+      uint32_t skip_until = 0;
+      while (cm) {
+        const int k = simt_ffs(cm) - 1;
+        cm &= cm - 1u;
+        const uint32_t ek = simt_shfl(e, k), qk = ek + 1u - n;
+        const uint32_t c = simt_shfl(fo, k);
+        const uint32_t fc = simt_shfl(fo, (int)(c & 31u));
+        const uint32_t lk = simt_shfl(len, k);
+        if (qk < skip_until) continue;
+        if (fc == c) {  // key seen: hit; first occurrences inside the skipped window lose their mark
+          rep += lk;
+          if (valid && lane > k && e < ek + n && fo == (uint32_t)lane) fo = NONE;
+          skip_until = qk + n;
+        } else if ((uint32_t)lane == c) {
+          fo = c;  // its first occurrence was skipped: this one inserts
+        }
+      }
+    }
+    sink(n, rep);
+  }
+}
+
+// Top n-grams of the levels above `cur` (text.rs:211-238) when at most 32 positions are still in play: position i
+// (its " "-joined key of level cur in h) on lane `lane`, valid for lane < count.  A level's count per key is the size
+// of its match group; the positions whose n-gram repeated stay in play.
+template <class Sink>
+TB_D void rep_top_small(const uint64_t* wh, const uint32_t* woff, const uint64_t* powtab, uint32_t i, Hash2 h, uint32_t count, uint32_t cur,
+                        uint32_t ntop_max, uint64_t top_levels, uint32_t W, int lane, Sink sink) {
+  bool valid = (uint32_t)lane < count;
+  for (uint32_t n = cur + 1; n <= ntop_max; n++) {
+    if (!((top_levels >> n) & 1ull)) continue;
+    const bool v = valid && i + n <= W;
+    if (v) {
+      for (uint32_t j = i + cur; j < i + n; j++) {
+        h.push(' ');
+        h = tb_hcat(h, tb_unpack(TB_LDG(wh + j)), tb_pow_pack(powtab, woff[j + 1] - woff[j]));
+      }
+    }
+    cur = n;
+    const uint32_t m = simt_match_any64(v ? h.pack() : (0x8000000000000000ull | (uint64_t)(uint32_t)lane));
+    const uint32_t c = v ? (uint32_t)simt_popc(m) : 0u;
+    const uint32_t cmax = simt_max(c);
+    uint64_t val = 0;
+    if (cmax > 1) val = (uint64_t)simt_max((v && c == cmax) ? woff[i + n] - woff[i] + n - 1 : 0u) * cmax;  // key length = bytes + (n - 1) spaces
+    sink(n, val);
+    valid = v && c > 1;
+    if (cmax <= 1) break;  // nothing repeats: the higher levels stay 0
+  }
+}
+
 struct RepArrays {
   // per-document working arrays (shared memory for tiers S/M, global work area for tier L)
   uint64_t* H;     // [cap] current n-gram key hash / paragraph hashes
@@ -268,8 +381,24 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
   const double text_char_len = (double)(gd.char_len ? gd.char_len : 1);
   uint32_t reasons = 0;
 
-  // ---- lines (gopher_rep.rs:120-156)
-  uint32_t de; uint64_t db;
+  // ---- lines (gopher_rep.rs:120-156) and paragraphs (:80-116)
+  uint32_t de = 0; uint64_t db = 0;
+  uint32_t NP = 0;
+  if (NL <= 32u) {
+    // few pieces: the first warp compares them in registers (no table, no barrier); only thread 0 needs the results
+    if (g.tid < 32) {
+      uint32_t pde; uint64_t pdb;
+      rep_lines_small(lh, ll, lg, NL, a.uc.powtab, g.tid, &de, &db, &NP, &pde, &pdb);
+      st.n_lines = NL; st.line_dup_elems = de; st.line_dup_bytes = db;
+      st.n_paras = NP; st.para_dup_elems = pde; st.para_dup_bytes = pdb;
+      const double r1 = (double)de / (double)(NL ? NL : 1u), r2 = (double)db / text_char_len;
+      const double q1 = (double)pde / (double)(NP ? NP : 1u), q2 = (double)pdb / text_char_len;
+      if ((cfg.has & TB_GR_HAS_DUP_PARA_FRAC) && q1 > cfg.dup_para_frac) reasons |= TB_GR_REASON_DUP_PARA_FRAC;
+      if ((cfg.has & TB_GR_HAS_DUP_PARA_CHAR_FRAC) && q2 > cfg.dup_para_char_frac) reasons |= TB_GR_REASON_DUP_PARA_CHAR_FRAC;
+      if ((cfg.has & TB_GR_HAS_DUP_LINE_FRAC) && r1 > cfg.dup_line_frac) reasons |= TB_GR_REASON_DUP_LINE_FRAC;
+      if ((cfg.has & TB_GR_HAS_DUP_LINE_CHAR_FRAC) && r2 > cfg.dup_line_char_frac) reasons |= TB_GR_REASON_DUP_LINE_CHAR_FRAC;
+    }
+  } else {
   rep_dedup(g, tab, lh, ll, NL, &de, &db);
   st.n_lines = NL; st.line_dup_elems = de; st.line_dup_bytes = db;
   {
@@ -279,7 +408,6 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
   }
   // ---- paragraphs (gopher_rep.rs:80-116): fold the ordered line pieces; a single '\n' joins lines
   // inside a paragraph, a run of >= 2 separates paragraphs.
-  uint32_t NP = 0;
   if (g.tid == 0) {
     Hash2 cur; cur.init(); uint32_t curlen = 0;
     for (uint32_t k = 0; k < NL; k++) {
@@ -300,6 +428,7 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
     if ((cfg.has & TB_GR_HAS_DUP_PARA_CHAR_FRAC) && r2 > cfg.dup_para_char_frac) reasons |= TB_GR_REASON_DUP_PARA_CHAR_FRAC;
   }
   g.sync();
+  }
 
   // ---- n-grams (gopher_rep.rs:159-196)
   uint32_t ntop_max = 0, ndup_max = 0;
@@ -332,6 +461,21 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
     uint32_t cur = 0;       // level of the keys in A.H (0: none yet)
     for (uint32_t n = 1; n <= ntop_max && count; n++) {
       if (!((top_levels >> n) & 1ull)) continue;  // only configured levels run a pass; the keys jump levels in registers
+      if (pruned && count <= 32u) {
+        // few positions left: the first warp takes them into registers and finishes the list on its own
+        uint32_t i = 0; Hash2 h; h.init();
+        if ((uint32_t)g.tid < count) { i = (uint32_t)list[g.tid]; h = tb_unpack(A.H[i]); }
+        g.sync();  // (the working arrays are free for what follows)
+        if (g.tid < 32)
+          rep_top_small(wh, woff, a.uc.powtab, i, h, count, cur, ntop_max, top_levels, W, g.tid, [&](uint32_t lvl, uint64_t v) {
+            for (int k = 0; k < cfg.n_top; k++) {
+              if (cfg.top_n[k] != lvl) continue;
+              st.top_bytes[k] = v;
+              if ((double)v / text_char_len > cfg.top_frac[k]) reasons |= 1u << (TB_GR_REASON_TOP_SHIFT + k);
+            }
+          });
+        break;
+      }
       const uint32_t cn = W - n + 1;
       const uint32_t T = rep_tab_size(count);
       for (uint32_t i = g.tid; i < T; i += g.size()) tab[i] = EMPTY;
@@ -444,6 +588,19 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
         }
       }
       if (items == 0) continue;  // nothing can repeat at this level: dup_bytes stays 0
+      if (pruned && items <= 32u) {
+        // few word ends in play: the first warp takes them into registers and finishes the list on its own
+        if (g.tid < 32)
+          rep_dup_small(wh, woff, a.uc.powtab, (uint32_t)g.tid < items ? (uint32_t)list[g.tid] : 0u, items, n, ndup_max, dup_levels, g.tid,
+                        [&](uint32_t lvl, uint64_t v) {
+                          for (int k = 0; k < cfg.n_dup; k++) {
+                            if (cfg.dup_n[k] != lvl) continue;
+                            st.dup_bytes[k] = v;
+                            if ((double)v / text_char_len > cfg.dup_frac[k]) reasons |= 1u << (TB_GR_REASON_DUP_SHIFT + k);
+                          }
+                        });
+        break;
+      }
       const uint32_t T = rep_tab_size(items);
       // one sweep: clear the table, bring the keys from level dcur to level n (new words go in front)
 #pragma unroll 2

@@ -21,6 +21,8 @@ TB_D uint32_t simt_sum(uint32_t v) { return __reduce_add_sync(SIMT_FULL, v); }
 TB_D uint32_t simt_or(uint32_t v) { return __reduce_or_sync(SIMT_FULL, v); }
 TB_D bool simt_any(bool p) { return __any_sync(SIMT_FULL, p) != 0; }
 TB_D uint32_t simt_ballot(bool p) { return __ballot_sync(SIMT_FULL, p); }
+TB_D uint32_t simt_match_any64(uint64_t v) { return __match_any_sync(SIMT_FULL, (unsigned long long)v); }  // lanes holding the same value
+TB_D uint32_t simt_max(uint32_t v) { return __reduce_max_sync(SIMT_FULL, v); }
 TB_D void simt_sync() { __syncwarp(); }
 TB_D uint32_t simt_cas(uint32_t* a, uint32_t cmp, uint32_t val) { return atomicCAS(a, cmp, val); }
 TB_D uint32_t simt_atomic_add(uint32_t* a, uint32_t v) { return atomicAdd(a, v); }
@@ -36,21 +38,30 @@ TB_D int simt_ffs(uint32_t v) { return __ffs(v); }
 
 #include <cstring>
 
-// Defined by the harness: suspends the calling lane and runs every other lane of the group up to its next
-// barrier.  All lanes execute the same sequence of barriers (full-mask collectives only), so this is a barrier.
+// Defined by the harness: suspends the calling fiber and runs the next one of the group.
 void simt_fiber_yield();
-struct SimtBar { void arrive_and_wait() { simt_fiber_yield(); } };
+// A counting barrier over n fibers of one host thread: the last to arrive opens it, the others hand over until then.
+// (Groups of different size -- the warps of a CTA and the CTA itself -- may synchronise independently.)
+struct SimtBar {
+  int n, count = 0, gen = 0;
+  explicit SimtBar(int n_) : n(n_) {}
+  void arrive_and_wait() {
+    const int g = gen;
+    if (++count == n) { count = 0; gen++; }
+    else while (gen == g) simt_fiber_yield();
+  }
+};
 struct SimtWarp {
-  SimtBar bar;
+  SimtBar bar{32};
   uint64_t box[32];
 };
 extern thread_local SimtWarp* simt_warp;
 extern thread_local int simt_lane;
-struct SimtBlock {  // one emulated CTA of n threads (block-level collectives only)
+struct SimtBlock {  // one emulated CTA of n threads
   int n;
   SimtBar bar;
   uint64_t box[1024];
-  explicit SimtBlock(int n_) : n(n_) {}
+  explicit SimtBlock(int n_) : n(n_), bar(n_) {}
 };
 extern thread_local SimtBlock* simt_block;
 
@@ -85,6 +96,24 @@ inline uint32_t simt_or(uint32_t v) {
   return s;
 }
 inline bool simt_any(bool p) { return simt_or(p ? 1u : 0u) != 0; }
+inline uint32_t simt_match_any64(uint64_t v) {
+  SimtWarp* w = simt_warp;
+  w->box[simt_lane] = v;
+  w->bar.arrive_and_wait();
+  uint32_t m = 0;
+  for (int i = 0; i < 32; i++) if (w->box[i] == v) m |= 1u << i;
+  w->bar.arrive_and_wait();
+  return m;
+}
+inline uint32_t simt_max(uint32_t v) {
+  SimtWarp* w = simt_warp;
+  w->box[simt_lane] = v;
+  w->bar.arrive_and_wait();
+  uint32_t s = 0;
+  for (int i = 0; i < 32; i++) s = (uint32_t)w->box[i] > s ? (uint32_t)w->box[i] : s;
+  w->bar.arrive_and_wait();
+  return s;
+}
 inline uint32_t simt_ballot(bool p) { return simt_or(p ? (1u << simt_lane) : 0u); }
 inline void simt_sync() { simt_warp->bar.arrive_and_wait(); }
 inline uint32_t simt_cas(uint32_t* a, uint32_t cmp, uint32_t val) {
