@@ -361,7 +361,7 @@ struct Gatherer {
   std::mutex mu; std::condition_variable cv; std::deque<Item> q; bool closed = false;
   std::thread th;
   GatherSrc src{}; uint8_t* dst = nullptr; int64_t* dst_off = nullptr; int T = 1, device = 0;
-  int64_t nk = 0, nb = 0; cudaError_t err = cudaSuccess;
+  int64_t nk = 0, nb = 0; cudaError_t err = cudaSuccess; double busy_ms = 0;
   void start() {
     th = std::thread([this] {
       cudaSetDevice(device);
@@ -371,7 +371,9 @@ struct Gatherer {
         cudaError_t e = cudaEventSynchronize(it.ev);
         if (e != cudaSuccess) { err = e; continue; }
         int64_t k = 0, b = 0;
+        const auto t0 = std::chrono::steady_clock::now();
         gather_range(src, it.d0, it.d1, it.last_end, dst, dst_off, nk, nb, T, &k, &b);
+        busy_ms += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
         nk += k; nb += b;
       }
     });
@@ -716,12 +718,13 @@ int run_impl(tb_pipeline* p, const uint8_t* utf8, const void* offsets, int is64,
     if (n_docs == 0) h_coff[0] = 0;
     out->content_kind = content_mode;
     if (content_mode == 2) { out->runs = (const tb_run*)h_content; out->run_offsets = h_coff; out->n_runs = content_base; }
+    else { out->content_rewritten = 1; out->content = h_content; out->content_offsets = h_coff; out->content_bytes = content_base; }
     if (gather_T > 0) {
       gth.finish();
+      if (trace) fprintf(stderr, "[tb] %.2f ms: kept documents gathered (%.1f ms of gathering in all)\n", since(), gth.busy_ms);
       if (gth.err != cudaSuccess) return fail(TB_ERR_CUDA, std::string("gather thread: ") + cudaGetErrorString(gth.err));
       out->kept_content = rsx->kept.as<uint8_t>(); out->kept_offsets = rsx->kept_off.as<int64_t>(); out->n_kept = gth.nk;
     }
-    else { out->content_rewritten = 1; out->content = h_content; out->content_offsets = h_coff; out->content_bytes = content_base; }
   }
   out->gpu_ms = p->ms_this_run;
   out->gpu_launches = p->launches_this_run;

@@ -22,6 +22,16 @@ Per code point we pack one u16 ("cinfo"):
   bit 15     has a lowercase mapping different from itself (str::to_lowercase)
 
 Layout: 2-stage trie, stage1[cp >> 8] -> block index, stage2[block * 256 + (cp & 255)].
+
+--colon {cldr-root,uax29}: Word_Break of U+003A COLON, U+FE55 SMALL COLON and U+FF1A FULLWIDTH COLON.
+  uax29      MidLetter, as UAX #29's WordBreakProperty.txt lists them ("a:b" is one word).
+  cldr-root  Other (the default here).  Since CLDR 42 / ICU 72 the ROOT word-break rules take these three out of MidLetter
+             ("$MidLetter = [\p{Word_Break = MidLetter} - [\: \uFE55 \uFF1A]];" in ICU's brkitr/rules/word.txt) and only the
+             Finnish and Swedish tailorings keep them; ICU4X carries exactly those two locale overrides for its word
+             segmenter, which only makes sense if its root data excludes the colon.  The reference calls
+             WordSegmenter::new_auto() without a locale (src/utils/text.rs:107), i.e. root: "foo:bar" is foo | : | bar, two
+             words.  Neither ICU4X nor CLDR data is in this image, so this is the best-evidence setting, not a pinned one
+             (DESIGN.md section 2); the ICU4C 71 cross-check (Unicode 14, before the change) cannot see it either way.
 """
 import os
 import subprocess
@@ -71,6 +81,10 @@ for my $i (0..$#$list) {
 
 
 def main():
+    import argparse
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--colon", default="cldr-root", choices=["cldr-root", "uax29"])
+    args = ap.parse_args()
     out = subprocess.run(["perl", "-e", PERL], capture_output=True, text=True, check=True).stdout
     N = 0x110000
     wb = [0] * N
@@ -131,6 +145,10 @@ def main():
         sb[cp] = SB.index("OLetter")
         flags["alpha"][cp] = 1
         flags["complex"][cp] = 1
+    assert all(wb[cp] == WB.index("MidLetter") for cp in (0x3A, 0xFE55, 0xFF1A))
+    if args.colon == "cldr-root":
+        for cp in (0x3A, 0xFE55, 0xFF1A):
+            wb[cp] = WB.index("Other")
     # sanity anchors from SURVEY.md Appendix B
     assert sum(1 for c in range(N) if flags["ws"][c]) == 25
     assert sum(1 for c in range(N) if wb[c] == WB.index("WSegSpace")) == 14
@@ -196,6 +214,7 @@ def main():
         w("// GENERATED by tools/gen_unicode_tables.py -- do not edit.\n")
         w("// Unicode 15.0.0 (perl Unicode::UCD) + 15.1 CJK Ext-I patch. See the generator for the bit layout.\n")
         w("#define TB_UC_VERSION \"15.1 (15.0.0 + ExtI patch)\"\n")
+        w("#define TB_UC_COLON_MIDLETTER %d  // 0: CLDR root tailoring (colon is Word_Break=Other), 1: plain UAX #29\n" % (0 if args.colon == "cldr-root" else 1))
         for i, n in enumerate(WB):
             w(f"#define TB_WB_{n.upper()} {i}\n")
         for i, n in enumerate(SB):
