@@ -20,7 +20,7 @@ WORDS = [
     "Mr.", "10,000", "...", "…", "-", "•", "#", "[1]", "[2, 3]", "[4,5,6]", "[7,", "[a]", "[١٢]",
     "(see)", "\"quoted\"", "end.", "stop!", "why?", "ok”", "caf\xe9", "na\xefve", "Жук",
     "ΣΟΦΟΣ", "İstanbul", "Kelvin", "TERMS OF USE", "Use Of Cookies", "JavaScript",
-    "LOREM IPSUM", "cooKie policy", "a:b", "1.5.2", "it's", "rock'n'roll", "\U0001f1e9\U0001f1f0\U0001f1e9",
+    "LOREM IPSUM", "cooKie policy", "a:b", "foo:bar", "a:b:c", "12:30", "http://x", "key:value", "1.5.2", "it's", "rock'n'roll", "\U0001f1e9\U0001f1f0\U0001f1e9",
 ]
 
 
