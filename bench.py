@@ -277,6 +277,145 @@ def run_reference(args, rank, world):
     emit(line)
 
 
+def run_config4(args, rank, local_rank, world):
+    """BASELINE.json configs[3]: the quality chain over a stream of row groups of 65 536 documents dealt round-robin to
+    the ranks, through the product's streaming runner (textblaster_b200/runner.py): several pipelines
+    per GPU fed from pinned host buffers, results drained in row-group order, kept documents' content rebuilt on the host.
+    The CPU generator sustains a small fraction of what one GPU consumes, so the row groups a rank streams are generated
+    before the timed region (a pool of distinct groups in pinned memory; --docs-total beyond the pool walks it again: every
+    pass copies the text to the device anew, nothing stays resident between groups)."""
+    import torch
+    import torch.distributed as dist
+
+    from textblaster_b200 import _abi, shard, synth
+    from textblaster_b200.executor import GpuBatchPipeline
+    from textblaster_b200.runner import RowGroup, StreamingRunner
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (no CPU fallback)")
+    torch.cuda.set_device(local_rank)
+    numa = pin_to_gpu_socket(torch, local_rank) if world > 1 else "single process, not pinned"
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    steps = shipped_chain(args.with_fineweb, args.order)
+    pool_groups = args.pool_groups
+    total_groups = max(world, (args.docs_total or pool_groups * world * GROUP_DOCS) // GROUP_DOCS)
+    mine = shard.groups_of_rank(total_groups, rank, world)  # round-robin: rank r takes groups r, r + world, ...
+    threads = max(1, (os.cpu_count() or 1) // world)
+    # ---- the pool: this rank's first `pool_groups` row groups, each generated from its own document indices
+    t0 = time.perf_counter()
+    pool = []
+    for k in range(min(pool_groups, len(mine))):
+        g = mine[k]
+        holder = {}
+
+        def pinned(nbytes, holder=holder):
+            holder["t"] = torch.empty(max(nbytes, 1), dtype=torch.uint8, pin_memory=True)
+            return holder["t"].numpy()
+
+        u, o = synth.generate(GROUP_DOCS, seed=synth.BASE_SEED + 4, first_index=g * GROUP_DOCS, nthreads=threads, out=pinned)
+        pool.append((u, o, holder))
+    gen_s = time.perf_counter() - t0
+    pool_bytes = sum(int(o[-1]) for _, o, _ in pool)
+    gen_gbs = pool_bytes / gen_s / 1e9
+
+    gather_threads = args.gather_threads or max(1, min(8, threads))
+    runner = StreamingRunner(lambda: GpuBatchPipeline(steps, device=local_rank), pipelines=args.pipelines,
+                             copy_stats=False, gather_kept=gather_threads if any(p.CTYPE == _abi.TB_STEP_C4_QUALITY for p in steps) else 0)
+
+    def source(n_groups):
+        for k in range(n_groups):
+            u, o, _ = pool[k % len(pool)]
+            yield RowGroup(mine[k], u, o)
+
+    # warm-up: buffers of every pipeline grow to their size, kernels are loaded
+    runner.run(source(min(len(mine), max(2 * args.pipelines, 2))))
+    kept_by_group = {}
+
+    def sink(index, s):
+        kept_by_group[index] = int(s.keep.sum())
+
+    barrier()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    t0 = time.perf_counter()
+    tot = runner.run(source(len(mine)), sink)
+    barrier()
+    dt = time.perf_counter() - t0
+    clocks = sampler.stop()
+    t = torch.tensor([dt], dtype=torch.float64, device="cuda")
+    agg = torch.tensor([tot.docs, tot.bytes, tot.kept, tot.kept_bytes, tot.gpu_launches], dtype=torch.int64, device="cuda")
+    gms = torch.tensor([tot.gpu_ms, tot.source_wait_s], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(agg, op=dist.ReduceOp.SUM)
+        dist.all_reduce(gms, op=dist.ReduceOp.MAX)
+    dt = float(t.item())
+    docs, nbytes, kept, kept_bytes, launches = (int(x) for x in agg.tolist())
+    # ---- parity on this rank's first row groups (rank 0): the same groups through a fresh pipeline with statistics, and the oracle
+    parity = None
+    if rank == 0 and not args.no_cpu_baseline:
+        import oracle
+        from parity_util import executed
+
+        check = min(args.parity_groups, len(pool))
+        pipe = GpuBatchPipeline(steps, device=local_rank)
+        mism = values = ndocs = 0
+        for k in range(check):
+            u, o, _ = pool[k]
+            res = pipe.run_packed(u, o)
+            ores = oracle.OraclePipeline(steps).run_packed(u, o.astype(np.int64), nthreads=os.cpu_count() or 1)
+            mism += int(((res.keep != ores.keep) | (res.failed_step != ores.failed_step)).sum())
+            values += 2 * res.n_docs
+            for s_i in range(len(steps)):
+                ran = executed(ores.failed_step, s_i)
+                for name in res.stats[s_i].dtype.names:
+                    ne = res.stats[s_i][name][ran] != ores.stats[s_i][name][ran]
+                    mism += int((ne.any(axis=1) if ne.ndim > 1 else ne).sum())
+                    values += int(ran.sum())
+            if res.content is not None:
+                ob, oo = ores.content_packed()
+                mism += 0 if (np.array_equal(res.content_offsets, oo) and np.array_equal(res.content, ob)) else 1
+                values += res.n_docs
+            mism += 0 if kept_by_group.get(mine[k]) == int(ores.keep.sum()) else 1  # what the streamed run reported for this group
+            ndocs += res.n_docs
+        pipe.close()
+        parity = {"docs": ndocs, "values": values, "mismatches": mism,
+                  "checked": "first %d row groups of rank 0: GPU vs oracle (keep, failed_step, statistics, content) and the streamed run's kept count" % check}
+    runner.close()
+    if rank == 0:
+        rate = docs / dt
+        line = {"metric": METRIC, "value": rate, "unit": UNIT, "n_gpus": world, "steps": 1, "warmup": 1, "ms_per_step": dt * 1e3,
+                "higher_is_better": True, "scaling": "weak" if not args.docs_total else "strong", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+                "config": {"workload": "full quality chain (%s order) over a stream of row groups of %d synthetic documents dealt round-robin to the ranks "
+                                       "(BASELINE.json configs[3]); %d documents in all, %d row groups per rank from a pool of %d distinct pre-generated "
+                                       "groups per rank (pinned host memory)" % (args.order, GROUP_DOCS, docs, len(mine), len(pool)),
+                           "runner": "textblaster_b200/runner.py: %d pipelines per GPU, chunk ramps off, content as runs + kept documents gathered on the host (%d threads per pipeline)" % (args.pipelines, gather_threads),
+                           "generator": "tb_synth on %d host threads sustains %.2f GB/s per rank (measured while filling the pool): far below one GPU's intake, so generation is outside the timed region" % (threads, gen_gbs),
+                           "host": numa, "l2": "every row group (%.0f MB) is copied from the host again each time it is streamed" % (pool_bytes / max(len(pool), 1) / 1e6)},
+                "text_gbs": nbytes / dt / 1e9, "total_docs_per_step": docs, "keep_rate": kept / max(docs, 1), "kept_bytes": kept_bytes,
+                "gpu_ms_per_step": float(gms[0].item()), "source_wait_s_max": float(gms[1].item()),
+                "e2e": {"value": rate, "unit": UNIT, "h2d_bytes_per_step": nbytes + 8 * docs, "d2h_bytes_per_step": None, "text_gbs": nbytes / dt / 1e9,
+                        "ms_per_step": dt * 1e3, "host_gathered_bytes_per_step": kept_bytes},
+                "gpu_launches": launches, "clocks": clocks}
+        if parity is not None:
+            line["parity"] = parity
+        emit(line)
+        if parity and parity["mismatches"]:
+            sys.exit(1)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -291,6 +430,12 @@ def main():
     ap.add_argument("--content", default="runs", choices=["runs", "bytes"],
                     help="how C4's rewritten content comes back: runs of the input text (TB_OPT_RETURN_CONTENT = 2; the end-to-end step "
                          "then gathers the kept documents' content on the host, inside the timed region) or the bytes themselves (1)")
+    ap.add_argument("--config", type=int, default=2, choices=[2, 3, 4], help="BASELINE.json configuration: 2 (headline, default), 3 (n-gram sweep on long documents), 4 (streamed row groups)")
+    ap.add_argument("--docs-total", type=int, default=0, help="config 4: documents over all ranks (0: one pass over every rank's pool)")
+    ap.add_argument("--pool-groups", type=int, default=16, help="config 4: distinct row groups generated per rank before the timed region")
+    ap.add_argument("--pipelines", type=int, default=3, help="config 4: pipelines (and host threads) per GPU")
+    ap.add_argument("--parity-groups", type=int, default=2, help="config 4: row groups of rank 0 checked against the oracle")
+    ap.add_argument("--gather-threads", type=int, default=0, help="host threads of TB_OPT_GATHER_KEPT (0: min(8, cpus / ranks))")
     ap.add_argument("--with-fineweb", action="store_true",
                     help="append FineWebQualityFilter (SURVEY 8(f) row 3) to the chain; not the headline workload")
     args = ap.parse_args()
@@ -302,6 +447,11 @@ def main():
 
     if args.impl == "reference":
         run_reference(args, rank, world)
+        return
+    if args.config == 4:
+        if args.order == "baseline" and "--order" not in sys.argv:
+            args.order = "shipped"  # config 4 is the shipped pipeline_config.yaml chain unless asked otherwise
+        run_config4(args, rank, local_rank, world)
         return
 
     import torch
@@ -352,7 +502,7 @@ def main():
     pipe.set_option(_abi.TB_OPT_RETURN_CONTENT, 2 if runs_mode else 1)
     # runs mode: the end-to-end call also rebuilds the content of the kept documents (what the writer of the output
     # file takes) on host threads inside the library, chunk by chunk behind the device
-    gather_threads = max(1, min(8, (os.cpu_count() or 1) // world))
+    gather_threads = args.gather_threads or max(1, min(8, (os.cpu_count() or 1) // world))
     if runs_mode:
         pipe.set_option(_abi.TB_OPT_GATHER_KEPT, gather_threads)
     d_text = holder["t"].cuda(non_blocking=False)

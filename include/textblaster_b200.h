@@ -345,6 +345,10 @@ enum {
                                      Arrow buffers of the text column as they are.  The decoded text is the document's content
                                      (content / content_offsets are then returned even without a C4 step).  Parity with the
                                      html-escape crate is unpinned, see textblaster_b200/csrc/tb_entities.cuh */
+  TB_OPT_CHUNK_RAMP = 7,        /* [1] chunk sizes ramp up at the start of a batch and down at its end, which hides the first copy to the
+                                     device and the last copy back behind kernels (one batch at a time).  0: every chunk has the full
+                                     size -- for callers that keep several pipelines of one context busy with a stream of batches
+                                     (textblaster_b200/runner.py), where another batch's kernels cover the copies */
   TB_OPT_GATHER_KEPT = 6        /* [0] with TB_OPT_RETURN_CONTENT = 2 and host input: number of host threads that copy the content of the
                                      kept documents out of the caller's input column (kept_content / kept_offsets of tb_batch_out), chunk
                                      by chunk behind the device; 0: the caller gathers what it needs itself (tb_gather_content) */

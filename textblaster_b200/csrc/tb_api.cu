@@ -16,6 +16,10 @@
 #include <thread>
 #include <vector>
 
+#if defined(__x86_64__)
+#include <emmintrin.h>
+#endif
+
 #include "tb_hostutil.h"
 #include "tb_kernels.cuh"
 #include "unicode_tables.inc"
@@ -154,7 +158,7 @@ struct tb_ctx {
 struct tb_pipeline {
   tb_ctx* ctx = nullptr;
   std::vector<StepHost> steps;
-  int64_t opt_return_content = 1, opt_validate = 0, opt_chunk = 1024ll << 20, opt_debug = 0, opt_decode = 0, opt_gather = 0;
+  int64_t opt_return_content = 1, opt_validate = 0, opt_chunk = 1024ll << 20, opt_debug = 0, opt_decode = 0, opt_gather = 0, opt_ramp = 1;
   std::vector<cudaEvent_t> ev_gather;  // one per chunk of a call (TB_OPT_GATHER_KEPT)
   std::mutex mu;
   // device buffers (grow-only)
@@ -305,6 +309,47 @@ inline int64_t off_at(const void* offsets, int is64, int64_t i) {
   return is64 ? ((const int64_t*)offsets)[i] : (int64_t)((const int32_t*)offsets)[i];
 }
 
+// Sequential writer for the gathered content.  The runs are short (hundreds of bytes) and the destination is written once
+// and not read again soon: plain stores would first fetch every destination line (read for ownership), a third of the
+// memory traffic of the gather.  So the bytes are collected in a small cache-resident block and leave it as whole
+// 64-byte lines with streaming stores; only the partial lines at the two ends of a thread's range are copied plainly.
+struct StreamWriter {
+  uint8_t* dst;          // destination base
+  int64_t pos;           // next offset to write
+  int fill = 0, cap = 0; // bytes in buf / bytes buf may take before the next flush
+  alignas(64) uint8_t buf[4096];
+  StreamWriter(uint8_t* d, int64_t o) : dst(d), pos(o) {
+    const int head = (int)((64 - ((uintptr_t)(d + o) & 63)) & 63);  // up to the next line boundary: plain
+    cap = head ? head : (int)sizeof buf;
+  }
+  void flush() {
+    uint8_t* q = dst + pos;
+#if defined(__x86_64__)
+    if (((uintptr_t)q & 63) == 0) {
+      const int lines = fill & ~63;
+      for (int k = 0; k < lines; k += 16) _mm_stream_si128((__m128i*)(q + k), _mm_load_si128((const __m128i*)(buf + k)));
+      if (fill > lines) memcpy(q + lines, buf + lines, (size_t)(fill - lines));
+    } else
+#endif
+      memcpy(q, buf, (size_t)fill);
+    pos += fill; fill = 0; cap = (int)sizeof buf;
+  }
+  void write(const uint8_t* src, size_t len) {
+    while (len) {
+      const size_t k = std::min(len, (size_t)(cap - fill));
+      memcpy(buf + fill, src, k);
+      fill += (int)k; src += k; len -= k;
+      if (fill == cap) flush();
+    }
+  }
+  void finish() {
+    if (fill) flush();
+#if defined(__x86_64__)
+    _mm_sfence();
+#endif
+  }
+};
+
 // The content of the documents d in [d0, d1) with select[d] != 0 (NULL: all), rebuilt from their runs and the input
 // column: bytes to dst + byte_base (dst may be NULL: sizes only), offsets to dst_off[k_base + 1 ...].  The documents
 // are dealt to T threads in contiguous shares; pass 1 sizes every share, pass 2 writes.  `last_end`: run_offsets[d1]
@@ -337,6 +382,7 @@ void gather_range(const GatherSrc& g, int64_t d0, int64_t d1, int64_t last_end, 
   *nk = share_docs[T]; *nb = share_bytes[T];
   each([&](int t) {
     int64_t k = k_base + share_docs[t], o = byte_base + share_bytes[t];
+    StreamWriter w(dst, o);
     for (int64_t d = d0 + n * t / T, e = d0 + n * (t + 1) / T; d < e; d++) {
       if (g.select && !g.select[d]) continue;
       const uint8_t* src = g.utf8 + off_at(g.offsets, g.is64, d);
@@ -345,12 +391,13 @@ void gather_range(const GatherSrc& g, int64_t d0, int64_t d1, int64_t last_end, 
         if (dst) {
           // the next run starts somewhere else in the input: ask for its first lines while this one is copied
           if (r + 1 < re) { const uint8_t* nx = src + g.runs[r + 1].begin; __builtin_prefetch(nx); __builtin_prefetch(nx + 64); __builtin_prefetch(nx + 128); }
-          memcpy(dst + o, src + g.runs[r].begin, len);
+          w.write(src + g.runs[r].begin, len);
         }
         o += (int64_t)len;
       }
       dst_off[++k] = o;
     }
+    if (dst) w.finish();
   });
 }
 
@@ -581,7 +628,9 @@ int run_impl(tb_pipeline* p, const uint8_t* utf8, const void* offsets, int is64,
   int64_t max_n = 0, max_b = 0;
   {
     const int64_t C = std::max<int64_t>(p->opt_chunk, 1);
-    const std::vector<int64_t> targets = tb_chunk_targets(total_bytes, C, device_input);
+    // (a caller that streams batch after batch through several pipelines has the copies of one batch hidden behind the
+    // kernels of another: no ramps then, TB_OPT_CHUNK_RAMP = 0)
+    const std::vector<int64_t> targets = p->opt_ramp ? tb_chunk_targets(total_bytes, C, device_input) : std::vector<int64_t>{C};
     size_t ti = 0;
     for (int64_t d = 0; d < n_docs;) {
       const int64_t b0 = off_at(offsets, is64, d);
@@ -887,6 +936,7 @@ int tb_pipeline_set_option(tb_pipeline* p, int32_t option, int64_t value) {
     case TB_OPT_VALIDATE_UTF8: p->opt_validate = value != 0; return TB_OK;
     case TB_OPT_GENERAL_WORD_PATH: p->opt_debug = value != 0 ? TB_DBG_FORCE_WALK : 0; return TB_OK;
     case TB_OPT_DECODE_HTML_ENTITIES: p->opt_decode = value != 0; return TB_OK;
+    case TB_OPT_CHUNK_RAMP: p->opt_ramp = value != 0; return TB_OK;
     case TB_OPT_GATHER_KEPT:
       if (value < 0) return fail(TB_ERR_INVALID_ARGUMENT, "TB_OPT_GATHER_KEPT: number of host threads, 0 = off");
       p->opt_gather = value; return TB_OK;
