@@ -148,7 +148,13 @@ class StreamingRunner:
         def worker(pipe):
             while True:
                 t0 = time.perf_counter()
-                g = q.get()
+                g = None
+                while not errors:
+                    try:
+                        g = q.get(timeout=0.05)
+                        break
+                    except queue.Empty:
+                        pass
                 dt = time.perf_counter() - t0
                 if g is None:
                     return
