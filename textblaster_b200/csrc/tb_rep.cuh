@@ -190,14 +190,23 @@ TB_D void rep_dedup(const G& g, uint32_t* tab, const uint64_t* h, const uint32_t
 
 // Ordered list of the set bits of a bitmap: out[0 .. count) = indices i < nbits with bit i set, increasing.
 // One prefix sum over the bitmap's words (a thread per word), then every thread expands its own word.
+// span > 1: only the indices i whose bits i, i + 1, ..., i + span - 1 are all set (span <= 32; bits at and beyond nbits
+// count as clear).
 template <class G, class IdxT>
-TB_D uint32_t rep_compact_bits(const G& g, const uint32_t* bits, uint32_t nbits, IdxT* out) {
+TB_D uint32_t rep_compact_bits(const G& g, const uint32_t* bits, uint32_t nbits, IdxT* out, uint32_t span = 1) {
   const uint32_t nwords = (nbits + 31u) >> 5;
+  const uint32_t lastmask = (nbits & 31u) ? (1u << (nbits & 31u)) - 1u : 0xFFFFFFFFu;
   uint32_t run = 0;
   for (uint32_t b0 = 0; b0 < nwords; b0 += (uint32_t)g.size()) {
     const uint32_t wi = b0 + (uint32_t)g.tid;
     uint32_t w = wi < nwords ? bits[wi] : 0u;
-    if (wi == nwords - 1u && (nbits & 31u)) w &= (1u << (nbits & 31u)) - 1u;
+    if (wi == nwords - 1u) w &= lastmask;
+    if (span > 1u && w) {
+      uint32_t nx = wi + 1u < nwords ? bits[wi + 1u] : 0u;
+      if (wi + 2u == nwords) nx &= lastmask;
+      const uint64_t both = ((uint64_t)nx << 32) | w;
+      for (uint32_t s = 1; s < span && w; s++) w &= (uint32_t)(both >> s);
+    }
     uint32_t tot, o = run + g.exscan((uint32_t)simt_popc(w), &tot);
     while (w) { out[o++] = (IdxT)(wi * 32u + (uint32_t)(simt_ffs(w) - 1)); w &= w - 1u; }
     run += tot;
@@ -531,9 +540,14 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
           if ((double)v / text_char_len > cfg.top_frac[k]) reasons |= 1u << (TB_GR_REASON_TOP_SHIFT + k);
         }
       }
-      // survivors: positions whose n-gram occurred at least twice, in order
+      // survivors, in order: an n'-gram (n' > n) that occurs twice holds n' - n + 1 n-grams that occur twice, so only
+      // the positions i whose n-grams at i, i + 1, ..., i + (n' - n) all repeated can repeat at the next counted level n'
       uint32_t ncount = 0;
-      if (any_hit && n < ntop_max) ncount = rep_compact_bits(g, A.flag, cn, list);
+      if (any_hit && n < ntop_max) {
+        uint32_t nn = n + 1;
+        while (nn <= ntop_max && !((top_levels >> nn) & 1ull)) nn++;
+        ncount = rep_compact_bits(g, A.flag, cn, list, nn - n + 1u > 32u ? 32u : nn - n + 1u);
+      }
       count = ncount; pruned = true;
       g.sync();
     }

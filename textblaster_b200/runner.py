@@ -9,9 +9,10 @@ order.  No collective: row groups are independent; the caller dea
 (``shard.groups_of_rank``) and gathers what it needs on the host.
 
 The source yields ``RowGroup(index, utf8, offsets)`` with the text in host memory (pinned for full link speed).  The
-sink is called as ``sink(index, summary)`` in increasing ``index``; ``summary`` holds the keep mask, the failing step,
-the per-step statistics and, with ``gather_kept``, the content of the kept documents (copied, so the library's buffers
-can be reused at once).
+sink is called as ``sink(index, summary)`` in source order; ``summary`` holds the keep mask, the failing step, the
+per-step statistics and, with ``gather_kept``, the content of the kept documents.  The arrays of a summary are views
+of the library's result buffers: they are valid during the sink call only (the batch is released when it returns);
+a pipeline takes its next row group meanwhile with a result set of its own.
 """
 from __future__ import annotations
 
@@ -47,6 +48,7 @@ class GroupSummary:
     kept_offsets: Optional[np.ndarray] = None
     gpu_ms: float = 0.0
     gpu_launches: int = 0
+    _release: Optional[Callable[[], None]] = None   # gives the result buffers back to the pipeline
 
 
 @dataclass
@@ -95,22 +97,25 @@ class StreamingRunner:
         pipe.run_raw(g.utf8.ctypes.data if g.utf8.size else None, g.offsets.ctypes.data, g.offsets.dtype == np.int64, n, out)
         try:
             s = GroupSummary(g.index, n, nb,
-                             np.ctypeslib.as_array(out.keep, (n,)).copy() if n else np.zeros(0, np.uint8),
-                             np.ctypeslib.as_array(out.failed_step, (n,)).copy() if n else np.zeros(0, np.int8),
+                             np.ctypeslib.as_array(out.keep, (n,)) if n else np.zeros(0, np.uint8),
+                             np.ctypeslib.as_array(out.failed_step, (n,)) if n else np.zeros(0, np.int8),
                              gpu_ms=out.gpu_ms, gpu_launches=out.gpu_launches)
             if self.copy_stats:
                 s.stats = []
                 for k, prm in enumerate(pipe.params):
                     dt = _abi.stats_dtype(prm.CTYPE)
-                    s.stats.append(np.frombuffer(C.string_at(out.step_stats[k], n * dt.itemsize), dtype=dt).copy() if n else np.zeros(0, dt))
+                    raw = (C.c_uint8 * (n * dt.itemsize)).from_address(out.step_stats[k]) if n else b""
+                    s.stats.append(np.frombuffer(raw, dtype=dt) if n else np.zeros(0, dt))
             if out.kept_offsets:
                 nk = int(out.n_kept)
-                s.kept_offsets = np.ctypeslib.as_array(out.kept_offsets, (nk + 1,)).copy()
+                s.kept_offsets = np.ctypeslib.as_array(out.kept_offsets, (nk + 1,))
                 kb = int(s.kept_offsets[-1])
-                s.kept_content = np.ctypeslib.as_array(out.kept_content, (kb,)).copy() if kb else np.zeros(0, np.uint8)
+                s.kept_content = np.ctypeslib.as_array(out.kept_content, (kb,)) if kb else np.zeros(0, np.uint8)
+            s._release = lambda: pipe.release(out)
             return s
-        finally:
+        except BaseException:
             pipe.release(out)
+            raise
 
     def run(self, source: Iterable[RowGroup], sink: Optional[Callable[[int, GroupSummary], None]] = None) -> RunTotals:
         tot = RunTotals()
@@ -205,10 +210,18 @@ class StreamingRunner:
             if fs.size:
                 for k, c in zip(*np.unique(fs, return_counts=True)):
                     tot.per_step_failed[int(k)] = tot.per_step_failed.get(int(k), 0) + int(c)
-            if sink:
-                sink(s.index, s)
+            try:
+                if sink:
+                    sink(s.index, s)
+            finally:
+                if s._release:
+                    s._release()
+                    s._release = None
         for t in threads:
             t.join(timeout=60)
+        for s in done.values():  # (a failed run leaves summaries nobody consumed)
+            if s._release:
+                s._release()
         if errors:
             raise errors[0]
         tot.wall_s = time.perf_counter() - t_start
