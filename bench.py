@@ -335,7 +335,9 @@ def run_config4(args, rank, local_rank, world):
             u, o, _ = pool[k % len(pool)]
             yield RowGroup(mine[k], u, o)
 
-    # warm-up: buffers of every pipeline grow to their size, kernels are loaded
+    # warm-up: the result sets and device buffers of every pipeline grow to their size, kernels are loaded
+    big = max(pool, key=lambda p: int(p[1][-1]))
+    runner.prime(RowGroup(-1, big[0], big[1]))
     runner.run(source(min(len(mine), max(2 * args.pipelines, 2))))
     kept_by_group = {}
 

@@ -160,6 +160,7 @@ TB_D uint32_t rep_slot(uint64_t key, uint32_t T) {  // the two residues are alre
 TB_D uint32_t rep_next(uint32_t sl, uint32_t T) { return sl + 1 == T ? 0u : sl + 1; }
 template <class G>
 TB_D void rep_fill(const G& g, uint32_t* a, uint32_t n, uint32_t v) {
+#pragma unroll 1
   for (uint32_t i = g.tid; i < n; i += g.size()) a[i] = v;
   g.sync();
 }
@@ -172,10 +173,12 @@ TB_D void rep_dedup(const G& g, uint32_t* tab, const uint64_t* h, const uint32_t
   uint32_t T = rep_tab_size(n);
   rep_fill(g, tab, T, EMPTY);
   uint32_t distinct = 0; uint64_t dbytes = 0, total = 0;
+#pragma unroll 1
   for (uint32_t i = g.tid; i < n; i += g.size()) {
     uint64_t hi = h[i]; uint32_t li = len[i];
     uint32_t sl = rep_slot(hi, T);
     total += li;
+#pragma unroll 1
     for (;;) {
       uint32_t old = idx_cas(&tab[sl], EMPTY, i);
       if (old == EMPTY) { distinct++; dbytes += li; break; }
@@ -197,6 +200,7 @@ TB_D uint32_t rep_compact_bits(const G& g, const uint32_t* bits, uint32_t nbits,
   const uint32_t nwords = (nbits + 31u) >> 5;
   const uint32_t lastmask = (nbits & 31u) ? (1u << (nbits & 31u)) - 1u : 0xFFFFFFFFu;
   uint32_t run = 0;
+#pragma unroll 1
   for (uint32_t b0 = 0; b0 < nwords; b0 += (uint32_t)g.size()) {
     const uint32_t wi = b0 + (uint32_t)g.tid;
     uint32_t w = wi < nwords ? bits[wi] : 0u;
@@ -205,9 +209,11 @@ TB_D uint32_t rep_compact_bits(const G& g, const uint32_t* bits, uint32_t nbits,
       uint32_t nx = wi + 1u < nwords ? bits[wi + 1u] : 0u;
       if (wi + 2u == nwords) nx &= lastmask;
       const uint64_t both = ((uint64_t)nx << 32) | w;
+#pragma unroll 1
       for (uint32_t s = 1; s < span && w; s++) w &= (uint32_t)(both >> s);
     }
     uint32_t tot, o = run + g.exscan((uint32_t)simt_popc(w), &tot);
+#pragma unroll 1
     while (w) { out[o++] = (IdxT)(wi * 32u + (uint32_t)(simt_ffs(w) - 1)); w &= w - 1u; }
     run += tot;
   }
@@ -230,6 +236,7 @@ TB_D uint64_t rep_dup_walk(const G& g, IdxT* fo, IdxT* cand, const uint32_t* cbi
   uint64_t rep = 0;
   if (g.tid == 0) {
     uint32_t skip_until = 0;
+#pragma unroll 1
     for (uint32_t kk = 0; kk < ncand; kk++) {
       const uint32_t k = cand[kk];
       const uint32_t e = elist ? (uint32_t)elist[k] : k, q = e + 1u - n;
@@ -237,6 +244,7 @@ TB_D uint64_t rep_dup_walk(const G& g, IdxT* fo, IdxT* cand, const uint32_t* cbi
       const uint32_t c = fo[k];
       if (fo[c] == c) {  // key seen: hit
         rep += woff[e + 1] - woff[q];
+#pragma unroll 1
         for (uint32_t p = k + 1; p < items && (elist ? (uint32_t)elist[p] : p) < e + n; p++) if (fo[p] == p) fo[p] = (IdxT)EMPTY;
         skip_until = q + n;
       } else {
@@ -272,6 +280,7 @@ TB_D void rep_lines_small(const uint64_t* lh, const uint32_t* ll, const uint8_t*
   uint32_t NP = 0;
   uint64_t myh = 0; uint32_t mylen = 0;
   Hash2 cur; cur.init(); uint32_t curlen = 0;
+#pragma unroll 1
   for (uint32_t k = 0; k < NL; k++) {
     const Hash2 hk = tb_unpack(lh[k]);
     const uint32_t lk = ll[k];
@@ -295,6 +304,7 @@ TB_D void rep_dup_small(const uint64_t* wh, const uint32_t* woff, const uint64_t
   const bool holder = (uint32_t)lane < items;
   uint32_t dcur = 0;
   Hash2 h; h.init();
+#pragma unroll 1
   for (uint32_t n = n_from; n <= ndup_max; n++) {
     if (!((dup_levels >> n) & 1ull)) continue;
     const bool valid = holder && e + 1u >= n;
@@ -302,6 +312,7 @@ TB_D void rep_dup_small(const uint64_t* wh, const uint32_t* woff, const uint64_t
     if (valid) {
       const uint32_t stop = dcur ? e + 1u - dcur : e + 1u;  // the words [stop, e] are in h already
       Hash2 p = tb_unpack(TB_LDG(wh + q));
+#pragma unroll 1
       for (uint32_t j = q + 1; j < stop; j++) p = tb_hcat(p, tb_unpack(TB_LDG(wh + j)), tb_pow_pack(powtab, woff[j + 1] - woff[j]));
       h = dcur ? tb_hcat(p, h, tb_pow_pack(powtab, woff[e + 1] - woff[stop])) : p;
     }
@@ -312,6 +323,7 @@ TB_D void rep_dup_small(const uint64_t* wh, const uint32_t* woff, const uint64_t
     if (cm) {
       const uint32_t len = valid ? woff[e + 1] - woff[q] : 0u;
       uint32_t skip_until = 0;
+#pragma unroll 1
       while (cm) {
         const int k = simt_ffs(cm) - 1;
         cm &= cm - 1u;
@@ -340,10 +352,12 @@ template <class Sink>
 TB_D void rep_top_small(const uint64_t* wh, const uint32_t* woff, const uint64_t* powtab, uint32_t i, Hash2 h, uint32_t count, uint32_t cur,
                         uint32_t ntop_max, uint64_t top_levels, uint32_t W, int lane, Sink sink) {
   bool valid = (uint32_t)lane < count;
+#pragma unroll 1
   for (uint32_t n = cur + 1; n <= ntop_max; n++) {
     if (!((top_levels >> n) & 1ull)) continue;
     const bool v = valid && i + n <= W;
     if (v) {
+#pragma unroll 1
       for (uint32_t j = i + cur; j < i + n; j++) {
         h.push(' ');
         h = tb_hcat(h, tb_unpack(TB_LDG(wh + j)), tb_pow_pack(powtab, woff[j + 1] - woff[j]));
@@ -377,6 +391,7 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
   tb_gr_stats st;
   st.reason_bits = 0; st.flags = gd.flags; st.char_len = gd.char_len; st.n_paras = 0; st.para_dup_elems = 0; st.para_dup_bytes = 0;
   st.n_lines = 0; st.line_dup_elems = 0; st.line_dup_bytes = 0; st.n_words = 0;
+#pragma unroll 1
   for (int k = 0; k < TB_MAX_NGRAMS; k++) { st.top_bytes[k] = 0; st.dup_bytes[k] = 0; }
   if (gd.empty) {  // gopher_rep.rs:60-74
     if (g.tid == 0) { st.reason_bits = TB_GR_REASON_EMPTY; out[d] = st; a.alive[d] = 0; a.failed[d] = (int8_t)step; }
@@ -419,6 +434,7 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
   // inside a paragraph, a run of >= 2 separates paragraphs.
   if (g.tid == 0) {
     Hash2 cur; cur.init(); uint32_t curlen = 0;
+#pragma unroll 1
     for (uint32_t k = 0; k < NL; k++) {
       Hash2 hk = tb_unpack(lh[k]);
       if (k == 0) { cur = hk; curlen = ll[k]; continue; }
@@ -442,7 +458,9 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
   // ---- n-grams (gopher_rep.rs:159-196)
   uint32_t ntop_max = 0, ndup_max = 0;
   uint64_t top_levels = 0, dup_levels = 0;  // bit n: some entry of the list asks for n-grams of n words (n <= TB_MAX_NGRAM_N)
+#pragma unroll 1
   for (int k = 0; k < cfg.n_top; k++) { ntop_max = cfg.top_n[k] > ntop_max ? cfg.top_n[k] : ntop_max; top_levels |= 1ull << cfg.top_n[k]; }
+#pragma unroll 1
   for (int k = 0; k < cfg.n_dup; k++) { ndup_max = cfg.dup_n[k] > ndup_max ? cfg.dup_n[k] : ndup_max; dup_levels |= 1ull << cfg.dup_n[k]; }
   if (ntop_max > W) ntop_max = W;
   if (ndup_max > W) ndup_max = W;
@@ -452,8 +470,10 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
     const uint32_t per = (W + (uint32_t)g.size() - 1u) / (uint32_t)g.size();
     const uint32_t i0 = (uint32_t)g.tid * per < W ? (uint32_t)g.tid * per : W, i1 = i0 + per < W ? i0 + per : W;
     uint32_t sum = 0;
+#pragma unroll 1
     for (uint32_t i = i0; i < i1; i++) sum += TB_LDG(wl_g + i);
     uint32_t tot, run = g.exscan(sum, &tot);
+#pragma unroll 1
     for (uint32_t i = i0; i < i1; i++) { A.woff[i] = run; run += TB_LDG(wl_g + i); }
     if (g.tid == 0) A.woff[W] = tot;
     g.sync();
@@ -468,6 +488,7 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
     uint32_t count = W;     // positions still in play: all, or list[0 .. count)
     bool pruned = false;
     uint32_t cur = 0;       // level of the keys in A.H (0: none yet)
+#pragma unroll 1
     for (uint32_t n = 1; n <= ntop_max && count; n++) {
       if (!((top_levels >> n) & 1ull)) continue;  // only configured levels run a pass; the keys jump levels in registers
       if (pruned && count <= 32u) {
@@ -477,6 +498,7 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
         g.sync();  // (the working arrays are free for what follows)
         if (g.tid < 32)
           rep_top_small(wh, woff, a.uc.powtab, i, h, count, cur, ntop_max, top_levels, W, g.tid, [&](uint32_t lvl, uint64_t v) {
+#pragma unroll 1
             for (int k = 0; k < cfg.n_top; k++) {
               if (cfg.top_n[k] != lvl) continue;
               st.top_bytes[k] = v;
@@ -487,13 +509,17 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
       }
       const uint32_t cn = W - n + 1;
       const uint32_t T = rep_tab_size(count);
+#pragma unroll 1
       for (uint32_t i = g.tid; i < T; i += g.size()) tab[i] = EMPTY;
+#pragma unroll 1
       for (uint32_t i = g.tid; i < fw; i += g.size()) A.flag[i] = 0;
+#pragma unroll 1
       for (uint32_t k = g.tid; k < count; k += g.size()) {
         const uint32_t i = pruned ? (uint32_t)list[k] : k;
         cnt[i] = 0;
         if (i >= cn) continue;
         Hash2 h = tb_unpack(cur ? A.H[i] : TB_LDG(wh + i));
+#pragma unroll 1
         for (uint32_t j = i + (cur ? cur : 1u); j < i + n; j++) {
           h.push(' ');
           h = tb_hcat(h, tb_unpack(TB_LDG(wh + j)), tb_pow_pack(a.uc.powtab, woff[j + 1] - woff[j]));
@@ -503,11 +529,13 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
       cur = n;
       g.sync();
       bool hit = false;
+#pragma unroll 1
       for (uint32_t k = g.tid; k < count; k += g.size()) {
         const uint32_t i = pruned ? (uint32_t)list[k] : k;
         if (i >= cn) continue;
         const uint64_t key = A.H[i];
         uint32_t sl = rep_slot(key, T);
+#pragma unroll 1
         for (;;) {
           uint32_t old = idx_cas(&tab[sl], EMPTY, i);
           if (old == EMPTY) { idx_inc(&cnt[i]); break; }
@@ -522,6 +550,7 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
       uint64_t best = 0;
       const bool any_hit = g.any(hit);  // (a barrier: the counts are complete)
       if (any_hit) {
+#pragma unroll 1
         for (uint32_t k = g.tid; k < count; k += g.size()) {
           const uint32_t i = pruned ? (uint32_t)list[k] : k;
           if (i >= cn) continue;
@@ -534,6 +563,7 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
       {
         const uint32_t c = (uint32_t)(best >> 32), len = (uint32_t)best;
         const uint64_t v = c > 1 ? (uint64_t)len * c : 0;
+#pragma unroll 1
         for (int k = 0; k < cfg.n_top; k++) {
           if (cfg.top_n[k] != n) continue;
           st.top_bytes[k] = v;
@@ -545,6 +575,7 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
       uint32_t ncount = 0;
       if (any_hit && n < ntop_max) {
         uint32_t nn = n + 1;
+#pragma unroll 1
         while (nn <= ntop_max && !((top_levels >> nn) & 1ull)) nn++;
         ncount = rep_compact_bits(g, A.flag, cn, list, nn - n + 1u > 32u ? 32u : nn - n + 1u);
       }
@@ -558,15 +589,18 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
   {
     const uint32_t fw = W / 32 + 1;
     uint32_t n_p = 0;  // first pruned level
+#pragma unroll 1
     for (uint32_t n = TB_REP_PRUNE_FROM; n <= ndup_max && !n_p; n++) if ((dup_levels >> n) & 1ull) n_p = n;
     bool pruned = false;   // the items are list[0 .. items)
     uint32_t items = W;
     uint32_t dcur = 0;     // level of the keys in A.H (0: none yet)
+#pragma unroll 1
     for (uint32_t n = 1; n <= ndup_max; n++) {
       if (!((dup_levels >> n) & 1ull)) continue;  // only configured levels run a pass; the keys jump levels in registers
       if (n == n_p) {
         // shortest n-gram of this level, in bytes
         uint32_t m = 0xFFFFFFFFu;
+#pragma unroll 1
         for (uint32_t i = g.tid; i + n <= W; i += g.size()) { const uint32_t v = woff[i + n] - woff[i]; m = v < m ? v : m; }
         m = 0xFFFFFFFFu - (uint32_t)g.max64((uint64_t)(0xFFFFFFFFu - m));
         const uint32_t k = m < 16u ? m : 16u;
@@ -574,18 +608,24 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
           // word ends whose last k key bytes occur at another word end too (signature in A.H, first end per value in the table)
           const uint64_t mask = tb_sig_mask(k);
           const uint32_t T = rep_tab_size(W - n + 1);
+#pragma unroll 1
           for (uint32_t i = g.tid; i < T; i += g.size()) tab[i] = EMPTY;
+#pragma unroll 1
           for (uint32_t i = g.tid; i < fw; i += g.size()) A.flag[i] = 0;
+#pragma unroll 1
           for (uint32_t e = n - 1 + g.tid; e < W; e += g.size()) {
             uint64_t sig = TB_LDG(wsg + e);
             uint32_t filled = woff[e + 1] - woff[e];
+#pragma unroll 1
             for (uint32_t j = e; filled < k; ) { j--; sig |= TB_LDG(wsg + j) << (4u * filled); filled += woff[j + 1] - woff[j]; }
             A.H[e] = sig & mask;
           }
           g.sync();
+#pragma unroll 1
           for (uint32_t e = n - 1 + g.tid; e < W; e += g.size()) {
             const uint64_t key = A.H[e];
             uint32_t sl = rep_slot(tb_mix64(key), T);
+#pragma unroll 1
             for (;;) {
               uint32_t old = idx_cas(&tab[sl], EMPTY, e);
               if (old == EMPTY) break;
@@ -607,6 +647,7 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
         if (g.tid < 32)
           rep_dup_small(wh, woff, a.uc.powtab, (uint32_t)g.tid < items ? (uint32_t)list[g.tid] : 0u, items, n, ndup_max, dup_levels, g.tid,
                         [&](uint32_t lvl, uint64_t v) {
+#pragma unroll 1
                           for (int k = 0; k < cfg.n_dup; k++) {
                             if (cfg.dup_n[k] != lvl) continue;
                             st.dup_bytes[k] = v;
@@ -626,6 +667,7 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
         const uint32_t q = e + 1u - n;  // first word of the n-gram
         Hash2 h = tb_unpack(TB_LDG(wh + q));
         const uint32_t stop = dcur ? e + 1u - dcur : e + 1u;  // the words [stop, e] are in the stored key already
+#pragma unroll 1
         for (uint32_t j = q + 1; j < stop; j++) h = tb_hcat(h, tb_unpack(TB_LDG(wh + j)), tb_pow_pack(a.uc.powtab, woff[j + 1] - woff[j]));
         if (dcur) h = tb_hcat(h, tb_unpack(A.H[i]), tb_pow_pack(a.uc.powtab, woff[e + 1] - woff[stop]));
         A.H[i] = h.pack();
@@ -633,11 +675,13 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
       dcur = n;
       g.sync();
       bool dup = false;
+#pragma unroll 1
       for (uint32_t i = g.tid; i < items; i += g.size()) {
         const uint32_t e = pruned ? (uint32_t)list[i] : i;
         if (e + 1u < n) { cnt[i] = (IdxT)EMPTY; continue; }
         const uint64_t key = A.H[i];
         uint32_t sl = rep_slot(key, T);
+#pragma unroll 1
         for (;;) {
           uint32_t old = idx_cas(&tab[sl], EMPTY, i);
           if (old == EMPTY) break;
@@ -651,6 +695,7 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
         // fo[i] = first item carrying the same key; the items that are not the first of their key form the bitmap
         // of candidates (assembled a word per warp from ballots: no atomics)
         const uint32_t rounds = (items + (uint32_t)g.size() - 1u) / (uint32_t)g.size();
+#pragma unroll 1
         for (uint32_t r = 0; r < rounds; r++) {
           const uint32_t i = r * (uint32_t)g.size() + (uint32_t)g.tid;
           uint32_t f = i;
@@ -663,6 +708,7 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
         v = rep_dup_walk(g, cnt, (IdxT*)tab, A.flag, woff, pruned ? list : (const IdxT*)nullptr, items, n);  // the table is dead now: it holds the candidate list
       }
       if (g.tid == 0) {
+#pragma unroll 1
         for (int k = 0; k < cfg.n_dup; k++) {
           if (cfg.dup_n[k] != n) continue;
           st.dup_bytes[k] = v;

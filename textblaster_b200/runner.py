@@ -67,19 +67,38 @@ class RunTotals:
 
 class StreamingRunner:
     def __init__(self, make_pipeline: Callable[[], object], pipelines: int = 2, copy_stats: bool = False, gather_kept: int = 0,
-                 queue_depth: Optional[int] = None):
+                 queue_depth: Optional[int] = None, results_per_pipeline: int = 2):
         """make_pipeline: () -> GpuBatchPipeline (called ``pipelines`` times; all on one device).  gather_kept: host
-        threads per pipeline that rebuild the kept documents' content (TB_OPT_GATHER_KEPT; needs a C4 step)."""
+        threads per pipeline that rebuild the kept documents' content (TB_OPT_GATHER_KEPT; needs a C4 step).
+        results_per_pipeline: result sets a pipeline may have outstanding (handed to the sink, not yet released); a
+        pipeline waits for the sink beyond that, so the pinned result buffers stay a fixed set (``prime`` creates them)."""
         self.pipes = [make_pipeline() for _ in range(max(1, pipelines))]
         self.copy_stats = copy_stats
         self.gather_kept = gather_kept
         self.queue_depth = queue_depth or (len(self.pipes) + 1)
+        self.results_per_pipeline = max(1, results_per_pipeline)
+        self._slots = {id(p): threading.Semaphore(self.results_per_pipeline) for p in self.pipes}
         for p in self.pipes:
             if hasattr(p, "set_option"):
                 p.set_option(_abi.TB_OPT_CHUNK_RAMP, 0)
                 if gather_kept:
                     p.set_option(_abi.TB_OPT_RETURN_CONTENT, 2)
                     p.set_option(_abi.TB_OPT_GATHER_KEPT, gather_kept)
+
+    def prime(self, g: RowGroup):
+        """Run one (full-size) row group through every pipeline ``results_per_pipeline`` times without releasing in
+        between: the library then owns that many result sets per pipeline, grown to size, before anything is timed."""
+        for p in self.pipes:
+            if not hasattr(p, "run_raw"):
+                continue
+            held = []
+            n = len(g.offsets) - 1
+            for _ in range(self.results_per_pipeline):
+                out = _abi.tb_batch_out()
+                p.run_raw(g.utf8.ctypes.data if g.utf8.size else None, g.offsets.ctypes.data, g.offsets.dtype == np.int64, n, out)
+                held.append(out)
+            for out in held:
+                p.release(out)
 
     def close(self):
         for p in self.pipes:
@@ -93,8 +112,14 @@ class StreamingRunner:
             r = pipe.run_packed(g.utf8, g.offsets)
             return GroupSummary(g.index, n, nb, np.asarray(r.keep).copy(), np.asarray(r.failed_step).copy(),
                                 list(r.stats) if self.copy_stats else None)
+        slot = self._slots[id(pipe)]
+        slot.acquire()  # (released with the result set, after the sink)
         out = _abi.tb_batch_out()
-        pipe.run_raw(g.utf8.ctypes.data if g.utf8.size else None, g.offsets.ctypes.data, g.offsets.dtype == np.int64, n, out)
+        try:
+            pipe.run_raw(g.utf8.ctypes.data if g.utf8.size else None, g.offsets.ctypes.data, g.offsets.dtype == np.int64, n, out)
+        except BaseException:
+            slot.release()
+            raise
         try:
             s = GroupSummary(g.index, n, nb,
                              np.ctypeslib.as_array(out.keep, (n,)) if n else np.zeros(0, np.uint8),
@@ -111,10 +136,11 @@ class StreamingRunner:
                 s.kept_offsets = np.ctypeslib.as_array(out.kept_offsets, (nk + 1,))
                 kb = int(s.kept_offsets[-1])
                 s.kept_content = np.ctypeslib.as_array(out.kept_content, (kb,)) if kb else np.zeros(0, np.uint8)
-            s._release = lambda: pipe.release(out)
+            s._release = lambda: (pipe.release(out), slot.release())
             return s
         except BaseException:
             pipe.release(out)
+            slot.release()
             raise
 
     def run(self, source: Iterable[RowGroup], sink: Optional[Callable[[int, GroupSummary], None]] = None) -> RunTotals:
