@@ -277,6 +277,234 @@ def run_reference(args, rank, world):
     emit(line)
 
 
+class _OracleParquetPipeline:
+    """CPU arm of config 1: the oracle behind the interface parquet_io.run_parquet drives (run_packed -> keep, content,
+    metadata) -- the in-process executor of the reference without the queue (src/executor.rs:30-57)."""
+
+    def __init__(self, steps, threads):
+        import oracle
+
+        self.oracle, self.pl, self.threads, self.decode = oracle, oracle.OraclePipeline(steps), threads, False
+
+    def set_option(self, option, value):
+        from textblaster_b200 import _abi
+
+        if option == _abi.TB_OPT_DECODE_HTML_ENTITIES:
+            self.decode = bool(value)
+
+    def run_packed(self, values, off):
+        values, off = np.asarray(values), np.asarray(off, dtype=np.int64)
+        r = self.pl.run_packed(values, off, nthreads=self.threads)
+
+        class R:
+            keep = r.keep
+            content = True
+
+            def metadata_and_reason(self, i):
+                return r.metadata(i), r.reason(i)
+
+            def content_of(self, i):
+                return r.content(i)
+
+        return R()
+
+
+def cpu_model():
+    try:
+        for line in open("/proc/cpuinfo"):
+            if line.startswith("model name"):
+                return line.split(":", 1)[1].strip()
+    except OSError:
+        pass
+    return "unknown"
+
+
+def run_config1(args, rank):
+    """BASELINE.json configs[0]: C4QualityFilter with the parameters of the reference's own unit tests
+    (c4_filters.rs:578-591 = the shipped defaults) over a 10 000-document synthetic Parquet file (length log-normal, median
+    2 KB, sigma 1, clipped to [64 B, 64 KB]) through the in-process executor: file -> reader -> filter -> the two output files
+    (textblaster_b200/parquet_io.run_parquet).  --impl reference: the oracle on the host cores (1 thread and all of them);
+    default: the same call with the GPU pipeline.  The file round trip (pyarrow) is inside the timed region of both."""
+    if rank != 0:
+        return
+    import shutil
+    import tempfile
+
+    import pyarrow as pa
+    import pyarrow.parquet as pq
+
+    from textblaster_b200 import parquet_io, synth
+    from textblaster_b200.config import C4QualityParams
+
+    n = 10_000
+    steps = [C4QualityParams(True, True, True, 5, 3, 1000, True, True, True, True)]
+    utf8, off = synth.generate(n, seed=synth.BASE_SEED + 1)
+    tmp = tempfile.mkdtemp(prefix="tb_config1_")
+    try:
+        src = os.path.join(tmp, "in.parquet")
+        col = pa.Array.from_buffers(pa.large_string(), n, [None, pa.py_buffer(off.astype(np.int64)), pa.py_buffer(utf8)])
+        pq.write_table(pa.table({"id": pa.array(["doc-%d" % i for i in range(n)]), "text": col.cast(pa.string())}), src)
+        cfg = parquet_io.ParquetInputConfig(src)
+        threads = os.cpu_count() or 1
+
+        def run(pipe, reps):
+            best = None
+            counts = None
+            for k in range(reps):
+                t0 = time.perf_counter()
+                counts = parquet_io.run_parquet(pipe, cfg, os.path.join(tmp, "kept%d.parquet" % k), os.path.join(tmp, "exc%d.parquet" % k),
+                                                decode_entities=False)
+                dt = time.perf_counter() - t0
+                best = dt if best is None else min(best, dt)
+            return best, counts
+
+        reps = max(1, args.steps)
+        if args.impl == "reference":
+            t1, c1 = run(_OracleParquetPipeline(steps, 1), max(1, min(reps, 2)))
+            tn, cn = run(_OracleParquetPipeline(steps, threads), reps)
+            assert c1 == cn
+            pl = _OracleParquetPipeline(steps, threads)
+            t0 = time.perf_counter()
+            pl.pl.run_packed(utf8, off, nthreads=threads)
+            t_filter = time.perf_counter() - t0
+            v = n / tn
+            line = {"impl": "reference", "metric": "docs/s through C4QualityFilter, Parquet file in, two Parquet files out", "value": v, "unit": UNIT,
+                    "n_gpus": 0, "steps": reps, "warmup": 0, "ms_per_step": tn * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                    "dtype": "u8", "data": "synthetic",
+                    "config": {"workload": "BASELINE.json configs[0]: C4QualityFilter (c4_filters.rs:578-591 parameters) on a 10k-document synthetic Parquet file via the in-process executor on the CPU",
+                               "docs": n, "bytes": int(off[-1]), "cpu": cpu_model(), "cores": threads, "received_kept_excluded": list(cn),
+                               "docs_per_s_1_thread": n / t1, "docs_per_s_filter_only_all_threads": n / t_filter},
+                    "cpu_baseline": {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
+                                     "sample": "the whole 10k-document file, best of %d runs; C++ restatement of the reference CPU chain (the Rust reference cannot be built here)" % reps},
+                    "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+            emit(line)
+            return
+        from textblaster_b200.executor import GpuBatchPipeline
+
+        pipe = GpuBatchPipeline(steps, device=0)
+        run(pipe, 1)  # warm-up: buffers, kernels
+        tg, cg = run(pipe, reps)
+        res = pipe.run_packed(utf8, off)
+        t0 = time.perf_counter()
+        res = pipe.run_packed(utf8, off)
+        t_filter = time.perf_counter() - t0
+        line = {"metric": "docs/s through C4QualityFilter, Parquet file in, two Parquet files out", "value": n / tg, "unit": UNIT, "n_gpus": 1, "steps": reps,
+                "warmup": 1, "ms_per_step": tg * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+                "config": {"workload": "BASELINE.json configs[0]: C4QualityFilter (c4_filters.rs:578-591 parameters) on a 10k-document synthetic Parquet file via the in-process executor, filter on the GPU",
+                           "docs": n, "bytes": int(off[-1]), "received_kept_excluded": list(cg),
+                           "note": "the file round trip (pyarrow read, per-document metadata, two writers) is host work inside the timed region and dominates it",
+                           "docs_per_s_filter_only": n / t_filter},
+                "e2e": {"value": n / tg, "unit": UNIT, "h2d_bytes_per_step": int(off[-1]) + 4 * (n + 1), "d2h_bytes_per_step": None},
+                "gpu_launches": int(res.gpu_launches)}
+        if not args.no_cpu_baseline:
+            import oracle
+
+            ores = oracle.OraclePipeline(steps).run_packed(utf8, off.astype(np.int64), nthreads=threads)
+            ob, oo = ores.content_packed()
+            mism = int((res.keep != ores.keep).sum()) + int(not (np.array_equal(res.content_offsets, oo) and np.array_equal(res.content, ob)))
+            for name in res.stats[0].dtype.names:
+                mism += int((res.stats[0][name] != ores.stats[0][name]).sum())
+            line["parity"] = {"docs": n, "mismatches": mism, "checked": "keep, every C4 counter, rewritten content vs the oracle; tolerance 0"}
+        pipe.close()
+        emit(line)
+    finally:
+        shutil.rmtree(tmp, ignore_errors=True)
+
+
+def run_config3(args, rank):
+    """BASELINE.json configs[2]: GopherRepetitionFilter alone on 20 000 long documents (10-200 KB, uniform in the logarithm),
+    one n-gram order at a time (n = 2..10) for the top-n-gram list (fraction 0.2) and the duplicate n-gram list (0.15); per
+    order docs/s and text GB/s end to end from pinned host memory, device time, and the share of documents whose tables do
+    not fit shared memory (tier X, global work area).  One JSON line: `value` is the rate over all 18 sweeps together,
+    `rows` the sweeps.  cpu_baseline / parity: the oracle on a bounded sample, all nine orders in both lists at once."""
+    if rank != 0:
+        return
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import torch
+
+    import config3_sweep
+    from textblaster_b200.config import GopherRepetitionParams
+    from textblaster_b200.executor import GpuBatchPipeline
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (no CPU fallback)")
+    utf8, off = config3_sweep.corpus()
+    n, nbytes = len(off) - 1, int(off[-1])
+    sampler = ClockSampler(0)
+    sampler.start()
+    rows = []
+    total_s = 0.0
+    total_gpu_ms = 0.0
+    launches = 0
+    ktot = {}
+    for kind in ("top_n_grams", "dup_n_grams"):
+        for order in range(2, 11):
+            p = GpuBatchPipeline([GopherRepetitionParams(**{kind: [(order, 0.2 if kind == "top_n_grams" else 0.15)]})])
+            for _ in range(max(args.warmup, 1)):
+                p.run_packed(utf8, off)
+            p.reset_kernel_times()
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            for _ in range(max(args.steps, 1)):
+                r = p.run_packed(utf8, off)
+            torch.cuda.synchronize()
+            dt = (time.perf_counter() - t0) / max(args.steps, 1)
+            kt = p.kernel_times()
+            for k, v in kt.items():
+                ktot[k] = ktot.get(k, 0.0) + v[0] / max(args.steps, 1)
+            total_s += dt
+            total_gpu_ms += r.gpu_ms
+            launches += r.gpu_launches
+            big = np.maximum(r.stats[0]["n_words"], r.stats[0]["n_lines"])
+            rows.append({"list": kind, "n": order, "docs_per_s": n / dt, "text_gbs": nbytes / dt / 1e9, "ms": dt * 1e3, "gpu_ms": r.gpu_ms, "kept": int(r.keep.sum())})
+            tier = {"S": float((big <= 512).mean()), "M": float(((big > 512) & (big <= 2048)).mean()),
+                    "L": float(((big > 2048) & (big <= 8192)).mean()), "X_global": float((big > 8192).mean())}
+            p.close()
+    clocks = sampler.stop()
+    peak, peak_src = measured_peaks()
+    dom = max(ktot.items(), key=lambda kv: kv[1])
+    sweeps = len(rows)
+    alg = nbytes + 8 * (n + 1) + 16 * n
+    line = {"metric": "docs/s through GopherRepetitionFilter, long documents", "value": n * sweeps / total_s, "unit": UNIT, "n_gpus": 1,
+            "steps": args.steps, "warmup": max(args.warmup, 1), "ms_per_step": total_s / sweeps * 1e3, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": {"workload": "BASELINE.json configs[2]: GopherRepetitionFilter n-gram sweep (n = 2..10, top and duplicate lists, one order at a time) on %d documents of 10-200 KB (%.2f GB)" % (n, nbytes / 1e9),
+                       "tier_share": tier, "spill_rate": tier["X_global"],
+                       "l2": "inputs (%.2f GB per sweep) larger than the 126 MB L2" % (nbytes / 1e9)},
+            "text_gbs": nbytes * sweeps / total_s / 1e9, "rows": rows,
+            "e2e": {"value": n * sweeps / total_s, "unit": UNIT, "h2d_bytes_per_step": nbytes + 8 * (n + 1), "d2h_bytes_per_step": n * (2 + 248),
+                    "text_gbs": nbytes * sweeps / total_s / 1e9, "ms_per_step": total_s / sweeps * 1e3},
+            "gpu_launches": launches, "gpu_ms_per_step": total_gpu_ms / sweeps,
+            "roofline": {"bound": "hbm", "kernel": dom[0], "achieved": alg / (dom[1] / sweeps * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+                         "frac": alg / (dom[1] / sweeps * 1e-3) / 1e9 / peak, "traffic": None, "peak_source": peak_src,
+                         "algorithmic_bytes_per_launch": alg, "avg_launch_ms": dom[1] / sweeps,
+                         "note": "one launch per sweep processes the whole corpus; tier X runs beside the other tiers on a second stream, so the per-kernel times overlap"},
+            "kernels_ms_per_step": {k: round(v / sweeps, 3) for k, v in sorted(ktot.items(), key=lambda kv: -kv[1])},
+            "clocks": clocks}
+    if not args.no_cpu_baseline:
+        import oracle
+        from parity_util import executed
+
+        orders = list(range(2, 11))
+        params = GopherRepetitionParams(dup_line_frac=0.3, dup_para_frac=0.3, dup_line_char_frac=0.2, dup_para_char_frac=0.2,
+                                        top_n_grams=[(k, 0.2) for k in orders], dup_n_grams=[(k, 0.15) for k in orders])
+        threads = os.cpu_count() or 1
+        sample = min(n, 16 * threads)
+        t0 = time.perf_counter()
+        ores = oracle.OraclePipeline([params]).run_packed(utf8[:int(off[sample])], off[:sample + 1].astype(np.int64), nthreads=threads)
+        dt = time.perf_counter() - t0
+        line["cpu_baseline"] = {"value": sample / dt, "unit": UNIT, "cores": threads, "kind": "port", "text_gbs": int(off[sample]) / dt / 1e9,
+                                "sample": "first %d documents (%.1f MB), all nine orders in both lists at once, %.1f s, oracle/tb_oracle.cpp with %d threads" % (sample, off[sample] / 1e6, dt, threads)}
+        res = GpuBatchPipeline([params]).run_packed(utf8[:int(off[sample])], off[:sample + 1])
+        mism = int(((res.keep != ores.keep) | (res.failed_step != ores.failed_step)).sum())
+        ran = executed(ores.failed_step, 0)
+        for name in res.stats[0].dtype.names:
+            ne = res.stats[0][name][ran] != ores.stats[0][name][ran]
+            mism += int((ne.any(axis=1) if ne.ndim > 1 else ne).sum())
+        line["parity"] = {"docs": sample, "mismatches": mism, "checked": "keep, failed_step, every statistic vs the oracle on the cpu_baseline sample (the whole corpus: tools/config3_parity.py, profiles/r02_config3_parity.json)"}
+    emit(line)
+
+
 def run_config4(args, rank, local_rank, world):
     """BASELINE.json configs[3]: the quality chain over a stream of row groups of 65 536 documents dealt round-robin to
     the ranks, through the product's streaming runner (textblaster_b200/runner.py): several pipelines
@@ -432,11 +660,15 @@ def main():
     ap.add_argument("--content", default="runs", choices=["runs", "bytes"],
                     help="how C4's rewritten content comes back: runs of the input text (TB_OPT_RETURN_CONTENT = 2; the end-to-end step "
                          "then gathers the kept documents' content on the host, inside the timed region) or the bytes themselves (1)")
-    ap.add_argument("--config", type=int, default=2, choices=[2, 3, 4], help="BASELINE.json configuration: 2 (headline, default), 3 (n-gram sweep on long documents), 4 (streamed row groups)")
+    ap.add_argument("--config", type=int, default=2, choices=[1, 2, 3, 4], help="BASELINE.json configuration: 1 (C4 on a 10k-document Parquet file), 2 (headline, default), 3 (n-gram sweep on long documents), 4 (streamed row groups)")
     ap.add_argument("--docs-total", type=int, default=0, help="config 4: documents over all ranks (0: one pass over every rank's pool)")
     ap.add_argument("--pool-groups", type=int, default=16, help="config 4: distinct row groups generated per rank before the timed region")
     ap.add_argument("--pipelines", type=int, default=3, help="config 4: pipelines (and host threads) per GPU")
     ap.add_argument("--parity-groups", type=int, default=2, help="config 4: row groups of rank 0 checked against the oracle")
+    ap.add_argument("--host-memory", default="pinned", choices=["pinned", "pageable"],
+                    help="where the text of the end-to-end step lives: pinned host memory (default) or pageable memory as Arrow allocates it "
+                         "(the library then stages it through its own pinned ring, TB_OPT_STAGE_THREADS)")
+    ap.add_argument("--stage-threads", type=int, default=-1, help="TB_OPT_STAGE_THREADS for --host-memory pageable (-1: library default, 0: off)")
     ap.add_argument("--gather-threads", type=int, default=0, help="host threads of TB_OPT_GATHER_KEPT (0: min(8, cpus / ranks))")
     ap.add_argument("--with-fineweb", action="store_true",
                     help="append FineWebQualityFilter (SURVEY 8(f) row 3) to the chain; not the headline workload")
@@ -447,8 +679,14 @@ def main():
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
 
+    if args.config == 1:
+        run_config1(args, rank)
+        return
     if args.impl == "reference":
         run_reference(args, rank, world)
+        return
+    if args.config == 3:
+        run_config3(args, rank)
         return
     if args.config == 4:
         if args.order == "baseline" and "--order" not in sys.argv:
@@ -522,8 +760,14 @@ def main():
 
     last_keep = {}
 
+    host_utf8 = utf8
+    if args.host_memory == "pageable":
+        host_utf8 = np.array(utf8, copy=True)  # ordinary (pageable) memory, as pyarrow hands a column over
+        if args.stage_threads >= 0:
+            pipe.set_option(_abi.TB_OPT_STAGE_THREADS, args.stage_threads)
+
     def step_host():
-        pipe.run_raw(utf8.ctypes.data, off.ctypes.data, True, n_docs, out)
+        pipe.run_raw(host_utf8.ctypes.data, off.ctypes.data, True, n_docs, out)
         keep = np.ctypeslib.as_array(out.keep, (n_docs,)) if n_docs else np.zeros(0, np.uint8)
         last_keep["k"] = keep.copy()
         if out.content_kind == 2:  # the content of the documents that are written out was rebuilt from the input column
@@ -631,6 +875,7 @@ def main():
                                    "on the host from the runs and the input column (TB_OPT_GATHER_KEPT, %d threads, %.2f GB per step), "
                                    "inside the timed region" % (gather_threads, last_keep.get("kept_bytes", 0) / 1e9))
                                   if runs_mode else "bytes (TB_OPT_RETURN_CONTENT = 1)",
+                       "host_memory": args.host_memory + ("" if args.host_memory == "pinned" else " (staged by the library, TB_OPT_STAGE_THREADS = %s)" % ("default 4" if args.stage_threads < 0 else args.stage_threads)),
                        "chunk_mb": args.chunk_mb, "host": numa, "l2": "inputs (%.2f GB per step) larger than the 126 MB L2" % (n_bytes / 1e9),
                        "generator_s": round(t_gen, 2)},
             "text_gbs": total_bytes * K / dt_dev / 1e9, "total_docs_per_step": total_docs,

@@ -349,6 +349,10 @@ enum {
                                      device and the last copy back behind kernels (one batch at a time).  0: every chunk has the full
                                      size -- for callers that keep several pipelines of one context busy with a stream of batches
                                      (textblaster_b200/runner.py), where another batch's kernels cover the copies */
+  TB_OPT_STAGE_THREADS = 8,     /* [4] text in pageable host memory (what Arrow allocates, src/pipeline/readers/parquet_reader.rs:103-112) is
+                                     staged by the library: this many host threads copy it piece by piece into a ring of pinned slots
+                                     (3 x 64 MiB) from which it goes to the device, instead of the driver's slow path for pageable
+                                     copies.  Pinned or registered memory is detected and copied from where it is.  0: never stage */
   TB_OPT_GATHER_KEPT = 6        /* [0] with TB_OPT_RETURN_CONTENT = 2 and host input: number of host threads that copy the content of the
                                      kept documents out of the caller's input column (kept_content / kept_offsets of tb_batch_out), chunk
                                      by chunk behind the device; 0: the caller gathers what it needs itself (tb_gather_content) */

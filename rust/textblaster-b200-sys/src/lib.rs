@@ -83,6 +83,7 @@ pub const TB_OPT_GENERAL_WORD_PATH: i32 = 4;
 pub const TB_OPT_DECODE_HTML_ENTITIES: i32 = 5;
 pub const TB_OPT_GATHER_KEPT: i32 = 6;
 pub const TB_OPT_CHUNK_RAMP: i32 = 7;
+pub const TB_OPT_STAGE_THREADS: i32 = 8;
 
 pub const TB_NOALLOC_MAX_DOCS: i64 = 2048;
 pub const TB_NOALLOC_MAX_BYTES: i64 = 512 * 1024;

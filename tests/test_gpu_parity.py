@@ -484,3 +484,23 @@ def test_content_as_runs_select_and_fallback():
         r = q.run_texts(["One sentence here. And a second one follows it. A third &amp; last one ends it. Four. Five is it."])
         assert r.runs is None and r.content is not None
         q.close()
+
+
+def test_pageable_input_is_staged_by_the_library():
+    """Text in ordinary (pageable) host memory -- what Arrow allocates -- goes through the library's pinned ring
+    (TB_OPT_STAGE_THREADS); the results are those of the direct copy, with one chunk and with many."""
+    utf8, off = synth.generate(30000, seed=synth.BASE_SEED + 7)   # ~100 MB: several slots of the ring
+    steps = CHAINS["baseline_order"]
+    p = GpuBatchPipeline(steps)
+    p.set_option(_abi.TB_OPT_STAGE_THREADS, 0)
+    ref = p.run_packed(utf8, off)
+    for threads, chunk in ((4, 1 << 30), (1, 24 << 20), (7, 5 << 20)):
+        p.set_option(_abi.TB_OPT_STAGE_THREADS, threads)
+        p.set_option(_abi.TB_OPT_CHUNK_BYTES, chunk)
+        r = p.run_packed(utf8, off)
+        assert np.array_equal(r.keep, ref.keep) and np.array_equal(r.failed_step, ref.failed_step)
+        _same_stats(r, ref)
+        assert np.array_equal(r.content_offsets, ref.content_offsets) and np.array_equal(r.content, ref.content)
+    ores = oracle.OraclePipeline(steps).run_packed(utf8, off.astype(np.int64), nthreads=NCPU)
+    compare(ores, ref.keep, ref.failed_step, ref.stats, None, step_types(steps), None, label="staged")
+    p.close()

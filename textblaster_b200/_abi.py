@@ -80,6 +80,7 @@ TB_OPT_GENERAL_WORD_PATH = 4
 TB_OPT_DECODE_HTML_ENTITIES = 5
 TB_OPT_GATHER_KEPT = 6
 TB_OPT_CHUNK_RAMP = 7
+TB_OPT_STAGE_THREADS = 8
 
 
 class tb_c4_params(C.Structure):

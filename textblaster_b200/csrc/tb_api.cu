@@ -143,6 +143,58 @@ struct ResultSet {  // host-side results of one run
   bool in_use = false;
 };
 
+// Pageable input (an Arrow buffer as pyarrow or the arrow crate allocate it): cudaMemcpyAsync from it goes through the
+// driver's own small staging buffer at a fraction of the link rate.  The library stages it itself: one thread per call
+// copies the text piece by piece into a ring of pinned slots (several workers per piece) and sends every slot on with one
+// cudaMemcpyAsync on the copy stream, so the link sees pinned memory and the copies overlap the kernels as before.
+struct Stager {
+  static constexpr int kSlots = 3;
+  static constexpr size_t kSlotBytes = 64ull << 20;
+  struct Job { int64_t ci; const uint8_t* src; size_t bytes; uint8_t* dst; const void* off_src; size_t off_bytes; void* off_dst; cudaEvent_t wait_before, record_after; };
+  std::mutex mu; std::condition_variable cv; std::deque<Job> q; bool closed = false;
+  int64_t recorded = -1;  // last chunk whose copies are all enqueued and whose event is recorded
+  std::thread th;
+  HostBuf* slots = nullptr; cudaEvent_t* slot_ev = nullptr; bool* slot_used = nullptr;
+  cudaStream_t copy = nullptr; int T = 4, device = 0; cudaError_t err = cudaSuccess;
+  static void par_copy(uint8_t* d, const uint8_t* s, size_t n, int T) {
+    if (T <= 1 || n < (8u << 20)) { memcpy(d, s, n); return; }
+    std::vector<std::thread> th;
+    const size_t per = (n / T + 4095) & ~(size_t)4095;
+    for (int t = 1; t < T; t++) { const size_t a = std::min(n, per * t), b = std::min(n, per * (t + 1)); if (b > a) th.emplace_back([=] { memcpy(d + a, s + a, b - a); }); }
+    memcpy(d, s, std::min(n, per));
+    for (auto& x : th) x.join();
+  }
+  void start() {
+    th = std::thread([this] {
+      cudaSetDevice(device);
+      int next = 0;
+      for (;;) {
+        Job j;
+        { std::unique_lock<std::mutex> lk(mu); cv.wait(lk, [&] { return closed || !q.empty(); }); if (q.empty()) return; j = q.front(); q.pop_front(); }
+        cudaError_t e = cudaStreamWaitEvent(copy, j.wait_before, 0);  // the device buffer is free again
+        for (size_t o = 0; o < j.bytes && e == cudaSuccess; o += kSlotBytes) {
+          const size_t n = std::min(kSlotBytes, j.bytes - o);
+          if (slot_used[next]) e = cudaEventSynchronize(slot_ev[next]);  // its last copy has left the slot
+          if (e != cudaSuccess) break;
+          par_copy(slots[next].as<uint8_t>(), j.src + o, n, T);
+          e = cudaMemcpyAsync(j.dst + o, slots[next].p, n, cudaMemcpyHostToDevice, copy);
+          if (e == cudaSuccess) e = cudaEventRecord(slot_ev[next], copy);
+          slot_used[next] = true;
+          next = (next + 1) % kSlots;
+        }
+        if (e == cudaSuccess) e = cudaMemcpyAsync(j.off_dst, j.off_src, j.off_bytes, cudaMemcpyHostToDevice, copy);
+        if (e == cudaSuccess) e = cudaEventRecord(j.record_after, copy);
+        { std::lock_guard<std::mutex> lk(mu); if (e != cudaSuccess) err = e; recorded = j.ci; }
+        cv.notify_all();
+      }
+    });
+  }
+  void push(const Job& j) { { std::lock_guard<std::mutex> lk(mu); q.push_back(j); } cv.notify_all(); }
+  cudaError_t wait_recorded(int64_t ci) { std::unique_lock<std::mutex> lk(mu); cv.wait(lk, [&] { return recorded >= ci || err != cudaSuccess; }); return err; }
+  void finish() { if (!th.joinable()) return; { std::lock_guard<std::mutex> lk(mu); closed = true; } cv.notify_all(); th.join(); }
+  ~Stager() { finish(); }
+};
+
 struct KTime { const char* name; double ms; int64_t launches; };
 
 }  // namespace
@@ -158,7 +210,8 @@ struct tb_ctx {
 struct tb_pipeline {
   tb_ctx* ctx = nullptr;
   std::vector<StepHost> steps;
-  int64_t opt_return_content = 1, opt_validate = 0, opt_chunk = 1024ll << 20, opt_debug = 0, opt_decode = 0, opt_gather = 0, opt_ramp = 1;
+  int64_t opt_return_content = 1, opt_validate = 0, opt_chunk = 1024ll << 20, opt_debug = 0, opt_decode = 0, opt_gather = 0, opt_ramp = 1, opt_stage = 4;
+  HostBuf stage_slots[Stager::kSlots]; cudaEvent_t stage_ev[Stager::kSlots] = {nullptr, nullptr, nullptr}; bool stage_used[Stager::kSlots] = {false, false, false};
   std::vector<cudaEvent_t> ev_gather;  // one per chunk of a call (TB_OPT_GATHER_KEPT)
   std::mutex mu;
   // device buffers (grow-only)
@@ -656,10 +709,36 @@ int run_impl(tb_pipeline* p, const uint8_t* utf8, const void* offsets, int is64,
   int64_t content_base = 0;
   int32_t h_bad = 0;
 
+  // pageable text goes through the library's pinned ring (Stager); pinned or registered text is copied from where it is
+  bool staged = false;
+  Stager stager;
+  if (!device_input && p->opt_stage > 0 && total_bytes >= (4ll << 20)) {
+    cudaPointerAttributes attr;
+    const cudaError_t e = cudaPointerGetAttributes(&attr, utf8 + base0);
+    if (e != cudaSuccess) cudaGetLastError();
+    staged = e != cudaSuccess || attr.type == cudaMemoryTypeUnregistered;
+  }
+  if (staged) {
+    for (int i = 0; i < Stager::kSlots; i++) {
+      if ((rc = p->stage_slots[i].ensure(Stager::kSlotBytes))) return rc;
+      if (!p->stage_ev[i]) CK(cudaEventCreateWithFlags(&p->stage_ev[i], cudaEventDisableTiming));
+      p->stage_used[i] = false;
+    }
+    stager.slots = p->stage_slots; stager.slot_ev = p->stage_ev; stager.slot_used = p->stage_used;
+    stager.copy = c->copy; stager.T = (int)std::min<int64_t>(p->opt_stage, 16); stager.device = c->device;
+    stager.start();
+    if (trace) fprintf(stderr, "[tb] %.2f ms: pageable input: staged through %d pinned slots of %zu MB with %d copy threads\n", since(), Stager::kSlots, Stager::kSlotBytes >> 20, stager.T);
+  }
   auto enqueue_h2d = [&](size_t ci) -> int {
     const Chunk& ch = chunks[ci];
     int buf = (int)(ci & 1);
     if (device_input) return TB_OK;
+    if (staged) {
+      const size_t osz = is64 ? 8 : 4;
+      stager.push({(int64_t)ci, utf8 + ch.b0, (size_t)(ch.b1 - ch.b0), p->text[buf].as<uint8_t>(), (const uint8_t*)offsets + (size_t)ch.d0 * osz,
+                   (size_t)(ch.d1 - ch.d0 + 1) * osz, p->offs[buf].p, p->ev_done[buf], p->ev_h2d[buf]});
+      return TB_OK;
+    }
     CK(cudaStreamWaitEvent(c->copy, p->ev_done[buf], 0));
     int64_t nb = ch.b1 - ch.b0, n = ch.d1 - ch.d0;
     if (nb) CK(cudaMemcpyAsync(p->text[buf].p, utf8 + ch.b0, (size_t)nb, cudaMemcpyHostToDevice, c->copy));
@@ -715,6 +794,10 @@ int run_impl(tb_pipeline* p, const uint8_t* utf8, const void* offsets, int is64,
       text = utf8 + ch.b0;
       tb_launch_init_ranges(c->compute, offsets_dev, 1, ch.d0, n, ch.b0, p->rs0.as<int64_t>(), p->re0.as<int64_t>(), p->alive[buf].as<uint8_t>(), p->failed[buf].as<int8_t>());
     } else {
+      if (staged) {  // the event is recorded by the staging thread: it must have been, before the compute stream can wait on it
+        const cudaError_t e = stager.wait_recorded((int64_t)ci);
+        if (e != cudaSuccess) return fail(TB_ERR_CUDA, std::string("staging thread: ") + cudaGetErrorString(e));
+      }
       CK(cudaStreamWaitEvent(c->compute, p->ev_h2d[buf], 0));
       text = p->text[buf].as<uint8_t>();
       tb_launch_init_ranges(c->compute, p->offs[buf].p, is64, 0, n, ch.b0, p->rs0.as<int64_t>(), p->re0.as<int64_t>(), p->alive[buf].as<uint8_t>(), p->failed[buf].as<int8_t>());
@@ -923,6 +1006,7 @@ void tb_pipeline_destroy(tb_pipeline* p) {
   }
   for (auto e : p->ev_pool) cudaEventDestroy(e);
   for (auto e : p->ev_gather) cudaEventDestroy(e);
+  for (int i = 0; i < Stager::kSlots; i++) { p->stage_slots[i].release(); if (p->stage_ev[i]) cudaEventDestroy(p->stage_ev[i]); }
   delete p;
 }
 
@@ -937,6 +1021,9 @@ int tb_pipeline_set_option(tb_pipeline* p, int32_t option, int64_t value) {
     case TB_OPT_GENERAL_WORD_PATH: p->opt_debug = value != 0 ? TB_DBG_FORCE_WALK : 0; return TB_OK;
     case TB_OPT_DECODE_HTML_ENTITIES: p->opt_decode = value != 0; return TB_OK;
     case TB_OPT_CHUNK_RAMP: p->opt_ramp = value != 0; return TB_OK;
+    case TB_OPT_STAGE_THREADS:
+      if (value < 0) return fail(TB_ERR_INVALID_ARGUMENT, "TB_OPT_STAGE_THREADS: number of host threads, 0 = off");
+      p->opt_stage = value; return TB_OK;
     case TB_OPT_GATHER_KEPT:
       if (value < 0) return fail(TB_ERR_INVALID_ARGUMENT, "TB_OPT_GATHER_KEPT: number of host threads, 0 = off");
       p->opt_gather = value; return TB_OK;
