@@ -73,15 +73,18 @@ TB_D_NOINLINE void gq_doc_walk(const Classifier& C, const TextRange& R, const Sw
 }
 #define TB_GQ_STAGE (23 * 32)  // stop-word candidates one tile can hold: a stretch ends at most 22 words (two per three bytes) + 1
 TB_D bool gq_doc_tiles(const KBatch& a, const LutEntry* lut, uint32_t* stage, const Classifier& C, const SwTable& sw,
-                       const TextRange& R, GqAcc& acc, int lane);
+                       const TextRange& R, GqAcc& acc, int lane, TileFeed& feed);
 // `stage`: 2 * TB_GQ_STAGE words of per-warp scratch (shared memory)
+// `feed`: the warp's bulk-copy ring for the tiles of long documents (tb_feed.cuh); NULL: plain loads only
 TB_D void body_gq(const KBatch& a, const uint16_t* s_ascii, const LutEntry* lut, uint32_t* stage, const SwTable& sw, const GqCfg& cfg,
-                  int step, tb_gq_stats* out, int64_t d, int lane) {
+                  int step, tb_gq_stats* out, int64_t d, int lane, TileFeed* feed = nullptr) {
+  TileFeed nofeed; nofeed.on = false;
+  TileFeed& F = feed ? *feed : nofeed;
   Classifier C{s_ascii, a.uc};
   C.key_maxlen = sw.maxlen; C.key_lenmask = sw.lenmask; C.key_firstmask = sw.firstmask;
   TextRange R{a.text, a.rs[d], a.re[d]};
   GqAcc acc; acc.zero();
-  if ((a.dbg & TB_DBG_FORCE_WALK) || !gq_doc_tiles(a, lut, stage, C, sw, R, acc, lane)) { acc.zero(); gq_doc_walk(C, R, sw, acc, lane); TBE_COUNT(tbe_stat_walk, lane); }
+  if ((a.dbg & TB_DBG_FORCE_WALK) || !gq_doc_tiles(a, lut, stage, C, sw, R, acc, lane, F)) { acc.zero(); gq_doc_walk(C, R, sw, acc, lane); TBE_COUNT(tbe_stat_walk, lane); }
   else TBE_COUNT(tbe_stat_tiles, lane);
   uint32_t n_words = simt_sum(acc.n_words), n_alpha = simt_sum(acc.n_alpha), n_stop = simt_sum(acc.n_stop),
            n_hash = simt_sum(acc.n_hash), n_ell = simt_sum(acc.n_ell), n_lines = simt_sum(acc.n_lines),
@@ -207,15 +210,17 @@ TB_D_NOINLINE void gr_doc_walk(const KBatch& a, const Classifier& C, const TextR
 // separator -- hands the document to the walking path instead of tripling every warp's shared memory.
 #define TB_GR_STAGE_WORDS (12 * 32)
 TB_D bool gr_doc_tiles(const KBatch& a, const LutEntry* lut, uint32_t* stage, const Classifier& C, const TextRange& R,
-                       const GrScratch& s, int64_t d, int lane, GrTotals& out);
+                       const GrScratch& s, int64_t d, int lane, GrTotals& out, TileFeed& feed);
 
 // `stage`: 5 * TB_GR_STAGE_WORDS words of per-warp scratch (shared memory, 8-byte aligned)
 TB_D void body_gr_scan(const KBatch& a, const uint16_t* s_ascii, const LutEntry* lut, uint32_t* stage, const int64_t* ts,
-                       const int64_t* te, const GrScratch& s, int64_t d, int lane) {
+                       const int64_t* te, const GrScratch& s, int64_t d, int lane, TileFeed* feed = nullptr) {
+  TileFeed nofeed; nofeed.on = false;
+  TileFeed& F = feed ? *feed : nofeed;
   Classifier C{s_ascii, a.uc};
   TextRange R{a.text, ts[d], te[d]};
   GrTotals o;
-  if ((a.dbg & TB_DBG_FORCE_WALK) || !gr_doc_tiles(a, lut, stage, C, R, s, d, lane, o)) { gr_doc_walk(a, C, R, s, d, lane, o); TBE_COUNT(tbe_stat_walk, lane); }
+  if ((a.dbg & TB_DBG_FORCE_WALK) || !gr_doc_tiles(a, lut, stage, C, R, s, d, lane, o, F)) { gr_doc_walk(a, C, R, s, d, lane, o); TBE_COUNT(tbe_stat_walk, lane); }
   else TBE_COUNT(tbe_stat_tiles, lane);
   const uint32_t flags = simt_or(o.flags);
   const uint64_t nchars = simt_sum64(o.nchars);
@@ -296,14 +301,16 @@ TB_D void body_gr_rep_x(const KBatch& a, uint64_t* red, const int64_t* ts, const
 // Pass A: doc-level checks, processed lines P, line count; zeroes the per-line slots.
 #define TB_STAGE_BYTES (TB_TILE + 64)  // per-warp staging buffer of the compacting stores (tile_store_kept)
 TB_D void c4a_doc_tiles(const KBatch& a, const LutEntry* lut, uint8_t* stage, const Classifier& C, const C4Cfg& cfg, const C4Scratch& s,
-                        const TextRange& R, int64_t d, int lane);
+                        const TextRange& R, int64_t d, int lane, TileFeed& feed);
 TB_D_NOINLINE void c4a_doc_walk(const KBatch& a, const Classifier& C, const C4Cfg& cfg, const C4Scratch& s, const TextRange& R, int64_t d, int lane);
 TB_D void body_c4_a(const KBatch& a, const uint16_t* s_ascii, const LutEntry* lut, uint8_t* stage, const C4Cfg& cfg, const C4Scratch& s,
-                    int64_t d, int lane) {
+                    int64_t d, int lane, TileFeed* feed = nullptr) {
+  TileFeed nofeed; nofeed.on = false;
+  TileFeed& F = feed ? *feed : nofeed;
   Classifier C{s_ascii, a.uc};
   TextRange R{a.text, a.rs[d], a.re[d]};
   if (a.dbg & TB_DBG_FORCE_WALK) { c4a_doc_walk(a, C, cfg, s, R, d, lane); TBE_COUNT(tbe_stat_walk, lane); }
-  else { c4a_doc_tiles(a, lut, stage, C, cfg, s, R, d, lane); TBE_COUNT(tbe_stat_tiles, lane); }
+  else { c4a_doc_tiles(a, lut, stage, C, cfg, s, R, d, lane, F); TBE_COUNT(tbe_stat_tiles, lane); }
 }
 TB_D_NOINLINE void c4a_doc_walk(const KBatch& a, const Classifier& C, const C4Cfg& cfg, const C4Scratch& s, const TextRange& R, int64_t d, int lane) {
   uint8_t* out = s.P + R.rs;
@@ -395,13 +402,15 @@ TB_D_NOINLINE void c4b_doc_walk(const Classifier& C, const C4Cfg& cfg, const C4S
   }
 }
 TB_D bool c4b_doc_tiles(const KBatch& a, const LutEntry* lut, const Classifier& C, const C4Cfg& cfg, const C4Scratch& s,
-                        const TextRange& R, uint64_t lb, int lane);
+                        const TextRange& R, uint64_t lb, int lane, TileFeed& feed);
 TB_D void body_c4_b(const KBatch& a, const uint16_t* s_ascii, const LutEntry* lut, const C4Cfg& cfg, const C4Scratch& s, int64_t d,
-                    int lane) {
+                    int lane, TileFeed* feed = nullptr) {
+  TileFeed nofeed; nofeed.on = false;
+  TileFeed& F = feed ? *feed : nofeed;
   Classifier C{s_ascii, a.uc};
   TextRange R{s.P, s.prs[d], s.pre[d]};
   const uint64_t lb = (uint64_t)a.rs[d] + (uint64_t)d;
-  if (!(a.dbg & TB_DBG_FORCE_WALK) && c4b_doc_tiles(a, lut, C, cfg, s, R, lb, lane)) { TBE_COUNT(tbe_stat_tiles, lane); return; }
+  if (!(a.dbg & TB_DBG_FORCE_WALK) && c4b_doc_tiles(a, lut, C, cfg, s, R, lb, lane, F)) { TBE_COUNT(tbe_stat_tiles, lane); return; }
   TBE_COUNT(tbe_stat_walk, lane);
   // general path: clear what the mask path may have added, then walk
   simt_sync();

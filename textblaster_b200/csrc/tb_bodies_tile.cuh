@@ -61,15 +61,18 @@ TB_D bool gq_len_may_match(const SwTable& sw, uint32_t len, bool pure_ascii) {
 }
 // `stage`: 2 * TB_GQ_STAGE words of per-warp scratch (shared memory)
 TB_D bool gq_doc_tiles(const KBatch& a, const LutEntry* lut, uint32_t* stage, const Classifier& C, const SwTable& sw, const TextRange& R,
-                       GqAcc& acc, int lane) {
+                       GqAcc& acc, int lane, TileFeed& feed) {
   const uint8_t* t = R.t;
   uint32_t* st_pos = stage; uint32_t* st_len = stage + TB_GQ_STAGE;
   Frag carry{0u, 0u};
+  feed.begin(t, a.ext_lo, a.ext_hi, tb_tile_origin(R), R.re, lane);
   for (int64_t base = tb_tile_origin(R); base < R.re; base += TB_TILE) {
     Tile T;
-    tile_classify<true>(lut, R, a.ext_lo, a.ext_hi, base + lane * TB_STRETCH, T);
+    const uint32_t sm = feed.tile(base);
+    tile_classify<true>(lut, R, a.ext_lo, a.ext_hi, base + lane * TB_STRETCH, T, sm == TB_FEED_NONE ? sm : sm + (uint32_t)(lane * TB_STRETCH));
+    feed.done(base, lane);  // (the stretch is in registers now)
     const uint32_t fl = T.dirty ? tile_fix_dirty(C, R, T) : 0u;
-    if (simt_any((fl & TILE_EXOTIC) != 0u)) return false;
+    if (simt_any((fl & TILE_EXOTIC) != 0u)) { feed.drain(base); return false; }
     acc.flags |= fl & CI_COMPLEX;
     const int64_t p0 = T.p0;
     const uint32_t V = T.valid, B = T.brk, WC = T.m[TL_WC], LEAD = V & ~T.h[TH_CONT], NAm = T.m[TL_NA], SWF = T.h[TH_SWF];
@@ -182,18 +185,21 @@ TB_D bool gq_doc_tiles(const KBatch& a, const LutEntry* lut, uint32_t* stage, co
 // C4QualityFilter pass B (c4_filters.rs:207-250): words per processed line, longest word, line flags
 // ---------------------------------------------------------------------------------------------
 TB_D bool c4b_doc_tiles(const KBatch& a, const LutEntry* lut, const Classifier& C, const C4Cfg& cfg, const C4Scratch& s,
-                        const TextRange& R, uint64_t lb, int lane) {
+                        const TextRange& R, uint64_t lb, int lane, TileFeed& feed) {
   const uint8_t* t = R.t;
   const bool check_len = cfg.max_word_length > 0;
   const bool small = check_len && cfg.max_word_length < 32;  // words inside one stretch can be too long
   const bool pats = cfg.filter_javascript != 0 || cfg.filter_policy != 0;
   Frag carry{0u, 0u};
   uint32_t nl = 0;
+  feed.begin(t, a.ext_lo, a.ext_hi, tb_tile_origin(R), R.re, lane);
   for (int64_t base = tb_tile_origin(R); base < R.re; base += TB_TILE) {
     Tile T;
-    tile_classify<true>(lut, R, a.ext_lo, a.ext_hi, base + lane * TB_STRETCH, T);
+    const uint32_t sm = feed.tile(base);
+    tile_classify<true>(lut, R, a.ext_lo, a.ext_hi, base + lane * TB_STRETCH, T, sm == TB_FEED_NONE ? sm : sm + (uint32_t)(lane * TB_STRETCH));
+    feed.done(base, lane);
     const uint32_t fl = T.dirty ? tile_fix_dirty(C, R, T) : 0u;
-    if (simt_any((fl & TILE_EXOTIC) != 0u)) return false;
+    if (simt_any((fl & TILE_EXOTIC) != 0u)) { feed.drain(base); return false; }
     const int64_t p0 = T.p0;
     const uint32_t V = T.valid, B = T.brk, WC = T.m[TL_WC], LEAD = V & ~T.h[TH_CONT], NLm = T.h[TH_NL];
     uint32_t tot, pre = simt_exscan((uint32_t)tb_popc32(NLm), lane, &tot);
@@ -280,7 +286,7 @@ TB_D HLS hls_shfl_up(HLS v, int o) { HLS r; r.h = hl_shfl_up(v.h, o); r.sig = (u
 TB_D HLS hls_shfl(HLS v, int src) { HLS r; r.h = hl_shfl(v.h, src); r.sig = simt_shfl(v.sig, src); return r; }
 
 TB_D bool gr_doc_tiles(const KBatch& a, const LutEntry* lut, uint32_t* stage, const Classifier& C, const TextRange& R,
-                       const GrScratch& s, int64_t d, int lane, GrTotals& out) {
+                       const GrScratch& s, int64_t d, int lane, GrTotals& out, TileFeed& feed) {
   uint64_t* st_s = (uint64_t*)stage;
   uint32_t* st_a = stage + 2 * TB_GR_STAGE_WORDS; uint32_t* st_b = stage + 3 * TB_GR_STAGE_WORDS; uint32_t* st_n = stage + 4 * TB_GR_STAGE_WORDS;
   const uint64_t uw = tb_wunit(R.rs, d), ul = tb_lunit(R.rs, d);
@@ -293,11 +299,14 @@ TB_D bool gr_doc_tiles(const KBatch& a, const LutEntry* lut, uint32_t* stage, co
   HLS wcarry{{0u, 0u, 0u}, 0ull};
   HL lcarry{0u, 0u, 0u};
   uint32_t wcarry_wc = 0;
+  feed.begin(R.t, a.ext_lo, a.ext_hi, tb_tile_origin(R), R.re, lane);
   for (int64_t base = tb_tile_origin(R); base < R.re; base += TB_TILE) {
     Tile T;
-    tile_classify<true>(lut, R, a.ext_lo, a.ext_hi, base + lane * TB_STRETCH, T);
+    const uint32_t sm = feed.tile(base);
+    tile_classify<true>(lut, R, a.ext_lo, a.ext_hi, base + lane * TB_STRETCH, T, sm == TB_FEED_NONE ? sm : sm + (uint32_t)(lane * TB_STRETCH));
+    feed.done(base, lane);
     const uint32_t fl = T.dirty ? tile_fix_dirty(C, R, T) : 0u;
-    if (simt_any((fl & TILE_EXOTIC) != 0u)) return false;
+    if (simt_any((fl & TILE_EXOTIC) != 0u)) { feed.drain(base); return false; }
     flags |= fl & CI_COMPLEX;
     const int64_t p0 = T.p0;
     const uint32_t V = T.valid, B = T.brk, WC = T.m[TL_WC];
@@ -318,7 +327,7 @@ TB_D bool gr_doc_tiles(const KBatch& a, const LutEntry* lut, uint32_t* stage, co
     const uint32_t first_word = (B && (in_wc || (WC & headm))) ? 1u : 0u;
     const uint32_t WEin = B & (H << 1) & ~tb_upto(fb);  // word ends after the first segment start
     uint32_t wtot, wpre = simt_exscan((uint32_t)tb_popc32(WEin) + first_word, lane, &wtot);
-    if (wtot > TB_GR_STAGE_WORDS) return false;  // more words than the staging arrays hold: the walking path takes the document
+    if (wtot > TB_GR_STAGE_WORDS) { feed.drain(base); return false; }  // more words than the staging arrays hold: the walking path takes the document
     // ---- line pieces: is the piece that is open at the start of the stretch non-empty?
     const int fn = tb_ctz32(NLx);
     const int ln_ = NLx ? 31 - tb_clz32(NLx) : -1;
@@ -492,7 +501,7 @@ TB_D uint32_t tile_store_kept(const uint32_t* w, uint32_t K, uint8_t* stage, uin
 // lines P: every line trimmed, citations removed, still joined by the original '\n'.
 // ---------------------------------------------------------------------------------------------
 TB_D void c4a_doc_tiles(const KBatch& a, const LutEntry* lut, uint8_t* stage, const Classifier& C, const C4Cfg& cfg, const C4Scratch& s,
-                        const TextRange& R, int64_t d, int lane) {
+                        const TextRange& R, int64_t d, int lane, TileFeed& feed) {
   const uint8_t* t = R.t;
   uint8_t* out = s.P + R.rs;
   const uint64_t lb = (uint64_t)R.rs + (uint64_t)d;
@@ -502,10 +511,13 @@ TB_D void c4a_doc_tiles(const KBatch& a, const LutEntry* lut, uint8_t* stage, co
   uint32_t carry_seen = 0;  // the current line showed a non-white-space character before this tile
   int64_t carry_cit = -1;   // end of a citation that runs into this tile
   if (lane == 0) { s.lwc[lb] = 0; s.lmax[lb] = 0; s.lflags[lb] = 0; }
+  feed.begin(t, a.ext_lo, a.ext_hi, tb_tile_origin(R), R.re, lane);
   for (int64_t base = tb_tile_origin(R); base < R.re; base += TB_TILE) {
     Tile T;
     const int64_t p0 = base + lane * TB_STRETCH;
-    tile_gather<true>(lut, R, a.ext_lo, a.ext_hi, p0, T);
+    const uint32_t sm = feed.tile(base);
+    tile_gather<true>(lut, R, a.ext_lo, a.ext_hi, p0, T, sm == TB_FEED_NONE ? sm : sm + (uint32_t)(lane * TB_STRETCH));
+    feed.done(base, lane);
     const uint32_t V = T.valid, NLm = T.m[CA_NL], NAm = T.m[CA_NA];
     uint32_t WSm = T.m[CA_WS];
     if (NAm) {  // non-ASCII White_Space: only a few lead bytes can begin one

@@ -74,11 +74,14 @@ __global__ void __launch_bounds__(TB_BLOCK, 12) k_gq(KBatch a, SwTable sw, GqCfg
     __syncthreads();
     sw.e = s_sw;
   }
+  __shared__ __align__(1024) uint8_t s_feed[TB_FEED_SMEM];  // tiles of long documents arrive here by bulk copy (tb_feed.cuh)
+  TileFeed feed;
+  feed.init(s_feed, threadIdx.x & 31);
   for (;;) {
     const int64_t d = next_doc(cursor, a);
     if (d == -1) break;
     if (d < 0) continue;
-    if (a.alive[d]) body_gq(a, s_ascii, s_lut, s_cand, sw, cfg, step, out, d, threadIdx.x & 31);
+    if (a.alive[d]) body_gq(a, s_ascii, s_lut, s_cand, sw, cfg, step, out, d, threadIdx.x & 31, &feed);
   }
 }
 __global__ void k_trim(KBatch a, int64_t* ts, int64_t* te) {
@@ -93,11 +96,14 @@ __global__ void __launch_bounds__(TB_BLOCK, 16) k_gr_scan(KBatch a, const int64_
   load_ascii(s_ascii, a.uc);
   load_lut(s_lut, a.uc, TB_LUT_GR, 0u);
   __shared__ __align__(8) uint32_t s_stage[5 * TB_GR_STAGE_WORDS];
+  __shared__ __align__(1024) uint8_t s_feed[TB_FEED_SMEM];
+  TileFeed feed;
+  feed.init(s_feed, threadIdx.x & 31);
   for (;;) {
     const int64_t d = next_doc(&s.counters[8], a);
     if (d == -1) break;
     if (d < 0) continue;
-    if (a.alive[d]) body_gr_scan(a, s_ascii, s_lut, s_stage, ts, te, s, d, threadIdx.x & 31);
+    if (a.alive[d]) body_gr_scan(a, s_ascii, s_lut, s_stage, ts, te, s, d, threadIdx.x & 31, &feed);
   }
 }
 // Repetition pass 2, persistent CTAs pulling document ids of their tier from the lists the scan pass built.
@@ -163,11 +169,14 @@ __global__ void __launch_bounds__(TB_BLOCK, 24) k_c4_a(KBatch a, C4Cfg cfg, C4Sc
   __shared__ __align__(16) uint8_t s_stage[TB_STAGE_BYTES];
   load_ascii(s_ascii, a.uc);
   load_lut(s_lut, a.uc, TB_LUT_C4A, 0u);
+  __shared__ __align__(1024) uint8_t s_feed[TB_FEED_SMEM];
+  TileFeed feed;
+  feed.init(s_feed, threadIdx.x & 31);
   for (;;) {
     const int64_t d = next_doc(cursor, a);
     if (d == -1) break;
     if (d < 0) continue;
-    if (a.alive[d]) body_c4_a(a, s_ascii, s_lut, s_stage, cfg, s, d, threadIdx.x & 31);
+    if (a.alive[d]) body_c4_a(a, s_ascii, s_lut, s_stage, cfg, s, d, threadIdx.x & 31, &feed);
   }
 }
 __global__ void __launch_bounds__(TB_BLOCK, 16) k_entities(KBatch a, const EntEntry* tab, uint32_t ntab, uint32_t* amp, uint32_t* drop,
@@ -199,11 +208,14 @@ __global__ void __launch_bounds__(TB_BLOCK, 20) k_c4_b(KBatch a, C4Cfg cfg, C4Sc
   __shared__ LutEntry s_lut[256];
   load_ascii(s_ascii, a.uc);
   load_lut(s_lut, a.uc, TB_LUT_C4B, 0u);
+  __shared__ __align__(1024) uint8_t s_feed[TB_FEED_SMEM];
+  TileFeed feed;
+  feed.init(s_feed, threadIdx.x & 31);
   for (;;) {
     const int64_t d = next_doc(cursor, a);
     if (d == -1) break;
     if (d < 0) continue;
-    if (a.alive[d] && !s.docflags[d] && s.nlines[d] != 0) body_c4_b(a, s_ascii, s_lut, cfg, s, d, threadIdx.x & 31);
+    if (a.alive[d] && !s.docflags[d] && s.nlines[d] != 0) body_c4_b(a, s_ascii, s_lut, cfg, s, d, threadIdx.x & 31, &feed);
   }
 }
 __global__ void __launch_bounds__(TB_BLOCK, 32) k_c4_c(KBatch a, C4Cfg cfg, C4Scratch s, uint32_t* cursor) {

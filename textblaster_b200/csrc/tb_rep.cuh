@@ -276,21 +276,36 @@ TB_D void rep_dedup_small(uint64_t h, uint32_t len, uint32_t n, int lane, uint32
 // pieces into paragraphs runs on every lane alike (uniform loads); lane p keeps paragraph p.
 TB_D void rep_lines_small(const uint64_t* lh, const uint32_t* ll, const uint8_t* lg, uint32_t NL, const uint64_t* powtab, int lane,
                           uint32_t* line_de, uint64_t* line_db, uint32_t* NPo, uint32_t* para_de, uint64_t* para_db) {
-  rep_dedup_small((uint32_t)lane < NL ? lh[lane] : 0ull, (uint32_t)lane < NL ? ll[lane] : 0u, NL, lane, line_de, line_db);
-  uint32_t NP = 0;
-  uint64_t myh = 0; uint32_t mylen = 0;
-  Hash2 cur; cur.init(); uint32_t curlen = 0;
+  const bool holder = (uint32_t)lane < NL;
+  const uint64_t myline = holder ? lh[lane] : 0ull;
+  const uint32_t mylen = holder ? ll[lane] : 0u;
+  rep_dedup_small(myline, mylen, NL, lane, line_de, line_db);
+  // paragraphs: a piece that follows a run of >= 2 newlines (lg) opens one, the others join the paragraph before them
+  // with a '\n' in between.  Joining is associative: an inclusive segmented scan over the lanes leaves every
+  // paragraph's hash and length on the lane of its last piece.
+  const bool head = holder && (lane == 0 || lg[lane] != 0);
+  Hash2 v = tb_unpack(myline);
+  uint32_t vl = mylen, f = head ? 1u : 0u;
 #pragma unroll 1
-  for (uint32_t k = 0; k < NL; k++) {
-    const Hash2 hk = tb_unpack(lh[k]);
-    const uint32_t lk = ll[k];
-    if (k == 0) { cur = hk; curlen = lk; continue; }
-    if (lg[k]) { if (NP == (uint32_t)lane) { myh = cur.pack(); mylen = curlen; } NP++; cur = hk; curlen = lk; }
-    else { cur.push('\n'); cur = tb_hcat(cur, hk, tb_pow_pack(powtab, lk)); curlen += 1 + lk; }
+  for (int off = 1; off < 32; off <<= 1) {
+    const uint32_t ua = simt_shfl_up(v.a, off), ub = simt_shfl_up(v.b, off), ul = simt_shfl_up(vl, off), uf = simt_shfl_up(f, off);
+    if (lane >= off && !f && holder) {
+      Hash2 x; x.a = ua; x.b = ub;
+      x.push('\n');
+      v = tb_hcat(x, v, tb_pow_pack(powtab, vl));
+      vl += ul + 1u; f = uf;
+    }
   }
-  if (NL) { if (NP == (uint32_t)lane) { myh = cur.pack(); mylen = curlen; } NP++; }
+  const uint32_t heads = simt_ballot(head);
+  const bool last = holder && ((uint32_t)lane + 1u == NL || ((heads >> ((lane + 1) & 31)) & 1u));  // the next piece opens a paragraph
+  const uint32_t NP = (uint32_t)simt_popc(heads);
   *NPo = NP;
-  rep_dedup_small(myh, mylen, NP, lane, para_de, para_db);
+  // find_duplicates over the paragraphs, each on the lane of its last piece (the order of the lanes is their order)
+  const uint32_t first = rep_small_first(v.pack(), last, lane);
+  const bool dup = last && first != (uint32_t)lane;
+  *para_de = (uint32_t)simt_popc(simt_ballot(dup));
+  const uint32_t l = dup ? vl : 0u;
+  *para_db = (uint64_t)simt_sum(l & 0xFFFFu) + ((uint64_t)simt_sum(l >> 16) << 16);
 }
 // Duplicate n-grams of every configured level from n_from on (text.rs:241-259) when at most 32 word ends are in play:
 // item `lane` is the n-gram that ends with word e (valid: lane < items).  Keys grow to the left in registers; equal

@@ -17,6 +17,7 @@
 #pragma once
 #include "tb_fastwords.cuh"
 #include "tb_wordmachine.cuh"
+#include "tb_feed.cuh"
 
 #ifndef TB_STRETCH
 #define TB_STRETCH 32
@@ -248,13 +249,24 @@ TB_HD void tb_load32(const uint8_t* p, uint32_t* w) {
   for (int k = 0; k < 8; k++) w[k] = (uint32_t)p[4 * k] | ((uint32_t)p[4 * k + 1] << 8) | ((uint32_t)p[4 * k + 2] << 16) | ((uint32_t)p[4 * k + 3] << 24);
 #endif
 }
+TB_HD uint32_t tb_byte_shared(uint32_t addr) {  // one byte at a shared-memory address (device only)
+#if defined(__CUDA_ARCH__)
+  uint32_t v;
+  asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(addr));
+  return v;
+#else
+  (void)addr;
+  return 0;
+#endif
+}
 // first tile position of a range: the stretch of lane 0 is the 32-byte aligned block that holds rs
 TB_HD int64_t tb_tile_origin(const TextRange& R) { return R.rs - (int64_t)((uintptr_t)(R.t + R.rs) & 31u); }
 
 // Load the stretch at p0 and look its bytes up: T.w, T.valid, T.m[] (and T.h[] if HI).  Returns false for a
 // stretch without any byte of the range.  [ext_lo, ext_hi): extent of the buffer that vector loads may touch.
 // the 32 bytes at p0 (0 outside [rs, re)); returns the mask of bytes inside the range
-TB_HD uint32_t tile_load(const TextRange& R, int64_t ext_lo, int64_t ext_hi, int64_t p0, uint32_t* w) {
+// `staged`: shared-memory address of the stretch in a tile the copy engine brought in (tb_feed.cuh), or TB_FEED_NONE
+TB_HD uint32_t tile_load(const TextRange& R, int64_t ext_lo, int64_t ext_hi, int64_t p0, uint32_t* w, uint32_t staged = TB_FEED_NONE) {
   const uint8_t* t = R.t;
   const int64_t a = R.rs - p0, b = R.re - p0;
   const uint32_t vlo = a <= 0 ? 0xFFFFFFFFu : (a >= 32 ? 0u : ~((1u << (uint32_t)a) - 1u));
@@ -263,8 +275,14 @@ TB_HD uint32_t tile_load(const TextRange& R, int64_t ext_lo, int64_t ext_hi, int
   if (V == 0u) {
 #pragma unroll
     for (int k = 0; k < 8; k++) w[k] = 0;
-  } else if (p0 >= ext_lo && p0 + 32 <= ext_hi) {
-    tb_load32(t + p0, w);
+  } else if (staged != TB_FEED_NONE || (p0 >= ext_lo && p0 + 32 <= ext_hi)) {
+#if defined(__CUDA_ARCH__)
+    if (staged != TB_FEED_NONE) {
+      asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]) : "r"(staged));
+      asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(w[4]), "=r"(w[5]), "=r"(w[6]), "=r"(w[7]) : "r"(staged + 16u));
+    } else
+#endif
+      tb_load32(t + p0, w);
     if (V != 0xFFFFFFFFu) {
 #pragma unroll
       for (int k = 0; k < 8; k++) {
@@ -295,9 +313,9 @@ TB_HD uint32_t tile_eq_mask(const uint32_t* w, uint32_t c) {
 // Load the stretch at p0 and look its bytes up: T.w, T.valid, T.m[] (and T.h[] if HI).  Returns false for a
 // stretch without any byte of the range.  [ext_lo, ext_hi): extent of the buffer that vector loads may touch.
 template <bool HI>
-TB_HD bool tile_gather(const LutEntry* lut, const TextRange& R, int64_t ext_lo, int64_t ext_hi, int64_t p0, Tile& T) {
+TB_HD bool tile_gather(const LutEntry* lut, const TextRange& R, int64_t ext_lo, int64_t ext_hi, int64_t p0, Tile& T, uint32_t staged = TB_FEED_NONE) {
   T.p0 = p0;
-  const uint32_t V = tile_load(R, ext_lo, ext_hi, p0, T.w);
+  const uint32_t V = tile_load(R, ext_lo, ext_hi, p0, T.w, staged);
   T.valid = V;
   if (V == 0u) {
 #pragma unroll
@@ -323,17 +341,20 @@ TB_HD bool tile_gather(const LutEntry* lut, const TextRange& R, int64_t ext_lo, 
 
 // Load and classify for the word passes: tile_gather plus the boundary mask.
 template <bool HI>
-TB_HD void tile_classify(const LutEntry* lut, const TextRange& R, int64_t ext_lo, int64_t ext_hi, int64_t p0, Tile& T) {
+TB_HD void tile_classify(const LutEntry* lut, const TextRange& R, int64_t ext_lo, int64_t ext_hi, int64_t p0, Tile& T, uint32_t staged = TB_FEED_NONE) {
   const uint8_t* t = R.t;
-  if (!tile_gather<HI>(lut, R, ext_lo, ext_hi, p0, T)) return;
+  if (!tile_gather<HI>(lut, R, ext_lo, ext_hi, p0, T, staged)) return;
   const uint32_t V = T.valid;
   // context bytes
   {
     const int64_t q2 = p0 - 2, q1 = p0 - 1, qr = p0 + 32;
     uint32_t l2 = 0, l1 = 0, l1h = 0, r1 = 0;
-    if (q2 >= R.rs && q2 < R.re) l2 = lut[tb_byte(t, q2)].lo;
-    if (q1 >= R.rs && q1 < R.re) { LutEntry e = lut[tb_byte(t, q1)]; l1 = e.lo; l1h = e.hi; }
-    if (qr >= R.rs && qr < R.re) r1 = lut[tb_byte(t, qr)].lo;
+    // (in a staged tile -- the ring is aligned on the tile size -- the neighbours' bytes are in shared memory too,
+    // except in front of the first stretch and behind the last)
+    const bool sl = staged != TB_FEED_NONE && (staged & (TB_TILE - 1u)) != 0u, sr = staged != TB_FEED_NONE && (staged & (TB_TILE - 1u)) != TB_TILE - 32u;
+    if (q2 >= R.rs && q2 < R.re) l2 = lut[sl ? tb_byte_shared(staged - 2u) : tb_byte(t, q2)].lo;
+    if (q1 >= R.rs && q1 < R.re) { LutEntry e = lut[sl ? tb_byte_shared(staged - 1u) : tb_byte(t, q1)]; l1 = e.lo; l1h = e.hi; }
+    if (qr >= R.rs && qr < R.re) r1 = lut[sr ? tb_byte_shared(staged + 32u) : tb_byte(t, qr)].lo;
     T.lctx = l2 | (l1 << 1); T.rctx = r1; T.l1hi = l1h;
   }
 #define TILE_L(c) (T.lctx << (30 - 4 * (c)))
