@@ -173,7 +173,7 @@ extern "C" int tbe_run_chain(const tb_step_cfg* steps, size_t n_steps, const uin
   const size_t wunits = tb_word_units(cbx, (size_t)n), units = tb_line_units(cbx, (size_t)n);
   // tables
   std::vector<uint64_t> pw(TB_POWTAB);
-  { uint32_t a = 1, b = 1; for (int i = 0; i < TB_POWTAB; i++) { pw[i] = ((uint64_t)a << 32) | b; a = tb_mm(a, TB_B1); b = tb_mm(b, TB_B2); } }
+  tb_fill_powtab(pw.data(), TB_B1_DEFAULT, TB_B2_DEFAULT);
   UcTables uc{tb_uc_stage1, tb_uc_stage2, &tb_uc_lower[0][0], &tb_uc_cased[0][0], &tb_uc_caseign[0][0], pw.data(),
               TB_UC_NLOWER, TB_UC_NCASED, TB_UC_NCASEIGN, {0}};
   tb_compute_wslead(tb_uc_stage1, tb_uc_stage2, uc.wslead);

@@ -12,6 +12,7 @@
 #include <condition_variable>
 #include <deque>
 #include <mutex>
+#include <random>
 #include <string>
 #include <thread>
 #include <vector>
@@ -901,9 +902,19 @@ int tb_ctx_create(int device, tb_ctx** out) {
   if ((rc = upload(c->t_stage1, tb_uc_stage1, sizeof tb_uc_stage1)) || (rc = upload(c->t_stage2, tb_uc_stage2, sizeof tb_uc_stage2)) ||
       (rc = upload(c->t_lower, tb_uc_lower, sizeof tb_uc_lower)) || (rc = upload(c->t_cased, tb_uc_cased, sizeof tb_uc_cased)) ||
       (rc = upload(c->t_caseign, tb_uc_caseign, sizeof tb_uc_caseign))) { delete c; return rc; }
+  // the two bases of the string hashes, drawn per context (TB_HASH_SEED fixes them for a reproducible run): an input
+  // cannot be built to collide under bases it does not know, and the collision bound of tb_common.cuh is over this draw
   std::vector<uint64_t> pw(TB_POWTAB);
-  uint32_t a = 1, b = 1;
-  for (int i = 0; i < TB_POWTAB; i++) { pw[i] = ((uint64_t)a << 32) | b; a = tb_mm(a, TB_B1); b = tb_mm(b, TB_B2); }
+  {
+    uint64_t seed;
+    if (const char* e = getenv("TB_HASH_SEED")) seed = strtoull(e, nullptr, 0);
+    else { std::random_device rd; seed = ((uint64_t)rd() << 32) ^ rd() ^ (uint64_t)std::chrono::steady_clock::now().time_since_epoch().count(); }
+    const uint64_t r1 = tb_mix64(seed + 0x9E3779B97F4A7C15ull), r2 = tb_mix64(seed + 2 * 0x9E3779B97F4A7C15ull);
+    const uint32_t half = 1u << (TB_BASE_BITS - 1);
+    uint32_t b1 = half + (uint32_t)(r1 % half), b2 = half + (uint32_t)(r2 % half);  // in [2^28, 2^29)
+    if (b2 == b1) b2 = half + (b2 + 1u - half) % half;
+    tb_fill_powtab(pw.data(), b1, b2);
+  }
   if ((rc = upload(c->t_pow, pw.data(), pw.size() * 8))) { delete c; return rc; }
   if ((rc = upload(c->t_ent, tb_ent_table, sizeof tb_ent_table))) { delete c; return rc; }
   c->uc = UcTables{c->t_stage1.as<uint16_t>(), c->t_stage2.as<uint16_t>(), c->t_lower.as<uint32_t>(), c->t_cased.as<uint32_t>(),

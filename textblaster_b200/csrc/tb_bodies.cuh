@@ -203,6 +203,10 @@ TB_D_NOINLINE void gr_doc_walk(const KBatch& a, const Classifier& C, const TextR
     if (lane == 0) { lh[NL] = hl_pack(carry); ll[NL] = carry.len; lg[NL] = (uint8_t)gr_gap2(R, R.re - carry.len); }
     NL++;
   }
+  // the signatures become those of the text up to each word (as the mask path stores them): one sequential pass
+  simt_sync();
+  if (lane == 0) for (uint32_t e = 1; e < W; e++) wsg[e] = tb_sig_cat(wsg[e - 1], wsg[e], wl[e]);
+  simt_sync();
   out.W = W; out.NL = NL; out.flags = flags; out.nchars = nchars;
 }
 // Words one tile can stage (five 32-bit words each).  A tile can end up to 23 * 32 words (two words per three

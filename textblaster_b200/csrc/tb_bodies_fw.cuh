@@ -65,6 +65,7 @@ TB_D void body_fw_scan(const KBatch& a, const uint16_t* s_ascii, const LutEntry*
   const uint64_t ub = tb_lunit(R.rs, d);
   uint64_t* lh = s.lh + ub; uint32_t* ll = s.ll + ub;
   const uint64_t* powtab = a.uc.powtab;
+  const uint32_t base1 = (uint32_t)(TB_LDG(powtab + 1) >> 32), base2 = (uint32_t)TB_LDG(powtab + 1);  // the context's hash bases
   const uint32_t below_lane = tb_below(lane);
   uint32_t NLc = 0;                                                   // lines emitted so far (uniform)
   uint32_t n_stop = 0, n_short = 0, n_words = 0, n_nl = 0, flags = 0;  // this lane's share
@@ -146,7 +147,7 @@ TB_D void body_fw_scan(const KBatch& a, const uint16_t* s_ascii, const LutEntry*
             la = 0; lb_ = 0; ln = 0; lc = 0;
           } else if (!((SKq >> j) & 1u)) {
             const uint32_t byte = (x >> (8 * j)) & 0xFFu;
-            la = tb_hpush(la, TB_B1, byte + 1u); lb_ = tb_hpush(lb_, TB_B2, byte + 1u); ln++;
+            la = tb_hpush(la, base1, byte + 1u); lb_ = tb_hpush(lb_, base2, byte + 1u); ln++;
             lc += (LDq >> j) & 1u;
           }
         }

@@ -293,11 +293,13 @@ TB_D bool gr_doc_tiles(const KBatch& a, const LutEntry* lut, uint32_t* stage, co
   uint64_t* wh = s.wh + uw; uint32_t* wl = s.wl + uw; uint64_t* wsg = s.ws + uw;
   uint64_t* lh = s.lh + ul; uint32_t* ll = s.ll + ul; uint8_t* lg = s.lg + ul;
   const uint64_t* powtab = a.uc.powtab;
+  const uint32_t base1 = (uint32_t)(TB_LDG(powtab + 1) >> 32), base2 = (uint32_t)TB_LDG(powtab + 1);  // the context's hash bases
   const uint32_t below_lane = tb_below(lane);
   uint32_t W = 0, NLc = 0, flags = 0;
   uint64_t nchars = 0;
   HLS wcarry{{0u, 0u, 0u}, 0ull};
   HL lcarry{0u, 0u, 0u};
+  uint64_t sig_carry = 0;  // signature of the text's words up to the last one stored (its last 16 bytes)
   uint32_t wcarry_wc = 0;
   feed.begin(R.t, a.ext_lo, a.ext_hi, tb_tile_origin(R), R.re, lane);
   for (int64_t base = tb_tile_origin(R); base < R.re; base += TB_TILE) {
@@ -366,7 +368,7 @@ TB_D bool gr_doc_tiles(const KBatch& a, const LutEntry* lut, uint32_t* stage, co
             hwa = head ? wa : hwa; hwb = head ? wb : hwb; hwn = head ? wn : hwn; hwsig = head ? wsig : hwsig;
             wa = brk ? 0u : wa; wb = brk ? 0u : wb; wn = brk ? 0u : wn; wsig = brk ? 0ull : wsig;
           }
-          wa = tb_hpush(wa, TB_B1, byte + 1u); wb = tb_hpush(wb, TB_B2, byte + 1u); wn++; wsig = tb_sig_push(wsig, byte);
+          wa = tb_hpush(wa, base1, byte + 1u); wb = tb_hpush(wb, base2, byte + 1u); wn++; wsig = tb_sig_push(wsig, byte);
           if ((NLq >> j) & 1u) {
             if (j == fnq) { hla = la; hlb = lb_; hln = ln; }
             else if (ln) {
@@ -375,7 +377,7 @@ TB_D bool gr_doc_tiles(const KBatch& a, const LutEntry* lut, uint32_t* stage, co
             }
             la = 0; lb_ = 0; ln = 0;
           } else {
-            la = tb_hpush(la, TB_B1, byte + 1u); lb_ = tb_hpush(lb_, TB_B2, byte + 1u); ln++;
+            la = tb_hpush(la, base1, byte + 1u); lb_ = tb_hpush(lb_, base2, byte + 1u); ln++;
           }
         }
 #pragma unroll
@@ -409,7 +411,18 @@ TB_D bool gr_doc_tiles(const KBatch& a, const LutEntry* lut, uint32_t* stage, co
       }
       // the tile's words, in order: reduce and store them with all lanes busy
       simt_sync();
-      for (uint32_t j = (uint32_t)lane; j < wtot; j += 32) { wh[W + j] = hl_pack(hl_fold(st_a[j], st_b[j], st_n[j])); wl[W + j] = st_n[j]; wsg[W + j] = st_s[j]; }
+      // (the signature stored with a word covers the last 16 bytes of all the words up to it: short words take
+      // the missing bytes from the words before them -- in the staging arrays, or before this tile: sig_carry)
+      uint64_t last_sig = 0;
+      for (uint32_t j = (uint32_t)lane; j < wtot; j += 32) {
+        wh[W + j] = hl_pack(hl_fold(st_a[j], st_b[j], st_n[j])); wl[W + j] = st_n[j];
+        uint64_t sig = st_s[j];
+        uint32_t filled = st_n[j], k = j;
+        while (filled < 16u && k > 0u) { k--; sig |= st_s[k] << (4u * filled); filled += st_n[k]; }
+        if (filled < 16u) sig |= sig_carry << (4u * filled);
+        wsg[W + j] = sig; last_sig = sig;
+      }
+      if (wtot) sig_carry = simt_shfl(last_sig, (int)((wtot - 1u) & 31u));
       simt_sync();
       // "word character seen" of the fragment open after lane 31
       if (brk_lanes) wcarry_wc = (twc_lanes & ~tb_below(31 - tb_clz32(brk_lanes))) != 0u;
@@ -437,7 +450,7 @@ TB_D bool gr_doc_tiles(const KBatch& a, const LutEntry* lut, uint32_t* stage, co
     W += wtot; NLc += ltot;
   }
   if (wcarry_wc && wcarry.h.len) {  // the word / the piece that runs to the end of the text
-    if (lane == 0) { wh[W] = hl_pack(wcarry.h); wl[W] = wcarry.h.len; wsg[W] = wcarry.sig; }
+    if (lane == 0) { wh[W] = hl_pack(wcarry.h); wl[W] = wcarry.h.len; wsg[W] = tb_sig_cat(sig_carry, wcarry.sig, wcarry.h.len); }
     W++;
   }
   if (lcarry.len) {

@@ -132,11 +132,14 @@ TB_HD uint32_t tb_simple_lower(const UcTables& u, uint32_t cp) {
 // H(b_0..b_{L-1}) = sum (b_k + 1) * B^(L-1-k)  mod p,  p = 2^31 - 1, two independent bases.
 // It composes under concatenation: H(xy) = H(x) * B^|y| + H(y), which is what the concatenated
 // n-gram keys of find_all_duplicate (text.rs:250) need.  Two keys are treated as equal when both
-// 31-bit residues AND the byte length agree; for two distinct strings of length <= L the
-// probability of that over the choice of bases is <= (L / 2^29)^2.
+// 31-bit residues agree.  The two bases are drawn at random when a context is created (tb_ctx_create; below 2^29, which
+// lets tb_hpush skip the reduction between steps) and reach the kernels as entry 1 of the power table: for two different
+// strings of length <= L the two residues agree with probability <= (L / 2^28)^2 over that draw, whatever the text.
 #define TB_P31 0x7FFFFFFFu
-#define TB_B1 0x1F0B4A27u  // < 2^29: lets tb_hpush (tb_tile.cuh) skip the reduction between steps
-#define TB_B2 0x0C4D3A11u  // < 2^29
+#define TB_BASE_BITS 29
+// the fixed pair the tests and the host emulation use (any pair in [2^28, 2^29) does)
+#define TB_B1_DEFAULT 0x1F0B4A27u
+#define TB_B2_DEFAULT 0x0C4D3A11u
 TB_HD uint32_t tb_mm(uint32_t a, uint32_t b) {  // a, b <= p  ->  result <= p (p itself stands for 0)
   uint64_t x = (uint64_t)a * b;
   x = (x & TB_P31) + (x >> 31);
@@ -152,7 +155,8 @@ TB_HD uint32_t tb_canon31(uint32_t x) { return x == TB_P31 ? 0u : x; }
 struct Hash2 {
   uint32_t a, b;
   TB_HD void init() { a = 0; b = 0; }
-  TB_HD void push(uint32_t byte) { a = tb_am(tb_mm(a, TB_B1), byte + 1u); b = tb_am(tb_mm(b, TB_B2), byte + 1u); }
+  // pw1: the packed bases (entry 1 of the power table)
+  TB_HD void push(uint32_t byte, uint64_t pw1) { a = tb_am(tb_mm(a, (uint32_t)(pw1 >> 32)), byte + 1u); b = tb_am(tb_mm(b, (uint32_t)pw1), byte + 1u); }
   TB_HD uint64_t pack() const { return ((uint64_t)tb_canon31(a) << 32) | tb_canon31(b); }
 };
 TB_HD Hash2 tb_unpack(uint64_t v) { Hash2 h; h.a = (uint32_t)(v >> 32); h.b = (uint32_t)v; return h; }
@@ -166,7 +170,8 @@ TB_HD Hash2 tb_hcat(Hash2 x, Hash2 y, uint64_t pw) {
 TB_HD uint64_t tb_pow_pack(const uint64_t* powtab, uint64_t len) {
   if (len < TB_POWTAB) return TB_LDG(powtab + len);
   // square-and-multiply for the rare long element
-  uint32_t ra = 1, rb = 1, ba = TB_B1, bb = TB_B2;
+  const uint64_t pw1 = TB_LDG(powtab + 1);
+  uint32_t ra = 1, rb = 1, ba = (uint32_t)(pw1 >> 32), bb = (uint32_t)pw1;
   uint64_t e = len;
   while (e) {
     if (e & 1) { ra = tb_mm(ra, ba); rb = tb_mm(rb, bb); }
@@ -183,6 +188,11 @@ TB_HD uint64_t tb_sig_push(uint64_t s, uint32_t byte) { return (s << 4) | (uint6
 TB_HD uint64_t tb_sig_cat(uint64_t x, uint64_t y, uint32_t ylen) { return ylen >= 16u ? y : (y | (x << (4u * ylen))); }  // x followed by y
 TB_HD uint64_t tb_sig_mask(uint32_t k) { return k >= 16u ? ~0ull : ((1ull << (4u * k)) - 1ull); }
 
+// the power table of a pair of bases: out[k] = (B1^k mod p) << 32 | (B2^k mod p), k < TB_POWTAB
+TB_HD void tb_fill_powtab(uint64_t* out, uint32_t b1, uint32_t b2) {
+  uint32_t a = 1, b = 1;
+  for (int i = 0; i < TB_POWTAB; i++) { out[i] = ((uint64_t)a << 32) | b; a = tb_mm(a, b1); b = tb_mm(b, b2); }
+}
 TB_HD uint64_t tb_mix64(uint64_t x) {  // splitmix64 finaliser, for table slot selection only
   x ^= x >> 30; x *= 0xBF58476D1CE4E5B9ull; x ^= x >> 27; x *= 0x94D049BB133111EBull; x ^= x >> 31;
   return x;

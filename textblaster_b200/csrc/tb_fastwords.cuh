@@ -156,7 +156,7 @@ TB_HD uint32_t tb_walk_words_fast(const Classifier& C, const TextRange& R, int64
     WordInfo wi;
     wi.start = w.base + s; wi.end = w.base + e; wi.nchars = e - s;
     wi.alpha = (w.A & seg) ? 1u : 0u;
-    if (MODE & WM_NEED_HASH) { wi.hash.init(); for (int64_t i = wi.start; i < wi.end; i++) wi.hash.push(tb_byte(R.t, i)); }
+    if (MODE & WM_NEED_HASH) { const uint64_t pw1 = TB_LDG(C.u.powtab + 1); wi.hash.init(); for (int64_t i = wi.start; i < wi.end; i++) wi.hash.push(tb_byte(R.t, i), pw1); }
     if (MODE & WM_NEED_LOWKEY) {
       wi.key.init();
       const uint32_t len = e - s;

@@ -68,7 +68,8 @@ TB_HD uint32_t tb_wunits_of(int64_t len) { return (uint32_t)((2 * len) / 3) + 1u
 // scratch of the repetition filter; word arrays are indexed from tb_wunit(rs[d], d), line arrays from tb_lunit(rs[d], d)
 struct GrScratch {
   uint64_t* wh; uint32_t* wl;               // words: hash, byte length
-  uint64_t* ws;                             //        suffix signature (tb_sig_push over the word's bytes)
+  uint64_t* ws;                             //        suffix signature of the words up to and including this one (tb_sig_push over
+                                            //        their bytes: the last 16 bytes of the concatenation that ends with the word)
   uint64_t* lh; uint32_t* ll; uint8_t* lg;  // line pieces: hash, byte length, "preceded by >= 2 newlines"
   GrDoc* doc;                               // [n]
   uint32_t* work;                           // tier-X work area, TB_REP_K words per word unit + TB_REP_DOC_EXTRA per doc

@@ -159,7 +159,7 @@ TB_HD void gr_lane(const Classifier& C, const TextRange& R, int64_t p0, int64_t 
       if (!o.has_nl) { o.has_nl = 1; o.first_nl = (uint32_t)(i - p0); o.head = cur; o.head_len = cur_len; }
       else if (cur_len) { o.ph[o.np] = cur.pack(); o.pl[o.np] = cur_len; o.pend[o.np] = (uint32_t)(i - p0); o.np++; }
       cur.init(); cur_len = 0;
-    } else { cur.push(b); cur_len++; }
+    } else { cur.push(b, TB_LDG(C.u.powtab + 1)); cur_len++; }
   }
   o.tail = cur; o.tail_len = cur_len;
 }

@@ -83,7 +83,7 @@ int setup_device(int dev, DeviceState** out) {
       return d;
     };
     uint64_t pw[TB_POWTAB];
-    { uint32_t a = 1, b = 1; for (int i = 0; i < TB_POWTAB; i++) { pw[i] = ((uint64_t)a << 32) | b; a = tb_mm(a, TB_B1); b = tb_mm(b, TB_B2); } }
+    tb_fill_powtab(pw, TB_B1_DEFAULT, TB_B2_DEFAULT);  // (a fixed pair: this entry point keeps no per-process state beyond the scratch)
     unsigned char* s1 = place(tb_uc_stage1, sizeof tb_uc_stage1);
     unsigned char* s2 = place(tb_uc_stage2, sizeof tb_uc_stage2);
     unsigned char* lo = place(tb_uc_lower, sizeof tb_uc_lower);

@@ -291,7 +291,7 @@ TB_D void rep_lines_small(const uint64_t* lh, const uint32_t* ll, const uint8_t*
     const uint32_t ua = simt_shfl_up(v.a, off), ub = simt_shfl_up(v.b, off), ul = simt_shfl_up(vl, off), uf = simt_shfl_up(f, off);
     if (lane >= off && !f && holder) {
       Hash2 x; x.a = ua; x.b = ub;
-      x.push('\n');
+      x.push('\n', TB_LDG(powtab + 1));
       v = tb_hcat(x, v, tb_pow_pack(powtab, vl));
       vl += ul + 1u; f = uf;
     }
@@ -374,7 +374,7 @@ TB_D void rep_top_small(const uint64_t* wh, const uint32_t* woff, const uint64_t
     if (v) {
 #pragma unroll 1
       for (uint32_t j = i + cur; j < i + n; j++) {
-        h.push(' ');
+        h.push(' ', TB_LDG(powtab + 1));
         h = tb_hcat(h, tb_unpack(TB_LDG(wh + j)), tb_pow_pack(powtab, woff[j + 1] - woff[j]));
       }
     }
@@ -454,7 +454,7 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
       Hash2 hk = tb_unpack(lh[k]);
       if (k == 0) { cur = hk; curlen = ll[k]; continue; }
       if (lg[k]) { A.H[NP] = cur.pack(); A.woff[NP] = curlen; NP++; cur = hk; curlen = ll[k]; }
-      else { cur.push('\n'); cur = tb_hcat(cur, hk, tb_pow_pack(a.uc.powtab, ll[k])); curlen += 1 + ll[k]; }
+      else { cur.push('\n', TB_LDG(a.uc.powtab + 1)); cur = tb_hcat(cur, hk, tb_pow_pack(a.uc.powtab, ll[k])); curlen += 1 + ll[k]; }
     }
     if (NL) { A.H[NP] = cur.pack(); A.woff[NP] = curlen; NP++; }
   }
@@ -536,7 +536,7 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
         Hash2 h = tb_unpack(cur ? A.H[i] : TB_LDG(wh + i));
 #pragma unroll 1
         for (uint32_t j = i + (cur ? cur : 1u); j < i + n; j++) {
-          h.push(' ');
+          h.push(' ', TB_LDG(a.uc.powtab + 1));
           h = tb_hcat(h, tb_unpack(TB_LDG(wh + j)), tb_pow_pack(a.uc.powtab, woff[j + 1] - woff[j]));
         }
         A.H[i] = h.pack();
@@ -620,31 +620,23 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
         m = 0xFFFFFFFFu - (uint32_t)g.max64((uint64_t)(0xFFFFFFFFu - m));
         const uint32_t k = m < 16u ? m : 16u;
         if (k >= TB_REP_SIG_MIN) {
-          // word ends whose last k key bytes occur at another word end too (signature in A.H, first end per value in the table)
+          // word ends whose last k key bytes occur at another word end too (first end per value in the table)
           const uint64_t mask = tb_sig_mask(k);
           const uint32_t T = rep_tab_size(W - n + 1);
 #pragma unroll 1
           for (uint32_t i = g.tid; i < T; i += g.size()) tab[i] = EMPTY;
 #pragma unroll 1
           for (uint32_t i = g.tid; i < fw; i += g.size()) A.flag[i] = 0;
-#pragma unroll 1
-          for (uint32_t e = n - 1 + g.tid; e < W; e += g.size()) {
-            uint64_t sig = TB_LDG(wsg + e);
-            uint32_t filled = woff[e + 1] - woff[e];
-#pragma unroll 1
-            for (uint32_t j = e; filled < k; ) { j--; sig |= TB_LDG(wsg + j) << (4u * filled); filled += woff[j + 1] - woff[j]; }
-            A.H[e] = sig & mask;
-          }
           g.sync();
 #pragma unroll 1
           for (uint32_t e = n - 1 + g.tid; e < W; e += g.size()) {
-            const uint64_t key = A.H[e];
+            const uint64_t key = TB_LDG(wsg + e) & mask;  // the last k bytes of the words up to e (the scan pass stores 16 of them)
             uint32_t sl = rep_slot(tb_mix64(key), T);
 #pragma unroll 1
             for (;;) {
               uint32_t old = idx_cas(&tab[sl], EMPTY, e);
               if (old == EMPTY) break;
-              if (A.H[old] == key) { simt_atomic_or(&A.flag[e >> 5], 1u << (e & 31)); simt_atomic_or(&A.flag[old >> 5], 1u << (old & 31)); break; }
+              if ((TB_LDG(wsg + old) & mask) == key) { simt_atomic_or(&A.flag[e >> 5], 1u << (e & 31)); simt_atomic_or(&A.flag[old >> 5], 1u << (old & 31)); break; }
               sl = rep_next(sl, T);
             }
           }

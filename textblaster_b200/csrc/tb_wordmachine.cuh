@@ -211,7 +211,7 @@ struct SegAcc {
       if (MODE & WM_NEED_ALPHA) alpha |= (ci & CI_ALPHA);
     }
     nchars_run++;
-    if (MODE & WM_NEED_HASH) for (int k = 0; k < len; k++) h_run.push(tb_byte(t, i + k));
+    if (MODE & WM_NEED_HASH) { const uint64_t pw1 = TB_LDG(C.u.powtab + 1); for (int k = 0; k < len; k++) h_run.push(tb_byte(t, i + k), pw1); }
     if (MODE & WM_NEED_LOWKEY) lowkey_push(C, k_run, cp, ci);
   }
   // returns true and fills w if the closed segment is a word (text.rs:139-157)
