@@ -423,6 +423,7 @@ def run_config3(args, rank):
     import torch
 
     import config3_sweep
+    from textblaster_b200 import _abi
     from textblaster_b200.config import GopherRepetitionParams
     from textblaster_b200.executor import GpuBatchPipeline
 
@@ -440,6 +441,8 @@ def run_config3(args, rank):
     for kind in ("top_n_grams", "dup_n_grams"):
         for order in range(2, 11):
             p = GpuBatchPipeline([GopherRepetitionParams(**{kind: [(order, 0.2 if kind == "top_n_grams" else 0.15)]})])
+            if args.bulk_stage_tiles:
+                p.set_option(_abi.TB_OPT_BULK_STAGE_TILES, args.bulk_stage_tiles)
             for _ in range(max(args.warmup, 1)):
                 p.run_packed(utf8, off)
             p.reset_kernel_times()
@@ -669,6 +672,7 @@ def main():
                     help="where the text of the end-to-end step lives: pinned host memory (default) or pageable memory as Arrow allocates it "
                          "(the library then stages it through its own pinned ring, TB_OPT_STAGE_THREADS)")
     ap.add_argument("--stage-threads", type=int, default=-1, help="TB_OPT_STAGE_THREADS for --host-memory pageable (-1: library default, 0: off)")
+    ap.add_argument("--bulk-stage-tiles", type=int, default=0, help="TB_OPT_BULK_STAGE_TILES: bulk-copy staging of documents of at least this many 1 KiB tiles (0: off)")
     ap.add_argument("--gather-threads", type=int, default=0, help="host threads of TB_OPT_GATHER_KEPT (0: min(8, cpus / ranks))")
     ap.add_argument("--with-fineweb", action="store_true",
                     help="append FineWebQualityFilter (SURVEY 8(f) row 3) to the chain; not the headline workload")
@@ -738,6 +742,8 @@ def main():
     pipe.set_option(_abi.TB_OPT_CHUNK_BYTES, args.chunk_mb << 20)
     if args.decode_entities:
         pipe.set_option(_abi.TB_OPT_DECODE_HTML_ENTITIES, 1)
+    if args.bulk_stage_tiles:
+        pipe.set_option(_abi.TB_OPT_BULK_STAGE_TILES, args.bulk_stage_tiles)
     runs_mode = args.content == "runs" and not args.decode_entities
     pipe.set_option(_abi.TB_OPT_RETURN_CONTENT, 2 if runs_mode else 1)
     # runs mode: the end-to-end call also rebuilds the content of the kept documents (what the writer of the output

@@ -353,6 +353,10 @@ enum {
                                      staged by the library: this many host threads copy it piece by piece into a ring of pinned slots
                                      (3 x 64 MiB) from which it goes to the device, instead of the driver's slow path for pageable
                                      copies.  Pinned or registered memory is detected and copied from where it is.  0: never stage */
+  TB_OPT_BULK_STAGE_TILES = 9,  /* [0] documents of at least this many 1 KiB tiles have their text brought into shared memory by the copy engine
+                                     (cp.async.bulk + mbarrier, a two-tile ring per warp) instead of per-lane vector loads in the
+                                     GopherQuality, repetition-scan and C4 A / B passes.  0: off -- measured slower on B200 for this chain
+                                     (the passes re-read bytes of the tile through L1, which a bulk copy bypasses) */
   TB_OPT_GATHER_KEPT = 6        /* [0] with TB_OPT_RETURN_CONTENT = 2 and host input: number of host threads that copy the content of the
                                      kept documents out of the caller's input column (kept_content / kept_offsets of tb_batch_out), chunk
                                      by chunk behind the device; 0: the caller gathers what it needs itself (tb_gather_content) */

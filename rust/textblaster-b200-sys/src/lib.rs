@@ -84,6 +84,7 @@ pub const TB_OPT_DECODE_HTML_ENTITIES: i32 = 5;
 pub const TB_OPT_GATHER_KEPT: i32 = 6;
 pub const TB_OPT_CHUNK_RAMP: i32 = 7;
 pub const TB_OPT_STAGE_THREADS: i32 = 8;
+pub const TB_OPT_BULK_STAGE_TILES: i32 = 9;
 
 pub const TB_NOALLOC_MAX_DOCS: i64 = 2048;
 pub const TB_NOALLOC_MAX_BYTES: i64 = 512 * 1024;

@@ -504,3 +504,24 @@ def test_pageable_input_is_staged_by_the_library():
     ores = oracle.OraclePipeline(steps).run_packed(utf8, off.astype(np.int64), nthreads=NCPU)
     compare(ores, ref.keep, ref.failed_step, ref.stats, None, step_types(steps), None, label="staged")
     p.close()
+
+
+@pytest.mark.parametrize("name", ["baseline_order", "shipped_order", "c4_then_open", "gq_shipped"])
+def test_bulk_copy_staging_of_long_documents(name):
+    """TB_OPT_BULK_STAGE_TILES: the tiles of long documents arrive in shared memory by cp.async.bulk (tb_feed.cuh) instead of
+    per-lane loads.  Same results on every document: long and short ones mixed, documents the mask path hands to the
+    walking path in the middle (the ring must be drained), the first and last tiles of the buffer (not staged)."""
+    steps = CHAINS[name]
+    rng = random.Random(61)
+    texts = [fuzzgen.english_doc(rng, sz) for sz in (300, 2100, 4096, 5000, 9000, 20000, 70000, 150000)]
+    texts += fuzzgen.FuzzGen(62).docs(40, max_lines=200) + multilingual.corpus(6, 40)
+    texts += ["plain words " * 900 + "a\u202fb mixed white space in a word here " + "tail words " * 700]   # exotic segment deep inside a long document
+    texts += [fuzzgen.english_doc(rng, 30000)]
+    p = GpuBatchPipeline(steps)
+    for tiles in (2, 8):
+        p.set_option(_abi.TB_OPT_BULK_STAGE_TILES, tiles)
+        res = p.run_texts(texts)
+        ores = oracle.OraclePipeline(steps).run_texts(texts, nthreads=NCPU)
+        contents = [res.content_of(i) for i in range(res.n_docs)] if res.content is not None else None
+        compare(ores, res.keep, res.failed_step, res.stats, contents, step_types(steps), texts, label=name + "/bulk%d" % tiles)
+    p.close()

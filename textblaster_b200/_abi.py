@@ -81,6 +81,7 @@ TB_OPT_DECODE_HTML_ENTITIES = 5
 TB_OPT_GATHER_KEPT = 6
 TB_OPT_CHUNK_RAMP = 7
 TB_OPT_STAGE_THREADS = 8
+TB_OPT_BULK_STAGE_TILES = 9
 
 
 class tb_c4_params(C.Structure):

@@ -202,16 +202,18 @@ struct KTime { const char* name; double ms; int64_t launches; };
 
 struct tb_ctx {
   int device = 0, sm_count = 148;
-  cudaStream_t compute = nullptr, copy = nullptr, d2h = nullptr, side = nullptr;
-  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   UcTables uc{};
   DevBuf t_stage1, t_stage2, t_lower, t_cased, t_caseign, t_pow, t_ent;
 };
 
 struct tb_pipeline {
   tb_ctx* ctx = nullptr;
+  // every pipeline has streams of its own: pipelines of one context run beside each other on the device, a call waits
+  // for its own work only, and the per-kernel event times of one pipeline hold none of another's kernels
+  cudaStream_t compute = nullptr, copy = nullptr, d2h = nullptr, side = nullptr;
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   std::vector<StepHost> steps;
-  int64_t opt_return_content = 1, opt_validate = 0, opt_chunk = 1024ll << 20, opt_debug = 0, opt_decode = 0, opt_gather = 0, opt_ramp = 1, opt_stage = 4;
+  int64_t opt_return_content = 1, opt_validate = 0, opt_chunk = 1024ll << 20, opt_debug = 0, opt_decode = 0, opt_gather = 0, opt_ramp = 1, opt_stage = 4, opt_bulk = 0;
   HostBuf stage_slots[Stager::kSlots]; cudaEvent_t stage_ev[Stager::kSlots] = {nullptr, nullptr, nullptr}; bool stage_used[Stager::kSlots] = {false, false, false};
   std::vector<cudaEvent_t> ev_gather;  // one per chunk of a call (TB_OPT_GATHER_KEPT)
   std::mutex mu;
@@ -263,9 +265,9 @@ struct Timed {  // brackets one kernel launch with events on the compute stream
   tb_pipeline* p; int k; cudaEvent_t a, b;
   Timed(tb_pipeline* p_, const char* name) : p(p_) {
     k = ktime_index(p, name); a = next_event(p); b = next_event(p);
-    cudaEventRecord(a, p->ctx->compute);
+    cudaEventRecord(a, p->compute);
   }
-  ~Timed() { cudaEventRecord(b, p->ctx->compute); p->pending.push_back({k, a, b}); p->launches_this_run++; }
+  ~Timed() { cudaEventRecord(b, p->compute); p->pending.push_back({k, a, b}); p->launches_this_run++; }
 };
 void resolve_times(tb_pipeline* p) {
   for (auto& q : p->pending) {
@@ -544,14 +546,14 @@ int ensure_chunk_buffers(tb_pipeline* p, int64_t n, int64_t nb, bool host_input)
 int enqueue_chain(tb_pipeline* p, const uint8_t* text, int64_t n, int64_t nbytes, int pb, int content_mode, bool* has_c4) {
   const bool want_content = content_mode != 0;
   tb_ctx* c = p->ctx;
-  cudaStream_t st = c->compute;
+  cudaStream_t st = p->compute;
   CK(cudaMemcpyAsync(p->rs.p, p->rs0.p, (size_t)n * 8, cudaMemcpyDeviceToDevice, st));
   CK(cudaMemcpyAsync(p->re.p, p->re0.p, (size_t)n * 8, cudaMemcpyDeviceToDevice, st));
   CK(cudaMemsetAsync(p->rewritten.p, 0, (size_t)n, st));
   CK(cudaMemsetAsync(p->cursors.p, 0, 256, st));
   uint32_t* cursors = p->cursors.as<uint32_t>();  // [0, 3 * TB_MAX_STEPS): kernel cursors; [48], [49]: counts of the work order
   KBatch b{text, p->rs.as<int64_t>(), p->re.as<int64_t>(), p->alive[pb].as<uint8_t>(), p->failed[pb].as<int8_t>(), n, c->uc, 0, nbytes,
-           (uint32_t)p->opt_debug, p->order.as<uint32_t>(), cursors + 48, p->sizecls.as<uint8_t>()};
+           (uint32_t)p->opt_debug, p->order.as<uint32_t>(), cursors + 48, p->sizecls.as<uint8_t>(), (uint32_t)p->opt_bulk};
   { Timed t(p, "k_order"); tb_launch_order(st, p->rs0.as<int64_t>(), p->re0.as<int64_t>(), n, p->order.as<uint32_t>(), cursors + 48, p->sizecls.as<uint8_t>()); }
   *has_c4 = false;
   if (p->opt_validate) {  // p->bad counts over the whole run (cleared by run_impl)
@@ -570,15 +572,15 @@ int enqueue_chain(tb_pipeline* p, const uint8_t* text, int64_t n, int64_t nbytes
       { Timed t(p, "k_trim"); tb_launch_trim(st, b, p->ts.as<int64_t>(), p->te.as<int64_t>()); }
       { Timed t(p, "k_gr_scan"); tb_launch_gr_scan(st, b, p->ts.as<int64_t>(), p->te.as<int64_t>(), g, c->sm_count); }
       // the few documents of tier X (each a long chain of passes on one CTA) run beside the other tiers
-      CK(cudaEventRecord(c->ev_fork, st));
-      CK(cudaStreamWaitEvent(c->side, c->ev_fork, 0));
-      tb_launch_gr_rep(c->side, b, p->ts.as<int64_t>(), p->te.as<int64_t>(), g, sh.gr, (int)s, p->stats[s][pb].as<tb_gr_stats>(), c->sm_count, 3);
-      CK(cudaEventRecord(c->ev_join, c->side));
+      CK(cudaEventRecord(p->ev_fork, st));
+      CK(cudaStreamWaitEvent(p->side, p->ev_fork, 0));
+      tb_launch_gr_rep(p->side, b, p->ts.as<int64_t>(), p->te.as<int64_t>(), g, sh.gr, (int)s, p->stats[s][pb].as<tb_gr_stats>(), c->sm_count, 3);
+      CK(cudaEventRecord(p->ev_join, p->side));
       p->launches_this_run++;
       { Timed t(p, "k_gr_rep_s"); tb_launch_gr_rep(st, b, p->ts.as<int64_t>(), p->te.as<int64_t>(), g, sh.gr, (int)s, p->stats[s][pb].as<tb_gr_stats>(), c->sm_count, 0); }
       { Timed t(p, "k_gr_rep_m"); tb_launch_gr_rep(st, b, p->ts.as<int64_t>(), p->te.as<int64_t>(), g, sh.gr, (int)s, p->stats[s][pb].as<tb_gr_stats>(), c->sm_count, 1); }
       { Timed t(p, "k_gr_rep_l"); tb_launch_gr_rep(st, b, p->ts.as<int64_t>(), p->te.as<int64_t>(), g, sh.gr, (int)s, p->stats[s][pb].as<tb_gr_stats>(), c->sm_count, 2); }
-      { Timed t(p, "k_gr_rep_x(join)"); CK(cudaStreamWaitEvent(st, c->ev_join, 0)); }
+      { Timed t(p, "k_gr_rep_x(join)"); CK(cudaStreamWaitEvent(st, p->ev_join, 0)); }
     } else if (sh.type == TB_STEP_FINEWEB_QUALITY) {
       FwScratch fs{p->f_lh.as<uint64_t>(), p->f_ll.as<uint32_t>(), p->f_doc.as<FwDoc>(), p->f_tab.as<uint32_t>()};
       { Timed t(p, "k_fw_scan"); tb_launch_fw_scan(st, b, sh.fw, fs, c->sm_count, cursors + s); }
@@ -726,7 +728,7 @@ int run_impl(tb_pipeline* p, const uint8_t* utf8, const void* offsets, int is64,
       p->stage_used[i] = false;
     }
     stager.slots = p->stage_slots; stager.slot_ev = p->stage_ev; stager.slot_used = p->stage_used;
-    stager.copy = c->copy; stager.T = (int)std::min<int64_t>(p->opt_stage, 16); stager.device = c->device;
+    stager.copy = p->copy; stager.T = (int)std::min<int64_t>(p->opt_stage, 16); stager.device = c->device;
     stager.start();
     if (trace) fprintf(stderr, "[tb] %.2f ms: pageable input: staged through %d pinned slots of %zu MB with %d copy threads\n", since(), Stager::kSlots, Stager::kSlotBytes >> 20, stager.T);
   }
@@ -740,12 +742,12 @@ int run_impl(tb_pipeline* p, const uint8_t* utf8, const void* offsets, int is64,
                    (size_t)(ch.d1 - ch.d0 + 1) * osz, p->offs[buf].p, p->ev_done[buf], p->ev_h2d[buf]});
       return TB_OK;
     }
-    CK(cudaStreamWaitEvent(c->copy, p->ev_done[buf], 0));
+    CK(cudaStreamWaitEvent(p->copy, p->ev_done[buf], 0));
     int64_t nb = ch.b1 - ch.b0, n = ch.d1 - ch.d0;
-    if (nb) CK(cudaMemcpyAsync(p->text[buf].p, utf8 + ch.b0, (size_t)nb, cudaMemcpyHostToDevice, c->copy));
+    if (nb) CK(cudaMemcpyAsync(p->text[buf].p, utf8 + ch.b0, (size_t)nb, cudaMemcpyHostToDevice, p->copy));
     size_t osz = is64 ? 8 : 4;
-    CK(cudaMemcpyAsync(p->offs[buf].p, (const uint8_t*)offsets + (size_t)ch.d0 * osz, (size_t)(n + 1) * osz, cudaMemcpyHostToDevice, c->copy));
-    CK(cudaEventRecord(p->ev_h2d[buf], c->copy));
+    CK(cudaMemcpyAsync(p->offs[buf].p, (const uint8_t*)offsets + (size_t)ch.d0 * osz, (size_t)(n + 1) * osz, cudaMemcpyHostToDevice, p->copy));
+    CK(cudaEventRecord(p->ev_h2d[buf], p->copy));
     return TB_OK;
   };
 
@@ -763,15 +765,15 @@ int run_impl(tb_pipeline* p, const uint8_t* utf8, const void* offsets, int is64,
       if (content_mode == 2 && tot > (ch.b1 - ch.b0) / 8 + n)
         return fail(TB_ERR_UNSUPPORTED, "content too fragmented for TB_OPT_RETURN_CONTENT = 2 (more than one run per 8 bytes of text in a chunk): use 1");
       for (int64_t i = 0; i <= n; i++) h_coff[ch.d0 + i] += content_base;  // chunk-relative -> absolute
-      if (tot) CK(cudaMemcpyAsync(h_content + (size_t)content_base * esz, p->packed[buf].p, (size_t)tot * esz, cudaMemcpyDeviceToHost, c->d2h));
+      if (tot) CK(cudaMemcpyAsync(h_content + (size_t)content_base * esz, p->packed[buf].p, (size_t)tot * esz, cudaMemcpyDeviceToHost, p->d2h));
       content_base += tot;
       if (gather_T > 0) {  // the chunk's runs are on their way: its kept documents can be gathered once they have landed
         while (p->ev_gather.size() <= ci) { cudaEvent_t e; CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); p->ev_gather.push_back(e); }
-        CK(cudaEventRecord(p->ev_gather[ci], c->d2h));
+        CK(cudaEventRecord(p->ev_gather[ci], p->d2h));
         gth.push({ch.d0, ch.d1, content_base, p->ev_gather[ci]});
       }
     }
-    CK(cudaEventRecord(p->ev_d2h[buf], c->d2h));
+    CK(cudaEventRecord(p->ev_d2h[buf], p->d2h));
     return TB_OK;
   };
 
@@ -781,7 +783,7 @@ int run_impl(tb_pipeline* p, const uint8_t* utf8, const void* offsets, int is64,
     gth.T = gather_T; gth.device = c->device;
     gth.start();
   }
-  if (p->opt_validate) CK(cudaMemsetAsync(p->bad.p, 0, 4, c->compute));
+  if (p->opt_validate) CK(cudaMemsetAsync(p->bad.p, 0, 4, p->compute));
   if (!chunks.empty()) if ((rc = enqueue_h2d(0))) return rc;
   for (size_t ci = 0; ci < chunks.size(); ci++) {
     const Chunk& ch = chunks[ci];
@@ -789,61 +791,61 @@ int run_impl(tb_pipeline* p, const uint8_t* utf8, const void* offsets, int is64,
     int64_t n = ch.d1 - ch.d0;
     if (ci + 1 < chunks.size()) if ((rc = enqueue_h2d(ci + 1))) return rc;
     // result buffers and packed[buf] may still be read by the copies of chunk ci-2
-    CK(cudaStreamWaitEvent(c->compute, p->ev_d2h[buf], 0));
+    CK(cudaStreamWaitEvent(p->compute, p->ev_d2h[buf], 0));
     const uint8_t* text;
     if (device_input) {
       text = utf8 + ch.b0;
-      tb_launch_init_ranges(c->compute, offsets_dev, 1, ch.d0, n, ch.b0, p->rs0.as<int64_t>(), p->re0.as<int64_t>(), p->alive[buf].as<uint8_t>(), p->failed[buf].as<int8_t>());
+      tb_launch_init_ranges(p->compute, offsets_dev, 1, ch.d0, n, ch.b0, p->rs0.as<int64_t>(), p->re0.as<int64_t>(), p->alive[buf].as<uint8_t>(), p->failed[buf].as<int8_t>());
     } else {
       if (staged) {  // the event is recorded by the staging thread: it must have been, before the compute stream can wait on it
         const cudaError_t e = stager.wait_recorded((int64_t)ci);
         if (e != cudaSuccess) return fail(TB_ERR_CUDA, std::string("staging thread: ") + cudaGetErrorString(e));
       }
-      CK(cudaStreamWaitEvent(c->compute, p->ev_h2d[buf], 0));
+      CK(cudaStreamWaitEvent(p->compute, p->ev_h2d[buf], 0));
       text = p->text[buf].as<uint8_t>();
-      tb_launch_init_ranges(c->compute, p->offs[buf].p, is64, 0, n, ch.b0, p->rs0.as<int64_t>(), p->re0.as<int64_t>(), p->alive[buf].as<uint8_t>(), p->failed[buf].as<int8_t>());
+      tb_launch_init_ranges(p->compute, p->offs[buf].p, is64, 0, n, ch.b0, p->rs0.as<int64_t>(), p->re0.as<int64_t>(), p->alive[buf].as<uint8_t>(), p->failed[buf].as<int8_t>());
     }
     p->launches_this_run++;
     int64_t text_extent = ch.b1 - ch.b0;
     if (p->opt_decode) {  // the decoded copy becomes the text, and its ranges the documents' original ranges
       const size_t bw = ((size_t)text_extent / 32 + 4) * 4;
-      CK(cudaMemsetAsync(p->e_amp.p, 0, bw, c->compute));
-      CK(cudaMemsetAsync(p->e_drop.p, 0, bw, c->compute));
-      CK(cudaMemsetAsync(p->cursors.p, 0, 256, c->compute));
+      CK(cudaMemsetAsync(p->e_amp.p, 0, bw, p->compute));
+      CK(cudaMemsetAsync(p->e_drop.p, 0, bw, p->compute));
+      CK(cudaMemsetAsync(p->cursors.p, 0, 256, p->compute));
       KBatch eb{text, p->rs0.as<int64_t>(), p->re0.as<int64_t>(), p->alive[buf].as<uint8_t>(), p->failed[buf].as<int8_t>(), n, c->uc, 0, text_extent,
-                0u, nullptr, nullptr, nullptr};
+                0u, nullptr, nullptr, nullptr, 0u};
       { Timed t(p, "k_entities");
-        tb_launch_entities(c->compute, eb, c->t_ent.as<EntEntry>(), TB_ENT_COUNT, p->e_amp.as<uint32_t>(), p->e_drop.as<uint32_t>(), p->e_D.as<uint8_t>(),
+        tb_launch_entities(p->compute, eb, c->t_ent.as<EntEntry>(), TB_ENT_COUNT, p->e_amp.as<uint32_t>(), p->e_drop.as<uint32_t>(), p->e_D.as<uint8_t>(),
                            p->e_drs.as<int64_t>(), p->e_dre.as<int64_t>(), c->sm_count, p->cursors.as<uint32_t>() + 51); }
-      CK(cudaMemcpyAsync(p->rs0.p, p->e_drs.p, (size_t)n * 8, cudaMemcpyDeviceToDevice, c->compute));
-      CK(cudaMemcpyAsync(p->re0.p, p->e_dre.p, (size_t)n * 8, cudaMemcpyDeviceToDevice, c->compute));
+      CK(cudaMemcpyAsync(p->rs0.p, p->e_drs.p, (size_t)n * 8, cudaMemcpyDeviceToDevice, p->compute));
+      CK(cudaMemcpyAsync(p->re0.p, p->e_dre.p, (size_t)n * 8, cudaMemcpyDeviceToDevice, p->compute));
       text = p->e_D.as<uint8_t>();
       text_extent = (int64_t)tb_grown_bytes(text_extent, n);
     }
     bool has_c4 = false;
     if ((rc = enqueue_chain(p, text, n, text_extent, buf, content_mode, &has_c4))) return rc;
-    CK(cudaEventRecord(p->ev_done[buf], c->compute));
+    CK(cudaEventRecord(p->ev_done[buf], p->compute));
     // the previous chunk's content goes out first (its copy must not queue behind this chunk's kernels)
     if (ci > 0) if ((rc = finish(ci - 1))) return rc;
     // small results
-    CK(cudaStreamWaitEvent(c->d2h, p->ev_done[buf], 0));
-    CK(cudaMemcpyAsync(h_keep + ch.d0, p->alive[buf].p, (size_t)n, cudaMemcpyDeviceToHost, c->d2h));
-    CK(cudaMemcpyAsync(h_failed + ch.d0, p->failed[buf].p, (size_t)n, cudaMemcpyDeviceToHost, c->d2h));
+    CK(cudaStreamWaitEvent(p->d2h, p->ev_done[buf], 0));
+    CK(cudaMemcpyAsync(h_keep + ch.d0, p->alive[buf].p, (size_t)n, cudaMemcpyDeviceToHost, p->d2h));
+    CK(cudaMemcpyAsync(h_failed + ch.d0, p->failed[buf].p, (size_t)n, cudaMemcpyDeviceToHost, p->d2h));
     for (size_t s = 0; s < p->steps.size(); s++) {
       size_t sz = stat_size(p->steps[s].type);
-      CK(cudaMemcpyAsync(rsx->stats[s].as<uint8_t>() + (size_t)ch.d0 * sz, p->stats[s][buf].p, (size_t)n * sz, cudaMemcpyDeviceToHost, c->d2h));
+      CK(cudaMemcpyAsync(rsx->stats[s].as<uint8_t>() + (size_t)ch.d0 * sz, p->stats[s][buf].p, (size_t)n * sz, cudaMemcpyDeviceToHost, p->d2h));
     }
-    if (want_content) CK(cudaMemcpyAsync(h_coff + ch.d0, p->out_off[buf].p, (size_t)(n + 1) * 8, cudaMemcpyDeviceToHost, c->d2h));
-    if (p->opt_validate) CK(cudaMemcpyAsync(&h_bad, p->bad.p, 4, cudaMemcpyDeviceToHost, c->d2h));
-    CK(cudaEventRecord(p->ev_small[buf], c->d2h));
+    if (want_content) CK(cudaMemcpyAsync(h_coff + ch.d0, p->out_off[buf].p, (size_t)(n + 1) * 8, cudaMemcpyDeviceToHost, p->d2h));
+    if (p->opt_validate) CK(cudaMemcpyAsync(&h_bad, p->bad.p, 4, cudaMemcpyDeviceToHost, p->d2h));
+    CK(cudaEventRecord(p->ev_small[buf], p->d2h));
   }
   if (trace) fprintf(stderr, "[tb] %.2f ms: all chunks enqueued\n", since());
   if (!chunks.empty()) if ((rc = finish(chunks.size() - 1))) return rc;
   if (trace) fprintf(stderr, "[tb] %.2f ms: last chunk's kernels done\n", since());
-  CK(cudaStreamSynchronize(c->compute));
+  CK(cudaStreamSynchronize(p->compute));
   resolve_times(p);
-  CK(cudaStreamSynchronize(c->d2h));
-  CK(cudaStreamSynchronize(c->copy));
+  CK(cudaStreamSynchronize(p->d2h));
+  CK(cudaStreamSynchronize(p->copy));
   out->keep = h_keep;
   out->failed_step = h_failed;
   for (size_t s = 0; s < p->steps.size(); s++) out->step_stats[s] = rsx->stats[s].p;
@@ -892,12 +894,6 @@ int tb_ctx_create(int device, tb_ctx** out) {
   c->device = device;
   { cudaDeviceProp prop; if (cudaGetDeviceProperties(&prop, device) == cudaSuccess) c->sm_count = prop.multiProcessorCount; }
   if (tb_kernels_init() != 0) { cudaGetLastError(); delete c; return fail(TB_ERR_CUDA, "cudaFuncSetAttribute(dynamic shared memory) failed: not an sm_100-class device?"); }
-  CK(cudaStreamCreateWithFlags(&c->compute, cudaStreamNonBlocking));
-  CK(cudaStreamCreateWithFlags(&c->copy, cudaStreamNonBlocking));
-  CK(cudaStreamCreateWithFlags(&c->d2h, cudaStreamNonBlocking));
-  CK(cudaStreamCreateWithFlags(&c->side, cudaStreamNonBlocking));
-  CK(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
-  CK(cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming));
   int rc;
   if ((rc = upload(c->t_stage1, tb_uc_stage1, sizeof tb_uc_stage1)) || (rc = upload(c->t_stage2, tb_uc_stage2, sizeof tb_uc_stage2)) ||
       (rc = upload(c->t_lower, tb_uc_lower, sizeof tb_uc_lower)) || (rc = upload(c->t_cased, tb_uc_cased, sizeof tb_uc_cased)) ||
@@ -928,12 +924,6 @@ void tb_ctx_destroy(tb_ctx* c) {
   if (!c) return;
   cudaSetDevice(c->device);
   for (DevBuf* b : {&c->t_stage1, &c->t_stage2, &c->t_lower, &c->t_cased, &c->t_caseign, &c->t_pow, &c->t_ent}) b->release();
-  if (c->compute) cudaStreamDestroy(c->compute);
-  if (c->copy) cudaStreamDestroy(c->copy);
-  if (c->d2h) cudaStreamDestroy(c->d2h);
-  if (c->side) cudaStreamDestroy(c->side);
-  if (c->ev_fork) cudaEventDestroy(c->ev_fork);
-  if (c->ev_join) cudaEventDestroy(c->ev_join);
   delete c;
 }
 
@@ -983,6 +973,12 @@ int tb_pipeline_create(tb_ctx* ctx, const tb_step_cfg* steps, size_t n_steps, tb
       sh.gr = g;
     }
   }
+  CK(cudaStreamCreateWithFlags(&p->compute, cudaStreamNonBlocking));
+  CK(cudaStreamCreateWithFlags(&p->copy, cudaStreamNonBlocking));
+  CK(cudaStreamCreateWithFlags(&p->d2h, cudaStreamNonBlocking));
+  CK(cudaStreamCreateWithFlags(&p->side, cudaStreamNonBlocking));
+  CK(cudaEventCreateWithFlags(&p->ev_fork, cudaEventDisableTiming));
+  CK(cudaEventCreateWithFlags(&p->ev_join, cudaEventDisableTiming));
   for (int i = 0; i < 2; i++) {
     CK(cudaEventCreateWithFlags(&p->ev_h2d[i], cudaEventDisableTiming));
     CK(cudaEventCreateWithFlags(&p->ev_done[i], cudaEventDisableTiming));
@@ -1015,6 +1011,12 @@ void tb_pipeline_destroy(tb_pipeline* p) {
     if (p->ev_d2h[i]) cudaEventDestroy(p->ev_d2h[i]);
     if (p->ev_small[i]) cudaEventDestroy(p->ev_small[i]);
   }
+  if (p->compute) cudaStreamDestroy(p->compute);
+  if (p->copy) cudaStreamDestroy(p->copy);
+  if (p->d2h) cudaStreamDestroy(p->d2h);
+  if (p->side) cudaStreamDestroy(p->side);
+  if (p->ev_fork) cudaEventDestroy(p->ev_fork);
+  if (p->ev_join) cudaEventDestroy(p->ev_join);
   for (auto e : p->ev_pool) cudaEventDestroy(e);
   for (auto e : p->ev_gather) cudaEventDestroy(e);
   for (int i = 0; i < Stager::kSlots; i++) { p->stage_slots[i].release(); if (p->stage_ev[i]) cudaEventDestroy(p->stage_ev[i]); }
@@ -1032,6 +1034,9 @@ int tb_pipeline_set_option(tb_pipeline* p, int32_t option, int64_t value) {
     case TB_OPT_GENERAL_WORD_PATH: p->opt_debug = value != 0 ? TB_DBG_FORCE_WALK : 0; return TB_OK;
     case TB_OPT_DECODE_HTML_ENTITIES: p->opt_decode = value != 0; return TB_OK;
     case TB_OPT_CHUNK_RAMP: p->opt_ramp = value != 0; return TB_OK;
+    case TB_OPT_BULK_STAGE_TILES:
+      if (value < 0 || value > (1 << 30)) return fail(TB_ERR_INVALID_ARGUMENT, "TB_OPT_BULK_STAGE_TILES: smallest document, in 1 KiB tiles, whose text is staged by bulk copies; 0 = off");
+      p->opt_bulk = value; return TB_OK;
     case TB_OPT_STAGE_THREADS:
       if (value < 0) return fail(TB_ERR_INVALID_ARGUMENT, "TB_OPT_STAGE_THREADS: number of host threads, 0 = off");
       p->opt_stage = value; return TB_OK;

@@ -65,7 +65,7 @@ TB_D bool gq_doc_tiles(const KBatch& a, const LutEntry* lut, uint32_t* stage, co
   const uint8_t* t = R.t;
   uint32_t* st_pos = stage; uint32_t* st_len = stage + TB_GQ_STAGE;
   Frag carry{0u, 0u};
-  feed.begin(t, a.ext_lo, a.ext_hi, tb_tile_origin(R), R.re, lane);
+  feed.begin(t, a.ext_lo, a.ext_hi, tb_tile_origin(R), R.re, lane, a.feed_min_tiles);
   for (int64_t base = tb_tile_origin(R); base < R.re; base += TB_TILE) {
     Tile T;
     const uint32_t sm = feed.tile(base);
@@ -192,7 +192,7 @@ TB_D bool c4b_doc_tiles(const KBatch& a, const LutEntry* lut, const Classifier& 
   const bool pats = cfg.filter_javascript != 0 || cfg.filter_policy != 0;
   Frag carry{0u, 0u};
   uint32_t nl = 0;
-  feed.begin(t, a.ext_lo, a.ext_hi, tb_tile_origin(R), R.re, lane);
+  feed.begin(t, a.ext_lo, a.ext_hi, tb_tile_origin(R), R.re, lane, a.feed_min_tiles);
   for (int64_t base = tb_tile_origin(R); base < R.re; base += TB_TILE) {
     Tile T;
     const uint32_t sm = feed.tile(base);
@@ -301,7 +301,7 @@ TB_D bool gr_doc_tiles(const KBatch& a, const LutEntry* lut, uint32_t* stage, co
   HL lcarry{0u, 0u, 0u};
   uint64_t sig_carry = 0;  // signature of the text's words up to the last one stored (its last 16 bytes)
   uint32_t wcarry_wc = 0;
-  feed.begin(R.t, a.ext_lo, a.ext_hi, tb_tile_origin(R), R.re, lane);
+  feed.begin(R.t, a.ext_lo, a.ext_hi, tb_tile_origin(R), R.re, lane, a.feed_min_tiles);
   for (int64_t base = tb_tile_origin(R); base < R.re; base += TB_TILE) {
     Tile T;
     const uint32_t sm = feed.tile(base);
@@ -524,7 +524,7 @@ TB_D void c4a_doc_tiles(const KBatch& a, const LutEntry* lut, uint8_t* stage, co
   uint32_t carry_seen = 0;  // the current line showed a non-white-space character before this tile
   int64_t carry_cit = -1;   // end of a citation that runs into this tile
   if (lane == 0) { s.lwc[lb] = 0; s.lmax[lb] = 0; s.lflags[lb] = 0; }
-  feed.begin(t, a.ext_lo, a.ext_hi, tb_tile_origin(R), R.re, lane);
+  feed.begin(t, a.ext_lo, a.ext_hi, tb_tile_origin(R), R.re, lane, a.feed_min_tiles);
   for (int64_t base = tb_tile_origin(R); base < R.re; base += TB_TILE) {
     Tile T;
     const int64_t p0 = base + lane * TB_STRETCH;

@@ -22,7 +22,6 @@
 #endif
 
 #define TB_FEED_STAGES 2
-#define TB_FEED_MIN_TILES 4  // documents shorter than this many tiles are read with plain loads
 #define TB_FEED_SMEM (TB_FEED_STAGES * TB_TILE + TB_FEED_STAGES * 8)
 #define TB_FEED_NONE 0xFFFFFFFFu
 
@@ -55,9 +54,10 @@ struct TileFeed {
                  : "memory");
   }
   // start of a document: first tile at `first` (tb_tile_origin), text ends at `re`
-  __device__ __forceinline__ void begin(const uint8_t* text, int64_t lo, int64_t hi, int64_t first, int64_t re, int lane) {
+  // min_tiles: documents of at least this many tiles are staged (0: none)
+  __device__ __forceinline__ void begin(const uint8_t* text, int64_t lo, int64_t hi, int64_t first, int64_t re, int lane, uint32_t min_tiles) {
     t = text; ext_lo = lo; ext_hi = hi; end = re; origin = first;
-    on = re - first >= (int64_t)TB_FEED_MIN_TILES * TB_TILE;
+    on = min_tiles != 0u && re - first >= (int64_t)min_tiles * TB_TILE;
     if (on && lane == 0)
       for (int s = 0; s < TB_FEED_STAGES; s++) if (wanted(first + (int64_t)s * TB_TILE)) request(first + (int64_t)s * TB_TILE, s);
   }
@@ -92,7 +92,7 @@ struct TileFeed {
 struct TileFeed {  // host emulation: nothing is staged
   bool on = false;
   void init(uint8_t*, int) {}
-  void begin(const uint8_t*, int64_t, int64_t, int64_t, int64_t, int) {}
+  void begin(const uint8_t*, int64_t, int64_t, int64_t, int64_t, int, uint32_t) {}
   uint32_t tile(int64_t) { return TB_FEED_NONE; }
   void done(int64_t, int) {}
   void drain(int64_t) {}

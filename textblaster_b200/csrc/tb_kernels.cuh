@@ -27,6 +27,7 @@ struct KBatch {
   // them is started when everything else is already done.  order[0 .. n): very long ones from the front, long
   // ones from the back; counts[0], counts[1] their numbers; sizecls[d] != 0 marks a listed document.
   const uint32_t* order; const uint32_t* order_counts; const uint8_t* sizecls;
+  uint32_t feed_min_tiles;  // documents of at least this many 1 KiB tiles get their tiles by bulk copy (tb_feed.cuh); 0: none
 };
 #define TB_LONG_DOC_BYTES (8 << 10)
 #define TB_XLONG_DOC_BYTES (32 << 10)

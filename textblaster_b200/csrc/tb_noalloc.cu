@@ -197,7 +197,7 @@ int tb_gopher_repetition_noalloc(const uint8_t* utf8_dev, const int64_t* offsets
   // keep_dev doubles as the kernels' "alive" flag: 1 for every document whose offsets are usable
   k_noalloc_ranges<<<1, 1024, 0, stream>>>(offsets_dev, n_docs, n_bytes, rs, re, keep_dev, failed, stats_dev);
   tb_launch_order(stream, rs, re, n_docs, order, g.counters + 12, sizecls);
-  KBatch b{utf8_dev, rs, re, keep_dev, failed, n_docs, st->uc, 0, n_bytes, 0u, order, g.counters + 12, sizecls};
+  KBatch b{utf8_dev, rs, re, keep_dev, failed, n_docs, st->uc, 0, n_bytes, 0u, order, g.counters + 12, sizecls, 0u};
   tb_launch_trim(stream, b, ts, te);
   tb_launch_gr_scan(stream, b, ts, te, g, st->sm_count);
   for (int tier = 0; tier < 4; tier++) tb_launch_gr_rep(stream, b, ts, te, g, cfg, 0, stats_dev, st->sm_count, tier);
