@@ -14,7 +14,8 @@ import multilingual
 import oracle
 from parity_cases import CHAINS, GQ_OPEN, GR_OPEN, step_types
 from parity_util import compare
-from test_emul_parity import GOLDEN_DOCS, SENTENCE_LINE_DOCS, boundary_sentence_docs, entity_docs, fineweb_docs, split_ambiguity_docs
+from test_emul_parity import (GOLDEN_DOCS, SENTENCE_LINE_DOCS, boundary_sentence_docs, entity_docs, fineweb_docs,
+                              signature_pruning_docs, split_ambiguity_docs)
 from test_oracle_golden import C4_LINE_CASES, c4_default
 from textblaster_b200 import _abi, synth
 from textblaster_b200.config import GopherRepetitionParams
@@ -525,3 +526,18 @@ def test_bulk_copy_staging_of_long_documents(name):
         contents = [res.content_of(i) for i in range(res.n_docs)] if res.content is not None else None
         compare(ores, res.keep, res.failed_step, res.stats, contents, step_types(steps), texts, label=name + "/bulk%d" % tiles)
     p.close()
+
+
+def repetition_pass_docs():
+    """what the second repetition pass is sensitive to: every tier size, few and many candidates (register and table
+    paths), split ambiguity at the pruned levels, the densest word pattern"""
+    rng = random.Random(8)
+    base = fuzzgen.english_doc(rng, 1500)
+    docs = [fuzzgen.english_doc(rng, 2500), fuzzgen.english_doc(rng, 12000), fuzzgen.english_doc(rng, 36000), fuzzgen.english_doc(rng, 90000),
+            (base + "\n") * 3, (base + "\n") * 9, (base + "\n") * 30, "a b c d e f g " * 700, "x y " * 5000]
+    return docs + signature_pruning_docs() + split_ambiguity_docs() + fuzzgen.dense_word_docs()
+
+
+@pytest.mark.parametrize("name", ["gr_open", "gr_shipped", "shipped_order"])
+def test_repetition_pass_documents(name):
+    check_texts(name, repetition_pass_docs())

@@ -551,10 +551,10 @@ int enqueue_chain(tb_pipeline* p, const uint8_t* text, int64_t n, int64_t nbytes
   CK(cudaMemcpyAsync(p->re.p, p->re0.p, (size_t)n * 8, cudaMemcpyDeviceToDevice, st));
   CK(cudaMemsetAsync(p->rewritten.p, 0, (size_t)n, st));
   CK(cudaMemsetAsync(p->cursors.p, 0, 256, st));
-  uint32_t* cursors = p->cursors.as<uint32_t>();  // [0, 3 * TB_MAX_STEPS): kernel cursors; [48], [49]: counts of the work order
+  uint32_t* cursors = p->cursors.as<uint32_t>();  // [0, 4 * TB_MAX_STEPS): kernel cursors; [40, 56): counts of the work order; [56..): pre-pass cursors
   KBatch b{text, p->rs.as<int64_t>(), p->re.as<int64_t>(), p->alive[pb].as<uint8_t>(), p->failed[pb].as<int8_t>(), n, c->uc, 0, nbytes,
-           (uint32_t)p->opt_debug, p->order.as<uint32_t>(), cursors + 48, p->sizecls.as<uint8_t>(), (uint32_t)p->opt_bulk};
-  { Timed t(p, "k_order"); tb_launch_order(st, p->rs0.as<int64_t>(), p->re0.as<int64_t>(), n, p->order.as<uint32_t>(), cursors + 48, p->sizecls.as<uint8_t>()); }
+           (uint32_t)p->opt_debug, p->order.as<uint32_t>(), cursors + 40, p->sizecls.as<uint8_t>(), (uint32_t)p->opt_bulk};
+  { Timed t(p, "k_order"); tb_launch_order(st, p->rs0.as<int64_t>(), p->re0.as<int64_t>(), n, p->order.as<uint32_t>(), cursors + 40, p->sizecls.as<uint8_t>()); }
   *has_c4 = false;
   if (p->opt_validate) {  // p->bad counts over the whole run (cleared by run_impl)
     { Timed t(p, "k_validate_utf8"); tb_launch_validate_utf8(st, text, b.rs, b.re, n, p->bad.as<int32_t>()); }
@@ -600,7 +600,7 @@ int enqueue_chain(tb_pipeline* p, const uint8_t* text, int64_t n, int64_t nbytes
         CK(cudaMemsetAsync(p->c_bits.p, 0, ((size_t)nbytes / 32 + 4) * 4, st));
         { Timed t(p, "k_trim"); tb_launch_trim(st, b, p->ts.as<int64_t>(), p->te.as<int64_t>()); }
         { Timed t(p, "k_c4_sent"); tb_launch_c4_sent(st, b, p->ts.as<int64_t>(), p->te.as<int64_t>(), p->c_bits.as<uint32_t>(), p->c_S.as<uint8_t>(),
-                                                     p->c_srs.as<int64_t>(), p->c_sre.as<int64_t>(), c->sm_count, cursors + 50); }
+                                                     p->c_srs.as<int64_t>(), p->c_sre.as<int64_t>(), c->sm_count, cursors + 58); }
         b.text = p->c_S.as<uint8_t>(); b.rs = p->c_srs.as<int64_t>(); b.re = p->c_sre.as<int64_t>();
         b.ext_hi = (int64_t)tb_grown_bytes(nbytes, n);
       }
@@ -816,7 +816,7 @@ int run_impl(tb_pipeline* p, const uint8_t* utf8, const void* offsets, int is64,
                 0u, nullptr, nullptr, nullptr, 0u};
       { Timed t(p, "k_entities");
         tb_launch_entities(p->compute, eb, c->t_ent.as<EntEntry>(), TB_ENT_COUNT, p->e_amp.as<uint32_t>(), p->e_drop.as<uint32_t>(), p->e_D.as<uint8_t>(),
-                           p->e_drs.as<int64_t>(), p->e_dre.as<int64_t>(), c->sm_count, p->cursors.as<uint32_t>() + 51); }
+                           p->e_drs.as<int64_t>(), p->e_dre.as<int64_t>(), c->sm_count, p->cursors.as<uint32_t>() + 59); }
       CK(cudaMemcpyAsync(p->rs0.p, p->e_drs.p, (size_t)n * 8, cudaMemcpyDeviceToDevice, p->compute));
       CK(cudaMemcpyAsync(p->re0.p, p->e_dre.p, (size_t)n * 8, cudaMemcpyDeviceToDevice, p->compute));
       text = p->e_D.as<uint8_t>();

@@ -33,21 +33,35 @@ __device__ __forceinline__ int64_t next_doc(uint32_t* cursor, const KBatch& a) {
   uint32_t i = 0;
   if ((threadIdx.x & 31) == 0) i = atomicAdd(cursor, 1u);
   i = __shfl_sync(0xFFFFFFFFu, i, 0);
-  const uint32_t nx = a.order_counts[0], nl = a.order_counts[1];
-  if (i < nx) return (int64_t)a.order[i];
-  if (i < nx + nl) return (int64_t)a.order[a.n - 1 - (i - nx)];
-  const int64_t d = (int64_t)i - nx - nl;
+  const uint32_t listed = a.order_counts[0];
+  if (i < listed) return (int64_t)a.order[i];
+  const int64_t d = (int64_t)i - listed;
   if (d >= a.n) return -1;
   return a.sizecls[d] ? -2 : d;
 }
-__global__ void k_order(const int64_t* rs, const int64_t* re, int64_t n, uint32_t* order, uint32_t* counts, uint8_t* sizecls) {
+// Size class of a document: 0 below 8 KiB (not listed), then one class per doubling up to 7 (512 KiB and more).
+__device__ __forceinline__ uint32_t size_class(int64_t len) {
+  if (len <= TB_LONG_DOC_BYTES) return 0u;
+  const uint32_t c = (uint32_t)(63 - __clzll((unsigned long long)(len - 1))) - 12u;  // (8K, 16K] -> 1, (16K, 32K] -> 2, ...
+  return c > 7u ? 7u : c;
+}
+// Work order, longest documents first (one class per doubling of the length: the last document to start is then at
+// most twice as long as any that could have been started instead).  Pass 0 counts the classes (counts[8 + c]),
+// pass 1 places every listed document behind the longer classes; counts[0] = number of listed documents.
+__global__ void k_order(const int64_t* rs, const int64_t* re, int64_t n, uint32_t* order, uint32_t* counts, uint8_t* sizecls, int pass) {
   int64_t d = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (d >= n) return;
-  const int64_t len = re[d] - rs[d];
-  uint8_t c = len > TB_XLONG_DOC_BYTES ? 2 : len > TB_LONG_DOC_BYTES ? 1 : 0;
-  sizecls[d] = c;
-  if (c == 2) order[atomicAdd(&counts[0], 1u)] = (uint32_t)d;
-  else if (c == 1) order[n - 1 - atomicAdd(&counts[1], 1u)] = (uint32_t)d;
+  const uint32_t c = size_class(re[d] - rs[d]);
+  if (pass == 0) {
+    sizecls[d] = (uint8_t)c;
+    if (c) atomicAdd(&counts[8 + c], 1u);
+    return;
+  }
+  if (!c) { if (d == 0) { uint32_t t = 0; for (uint32_t k = 1; k < 8; k++) t += counts[8 + k]; counts[0] = t; } return; }
+  uint32_t base = 0;
+  for (uint32_t k = c + 1; k < 8; k++) base += counts[8 + k];
+  order[base + atomicAdd(&counts[c], 1u)] = (uint32_t)d;
+  if (d == 0) { uint32_t t = 0; for (uint32_t k = 1; k < 8; k++) t += counts[8 + k]; counts[0] = t; }
 }
 __device__ __forceinline__ int64_t warp_doc() { return ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; }
 __device__ __forceinline__ int64_t thread_doc() { return (int64_t)blockIdx.x * blockDim.x + threadIdx.x; }
@@ -315,7 +329,9 @@ inline int blocks_for_threads(int64_t n) { return (int)((n + 255) / 256); }
 }  // namespace
 
 void tb_launch_order(cudaStream_t st, const int64_t* rs, const int64_t* re, int64_t n, uint32_t* order, uint32_t* counts, uint8_t* sizecls) {
-  if (n) k_order<<<(int)((n + 255) / 256), 256, 0, st>>>(rs, re, n, order, counts, sizecls);
+  if (!n) return;
+  k_order<<<(int)((n + 255) / 256), 256, 0, st>>>(rs, re, n, order, counts, sizecls, 0);
+  k_order<<<(int)((n + 255) / 256), 256, 0, st>>>(rs, re, n, order, counts, sizecls, 1);
 }
 void tb_launch_init_ranges(cudaStream_t st, const void* off, int off64, int64_t doc0, int64_t n, int64_t base,
                            int64_t* rs, int64_t* re, uint8_t* alive, int8_t* failed) {

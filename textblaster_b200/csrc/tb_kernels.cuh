@@ -23,9 +23,9 @@ struct KBatch {
   UcTables uc;
   int64_t ext_lo, ext_hi;  // positions of `text` (and of the C4 work buffers) that 32-byte vector loads may touch
   uint32_t dbg;            // TB_DBG_*
-  // Work order of the persistent kernels (built by tb_launch_order): long documents go first so that none of
-  // them is started when everything else is already done.  order[0 .. n): very long ones from the front, long
-  // ones from the back; counts[0], counts[1] their numbers; sizecls[d] != 0 marks a listed document.
+  // Work order of the persistent kernels (built by tb_launch_order): long documents go first, longest class first, so
+  // that none of them is started when everything else is already done.  order[0 .. counts[0]): the listed documents
+  // (8 KiB and more); sizecls[d] != 0 marks a listed document.  counts: 16 words, zero before tb_launch_order.
   const uint32_t* order; const uint32_t* order_counts; const uint8_t* sizecls;
   uint32_t feed_min_tiles;  // documents of at least this many 1 KiB tiles get their tiles by bulk copy (tb_feed.cuh); 0: none
 };

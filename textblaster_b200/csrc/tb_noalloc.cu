@@ -180,7 +180,7 @@ int tb_gopher_repetition_noalloc(const uint8_t* utf8_dev, const int64_t* offsets
   g.doc = (GrDoc*)carve(n1 * sizeof(GrDoc));
   g.work = (uint32_t*)carve((wunits * TB_REP_K + n1 * TB_REP_DOC_EXTRA) * 4);
   g.lists = (uint32_t*)carve(4 * n1 * 4);
-  g.counters = (uint32_t*)carve(64);  // [12], [13] double as the counts of the work order
+  g.counters = (uint32_t*)carve(256);  // [16, 32): the counts of the work order
   uint32_t* order = (uint32_t*)carve(n1 * 4);
   uint8_t* sizecls = (uint8_t*)carve(n1);
   g.n = n_docs;
@@ -193,11 +193,11 @@ int tb_gopher_repetition_noalloc(const uint8_t* utf8_dev, const int64_t* offsets
   for (int k = 0; k < TB_MAX_NGRAMS; k++) { cfg.top_n[k] = params->top_n[k]; cfg.top_frac[k] = params->top_frac[k]; cfg.dup_n[k] = params->dup_n[k]; cfg.dup_frac[k] = params->dup_frac[k]; }
 
   // state that must start at zero: tier list lengths and work cursors (the array keeps the last call's contents)
-  if (cudaMemsetAsync(g.counters, 0, 64, stream) != cudaSuccess) { cudaGetLastError(); return fail(TB_ERR_CUDA, "cudaMemsetAsync failed"); }
+  if (cudaMemsetAsync(g.counters, 0, 256, stream) != cudaSuccess) { cudaGetLastError(); return fail(TB_ERR_CUDA, "cudaMemsetAsync failed"); }
   // keep_dev doubles as the kernels' "alive" flag: 1 for every document whose offsets are usable
   k_noalloc_ranges<<<1, 1024, 0, stream>>>(offsets_dev, n_docs, n_bytes, rs, re, keep_dev, failed, stats_dev);
-  tb_launch_order(stream, rs, re, n_docs, order, g.counters + 12, sizecls);
-  KBatch b{utf8_dev, rs, re, keep_dev, failed, n_docs, st->uc, 0, n_bytes, 0u, order, g.counters + 12, sizecls, 0u};
+  tb_launch_order(stream, rs, re, n_docs, order, g.counters + 16, sizecls);
+  KBatch b{utf8_dev, rs, re, keep_dev, failed, n_docs, st->uc, 0, n_bytes, 0u, order, g.counters + 16, sizecls, 0u};
   tb_launch_trim(stream, b, ts, te);
   tb_launch_gr_scan(stream, b, ts, te, g, st->sm_count);
   for (int tier = 0; tier < 4; tier++) tb_launch_gr_rep(stream, b, ts, te, g, cfg, 0, stats_dev, st->sm_count, tier);
