@@ -20,6 +20,7 @@
 #if defined(__x86_64__)
 #include <emmintrin.h>
 #endif
+#include <nvtx3/nvToolsExt.h>  // header-only; ranges show up under Nsight Systems / Compute, and cost nothing without a tool attached
 
 #include "tb_hostutil.h"
 #include "tb_kernels.cuh"
@@ -140,6 +141,7 @@ struct PlainBuf {  // grow-only pageable host allocation (not initialised)
 struct ResultSet {  // host-side results of one run
   HostBuf keep, failed, content, content_off;
   PlainBuf kept, kept_off;  // TB_OPT_GATHER_KEPT
+  HostBuf bad;              // TB_OPT_VALIDATE_UTF8: the device's count of malformed documents lands here (pinned: the copy does not block)
   HostBuf stats[TB_MAX_STEPS];
   bool in_use = false;
 };
@@ -194,6 +196,11 @@ struct Stager {
   cudaError_t wait_recorded(int64_t ci) { std::unique_lock<std::mutex> lk(mu); cv.wait(lk, [&] { return recorded >= ci || err != cudaSuccess; }); return err; }
   void finish() { if (!th.joinable()) return; { std::lock_guard<std::mutex> lk(mu); closed = true; } cv.notify_all(); th.join(); }
   ~Stager() { finish(); }
+};
+
+struct NvtxRange {  // one named range on the calling thread (a call, a chunk, a step of the chain)
+  explicit NvtxRange(const char* name) { nvtxRangePushA(name); }
+  ~NvtxRange() { nvtxRangePop(); }
 };
 
 struct KTime { const char* name; double ms; int64_t launches; };
@@ -561,6 +568,7 @@ int enqueue_chain(tb_pipeline* p, const uint8_t* text, int64_t n, int64_t nbytes
   }
   for (size_t s = 0; s < p->steps.size(); s++) {
     StepHost& sh = p->steps[s];
+    NvtxRange nvtx_step(tb_step_name(sh.type));
     if (sh.type == TB_STEP_GOPHER_QUALITY) {
       Timed t(p, "k_gq");
       tb_launch_gq(st, b, sh.sw, sh.gq, (int)s, p->stats[s][pb].as<tb_gq_stats>(), c->sm_count, cursors + s);
@@ -638,6 +646,7 @@ int run_impl(tb_pipeline* p, const uint8_t* utf8, const void* offsets, int is64,
              const int64_t* offsets_dev, tb_batch_out* out) {
   tb_ctx* c = p->ctx;
   CK(cudaSetDevice(c->device));
+  NvtxRange nvtx_call(device_input ? "tb_pipeline_run_batch_device" : "tb_pipeline_run_batch");
   static const bool trace = getenv("TB_TRACE") != nullptr;  // host-side timeline of one call on stderr
   const auto t_entry = std::chrono::steady_clock::now();
   auto since = [&]() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_entry).count(); };
@@ -710,7 +719,8 @@ int run_impl(tb_pipeline* p, const uint8_t* utf8, const void* offsets, int is64,
   int64_t* h_coff = rsx->content_off.as<int64_t>();
   uint8_t* h_content = rsx->content.as<uint8_t>();
   int64_t content_base = 0;
-  int32_t h_bad = 0;
+  if (p->opt_validate) { if ((rc = rsx->bad.ensure(16))) return rc; *rsx->bad.as<int32_t>() = 0; }
+  volatile int32_t* h_bad = p->opt_validate ? rsx->bad.as<int32_t>() : nullptr;
 
   // pageable text goes through the library's pinned ring (Stager); pinned or registered text is copied from where it is
   bool staged = false;
@@ -759,7 +769,7 @@ int run_impl(tb_pipeline* p, const uint8_t* utf8, const void* offsets, int is64,
     const int64_t n = ch.d1 - ch.d0;
     CK(cudaEventSynchronize(p->ev_small[buf]));
     if (trace) fprintf(stderr, "[tb] %.2f ms: chunk %zu (%lld docs, %.0f MB) results on the host\n", since(), ci, (long long)n, (ch.b1 - ch.b0) / 1048576.0);
-    if (p->opt_validate && h_bad) return fail(TB_ERR_INVALID_UTF8, "input contains " + std::to_string(h_bad) + " document(s) with invalid UTF-8 (first chunk doc " + std::to_string(ch.d0) + ")");
+    if (p->opt_validate && *h_bad) return fail(TB_ERR_INVALID_UTF8, "input contains " + std::to_string((int)*h_bad) + " document(s) with invalid UTF-8 (first chunk doc " + std::to_string(ch.d0) + ")");
     if (want_content) {
       int64_t tot = h_coff[ch.d0 + n];
       if (content_mode == 2 && tot > (ch.b1 - ch.b0) / 8 + n)
@@ -823,7 +833,10 @@ int run_impl(tb_pipeline* p, const uint8_t* utf8, const void* offsets, int is64,
       text_extent = (int64_t)tb_grown_bytes(text_extent, n);
     }
     bool has_c4 = false;
-    if ((rc = enqueue_chain(p, text, n, text_extent, buf, content_mode, &has_c4))) return rc;
+    {
+      NvtxRange nvtx_chunk("chunk: enqueue chain");
+      if ((rc = enqueue_chain(p, text, n, text_extent, buf, content_mode, &has_c4))) return rc;
+    }
     CK(cudaEventRecord(p->ev_done[buf], p->compute));
     // the previous chunk's content goes out first (its copy must not queue behind this chunk's kernels)
     if (ci > 0) if ((rc = finish(ci - 1))) return rc;
@@ -836,7 +849,7 @@ int run_impl(tb_pipeline* p, const uint8_t* utf8, const void* offsets, int is64,
       CK(cudaMemcpyAsync(rsx->stats[s].as<uint8_t>() + (size_t)ch.d0 * sz, p->stats[s][buf].p, (size_t)n * sz, cudaMemcpyDeviceToHost, p->d2h));
     }
     if (want_content) CK(cudaMemcpyAsync(h_coff + ch.d0, p->out_off[buf].p, (size_t)(n + 1) * 8, cudaMemcpyDeviceToHost, p->d2h));
-    if (p->opt_validate) CK(cudaMemcpyAsync(&h_bad, p->bad.p, 4, cudaMemcpyDeviceToHost, p->d2h));
+    if (p->opt_validate) CK(cudaMemcpyAsync((void*)h_bad, p->bad.p, 4, cudaMemcpyDeviceToHost, p->d2h));
     CK(cudaEventRecord(p->ev_small[buf], p->d2h));
   }
   if (trace) fprintf(stderr, "[tb] %.2f ms: all chunks enqueued\n", since());
@@ -1001,7 +1014,7 @@ void tb_pipeline_destroy(tb_pipeline* p) {
   for (auto& b : p->stats) { b[0].release(); b[1].release(); }
   for (auto& s : p->steps) s.sw_dev.release();
   for (auto* r : p->results) {
-    r->keep.release(); r->failed.release(); r->content.release(); r->content_off.release(); r->kept.release(); r->kept_off.release();
+    r->keep.release(); r->failed.release(); r->content.release(); r->content_off.release(); r->kept.release(); r->kept_off.release(); r->bad.release();
     for (auto& s : r->stats) s.release();
     delete r;
   }
