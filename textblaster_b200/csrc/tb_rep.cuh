@@ -307,6 +307,46 @@ TB_D void rep_lines_small(const uint64_t* lh, const uint32_t* ll, const uint8_t*
   const uint32_t l = dup ? vl : 0u;
   *para_db = (uint64_t)simt_sum(l & 0xFFFFu) + ((uint64_t)simt_sum(l >> 16) << 16);
 }
+// Paragraphs of a document with any number of line pieces, by one warp: 32 pieces at a time, the segmented scan of
+// rep_lines_small within the chunk, the paragraph that is open at the chunk's start carried in.  Writes hash and
+// length of paragraph p to H[p] / len[p] in order; returns their number.
+TB_D uint32_t rep_paragraphs_scan(const uint64_t* lh, const uint32_t* ll, const uint8_t* lg, uint32_t NL, const uint64_t* powtab, int lane,
+                                  uint64_t* H, uint32_t* len) {
+  uint32_t NP = 0;
+  Hash2 cv; cv.init(); uint32_t cl = 0;  // the open paragraph before this chunk (none for the first)
+#pragma unroll 1
+  for (uint32_t c0 = 0; c0 < NL; c0 += 32) {
+    const uint32_t k = c0 + (uint32_t)lane;
+    const bool holder = k < NL;
+    const bool head = holder && (k == 0 || lg[k] != 0);
+    Hash2 v = tb_unpack(holder ? lh[k] : 0ull);
+    uint32_t vl = holder ? ll[k] : 0u, f = head ? 1u : 0u;
+#pragma unroll 1
+    for (int off = 1; off < 32; off <<= 1) {
+      const uint32_t ua = simt_shfl_up(v.a, off), ub = simt_shfl_up(v.b, off), ul = simt_shfl_up(vl, off), uf = simt_shfl_up(f, off);
+      if (lane >= off && !f && holder) {
+        Hash2 x; x.a = ua; x.b = ub;
+        x.push('\n', TB_LDG(powtab + 1));
+        v = tb_hcat(x, v, tb_pow_pack(powtab, vl));
+        vl += ul + 1u; f = uf;
+      }
+    }
+    if (holder && !f && c0) {  // no paragraph opens at or before this piece in the chunk: it continues the carried one
+      Hash2 x = cv;
+      x.push('\n', TB_LDG(powtab + 1));
+      v = tb_hcat(x, v, tb_pow_pack(powtab, vl));
+      vl += cl + 1u;
+    }
+    const uint32_t heads = simt_ballot(head);
+    const bool next_head = lane < 31 ? ((heads >> (lane + 1)) & 1u) != 0u : (k + 1u < NL && lg[k + 1u] != 0);
+    const bool last = holder && (k + 1u == NL || next_head);
+    const uint32_t lasts = simt_ballot(last);
+    if (last) { const uint32_t p = NP + (uint32_t)simt_popc(lasts & ((1u << lane) - 1u)); H[p] = v.pack(); len[p] = vl; }
+    NP += (uint32_t)simt_popc(lasts);
+    cv.a = simt_shfl(v.a, 31); cv.b = simt_shfl(v.b, 31); cl = simt_shfl(vl, 31);
+  }
+  return NP;
+}
 // Duplicate n-grams of every configured level from n_from on (text.rs:241-259) when at most 32 word ends are in play:
 // item `lane` is the n-gram that ends with word e (valid: lane < items).  Keys grow to the left in registers; equal
 // keys are found with one match per level; the order-dependent walk over the candidates runs on all lanes alike,
@@ -447,17 +487,7 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
   }
   // ---- paragraphs (gopher_rep.rs:80-116): fold the ordered line pieces; a single '\n' joins lines
   // inside a paragraph, a run of >= 2 separates paragraphs.
-  if (g.tid == 0) {
-    Hash2 cur; cur.init(); uint32_t curlen = 0;
-#pragma unroll 1
-    for (uint32_t k = 0; k < NL; k++) {
-      Hash2 hk = tb_unpack(lh[k]);
-      if (k == 0) { cur = hk; curlen = ll[k]; continue; }
-      if (lg[k]) { A.H[NP] = cur.pack(); A.woff[NP] = curlen; NP++; cur = hk; curlen = ll[k]; }
-      else { cur.push('\n', TB_LDG(a.uc.powtab + 1)); cur = tb_hcat(cur, hk, tb_pow_pack(a.uc.powtab, ll[k])); curlen += 1 + ll[k]; }
-    }
-    if (NL) { A.H[NP] = cur.pack(); A.woff[NP] = curlen; NP++; }
-  }
+  if (g.tid < 32) NP = rep_paragraphs_scan(lh, ll, lg, NL, a.uc.powtab, g.tid, A.H, A.woff);  // (the first warp; the others wait at the broadcast)
   NP = g.bcast(NP);
   g.sync();
   rep_dedup(g, tab, A.H, A.woff, NP, &de, &db);
