@@ -866,6 +866,20 @@ def main():
         alg_bytes_step = n_bytes + 8 * (n_docs + 1) + 16 * n_docs  # text once + i64 offsets + minimal per-doc output
         launches_per_step = max(dom_launches / K, 1)
         alg_bytes_launch = alg_bytes_step / launches_per_step
+        units_note = "every document of the chunk"
+        tier_of = {"k_gr_rep_s": 0, "k_gr_rep_m": 1, "k_gr_rep_l": 2}
+        if dom_name in tier_of:
+            # a tier kernel of the repetition pass only works on the documents of its size class that reached the step:
+            # it is credited with their text (and their 24 bytes of offsets / results), not with the whole chunk's
+            gr_idx = [i for i, prm in enumerate(steps) if prm.CTYPE == _abi.TB_STEP_GOPHER_REPETITION][0]
+            res = pipe.run_packed(utf8, off, copy_content=False)
+            ran = (res.failed_step < 0) | (res.failed_step >= gr_idx)
+            big = np.maximum(res.stats[gr_idx]["n_words"], res.stats[gr_idx]["n_lines"])
+            lo, hi = [(0, 512), (512, 2048), (2048, 8192)][tier_of[dom_name]]
+            sel = ran & (big > lo if lo else big >= 0) & (big <= hi)
+            tier_bytes = int(np.diff(off)[sel].sum()) + 24 * int(sel.sum())
+            alg_bytes_launch = tier_bytes / launches_per_step
+            units_note = "the %d documents with %d < max(words, line pieces) <= %d that reached the step (%.2f GB of the step's text)" % (int(sel.sum()), lo, hi, tier_bytes / 1e9)
         avg_ms = dom_ms / max(dom_launches, 1)
         achieved = alg_bytes_launch / (avg_ms * 1e-3) / 1e9 if avg_ms > 0 else 0.0
         peak, peak_src = measured_peaks()
@@ -893,7 +907,7 @@ def main():
             "gpu_launches": launches,
             "roofline": {"bound": "hbm", "kernel": dom_name, "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak if peak else None, "traffic": ncu_traffic(dom_name, alg_bytes_launch), "peak_source": peak_src,
-                         "algorithmic_bytes_per_launch": alg_bytes_launch, "avg_launch_ms": avg_ms,
+                         "algorithmic_bytes_per_launch": alg_bytes_launch, "avg_launch_ms": avg_ms, "units": units_note,
                          "share_of_gpu_time": dom_ms / max(sum(v[0] for v in ktimes.values()), 1e-9)},
             # the whole chain against HBM (algorithmic bytes / sum of kernel time) and the end-to-end
             # run against the host-to-device link (bytes sent / wall time of the copy-overlapped pipeline)
