@@ -541,3 +541,25 @@ def repetition_pass_docs():
 @pytest.mark.parametrize("name", ["gr_open", "gr_shipped", "shipped_order"])
 def test_repetition_pass_documents(name):
     check_texts(name, repetition_pass_docs())
+
+
+def test_utf8_validation_option():
+    """TB_OPT_VALIDATE_UTF8: the reference only ever sees Rust Strings; a caller that cannot vouch for its bytes has them
+    checked on the device (the count of malformed documents comes back through a pinned word, chunk by chunk)."""
+    from textblaster_b200.error import PipelineError
+    good = ["plain text. more of it here.", "café naïve 中文 \U0001f600 fine."] * 50
+    p = GpuBatchPipeline(CHAINS["gq_open"])
+    p.set_option(_abi.TB_OPT_VALIDATE_UTF8, 1)
+    assert p.run_texts(good).n_docs == 100
+    enc = [t.encode("utf-8") for t in good]
+    enc[37] = b"broken \xc3 lead without continuation"
+    enc[80] = b"overlong \xc0\xaf and a lone \x80 byte"
+    off = np.zeros(len(enc) + 1, np.int64)
+    off[1:] = np.cumsum([len(e) for e in enc])
+    blob = np.frombuffer(b"".join(enc), np.uint8)
+    for chunk in (1 << 30, 1 << 16):
+        p.set_option(_abi.TB_OPT_CHUNK_BYTES, chunk)
+        with pytest.raises(PipelineError, match="invalid UTF-8"):
+            p.run_packed(blob, off)
+    p.set_option(_abi.TB_OPT_VALIDATE_UTF8, 0)
+    p.close()

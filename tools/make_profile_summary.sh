@@ -1,8 +1,8 @@
 #!/bin/bash
-# Rebuild profiles/r01_* from the captures in gpurun_out/ (launch list, full ncu report, bench lines).
+# Rebuild profiles/r02_* from the captures in gpurun_out/ (launch list, full ncu report, bench lines).
 # usage: tools/make_profile_summary.sh <full-report.ncu-rep>
 set -e
-REP=${1:-gpurun_out/r01_full_top4.ncu-rep}
+REP=${1:-gpurun_out/r02_full_top4.ncu-rep}
 ncu -i "$REP" --page raw --csv 2>/dev/null | python -c "
 import csv,sys,json
 rows=list(csv.reader(sys.stdin)); hdr=rows[0]; units=rows[1]; out={}
@@ -17,14 +17,14 @@ out['_captured_launch_algorithmic_bytes']=float(sys.argv[1]) if len(sys.argv)>1 
 json.dump(out, open('profiles/roofline_traffic.json','w'), indent=1)
 "
 {
-echo "# Round 1 -- ncu evidence for the bench command (python bench.py, 1M docs per step, chunks ramping up to 1 GiB)"
+echo "# Round 2 -- ncu evidence for the bench command (python bench.py, 1M docs per step, chunks ramping up to 1 GiB)"
 echo "# capture: ncu --set full --clock-control none --import-source on, first launch of each listed kernel (the first chunk of the device-resident run: 256 MiB, ~76k docs)"
-echo "# launch list: profiles/r01_launches.csv (ncu --metrics gpu__time_duration.sum --clock-control none, serialised, cold caches)"
+echo "# launch list: profiles/r02_launches.csv (ncu --metrics gpu__time_duration.sum --clock-control none, serialised, cold caches)"
 echo
-echo "## kernel share of the step: ncu launch list vs CUDA events inside bench.py (profiles/r01_bench_n1_1Mdocs.json)"
+echo "## kernel share of the step: ncu launch list vs CUDA events inside bench.py (profiles/r02_bench_n1_1Mdocs.json)"
 python - <<'PY'
 import csv, collections, json
-rows=list(csv.reader(open('gpurun_out/r01_launches.csv')))
+rows=list(csv.reader(open('gpurun_out/r02_launches.csv')))
 hi=[i for i,r in enumerate(rows) if r and r[0]=="ID"][0]
 hdr=rows[hi]; kn=hdr.index("Kernel Name"); mv=hdr.index("Metric Value"); mu=hdr.index("Metric Unit")
 agg=collections.defaultdict(lambda:[0,0.0])
@@ -33,7 +33,7 @@ for r in rows[hi+1:]:
     name=r[kn].split("(")[0].split("::")[-1]; v=float(r[mv].replace(",","")); u=r[mu]
     agg[name][0]+=1; agg[name][1]+= v*1e3 if u=="us" else v*1e6 if u=="ms" else v
 tot=sum(v[1] for v in agg.values())
-live=json.load(open('gpurun_out/r01_bench_n1.json'))["kernels_ms_per_step"]; lt=sum(live.values())
+live=json.load(open('gpurun_out/r02_bench_n1.json'))["kernels_ms_per_step"]; lt=sum(live.values())
 print("%-18s %9s %12s %8s %10s"%("kernel","launches","ncu ms","ncu %","events %"))
 for k,v in sorted(agg.items(), key=lambda kv:-kv[1][1]):
     print("%-18s %9d %12.3f %7.1f%% %9s"%(k,v[0],v[1]/1e6,100*v[1]/tot, ("%.1f%%"%(100*live[k]/lt)) if k in live else "-"))
@@ -47,10 +47,10 @@ python tools/ncu_footprint.py "$REP"
 echo
 echo "## where the instructions go (per source file, hottest lines)"
 python tools/ncu_regions.py "$REP" 14
-} > profiles/r01_ncu_summary.txt 2>&1
-cp gpurun_out/r01_launches.csv profiles/r01_launches.csv
-cp gpurun_out/r01_bench_n1.json profiles/r01_bench_n1_1Mdocs.json
-cp gpurun_out/r01_bench_reference.json profiles/r01_bench_reference_arm.json
-cp gpurun_out/r01_gpu_tests.log profiles/r01_gpu_tests.log
-[ -f gpurun_out/r01_bench_n1_with_fineweb.json ] && cp gpurun_out/r01_bench_n1_with_fineweb.json profiles/r01_bench_n1_with_fineweb.json
+} > profiles/r02_ncu_summary.txt 2>&1
+cp gpurun_out/r02_launches.csv profiles/r02_launches.csv
+cp gpurun_out/r02_bench_n1.json profiles/r02_bench_n1_1Mdocs.json
+cp gpurun_out/r02_bench_reference.json profiles/r02_bench_reference_arm.json
+cp gpurun_out/r02_gpu_tests.log profiles/r02_gpu_tests.log
+[ -f gpurun_out/r02_bench_n1_with_fineweb.json ] && cp gpurun_out/r02_bench_n1_with_fineweb.json profiles/r02_bench_n1_with_fineweb.json
 echo done
