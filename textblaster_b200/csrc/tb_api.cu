@@ -446,16 +446,28 @@ void gather_range(const GatherSrc& g, int64_t d0, int64_t d1, int64_t last_end, 
   each([&](int t) {
     int64_t k = k_base + share_docs[t], o = byte_base + share_bytes[t];
     StreamWriter w(dst, o);
-    for (int64_t d = d0 + n * t / T, e = d0 + n * (t + 1) / T; d < e; d++) {
+    // Every run starts somewhere else in the input, so a copy begins with a miss.  A second cursor runs a few runs
+    // ahead of the copy (across documents) and asks for the first lines of each run it passes.
+    const int64_t d_end = d0 + n * (t + 1) / T;
+    int64_t pd = d0 + n * t / T, pr = -1, ahead = 0;
+    auto prefetch_next = [&]() {
+      for (;;) {
+        if (pd >= d_end) return;
+        if (pr < 0) { if (g.select && !g.select[pd]) { pd++; continue; } pr = g.ro[pd]; }
+        if (pr >= ro_end(pd)) { pd++; pr = -1; continue; }
+        const uint8_t* nx = g.utf8 + off_at(g.offsets, g.is64, pd) + g.runs[pr].begin;
+        __builtin_prefetch(nx); __builtin_prefetch(nx + 64); __builtin_prefetch(nx + 128); __builtin_prefetch(nx + 192);
+        pr++; ahead++;
+        return;
+      }
+    };
+    if (dst) for (int i = 0; i < 6; i++) prefetch_next();
+    for (int64_t d = d0 + n * t / T; d < d_end; d++) {
       if (g.select && !g.select[d]) continue;
       const uint8_t* src = g.utf8 + off_at(g.offsets, g.is64, d);
       for (int64_t r = g.ro[d], re = ro_end(d); r < re; r++) {
         const size_t len = (size_t)g.runs[r].end - g.runs[r].begin;
-        if (dst) {
-          // the next run starts somewhere else in the input: ask for its first lines while this one is copied
-          if (r + 1 < re) { const uint8_t* nx = src + g.runs[r + 1].begin; __builtin_prefetch(nx); __builtin_prefetch(nx + 64); __builtin_prefetch(nx + 128); }
-          w.write(src + g.runs[r].begin, len);
-        }
+        if (dst) { prefetch_next(); w.write(src + g.runs[r].begin, len); }
         o += (int64_t)len;
       }
       dst_off[++k] = o;
