@@ -72,14 +72,16 @@ TB_D_NOINLINE void gq_doc_walk(const Classifier& C, const TextRange& R, const Sw
   }
 }
 #define TB_GQ_STAGE (23 * 32)  // stop-word candidates one tile can hold: a stretch ends at most 22 words (two per three bytes) + 1
+template <class Feed>
 TB_D bool gq_doc_tiles(const KBatch& a, const LutEntry* lut, uint32_t* stage, const Classifier& C, const SwTable& sw,
-                       const TextRange& R, GqAcc& acc, int lane, TileFeed& feed);
+                       const TextRange& R, GqAcc& acc, int lane, Feed& feed);
 // `stage`: 2 * TB_GQ_STAGE words of per-warp scratch (shared memory)
-// `feed`: the warp's bulk-copy ring for the tiles of long documents (tb_feed.cuh); NULL: plain loads only
+// `feed`: the warp's bulk-copy ring for the tiles of long documents (TileFeed, tb_feed.cuh), or NoFeed: plain loads only
+template <class Feed = NoFeed>
 TB_D void body_gq(const KBatch& a, const uint16_t* s_ascii, const LutEntry* lut, uint32_t* stage, const SwTable& sw, const GqCfg& cfg,
-                  int step, tb_gq_stats* out, int64_t d, int lane, TileFeed* feed = nullptr) {
-  TileFeed nofeed; nofeed.on = false;
-  TileFeed& F = feed ? *feed : nofeed;
+                  int step, tb_gq_stats* out, int64_t d, int lane, Feed* feed = nullptr) {
+  Feed nofeed{};
+  Feed& F = feed ? *feed : nofeed;
   Classifier C{s_ascii, a.uc};
   C.key_maxlen = sw.maxlen; C.key_lenmask = sw.lenmask; C.key_firstmask = sw.firstmask;
   TextRange R{a.text, a.rs[d], a.re[d]};
@@ -213,14 +215,16 @@ TB_D_NOINLINE void gr_doc_walk(const KBatch& a, const Classifier& C, const TextR
 // bytes, "a\u00a9a\u00a9..."); a tile with more than this many -- twelve per stretch, under three bytes per word and
 // separator -- hands the document to the walking path instead of tripling every warp's shared memory.
 #define TB_GR_STAGE_WORDS (12 * 32)
+template <class Feed>
 TB_D bool gr_doc_tiles(const KBatch& a, const LutEntry* lut, uint32_t* stage, const Classifier& C, const TextRange& R,
-                       const GrScratch& s, int64_t d, int lane, GrTotals& out, TileFeed& feed);
+                       const GrScratch& s, int64_t d, int lane, GrTotals& out, Feed& feed);
 
 // `stage`: 5 * TB_GR_STAGE_WORDS words of per-warp scratch (shared memory, 8-byte aligned)
+template <class Feed = NoFeed>
 TB_D void body_gr_scan(const KBatch& a, const uint16_t* s_ascii, const LutEntry* lut, uint32_t* stage, const int64_t* ts,
-                       const int64_t* te, const GrScratch& s, int64_t d, int lane, TileFeed* feed = nullptr) {
-  TileFeed nofeed; nofeed.on = false;
-  TileFeed& F = feed ? *feed : nofeed;
+                       const int64_t* te, const GrScratch& s, int64_t d, int lane, Feed* feed = nullptr) {
+  Feed nofeed{};
+  Feed& F = feed ? *feed : nofeed;
   Classifier C{s_ascii, a.uc};
   TextRange R{a.text, ts[d], te[d]};
   GrTotals o;
@@ -304,13 +308,15 @@ TB_D void body_gr_rep_x(const KBatch& a, uint64_t* red, const int64_t* ts, const
 // ---------------------------------------------------------------------------------------------
 // Pass A: doc-level checks, processed lines P, line count; zeroes the per-line slots.
 #define TB_STAGE_BYTES (TB_TILE + 64)  // per-warp staging buffer of the compacting stores (tile_store_kept)
+template <class Feed>
 TB_D void c4a_doc_tiles(const KBatch& a, const LutEntry* lut, uint8_t* stage, const Classifier& C, const C4Cfg& cfg, const C4Scratch& s,
-                        const TextRange& R, int64_t d, int lane, TileFeed& feed);
+                        const TextRange& R, int64_t d, int lane, Feed& feed);
 TB_D_NOINLINE void c4a_doc_walk(const KBatch& a, const Classifier& C, const C4Cfg& cfg, const C4Scratch& s, const TextRange& R, int64_t d, int lane);
+template <class Feed = NoFeed>
 TB_D void body_c4_a(const KBatch& a, const uint16_t* s_ascii, const LutEntry* lut, uint8_t* stage, const C4Cfg& cfg, const C4Scratch& s,
-                    int64_t d, int lane, TileFeed* feed = nullptr) {
-  TileFeed nofeed; nofeed.on = false;
-  TileFeed& F = feed ? *feed : nofeed;
+                    int64_t d, int lane, Feed* feed = nullptr) {
+  Feed nofeed{};
+  Feed& F = feed ? *feed : nofeed;
   Classifier C{s_ascii, a.uc};
   TextRange R{a.text, a.rs[d], a.re[d]};
   if (a.dbg & TB_DBG_FORCE_WALK) { c4a_doc_walk(a, C, cfg, s, R, d, lane); TBE_COUNT(tbe_stat_walk, lane); }
@@ -405,12 +411,14 @@ TB_D_NOINLINE void c4b_doc_walk(const Classifier& C, const C4Cfg& cfg, const C4S
     nl += tot;
   }
 }
+template <class Feed>
 TB_D bool c4b_doc_tiles(const KBatch& a, const LutEntry* lut, const Classifier& C, const C4Cfg& cfg, const C4Scratch& s,
-                        const TextRange& R, uint64_t lb, int lane, TileFeed& feed);
+                        const TextRange& R, uint64_t lb, int lane, Feed& feed);
+template <class Feed = NoFeed>
 TB_D void body_c4_b(const KBatch& a, const uint16_t* s_ascii, const LutEntry* lut, const C4Cfg& cfg, const C4Scratch& s, int64_t d,
-                    int lane, TileFeed* feed = nullptr) {
-  TileFeed nofeed; nofeed.on = false;
-  TileFeed& F = feed ? *feed : nofeed;
+                    int lane, Feed* feed = nullptr) {
+  Feed nofeed{};
+  Feed& F = feed ? *feed : nofeed;
   Classifier C{s_ascii, a.uc};
   TextRange R{s.P, s.prs[d], s.pre[d]};
   const uint64_t lb = (uint64_t)a.rs[d] + (uint64_t)d;

@@ -60,8 +60,9 @@ TB_D bool gq_len_may_match(const SwTable& sw, uint32_t len, bool pure_ascii) {
   return (uint64_t)len <= 3ull * sw.maxlen;
 }
 // `stage`: 2 * TB_GQ_STAGE words of per-warp scratch (shared memory)
+template <class Feed>
 TB_D bool gq_doc_tiles(const KBatch& a, const LutEntry* lut, uint32_t* stage, const Classifier& C, const SwTable& sw, const TextRange& R,
-                       GqAcc& acc, int lane, TileFeed& feed) {
+                       GqAcc& acc, int lane, Feed& feed) {
   const uint8_t* t = R.t;
   uint32_t* st_pos = stage; uint32_t* st_len = stage + TB_GQ_STAGE;
   Frag carry{0u, 0u};
@@ -184,8 +185,9 @@ TB_D bool gq_doc_tiles(const KBatch& a, const LutEntry* lut, uint32_t* stage, co
 // ---------------------------------------------------------------------------------------------
 // C4QualityFilter pass B (c4_filters.rs:207-250): words per processed line, longest word, line flags
 // ---------------------------------------------------------------------------------------------
+template <class Feed>
 TB_D bool c4b_doc_tiles(const KBatch& a, const LutEntry* lut, const Classifier& C, const C4Cfg& cfg, const C4Scratch& s,
-                        const TextRange& R, uint64_t lb, int lane, TileFeed& feed) {
+                        const TextRange& R, uint64_t lb, int lane, Feed& feed) {
   const uint8_t* t = R.t;
   const bool check_len = cfg.max_word_length > 0;
   const bool small = check_len && cfg.max_word_length < 32;  // words inside one stretch can be too long
@@ -285,8 +287,9 @@ TB_D HLS hls_cat(HLS x, HLS y, const uint64_t* powtab) { HLS r; r.sig = tb_sig_c
 TB_D HLS hls_shfl_up(HLS v, int o) { HLS r; r.h = hl_shfl_up(v.h, o); r.sig = (uint64_t)simt_shfl_up64((int64_t)v.sig, o); return r; }
 TB_D HLS hls_shfl(HLS v, int src) { HLS r; r.h = hl_shfl(v.h, src); r.sig = simt_shfl(v.sig, src); return r; }
 
+template <class Feed>
 TB_D bool gr_doc_tiles(const KBatch& a, const LutEntry* lut, uint32_t* stage, const Classifier& C, const TextRange& R,
-                       const GrScratch& s, int64_t d, int lane, GrTotals& out, TileFeed& feed) {
+                       const GrScratch& s, int64_t d, int lane, GrTotals& out, Feed& feed) {
   uint64_t* st_s = (uint64_t*)stage;
   uint32_t* st_a = stage + 2 * TB_GR_STAGE_WORDS; uint32_t* st_b = stage + 3 * TB_GR_STAGE_WORDS; uint32_t* st_n = stage + 4 * TB_GR_STAGE_WORDS;
   const uint64_t uw = tb_wunit(R.rs, d), ul = tb_lunit(R.rs, d);
@@ -513,8 +516,9 @@ TB_D uint32_t tile_store_kept(const uint32_t* w, uint32_t K, uint8_t* stage, uin
 // C4QualityFilter pass A (c4_filters.rs:150-151,175-199): document flags, line count, and the processed
 // lines P: every line trimmed, citations removed, still joined by the original '\n'.
 // ---------------------------------------------------------------------------------------------
+template <class Feed>
 TB_D void c4a_doc_tiles(const KBatch& a, const LutEntry* lut, uint8_t* stage, const Classifier& C, const C4Cfg& cfg, const C4Scratch& s,
-                        const TextRange& R, int64_t d, int lane, TileFeed& feed) {
+                        const TextRange& R, int64_t d, int lane, Feed& feed) {
   const uint8_t* t = R.t;
   uint8_t* out = s.P + R.rs;
   const uint64_t lb = (uint64_t)R.rs + (uint64_t)d;

@@ -25,6 +25,14 @@
 #define TB_FEED_SMEM (TB_FEED_STAGES * TB_TILE + TB_FEED_STAGES * 8)
 #define TB_FEED_NONE 0xFFFFFFFFu
 
+// What the kernels without bulk staging are built with: nothing is staged, and every call folds away.
+struct NoFeed {
+  TB_HD void begin(const uint8_t*, int64_t, int64_t, int64_t, int64_t, int, uint32_t) {}
+  TB_HD uint32_t tile(int64_t) const { return 0xFFFFFFFFu; }
+  TB_HD void done(int64_t, int) {}
+  TB_HD void drain(int64_t) {}
+};
+
 #if defined(__CUDA_ARCH__)
 struct TileFeed {
   uint32_t buf;      // shared-memory address of the ring (TB_FEED_STAGES tiles, 128-byte aligned)
@@ -98,3 +106,8 @@ struct TileFeed {  // host emulation: nothing is staged
   void drain(int64_t) {}
 };
 #endif
+
+template <bool FEED> struct FeedOf { using type = NoFeed; };
+template <> struct FeedOf<true> { using type = TileFeed; };
+TB_HD void feed_init(NoFeed&, uint8_t*, int) {}
+TB_HD void feed_init(TileFeed& f, uint8_t* shared, int lane) { f.init(shared, lane); }

@@ -76,6 +76,8 @@ __global__ void __launch_bounds__(TB_BLOCK) k_validate_utf8(const uint8_t* t, co
   int64_t d = warp_doc();
   if (d < n) body_validate_utf8(t, rs, re, bad, d, threadIdx.x & 31);
 }
+// FEED: the tiles of long documents arrive by bulk copy (tb_feed.cuh); the plain build carries none of that code
+template <bool FEED>
 __global__ void __launch_bounds__(TB_BLOCK, 12) k_gq(KBatch a, SwTable sw, GqCfg cfg, int step, tb_gq_stats* out, uint32_t* cursor) {
   __shared__ uint16_t s_ascii[192];
   __shared__ LutEntry s_lut[256];
@@ -88,9 +90,9 @@ __global__ void __launch_bounds__(TB_BLOCK, 12) k_gq(KBatch a, SwTable sw, GqCfg
     __syncthreads();
     sw.e = s_sw;
   }
-  __shared__ __align__(1024) uint8_t s_feed[TB_FEED_SMEM];  // tiles of long documents arrive here by bulk copy (tb_feed.cuh)
-  TileFeed feed;
-  feed.init(s_feed, threadIdx.x & 31);
+  __shared__ __align__(128) uint8_t s_feed[FEED ? TB_FEED_SMEM : 16];
+  typename FeedOf<FEED>::type feed;
+  feed_init(feed, s_feed, threadIdx.x & 31);
   for (;;) {
     const int64_t d = next_doc(cursor, a);
     if (d == -1) break;
@@ -104,15 +106,16 @@ __global__ void k_trim(KBatch a, int64_t* ts, int64_t* te) {
   int64_t d = thread_doc();
   if (d < a.n) body_trim(a, s_ascii, ts, te, d);
 }
+template <bool FEED>
 __global__ void __launch_bounds__(TB_BLOCK, 16) k_gr_scan(KBatch a, const int64_t* ts, const int64_t* te, GrScratch s) {
   __shared__ uint16_t s_ascii[192];
   __shared__ LutEntry s_lut[256];
   load_ascii(s_ascii, a.uc);
   load_lut(s_lut, a.uc, TB_LUT_GR, 0u);
   __shared__ __align__(8) uint32_t s_stage[5 * TB_GR_STAGE_WORDS];
-  __shared__ __align__(1024) uint8_t s_feed[TB_FEED_SMEM];
-  TileFeed feed;
-  feed.init(s_feed, threadIdx.x & 31);
+  __shared__ __align__(128) uint8_t s_feed[FEED ? TB_FEED_SMEM : 16];
+  typename FeedOf<FEED>::type feed;
+  feed_init(feed, s_feed, threadIdx.x & 31);
   for (;;) {
     const int64_t d = next_doc(&s.counters[8], a);
     if (d == -1) break;
@@ -177,15 +180,16 @@ __global__ void __launch_bounds__(TB_REP_X_THREADS) k_gr_rep_x(KBatch a, const i
     body_gr_rep_x(a, s_red, ts, te, s, cfg, step, out, (int64_t)s.lists[3 * (uint64_t)s.n + i], (int)threadIdx.x);
   }
 }
+template <bool FEED>
 __global__ void __launch_bounds__(TB_BLOCK, 24) k_c4_a(KBatch a, C4Cfg cfg, C4Scratch s, uint32_t* cursor) {
   __shared__ uint16_t s_ascii[192];
   __shared__ LutEntry s_lut[256];
   __shared__ __align__(16) uint8_t s_stage[TB_STAGE_BYTES];
   load_ascii(s_ascii, a.uc);
   load_lut(s_lut, a.uc, TB_LUT_C4A, 0u);
-  __shared__ __align__(1024) uint8_t s_feed[TB_FEED_SMEM];
-  TileFeed feed;
-  feed.init(s_feed, threadIdx.x & 31);
+  __shared__ __align__(128) uint8_t s_feed[FEED ? TB_FEED_SMEM : 16];
+  typename FeedOf<FEED>::type feed;
+  feed_init(feed, s_feed, threadIdx.x & 31);
   for (;;) {
     const int64_t d = next_doc(cursor, a);
     if (d == -1) break;
@@ -217,14 +221,15 @@ __global__ void __launch_bounds__(TB_BLOCK, 16) k_c4_sent(KBatch a, const int64_
     else if ((threadIdx.x & 31) == 0) { srs[d] = tb_sent_off(a.rs[d], d); sre[d] = srs[d]; }
   }
 }
+template <bool FEED>
 __global__ void __launch_bounds__(TB_BLOCK, 20) k_c4_b(KBatch a, C4Cfg cfg, C4Scratch s, uint32_t* cursor) {
   __shared__ uint16_t s_ascii[192];
   __shared__ LutEntry s_lut[256];
   load_ascii(s_ascii, a.uc);
   load_lut(s_lut, a.uc, TB_LUT_C4B, 0u);
-  __shared__ __align__(1024) uint8_t s_feed[TB_FEED_SMEM];
-  TileFeed feed;
-  feed.init(s_feed, threadIdx.x & 31);
+  __shared__ __align__(128) uint8_t s_feed[FEED ? TB_FEED_SMEM : 16];
+  typename FeedOf<FEED>::type feed;
+  feed_init(feed, s_feed, threadIdx.x & 31);
   for (;;) {
     const int64_t d = next_doc(cursor, a);
     if (d == -1) break;
@@ -343,13 +348,19 @@ void tb_launch_validate_utf8(cudaStream_t st, const uint8_t* text, const int64_t
 }
 void tb_launch_gq(cudaStream_t st, const KBatch& b, const SwTable& sw, const GqCfg& cfg, int step, tb_gq_stats* out,
                   int sm_count, uint32_t* cursor) {
-  if (b.n) k_gq<<<persistent_grid(b.n, sm_count, 12), TB_BLOCK, 0, st>>>(b, sw, cfg, step, out, cursor);
+  if (b.n) {
+    if (b.feed_min_tiles) k_gq<true><<<persistent_grid(b.n, sm_count, 12), TB_BLOCK, 0, st>>>(b, sw, cfg, step, out, cursor);
+    else k_gq<false><<<persistent_grid(b.n, sm_count, 12), TB_BLOCK, 0, st>>>(b, sw, cfg, step, out, cursor);
+  }
 }
 void tb_launch_trim(cudaStream_t st, const KBatch& b, int64_t* ts, int64_t* te) {
   if (b.n) k_trim<<<blocks_for_threads(b.n), 256, 0, st>>>(b, ts, te);
 }
 void tb_launch_gr_scan(cudaStream_t st, const KBatch& b, const int64_t* ts, const int64_t* te, const GrScratch& s, int sm_count) {
-  if (b.n) k_gr_scan<<<persistent_grid(b.n, sm_count, 16), TB_BLOCK, 0, st>>>(b, ts, te, s);
+  if (b.n) {
+    if (b.feed_min_tiles) k_gr_scan<true><<<persistent_grid(b.n, sm_count, 16), TB_BLOCK, 0, st>>>(b, ts, te, s);
+    else k_gr_scan<false><<<persistent_grid(b.n, sm_count, 16), TB_BLOCK, 0, st>>>(b, ts, te, s);
+  }
 }
 void tb_launch_gr_rep(cudaStream_t st, const KBatch& b, const int64_t* ts, const int64_t* te, const GrScratch& s,
                       const GrCfg& cfg, int step, tb_gr_stats* out, int sm_count, int tier) {
@@ -372,7 +383,10 @@ int tb_kernels_init() {
   return (int)e;
 }
 void tb_launch_c4_a(cudaStream_t st, const KBatch& b, const C4Cfg& cfg, const C4Scratch& s, int sm_count, uint32_t* cursor) {
-  if (b.n) k_c4_a<<<persistent_grid(b.n, sm_count, 24), TB_BLOCK, 0, st>>>(b, cfg, s, cursor);
+  if (b.n) {
+    if (b.feed_min_tiles) k_c4_a<true><<<persistent_grid(b.n, sm_count, 24), TB_BLOCK, 0, st>>>(b, cfg, s, cursor);
+    else k_c4_a<false><<<persistent_grid(b.n, sm_count, 24), TB_BLOCK, 0, st>>>(b, cfg, s, cursor);
+  }
 }
 void tb_launch_entities(cudaStream_t st, const KBatch& b, const EntEntry* tab, uint32_t ntab, uint32_t* amp, uint32_t* drop,
                         uint8_t* D, int64_t* drs, int64_t* dre, int sm_count, uint32_t* cursor) {
@@ -383,7 +397,10 @@ void tb_launch_c4_sent(cudaStream_t st, const KBatch& b, const int64_t* ts, cons
   if (b.n) k_c4_sent<<<persistent_grid(b.n, sm_count, 16), TB_BLOCK, 0, st>>>(b, ts, te, bits, S, srs, sre, cursor);
 }
 void tb_launch_c4_b(cudaStream_t st, const KBatch& b, const C4Cfg& cfg, const C4Scratch& s, int sm_count, uint32_t* cursor) {
-  if (b.n) k_c4_b<<<persistent_grid(b.n, sm_count, 20), TB_BLOCK, 0, st>>>(b, cfg, s, cursor);
+  if (b.n) {
+    if (b.feed_min_tiles) k_c4_b<true><<<persistent_grid(b.n, sm_count, 20), TB_BLOCK, 0, st>>>(b, cfg, s, cursor);
+    else k_c4_b<false><<<persistent_grid(b.n, sm_count, 20), TB_BLOCK, 0, st>>>(b, cfg, s, cursor);
+  }
 }
 void tb_launch_c4_c(cudaStream_t st, const KBatch& b, const C4Cfg& cfg, const C4Scratch& s, int sm_count, uint32_t* cursor) {
   if (b.n) k_c4_c<<<persistent_grid(b.n, sm_count, 32), TB_BLOCK, 0, st>>>(b, cfg, s, cursor);
