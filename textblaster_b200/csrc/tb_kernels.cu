@@ -90,7 +90,7 @@ __global__ void __launch_bounds__(TB_BLOCK, 12) k_gq(KBatch a, SwTable sw, GqCfg
     __syncthreads();
     sw.e = s_sw;
   }
-  __shared__ __align__(128) uint8_t s_feed[FEED ? TB_FEED_SMEM : 16];
+  __shared__ __align__(FEED ? TB_TILE : 16) uint8_t s_feed[FEED ? TB_FEED_SMEM : 16];  // the ring is aligned on the tile size (tile_classify relies on it)
   typename FeedOf<FEED>::type feed;
   feed_init(feed, s_feed, threadIdx.x & 31);
   for (;;) {
@@ -113,7 +113,7 @@ __global__ void __launch_bounds__(TB_BLOCK, 16) k_gr_scan(KBatch a, const int64_
   load_ascii(s_ascii, a.uc);
   load_lut(s_lut, a.uc, TB_LUT_GR, 0u);
   __shared__ __align__(8) uint32_t s_stage[5 * TB_GR_STAGE_WORDS];
-  __shared__ __align__(128) uint8_t s_feed[FEED ? TB_FEED_SMEM : 16];
+  __shared__ __align__(FEED ? TB_TILE : 16) uint8_t s_feed[FEED ? TB_FEED_SMEM : 16];  // the ring is aligned on the tile size (tile_classify relies on it)
   typename FeedOf<FEED>::type feed;
   feed_init(feed, s_feed, threadIdx.x & 31);
   for (;;) {
@@ -187,7 +187,7 @@ __global__ void __launch_bounds__(TB_BLOCK, 24) k_c4_a(KBatch a, C4Cfg cfg, C4Sc
   __shared__ __align__(16) uint8_t s_stage[TB_STAGE_BYTES];
   load_ascii(s_ascii, a.uc);
   load_lut(s_lut, a.uc, TB_LUT_C4A, 0u);
-  __shared__ __align__(128) uint8_t s_feed[FEED ? TB_FEED_SMEM : 16];
+  __shared__ __align__(FEED ? TB_TILE : 16) uint8_t s_feed[FEED ? TB_FEED_SMEM : 16];  // the ring is aligned on the tile size (tile_classify relies on it)
   typename FeedOf<FEED>::type feed;
   feed_init(feed, s_feed, threadIdx.x & 31);
   for (;;) {
@@ -227,7 +227,7 @@ __global__ void __launch_bounds__(TB_BLOCK, 20) k_c4_b(KBatch a, C4Cfg cfg, C4Sc
   __shared__ LutEntry s_lut[256];
   load_ascii(s_ascii, a.uc);
   load_lut(s_lut, a.uc, TB_LUT_C4B, 0u);
-  __shared__ __align__(128) uint8_t s_feed[FEED ? TB_FEED_SMEM : 16];
+  __shared__ __align__(FEED ? TB_TILE : 16) uint8_t s_feed[FEED ? TB_FEED_SMEM : 16];  // the ring is aligned on the tile size (tile_classify relies on it)
   typename FeedOf<FEED>::type feed;
   feed_init(feed, s_feed, threadIdx.x & 31);
   for (;;) {
