@@ -460,8 +460,8 @@ def run_config3(args, rank):
             launches += r.gpu_launches
             big = np.maximum(r.stats[0]["n_words"], r.stats[0]["n_lines"])
             rows.append({"list": kind, "n": order, "docs_per_s": n / dt, "text_gbs": nbytes / dt / 1e9, "ms": dt * 1e3, "gpu_ms": r.gpu_ms, "kept": int(r.keep.sum())})
-            tier = {"S": float((big <= 512).mean()), "M": float(((big > 512) & (big <= 2048)).mean()),
-                    "L": float(((big > 2048) & (big <= 8192)).mean()), "X_global": float((big > 8192).mean())}
+            tier = {"w256_w512": float((big <= 512).mean()), "c1k_c2k": float(((big > 512) & (big <= 2048)).mean()),
+                    "c4k_c8k": float(((big > 2048) & (big <= 8192)).mean()), "X_global": float((big > 8192).mean())}
             p.close()
     clocks = sampler.stop()
     peak, peak_src = measured_peaks()
@@ -867,7 +867,8 @@ def main():
         launches_per_step = max(dom_launches / K, 1)
         alg_bytes_launch = alg_bytes_step / launches_per_step
         units_note = "every document of the chunk"
-        tier_of = {"k_gr_rep_s": 0, "k_gr_rep_m": 1, "k_gr_rep_l": 2}
+        # (the repetition pass's tiers by size: tb_rep_cap in csrc/tb_kernels.cuh)
+        tier_of = {"k_gr_rep_w256": 0, "k_gr_rep_w512": 1, "k_gr_rep_c1k": 2, "k_gr_rep_c2k": 3, "k_gr_rep_c4k": 4, "k_gr_rep_c8k": 5}
         if dom_name in tier_of:
             # a tier kernel of the repetition pass only works on the documents of its size class that reached the step:
             # it is credited with their text (and their 24 bytes of offsets / results), not with the whole chunk's
@@ -875,7 +876,7 @@ def main():
             res = pipe.run_packed(utf8, off, copy_content=False)
             ran = (res.failed_step < 0) | (res.failed_step >= gr_idx)
             big = np.maximum(res.stats[gr_idx]["n_words"], res.stats[gr_idx]["n_lines"])
-            lo, hi = [(0, 512), (512, 2048), (2048, 8192)][tier_of[dom_name]]
+            lo, hi = [(0, 256), (256, 512), (512, 1024), (1024, 2048), (2048, 4096), (4096, 8192)][tier_of[dom_name]]
             sel = ran & (big > lo if lo else big >= 0) & (big <= hi)
             tier_bytes = int(np.diff(off)[sel].sum()) + 24 * int(sel.sum())
             alg_bytes_launch = tier_bytes / launches_per_step

@@ -234,19 +234,23 @@ extern "C" int tbe_run_chain(const tb_step_cfg* steps, size_t n_steps, const uin
       g.dup_line_char_frac = q.dup_line_char_frac; g.dup_para_char_frac = q.dup_para_char_frac;
       for (int k = 0; k < TB_MAX_NGRAMS; k++) { g.top_n[k] = q.top_n[k]; g.top_frac[k] = q.top_frac[k]; g.dup_n[k] = q.dup_n[k]; g.dup_frac[k] = q.dup_frac[k]; }
       GrScratch gs{(uint64_t*)G64(wunits), G32(wunits), (uint64_t*)G64(wunits), (uint64_t*)G64(units), G32(units), G8(units),
-                   (GrDoc*)G8(n1 * sizeof(GrDoc)), G32(wunits * TB_REP_K + n1 * TB_REP_DOC_EXTRA), G32(4 * n1), G32(16), n};
-      memset(gs.counters, 0, 64);
+                   (GrDoc*)G8(n1 * sizeof(GrDoc)), G32(wunits * TB_REP_K + n1 * TB_REP_DOC_EXTRA), G32(TB_REP_NT * n1), G32(TB_GR_COUNTERS), n};
+      memset(gs.counters, 0, TB_GR_COUNTERS * 4);
       for (int64_t d = 0; d < n; d++) body_trim(b, ascii, ts, te, d);
       build_lut(TB_LUT_GR, 0u);
       uint32_t* stage = (uint32_t*)G64(5 * TB_GR_STAGE_WORDS / 2 + 1);
       run_warps(n, alive_pred, [&](int64_t d, int lane) { body_gr_scan(b, ascii, lut.data(), stage, ts, te, gs, d, lane); });
-      uint8_t* smem_s = (uint8_t*)G64(TB_REP_S_SMEM / 8 + 2);
-      uint8_t* smem_m = (uint8_t*)G64(TB_REP_M_SMEM / 8 + 2);
-      run_warps_list(gs.lists, gs.counters[0], [&](int64_t d, int lane) { body_gr_rep_s(b, smem_s, ts, te, gs, g, (int)s, (tb_gr_stats*)stats, d, lane); });
-      run_blocks(gs.lists + n, gs.counters[1], TB_REP_M_THREADS, [&](int64_t d, int tid) { body_gr_rep_m(b, smem_m, ts, te, gs, g, (int)s, (tb_gr_stats*)stats, d, tid); });
-      uint8_t* smem_l = (uint8_t*)G64(TB_REP_L_SMEM / 8 + 2);
-      run_blocks(gs.lists + 2 * n, gs.counters[2], TB_REP_L_THREADS, [&](int64_t d, int tid) { body_gr_rep_l(b, smem_l, ts, te, gs, g, (int)s, (tb_gr_stats*)stats, d, tid); });
-      run_blocks(gs.lists + 3 * n, gs.counters[3], TB_REP_X_THREADS, [&](int64_t d, int tid) { body_gr_rep_x(b, nullptr, ts, te, gs, g, (int)s, (tb_gr_stats*)stats, d, tid); });
+      for (int tier = 0; tier < TB_REP_TIER_X; tier++) {
+        const uint32_t cap = tb_rep_cap(tier);
+        uint8_t* smem = (uint8_t*)G64(TB_REP_CTA_SMEM(cap) / 8 + 2);
+        if (tier < TB_REP_WARP_TIERS)
+          run_warps_list(gs.lists + (int64_t)tier * n, gs.counters[TB_GR_CNT_LEN(tier)],
+                         [&](int64_t d, int lane) { body_gr_rep_warp(b, smem, cap, ts, te, gs, g, (int)s, (tb_gr_stats*)stats, d, lane); });
+        else
+          run_blocks(gs.lists + (int64_t)tier * n, gs.counters[TB_GR_CNT_LEN(tier)], tb_rep_threads(tier),
+                     [&](int64_t d, int tid) { body_gr_rep_cta(b, smem, cap, ts, te, gs, g, (int)s, (tb_gr_stats*)stats, d, tid); });
+      }
+      run_blocks(gs.lists + (int64_t)TB_REP_TIER_X * n, gs.counters[TB_GR_CNT_LEN(TB_REP_TIER_X)], TB_REP_X_THREADS, [&](int64_t d, int tid) { body_gr_rep_x(b, nullptr, ts, te, gs, g, (int)s, (tb_gr_stats*)stats, d, tid); });
     } else if (sc.type == TB_STEP_FINEWEB_QUALITY) {
       const tb_fw_params& q = sc.u.fw;
       FwCfg f{};

@@ -542,7 +542,7 @@ int ensure_chunk_buffers(tb_pipeline* p, int64_t n, int64_t nb, bool host_input)
       ENS(p->g_wh, wunits * 8); ENS(p->g_wl, wunits * 4); ENS(p->g_ws, wunits * 8); ENS(p->g_lh, units * 8); ENS(p->g_ll, units * 4); ENS(p->g_lg, units);
       ENS(p->g_doc, n1 * sizeof(GrDoc));
       ENS(p->g_work, (wunits * TB_REP_K + n1 * TB_REP_DOC_EXTRA) * 4);
-      ENS(p->g_lists, 4 * n1 * 4); ENS(p->g_counters, 64);
+      ENS(p->g_lists, TB_REP_NT * n1 * 4); ENS(p->g_counters, TB_GR_COUNTERS * 4);
     } else if (sh.type == TB_STEP_FINEWEB_QUALITY) {
       ENS(p->f_lh, units * 8); ENS(p->f_ll, units * 4); ENS(p->f_doc, n1 * sizeof(FwDoc)); ENS(p->f_tab, (units * 2 + n1 * 16) * 4);
     } else if (sh.type == TB_STEP_C4_QUALITY) {
@@ -588,18 +588,20 @@ int enqueue_chain(tb_pipeline* p, const uint8_t* text, int64_t n, int64_t nbytes
       GrScratch g{p->g_wh.as<uint64_t>(), p->g_wl.as<uint32_t>(), p->g_ws.as<uint64_t>(), p->g_lh.as<uint64_t>(), p->g_ll.as<uint32_t>(),
                   p->g_lg.as<uint8_t>(), p->g_doc.as<GrDoc>(), p->g_work.as<uint32_t>(), p->g_lists.as<uint32_t>(),
                   p->g_counters.as<uint32_t>(), n};
-      CK(cudaMemsetAsync(p->g_counters.p, 0, 64, st));
+      CK(cudaMemsetAsync(p->g_counters.p, 0, TB_GR_COUNTERS * 4, st));
       { Timed t(p, "k_trim"); tb_launch_trim(st, b, p->ts.as<int64_t>(), p->te.as<int64_t>()); }
       { Timed t(p, "k_gr_scan"); tb_launch_gr_scan(st, b, p->ts.as<int64_t>(), p->te.as<int64_t>(), g, c->sm_count); }
       // the few documents of tier X (each a long chain of passes on one CTA) run beside the other tiers
       CK(cudaEventRecord(p->ev_fork, st));
       CK(cudaStreamWaitEvent(p->side, p->ev_fork, 0));
-      tb_launch_gr_rep(p->side, b, p->ts.as<int64_t>(), p->te.as<int64_t>(), g, sh.gr, (int)s, p->stats[s][pb].as<tb_gr_stats>(), c->sm_count, 3);
+      tb_launch_gr_rep(p->side, b, p->ts.as<int64_t>(), p->te.as<int64_t>(), g, sh.gr, (int)s, p->stats[s][pb].as<tb_gr_stats>(), c->sm_count, TB_REP_TIER_X);
       CK(cudaEventRecord(p->ev_join, p->side));
       p->launches_this_run++;
-      { Timed t(p, "k_gr_rep_s"); tb_launch_gr_rep(st, b, p->ts.as<int64_t>(), p->te.as<int64_t>(), g, sh.gr, (int)s, p->stats[s][pb].as<tb_gr_stats>(), c->sm_count, 0); }
-      { Timed t(p, "k_gr_rep_m"); tb_launch_gr_rep(st, b, p->ts.as<int64_t>(), p->te.as<int64_t>(), g, sh.gr, (int)s, p->stats[s][pb].as<tb_gr_stats>(), c->sm_count, 1); }
-      { Timed t(p, "k_gr_rep_l"); tb_launch_gr_rep(st, b, p->ts.as<int64_t>(), p->te.as<int64_t>(), g, sh.gr, (int)s, p->stats[s][pb].as<tb_gr_stats>(), c->sm_count, 2); }
+      static const char* const kTierName[TB_REP_TIER_X] = {"k_gr_rep_w256", "k_gr_rep_w512", "k_gr_rep_c1k", "k_gr_rep_c2k", "k_gr_rep_c4k", "k_gr_rep_c8k"};
+      for (int tier = TB_REP_TIER_X - 1; tier >= 0; tier--) {  // the few large documents first
+        Timed t(p, kTierName[tier]);
+        tb_launch_gr_rep(st, b, p->ts.as<int64_t>(), p->te.as<int64_t>(), g, sh.gr, (int)s, p->stats[s][pb].as<tb_gr_stats>(), c->sm_count, tier);
+      }
       { Timed t(p, "k_gr_rep_x(join)"); CK(cudaStreamWaitEvent(st, p->ev_join, 0)); }
     } else if (sh.type == TB_STEP_FINEWEB_QUALITY) {
       FwScratch fs{p->f_lh.as<uint64_t>(), p->f_ll.as<uint32_t>(), p->f_doc.as<FwDoc>(), p->f_tab.as<uint32_t>()};

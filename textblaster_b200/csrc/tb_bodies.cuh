@@ -237,20 +237,19 @@ TB_D void body_gr_scan(const KBatch& a, const uint16_t* s_ascii, const LutEntry*
     GrDoc g; g.char_len = nchars; g.W = W; g.NL = NL; g.flags = flags ? TB_DOCFLAG_COMPLEX_SCRIPT : 0; g.empty = (R.re <= R.rs);
     s.doc[d] = g;
     uint32_t big = W > NL ? W : NL;
-    uint32_t tier = big <= TB_REP_S_CAP ? 0u : big <= TB_REP_M_CAP ? 1u : big <= TB_REP_L_CAP ? 2u : 3u;
-    uint32_t k = simt_atomic_add(&s.counters[tier], 1u);
+    const uint32_t tier = tb_rep_tier(big);
+    uint32_t k = simt_atomic_add(&s.counters[TB_GR_CNT_LEN(tier)], 1u);
     s.lists[(uint64_t)tier * (uint64_t)s.n + k] = (uint32_t)d;
   }
 }
 
 // ---------------------------------------------------------------------------------------------
-// GopherRepetitionFilter, pass 2 (tb_rep.cuh): three tiers by document size
+// GopherRepetitionFilter, pass 2 (tb_rep.cuh): tiers by document size
 // ---------------------------------------------------------------------------------------------
 // shared-memory layout of one document's working arrays for capacity CAP (8-byte aligned pieces first)
 #define TB_REP_SMEM(CAP) ((CAP) * 8 + ((CAP) + 2) * 4 + 2 * (CAP) * 4 + ((CAP) / 32 + 2) * 4 + (CAP) * 2 + (CAP) * 2)
-#define TB_REP_S_SMEM TB_REP_SMEM(TB_REP_S_CAP)
-#define TB_REP_M_SMEM (TB_REP_SMEM(TB_REP_M_CAP) + 64 * 8)
-#define TB_REP_L_SMEM (TB_REP_SMEM(TB_REP_L_CAP) + 64 * 8)
+#define TB_REP_WARP_SMEM(CAP) TB_REP_SMEM(CAP)              // a warp tier
+#define TB_REP_CTA_SMEM(CAP) (TB_REP_SMEM(CAP) + 64 * 8)    // a CTA tier: + the scratch of the CTA's collectives
 struct RepCarve { RepArrays A; uint32_t* tab; uint16_t* cnt; uint16_t* list; uint8_t* end; };
 TB_D RepCarve rep_carve(uint8_t* smem, uint32_t cap) {
   RepCarve c;
@@ -264,24 +263,17 @@ TB_D RepCarve rep_carve(uint8_t* smem, uint32_t cap) {
   return c;
 }
 
-// tier S: one warp, working arrays carved from `smem` (TB_REP_S_SMEM bytes, 8-byte aligned)
-TB_D void body_gr_rep_s(const KBatch& a, uint8_t* smem, const int64_t* ts, const int64_t* te, const GrScratch& s,
-                        const GrCfg& cfg, int step, tb_gr_stats* out, int64_t d, int lane) {
-  RepCarve c = rep_carve(smem, TB_REP_S_CAP);
+// a warp tier: one warp, working arrays of capacity `cap` carved from `smem` (TB_REP_WARP_SMEM(cap) bytes, 8-byte aligned)
+TB_D void body_gr_rep_warp(const KBatch& a, uint8_t* smem, uint32_t cap, const int64_t* ts, const int64_t* te, const GrScratch& s,
+                           const GrCfg& cfg, int step, tb_gr_stats* out, int64_t d, int lane) {
+  RepCarve c = rep_carve(smem, cap);
   WarpGroup g{lane};
   rep_body<WarpGroup, uint16_t>(g, a, ts, te, s, cfg, step, out, d, c.A, c.tab, c.cnt, c.list);
 }
-// tier M: one CTA, working arrays carved from `smem` (TB_REP_M_SMEM bytes)
-TB_D void body_gr_rep_m(const KBatch& a, uint8_t* smem, const int64_t* ts, const int64_t* te, const GrScratch& s,
-                        const GrCfg& cfg, int step, tb_gr_stats* out, int64_t d, int tid) {
-  RepCarve c = rep_carve(smem, TB_REP_M_CAP);
-  BlockGroup g{tid, (uint64_t*)(((uintptr_t)c.end + 7) & ~(uintptr_t)7)};
-  rep_body<BlockGroup, uint16_t>(g, a, ts, te, s, cfg, step, out, d, c.A, c.tab, c.cnt, c.list);
-}
-// tier L: one large CTA, working arrays carved from `smem` (TB_REP_L_SMEM bytes: one CTA per SM)
-TB_D void body_gr_rep_l(const KBatch& a, uint8_t* smem, const int64_t* ts, const int64_t* te, const GrScratch& s,
-                        const GrCfg& cfg, int step, tb_gr_stats* out, int64_t d, int tid) {
-  RepCarve c = rep_carve(smem, TB_REP_L_CAP);
+// a CTA tier: one CTA, working arrays of capacity `cap` carved from `smem` (TB_REP_CTA_SMEM(cap) bytes)
+TB_D void body_gr_rep_cta(const KBatch& a, uint8_t* smem, uint32_t cap, const int64_t* ts, const int64_t* te, const GrScratch& s,
+                          const GrCfg& cfg, int step, tb_gr_stats* out, int64_t d, int tid) {
+  RepCarve c = rep_carve(smem, cap);
   BlockGroup g{tid, (uint64_t*)(((uintptr_t)c.end + 7) & ~(uintptr_t)7)};
   rep_body<BlockGroup, uint16_t>(g, a, ts, te, s, cfg, step, out, d, c.A, c.tab, c.cnt, c.list);
 }

@@ -117,67 +117,61 @@ __global__ void __launch_bounds__(TB_BLOCK, 16) k_gr_scan(KBatch a, const int64_
   typename FeedOf<FEED>::type feed;
   feed_init(feed, s_feed, threadIdx.x & 31);
   for (;;) {
-    const int64_t d = next_doc(&s.counters[8], a);
+    const int64_t d = next_doc(&s.counters[TB_GR_CNT_SCAN], a);
     if (d == -1) break;
     if (d < 0) continue;
     if (a.alive[d]) body_gr_scan(a, s_ascii, s_lut, s_stage, ts, te, s, d, threadIdx.x & 31, &feed);
   }
 }
 // Repetition pass 2, persistent CTAs pulling document ids of their tier from the lists the scan pass built.
-__global__ void __launch_bounds__(32) k_gr_rep_s(KBatch a, const int64_t* ts, const int64_t* te, GrScratch s, GrCfg cfg,
-                                                 int step, tb_gr_stats* out) {
-  __shared__ __align__(16) uint8_t smem[TB_REP_S_SMEM];
+// Warp tiers: RES CTAs of one warp per SM (the register budget follows from it).
+template <int TIER, int RES>
+__global__ void __launch_bounds__(32, RES) k_gr_rep_w(KBatch a, const int64_t* ts, const int64_t* te, GrScratch s, GrCfg cfg,
+                                                      int step, tb_gr_stats* out) {
+  constexpr uint32_t CAP = TB_REP_CAP0 << TIER;
+  __shared__ __align__(16) uint8_t smem[TB_REP_WARP_SMEM(CAP)];
   const int lane = threadIdx.x;
-  const uint32_t count = s.counters[0];
+  const uint32_t count = s.counters[TB_GR_CNT_LEN(TIER)];
+  const uint32_t* list = s.lists + (uint64_t)TIER * (uint64_t)s.n;
   for (;;) {
     uint32_t i = 0;
-    if (lane == 0) i = atomicAdd(&s.counters[4], 1u);
+    if (lane == 0) i = atomicAdd(&s.counters[TB_GR_CNT_CUR(TIER)], 1u);
     i = __shfl_sync(0xFFFFFFFFu, i, 0);
     if (i >= count) break;
-    body_gr_rep_s(a, smem, ts, te, s, cfg, step, out, (int64_t)s.lists[i], lane);
+    body_gr_rep_warp(a, smem, CAP, ts, te, s, cfg, step, out, (int64_t)list[i], lane);
     __syncwarp();
   }
 }
-__global__ void __launch_bounds__(TB_REP_M_THREADS) k_gr_rep_m(KBatch a, const int64_t* ts, const int64_t* te, GrScratch s,
-                                                               GrCfg cfg, int step, tb_gr_stats* out) {
+// CTA tiers: capacity / 8 threads, the working arrays in dynamic shared memory
+template <int TIER>
+__global__ void __launch_bounds__((TB_REP_CAP0 << TIER) / 8) k_gr_rep_c(KBatch a, const int64_t* ts, const int64_t* te, GrScratch s,
+                                                                        GrCfg cfg, int step, tb_gr_stats* out) {
+  constexpr uint32_t CAP = TB_REP_CAP0 << TIER;
   extern __shared__ __align__(16) uint8_t dsmem[];
   __shared__ uint32_t s_i;
-  const uint32_t count = s.counters[1];
+  const uint32_t count = s.counters[TB_GR_CNT_LEN(TIER)];
+  const uint32_t* list = s.lists + (uint64_t)TIER * (uint64_t)s.n;
   for (;;) {
     __syncthreads();
-    if (threadIdx.x == 0) s_i = atomicAdd(&s.counters[5], 1u);
+    if (threadIdx.x == 0) s_i = atomicAdd(&s.counters[TB_GR_CNT_CUR(TIER)], 1u);
     __syncthreads();
     uint32_t i = s_i;
     if (i >= count) break;
-    body_gr_rep_m(a, dsmem, ts, te, s, cfg, step, out, (int64_t)s.lists[(uint64_t)s.n + i], (int)threadIdx.x);
-  }
-}
-__global__ void __launch_bounds__(TB_REP_L_THREADS) k_gr_rep_l(KBatch a, const int64_t* ts, const int64_t* te, GrScratch s,
-                                                               GrCfg cfg, int step, tb_gr_stats* out) {
-  extern __shared__ __align__(16) uint8_t dsmem[];
-  __shared__ uint32_t s_i;
-  const uint32_t count = s.counters[2];
-  for (;;) {
-    __syncthreads();
-    if (threadIdx.x == 0) s_i = atomicAdd(&s.counters[6], 1u);
-    __syncthreads();
-    uint32_t i = s_i;
-    if (i >= count) break;
-    body_gr_rep_l(a, dsmem, ts, te, s, cfg, step, out, (int64_t)s.lists[2 * (uint64_t)s.n + i], (int)threadIdx.x);
+    body_gr_rep_cta(a, dsmem, CAP, ts, te, s, cfg, step, out, (int64_t)list[i], (int)threadIdx.x);
   }
 }
 __global__ void __launch_bounds__(TB_REP_X_THREADS) k_gr_rep_x(KBatch a, const int64_t* ts, const int64_t* te, GrScratch s,
                                                                GrCfg cfg, int step, tb_gr_stats* out) {
   __shared__ uint64_t s_red[64];
   __shared__ uint32_t s_i;
-  const uint32_t count = s.counters[3];
+  const uint32_t count = s.counters[TB_GR_CNT_LEN(TB_REP_TIER_X)];
   for (;;) {
     __syncthreads();
-    if (threadIdx.x == 0) s_i = atomicAdd(&s.counters[7], 1u);
+    if (threadIdx.x == 0) s_i = atomicAdd(&s.counters[TB_GR_CNT_CUR(TB_REP_TIER_X)], 1u);
     __syncthreads();
     uint32_t i = s_i;
     if (i >= count) break;
-    body_gr_rep_x(a, s_red, ts, te, s, cfg, step, out, (int64_t)s.lists[3 * (uint64_t)s.n + i], (int)threadIdx.x);
+    body_gr_rep_x(a, s_red, ts, te, s, cfg, step, out, (int64_t)s.lists[(uint64_t)TB_REP_TIER_X * (uint64_t)s.n + i], (int)threadIdx.x);
   }
 }
 template <bool FEED>
@@ -365,9 +359,13 @@ void tb_launch_gr_scan(cudaStream_t st, const KBatch& b, const int64_t* ts, cons
 void tb_launch_gr_rep(cudaStream_t st, const KBatch& b, const int64_t* ts, const int64_t* te, const GrScratch& s,
                       const GrCfg& cfg, int step, tb_gr_stats* out, int sm_count, int tier) {
   if (!b.n) return;
-  if (tier == 0) k_gr_rep_s<<<sm_count * 20, 32, 0, st>>>(b, ts, te, s, cfg, step, out);
-  else if (tier == 1) k_gr_rep_m<<<sm_count * 5, TB_REP_M_THREADS, TB_REP_M_SMEM, st>>>(b, ts, te, s, cfg, step, out);
-  else if (tier == 2) k_gr_rep_l<<<sm_count, TB_REP_L_THREADS, TB_REP_L_SMEM, st>>>(b, ts, te, s, cfg, step, out);
+  // grids: what fits an SM by shared memory (227 KB) and registers, a little over for the tiers whose CTAs are small
+  if (tier == 0) k_gr_rep_w<0, 32><<<sm_count * 32, 32, 0, st>>>(b, ts, te, s, cfg, step, out);
+  else if (tier == 1) k_gr_rep_w<1, 17><<<sm_count * 17, 32, 0, st>>>(b, ts, te, s, cfg, step, out);
+  else if (tier == 2) k_gr_rep_c<2><<<sm_count * 8, tb_rep_threads(2), TB_REP_CTA_SMEM(tb_rep_cap(2)), st>>>(b, ts, te, s, cfg, step, out);
+  else if (tier == 3) k_gr_rep_c<3><<<sm_count * 4, tb_rep_threads(3), TB_REP_CTA_SMEM(tb_rep_cap(3)), st>>>(b, ts, te, s, cfg, step, out);
+  else if (tier == 4) k_gr_rep_c<4><<<sm_count * 2, tb_rep_threads(4), TB_REP_CTA_SMEM(tb_rep_cap(4)), st>>>(b, ts, te, s, cfg, step, out);
+  else if (tier == 5) k_gr_rep_c<5><<<sm_count, tb_rep_threads(5), TB_REP_CTA_SMEM(tb_rep_cap(5)), st>>>(b, ts, te, s, cfg, step, out);
   else k_gr_rep_x<<<sm_count * 3, TB_REP_X_THREADS, 0, st>>>(b, ts, te, s, cfg, step, out);  // global-memory tables: several CTAs per SM hide the latency
 }
 void tb_launch_fw_scan(cudaStream_t st, const KBatch& b, const FwCfg& cfg, const FwScratch& s, int sm_count, uint32_t* cursor) {
@@ -378,8 +376,9 @@ void tb_launch_fw_fin(cudaStream_t st, const KBatch& b, const FwCfg& cfg, const 
   if (b.n) k_fw_fin<<<persistent_grid(b.n, sm_count, 16), TB_BLOCK, 0, st>>>(b, cfg, s, step, out, cursor);
 }
 int tb_kernels_init() {
-  cudaError_t e = cudaFuncSetAttribute(k_gr_rep_m, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TB_REP_M_SMEM);
-  if (e == cudaSuccess) e = cudaFuncSetAttribute(k_gr_rep_l, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TB_REP_L_SMEM);
+  cudaError_t e = cudaFuncSetAttribute(k_gr_rep_c<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TB_REP_CTA_SMEM(tb_rep_cap(3)));
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(k_gr_rep_c<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TB_REP_CTA_SMEM(tb_rep_cap(4)));
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(k_gr_rep_c<5>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TB_REP_CTA_SMEM(tb_rep_cap(5)));
   return (int)e;
 }
 void tb_launch_c4_a(cudaStream_t st, const KBatch& b, const C4Cfg& cfg, const C4Scratch& s, int sm_count, uint32_t* cursor) {

@@ -66,6 +66,27 @@ TB_HD uint64_t tb_wunit(int64_t rs, int64_t d) { return (uint64_t)((2 * rs) / 3)
 TB_HD uint64_t tb_lunit(int64_t rs, int64_t d) { return (uint64_t)(rs >> 1) + (uint64_t)d; }
 TB_HD uint32_t tb_wunits_of(int64_t len) { return (uint32_t)((2 * len) / 3) + 1u; }  // word slots a text of len bytes needs at most
 
+// Tiers by document size (max of words and line pieces): six in shared memory, capacity doubling from tier to
+// tier, and tier X (global work area) above.  Tiers 0 and 1 are one warp per document; from tier 2 on a CTA of
+// capacity / 8 threads.  A document in flight costs its tier's shared memory and nothing more, so the many
+// short documents run many to an SM: the pass is bound by the latency of its dependent phases, not by issue.
+#define TB_REP_NT 7          // number of tiers, X included
+#define TB_REP_TIER_X 6
+#define TB_REP_CAP0 256u     // capacity of tier t: TB_REP_CAP0 << t
+#define TB_REP_WARP_TIERS 2  // tiers 0, 1: one warp
+TB_HD uint32_t tb_rep_cap(int tier) { return TB_REP_CAP0 << tier; }
+TB_HD int tb_rep_threads(int tier) { return tier < TB_REP_WARP_TIERS ? 32 : (int)(tb_rep_cap(tier) >> 3); }
+TB_HD uint32_t tb_rep_tier(uint32_t big) {
+  uint32_t t = 0;
+  while (t < TB_REP_TIER_X && big > tb_rep_cap((int)t)) t++;
+  return t;
+}
+// GrScratch.counters: list lengths, work cursors, the scan pass's cursor
+#define TB_GR_CNT_LEN(t) (t)
+#define TB_GR_CNT_CUR(t) (8 + (t))
+#define TB_GR_CNT_SCAN 16
+#define TB_GR_COUNTERS 32
+
 // scratch of the repetition filter; word arrays are indexed from tb_wunit(rs[d], d), line arrays from tb_lunit(rs[d], d)
 struct GrScratch {
   uint64_t* wh; uint32_t* wl;               // words: hash, byte length
@@ -74,8 +95,8 @@ struct GrScratch {
   uint64_t* lh; uint32_t* ll; uint8_t* lg;  // line pieces: hash, byte length, "preceded by >= 2 newlines"
   GrDoc* doc;                               // [n]
   uint32_t* work;                           // tier-X work area, TB_REP_K words per word unit + TB_REP_DOC_EXTRA per doc
-  uint32_t* lists;                          // [4][n] document ids per tier (S, M, L, X), filled by the scan pass
-  uint32_t* counters;                       // [16]: list lengths [0..3], work cursors [4..7], scan cursor [8]
+  uint32_t* lists;                          // [TB_REP_NT][n] document ids per tier, filled by the scan pass
+  uint32_t* counters;                       // [TB_GR_COUNTERS]: list lengths, work cursors, scan cursor (TB_GR_CNT_*, tb_rep.cuh)
   int64_t n;
 };
 #define TB_REP_K 8u           // tier-L words per unit: H[2U] woff[U+2] tab[2U+16] cnt[U] list[U] flag[U/32+1]

@@ -179,8 +179,8 @@ int tb_gopher_repetition_noalloc(const uint8_t* utf8_dev, const int64_t* offsets
   g.lh = (uint64_t*)carve(units * 8); g.ll = (uint32_t*)carve(units * 4); g.lg = (uint8_t*)carve(units);
   g.doc = (GrDoc*)carve(n1 * sizeof(GrDoc));
   g.work = (uint32_t*)carve((wunits * TB_REP_K + n1 * TB_REP_DOC_EXTRA) * 4);
-  g.lists = (uint32_t*)carve(4 * n1 * 4);
-  g.counters = (uint32_t*)carve(256);  // [16, 32): the counts of the work order
+  g.lists = (uint32_t*)carve(TB_REP_NT * n1 * 4);
+  g.counters = (uint32_t*)carve(256);  // [TB_GR_COUNTERS, +16): the counts of the work order
   uint32_t* order = (uint32_t*)carve(n1 * 4);
   uint8_t* sizecls = (uint8_t*)carve(n1);
   g.n = n_docs;
@@ -196,11 +196,11 @@ int tb_gopher_repetition_noalloc(const uint8_t* utf8_dev, const int64_t* offsets
   if (cudaMemsetAsync(g.counters, 0, 256, stream) != cudaSuccess) { cudaGetLastError(); return fail(TB_ERR_CUDA, "cudaMemsetAsync failed"); }
   // keep_dev doubles as the kernels' "alive" flag: 1 for every document whose offsets are usable
   k_noalloc_ranges<<<1, 1024, 0, stream>>>(offsets_dev, n_docs, n_bytes, rs, re, keep_dev, failed, stats_dev);
-  tb_launch_order(stream, rs, re, n_docs, order, g.counters + 16, sizecls);
-  KBatch b{utf8_dev, rs, re, keep_dev, failed, n_docs, st->uc, 0, n_bytes, 0u, order, g.counters + 16, sizecls, 0u};
+  tb_launch_order(stream, rs, re, n_docs, order, g.counters + TB_GR_COUNTERS, sizecls);
+  KBatch b{utf8_dev, rs, re, keep_dev, failed, n_docs, st->uc, 0, n_bytes, 0u, order, g.counters + TB_GR_COUNTERS, sizecls, 0u};
   tb_launch_trim(stream, b, ts, te);
   tb_launch_gr_scan(stream, b, ts, te, g, st->sm_count);
-  for (int tier = 0; tier < 4; tier++) tb_launch_gr_rep(stream, b, ts, te, g, cfg, 0, stats_dev, st->sm_count, tier);
+  for (int tier = 0; tier < TB_REP_NT; tier++) tb_launch_gr_rep(stream, b, ts, te, g, cfg, 0, stats_dev, st->sm_count, tier);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return fail(TB_ERR_CUDA, std::string("tb_gopher_repetition_noalloc: launch failed: ") + cudaGetErrorString(e));
   return TB_OK;

@@ -27,11 +27,6 @@
 extern uint64_t tbe_stat_rep_words, tbe_stat_rep_items, tbe_stat_rep_pruned;  // word ends / candidates among them / documents pruned
 #endif
 
-#define TB_REP_S_CAP 512u
-#define TB_REP_M_CAP 2048u
-#define TB_REP_L_CAP 8192u
-#define TB_REP_M_THREADS 256
-#define TB_REP_L_THREADS 1024
 #define TB_REP_X_THREADS 512
 #define TB_REP_PRUNE_FROM 4u  // duplicate n-gram levels from this order on run over the signature candidates only
 #define TB_REP_SIG_MIN 6u     // ... if the shortest n-gram of the first such level has at least this many bytes

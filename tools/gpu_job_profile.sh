@@ -13,7 +13,7 @@ timeout 300 python bench.py --steps 2 --warmup 1 --no-cpu-baseline > gpurun_out/
       python bench.py --steps 2 --warmup 1 --no-cpu-baseline > gpurun_out/r02_ncu_run.log 2>&1
 echo "launch list rc=$?"
 timeout 300 python bench.py --docs 200000 --steps 1 --warmup 1 --no-cpu-baseline > gpurun_out/r02_plain2.json 2> gpurun_out/r02_plain2.err && \
-  timeout 900 ncu --set full --clock-control none --import-source on -k regex:"k_gr_rep_s|k_gr_rep_m|k_gr_rep_l|k_gr_scan|k_gq|k_c4_b" -c 6 \
+  timeout 900 ncu --set full --clock-control none --import-source on -k regex:"k_gr_rep_w|k_gr_rep_c|k_gr_scan|k_gq|k_c4_b|k_c4_a" -c 10 \
       -o gpurun_out/r02_full_top4 python bench.py --docs 200000 --steps 1 --warmup 1 --no-cpu-baseline > gpurun_out/r02_ncu_full.log 2>&1
 echo "full capture rc=$?"
 ls -la gpurun_out | tail -20
