@@ -238,7 +238,7 @@ extern "C" int tbe_run_chain(const tb_step_cfg* steps, size_t n_steps, const uin
       memset(gs.counters, 0, TB_GR_COUNTERS * 4);
       for (int64_t d = 0; d < n; d++) body_trim(b, ascii, ts, te, d);
       build_lut(TB_LUT_GR, 0u);
-      uint32_t* stage = (uint32_t*)G64(5 * TB_GR_STAGE_WORDS / 2 + 1);
+      uint32_t* stage = (uint32_t*)G64(TB_GR_STAGE_U32 / 2 + 1);
       run_warps(n, alive_pred, [&](int64_t d, int lane) { body_gr_scan(b, ascii, lut.data(), stage, ts, te, gs, d, lane); });
       for (int tier = 0; tier < TB_REP_TIER_X; tier++) {
         const uint32_t cap = tb_rep_cap(tier);

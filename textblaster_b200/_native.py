@@ -10,7 +10,8 @@ from . import _abi
 from .error import ConfigValidationError, PipelineError, Unexpected
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libtextblaster_b200.so")
+# TB_LIB_PATH: load another build of the library (A/B measurements of build-time settings, tools/build_variant.sh)
+LIB_PATH = os.environ.get("TB_LIB_PATH") or os.path.join(_HERE, "libtextblaster_b200.so")
 _lib = None
 
 EXPORTS = [

@@ -215,11 +215,13 @@ TB_D_NOINLINE void gr_doc_walk(const KBatch& a, const Classifier& C, const TextR
 // bytes, "a\u00a9a\u00a9..."); a tile with more than this many -- twelve per stretch, under three bytes per word and
 // separator -- hands the document to the walking path instead of tripling every warp's shared memory.
 #define TB_GR_STAGE_WORDS (12 * 32)
+#define TB_GR_STAGE_U32 (5 * TB_GR_STAGE_WORDS + 2 * 32 * 32)
 template <class Feed>
 TB_D bool gr_doc_tiles(const KBatch& a, const LutEntry* lut, uint32_t* stage, const Classifier& C, const TextRange& R,
                        const GrScratch& s, int64_t d, int lane, GrTotals& out, Feed& feed);
 
-// `stage`: 5 * TB_GR_STAGE_WORDS words of per-warp scratch (shared memory, 8-byte aligned)
+// `stage`: TB_GR_STAGE_U32 words of per-warp scratch (shared memory, 8-byte aligned): the staging arrays of a tile's
+// words and the prefix-hash columns of the lanes' stretches
 template <class Feed = NoFeed>
 TB_D void body_gr_scan(const KBatch& a, const uint16_t* s_ascii, const LutEntry* lut, uint32_t* stage, const int64_t* ts,
                        const int64_t* te, const GrScratch& s, int64_t d, int lane, Feed* feed = nullptr) {

@@ -281,6 +281,30 @@ TB_D bool c4b_doc_tiles(const KBatch& a, const LutEntry* lut, const Classifier& 
 // GopherRepetitionFilter, pass 1 (gopher_rep.rs:57-58,80-84,120-124,159): word and line-piece hashes
 // ---------------------------------------------------------------------------------------------
 TB_D HL hl_fold(uint32_t a, uint32_t b, uint32_t len) { HL r; r.a = tb_hfold(a); r.b = tb_hfold(b); r.len = len; return r; }
+// hash of a segment from the prefix hashes at its two ends: pe - ps * B^len mod p (pe, ps lazily reduced, pw <= p) -> <= p
+TB_D uint32_t tb_hseg(uint32_t pe, uint32_t ps, uint32_t pw) {
+  const uint32_t r = tb_hfold(pe) + (TB_P31 - tb_mm(tb_hfold(ps), pw));
+  return (r & TB_P31) + (r >> 31);
+}
+// the low nibbles of the four bytes of x, the first byte (bits 0-7) in the top nibble of the 16-bit result
+TB_D uint32_t tb_nib16(uint32_t x) {
+  x &= 0x0F0F0F0Fu;
+  x = ((x & 0x000000FFu) << 24) | ((x & 0x0000FF00u) << 8) | ((x >> 8) & 0x0000FF00u) | (x >> 24);  // bytes reversed
+  x = (x | (x >> 4)) & 0x00FF00FFu;
+  return (x | (x >> 8)) & 0xFFFFu;
+}
+// suffix signature (tb_sig_push) of the bytes [s, e) of a stretch, from its nibble string (byte j in nibble 31 - j of the
+// 128-bit number n[3] : n[2] : n[1] : n[0]): the nibbles of the last min(16, e - s) bytes, the last byte lowest
+TB_D uint64_t tb_nib_sig(const uint32_t* n, int s, int e) {
+  if (e <= s) return 0ull;
+  const int sh = 4 * (32 - e);  // the string shifted right by this has byte e - 1 in its low nibble
+  const int w = sh >> 5, r = sh & 31;
+  uint32_t x0 = n[0], x1 = n[1], x2 = n[2], x3 = n[3];
+  if (w & 2) { x0 = x2; x1 = x3; x2 = 0u; x3 = 0u; }
+  if (w & 1) { x0 = x1; x1 = x2; x2 = x3; }
+  const uint32_t lo = r ? (x0 >> r) | (x1 << (32 - r)) : x0, hi = r ? (x1 >> r) | (x2 << (32 - r)) : x1;
+  return (((uint64_t)hi << 32) | lo) & tb_sig_mask((uint32_t)(e - s));
+}
 // word fragments also carry their suffix signature (tb_sig_push)
 struct HLS { HL h; uint64_t sig; };
 TB_D HLS hls_cat(HLS x, HLS y, const uint64_t* powtab) { HLS r; r.sig = tb_sig_cat(x.sig, y.sig, y.h.len); r.h = hl_cat(x.h, y.h, powtab); return r; }
@@ -292,6 +316,7 @@ TB_D bool gr_doc_tiles(const KBatch& a, const LutEntry* lut, uint32_t* stage, co
                        const GrScratch& s, int64_t d, int lane, GrTotals& out, Feed& feed) {
   uint64_t* st_s = (uint64_t*)stage;
   uint32_t* st_a = stage + 2 * TB_GR_STAGE_WORDS; uint32_t* st_b = stage + 3 * TB_GR_STAGE_WORDS; uint32_t* st_n = stage + 4 * TB_GR_STAGE_WORDS;
+  uint64_t* pfx = (uint64_t*)(stage + 5 * TB_GR_STAGE_WORDS);  // [32][32]: the prefix hashes of the lanes' stretches, a column per lane
   const uint64_t uw = tb_wunit(R.rs, d), ul = tb_lunit(R.rs, d);
   uint64_t* wh = s.wh + uw; uint32_t* wl = s.wl + uw; uint64_t* wsg = s.ws + uw;
   uint64_t* lh = s.lh + ul; uint32_t* ll = s.ll + ul; uint8_t* lg = s.lg + ul;
@@ -346,46 +371,87 @@ TB_D bool gr_doc_tiles(const KBatch& a, const LutEntry* lut, uint32_t* stage, co
     const uint32_t first_piece = (NLx && (in_nz || fn > 0)) ? 1u : 0u;
     const uint32_t PEin = NLx & ~(NLx << 1) & ~tb_upto(fn);  // a later '\n' that ends a non-empty piece
     uint32_t ltot, lpre = simt_exscan((uint32_t)tb_popc32(PEin) + first_piece, lane, &ltot);
-    // ---- one pass over the 32 bytes: running word hash (restarts at segment starts) and piece hash
-    uint32_t wa = 0, wb = 0, wn = 0, la = 0, lb_ = 0, ln = 0;
-    uint32_t hwa = 0, hwb = 0, hwn = 0, hla = 0, hlb = 0, hln = 0;
-    uint64_t wsig = 0, hwsig = 0;  // suffix signature of the running word fragment / of the one before the first segment start
-    uint32_t widx = wpre + first_word, lidx = NLc + lpre + first_piece;  // widx: slot in the tile's staging arrays
-    // (eight rounds of four bytes; the words and masks rotate so that the round body is one piece of code)
+    // ---- the stretch's 32 prefix hashes P_1 .. P_32 (P_j covers the bytes [0, j); no restarts, no branches) go to the
+    // lane's column of `pfx`; the hash of any segment [s, e) of the stretch is then P_e - P_s * B^(e-s), taken only
+    // where a word or a line piece ends.  Its length is e - s, its signature a piece of the stretch's nibble string.
+    uint64_t* const pcol = pfx + lane;  // P_j at pcol[(j - 1) * 32]
+    uint32_t P32a, P32b;
     {
       uint32_t wq[8];
 #pragma unroll
       for (int k = 0; k < 8; k++) wq[k] = T.w[k];
-      uint32_t Bq = B, WEq = WEin, NLq = NLx;
-      int fbq = fb, fnq = fn;
+      uint32_t pa = 0, pb = 0;
+      uint64_t* pc = pcol;
 #pragma unroll 1
-      for (int k = 0; k < 8; k++) {
+      for (int k = 0; k < 8; k++) {  // (eight rounds of four bytes; the words rotate so that the round body is one piece of code)
         const uint32_t x = wq[0];
 #pragma unroll
         for (int j = 0; j < 4; j++) {
           const uint32_t byte = (x >> (8 * j)) & 0xFFu;
-          {  // segment start: written as selects and predicated stores so that the lanes stay together
-            const bool brk = (Bq >> j) & 1u, emit = (WEq >> j) & 1u, head = brk && j == fbq;  // WEq is a subset of Bq without fb
-            if (emit) { st_a[widx] = wa; st_b[widx] = wb; st_n[widx] = wn; st_s[widx] = wsig; }
-            widx += emit ? 1u : 0u;
-            hwa = head ? wa : hwa; hwb = head ? wb : hwb; hwn = head ? wn : hwn; hwsig = head ? wsig : hwsig;
-            wa = brk ? 0u : wa; wb = brk ? 0u : wb; wn = brk ? 0u : wn; wsig = brk ? 0ull : wsig;
-          }
-          wa = tb_hpush(wa, base1, byte + 1u); wb = tb_hpush(wb, base2, byte + 1u); wn++; wsig = tb_sig_push(wsig, byte);
-          if ((NLq >> j) & 1u) {
-            if (j == fnq) { hla = la; hlb = lb_; hln = ln; }
-            else if (ln) {
-              lh[lidx] = hl_pack(hl_fold(la, lb_, ln)); ll[lidx] = ln; lg[lidx] = (uint8_t)gr_gap2(R, p0 + 4 * k + j - (int64_t)ln);
-              lidx++;
-            }
-            la = 0; lb_ = 0; ln = 0;
-          } else {
-            la = tb_hpush(la, base1, byte + 1u); lb_ = tb_hpush(lb_, base2, byte + 1u); ln++;
-          }
+          pa = tb_hpush(pa, base1, byte + 1u); pb = tb_hpush(pb, base2, byte + 1u);
+          pc[j * 32] = ((uint64_t)pa << 32) | pb;
         }
+        pc += 4 * 32;
 #pragma unroll
         for (int q = 0; q < 7; q++) wq[q] = wq[q + 1];
-        Bq >>= 4; WEq >>= 4; NLq >>= 4; fbq -= 4; fnq -= 4;
+      }
+      P32a = pa; P32b = pb;
+    }
+    uint32_t nib[4];  // the low nibbles of the 32 bytes, byte 0 in the top nibble of nib[3], byte 31 in the low nibble of nib[0]
+#pragma unroll
+    for (int k = 0; k < 4; k++) nib[3 - k] = (tb_nib16(T.w[2 * k]) << 16) | tb_nib16(T.w[2 * k + 1]);
+    // (a lane reads back its own column only: no barrier)
+    uint32_t wa, wb, wn, la, lb_, ln;
+    uint32_t hwa = 0, hwb = 0, hwn = 0, hla = 0, hlb = 0, hln = 0;
+    uint64_t wsig, hwsig = 0;  // suffix signature of the fragment after the last segment start / of the one before the first
+    {
+      // ---- words: the fragment before the first segment start, the words that end inside the stretch, the open tail
+      if (B) {
+        if (fb) { const uint64_t pe = pcol[(fb - 1) * 32]; hwa = (uint32_t)(pe >> 32); hwb = (uint32_t)pe; }
+        hwn = (uint32_t)fb; hwsig = tb_nib_sig(nib, 0, fb);
+        uint32_t widx = wpre + first_word;  // slot in the tile's staging arrays
+        uint32_t we = WEin;
+#pragma unroll 1
+        while (we) {
+          const int e = tb_ctz32(we);
+          we &= we - 1u;
+          const int sp = 31 - tb_clz32(B & tb_below(e));  // the segment start before e (e > fb: there is one)
+          const uint64_t pe = pcol[(e - 1) * 32], ps = sp ? pcol[(sp - 1) * 32] : 0ull, pw = TB_LDG(powtab + (e - sp));
+          st_a[widx] = tb_hseg((uint32_t)(pe >> 32), (uint32_t)(ps >> 32), (uint32_t)(pw >> 32));
+          st_b[widx] = tb_hseg((uint32_t)pe, (uint32_t)ps, (uint32_t)pw);
+          st_n[widx] = (uint32_t)(e - sp); st_s[widx] = tb_nib_sig(nib, sp, e);
+          widx++;
+        }
+        const uint64_t ps = lbk ? pcol[(lbk - 1) * 32] : 0ull, pw = TB_LDG(powtab + (32 - lbk));
+        wa = tb_hseg(P32a, (uint32_t)(ps >> 32), (uint32_t)(pw >> 32)); wb = tb_hseg(P32b, (uint32_t)ps, (uint32_t)pw);
+        wn = (uint32_t)(32 - lbk); wsig = tb_nib_sig(nib, lbk, 32);
+      } else {
+        wa = P32a; wb = P32b; wn = 32u; wsig = tb_nib_sig(nib, 0, 32);
+      }
+      // ---- line pieces ('\n' bytes and the bytes outside the text belong to no piece)
+      if (NLx) {
+        if (fn) { const uint64_t pe = pcol[(fn - 1) * 32]; hla = (uint32_t)(pe >> 32); hlb = (uint32_t)pe; }
+        hln = (uint32_t)fn;
+        uint32_t lidx = NLc + lpre + first_piece;
+        uint32_t pe_ = PEin;
+#pragma unroll 1
+        while (pe_) {
+          const int e = tb_ctz32(pe_);
+          pe_ &= pe_ - 1u;
+          const int sp = 32 - tb_clz32(NLx & tb_below(e));  // the byte after the '\n' before e (e > fn: there is one)
+          const uint64_t pe = pcol[(e - 1) * 32], ps = pcol[(sp - 1) * 32], pw = TB_LDG(powtab + (e - sp));
+          HL piece; piece.a = tb_hseg((uint32_t)(pe >> 32), (uint32_t)(ps >> 32), (uint32_t)(pw >> 32));
+          piece.b = tb_hseg((uint32_t)pe, (uint32_t)ps, (uint32_t)pw); piece.len = (uint32_t)(e - sp);
+          lh[lidx] = hl_pack(piece); ll[lidx] = piece.len; lg[lidx] = (uint8_t)gr_gap2(R, p0 + sp);
+          lidx++;
+        }
+        if (ln_ < 31) {
+          const uint64_t ps = pcol[ln_ * 32], pw = TB_LDG(powtab + (31 - ln_));
+          la = tb_hseg(P32a, (uint32_t)(ps >> 32), (uint32_t)(pw >> 32)); lb_ = tb_hseg(P32b, (uint32_t)ps, (uint32_t)pw);
+        } else { la = 0; lb_ = 0; }
+        ln = (uint32_t)(31 - ln_);
+      } else {
+        la = P32a; lb_ = P32b; ln = 32u;
       }
     }
     // ---- words: hash of the fragment open at the start of the stretch

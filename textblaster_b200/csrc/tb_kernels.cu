@@ -26,6 +26,25 @@ __device__ __forceinline__ void load_lut(LutEntry* s_lut, const UcTables& uc, in
   }
   __syncthreads();
 }
+// CTAs (of one warp) per SM each persistent text pass is built and launched for: the register budget follows from it
+#ifndef TB_RES_GQ
+#define TB_RES_GQ 12
+#endif
+#ifndef TB_RES_GR_SCAN
+#define TB_RES_GR_SCAN 16
+#endif
+#ifndef TB_RES_C4_A
+#define TB_RES_C4_A 24
+#endif
+#ifndef TB_RES_C4_B
+#define TB_RES_C4_B 20
+#endif
+#ifndef TB_RES_C4_C
+#define TB_RES_C4_C 32
+#endif
+#ifndef TB_RES_C4_D
+#define TB_RES_C4_D 24
+#endif
 // persistent one-warp CTAs pull work items from a cursor (zeroed by the host before the launch): first the
 // listed long documents, then all documents in index order (listed ones are skipped there).
 // Returns -1 when the work is exhausted, -2 for an item to skip.
@@ -78,7 +97,7 @@ __global__ void __launch_bounds__(TB_BLOCK) k_validate_utf8(const uint8_t* t, co
 }
 // FEED: the tiles of long documents arrive by bulk copy (tb_feed.cuh); the plain build carries none of that code
 template <bool FEED>
-__global__ void __launch_bounds__(TB_BLOCK, 12) k_gq(KBatch a, SwTable sw, GqCfg cfg, int step, tb_gq_stats* out, uint32_t* cursor) {
+__global__ void __launch_bounds__(TB_BLOCK, TB_RES_GQ) k_gq(KBatch a, SwTable sw, GqCfg cfg, int step, tb_gq_stats* out, uint32_t* cursor) {
   __shared__ uint16_t s_ascii[192];
   __shared__ LutEntry s_lut[256];
   load_ascii(s_ascii, a.uc);
@@ -107,12 +126,12 @@ __global__ void k_trim(KBatch a, int64_t* ts, int64_t* te) {
   if (d < a.n) body_trim(a, s_ascii, ts, te, d);
 }
 template <bool FEED>
-__global__ void __launch_bounds__(TB_BLOCK, 16) k_gr_scan(KBatch a, const int64_t* ts, const int64_t* te, GrScratch s) {
+__global__ void __launch_bounds__(TB_BLOCK, TB_RES_GR_SCAN) k_gr_scan(KBatch a, const int64_t* ts, const int64_t* te, GrScratch s) {
   __shared__ uint16_t s_ascii[192];
   __shared__ LutEntry s_lut[256];
   load_ascii(s_ascii, a.uc);
   load_lut(s_lut, a.uc, TB_LUT_GR, 0u);
-  __shared__ __align__(8) uint32_t s_stage[5 * TB_GR_STAGE_WORDS];
+  __shared__ __align__(8) uint32_t s_stage[TB_GR_STAGE_U32];
   __shared__ __align__(FEED ? TB_TILE : 16) uint8_t s_feed[FEED ? TB_FEED_SMEM : 16];  // the ring is aligned on the tile size (tile_classify relies on it)
   typename FeedOf<FEED>::type feed;
   feed_init(feed, s_feed, threadIdx.x & 31);
@@ -175,7 +194,7 @@ __global__ void __launch_bounds__(TB_REP_X_THREADS) k_gr_rep_x(KBatch a, const i
   }
 }
 template <bool FEED>
-__global__ void __launch_bounds__(TB_BLOCK, 24) k_c4_a(KBatch a, C4Cfg cfg, C4Scratch s, uint32_t* cursor) {
+__global__ void __launch_bounds__(TB_BLOCK, TB_RES_C4_A) k_c4_a(KBatch a, C4Cfg cfg, C4Scratch s, uint32_t* cursor) {
   __shared__ uint16_t s_ascii[192];
   __shared__ LutEntry s_lut[256];
   __shared__ __align__(16) uint8_t s_stage[TB_STAGE_BYTES];
@@ -216,7 +235,7 @@ __global__ void __launch_bounds__(TB_BLOCK, 16) k_c4_sent(KBatch a, const int64_
   }
 }
 template <bool FEED>
-__global__ void __launch_bounds__(TB_BLOCK, 20) k_c4_b(KBatch a, C4Cfg cfg, C4Scratch s, uint32_t* cursor) {
+__global__ void __launch_bounds__(TB_BLOCK, TB_RES_C4_B) k_c4_b(KBatch a, C4Cfg cfg, C4Scratch s, uint32_t* cursor) {
   __shared__ uint16_t s_ascii[192];
   __shared__ LutEntry s_lut[256];
   load_ascii(s_ascii, a.uc);
@@ -231,7 +250,7 @@ __global__ void __launch_bounds__(TB_BLOCK, 20) k_c4_b(KBatch a, C4Cfg cfg, C4Sc
     if (a.alive[d] && !s.docflags[d] && s.nlines[d] != 0) body_c4_b(a, s_ascii, s_lut, cfg, s, d, threadIdx.x & 31, &feed);
   }
 }
-__global__ void __launch_bounds__(TB_BLOCK, 32) k_c4_c(KBatch a, C4Cfg cfg, C4Scratch s, uint32_t* cursor) {
+__global__ void __launch_bounds__(TB_BLOCK, TB_RES_C4_C) k_c4_c(KBatch a, C4Cfg cfg, C4Scratch s, uint32_t* cursor) {
   __shared__ __align__(16) uint8_t s_stage[TB_STAGE_BYTES];
   for (;;) {
     const int64_t d = next_doc(cursor, a);
@@ -240,7 +259,7 @@ __global__ void __launch_bounds__(TB_BLOCK, 32) k_c4_c(KBatch a, C4Cfg cfg, C4Sc
     body_c4_c(a, s_stage, cfg, s, d, threadIdx.x & 31);
   }
 }
-__global__ void __launch_bounds__(TB_BLOCK, 24) k_c4_d(KBatch a, C4Cfg cfg, C4Scratch s, int step, tb_c4_stats* out,
+__global__ void __launch_bounds__(TB_BLOCK, TB_RES_C4_D) k_c4_d(KBatch a, C4Cfg cfg, C4Scratch s, int step, tb_c4_stats* out,
                                                        uint8_t* rewritten, int64_t* rs_out, int64_t* re_out, uint32_t* cursor) {
   __shared__ uint16_t s_ascii[192];
   load_ascii(s_ascii, a.uc);
@@ -343,8 +362,8 @@ void tb_launch_validate_utf8(cudaStream_t st, const uint8_t* text, const int64_t
 void tb_launch_gq(cudaStream_t st, const KBatch& b, const SwTable& sw, const GqCfg& cfg, int step, tb_gq_stats* out,
                   int sm_count, uint32_t* cursor) {
   if (b.n) {
-    if (b.feed_min_tiles) k_gq<true><<<persistent_grid(b.n, sm_count, 12), TB_BLOCK, 0, st>>>(b, sw, cfg, step, out, cursor);
-    else k_gq<false><<<persistent_grid(b.n, sm_count, 12), TB_BLOCK, 0, st>>>(b, sw, cfg, step, out, cursor);
+    if (b.feed_min_tiles) k_gq<true><<<persistent_grid(b.n, sm_count, TB_RES_GQ), TB_BLOCK, 0, st>>>(b, sw, cfg, step, out, cursor);
+    else k_gq<false><<<persistent_grid(b.n, sm_count, TB_RES_GQ), TB_BLOCK, 0, st>>>(b, sw, cfg, step, out, cursor);
   }
 }
 void tb_launch_trim(cudaStream_t st, const KBatch& b, int64_t* ts, int64_t* te) {
@@ -352,8 +371,8 @@ void tb_launch_trim(cudaStream_t st, const KBatch& b, int64_t* ts, int64_t* te) 
 }
 void tb_launch_gr_scan(cudaStream_t st, const KBatch& b, const int64_t* ts, const int64_t* te, const GrScratch& s, int sm_count) {
   if (b.n) {
-    if (b.feed_min_tiles) k_gr_scan<true><<<persistent_grid(b.n, sm_count, 16), TB_BLOCK, 0, st>>>(b, ts, te, s);
-    else k_gr_scan<false><<<persistent_grid(b.n, sm_count, 16), TB_BLOCK, 0, st>>>(b, ts, te, s);
+    if (b.feed_min_tiles) k_gr_scan<true><<<persistent_grid(b.n, sm_count, TB_RES_GR_SCAN), TB_BLOCK, 0, st>>>(b, ts, te, s);
+    else k_gr_scan<false><<<persistent_grid(b.n, sm_count, TB_RES_GR_SCAN), TB_BLOCK, 0, st>>>(b, ts, te, s);
   }
 }
 void tb_launch_gr_rep(cudaStream_t st, const KBatch& b, const int64_t* ts, const int64_t* te, const GrScratch& s,
@@ -383,8 +402,8 @@ int tb_kernels_init() {
 }
 void tb_launch_c4_a(cudaStream_t st, const KBatch& b, const C4Cfg& cfg, const C4Scratch& s, int sm_count, uint32_t* cursor) {
   if (b.n) {
-    if (b.feed_min_tiles) k_c4_a<true><<<persistent_grid(b.n, sm_count, 24), TB_BLOCK, 0, st>>>(b, cfg, s, cursor);
-    else k_c4_a<false><<<persistent_grid(b.n, sm_count, 24), TB_BLOCK, 0, st>>>(b, cfg, s, cursor);
+    if (b.feed_min_tiles) k_c4_a<true><<<persistent_grid(b.n, sm_count, TB_RES_C4_A), TB_BLOCK, 0, st>>>(b, cfg, s, cursor);
+    else k_c4_a<false><<<persistent_grid(b.n, sm_count, TB_RES_C4_A), TB_BLOCK, 0, st>>>(b, cfg, s, cursor);
   }
 }
 void tb_launch_entities(cudaStream_t st, const KBatch& b, const EntEntry* tab, uint32_t ntab, uint32_t* amp, uint32_t* drop,
@@ -397,17 +416,17 @@ void tb_launch_c4_sent(cudaStream_t st, const KBatch& b, const int64_t* ts, cons
 }
 void tb_launch_c4_b(cudaStream_t st, const KBatch& b, const C4Cfg& cfg, const C4Scratch& s, int sm_count, uint32_t* cursor) {
   if (b.n) {
-    if (b.feed_min_tiles) k_c4_b<true><<<persistent_grid(b.n, sm_count, 20), TB_BLOCK, 0, st>>>(b, cfg, s, cursor);
-    else k_c4_b<false><<<persistent_grid(b.n, sm_count, 20), TB_BLOCK, 0, st>>>(b, cfg, s, cursor);
+    if (b.feed_min_tiles) k_c4_b<true><<<persistent_grid(b.n, sm_count, TB_RES_C4_B), TB_BLOCK, 0, st>>>(b, cfg, s, cursor);
+    else k_c4_b<false><<<persistent_grid(b.n, sm_count, TB_RES_C4_B), TB_BLOCK, 0, st>>>(b, cfg, s, cursor);
   }
 }
 void tb_launch_c4_c(cudaStream_t st, const KBatch& b, const C4Cfg& cfg, const C4Scratch& s, int sm_count, uint32_t* cursor) {
-  if (b.n) k_c4_c<<<persistent_grid(b.n, sm_count, 32), TB_BLOCK, 0, st>>>(b, cfg, s, cursor);
+  if (b.n) k_c4_c<<<persistent_grid(b.n, sm_count, TB_RES_C4_C), TB_BLOCK, 0, st>>>(b, cfg, s, cursor);
 }
 void tb_launch_c4_d(cudaStream_t st, const KBatch& b, const C4Cfg& cfg, const C4Scratch& s, int step, tb_c4_stats* out,
                     uint8_t* rewritten, int64_t* rs_out, int64_t* re_out, int sm_count, uint32_t* cursor) {
   // the new ranges go to rs_out / re_out (the chain's rs / re), only for documents that were rewritten
-  if (b.n) k_c4_d<<<persistent_grid(b.n, sm_count, 24), TB_BLOCK, 0, st>>>(b, cfg, s, step, out, rewritten, rs_out, re_out, cursor);
+  if (b.n) k_c4_d<<<persistent_grid(b.n, sm_count, TB_RES_C4_D), TB_BLOCK, 0, st>>>(b, cfg, s, step, out, rewritten, rs_out, re_out, cursor);
 }
 void tb_launch_c4_runs(cudaStream_t st, int64_t n, const int64_t* rs0, const int64_t* re0, const uint8_t* rewritten, const uint32_t* kf,
                        uint32_t mis, const int64_t* frs, const int64_t* fre, int64_t* nruns, const int64_t* run_off, void* runs, int64_t cap, int emit) {
