@@ -461,13 +461,18 @@ void gather_range(const GatherSrc& g, int64_t d0, int64_t d1, int64_t last_end, 
         return;
       }
     };
+    static const bool plain = [] { const char* e = getenv("TB_GATHER_COPY"); return e && !strcmp(e, "plain"); }();  // (measurement knob: memcpy straight into the destination)
     if (dst) for (int i = 0; i < 6; i++) prefetch_next();
     for (int64_t d = d0 + n * t / T; d < d_end; d++) {
       if (g.select && !g.select[d]) continue;
       const uint8_t* src = g.utf8 + off_at(g.offsets, g.is64, d);
       for (int64_t r = g.ro[d], re = ro_end(d); r < re; r++) {
         const size_t len = (size_t)g.runs[r].end - g.runs[r].begin;
-        if (dst) { prefetch_next(); w.write(src + g.runs[r].begin, len); }
+        if (dst) {
+          prefetch_next();
+          if (plain) memcpy(dst + o, src + g.runs[r].begin, len);
+          else w.write(src + g.runs[r].begin, len);
+        }
         o += (int64_t)len;
       }
       dst_off[++k] = o;
