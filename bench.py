@@ -152,10 +152,11 @@ def measured_peaks():
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
-def ncu_traffic(kernel, alg_bytes_per_launch):
+def ncu_traffic(kernel, chunk_bytes_per_launch):
     """dram bytes per launch of the dominant kernel from the committed ncu capture, if any.  The capture is of ONE
-    launch (whose algorithmic bytes the file records); launches differ in size, so the figure is scaled to the
-    average launch that `achieved` is quoted on."""
+    launch (the algorithmic bytes of the chunk it worked on are in the file); launches differ in size, so the figure is
+    scaled by chunk size to the average launch that `achieved` is quoted on (a tier kernel of the repetition pass works
+    on its share of every chunk: the same ratio applies)."""
     p = os.path.join(ROOT, "profiles", "roofline_traffic.json")
     if os.path.exists(p):
         try:
@@ -163,7 +164,7 @@ def ncu_traffic(kernel, alg_bytes_per_launch):
             t, cap = d.get(kernel), d.get("_captured_launch_algorithmic_bytes")
             if t is None:
                 return None
-            return t * alg_bytes_per_launch / cap if cap else t
+            return t * chunk_bytes_per_launch / cap if cap else t
         except Exception:
             return None
     return None
@@ -907,7 +908,7 @@ def main():
                     "host_gathered_bytes_per_step": last_keep.get("kept_bytes") if runs_mode else None},
             "gpu_launches": launches,
             "roofline": {"bound": "hbm", "kernel": dom_name, "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak if peak else None, "traffic": ncu_traffic(dom_name, alg_bytes_launch), "peak_source": peak_src,
+                         "frac": achieved / peak if peak else None, "traffic": ncu_traffic(dom_name, alg_bytes_step / launches_per_step), "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": alg_bytes_launch, "avg_launch_ms": avg_ms, "units": units_note,
                          "share_of_gpu_time": dom_ms / max(sum(v[0] for v in ktimes.values()), 1e-9)},
             # the whole chain against HBM (algorithmic bytes / sum of kernel time) and the end-to-end

@@ -12,7 +12,10 @@ from textblaster_b200 import _abi
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _SRC = os.path.join(_HERE, "host_emul", "tb_emul.cpp")
-_SO = os.path.join(_HERE, "host_emul", "libtb_emul.so")
+# TB_EMUL_SANITIZE=1: an AddressSanitizer + UndefinedBehaviorSanitizer build of the same source (tests/test_emul_sanitized.py
+# runs it in a child process with the sanitizer runtimes preloaded)
+_SANITIZE = os.environ.get("TB_EMUL_SANITIZE") == "1"
+_SO = os.path.join(_HERE, "host_emul", "libtb_emul_asan.so" if _SANITIZE else "libtb_emul.so")
 _CSRC = os.path.join(_HERE, "..", "textblaster_b200", "csrc")
 _lib = None
 
@@ -22,7 +25,8 @@ def lib():
     if _lib is None:
         deps = [_SRC] + [os.path.join(_CSRC, f) for f in os.listdir(_CSRC) if f.endswith((".cuh", ".h", ".inc"))]
         if not os.path.exists(_SO) or any(os.path.getmtime(d) > os.path.getmtime(_SO) for d in deps):
-            subprocess.run(["g++", "-std=c++20", "-O2", "-fPIC", "-shared", "-pthread", "-x", "c++", _SRC, "-o", _SO], check=True)
+            flags = ["-O1", "-g", "-fsanitize=address,undefined", "-fno-sanitize-recover=undefined", "-fno-omit-frame-pointer"] if _SANITIZE else ["-O2"]
+            subprocess.run(["g++", "-std=c++20"] + flags + ["-fPIC", "-shared", "-pthread", "-x", "c++", _SRC, "-o", _SO], check=True)
         L = C.CDLL(_SO)
         L.tbe_run_chain.restype = C.c_int
         L.tbe_run_chain.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p,

@@ -8,6 +8,10 @@ import csv,sys,json
 rows=list(csv.reader(sys.stdin)); hdr=rows[0]; units=rows[1]; out={}
 for r in rows[2:]:
     name=r[hdr.index('Kernel Name')].split('(')[0].split('::')[-1]
+    # the names the library's event timers (and bench.py) use for template instantiations
+    for k,v in {'k_gr_rep_w<0':'k_gr_rep_w256','k_gr_rep_w<1':'k_gr_rep_w512','k_gr_rep_c<2>':'k_gr_rep_c1k','k_gr_rep_c<3>':'k_gr_rep_c2k','k_gr_rep_c<4>':'k_gr_rep_c4k','k_gr_rep_c<5>':'k_gr_rep_c8k'}.items():
+        if name.startswith(k): name=v
+    name=name.split('<')[0]
     def val(m):
         i=hdr.index(m); v=float(r[i].replace(',','')); return v*{'byte':1,'Kbyte':1e3,'Mbyte':1e6,'Gbyte':1e9}[units[i]]
     out[name]=val('dram__bytes_read.sum')+val('dram__bytes_write.sum')
@@ -27,10 +31,17 @@ import csv, collections, json
 rows=list(csv.reader(open('gpurun_out/r02_launches.csv')))
 hi=[i for i,r in enumerate(rows) if r and r[0]=="ID"][0]
 hdr=rows[hi]; kn=hdr.index("Kernel Name"); mv=hdr.index("Metric Value"); mu=hdr.index("Metric Unit")
+# ncu prints template instantiations (k_gq<0>, k_gr_rep_w<0, 32>, k_gr_rep_c<3>); the library's event timers use the
+# names below
+TIER={"k_gr_rep_w<0":"k_gr_rep_w256","k_gr_rep_w<1":"k_gr_rep_w512","k_gr_rep_c<2>":"k_gr_rep_c1k","k_gr_rep_c<3>":"k_gr_rep_c2k","k_gr_rep_c<4>":"k_gr_rep_c4k","k_gr_rep_c<5>":"k_gr_rep_c8k"}
+def canon(n):
+    for k,v in TIER.items():
+        if n.startswith(k): return v
+    return n.split("<")[0]
 agg=collections.defaultdict(lambda:[0,0.0])
 for r in rows[hi+1:]:
     if len(r)<=mv: continue
-    name=r[kn].split("(")[0].split("::")[-1]; v=float(r[mv].replace(",","")); u=r[mu]
+    name=canon(r[kn].split("(")[0].split("::")[-1]); v=float(r[mv].replace(",","")); u=r[mu]
     agg[name][0]+=1; agg[name][1]+= v*1e3 if u=="us" else v*1e6 if u=="ms" else v
 tot=sum(v[1] for v in agg.values())
 live=json.load(open('gpurun_out/r02_bench_n1.json'))["kernels_ms_per_step"]; lt=sum(live.values())
