@@ -44,6 +44,13 @@ def rep_stats(reset=True):
     return w.value, i.value, p.value
 
 
+def rep_task_stats(reset=True):
+    """(levels worked off by one warp of a CTA tier in registers, ... with a table of its own) since the last reset"""
+    a, b = C.c_uint64(), C.c_uint64()
+    lib().tbe_rep_task_stats(C.byref(a), C.byref(b), 1 if reset else 0)
+    return a.value, b.value
+
+
 def chunk_targets(total_bytes, chunk_bytes, device_input=False):
     """tb_chunk_targets (csrc/tb_hostutil.h): the sizes the host executor cuts a batch into"""
     out = np.zeros(4096, np.int64)

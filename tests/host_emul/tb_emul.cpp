@@ -23,9 +23,14 @@ thread_local int simt_lane = 0;
 thread_local SimtBlock* simt_block = nullptr;
 uint64_t tbe_stat_tiles = 0, tbe_stat_walk = 0;
 uint64_t tbe_stat_rep_words = 0, tbe_stat_rep_items = 0, tbe_stat_rep_pruned = 0;
+uint64_t tbe_stat_rep_task_small = 0, tbe_stat_rep_task_table = 0;
 extern "C" void tbe_rep_stats(uint64_t* words, uint64_t* items, uint64_t* pruned, int reset) {
   *words = tbe_stat_rep_words; *items = tbe_stat_rep_items; *pruned = tbe_stat_rep_pruned;
   if (reset) tbe_stat_rep_words = tbe_stat_rep_items = tbe_stat_rep_pruned = 0;
+}
+extern "C" void tbe_rep_task_stats(uint64_t* small, uint64_t* table, int reset) {
+  *small = tbe_stat_rep_task_small; *table = tbe_stat_rep_task_table;
+  if (reset) tbe_stat_rep_task_small = tbe_stat_rep_task_table = 0;
 }
 extern "C" void tbe_stats(uint64_t* tiles, uint64_t* walk) { *tiles = tbe_stat_tiles; *walk = tbe_stat_walk; }
 // the chunk plan of the host executor (tb_hostutil.h): sizes into out[0 .. cap), returns their number
@@ -250,7 +255,8 @@ extern "C" int tbe_run_chain(const tb_step_cfg* steps, size_t n_steps, const uin
           run_blocks(gs.lists + (int64_t)tier * n, gs.counters[TB_GR_CNT_LEN(tier)], tb_rep_threads(tier),
                      [&](int64_t d, int tid) { body_gr_rep_cta(b, smem, cap, ts, te, gs, g, (int)s, (tb_gr_stats*)stats, d, tid); });
       }
-      run_blocks(gs.lists + (int64_t)TB_REP_TIER_X * n, gs.counters[TB_GR_CNT_LEN(TB_REP_TIER_X)], TB_REP_X_THREADS, [&](int64_t d, int tid) { body_gr_rep_x(b, nullptr, ts, te, gs, g, (int)s, (tb_gr_stats*)stats, d, tid); });
+      uint64_t* red_x = (uint64_t*)G64(64 + 40);
+      run_blocks(gs.lists + (int64_t)TB_REP_TIER_X * n, gs.counters[TB_GR_CNT_LEN(TB_REP_TIER_X)], TB_REP_X_THREADS, [&](int64_t d, int tid) { body_gr_rep_x(b, red_x, ts, te, gs, g, (int)s, (tb_gr_stats*)stats, d, tid); });
     } else if (sc.type == TB_STEP_FINEWEB_QUALITY) {
       const tb_fw_params& q = sc.u.fw;
       FwCfg f{};

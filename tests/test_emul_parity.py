@@ -204,9 +204,30 @@ def signature_pruning_docs():
     return docs
 
 
+def level_task_docs():
+    """Documents of the CTA tiers (more than 512 words) whose pruned duplicate n-gram levels keep few word ends in play:
+    there a warp works a whole level off alone (tb_rep.cuh) -- up to 32 ends in registers, up to 256 with a table in its
+    share of the CTA's arrays, more than that the CTA does level by level.  Repeated blocks of several sizes at each tier."""
+    rng = random.Random(77)
+    docs = []
+    for nw in (700, 1500, 3000, 6000, 12000):
+        for block, reps in ((8, 2), (14, 3), (40, 2), (60, 3), (120, 2), (300, 2)):
+            body = ["".join(rng.choice("klmnopqrstuvwxyz") for _ in range(rng.randint(2, 9))) for _ in range(nw)]  # (hardly any chance repeats)
+            rep = body[10:10 + block]
+            for r in range(reps):
+                at = rng.randrange(len(body))
+                body[at:at] = rep
+            docs.append(" ".join(body))
+    return docs
+
+
 def test_signature_pruning():
     for name in ("gr_open", "gr_shipped"):
         _check(name, signature_pruning_docs())
+    _emul.rep_task_stats()
+    _check("gr_shipped", level_task_docs())
+    small, table = _emul.rep_task_stats()
+    assert small > 20 and table > 20, (small, table)
     # and it does prune: on C4-shaped prose only a few percent of the word ends stay in play
     from textblaster_b200 import synth
     utf8, off = synth.generate(300, seed=9)

@@ -14,7 +14,7 @@ import multilingual
 import oracle
 from parity_cases import CHAINS, GQ_OPEN, GR_OPEN, step_types
 from parity_util import compare, executed
-from test_emul_parity import (GOLDEN_DOCS, SENTENCE_LINE_DOCS, boundary_sentence_docs, entity_docs, fineweb_docs,
+from test_emul_parity import (level_task_docs, GOLDEN_DOCS, SENTENCE_LINE_DOCS, boundary_sentence_docs, entity_docs, fineweb_docs,
                               signature_pruning_docs, split_ambiguity_docs)
 from test_oracle_golden import C4_LINE_CASES, c4_default
 from textblaster_b200 import _abi, synth
@@ -535,7 +535,7 @@ def repetition_pass_docs():
     base = fuzzgen.english_doc(rng, 1500)
     docs = [fuzzgen.english_doc(rng, 2500), fuzzgen.english_doc(rng, 12000), fuzzgen.english_doc(rng, 36000), fuzzgen.english_doc(rng, 90000),
             (base + "\n") * 3, (base + "\n") * 9, (base + "\n") * 30, "a b c d e f g " * 700, "x y " * 5000]
-    return docs + signature_pruning_docs() + split_ambiguity_docs() + fuzzgen.dense_word_docs()
+    return docs + signature_pruning_docs() + split_ambiguity_docs() + fuzzgen.dense_word_docs() + level_task_docs()
 
 
 @pytest.mark.parametrize("name", ["gr_open", "gr_shipped", "shipped_order"])

@@ -251,7 +251,7 @@ TB_D void body_gr_scan(const KBatch& a, const uint16_t* s_ascii, const LutEntry*
 // shared-memory layout of one document's working arrays for capacity CAP (8-byte aligned pieces first)
 #define TB_REP_SMEM(CAP) ((CAP) * 8 + ((CAP) + 2) * 4 + 2 * (CAP) * 4 + ((CAP) / 32 + 2) * 4 + (CAP) * 2 + (CAP) * 2)
 #define TB_REP_WARP_SMEM(CAP) TB_REP_SMEM(CAP)              // a warp tier
-#define TB_REP_CTA_SMEM(CAP) (TB_REP_SMEM(CAP) + 64 * 8)    // a CTA tier: + the scratch of the CTA's collectives
+#define TB_REP_CTA_SMEM(CAP) (TB_REP_SMEM(CAP) + (64 + 40) * 8)    // a CTA tier: + the scratch of the CTA's collectives (64 words) and the per-level results of the warps' tasks
 struct RepCarve { RepArrays A; uint32_t* tab; uint16_t* cnt; uint16_t* list; uint8_t* end; };
 TB_D RepCarve rep_carve(uint8_t* smem, uint32_t cap) {
   RepCarve c;
@@ -279,7 +279,7 @@ TB_D void body_gr_rep_cta(const KBatch& a, uint8_t* smem, uint32_t cap, const in
   BlockGroup g{tid, (uint64_t*)(((uintptr_t)c.end + 7) & ~(uintptr_t)7)};
   rep_body<BlockGroup, uint16_t>(g, a, ts, te, s, cfg, step, out, d, c.A, c.tab, c.cnt, c.list);
 }
-// tier X: one CTA, working arrays in the document's region of the global work area; `red` = 64 u64 of shared scratch
+// tier X: one CTA, working arrays in the document's region of the global work area; `red` = 64 + 40 u64 of shared scratch
 TB_D void body_gr_rep_x(const KBatch& a, uint64_t* red, const int64_t* ts, const int64_t* te, const GrScratch& s,
                         const GrCfg& cfg, int step, tb_gr_stats* out, int64_t d, int tid) {
   const int64_t rs = ts[d], re = te[d];

@@ -141,10 +141,9 @@ TB_HD uint32_t tb_simple_lower(const UcTables& u, uint32_t cp) {
 #define TB_B1_DEFAULT 0x1F0B4A27u
 #define TB_B2_DEFAULT 0x0C4D3A11u
 TB_HD uint32_t tb_mm(uint32_t a, uint32_t b) {  // a, b <= p  ->  result <= p (p itself stands for 0)
-  uint64_t x = (uint64_t)a * b;
-  x = (x & TB_P31) + (x >> 31);
-  x = (x & TB_P31) + (x >> 31);
-  return (uint32_t)x;
+  const uint64_t x = (uint64_t)a * b;  // < 2^62: both halves of the first fold are below 2^31, their sum fits 32 bits
+  const uint32_t s = ((uint32_t)x & TB_P31) + (uint32_t)(x >> 31);
+  return (s & TB_P31) + (s >> 31);
 }
 TB_HD uint32_t tb_am(uint32_t a, uint32_t b) {  // a, b <= p -> <= p
   uint32_t x = a + b;
@@ -167,9 +166,8 @@ TB_HD Hash2 tb_hcat(Hash2 x, Hash2 y, uint64_t pw) {
   r.b = tb_am(tb_mm(x.b, (uint32_t)pw), y.b);
   return r;
 }
-TB_HD uint64_t tb_pow_pack(const uint64_t* powtab, uint64_t len) {
-  if (len < TB_POWTAB) return TB_LDG(powtab + len);
-  // square-and-multiply for the rare long element
+// (B1^len, B2^len) packed, by square-and-multiply: the rare element longer than the table (out of line)
+TB_HD_NOINLINE uint64_t tb_pow_long(const uint64_t* powtab, uint64_t len) {
   const uint64_t pw1 = TB_LDG(powtab + 1);
   uint32_t ra = 1, rb = 1, ba = (uint32_t)(pw1 >> 32), bb = (uint32_t)pw1;
   uint64_t e = len;
@@ -180,6 +178,7 @@ TB_HD uint64_t tb_pow_pack(const uint64_t* powtab, uint64_t len) {
   }
   return ((uint64_t)ra << 32) | rb;
 }
+TB_HD uint64_t tb_pow_pack(const uint64_t* powtab, uint64_t len) { return len < TB_POWTAB ? TB_LDG(powtab + len) : tb_pow_long(powtab, len); }
 // ---- suffix signature of a byte string: its last 16 bytes, four bits of each, the last byte in the low nibble
 // (a string shorter than 16 bytes leaves the upper nibbles zero).  Equal strings have equal signatures, and so
 // do their suffixes of any common length k <= 16 (mask with tb_sig_mask(k)): the repetition pass uses that as a

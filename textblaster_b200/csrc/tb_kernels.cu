@@ -181,7 +181,7 @@ __global__ void __launch_bounds__((TB_REP_CAP0 << TIER) / 8) k_gr_rep_c(KBatch a
 }
 __global__ void __launch_bounds__(TB_REP_X_THREADS) k_gr_rep_x(KBatch a, const int64_t* ts, const int64_t* te, GrScratch s,
                                                                GrCfg cfg, int step, tb_gr_stats* out) {
-  __shared__ uint64_t s_red[64];
+  __shared__ uint64_t s_red[64 + 40];  // the CTA collectives' scratch and the per-level results of the warps' tasks (tb_rep.cuh)
   __shared__ uint32_t s_i;
   const uint32_t count = s.counters[TB_GR_CNT_LEN(TB_REP_TIER_X)];
   for (;;) {
@@ -394,6 +394,15 @@ void tb_launch_fw_fin(cudaStream_t st, const KBatch& b, const FwCfg& cfg, const 
                       uint32_t* cursor) {
   if (b.n) k_fw_fin<<<persistent_grid(b.n, sm_count, 16), TB_BLOCK, 0, st>>>(b, cfg, s, step, out, cursor);
 }
+#if defined(TB_REP_PROFILE)
+// measurement build: the clocks of the repetition pass per tier and phase (tb_rep.cuh), read out and cleared
+extern "C" int tb_debug_rep_profile(unsigned long long* out) {
+  cudaDeviceSynchronize();
+  if (cudaMemcpyFromSymbol(out, tb_rep_prof, sizeof(unsigned long long) * 8 * 32) != cudaSuccess) return 1;
+  unsigned long long zero[8 * 32] = {};
+  return cudaMemcpyToSymbol(tb_rep_prof, zero, sizeof zero) == cudaSuccess ? 0 : 1;
+}
+#endif
 int tb_kernels_init() {
   cudaError_t e = cudaFuncSetAttribute(k_gr_rep_c<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TB_REP_CTA_SMEM(tb_rep_cap(3)));
   if (e == cudaSuccess) e = cudaFuncSetAttribute(k_gr_rep_c<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TB_REP_CTA_SMEM(tb_rep_cap(4)));

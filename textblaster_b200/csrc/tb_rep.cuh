@@ -23,11 +23,26 @@
 #include "tb_kernels.cuh"
 #include "tb_simt.cuh"
 
+// -DTB_REP_PROFILE (a measurement build, tools/build_variant.sh): thread 0 of every document's group adds the clocks it
+// spent in each phase of rep_body to tb_rep_prof[tier][phase]; tb_debug_rep_profile (tb_kernels.cu) reads them out.
+#if defined(TB_REP_PROFILE) && !defined(TB_HOST_EMUL)
+static __device__ unsigned long long tb_rep_prof[8][32];
+#define REP_PROF_BEGIN(tier_) const int prof_tier_ = (tier_); long long prof_t0_ = clock64();
+#define REP_PROF(ph) { if (g.tid == 0) { const long long t1_ = clock64(); atomicAdd(&tb_rep_prof[prof_tier_][ph], (unsigned long long)(t1_ - prof_t0_)); prof_t0_ = t1_; } }
+#define REP_PROF_COUNT(slot) { if (g.tid == 0) atomicAdd(&tb_rep_prof[prof_tier_][slot], 1ull); }
+#else
+#define REP_PROF_BEGIN(tier_)
+#define REP_PROF(ph) {}
+#define REP_PROF_COUNT(slot) {}
+#endif
+
 #if defined(TB_HOST_EMUL)
 extern uint64_t tbe_stat_rep_words, tbe_stat_rep_items, tbe_stat_rep_pruned;  // word ends / candidates among them / documents pruned
+extern uint64_t tbe_stat_rep_task_small, tbe_stat_rep_task_table;             // levels a warp of a CTA tier worked off alone: in registers / with a table
 #endif
 
 #define TB_REP_X_THREADS 512
+#define TB_REP_TASK_ITEMS 256u  // CTA tiers: up to this many pruned word ends, a warp works a whole level off by itself (capacity / 8 threads = capacity / 256 warps share the arrays)
 #define TB_REP_PRUNE_FROM 4u  // duplicate n-gram levels from this order on run over the signature candidates only
 #define TB_REP_SIG_MIN 6u     // ... if the shortest n-gram of the first such level has at least this many bytes
 
@@ -54,6 +69,7 @@ struct BlockGroup {
   int tid;
   uint64_t* red;
   mutable int phase = 0;
+  static constexpr int kSize = 0;  // (not one warp)
   TB_D int size() const { return (int)blockDim.x; }
   TB_D void sync() const { __syncthreads(); }
   TB_D uint64_t* publish(uint64_t v) const {  // lane 0 of every warp posts v; returns the half holding the posts
@@ -96,8 +112,9 @@ struct BlockGroup {
 // host emulation: N threads share one barrier + mailbox (tb_simt.cuh SimtBlock)
 struct BlockGroup {
   int tid;
-  uint64_t* red;  // unused
+  uint64_t* red;  // the collectives go through the emulated CTA's mailbox; the words behind the first 64 are used as on the device
   mutable int phase = 0;
+  static constexpr int kSize = 0;
   TB_D int size() const { return simt_block->n; }
   TB_D void sync() const { simt_block->bar.arrive_and_wait(); }
   TB_D uint64_t sum64(uint64_t v) const {
@@ -130,6 +147,10 @@ struct BlockGroup {
   }
 };
 #endif
+
+// num / den > thr in double precision (the reference's f64 comparison); out of line: a double division is some forty
+// instructions and the repetition pass has a dozen of them, all rarely on the critical path
+TB_HD_NOINLINE bool rep_frac_gt(uint64_t num, double den, double thr) { return (double)num / den > thr; }
 
 // ---- tables ----------------------------------------------------------------------------------
 template <class IdxT> struct IdxTraits;
@@ -249,6 +270,67 @@ TB_D uint64_t rep_dup_walk(const G& g, IdxT* fo, IdxT* cand, const uint32_t* cbi
   }
   g.sync();
   return rep;  // valid on tid 0
+}
+
+// One level of find_all_duplicate over the items list[0 .. items) (word ends, increasing; NULL: item i ends with word i):
+// the keys of level n in H (brought up from level dcur, 0: from scratch -- new words go in front), a table of first
+// items per key, the candidates, the walk.  Returns the repeated bytes (valid on tid 0).  tab: rep_tab_size(items)
+// words; H, cnt: one entry per item; flag: a bit per item.  Ends with a barrier of the group.
+template <class G, class IdxT>
+TB_D uint64_t rep_dup_level(const G& g, const uint64_t* wh, const uint32_t* woff, const uint64_t* powtab, const IdxT* list, uint32_t items,
+                            uint32_t n, uint32_t dcur, uint64_t* H, uint32_t* tab, IdxT* cnt, uint32_t* flag) {
+  const uint32_t EMPTY = 0xFFFFFFFFu;
+  const uint32_t T = rep_tab_size(items);
+  // one sweep: clear the table, build the keys
+#pragma unroll 2
+  for (uint32_t i = g.tid; i < T; i += g.size()) {
+    tab[i] = EMPTY;
+    if (i >= items) continue;
+    const uint32_t e = list ? (uint32_t)list[i] : i;
+    if (e + 1u < n) continue;
+    const uint32_t q = e + 1u - n;  // first word of the n-gram
+    Hash2 h = tb_unpack(TB_LDG(wh + q));
+    const uint32_t stop = dcur ? e + 1u - dcur : e + 1u;  // the words [stop, e] are in the stored key already
+#pragma unroll 1
+    for (uint32_t j = q + 1; j < stop; j++) h = tb_hcat(h, tb_unpack(TB_LDG(wh + j)), tb_pow_pack(powtab, woff[j + 1] - woff[j]));
+    if (dcur) h = tb_hcat(h, tb_unpack(H[i]), tb_pow_pack(powtab, woff[e + 1] - woff[stop]));
+    H[i] = h.pack();
+  }
+  g.sync();
+  bool dup = false;
+#pragma unroll 1
+  for (uint32_t i = g.tid; i < items; i += g.size()) {
+    const uint32_t e = list ? (uint32_t)list[i] : i;
+    if (e + 1u < n) { cnt[i] = (IdxT)EMPTY; continue; }
+    const uint64_t key = H[i];
+    uint32_t sl = rep_slot(key, T);
+#pragma unroll 1
+    for (;;) {
+      uint32_t old = idx_cas(&tab[sl], EMPTY, i);
+      if (old == EMPTY) break;
+      if (H[old] == key) { idx_min(&tab[sl], i); dup = true; break; }
+      sl = rep_next(sl, T);
+    }
+    cnt[i] = (IdxT)sl;  // the slot of this key; resolved to its first item below
+  }
+  uint64_t v = 0;
+  if (g.any(dup)) {  // (a barrier: the table is complete)
+    // fo[i] = first item carrying the same key; the items that are not the first of their key form the bitmap
+    // of candidates (assembled a word per warp from ballots: no atomics)
+    const uint32_t rounds = (items + (uint32_t)g.size() - 1u) / (uint32_t)g.size();
+#pragma unroll 1
+    for (uint32_t r = 0; r < rounds; r++) {
+      const uint32_t i = r * (uint32_t)g.size() + (uint32_t)g.tid;
+      uint32_t f = i;
+      if (i < items && cnt[i] != (IdxT)EMPTY) f = tab[cnt[i]];
+      const uint32_t bits = g.warp_ballot(f != i);
+      if (i < items) cnt[i] = (IdxT)f;
+      if ((g.tid & 31) == 0 && i < items) flag[i >> 5] = bits;
+    }
+    g.sync();
+    v = rep_dup_walk(g, cnt, (IdxT*)tab, flag, woff, list, items, n);  // the table is dead now: it holds the candidate list
+  }
+  return v;
 }
 
 // ---- sets of at most 32 elements, one per lane of a warp, compared in registers (no table) --------------------
@@ -438,6 +520,7 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
   (void)te;
   const uint32_t EMPTY = 0xFFFFFFFFu;
   const GrDoc gd = s.doc[d];
+  REP_PROF_BEGIN(sizeof(IdxT) == 4 ? TB_REP_TIER_X : (int)tb_rep_tier(gd.W > gd.NL ? gd.W : gd.NL))
   tb_gr_stats st;
   st.reason_bits = 0; st.flags = gd.flags; st.char_len = gd.char_len; st.n_paras = 0; st.para_dup_elems = 0; st.para_dup_bytes = 0;
   st.n_lines = 0; st.line_dup_elems = 0; st.line_dup_bytes = 0; st.n_words = 0;
@@ -465,20 +548,17 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
       rep_lines_small(lh, ll, lg, NL, a.uc.powtab, g.tid, &de, &db, &NP, &pde, &pdb);
       st.n_lines = NL; st.line_dup_elems = de; st.line_dup_bytes = db;
       st.n_paras = NP; st.para_dup_elems = pde; st.para_dup_bytes = pdb;
-      const double r1 = (double)de / (double)(NL ? NL : 1u), r2 = (double)db / text_char_len;
-      const double q1 = (double)pde / (double)(NP ? NP : 1u), q2 = (double)pdb / text_char_len;
-      if ((cfg.has & TB_GR_HAS_DUP_PARA_FRAC) && q1 > cfg.dup_para_frac) reasons |= TB_GR_REASON_DUP_PARA_FRAC;
-      if ((cfg.has & TB_GR_HAS_DUP_PARA_CHAR_FRAC) && q2 > cfg.dup_para_char_frac) reasons |= TB_GR_REASON_DUP_PARA_CHAR_FRAC;
-      if ((cfg.has & TB_GR_HAS_DUP_LINE_FRAC) && r1 > cfg.dup_line_frac) reasons |= TB_GR_REASON_DUP_LINE_FRAC;
-      if ((cfg.has & TB_GR_HAS_DUP_LINE_CHAR_FRAC) && r2 > cfg.dup_line_char_frac) reasons |= TB_GR_REASON_DUP_LINE_CHAR_FRAC;
+      if ((cfg.has & TB_GR_HAS_DUP_PARA_FRAC) && rep_frac_gt(pde, (double)(NP ? NP : 1u), cfg.dup_para_frac)) reasons |= TB_GR_REASON_DUP_PARA_FRAC;
+      if ((cfg.has & TB_GR_HAS_DUP_PARA_CHAR_FRAC) && rep_frac_gt(pdb, text_char_len, cfg.dup_para_char_frac)) reasons |= TB_GR_REASON_DUP_PARA_CHAR_FRAC;
+      if ((cfg.has & TB_GR_HAS_DUP_LINE_FRAC) && rep_frac_gt(de, (double)(NL ? NL : 1u), cfg.dup_line_frac)) reasons |= TB_GR_REASON_DUP_LINE_FRAC;
+      if ((cfg.has & TB_GR_HAS_DUP_LINE_CHAR_FRAC) && rep_frac_gt(db, text_char_len, cfg.dup_line_char_frac)) reasons |= TB_GR_REASON_DUP_LINE_CHAR_FRAC;
     }
   } else {
   rep_dedup(g, tab, lh, ll, NL, &de, &db);
   st.n_lines = NL; st.line_dup_elems = de; st.line_dup_bytes = db;
   {
-    double r1 = (double)de / (double)(NL ? NL : 1u), r2 = (double)db / text_char_len;
-    if ((cfg.has & TB_GR_HAS_DUP_LINE_FRAC) && r1 > cfg.dup_line_frac) reasons |= TB_GR_REASON_DUP_LINE_FRAC;
-    if ((cfg.has & TB_GR_HAS_DUP_LINE_CHAR_FRAC) && r2 > cfg.dup_line_char_frac) reasons |= TB_GR_REASON_DUP_LINE_CHAR_FRAC;
+    if ((cfg.has & TB_GR_HAS_DUP_LINE_FRAC) && rep_frac_gt(de, (double)(NL ? NL : 1u), cfg.dup_line_frac)) reasons |= TB_GR_REASON_DUP_LINE_FRAC;
+    if ((cfg.has & TB_GR_HAS_DUP_LINE_CHAR_FRAC) && rep_frac_gt(db, text_char_len, cfg.dup_line_char_frac)) reasons |= TB_GR_REASON_DUP_LINE_CHAR_FRAC;
   }
   // ---- paragraphs (gopher_rep.rs:80-116): fold the ordered line pieces; a single '\n' joins lines
   // inside a paragraph, a run of >= 2 separates paragraphs.
@@ -488,13 +568,13 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
   rep_dedup(g, tab, A.H, A.woff, NP, &de, &db);
   st.n_paras = NP; st.para_dup_elems = de; st.para_dup_bytes = db;
   {
-    double r1 = (double)de / (double)(NP ? NP : 1u), r2 = (double)db / text_char_len;
-    if ((cfg.has & TB_GR_HAS_DUP_PARA_FRAC) && r1 > cfg.dup_para_frac) reasons |= TB_GR_REASON_DUP_PARA_FRAC;
-    if ((cfg.has & TB_GR_HAS_DUP_PARA_CHAR_FRAC) && r2 > cfg.dup_para_char_frac) reasons |= TB_GR_REASON_DUP_PARA_CHAR_FRAC;
+    if ((cfg.has & TB_GR_HAS_DUP_PARA_FRAC) && rep_frac_gt(de, (double)(NP ? NP : 1u), cfg.dup_para_frac)) reasons |= TB_GR_REASON_DUP_PARA_FRAC;
+    if ((cfg.has & TB_GR_HAS_DUP_PARA_CHAR_FRAC) && rep_frac_gt(db, text_char_len, cfg.dup_para_char_frac)) reasons |= TB_GR_REASON_DUP_PARA_CHAR_FRAC;
   }
   g.sync();
   }
 
+  REP_PROF(1)  // lines and paragraphs
   // ---- n-grams (gopher_rep.rs:159-196)
   uint32_t ntop_max = 0, ndup_max = 0;
   uint64_t top_levels = 0, dup_levels = 0;  // bit n: some entry of the list asks for n-grams of n words (n <= TB_MAX_NGRAM_N)
@@ -505,19 +585,24 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
   if (ntop_max > W) ntop_max = W;
   if (ndup_max > W) ndup_max = W;
   if (ntop_max || ndup_max) {
-    // byte offsets of the words in the concatenation: every thread sums a run of consecutive words, one prefix
-    // sum over the threads, then the run is written out
+    // byte offsets of the words in the concatenation: the lengths come into place first (coalesced, the loads in flight
+    // together), then every thread sums a run of consecutive words, one prefix sum over the threads, and the run is
+    // rewritten as offsets
+#pragma unroll 4
+    for (uint32_t i = g.tid; i < W; i += g.size()) A.woff[i + 1] = TB_LDG(wl_g + i);
+    g.sync();
     const uint32_t per = (W + (uint32_t)g.size() - 1u) / (uint32_t)g.size();
     const uint32_t i0 = (uint32_t)g.tid * per < W ? (uint32_t)g.tid * per : W, i1 = i0 + per < W ? i0 + per : W;
     uint32_t sum = 0;
 #pragma unroll 1
-    for (uint32_t i = i0; i < i1; i++) sum += TB_LDG(wl_g + i);
+    for (uint32_t i = i0; i < i1; i++) sum += A.woff[i + 1];
     uint32_t tot, run = g.exscan(sum, &tot);
 #pragma unroll 1
-    for (uint32_t i = i0; i < i1; i++) { A.woff[i] = run; run += TB_LDG(wl_g + i); }
-    if (g.tid == 0) A.woff[W] = tot;
+    for (uint32_t i = i0; i < i1; i++) { run += A.woff[i + 1]; A.woff[i + 1] = run; }
+    if (g.tid == 0) A.woff[0] = 0;
     g.sync();
   }
+  REP_PROF(2)  // word offsets
   const uint64_t* wh = wh_g;  // read in place (coalesced, once per pass)
   const uint32_t* woff = A.woff;
   // -- top n-grams: keys are the " "-joined strings (find_top_duplicate, text.rs:211-238).  A joined key
@@ -542,32 +627,60 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
             for (int k = 0; k < cfg.n_top; k++) {
               if (cfg.top_n[k] != lvl) continue;
               st.top_bytes[k] = v;
-              if ((double)v / text_char_len > cfg.top_frac[k]) reasons |= 1u << (TB_GR_REASON_TOP_SHIFT + k);
+              if (rep_frac_gt(v, text_char_len, cfg.top_frac[k])) reasons |= 1u << (TB_GR_REASON_TOP_SHIFT + k);
             }
           });
         break;
       }
       const uint32_t cn = W - n + 1;
       const uint32_t T = rep_tab_size(count);
+      if (sizeof(IdxT) == 2 && !pruned) {
+        // The first counted level of a shared-memory tier runs over every position: the word hashes come into shared
+        // memory first (the table's space, with all the loads in flight together), so that the key loop waits for no
+        // global load; the table is cleared once the keys are made.
+        uint64_t* const whs = (uint64_t*)tab;
+#pragma unroll 4
+        for (uint32_t i = g.tid; i < W; i += g.size()) whs[i] = TB_LDG(wh + i);
 #pragma unroll 1
-      for (uint32_t i = g.tid; i < T; i += g.size()) tab[i] = EMPTY;
+        for (uint32_t i = g.tid; i < fw; i += g.size()) A.flag[i] = 0;
+        g.sync();
 #pragma unroll 1
-      for (uint32_t i = g.tid; i < fw; i += g.size()) A.flag[i] = 0;
+        for (uint32_t i = g.tid; i < W; i += g.size()) {
+          cnt[i] = 0;
+          if (i >= cn) continue;
+          Hash2 h = tb_unpack(whs[i]);
 #pragma unroll 1
-      for (uint32_t k = g.tid; k < count; k += g.size()) {
-        const uint32_t i = pruned ? (uint32_t)list[k] : k;
-        cnt[i] = 0;
-        if (i >= cn) continue;
-        Hash2 h = tb_unpack(cur ? A.H[i] : TB_LDG(wh + i));
-#pragma unroll 1
-        for (uint32_t j = i + (cur ? cur : 1u); j < i + n; j++) {
-          h.push(' ', TB_LDG(a.uc.powtab + 1));
-          h = tb_hcat(h, tb_unpack(TB_LDG(wh + j)), tb_pow_pack(a.uc.powtab, woff[j + 1] - woff[j]));
+          for (uint32_t j = i + 1u; j < i + n; j++) {
+            h.push(' ', TB_LDG(a.uc.powtab + 1));
+            h = tb_hcat(h, tb_unpack(whs[j]), tb_pow_pack(a.uc.powtab, woff[j + 1] - woff[j]));
+          }
+          A.H[i] = h.pack();
         }
-        A.H[i] = h.pack();
+        g.sync();
+#pragma unroll 1
+        for (uint32_t i = g.tid; i < T; i += g.size()) tab[i] = EMPTY;
+      } else {
+#pragma unroll 1
+        for (uint32_t i = g.tid; i < T; i += g.size()) tab[i] = EMPTY;
+#pragma unroll 1
+        for (uint32_t i = g.tid; i < fw; i += g.size()) A.flag[i] = 0;
+#pragma unroll 1
+        for (uint32_t k = g.tid; k < count; k += g.size()) {
+          const uint32_t i = pruned ? (uint32_t)list[k] : k;
+          cnt[i] = 0;
+          if (i >= cn) continue;
+          Hash2 h = tb_unpack(cur ? A.H[i] : TB_LDG(wh + i));
+#pragma unroll 1
+          for (uint32_t j = i + (cur ? cur : 1u); j < i + n; j++) {
+            h.push(' ', TB_LDG(a.uc.powtab + 1));
+            h = tb_hcat(h, tb_unpack(TB_LDG(wh + j)), tb_pow_pack(a.uc.powtab, woff[j + 1] - woff[j]));
+          }
+          A.H[i] = h.pack();
+        }
       }
       cur = n;
       g.sync();
+      if (!pruned) { REP_PROF(12) }
       bool hit = false;
 #pragma unroll 1
       for (uint32_t k = g.tid; k < count; k += g.size()) {
@@ -589,6 +702,7 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
       }
       uint64_t best = 0;
       const bool any_hit = g.any(hit);  // (a barrier: the counts are complete)
+      if (!pruned) { REP_PROF(13) }
       if (any_hit) {
 #pragma unroll 1
         for (uint32_t k = g.tid; k < count; k += g.size()) {
@@ -607,9 +721,10 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
         for (int k = 0; k < cfg.n_top; k++) {
           if (cfg.top_n[k] != n) continue;
           st.top_bytes[k] = v;
-          if ((double)v / text_char_len > cfg.top_frac[k]) reasons |= 1u << (TB_GR_REASON_TOP_SHIFT + k);
+          if (rep_frac_gt(v, text_char_len, cfg.top_frac[k])) reasons |= 1u << (TB_GR_REASON_TOP_SHIFT + k);
         }
       }
+      if (!pruned) { REP_PROF(14) }
       // survivors, in order: an n'-gram (n' > n) that occurs twice holds n' - n + 1 n-grams that occur twice, so only
       // the positions i whose n-grams at i, i + 1, ..., i + (n' - n) all repeated can repeat at the next counted level n'
       uint32_t ncount = 0;
@@ -619,10 +734,12 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
         while (nn <= ntop_max && !((top_levels >> nn) & 1ull)) nn++;
         ncount = rep_compact_bits(g, A.flag, cn, list, nn - n + 1u > 32u ? 32u : nn - n + 1u);
       }
+      if (!pruned) { REP_PROF(7) }  // (the first counted level, over every position)
       count = ncount; pruned = true;
       g.sync();
     }
   }
+  REP_PROF(3)  // top n-grams
   // -- duplicate n-grams: keys are the concatenated strings (find_all_duplicate, text.rs:241-259).
   // An item is the n-gram that ends with word e; its key grows to the left from level to level.  Levels below
   // TB_REP_PRUNE_FROM run over every word end; from there on only over the ends whose suffix signature repeats.
@@ -644,6 +761,7 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
         for (uint32_t i = g.tid; i + n <= W; i += g.size()) { const uint32_t v = woff[i + n] - woff[i]; m = v < m ? v : m; }
         m = 0xFFFFFFFFu - (uint32_t)g.max64((uint64_t)(0xFFFFFFFFu - m));
         const uint32_t k = m < 16u ? m : 16u;
+        REP_PROF(15)
         if (k >= TB_REP_SIG_MIN) {
           // word ends whose last k key bytes occur at another word end too (first end per value in the table)
           const uint64_t mask = tb_sig_mask(k);
@@ -652,28 +770,75 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
           for (uint32_t i = g.tid; i < T; i += g.size()) tab[i] = EMPTY;
 #pragma unroll 1
           for (uint32_t i = g.tid; i < fw; i += g.size()) A.flag[i] = 0;
+          // the last k bytes of the words up to e (the scan pass stores 16 of them), into the key array: the probes
+          // below compare keys, and must not wait for global memory each time
+#pragma unroll 4
+          for (uint32_t e = n - 1 + g.tid; e < W; e += g.size()) A.H[e] = TB_LDG(wsg + e) & mask;
           g.sync();
+          REP_PROF(16)
 #pragma unroll 1
           for (uint32_t e = n - 1 + g.tid; e < W; e += g.size()) {
-            const uint64_t key = TB_LDG(wsg + e) & mask;  // the last k bytes of the words up to e (the scan pass stores 16 of them)
+            const uint64_t key = A.H[e];
             uint32_t sl = rep_slot(tb_mix64(key), T);
 #pragma unroll 1
             for (;;) {
               uint32_t old = idx_cas(&tab[sl], EMPTY, e);
               if (old == EMPTY) break;
-              if ((TB_LDG(wsg + old) & mask) == key) { simt_atomic_or(&A.flag[e >> 5], 1u << (e & 31)); simt_atomic_or(&A.flag[old >> 5], 1u << (old & 31)); break; }
+              if (A.H[old] == key) { simt_atomic_or(&A.flag[e >> 5], 1u << (e & 31)); simt_atomic_or(&A.flag[old >> 5], 1u << (old & 31)); break; }
               sl = rep_next(sl, T);
             }
           }
           g.sync();
+          REP_PROF(17)
           items = rep_compact_bits(g, A.flag, W, list);
           pruned = true; dcur = 0;
+          REP_PROF(4)  // signature pass
+          REP_PROF_COUNT(items <= 32u ? 9 : items <= TB_REP_TASK_ITEMS ? 10 : 11)
 #if defined(TB_HOST_EMUL)
           if (g.tid == 0) { tbe_stat_rep_words += W; tbe_stat_rep_items += items; tbe_stat_rep_pruned++; }
 #endif
         }
       }
       if (items == 0) continue;  // nothing can repeat at this level: dup_bytes stays 0
+      if constexpr (G::kSize != 32) if (pruned && items <= TB_REP_TASK_ITEMS) {
+        // A CTA, and few word ends in play: given the list, the remaining levels are independent of one another.  A warp
+        // takes a level at a time and works it off on its own -- in registers for up to 32 items, else with a table in
+        // its share of the working arrays -- so that the order-dependent walks of the levels run side by side instead
+        // of one after the other with the rest of the CTA waiting.
+        const int w = g.tid >> 5, lane = g.tid & 31, nw = g.size() >> 5;
+        const WarpGroup wg{lane};
+        uint64_t* const res = g.red + 64;  // [TB_MAX_NGRAM_N + 1] repeated bytes per level
+        uint32_t t = 0;
+#pragma unroll 1
+        for (uint32_t n2 = n; n2 <= ndup_max; n2++) {
+          if (!((dup_levels >> n2) & 1ull)) continue;
+          if ((int)(t++ % (uint32_t)nw) != w) continue;
+          uint64_t v = 0;
+#if defined(TB_HOST_EMUL)
+          if (lane == 0) { if (items <= 32u) tbe_stat_rep_task_small++; else tbe_stat_rep_task_table++; }
+#endif
+          if (items <= 32u)
+            rep_dup_small(wh, woff, a.uc.powtab, (uint32_t)lane < items ? (uint32_t)list[lane] : 0u, items, n2, n2, 1ull << n2, lane,
+                          [&](uint32_t, uint64_t val) { v = val; });
+          else
+            v = rep_dup_level<WarpGroup, IdxT>(wg, wh, woff, a.uc.powtab, list, items, n2, 0u, A.H + (uint32_t)w * TB_REP_TASK_ITEMS,
+                                               tab + (uint32_t)w * 2u * TB_REP_TASK_ITEMS, cnt + (uint32_t)w * TB_REP_TASK_ITEMS,
+                                               A.flag + (uint32_t)w * (TB_REP_TASK_ITEMS / 32u));
+          if (lane == 0) res[n2] = v;
+        }
+        g.sync();
+        if (g.tid == 0) {
+#pragma unroll 1
+          for (int k = 0; k < cfg.n_dup; k++) {
+            const uint32_t lvl = cfg.dup_n[k];
+            if (lvl < n || lvl > ndup_max) continue;
+            const uint64_t v = res[lvl];
+            st.dup_bytes[k] = v;
+            if (rep_frac_gt(v, text_char_len, cfg.dup_frac[k])) reasons |= 1u << (TB_GR_REASON_DUP_SHIFT + k);
+          }
+        }
+        break;
+      }
       if (pruned && items <= 32u) {
         // few word ends in play: the first warp takes them into registers and finishes the list on its own
         if (g.tid < 32)
@@ -683,76 +848,30 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
                           for (int k = 0; k < cfg.n_dup; k++) {
                             if (cfg.dup_n[k] != lvl) continue;
                             st.dup_bytes[k] = v;
-                            if ((double)v / text_char_len > cfg.dup_frac[k]) reasons |= 1u << (TB_GR_REASON_DUP_SHIFT + k);
+                            if (rep_frac_gt(v, text_char_len, cfg.dup_frac[k])) reasons |= 1u << (TB_GR_REASON_DUP_SHIFT + k);
                           }
                         });
         break;
       }
-      const uint32_t T = rep_tab_size(items);
-      // one sweep: clear the table, bring the keys from level dcur to level n (new words go in front)
-#pragma unroll 2
-      for (uint32_t i = g.tid; i < T; i += g.size()) {
-        tab[i] = EMPTY;
-        if (i >= items) continue;
-        const uint32_t e = pruned ? (uint32_t)list[i] : i;
-        if (e + 1u < n) continue;
-        const uint32_t q = e + 1u - n;  // first word of the n-gram
-        Hash2 h = tb_unpack(TB_LDG(wh + q));
-        const uint32_t stop = dcur ? e + 1u - dcur : e + 1u;  // the words [stop, e] are in the stored key already
-#pragma unroll 1
-        for (uint32_t j = q + 1; j < stop; j++) h = tb_hcat(h, tb_unpack(TB_LDG(wh + j)), tb_pow_pack(a.uc.powtab, woff[j + 1] - woff[j]));
-        if (dcur) h = tb_hcat(h, tb_unpack(A.H[i]), tb_pow_pack(a.uc.powtab, woff[e + 1] - woff[stop]));
-        A.H[i] = h.pack();
-      }
+      const uint64_t v = rep_dup_level<G, IdxT>(g, wh, woff, a.uc.powtab, pruned ? list : (const IdxT*)nullptr, items, n, dcur, A.H, tab, cnt, A.flag);
       dcur = n;
-      g.sync();
-      bool dup = false;
-#pragma unroll 1
-      for (uint32_t i = g.tid; i < items; i += g.size()) {
-        const uint32_t e = pruned ? (uint32_t)list[i] : i;
-        if (e + 1u < n) { cnt[i] = (IdxT)EMPTY; continue; }
-        const uint64_t key = A.H[i];
-        uint32_t sl = rep_slot(key, T);
-#pragma unroll 1
-        for (;;) {
-          uint32_t old = idx_cas(&tab[sl], EMPTY, i);
-          if (old == EMPTY) break;
-          if (A.H[old] == key) { idx_min(&tab[sl], i); dup = true; break; }
-          sl = rep_next(sl, T);
-        }
-        cnt[i] = (IdxT)sl;  // the slot of this key; resolved to its first item below
-      }
-      uint64_t v = 0;
-      if (g.any(dup)) {  // (a barrier: the table is complete)
-        // fo[i] = first item carrying the same key; the items that are not the first of their key form the bitmap
-        // of candidates (assembled a word per warp from ballots: no atomics)
-        const uint32_t rounds = (items + (uint32_t)g.size() - 1u) / (uint32_t)g.size();
-#pragma unroll 1
-        for (uint32_t r = 0; r < rounds; r++) {
-          const uint32_t i = r * (uint32_t)g.size() + (uint32_t)g.tid;
-          uint32_t f = i;
-          if (i < items && cnt[i] != (IdxT)EMPTY) f = tab[cnt[i]];
-          const uint32_t bits = g.warp_ballot(f != i);
-          if (i < items) cnt[i] = (IdxT)f;
-          if ((g.tid & 31) == 0 && i < items) A.flag[i >> 5] = bits;
-        }
-        g.sync();
-        v = rep_dup_walk(g, cnt, (IdxT*)tab, A.flag, woff, pruned ? list : (const IdxT*)nullptr, items, n);  // the table is dead now: it holds the candidate list
-      }
       if (g.tid == 0) {
 #pragma unroll 1
         for (int k = 0; k < cfg.n_dup; k++) {
           if (cfg.dup_n[k] != n) continue;
           st.dup_bytes[k] = v;
-          if ((double)v / text_char_len > cfg.dup_frac[k]) reasons |= 1u << (TB_GR_REASON_DUP_SHIFT + k);
+          if (rep_frac_gt(v, text_char_len, cfg.dup_frac[k])) reasons |= 1u << (TB_GR_REASON_DUP_SHIFT + k);
         }
       }
       // no barrier here: the next level's sweep only follows g.any() above or the one that ends rep_dup_walk
     }
   }
+  REP_PROF(5)  // duplicate n-gram levels
   if (g.tid == 0) {
     st.n_words = W; st.reason_bits = reasons;
     out[d] = st;
     if (reasons) { a.alive[d] = 0; a.failed[d] = (int8_t)step; }
   }
+  REP_PROF(6)  // result
+  REP_PROF_COUNT(8)
 }

@@ -6,6 +6,9 @@ import collections
 import csv
 import subprocess
 import sys
+import os
+sys.path.insert(0, "/root/repo/tools" if not os.path.exists(os.path.join(os.path.dirname(os.path.abspath(__file__)), "ncu_names.py")) else os.path.dirname(os.path.abspath(__file__)))
+from ncu_names import kname
 
 src = subprocess.run(["ncu", "-i", sys.argv[1], "--page", "source", "--csv", "--print-source", "sass"],
                      capture_output=True, text=True).stdout
@@ -16,7 +19,7 @@ for r in csv.reader(src.splitlines()):
     if not r:
         continue
     if r[0] == "Kernel Name":
-        fn = r[1].split("(")[0].split("::")[-1]
+        fn = kname(r[1])
         continue
     if r[0] == "Address":
         ie = r.index("Instructions Executed")

@@ -1,6 +1,9 @@
 #!/usr/bin/env python3
 """Summarise an .ncu-rep: per kernel headline metrics + hottest source lines (needs -lineinfo + --import-source on)."""
 import collections, csv, subprocess, sys
+import os
+sys.path.insert(0, "/root/repo/tools" if not os.path.exists(os.path.join(os.path.dirname(os.path.abspath(__file__)), "ncu_names.py")) else os.path.dirname(os.path.abspath(__file__)))
+from ncu_names import kname
 
 rep = sys.argv[1]
 top = int(sys.argv[2]) if len(sys.argv) > 2 else 18
@@ -11,7 +14,7 @@ want = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum
         "launch__registers_per_thread", "smsp__inst_executed.sum", "smsp__thread_inst_executed_per_inst_executed.ratio",
         "smsp__issue_active.avg.pct_of_peak_sustained_active", "l1tex__t_sector_hit_rate.pct", "lts__t_sector_hit_rate.pct"]
 for r in rows[2:]:
-    name = r[h.index("Kernel Name")].split("(")[0].split("::")[-1]
+    name = kname(r[h.index("Kernel Name")])
     print(name, {w.split(".")[0][-22:]: r[h.index(w)] for w in want if w in h})
 src = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--print-source", "cuda,sass"], capture_output=True, text=True).stdout
 fn = fpath = hdr = None
@@ -22,7 +25,7 @@ for r in csv.reader(src.splitlines()):
     if r[0] == "File Path":
         fpath = r[1].split("/")[-1]; continue
     if r[0] == "Function Name":
-        fn = r[1].split("(")[0].split("::")[-1]; continue
+        fn = kname(r[1]); continue
     if r[0] == "Line No":
         hdr = r; ie = hdr.index("Instructions Executed"); si = hdr.index("# Samples"); ti = hdr.index("Thread Instructions Executed"); continue
     if hdr and fn and r[0].isdigit() and r[2] == "-" and r[ie].isdigit():

@@ -6,6 +6,9 @@ import collections
 import csv
 import subprocess
 import sys
+import os
+sys.path.insert(0, "/root/repo/tools" if not os.path.exists(os.path.join(os.path.dirname(os.path.abspath(__file__)), "ncu_names.py")) else os.path.dirname(os.path.abspath(__file__)))
+from ncu_names import kname
 
 rep = sys.argv[1]
 top = int(sys.argv[2]) if len(sys.argv) > 2 else 12
@@ -21,7 +24,7 @@ for r in csv.reader(src.splitlines()):
         fpath = r[1].split("/")[-1]
         continue
     if r[0] == "Function Name":
-        fn = r[1].split("(")[0].split("::")[-1]
+        fn = kname(r[1])
         continue
     if r[0] == "Line No":
         hdr = r
