@@ -661,13 +661,14 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--decode-entities", action="store_true", help="also run the HTML-entity pre-pass of the reader (SURVEY 8f row 1); not part of the headline workload")
     ap.add_argument("--order", default="baseline", choices=["baseline", "shipped"], help="step order: BASELINE.json configs[1] (C4, GopherQuality, GopherRepetition; the headline) or the shipped pipeline_config.yaml (GopherRepetition, GopherQuality, C4)")
-    ap.add_argument("--content", default="runs", choices=["runs", "bytes"],
+    ap.add_argument("--content", default="auto", choices=["auto", "runs", "bytes"],
                     help="how C4's rewritten content comes back: runs of the input text (TB_OPT_RETURN_CONTENT = 2; the end-to-end step "
-                         "then gathers the kept documents' content on the host, inside the timed region) or the bytes themselves (1)")
+                         "then gathers the kept documents' content on the host, inside the timed region) or the bytes themselves (1); auto: runs, "
+                         "except that the end-to-end step takes the bytes when the host has fewer than 6 cores per rank to gather with")
     ap.add_argument("--config", type=int, default=2, choices=[1, 2, 3, 4], help="BASELINE.json configuration: 1 (C4 on a 10k-document Parquet file), 2 (headline, default), 3 (n-gram sweep on long documents), 4 (streamed row groups)")
     ap.add_argument("--docs-total", type=int, default=0, help="config 4: documents over all ranks (0: one pass over every rank's pool)")
     ap.add_argument("--pool-groups", type=int, default=16, help="config 4: distinct row groups generated per rank before the timed region")
-    ap.add_argument("--pipelines", type=int, default=3, help="config 4: pipelines (and host threads) per GPU")
+    ap.add_argument("--pipelines", type=int, default=4, help="config 4: pipelines (and host threads) per GPU")
     ap.add_argument("--parity-groups", type=int, default=2, help="config 4: row groups of rank 0 checked against the oracle")
     ap.add_argument("--host-memory", default="pinned", choices=["pinned", "pageable"],
                     help="where the text of the end-to-end step lives: pinned host memory (default) or pageable memory as Arrow allocates it "
@@ -745,7 +746,10 @@ def main():
         pipe.set_option(_abi.TB_OPT_DECODE_HTML_ENTITIES, 1)
     if args.bulk_stage_tiles:
         pipe.set_option(_abi.TB_OPT_BULK_STAGE_TILES, args.bulk_stage_tiles)
-    runs_mode = args.content == "runs" and not args.decode_entities
+    runs_mode = args.content in ("runs", "auto") and not args.decode_entities
+    # the end-to-end step rebuilds the kept documents' content on host threads: with few cores per rank (many GPUs on
+    # one host) the copy engine is the cheaper way to get the content into host memory, so `auto` takes the bytes there
+    e2e_runs_mode = runs_mode and (args.content == "runs" or (os.cpu_count() or 1) // world >= 6)
     pipe.set_option(_abi.TB_OPT_RETURN_CONTENT, 2 if runs_mode else 1)
     # runs mode: the end-to-end call also rebuilds the content of the kept documents (what the writer of the output
     # file takes) on host threads inside the library, chunk by chunk behind the device
@@ -842,6 +846,9 @@ def main():
     h2d_all = concurrent_probe() if world > 1 and pinned else None
     d2h_all = concurrent_probe(back=True) if world > 1 and pinned else None
     dt_dev, launches, gpu_ms, kept, cbytes, clocks, ktimes = timed(step_device)
+    if runs_mode and not e2e_runs_mode:
+        pipe.set_option(_abi.TB_OPT_RETURN_CONTENT, 1)
+        pipe.set_option(_abi.TB_OPT_GATHER_KEPT, 0)
     dt_e2e, launches_e, gpu_ms_e, _, cbytes_e, clocks_e, _ = timed(step_host)
     # host-side gather of the keep masks onto rank 0, ordered by row group (the only cross-rank traffic of the job)
     t0 = time.perf_counter()
@@ -896,6 +903,9 @@ def main():
                        "content": ("runs of the input text (TB_OPT_RETURN_CONTENT = 2); the e2e call also rebuilds the content of the kept documents "
                                    "on the host from the runs and the input column (TB_OPT_GATHER_KEPT, %d threads, %.2f GB per step), "
                                    "inside the timed region" % (gather_threads, last_keep.get("kept_bytes", 0) / 1e9))
+                                  if e2e_runs_mode else
+                                  ("value: runs of the input text (TB_OPT_RETURN_CONTENT = 2); e2e: the bytes (TB_OPT_RETURN_CONTENT = 1) -- %d host cores per rank "
+                                   "are too few to rebuild the kept documents' content behind the device" % ((os.cpu_count() or 1) // world))
                                   if runs_mode else "bytes (TB_OPT_RETURN_CONTENT = 1)",
                        "host_memory": args.host_memory + ("" if args.host_memory == "pinned" else " (staged by the library, TB_OPT_STAGE_THREADS = %s)" % ("default 4" if args.stage_threads < 0 else args.stage_threads)),
                        "chunk_mb": args.chunk_mb, "host": numa, "l2": "inputs (%.2f GB per step) larger than the 126 MB L2" % (n_bytes / 1e9),
@@ -905,7 +915,8 @@ def main():
             "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": n_bytes + 8 * (n_docs + 1),
                     "d2h_bytes_per_step": n_docs * (2 + stats_bytes) + cbytes_e + 8 * (n_docs + 1), "text_gbs": total_bytes * K / dt_e2e / 1e9,
                     "ms_per_step": dt_e2e / K * 1e3,
-                    "host_gathered_bytes_per_step": last_keep.get("kept_bytes") if runs_mode else None},
+                    "content": "runs + host gather" if e2e_runs_mode else "bytes",
+                    "host_gathered_bytes_per_step": last_keep.get("kept_bytes") if e2e_runs_mode else None},
             "gpu_launches": launches,
             "roofline": {"bound": "hbm", "kernel": dom_name, "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak if peak else None, "traffic": ncu_traffic(dom_name, alg_bytes_step / launches_per_step), "peak_source": peak_src,
