@@ -214,7 +214,9 @@ TB_D_NOINLINE void gr_doc_walk(const KBatch& a, const Classifier& C, const TextR
 // Words one tile can stage (five 32-bit words each).  A tile can end up to 23 * 32 words (two words per three
 // bytes, "a\u00a9a\u00a9..."); a tile with more than this many -- twelve per stretch, under three bytes per word and
 // separator -- hands the document to the walking path instead of tripling every warp's shared memory.
+#ifndef TB_GR_STAGE_WORDS
 #define TB_GR_STAGE_WORDS (12 * 32)
+#endif
 #define TB_GR_STAGE_U32 (5 * TB_GR_STAGE_WORDS + 2 * 32 * 32)
 template <class Feed>
 TB_D bool gr_doc_tiles(const KBatch& a, const LutEntry* lut, uint32_t* stage, const Classifier& C, const TextRange& R,
