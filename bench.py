@@ -908,7 +908,7 @@ def main():
                                    "are too few to rebuild the kept documents' content behind the device" % ((os.cpu_count() or 1) // world))
                                   if runs_mode else "bytes (TB_OPT_RETURN_CONTENT = 1)",
                        "host_memory": args.host_memory + ("" if args.host_memory == "pinned" else " (staged by the library, TB_OPT_STAGE_THREADS = %s)" % ("default 4" if args.stage_threads < 0 else args.stage_threads)),
-                       "chunk_mb": args.chunk_mb, "host": numa, "l2": "inputs (%.2f GB per step) larger than the 126 MB L2" % (n_bytes / 1e9),
+                       "chunk_mb": args.chunk_mb, "host": numa, "host_cpus": os.cpu_count(), "l2": "inputs (%.2f GB per step) larger than the 126 MB L2" % (n_bytes / 1e9),
                        "generator_s": round(t_gen, 2)},
             "text_gbs": total_bytes * K / dt_dev / 1e9, "total_docs_per_step": total_docs,
             "gpu_ms_per_step": gpu_ms / K, "keep_rate": kept / max(n_docs, 1),
