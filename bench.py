@@ -538,7 +538,9 @@ def run_config4(args, rank, local_rank, world):
 
     steps = shipped_chain(args.with_fineweb, args.order)
     pool_groups = args.pool_groups
-    total_groups = max(world, (args.docs_total or pool_groups * world * GROUP_DOCS) // GROUP_DOCS)
+    # by default four passes over every rank's pool (each pass copies the text to the device anew): long enough for the
+    # start and the end of the stream not to weigh
+    total_groups = max(world, (args.docs_total or 4 * pool_groups * world * GROUP_DOCS) // GROUP_DOCS)
     mine = shard.groups_of_rank(total_groups, rank, world)  # round-robin: rank r takes groups r, r + world, ...
     threads = max(1, (os.cpu_count() or 1) // world)
     # ---- the pool: this rank's first `pool_groups` row groups, each generated from its own document indices
@@ -558,7 +560,8 @@ def run_config4(args, rank, local_rank, world):
     pool_bytes = sum(int(o[-1]) for _, o, _ in pool)
     gen_gbs = pool_bytes / gen_s / 1e9
 
-    gather_threads = args.gather_threads or max(1, min(8, threads))
+    # (every pipeline gathers the kept content of its own batch: the rank's host threads are shared out among them)
+    gather_threads = args.gather_threads or max(1, min(8, threads // max(args.pipelines, 1)))
     runner = StreamingRunner(lambda: GpuBatchPipeline(steps, device=local_rank), pipelines=args.pipelines,
                              copy_stats=False, gather_kept=gather_threads if any(p.CTYPE == _abi.TB_STEP_C4_QUALITY for p in steps) else 0)
 
@@ -666,7 +669,7 @@ def main():
                          "then gathers the kept documents' content on the host, inside the timed region) or the bytes themselves (1); auto: runs, "
                          "except that the end-to-end step takes the bytes when the host has fewer than 6 cores per rank to gather with")
     ap.add_argument("--config", type=int, default=2, choices=[1, 2, 3, 4], help="BASELINE.json configuration: 1 (C4 on a 10k-document Parquet file), 2 (headline, default), 3 (n-gram sweep on long documents), 4 (streamed row groups)")
-    ap.add_argument("--docs-total", type=int, default=0, help="config 4: documents over all ranks (0: one pass over every rank's pool)")
+    ap.add_argument("--docs-total", type=int, default=0, help="config 4: documents over all ranks (0: four passes over every rank's pool)")
     ap.add_argument("--pool-groups", type=int, default=16, help="config 4: distinct row groups generated per rank before the timed region")
     ap.add_argument("--pipelines", type=int, default=4, help="config 4: pipelines (and host threads) per GPU")
     ap.add_argument("--parity-groups", type=int, default=2, help="config 4: row groups of rank 0 checked against the oracle")
@@ -675,6 +678,10 @@ def main():
                          "(the library then stages it through its own pinned ring, TB_OPT_STAGE_THREADS)")
     ap.add_argument("--stage-threads", type=int, default=-1, help="TB_OPT_STAGE_THREADS for --host-memory pageable (-1: library default, 0: off)")
     ap.add_argument("--bulk-stage-tiles", type=int, default=0, help="TB_OPT_BULK_STAGE_TILES: bulk-copy staging of documents of at least this many 1 KiB tiles (0: off)")
+    ap.add_argument("--e2e-api", default="call", choices=["call", "runner"],
+                    help="how the end-to-end figure of the headline is taken: one tb_pipeline_run_batch call per step (default), or the step's "
+                         "row groups streamed through StreamingRunner with --pipelines pipelines per GPU (the single call is then reported beside "
+                         "it as e2e.single_call; measured 116-134 ms per step against 125 for the call: it depends on how the pipelines fall into step)")
     ap.add_argument("--gather-threads", type=int, default=0, help="host threads of TB_OPT_GATHER_KEPT (0: min(8, cpus / ranks))")
     ap.add_argument("--with-fineweb", action="store_true",
                     help="append FineWebQualityFilter (SURVEY 8(f) row 3) to the chain; not the headline workload")
@@ -850,6 +857,79 @@ def main():
         pipe.set_option(_abi.TB_OPT_RETURN_CONTENT, 1)
         pipe.set_option(_abi.TB_OPT_GATHER_KEPT, 0)
     dt_e2e, launches_e, gpu_ms_e, _, cbytes_e, clocks_e, _ = timed(step_host)
+    # ---- the same steps as a stream of row groups through the runner (textblaster_b200/runner.py): several pipelines of
+    # one context take the rank's row groups in turn, so the copies of one batch and the kernel tails of another overlap
+    single_call = {"value": None, "ms_per_step": dt_e2e / max(args.steps, 1) * 1e3, "d2h_content_bytes_per_step": cbytes_e}
+    use_runner = (args.e2e_api == "runner" and args.host_memory == "pinned" and not args.decode_entities and not args.bulk_stage_tiles
+                  and n_docs >= 4 * min(GROUP_DOCS, args.docs))
+    stream = None
+    if use_runner:
+        from textblaster_b200.runner import RowGroup, StreamingRunner
+        P = max(1, args.pipelines)
+        gt = (args.gather_threads or max(1, min(8, ((os.cpu_count() or 1) // world) // P))) if e2e_runs_mode else 0
+        bounds, d0 = [], 0
+        for g in mine:
+            a, b = groups[g]
+            bounds.append((d0, d0 + (b - a)))
+            d0 += b - a
+
+        def make():
+            return GpuBatchPipeline(steps, device=local_rank)  # (content as bytes unless the runner is told to gather: gather_kept)
+
+        runner = StreamingRunner(make, pipelines=P, copy_stats=False, gather_kept=gt)
+
+        copies = None
+        if os.environ.get("TB_BENCH_STREAM_COPY") == "1":  # (diagnosis: every row group in a pinned buffer of its own, offsets from 0)
+            copies = []
+            for a, b in bounds:
+                tu = torch.empty(int(off[b] - off[a]) + 64, dtype=torch.uint8, pin_memory=True)
+                to = torch.empty(b - a + 1, dtype=torch.int64, pin_memory=True)
+                tu.numpy()[:int(off[b] - off[a])] = utf8[int(off[a]):int(off[b])]
+                to.numpy()[:] = off[a:b + 1] - off[a]
+                copies.append((tu, to))
+
+        def source(n_steps):
+            for s_ in range(n_steps):
+                for k, (a, b) in enumerate(bounds):
+                    if copies:
+                        yield RowGroup(s_ * len(bounds) + k, copies[k][0].numpy()[:int(off[b] - off[a])], copies[k][1].numpy())
+                    else:
+                        yield RowGroup(s_ * len(bounds) + k, utf8, off[a:b + 1])
+
+        big = max(bounds, key=lambda ab: int(off[ab[1]] - off[ab[0]]))
+        runner.prime(RowGroup(-1, utf8, off[big[0]:big[1] + 1]))
+        stream_dbg = {}
+        runner.run(source(max(args.warmup, 1)))
+        stream_keep = np.zeros(n_docs, np.uint8)
+        stream_tot = {"kept_bytes": 0, "runs_bytes": 0}
+
+        def sink(index, sm):
+            a, b = bounds[index % len(bounds)]
+            if index < len(bounds):
+                stream_keep[a:b] = sm.keep
+            if sm.kept_offsets is not None:
+                stream_tot["kept_bytes"] += int(sm.kept_offsets[-1])
+
+        barrier()
+        sampler_s = ClockSampler(local_rank)
+        if rank == 0:
+            sampler_s.start()
+        t0 = time.perf_counter()
+        tot_s = runner.run(source(args.steps), sink)
+        barrier()
+        dt_s = time.perf_counter() - t0
+        clocks_s = sampler_s.stop()
+        ts = torch.tensor([dt_s], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(ts, op=dist.ReduceOp.MAX)
+        dt_s = float(ts.item())
+        assert np.array_equal(stream_keep, last_keep["k"]), "the streamed run and the single call disagree on the keep mask"
+        stream_dbg.update(gpu_ms=tot_s.gpu_ms, source_wait_s=tot_s.source_wait_s)
+        if rank == 0 and os.environ.get("TB_BENCH_DEBUG"):
+            print("[bench] stream: %.1f ms/step, gpu_ms %.1f per step, source wait %.3f s" % (dt_s / args.steps * 1e3, tot_s.gpu_ms / args.steps, tot_s.source_wait_s), file=sys.stderr)
+        stream = {"dt": dt_s, "pipelines": P, "gather_threads": gt, "launches": tot_s.gpu_launches, "clocks": clocks_s,
+                  "kept_bytes_per_step": stream_tot["kept_bytes"] // max(args.steps, 1)}
+        runner.close()
     # host-side gather of the keep masks onto rank 0, ordered by row group (the only cross-rank traffic of the job)
     t0 = time.perf_counter()
     local, pos = {}, 0
@@ -867,6 +947,9 @@ def main():
     if rank == 0:
         K = max(args.steps, 1)
         value = total_docs * K / dt_dev
+        single_call["value"] = total_docs * K / dt_e2e
+        if stream:  # the headline end-to-end figure is the streamed one; the single call stays beside it
+            dt_e2e = stream["dt"]
         e2e = total_docs * K / dt_e2e
         # roofline of the dominant kernel (device-resident run)
         dom = max(ktimes.items(), key=lambda kv: kv[1][0]) if ktimes else ("", (0.0, 0))
@@ -916,7 +999,12 @@ def main():
                     "d2h_bytes_per_step": n_docs * (2 + stats_bytes) + cbytes_e + 8 * (n_docs + 1), "text_gbs": total_bytes * K / dt_e2e / 1e9,
                     "ms_per_step": dt_e2e / K * 1e3,
                     "content": "runs + host gather" if e2e_runs_mode else "bytes",
-                    "host_gathered_bytes_per_step": last_keep.get("kept_bytes") if e2e_runs_mode else None},
+                    "host_gathered_bytes_per_step": last_keep.get("kept_bytes") if e2e_runs_mode else None,
+                    "api": ("StreamingRunner.run (textblaster_b200/runner.py): the step's %d row groups of %d documents streamed through %d pipelines of "
+                            "one context, %d gather threads each; results drained in row-group order; keep mask equal to the single call's"
+                            % (len(mine), min(GROUP_DOCS, args.docs), stream["pipelines"], stream["gather_threads"])) if stream
+                           else "tb_pipeline_run_batch: one call per step",
+                    "single_call": single_call if stream else None},
             "gpu_launches": launches,
             "roofline": {"bound": "hbm", "kernel": dom_name, "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak if peak else None, "traffic": ncu_traffic(dom_name, alg_bytes_step / launches_per_step), "peak_source": peak_src,
