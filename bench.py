@@ -444,6 +444,9 @@ def run_config3(args, rank):
             p = GpuBatchPipeline([GopherRepetitionParams(**{kind: [(order, 0.2 if kind == "top_n_grams" else 0.15)]})])
             if args.bulk_stage_tiles:
                 p.set_option(_abi.TB_OPT_BULK_STAGE_TILES, args.bulk_stage_tiles)
+            if args.chunk_ramp >= 0:
+                p.set_option(_abi.TB_OPT_CHUNK_RAMP, args.chunk_ramp)
+            p.set_option(_abi.TB_OPT_CHUNK_BYTES, args.chunk_mb << 20)
             for _ in range(max(args.warmup, 1)):
                 p.run_packed(utf8, off)
             p.reset_kernel_times()
@@ -683,6 +686,8 @@ def main():
                          "as equal row groups streamed through StreamingRunner with --pipelines pipelines per GPU (runner), or both and the faster "
                          "of the two as the figure, the other beside it (best, the default: the stream wins when the chain starts with the cheap C4 "
                          "passes, the single call when it starts with the repetition filter)")
+    ap.add_argument("--stream-group-docs", type=int, default=0, help="headline, streamed end-to-end figure: documents per row group (0: about %d)" % GROUP_DOCS)
+    ap.add_argument("--chunk-ramp", type=int, default=-1, help="TB_OPT_CHUNK_RAMP (-1: library default)")
     ap.add_argument("--gather-threads", type=int, default=0, help="host threads of TB_OPT_GATHER_KEPT (0: min(8, cpus / ranks))")
     ap.add_argument("--with-fineweb", action="store_true",
                     help="append FineWebQualityFilter (SURVEY 8(f) row 3) to the chain; not the headline workload")
@@ -870,7 +875,7 @@ def main():
         gt = (args.gather_threads or max(1, min(8, ((os.cpu_count() or 1) // world) // P))) if e2e_runs_mode else 0
         # the rank's documents as equal row groups of about GROUP_DOCS (a short last group would have the pipelines fall
         # out of step: the results are drained in order)
-        G = max(1, round(n_docs / min(GROUP_DOCS, args.docs)))
+        G = max(1, round(n_docs / min(args.stream_group_docs or GROUP_DOCS, args.docs)))
         bounds = [(n_docs * k // G, n_docs * (k + 1) // G) for k in range(G)]
 
         def make():

@@ -719,7 +719,10 @@ int run_impl(tb_pipeline* p, const uint8_t* utf8, const void* offsets, int is64,
     const int64_t C = std::max<int64_t>(p->opt_chunk, 1);
     // (a caller that streams batch after batch through several pipelines has the copies of one batch hidden behind the
     // kernels of another: no ramps then, TB_OPT_CHUNK_RAMP = 0)
-    const std::vector<int64_t> targets = p->opt_ramp ? tb_chunk_targets(total_bytes, C, device_input) : std::vector<int64_t>{C};
+    // (a chunk should hold some thousand documents whatever their length: a persistent kernel over a few hundred long
+    // documents leaves most of the GPU idle while the longest of them is worked off)
+    const int64_t floor_bytes = n_docs ? (int64_t)((double)total_bytes / (double)n_docs * 4096.0) : 0;
+    const std::vector<int64_t> targets = p->opt_ramp ? tb_chunk_targets(total_bytes, C, device_input, floor_bytes) : std::vector<int64_t>{C};
     size_t ti = 0;
     for (int64_t d = 0; d < n_docs;) {
       const int64_t b0 = off_at(offsets, is64, d);

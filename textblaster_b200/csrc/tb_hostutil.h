@@ -65,9 +65,12 @@ inline size_t tb_grown_bytes(int64_t nb, int64_t n) { return (size_t)nb + (size_
 // so a chunk ends up a little under its target).  Ramp up by doubling from 64 MiB (host input: the first copy to the
 // device is exposed) or 256 MiB (text already on the device), plateau at C, ramp down by thirds to 48 MiB (the
 // results of a chunk leave while the next, smaller one is computed).  The sizes sum to B.
-inline std::vector<int64_t> tb_chunk_targets(int64_t B, int64_t C, bool device_input) {
+// `floor_bytes`: no chunk smaller than this (a chunk of a few hundred long documents cannot fill the GPU: the caller
+// passes the size of some thousand average documents).
+inline std::vector<int64_t> tb_chunk_targets(int64_t B, int64_t C, bool device_input, int64_t floor_bytes = 0) {
   if (C < 1) C = 1;
-  const int64_t lo_up = std::min<int64_t>(C, (device_input ? 256ll : 64ll) << 20), lo_down = std::min<int64_t>(C, 48ll << 20);
+  const int64_t lo_up = std::min<int64_t>(C, std::max<int64_t>(floor_bytes, (device_input ? 256ll : 64ll) << 20)),
+                lo_down = std::min<int64_t>(C, std::max<int64_t>(floor_bytes, 48ll << 20));
   std::vector<int64_t> up, down;  // ramp sizes, smallest first
   for (int64_t v = lo_up; v < C; v *= 2) up.push_back(v);
   for (int64_t v = lo_down; v < C; v *= 3) down.push_back(v);

@@ -385,7 +385,7 @@ void tb_launch_gr_rep(cudaStream_t st, const KBatch& b, const int64_t* ts, const
   else if (tier == 3) k_gr_rep_c<3><<<sm_count * 4, tb_rep_threads(3), TB_REP_CTA_SMEM(tb_rep_cap(3)), st>>>(b, ts, te, s, cfg, step, out);
   else if (tier == 4) k_gr_rep_c<4><<<sm_count * 2, tb_rep_threads(4), TB_REP_CTA_SMEM(tb_rep_cap(4)), st>>>(b, ts, te, s, cfg, step, out);
   else if (tier == 5) k_gr_rep_c<5><<<sm_count, tb_rep_threads(5), TB_REP_CTA_SMEM(tb_rep_cap(5)), st>>>(b, ts, te, s, cfg, step, out);
-  else k_gr_rep_x<<<sm_count * 3, TB_REP_X_THREADS, 0, st>>>(b, ts, te, s, cfg, step, out);  // global-memory tables: several CTAs per SM hide the latency
+  else k_gr_rep_x<<<sm_count * TB_REP_X_PER_SM, TB_REP_X_THREADS, 0, st>>>(b, ts, te, s, cfg, step, out);  // global-memory tables: several CTAs per SM hide the latency
 }
 void tb_launch_fw_scan(cudaStream_t st, const KBatch& b, const FwCfg& cfg, const FwScratch& s, int sm_count, uint32_t* cursor) {
   if (b.n) k_fw_scan<<<persistent_grid(b.n, sm_count, 24), TB_BLOCK, 0, st>>>(b, cfg, s, cursor);

@@ -41,7 +41,12 @@ extern uint64_t tbe_stat_rep_words, tbe_stat_rep_items, tbe_stat_rep_pruned;  //
 extern uint64_t tbe_stat_rep_task_small, tbe_stat_rep_task_table;             // levels a warp of a CTA tier worked off alone: in registers / with a table
 #endif
 
+#ifndef TB_REP_X_THREADS
 #define TB_REP_X_THREADS 512
+#endif
+#ifndef TB_REP_X_PER_SM
+#define TB_REP_X_PER_SM 3
+#endif
 #define TB_REP_TASK_ITEMS 256u  // CTA tiers: up to this many pruned word ends, a warp works a whole level off by itself (capacity / 8 threads = capacity / 256 warps share the arrays)
 #define TB_REP_PRUNE_FROM 4u  // duplicate n-gram levels from this order on run over the signature candidates only
 #define TB_REP_SIG_MIN 6u     // ... if the shortest n-gram of the first such level has at least this many bytes
