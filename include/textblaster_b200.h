@@ -336,7 +336,8 @@ enum {
                                 (c4_filters.rs:192-258: lines trimmed, citations cut, kept lines joined by the '\n' in front of them), so
                                 a few (begin, end) pairs per document replace the bytes on the device->host link, and the caller (or
                                 tb_gather_content) copies the runs of the documents it writes out straight from its input column.  Falls
-                                back to 1 where the text C4 reads is not the caller's (entity pre-pass, split_paragraph = false) */
+                                back to 1 where the text C4 reads is not the caller's (entity pre-pass, split_paragraph = false, a chain with
+                                several C4 steps) */
   TB_OPT_VALIDATE_UTF8 = 2,  /* [0] check inputs on the device, TB_ERR_INVALID_UTF8 on failure */
   TB_OPT_CHUNK_BYTES = 3,    /* [1 GiB] largest chunk the batch is processed in (device scratch: ~45 bytes per byte of it) */
   TB_OPT_GENERAL_WORD_PATH = 4, /* [0] testing: run the segment-walking word passes for every document (same results, slower) */

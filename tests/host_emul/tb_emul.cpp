@@ -217,6 +217,9 @@ extern "C" int tbe_run_chain(const tb_step_cfg* steps, size_t n_steps, const uin
   };
   auto alive_pred = [&](int64_t d) { return alive[d] != 0; };
   bool has_c4 = false;
+  int n_c4 = 0, c4_seen = 0;
+  for (size_t s = 0; s < n_steps; s++) n_c4 += steps[s].type == TB_STEP_C4_QUALITY;
+  uint8_t* Fbuf[2] = {nullptr, nullptr};
   const uint32_t* runs_kf = nullptr; const int64_t* runs_frs = nullptr; const int64_t* runs_fre = nullptr;  // for the runs check below
   for (size_t s = 0; s < n_steps; s++) {
     const tb_step_cfg& sc = steps[s];
@@ -270,13 +273,16 @@ extern "C" int tbe_run_chain(const tb_step_cfg* steps, size_t n_steps, const uin
       uint32_t* ftab = G32(2 * TB_FW_SMEM_LINES);
       run_warps(n, alive_pred, [&](int64_t d, int lane) { body_fw_fin(b, ftab, f, fs, (int)s, (tb_fw_stats*)stats, d, lane); });
     } else if (sc.type == TB_STEP_C4_QUALITY) {
-      if (has_c4) return 5;
       C4Cfg cfg = tb_c4cfg_of(sc.u.c4);
       const bool sent = !sc.u.c4.split_paragraph;
+      if (n_c4 > 1 && sent) return 5;  // (several C4 steps: only with split_paragraph = true, as in tb_pipeline_create)
       const size_t cb = sent ? tb_grown_bytes(nb, n) : (size_t)nb, clines = cb + n1 + 1;
       const size_t bw = cb / 32 + 4;
-      C4Scratch cs{G8(cb + 64), G8(cb + 64), G64(n1), G32(n1), G32(n1), G32(clines), G32(clines), G32(clines),
-                   G64(n1), G64(n1), G64(n1), G64(n1), G32(4 * n1), G32(bw), G32(bw)};
+      // the C4 steps of a chain write the two output buffers in turn (a step reads the one before it), like enqueue_chain
+      if (!Fbuf[c4_seen & 1]) Fbuf[c4_seen & 1] = G8(cb + 64);
+      C4Scratch cs{G8(cb + 64), Fbuf[c4_seen & 1], G64(n1), G32(n1), G32(n1), G32(clines), G32(clines), G32(clines),
+                   G64(n1), G64(n1), G64(n1), G64(n1), G32(4 * n1), G32(bw), G32(bw), (uint8_t)(1 + (c4_seen & 1))};
+      c4_seen++;
       memset(cs.ka, 0, bw * 4); memset(cs.kf, 0, bw * 4);
       const KBatch b_in = b;
       if (sent) {  // one sentence per line into S (the launch sequence of enqueue_chain)
@@ -302,7 +308,7 @@ extern "C" int tbe_run_chain(const tb_step_cfg* steps, size_t n_steps, const uin
       b.rs = b_in.rs; b.re = b_in.re;
       b.text = cs.F;
       has_c4 = true;
-      if (!sent && !decode_entities) { runs_kf = cs.kf; runs_frs = cs.frs; runs_fre = cs.fre; }
+      if (!sent && !decode_entities && n_c4 == 1) { runs_kf = cs.kf; runs_frs = cs.frs; runs_fre = cs.fre; }
     } else {
       return 1;
     }
@@ -316,7 +322,7 @@ extern "C" int tbe_run_chain(const tb_step_cfg* steps, size_t n_steps, const uin
     for (int64_t d = 0; d < n; d++) { out_off[d] = acc; acc += len[d]; }
     out_off[n] = acc;
     run_warps(n, [&](int64_t) { return true; },
-              [&](int64_t d, int lane) { body_pack(text, rs0, b.text, rs, rewritten, out_off, content_out, d, lane); });
+              [&](int64_t d, int lane) { body_pack(text, rs0, has_c4 ? Fbuf[0] : b.text, Fbuf[1], rs, rewritten, out_off, content_out, d, lane); });
     memcpy(content_off_out, out_off, n1 * 8);
     if (runs_kf) {
       // TB_OPT_RETURN_CONTENT = 2: the runs of the input text (count, offsets, write, as enqueue_chain does) must

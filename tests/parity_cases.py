@@ -52,6 +52,10 @@ CHAINS = {
     "baseline_order": [C4_SHIPPED, GQ_DEFAULT_SW, GR_SHIPPED],      # BASELINE.json config 2 order
     "shipped_order": [GR_SHIPPED, GQ_SHIPPED, C4_SHIPPED],          # config/pipeline_config.yaml order
     "c4_then_open": [C4_ONE_SENT, GQ_OPEN, GR_OPEN],
+    # several C4 steps in one chain (the reference takes any list of steps, worker_logic.rs:39-134): each reads the
+    # output of the one before it; documents that drop out in between keep the content they had at that point
+    "c4_twice": [C4_LAX, GQ_SHIPPED, C4_ONE_SENT],
+    "c4_thrice": [C4_LAX, C4_NOPUNCT, GQ_SHIPPED, C4_SHIPPED, GR_OPEN],
 }
 
 

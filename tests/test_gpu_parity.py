@@ -594,3 +594,39 @@ def test_repeated_runs_are_identical():
                     for f in a.dtype.names:
                         assert np.array_equal(a[f][ran], b[f][ran]), f"{name}: run {it}, step {si}, field {f} differs"
         p.close()
+
+
+def test_streaming_runner_matches_oracle_and_single_call():
+    """textblaster_b200/runner.py on the GPU: row groups given as views of one column (absolute offsets) go through three
+    pipelines of one context, the kept documents' content rebuilt on the host; the summaries arrive in row-group order
+    and equal the oracle's result (and so the single call's) document by document, content included."""
+    from textblaster_b200.runner import RowGroup, StreamingRunner
+    utf8, off = synth.generate(24000, seed=77)
+    off = off.astype(np.int64)
+    steps = CHAINS["baseline_order"]
+    want = oracle.OraclePipeline(steps).run_packed(utf8, off, nthreads=os.cpu_count() or 1)
+    n = len(off) - 1
+    G = 7
+    bounds = [(n * k // G, n * (k + 1) // G) for k in range(G)]
+    runner = StreamingRunner(lambda: GpuBatchPipeline(steps), pipelines=3, copy_stats=True, gather_kept=2)
+    seen = []
+
+    def sink(index, s):
+        a, b = bounds[index % G]
+        seen.append(index)
+        assert np.array_equal(s.keep, want.keep[a:b]) and np.array_equal(s.failed_step, want.failed_step[a:b]), f"group {index}"
+        kept = np.nonzero(want.keep[a:b])[0]
+        assert len(s.kept_offsets) == len(kept) + 1
+        for j, d in enumerate(kept[:: max(1, len(kept) // 200)]):  # a sample of the kept documents, byte for byte
+            jj = int(np.searchsorted(kept, d))
+            got = bytes(s.kept_content[int(s.kept_offsets[jj]):int(s.kept_offsets[jj + 1])])
+            c = want.content(a + int(d))
+            assert got == (c.encode("utf-8") if isinstance(c, str) else bytes(c)), f"group {index}, document {a + int(d)}"
+        for si, t in enumerate(step_types(steps)):
+            ran = executed(want.failed_step[a:b], si)
+            for f in s.stats[si].dtype.names:
+                assert np.array_equal(s.stats[si][f][ran], want.stats[si][f][a:b][ran]), f"group {index}, step {si}, field {f}"
+
+    tot = runner.run((RowGroup(i, utf8, off[bounds[i % G][0]:bounds[i % G][1] + 1]) for i in range(2 * G)), sink)
+    runner.close()
+    assert seen == list(range(2 * G)) and tot.docs == 2 * n and tot.kept == 2 * int(want.keep.sum())

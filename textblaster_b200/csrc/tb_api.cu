@@ -237,6 +237,7 @@ struct tb_pipeline {
   DevBuf e_D, e_amp, e_drop, e_drs, e_dre;  // HTML entity pre-pass
   DevBuf c_S, c_bits, c_srs, c_sre;  // sentence-wise lines
   DevBuf c_ka, c_kf;                 // kept-byte bitmaps of passes A and C (tb_kernels.cuh C4Scratch)
+  DevBuf c_F2;                       // second C4 output buffer: the C4 steps of a chain write F and F2 in turn (a step reads the one before it)
   DevBuf c_P, c_F, c_plen, c_nlines, c_docflags, c_lwc, c_lmax, c_lflags, c_prs, c_pre, c_frs, c_fre, c_cnt;
   cudaEvent_t ev_h2d[2] = {nullptr, nullptr}, ev_done[2] = {nullptr, nullptr}, ev_d2h[2] = {nullptr, nullptr}, ev_small[2] = {nullptr, nullptr};
   std::vector<ResultSet*> results;
@@ -247,6 +248,7 @@ struct tb_pipeline {
   std::vector<KTime> ktimes;
   size_t ev_next = 0;
   int launches_this_run = 0;
+  int n_c4 = 0;  // C4QualityFilter steps in the chain
   double ms_this_run = 0;
 };
 
@@ -553,6 +555,7 @@ int ensure_chunk_buffers(tb_pipeline* p, int64_t n, int64_t nb, bool host_input)
     } else if (sh.type == TB_STEP_C4_QUALITY) {
       size_t lines = cb + n1 + 1;
       ENS(p->c_P, cb + 64); ENS(p->c_F, cb + 64);
+      if (p->n_c4 > 1) ENS(p->c_F2, cb + 64);
       ENS(p->c_ka, (cb / 32 + 4) * 4); ENS(p->c_kf, (cb / 32 + 4) * 4);
       if (sh.c4_sentences) { ENS(p->c_S, cb + 64); ENS(p->c_bits, (cb_in / 32 + 4) * 4); ENS(p->c_srs, n1 * 8); ENS(p->c_sre, n1 * 8); }
       ENS(p->c_plen, n1 * 8); ENS(p->c_nlines, n1 * 4); ENS(p->c_docflags, n1 * 4);
@@ -580,6 +583,7 @@ int enqueue_chain(tb_pipeline* p, const uint8_t* text, int64_t n, int64_t nbytes
            (uint32_t)p->opt_debug, p->order.as<uint32_t>(), cursors + 40, p->sizecls.as<uint8_t>(), (uint32_t)p->opt_bulk};
   { Timed t(p, "k_order"); tb_launch_order(st, p->rs0.as<int64_t>(), p->re0.as<int64_t>(), n, p->order.as<uint32_t>(), cursors + 40, p->sizecls.as<uint8_t>()); }
   *has_c4 = false;
+  int c4_seen = 0;
   if (p->opt_validate) {  // p->bad counts over the whole run (cleared by run_impl)
     { Timed t(p, "k_validate_utf8"); tb_launch_validate_utf8(st, text, b.rs, b.re, n, p->bad.as<int32_t>()); }
   }
@@ -613,10 +617,12 @@ int enqueue_chain(tb_pipeline* p, const uint8_t* text, int64_t n, int64_t nbytes
       { Timed t(p, "k_fw_scan"); tb_launch_fw_scan(st, b, sh.fw, fs, c->sm_count, cursors + s); }
       { Timed t(p, "k_fw_fin"); tb_launch_fw_fin(st, b, sh.fw, fs, (int)s, p->stats[s][pb].as<tb_fw_stats>(), c->sm_count, cursors + TB_MAX_STEPS + s); }
     } else {
-      C4Scratch cs{p->c_P.as<uint8_t>(), p->c_F.as<uint8_t>(), p->c_plen.as<int64_t>(), p->c_nlines.as<uint32_t>(),
+      uint8_t* const Fout = (c4_seen++ & 1) ? p->c_F2.as<uint8_t>() : p->c_F.as<uint8_t>();  // (never the buffer this step reads)
+      C4Scratch cs{p->c_P.as<uint8_t>(), Fout, p->c_plen.as<int64_t>(), p->c_nlines.as<uint32_t>(),
                    p->c_docflags.as<uint32_t>(), p->c_lwc.as<uint32_t>(), p->c_lmax.as<uint32_t>(), p->c_lflags.as<uint32_t>(),
                    p->c_prs.as<int64_t>(), p->c_pre.as<int64_t>(), p->c_frs.as<int64_t>(), p->c_fre.as<int64_t>(), p->c_cnt.as<uint32_t>(),
-                   p->c_ka.as<uint32_t>(), content_mode == 2 ? p->c_kf.as<uint32_t>() : nullptr};
+                   p->c_ka.as<uint32_t>(), content_mode == 2 ? p->c_kf.as<uint32_t>() : nullptr,
+                   (uint8_t)(Fout == p->c_F.as<uint8_t>() ? 1 : 2)};
       {  // the bitmaps are OR-ed into where two documents share a word
         const size_t bw = ((size_t)(sh.c4_sentences ? tb_grown_bytes(nbytes, n) : (size_t)nbytes) / 32 + 4) * 4;
         CK(cudaMemsetAsync(p->c_ka.p, 0, bw, st));
@@ -655,7 +661,7 @@ int enqueue_chain(tb_pipeline* p, const uint8_t* text, int64_t n, int64_t nbytes
   } else if (want_content) {  // a C4 step rewrote documents, or the entity pre-pass made `text` a copy of its own
     { Timed t(p, "k_final_len"); tb_launch_final_len(st, n, p->rs0.as<int64_t>(), p->re0.as<int64_t>(), b.rs, b.re, p->rewritten.as<uint8_t>(), p->len.as<int64_t>()); }
     { Timed t(p, "k_scan_i64"); tb_launch_scan_i64(st, p->len.as<int64_t>(), p->out_off[pb].as<int64_t>(), n); }
-    { Timed t(p, "k_pack"); tb_launch_pack(st, n, text, p->rs0.as<int64_t>(), b.text, b.rs, p->rewritten.as<uint8_t>(), p->out_off[pb].as<int64_t>(), p->packed[pb].as<uint8_t>()); }
+    { Timed t(p, "k_pack"); tb_launch_pack(st, n, text, p->rs0.as<int64_t>(), *has_c4 ? p->c_F.as<uint8_t>() : b.text, p->c_F2.as<uint8_t>(), b.rs, p->rewritten.as<uint8_t>(), p->out_off[pb].as<int64_t>(), p->packed[pb].as<uint8_t>()); }
   }
   CK(cudaGetLastError());
   return TB_OK;
@@ -680,7 +686,7 @@ int run_impl(tb_pipeline* p, const uint8_t* utf8, const void* offsets, int is64,
   // what comes back as the content: nothing, the bytes, or runs of the caller's own text.  Runs need the text C4 reads to
   // be the caller's (no entity pre-pass, lines = str::lines); otherwise the bytes are returned.
   int content_mode = (any_c4 || p->opt_decode) ? (int)p->opt_return_content : 0;
-  if (content_mode == 2 && (p->opt_decode || sent_mode || !any_c4)) content_mode = 1;
+  if (content_mode == 2 && (p->opt_decode || sent_mode || p->n_c4 != 1)) content_mode = 1;
   const bool want_content = content_mode != 0;
   const size_t esz = content_mode == 2 ? sizeof(tb_run) : 1;  // bytes per element of the content buffer
 
@@ -979,10 +985,15 @@ int tb_pipeline_create(tb_ctx* ctx, const tb_step_cfg* steps, size_t n_steps, tb
     if (rc) return rc;
     n_c4 += steps[i].type == TB_STEP_C4_QUALITY;
   }
-  if (n_c4 > 1) return fail(TB_ERR_UNSUPPORTED, "at most one C4QualityFilter step per pipeline");
+  if (n_c4 > 1) {  // several C4 steps: each reads the output of the one before it; sentence-wise lines grow the text, once
+    for (size_t i = 0; i < n_steps; i++)
+      if (steps[i].type == TB_STEP_C4_QUALITY && !steps[i].u.c4.split_paragraph)
+        return fail(TB_ERR_UNSUPPORTED, "several C4QualityFilter steps in one pipeline: only with split_paragraph = true");
+  }
   CK(cudaSetDevice(ctx->device));
   auto* p = new tb_pipeline();
   p->ctx = ctx;
+  p->n_c4 = n_c4;
   p->steps.resize(n_steps);
   for (size_t i = 0; i < n_steps; i++) {
     StepHost& sh = p->steps[i];
@@ -1037,7 +1048,7 @@ void tb_pipeline_destroy(tb_pipeline* p) {
   cudaDeviceSynchronize();
   for (DevBuf* b : {&p->text[0], &p->text[1], &p->offs[0], &p->offs[1], &p->packed[0], &p->packed[1], &p->rs0, &p->re0, &p->rs,
                     &p->re, &p->ts, &p->te, &p->alive[0], &p->alive[1], &p->failed[0], &p->failed[1], &p->rewritten, &p->len, &p->out_off[0], &p->out_off[1], &p->bad, &p->cursors, &p->order, &p->sizecls, &p->g_wh,
-                    &p->g_wl, &p->g_ws, &p->g_lh, &p->g_ll, &p->g_lg, &p->g_doc, &p->g_work, &p->g_lists, &p->g_counters, &p->f_lh, &p->f_ll, &p->f_doc, &p->f_tab, &p->e_D, &p->e_amp, &p->e_drop, &p->e_drs, &p->e_dre, &p->c_S, &p->c_bits, &p->c_srs, &p->c_sre, &p->c_ka, &p->c_kf, &p->c_P, &p->c_F, &p->c_plen, &p->c_nlines,
+                    &p->g_wl, &p->g_ws, &p->g_lh, &p->g_ll, &p->g_lg, &p->g_doc, &p->g_work, &p->g_lists, &p->g_counters, &p->f_lh, &p->f_ll, &p->f_doc, &p->f_tab, &p->e_D, &p->e_amp, &p->e_drop, &p->e_drs, &p->e_dre, &p->c_S, &p->c_bits, &p->c_srs, &p->c_sre, &p->c_ka, &p->c_kf, &p->c_P, &p->c_F, &p->c_F2, &p->c_plen, &p->c_nlines,
                     &p->c_docflags, &p->c_lwc, &p->c_lmax, &p->c_lflags, &p->c_prs, &p->c_pre, &p->c_frs, &p->c_fre, &p->c_cnt})
     b->release();
   for (auto& b : p->stats) { b[0].release(); b[1].release(); }

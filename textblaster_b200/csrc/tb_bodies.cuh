@@ -533,7 +533,7 @@ TB_D void body_c4_d(const KBatch& a, const uint16_t* s_ascii, const C4Cfg& cfg, 
   st.too_few_words = s.cnt[4 * d + 2]; st.n_kept_lines = s.cnt[4 * d + 3]; st.n_sentences = ns; st.rewritten = 1;
   if (cfg.min_num_sentences > 0 && (uint64_t)ns < cfg.min_num_sentences) st.reason_bits |= TB_C4_REASON_TOO_FEW_SENTENCES;
   out[d] = st;
-  rewritten[d] = 1;
+  rewritten[d] = s.ftag;
   rs_out[d] = R.rs; re_out[d] = R.re;
   if (st.reason_bits) { a.alive[d] = 0; a.failed[d] = (int8_t)step; }
 }
@@ -755,9 +755,9 @@ TB_D void body_final_len(const int64_t* rs0, const int64_t* re0, const int64_t* 
                          const uint8_t* rewritten, int64_t* len, int64_t d) {
   len[d] = rewritten[d] ? re[d] - rs[d] : re0[d] - rs0[d];
 }
-TB_D void body_pack(const uint8_t* orig, const int64_t* rs0, const uint8_t* cur, const int64_t* rs, const uint8_t* rewritten,
+TB_D void body_pack(const uint8_t* orig, const int64_t* rs0, const uint8_t* cur, const uint8_t* cur2, const int64_t* rs, const uint8_t* rewritten,
                     const int64_t* out_off, uint8_t* out, int64_t d, int lane) {
-  const uint8_t* src = rewritten[d] ? cur + rs[d] : orig + rs0[d];
+  const uint8_t* src = rewritten[d] == 2 ? cur2 + rs[d] : rewritten[d] ? cur + rs[d] : orig + rs0[d];  // (the buffer the document was last rewritten into)
   const int64_t o = out_off[d], len = out_off[d + 1] - o;
   uint8_t* dst = out + o;
 #if defined(__CUDA_ARCH__)

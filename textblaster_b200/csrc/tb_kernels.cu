@@ -330,11 +330,11 @@ __global__ void k_scan_i64(const int64_t* in, int64_t* out, int64_t n) {
   }
   if (threadIdx.x == 0) out[n] = s_carry;
 }
-__global__ void __launch_bounds__(TB_BLOCK) k_pack(int64_t n, const uint8_t* orig, const int64_t* rs0, const uint8_t* cur,
+__global__ void __launch_bounds__(TB_BLOCK) k_pack(int64_t n, const uint8_t* orig, const int64_t* rs0, const uint8_t* cur, const uint8_t* cur2,
                                                    const int64_t* rs, const uint8_t* rewritten, const int64_t* out_off,
                                                    uint8_t* out) {
   int64_t d = warp_doc();
-  if (d < n) body_pack(orig, rs0, cur, rs, rewritten, out_off, out, d, threadIdx.x & 31);
+  if (d < n) body_pack(orig, rs0, cur, cur2, rs, rewritten, out_off, out, d, threadIdx.x & 31);
 }
 
 inline int persistent_grid(int64_t n, int sm_count, int per_sm) {
@@ -448,7 +448,7 @@ void tb_launch_final_len(cudaStream_t st, int64_t n, const int64_t* rs0, const i
 void tb_launch_scan_i64(cudaStream_t st, const int64_t* in, int64_t* out, int64_t n) {
   k_scan_i64<<<1, 1024, 0, st>>>(in, out, n);
 }
-void tb_launch_pack(cudaStream_t st, int64_t n, const uint8_t* orig, const int64_t* rs0, const uint8_t* cur,
+void tb_launch_pack(cudaStream_t st, int64_t n, const uint8_t* orig, const int64_t* rs0, const uint8_t* cur, const uint8_t* cur2,
                     const int64_t* rs, const uint8_t* rewritten, const int64_t* out_off, uint8_t* out) {
-  if (n) k_pack<<<blocks_for_warps(n), TB_BLOCK, 0, st>>>(n, orig, rs0, cur, rs, rewritten, out_off, out);
+  if (n) k_pack<<<blocks_for_warps(n), TB_BLOCK, 0, st>>>(n, orig, rs0, cur, cur2, rs, rewritten, out_off, out);
 }

@@ -141,6 +141,7 @@ struct C4Scratch {
   // citations cut, '\n' kept except the document's last); kf = the byte is part of the joined kept lines (pass C,
   // before the final trim; only written when kf != NULL).  Words shared by two documents are OR-ed: zero them first.
   uint32_t* ka; uint32_t* kf;
+  uint8_t ftag = 1;    // what pass D writes into rewritten[d]: which of the two C4 output buffers F is (1, 2): the C4 steps of a chain write them in turn
 };
 // store the word of a stretch into such a bitmap (V: the bytes of the stretch that belong to this document)
 TB_D void tb_bits_store(uint32_t* bits, int64_t p0, uint32_t mis, uint32_t V, uint32_t K) {
@@ -186,5 +187,5 @@ void tb_launch_c4_runs(cudaStream_t st, int64_t n, const int64_t* rs0, const int
 void tb_launch_final_len(cudaStream_t st, int64_t n, const int64_t* rs0, const int64_t* re0, const int64_t* rs,
                          const int64_t* re, const uint8_t* rewritten, int64_t* len);
 void tb_launch_scan_i64(cudaStream_t st, const int64_t* in, int64_t* out, int64_t n);  // out[n] = total
-void tb_launch_pack(cudaStream_t st, int64_t n, const uint8_t* orig, const int64_t* rs0, const uint8_t* cur,
+void tb_launch_pack(cudaStream_t st, int64_t n, const uint8_t* orig, const int64_t* rs0, const uint8_t* cur, const uint8_t* cur2,
                     const int64_t* rs, const uint8_t* rewritten, const int64_t* out_off, uint8_t* out);
