@@ -8,12 +8,12 @@ timeout 300 python bench.py > gpurun_out/r02_bench_n1.json 2> gpurun_out/r02_ben
 timeout 300 python bench.py --impl reference > gpurun_out/r02_bench_reference.json 2>/dev/null; echo "reference rc=$?"
 timeout 300 python bench.py --content bytes --no-cpu-baseline > gpurun_out/r02_bench_n1_bytes.json 2>/dev/null
 timeout 300 python bench.py --order shipped --no-cpu-baseline > gpurun_out/r02_bench_n1_shipped_order.json 2>/dev/null
-timeout 300 python bench.py --steps 2 --warmup 1 --no-cpu-baseline > gpurun_out/r02_plain.json 2> gpurun_out/r02_plain.err && \
+timeout 300 python bench.py --steps 2 --warmup 1 --no-cpu-baseline --e2e-api call > gpurun_out/r02_plain.json 2> gpurun_out/r02_plain.err && \
   timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 3000 --csv --log-file gpurun_out/r02_launches.csv \
-      python bench.py --steps 2 --warmup 1 --no-cpu-baseline > gpurun_out/r02_ncu_run.log 2>&1
+      python bench.py --steps 2 --warmup 1 --no-cpu-baseline --e2e-api call > gpurun_out/r02_ncu_run.log 2>&1
 echo "launch list rc=$?"
-timeout 300 python bench.py --docs 200000 --steps 1 --warmup 1 --no-cpu-baseline > gpurun_out/r02_plain2.json 2> gpurun_out/r02_plain2.err && \
+timeout 300 python bench.py --docs 200000 --steps 1 --warmup 1 --no-cpu-baseline --e2e-api call > gpurun_out/r02_plain2.json 2> gpurun_out/r02_plain2.err && \
   timeout 900 ncu --set full --clock-control none --import-source on -k regex:"k_gr_rep_w|k_gr_rep_c|k_gr_scan|k_gq|k_c4_b|k_c4_a" -c 10 \
-      -o gpurun_out/r02_full_top4 python bench.py --docs 200000 --steps 1 --warmup 1 --no-cpu-baseline > gpurun_out/r02_ncu_full.log 2>&1
+      -o gpurun_out/r02_full_top4 python bench.py --docs 200000 --steps 1 --warmup 1 --no-cpu-baseline --e2e-api call > gpurun_out/r02_ncu_full.log 2>&1
 echo "full capture rc=$?"
 ls -la gpurun_out | tail -20
