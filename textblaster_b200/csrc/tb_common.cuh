@@ -149,6 +149,14 @@ TB_HD uint32_t tb_am(uint32_t a, uint32_t b) {  // a, b <= p -> <= p
   uint32_t x = a + b;
   return (x & TB_P31) + (x >> 31);
 }
+// bring the cache line of p towards L1 (no register, no wait); nothing on the host
+TB_HD void tb_prefetch(const void* p) {
+#if defined(__CUDA_ARCH__)
+  asm volatile("prefetch.global.L1 [%0];" ::"l"(p));
+#else
+  (void)p;
+#endif
+}
 TB_HD uint32_t tb_canon31(uint32_t x) { return x == TB_P31 ? 0u : x; }
 
 struct Hash2 {

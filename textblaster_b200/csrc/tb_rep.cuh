@@ -439,6 +439,9 @@ TB_D void rep_dup_small(const uint64_t* wh, const uint32_t* woff, const uint64_t
                         uint32_t ndup_max, uint64_t dup_levels, int lane, Sink sink) {
   const uint32_t NONE = 0xFFFFFFFFu;
   const bool holder = (uint32_t)lane < items;
+  // every level reaches one word further back from e: the ten or so word hashes an item needs over all levels sit in one
+  // or two cache lines, asked for now so that the levels' loads find them in L1
+  if (holder) { tb_prefetch(wh + (e + 1u >= ndup_max ? e + 1u - ndup_max : 0u)); tb_prefetch(wh + e); }
   uint32_t dcur = 0;
   Hash2 h; h.init();
 #pragma unroll 1
@@ -489,6 +492,7 @@ template <class Sink>
 TB_D void rep_top_small(const uint64_t* wh, const uint32_t* woff, const uint64_t* powtab, uint32_t i, Hash2 h, uint32_t count, uint32_t cur,
                         uint32_t ntop_max, uint64_t top_levels, uint32_t W, int lane, Sink sink) {
   bool valid = (uint32_t)lane < count;
+  if (valid) { tb_prefetch(wh + i + cur); tb_prefetch(wh + (i + ntop_max < W ? i + ntop_max : W - 1u)); }  // the words the levels will append
 #pragma unroll 1
   for (uint32_t n = cur + 1; n <= ntop_max; n++) {
     if (!((top_levels >> n) & 1ull)) continue;
@@ -593,7 +597,7 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
     // byte offsets of the words in the concatenation: the lengths come into place first (coalesced, the loads in flight
     // together), then every thread sums a run of consecutive words, one prefix sum over the threads, and the run is
     // rewritten as offsets
-#pragma unroll 4
+#pragma unroll 8
     for (uint32_t i = g.tid; i < W; i += g.size()) A.woff[i + 1] = TB_LDG(wl_g + i);
     g.sync();
     const uint32_t per = (W + (uint32_t)g.size() - 1u) / (uint32_t)g.size();
