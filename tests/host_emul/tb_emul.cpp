@@ -177,7 +177,7 @@ extern "C" int tbe_run_chain(const tb_step_cfg* steps, size_t n_steps, const uin
   const size_t n1 = (size_t)n + 1, cbx = any_sent ? tb_grown_bytes(nb, n) : (size_t)nb;
   const size_t wunits = tb_word_units(cbx, (size_t)n), units = tb_line_units(cbx, (size_t)n);
   // tables
-  std::vector<uint64_t> pw(TB_POWTAB);
+  std::vector<uint64_t> pw(TB_POWTAB_ALL);
   tb_fill_powtab(pw.data(), TB_B1_DEFAULT, TB_B2_DEFAULT);
   UcTables uc{tb_uc_stage1, tb_uc_stage2, &tb_uc_lower[0][0], &tb_uc_cased[0][0], &tb_uc_caseign[0][0], pw.data(),
               TB_UC_NLOWER, TB_UC_NCASED, TB_UC_NCASEIGN, {0}};
@@ -241,6 +241,7 @@ extern "C" int tbe_run_chain(const tb_step_cfg* steps, size_t n_steps, const uin
       g.dup_line_frac = q.dup_line_frac; g.dup_para_frac = q.dup_para_frac;
       g.dup_line_char_frac = q.dup_line_char_frac; g.dup_para_char_frac = q.dup_para_char_frac;
       for (int k = 0; k < TB_MAX_NGRAMS; k++) { g.top_n[k] = q.top_n[k]; g.top_frac[k] = q.top_frac[k]; g.dup_n[k] = q.dup_n[k]; g.dup_frac[k] = q.dup_frac[k]; }
+      tb_grcfg_finish(g);
       GrScratch gs{(uint64_t*)G64(wunits), G32(wunits), (uint64_t*)G64(wunits), (uint64_t*)G64(units), G32(units), G8(units),
                    (GrDoc*)G8(n1 * sizeof(GrDoc)), G32(wunits * TB_REP_K + n1 * TB_REP_DOC_EXTRA), G32(TB_REP_NT * n1), G32(TB_GR_COUNTERS), n};
       memset(gs.counters, 0, TB_GR_COUNTERS * 4);

@@ -948,7 +948,7 @@ int tb_ctx_create(int device, tb_ctx** out) {
       (rc = upload(c->t_caseign, tb_uc_caseign, sizeof tb_uc_caseign))) { delete c; return rc; }
   // the two bases of the string hashes, drawn per context (TB_HASH_SEED fixes them for a reproducible run): an input
   // cannot be built to collide under bases it does not know, and the collision bound of tb_common.cuh is over this draw
-  std::vector<uint64_t> pw(TB_POWTAB);
+  std::vector<uint64_t> pw(TB_POWTAB_ALL);
   {
     uint64_t seed;
     if (const char* e = getenv("TB_HASH_SEED")) seed = strtoull(e, nullptr, 0);
@@ -1023,6 +1023,7 @@ int tb_pipeline_create(tb_ctx* ctx, const tb_step_cfg* steps, size_t n_steps, tb
       g.dup_line_frac = q.dup_line_frac; g.dup_para_frac = q.dup_para_frac;
       g.dup_line_char_frac = q.dup_line_char_frac; g.dup_para_char_frac = q.dup_para_char_frac;
       for (int k = 0; k < TB_MAX_NGRAMS; k++) { g.top_n[k] = q.top_n[k]; g.top_frac[k] = q.top_frac[k]; g.dup_n[k] = q.dup_n[k]; g.dup_frac[k] = q.dup_frac[k]; }
+      tb_grcfg_finish(g);
       sh.gr = g;
     }
   }

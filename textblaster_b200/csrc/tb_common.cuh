@@ -49,11 +49,12 @@ struct UcTables {
   const uint32_t* lower;    // [n_lower][2] sorted by code point
   const uint32_t* cased;    // [n_cased][2] ranges [a,b)
   const uint32_t* caseign;  // [n_caseign][2]
-  const uint64_t* powtab;   // [TB_POWTAB] packed B^k for both moduli
+  const uint64_t* powtab;   // [TB_POWTAB_ALL] packed B^k for both moduli, k <= 1024, then B^(1024 k), k = 1 .. 1024
   int n_lower, n_cased, n_caseign;
   uint32_t wslead[8];       // bit b: some non-ASCII White_Space character starts with byte b (tb_compute_wslead)
 };
 #define TB_POWTAB 1025
+#define TB_POWTAB_ALL (TB_POWTAB + 1024)  // + the coarse table: entry TB_POWTAB - 1 + k = B^(1024 k), k = 1 .. 1024
 
 #if defined(__CUDA_ARCH__)
 #define TB_LDG(p) __ldg(p)
@@ -186,7 +187,15 @@ TB_HD_NOINLINE uint64_t tb_pow_long(const uint64_t* powtab, uint64_t len) {
   }
   return ((uint64_t)ra << 32) | rb;
 }
-TB_HD uint64_t tb_pow_pack(const uint64_t* powtab, uint64_t len) { return len < TB_POWTAB ? TB_LDG(powtab + len) : tb_pow_long(powtab, len); }
+// (lengths up to a megabyte -- long lines, paragraphs -- from two table entries and one multiplication per modulus)
+TB_HD uint64_t tb_pow_pack(const uint64_t* powtab, uint64_t len) {
+  if (len < TB_POWTAB) return TB_LDG(powtab + len);
+  if (len < (1024ull << 10)) {
+    const uint64_t hi = TB_LDG(powtab + (TB_POWTAB - 1) + (len >> 10)), lo = TB_LDG(powtab + (len & 1023u));
+    return ((uint64_t)tb_mm((uint32_t)(hi >> 32), (uint32_t)(lo >> 32)) << 32) | tb_mm((uint32_t)hi, (uint32_t)lo);
+  }
+  return tb_pow_long(powtab, len);
+}
 // ---- suffix signature of a byte string: its last 16 bytes, four bits of each, the last byte in the low nibble
 // (a string shorter than 16 bytes leaves the upper nibbles zero).  Equal strings have equal signatures, and so
 // do their suffixes of any common length k <= 16 (mask with tb_sig_mask(k)): the repetition pass uses that as a
@@ -195,10 +204,14 @@ TB_HD uint64_t tb_sig_push(uint64_t s, uint32_t byte) { return (s << 4) | (uint6
 TB_HD uint64_t tb_sig_cat(uint64_t x, uint64_t y, uint32_t ylen) { return ylen >= 16u ? y : (y | (x << (4u * ylen))); }  // x followed by y
 TB_HD uint64_t tb_sig_mask(uint32_t k) { return k >= 16u ? ~0ull : ((1ull << (4u * k)) - 1ull); }
 
-// the power table of a pair of bases: out[k] = (B1^k mod p) << 32 | (B2^k mod p), k < TB_POWTAB
+// the power table of a pair of bases: out[k] = (B1^k mod p) << 32 | (B2^k mod p), k < TB_POWTAB; out has TB_POWTAB_ALL entries
 TB_HD void tb_fill_powtab(uint64_t* out, uint32_t b1, uint32_t b2) {
   uint32_t a = 1, b = 1;
   for (int i = 0; i < TB_POWTAB; i++) { out[i] = ((uint64_t)a << 32) | b; a = tb_mm(a, b1); b = tb_mm(b, b2); }
+  // the coarse table: powers of B^1024
+  const uint32_t s1 = (uint32_t)(out[1024] >> 32), s2 = (uint32_t)out[1024];
+  a = s1; b = s2;
+  for (int k = 1; k <= 1024; k++) { out[TB_POWTAB - 1 + k] = ((uint64_t)a << 32) | b; a = tb_mm(a, s1); b = tb_mm(b, s2); }
 }
 TB_HD uint64_t tb_mix64(uint64_t x) {  // splitmix64 finaliser, for table slot selection only
   x ^= x >> 30; x *= 0xBF58476D1CE4E5B9ull; x ^= x >> 27; x *= 0x94D049BB133111EBull; x ^= x >> 31;

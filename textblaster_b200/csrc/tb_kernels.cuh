@@ -48,7 +48,15 @@ struct GrCfg {
   double top_frac[TB_MAX_NGRAMS];
   uint32_t dup_n[TB_MAX_NGRAMS];
   double dup_frac[TB_MAX_NGRAMS];
+  // derived once per pipeline (tb_grcfg_finish): largest configured order and the set of configured orders per list
+  uint32_t ntop_max, ndup_max;
+  uint64_t top_levels, dup_levels;  // bit n: some entry asks for n-grams of n words (n <= TB_MAX_NGRAM_N)
 };
+inline void tb_grcfg_finish(GrCfg& c) {
+  c.ntop_max = c.ndup_max = 0; c.top_levels = c.dup_levels = 0;
+  for (int k = 0; k < c.n_top; k++) { if (c.top_n[k] > c.ntop_max) c.ntop_max = c.top_n[k]; c.top_levels |= 1ull << c.top_n[k]; }
+  for (int k = 0; k < c.n_dup; k++) { if (c.dup_n[k] > c.ndup_max) c.ndup_max = c.dup_n[k]; c.dup_levels |= 1ull << c.dup_n[k]; }
+}
 
 // per-document result of the repetition scan pass
 struct GrDoc {

@@ -82,7 +82,7 @@ int setup_device(int dev, DeviceState** out) {
       if (cudaMemcpy(d, src, bytes, cudaMemcpyHostToDevice) != cudaSuccess) return nullptr;
       return d;
     };
-    uint64_t pw[TB_POWTAB];
+    uint64_t pw[TB_POWTAB_ALL];
     tb_fill_powtab(pw, TB_B1_DEFAULT, TB_B2_DEFAULT);  // (a fixed pair: this entry point keeps no per-process state beyond the scratch)
     unsigned char* s1 = place(tb_uc_stage1, sizeof tb_uc_stage1);
     unsigned char* s2 = place(tb_uc_stage2, sizeof tb_uc_stage2);
@@ -191,6 +191,7 @@ int tb_gopher_repetition_noalloc(const uint8_t* utf8_dev, const int64_t* offsets
   cfg.dup_line_frac = params->dup_line_frac; cfg.dup_para_frac = params->dup_para_frac;
   cfg.dup_line_char_frac = params->dup_line_char_frac; cfg.dup_para_char_frac = params->dup_para_char_frac;
   for (int k = 0; k < TB_MAX_NGRAMS; k++) { cfg.top_n[k] = params->top_n[k]; cfg.top_frac[k] = params->top_frac[k]; cfg.dup_n[k] = params->dup_n[k]; cfg.dup_frac[k] = params->dup_frac[k]; }
+  tb_grcfg_finish(cfg);
 
   // state that must start at zero: tier list lengths and work cursors (the array keeps the last call's contents)
   if (cudaMemsetAsync(g.counters, 0, 256, stream) != cudaSuccess) { cudaGetLastError(); return fail(TB_ERR_CUDA, "cudaMemsetAsync failed"); }

@@ -60,6 +60,7 @@ struct WarpGroup {
   TB_D uint32_t sum(uint32_t v) const { return simt_sum(v); }
   TB_D uint64_t sum64(uint64_t v) const { return simt_sum64(v); }
   TB_D uint64_t max64(uint64_t v) const { return simt_max64(v); }
+  TB_D uint32_t max32(uint32_t v) const { return simt_max(v); }
   TB_D bool any(bool p) const { simt_sync(); return simt_any(p); }  // also a barrier with memory ordering, like the CTA's
   TB_D uint32_t exscan(uint32_t v, uint32_t* total) const { return simt_exscan(v, tid, total); }
   TB_D uint32_t bcast(uint32_t v) const { return simt_shfl(v, 0); }
@@ -95,6 +96,7 @@ struct BlockGroup {
     const int lane = tid & 31, nw = (int)blockDim.x >> 5;
     return simt_max64(lane < nw ? r[lane] : 0ull);
   }
+  TB_D uint32_t max32(uint32_t v) const { return (uint32_t)max64(v); }
   TB_D bool any(bool p) const { return __syncthreads_or(p ? 1 : 0) != 0; }
   TB_D uint32_t exscan(uint32_t v, uint32_t* total) const {
     uint32_t wt, pre = simt_exscan(v, tid & 31, &wt);
@@ -133,6 +135,7 @@ struct BlockGroup {
     uint64_t s = 0; for (int i = 0; i < b->n; i++) s = b->box[i] > s ? b->box[i] : s;
     b->bar.arrive_and_wait(); return s;
   }
+  TB_D uint32_t max32(uint32_t v) const { return (uint32_t)max64(v); }
   TB_D bool any(bool p) const { return sum64(p ? 1 : 0) != 0; }
   TB_D uint32_t exscan(uint32_t v, uint32_t* total) const {
     SimtBlock* b = simt_block; b->box[tid] = v; b->bar.arrive_and_wait();
@@ -155,7 +158,9 @@ struct BlockGroup {
 
 // num / den > thr in double precision (the reference's f64 comparison); out of line: a double division is some forty
 // instructions and the repetition pass has a dozen of them, all rarely on the critical path
-TB_HD_NOINLINE bool rep_frac_gt(uint64_t num, double den, double thr) { return (double)num / den > thr; }
+TB_HD_NOINLINE bool rep_frac_gt_slow(uint64_t num, double den, double thr) { return (double)num / den > thr; }
+// (most numerators are zero -- nothing repeated -- and 0 / den is +0.0 for the positive denominators used here: no division then)
+TB_HD bool rep_frac_gt(uint64_t num, double den, double thr) { return num == 0 ? 0.0 > thr : rep_frac_gt_slow(num, den, thr); }
 
 // ---- tables ----------------------------------------------------------------------------------
 template <class IdxT> struct IdxTraits;
@@ -369,7 +374,7 @@ TB_D void rep_lines_small(const uint64_t* lh, const uint32_t* ll, const uint8_t*
   Hash2 v = tb_unpack(myline);
   uint32_t vl = mylen, f = head ? 1u : 0u;
 #pragma unroll 1
-  for (int off = 1; off < 32; off <<= 1) {
+  for (int off = 1; off < (int)NL; off <<= 1) {  // (no piece has more than NL - 1 pieces before it)
     const uint32_t ua = simt_shfl_up(v.a, off), ub = simt_shfl_up(v.b, off), ul = simt_shfl_up(vl, off), uf = simt_shfl_up(f, off);
     if (lane >= off && !f && holder) {
       Hash2 x; x.a = ua; x.b = ub;
@@ -585,12 +590,8 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
 
   REP_PROF(1)  // lines and paragraphs
   // ---- n-grams (gopher_rep.rs:159-196)
-  uint32_t ntop_max = 0, ndup_max = 0;
-  uint64_t top_levels = 0, dup_levels = 0;  // bit n: some entry of the list asks for n-grams of n words (n <= TB_MAX_NGRAM_N)
-#pragma unroll 1
-  for (int k = 0; k < cfg.n_top; k++) { ntop_max = cfg.top_n[k] > ntop_max ? cfg.top_n[k] : ntop_max; top_levels |= 1ull << cfg.top_n[k]; }
-#pragma unroll 1
-  for (int k = 0; k < cfg.n_dup; k++) { ndup_max = cfg.dup_n[k] > ndup_max ? cfg.dup_n[k] : ndup_max; dup_levels |= 1ull << cfg.dup_n[k]; }
+  uint32_t ntop_max = cfg.ntop_max, ndup_max = cfg.ndup_max;
+  const uint64_t top_levels = cfg.top_levels, dup_levels = cfg.dup_levels;  // bit n: some entry of the list asks for n-grams of n words
   if (ntop_max > W) ntop_max = W;
   if (ndup_max > W) ndup_max = W;
   if (ntop_max || ndup_max) {
@@ -768,7 +769,7 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
         uint32_t m = 0xFFFFFFFFu;
 #pragma unroll 1
         for (uint32_t i = g.tid; i + n <= W; i += g.size()) { const uint32_t v = woff[i + n] - woff[i]; m = v < m ? v : m; }
-        m = 0xFFFFFFFFu - (uint32_t)g.max64((uint64_t)(0xFFFFFFFFu - m));
+        m = 0xFFFFFFFFu - g.max32(0xFFFFFFFFu - m);
         const uint32_t k = m < 16u ? m : 16u;
         REP_PROF(15)
         if (k >= TB_REP_SIG_MIN) {

@@ -143,9 +143,10 @@ TB_D uint64_t simt_sum64(uint64_t v) {
   for (int o = 16; o; o >>= 1) v += simt_shfl_xor(v, o);
   return v;
 }
-TB_D uint64_t simt_max64(uint64_t v) {
-  for (int o = 16; o; o >>= 1) { uint64_t x = simt_shfl_xor(v, o); v = x > v ? x : v; }
-  return v;
+TB_D uint64_t simt_max64(uint64_t v) {  // two 32-bit reductions: the largest high word, then the largest low word among its holders
+  const uint32_t hi = simt_max((uint32_t)(v >> 32));
+  const uint32_t lo = simt_max((uint32_t)(v >> 32) == hi ? (uint32_t)v : 0u);
+  return ((uint64_t)hi << 32) | lo;
 }
 TB_D int64_t simt_shfl_up64(int64_t v, int o) {
   uint32_t lo = simt_shfl_up((uint32_t)(uint64_t)v, o), hi = simt_shfl_up((uint32_t)((uint64_t)v >> 32), o);
