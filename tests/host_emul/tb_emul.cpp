@@ -245,6 +245,7 @@ extern "C" int tbe_run_chain(const tb_step_cfg* steps, size_t n_steps, const uin
       GrScratch gs{(uint64_t*)G64(wunits), G32(wunits), (uint64_t*)G64(wunits), (uint64_t*)G64(units), G32(units), G8(units),
                    (GrDoc*)G8(n1 * sizeof(GrDoc)), G32(wunits * TB_REP_K + n1 * TB_REP_DOC_EXTRA), G32(TB_REP_NT * n1), G32(TB_GR_COUNTERS), n};
       memset(gs.counters, 0, TB_GR_COUNTERS * 4);
+      memset(stats, 0, (size_t)n * sizeof(tb_gr_stats));  // (pass 2 writes the non-zero fields only)
       for (int64_t d = 0; d < n; d++) body_trim(b, ascii, ts, te, d);
       build_lut(TB_LUT_GR, 0u);
       uint32_t* stage = (uint32_t*)G64(TB_GR_STAGE_U32 / 2 + 1);

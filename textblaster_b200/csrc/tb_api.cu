@@ -598,6 +598,7 @@ int enqueue_chain(tb_pipeline* p, const uint8_t* text, int64_t n, int64_t nbytes
                   p->g_lg.as<uint8_t>(), p->g_doc.as<GrDoc>(), p->g_work.as<uint32_t>(), p->g_lists.as<uint32_t>(),
                   p->g_counters.as<uint32_t>(), n};
       CK(cudaMemsetAsync(p->g_counters.p, 0, TB_GR_COUNTERS * 4, st));
+      CK(cudaMemsetAsync(p->stats[s][pb].p, 0, (size_t)n * sizeof(tb_gr_stats), st));  // pass 2 writes the non-zero fields only
       { Timed t(p, "k_trim"); tb_launch_trim(st, b, p->ts.as<int64_t>(), p->te.as<int64_t>()); }
       { Timed t(p, "k_gr_scan"); tb_launch_gr_scan(st, b, p->ts.as<int64_t>(), p->te.as<int64_t>(), g, c->sm_count); }
       // the few documents of tier X (each a long chain of passes on one CTA) run beside the other tiers

@@ -194,7 +194,10 @@ int tb_gopher_repetition_noalloc(const uint8_t* utf8_dev, const int64_t* offsets
   tb_grcfg_finish(cfg);
 
   // state that must start at zero: tier list lengths and work cursors (the array keeps the last call's contents)
-  if (cudaMemsetAsync(g.counters, 0, 256, stream) != cudaSuccess) { cudaGetLastError(); return fail(TB_ERR_CUDA, "cudaMemsetAsync failed"); }
+  if (cudaMemsetAsync(g.counters, 0, 256, stream) != cudaSuccess ||
+      cudaMemsetAsync(stats_dev, 0, (size_t)n_docs * sizeof(tb_gr_stats), stream) != cudaSuccess) {  // (pass 2 writes the non-zero fields only)
+    cudaGetLastError(); return fail(TB_ERR_CUDA, "cudaMemsetAsync failed");
+  }
   // keep_dev doubles as the kernels' "alive" flag: 1 for every document whose offsets are usable
   k_noalloc_ranges<<<1, 1024, 0, stream>>>(offsets_dev, n_docs, n_bytes, rs, re, keep_dev, failed, stats_dev);
   tb_launch_order(stream, rs, re, n_docs, order, g.counters + TB_GR_COUNTERS, sizecls);

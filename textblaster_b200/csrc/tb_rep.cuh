@@ -183,6 +183,12 @@ TB_D uint32_t rep_slot(uint64_t key, uint32_t T) {  // the two residues are alre
   h ^= h >> 15;
   return (uint32_t)(((uint64_t)h * T) >> 32);
 }
+// slot for a key that is not a hash (the suffix signatures: four bits of each byte): the top half of one 64-bit product
+// depends on every bit of the key
+TB_D uint32_t rep_slot_raw(uint64_t key, uint32_t T) {
+  const uint32_t h = (uint32_t)((key * 0x9E3779B97F4A7C15ull) >> 32);
+  return (uint32_t)(((uint64_t)h * T) >> 32);
+}
 TB_D uint32_t rep_next(uint32_t sl, uint32_t T) { return sl + 1 == T ? 0u : sl + 1; }
 template <class G>
 TB_D void rep_fill(const G& g, uint32_t* a, uint32_t n, uint32_t v) {
@@ -535,13 +541,12 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
   const uint32_t EMPTY = 0xFFFFFFFFu;
   const GrDoc gd = s.doc[d];
   REP_PROF_BEGIN(sizeof(IdxT) == 4 ? TB_REP_TIER_X : (int)tb_rep_tier(gd.W > gd.NL ? gd.W : gd.NL))
-  tb_gr_stats st;
-  st.reason_bits = 0; st.flags = gd.flags; st.char_len = gd.char_len; st.n_paras = 0; st.para_dup_elems = 0; st.para_dup_bytes = 0;
-  st.n_lines = 0; st.line_dup_elems = 0; st.line_dup_bytes = 0; st.n_words = 0;
-#pragma unroll 1
-  for (int k = 0; k < TB_MAX_NGRAMS; k++) { st.top_bytes[k] = 0; st.dup_bytes[k] = 0; }
+  // The document's record was zeroed before the pass (the caller clears the statistics of a chunk): thread 0 writes the
+  // fields that are not zero straight into it -- no 248-byte copy of the record in every thread's local memory.
+  tb_gr_stats* const o = out + d;
+  const bool writer = g.tid == 0;
   if (gd.empty) {  // gopher_rep.rs:60-74
-    if (g.tid == 0) { st.reason_bits = TB_GR_REASON_EMPTY; out[d] = st; a.alive[d] = 0; a.failed[d] = (int8_t)step; }
+    if (writer) { o->reason_bits = TB_GR_REASON_EMPTY; o->flags = gd.flags; o->char_len = gd.char_len; a.alive[d] = 0; a.failed[d] = (int8_t)step; }
     return;
   }
   const int64_t rs = ts[d];
@@ -560,8 +565,10 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
     if (g.tid < 32) {
       uint32_t pde; uint64_t pdb;
       rep_lines_small(lh, ll, lg, NL, a.uc.powtab, g.tid, &de, &db, &NP, &pde, &pdb);
-      st.n_lines = NL; st.line_dup_elems = de; st.line_dup_bytes = db;
-      st.n_paras = NP; st.para_dup_elems = pde; st.para_dup_bytes = pdb;
+      if (writer) {
+        o->n_lines = NL; o->line_dup_elems = de; o->line_dup_bytes = db;
+        o->n_paras = NP; o->para_dup_elems = pde; o->para_dup_bytes = pdb;
+      }
       if ((cfg.has & TB_GR_HAS_DUP_PARA_FRAC) && rep_frac_gt(pde, (double)(NP ? NP : 1u), cfg.dup_para_frac)) reasons |= TB_GR_REASON_DUP_PARA_FRAC;
       if ((cfg.has & TB_GR_HAS_DUP_PARA_CHAR_FRAC) && rep_frac_gt(pdb, text_char_len, cfg.dup_para_char_frac)) reasons |= TB_GR_REASON_DUP_PARA_CHAR_FRAC;
       if ((cfg.has & TB_GR_HAS_DUP_LINE_FRAC) && rep_frac_gt(de, (double)(NL ? NL : 1u), cfg.dup_line_frac)) reasons |= TB_GR_REASON_DUP_LINE_FRAC;
@@ -569,7 +576,7 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
     }
   } else {
   rep_dedup(g, tab, lh, ll, NL, &de, &db);
-  st.n_lines = NL; st.line_dup_elems = de; st.line_dup_bytes = db;
+  if (writer) { o->n_lines = NL; o->line_dup_elems = de; o->line_dup_bytes = db; }
   {
     if ((cfg.has & TB_GR_HAS_DUP_LINE_FRAC) && rep_frac_gt(de, (double)(NL ? NL : 1u), cfg.dup_line_frac)) reasons |= TB_GR_REASON_DUP_LINE_FRAC;
     if ((cfg.has & TB_GR_HAS_DUP_LINE_CHAR_FRAC) && rep_frac_gt(db, text_char_len, cfg.dup_line_char_frac)) reasons |= TB_GR_REASON_DUP_LINE_CHAR_FRAC;
@@ -580,7 +587,7 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
   NP = g.bcast(NP);
   g.sync();
   rep_dedup(g, tab, A.H, A.woff, NP, &de, &db);
-  st.n_paras = NP; st.para_dup_elems = de; st.para_dup_bytes = db;
+  if (writer) { o->n_paras = NP; o->para_dup_elems = de; o->para_dup_bytes = db; }
   {
     if ((cfg.has & TB_GR_HAS_DUP_PARA_FRAC) && rep_frac_gt(de, (double)(NP ? NP : 1u), cfg.dup_para_frac)) reasons |= TB_GR_REASON_DUP_PARA_FRAC;
     if ((cfg.has & TB_GR_HAS_DUP_PARA_CHAR_FRAC) && rep_frac_gt(db, text_char_len, cfg.dup_para_char_frac)) reasons |= TB_GR_REASON_DUP_PARA_CHAR_FRAC;
@@ -636,7 +643,7 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
 #pragma unroll 1
             for (int k = 0; k < cfg.n_top; k++) {
               if (cfg.top_n[k] != lvl) continue;
-              st.top_bytes[k] = v;
+              if (writer && v) o->top_bytes[k] = v;
               if (rep_frac_gt(v, text_char_len, cfg.top_frac[k])) reasons |= 1u << (TB_GR_REASON_TOP_SHIFT + k);
             }
           });
@@ -730,7 +737,7 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
 #pragma unroll 1
         for (int k = 0; k < cfg.n_top; k++) {
           if (cfg.top_n[k] != n) continue;
-          st.top_bytes[k] = v;
+          if (writer && v) o->top_bytes[k] = v;
           if (rep_frac_gt(v, text_char_len, cfg.top_frac[k])) reasons |= 1u << (TB_GR_REASON_TOP_SHIFT + k);
         }
       }
@@ -789,7 +796,7 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
 #pragma unroll 1
           for (uint32_t e = n - 1 + g.tid; e < W; e += g.size()) {
             const uint64_t key = A.H[e];
-            uint32_t sl = rep_slot(tb_mix64(key), T);
+            uint32_t sl = rep_slot_raw(key, T);
 #pragma unroll 1
             for (;;) {
               uint32_t old = idx_cas(&tab[sl], EMPTY, e);
@@ -843,7 +850,7 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
             const uint32_t lvl = cfg.dup_n[k];
             if (lvl < n || lvl > ndup_max) continue;
             const uint64_t v = res[lvl];
-            st.dup_bytes[k] = v;
+            if (writer && v) o->dup_bytes[k] = v;
             if (rep_frac_gt(v, text_char_len, cfg.dup_frac[k])) reasons |= 1u << (TB_GR_REASON_DUP_SHIFT + k);
           }
         }
@@ -857,7 +864,7 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
 #pragma unroll 1
                           for (int k = 0; k < cfg.n_dup; k++) {
                             if (cfg.dup_n[k] != lvl) continue;
-                            st.dup_bytes[k] = v;
+                            if (writer && v) o->dup_bytes[k] = v;
                             if (rep_frac_gt(v, text_char_len, cfg.dup_frac[k])) reasons |= 1u << (TB_GR_REASON_DUP_SHIFT + k);
                           }
                         });
@@ -869,7 +876,7 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
 #pragma unroll 1
         for (int k = 0; k < cfg.n_dup; k++) {
           if (cfg.dup_n[k] != n) continue;
-          st.dup_bytes[k] = v;
+          if (writer && v) o->dup_bytes[k] = v;
           if (rep_frac_gt(v, text_char_len, cfg.dup_frac[k])) reasons |= 1u << (TB_GR_REASON_DUP_SHIFT + k);
         }
       }
@@ -878,8 +885,7 @@ TB_D void rep_body(const G& g, const KBatch& a, const int64_t* ts, const int64_t
   }
   REP_PROF(5)  // duplicate n-gram levels
   if (g.tid == 0) {
-    st.n_words = W; st.reason_bits = reasons;
-    out[d] = st;
+    o->n_words = W; o->reason_bits = reasons; o->flags = gd.flags; o->char_len = gd.char_len;
     if (reasons) { a.alive[d] = 0; a.failed[d] = (int8_t)step; }
   }
   REP_PROF(6)  // result
