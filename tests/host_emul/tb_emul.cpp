@@ -212,8 +212,8 @@ extern "C" int tbe_run_chain(const tb_step_cfg* steps, size_t n_steps, const uin
   const char* fw = getenv("TBE_FORCE_WALK");
   KBatch b{text, rs, re, alive, failed, n, uc, 0, nb, (fw && fw[0] == '1') ? TB_DBG_FORCE_WALK : 0u};
   std::vector<LutEntry> lut(256);
-  auto build_lut = [&](int kind, uint32_t firstmask) {
-    for (uint32_t i = 0; i < 256; i++) lut[i] = tb_lut_entry(kind, i, i < 128 ? ascii[i] : 0u, (kind == TB_LUT_C4A || kind == TB_LUT_FW) ? ((uc.wslead[i >> 5] >> (i & 31)) & 1u) : firstmask);
+  auto build_lut = [&](int kind, uint64_t firstmask) {
+    for (uint32_t i = 0; i < 256; i++) lut[i] = tb_lut_entry(kind, i, i < 128 ? ascii[i] : 0u, (kind == TB_LUT_C4A || kind == TB_LUT_FW) ? (uint64_t)((uc.wslead[i >> 5] >> (i & 31)) & 1u) : firstmask);
   };
   auto alive_pred = [&](int64_t d) { return alive[d] != 0; };
   bool has_c4 = false;
@@ -228,10 +228,10 @@ extern "C" int tbe_run_chain(const tb_step_cfg* steps, size_t n_steps, const uin
       const tb_gq_params& q = sc.u.gq;
       GqCfg cfg{q.has, q.min_doc_words, q.max_doc_words, q.min_stop_words, q.min_avg_word_length, q.max_avg_word_length,
                 q.max_symbol_word_ratio, q.max_bullet_lines_ratio, q.max_ellipsis_lines_ratio, q.max_non_alpha_words_ratio};
-      uint32_t mask, maxlen, lenmask, firstmask;
-      std::vector<SwEntry> tab = tb_build_stop_table(tb_stop_words_of(q), &mask, &maxlen, &lenmask, &firstmask);
-      SwTable sw{tab.data(), mask, maxlen, lenmask, firstmask};
-      build_lut(TB_LUT_GQ, firstmask);
+      uint32_t mask, maxlen, lenmask, firstmask, secondmask;
+      std::vector<SwEntry> tab = tb_build_stop_table(tb_stop_words_of(q), &mask, &maxlen, &lenmask, &firstmask, &secondmask);
+      SwTable sw{tab.data(), mask, maxlen, lenmask, firstmask, secondmask};
+      build_lut(TB_LUT_GQ, ((uint64_t)secondmask << 32) | firstmask);
       uint32_t* gstage = G32(2 * TB_GQ_STAGE);
       run_warps(n, alive_pred, [&](int64_t d, int lane) { body_gq(b, ascii, lut.data(), gstage, sw, cfg, (int)s, (tb_gq_stats*)stats, d, lane); });
     } else if (sc.type == TB_STEP_GOPHER_REPETITION) {

@@ -11,6 +11,12 @@ GQ_SHIPPED = GopherQualityParams(min_doc_words=5, max_doc_words=200, min_avg_wor
                                  max_non_alpha_words_ratio=0.8, min_stop_words=2,
                                  stop_words=["the", "of", "café", "σοφος", "i̇stanbul", "kelvin", "a", "i",
                                              "thisisaverylongstopwordxx", "og", "på"])
+# a short stop list without one-byte entries (the second-byte prefilter and the mask-domain length test of the tile path
+# are live): mixed case, non-ASCII second bytes, digits
+GQ_SHORT_SW = GopherQualityParams(min_doc_words=1, max_doc_words=1000000, min_avg_word_length=0.01, max_avg_word_length=5000.0,
+                                  max_symbol_word_ratio=1000.0, max_bullet_lines_ratio=1.0, max_ellipsis_lines_ratio=1.0,
+                                  max_non_alpha_words_ratio=0.0, min_stop_words=0,
+                                  stop_words=["the", "Of", "på", "og", "to", "it's", "x9", "9x", "http", "foo_bar", "café"])
 GQ_DEFAULT_SW = GopherQualityParams(min_doc_words=50, max_doc_words=100000, min_avg_word_length=3.0, max_avg_word_length=10.0,
                                     max_symbol_word_ratio=0.1, max_bullet_lines_ratio=0.9, max_ellipsis_lines_ratio=0.3,
                                     max_non_alpha_words_ratio=0.8, min_stop_words=2)
@@ -40,6 +46,7 @@ CHAINS = {
     "shipped_with_fineweb": [GR_SHIPPED, GQ_SHIPPED, C4_SHIPPED, FW_SHIPPED],  # the accelerated steps of pipeline_config.yaml, in its order
     "gq_open": [GQ_OPEN],
     "gq_shipped": [GQ_SHIPPED],
+    "gq_short_sw": [GQ_SHORT_SW],
     "gr_open": [GR_OPEN],
     "gr_shipped": [GR_SHIPPED],
     "c4_one_sentence": [C4_ONE_SENT],

@@ -122,7 +122,7 @@ struct StepHost {
   GqCfg gq;
   GrCfg gr;
   FwCfg fw;
-  SwTable sw{nullptr, 0, 0, 0, 0};
+  SwTable sw{nullptr, 0, 0, 0, 0, 0};
   DevBuf sw_dev;
 };
 
@@ -360,11 +360,11 @@ int validate_step(const tb_step_cfg& s) {
 }
 
 int build_stop_table(StepHost& sh, const tb_gq_params& p) {
-  uint32_t mask = 0, maxlen = 0, lenmask = 0, firstmask = 0;
-  std::vector<SwEntry> tab = tb_build_stop_table(tb_stop_words_of(p), &mask, &maxlen, &lenmask, &firstmask);
+  uint32_t mask = 0, maxlen = 0, lenmask = 0, firstmask = 0, secondmask = 0;
+  std::vector<SwEntry> tab = tb_build_stop_table(tb_stop_words_of(p), &mask, &maxlen, &lenmask, &firstmask, &secondmask);
   int rc = upload(sh.sw_dev, tab.data(), tab.size() * sizeof(SwEntry));
   if (rc) return rc;
-  sh.sw = SwTable{sh.sw_dev.as<SwEntry>(), mask, maxlen, lenmask, firstmask};
+  sh.sw = SwTable{sh.sw_dev.as<SwEntry>(), mask, maxlen, lenmask, firstmask, secondmask};
   return TB_OK;
 }
 

@@ -100,7 +100,10 @@ TB_D bool gq_doc_tiles(const KBatch& a, const LutEntry* lut, uint32_t* stage, co
     }
     // ---- stop-word candidates (first letter and length fit): collected per tile, then tested with all lanes busy
     {
-      uint32_t cand = B & H & inner & SWF, keepc = 0;
+      // first byte fits, and the byte after it can be the second byte of an entry (a one-byte word passes or fails on its
+      // length below either way: secondmask is all ones as soon as the list has a one-byte entry)
+      const uint32_t cand = B & H & inner & SWF & ((T.h[TH_SW2] | ~V) >> 1);  // (a byte beyond the text filters nothing)
+      uint32_t keepc = 0;
       for (uint32_t c = cand; c; c &= c - 1u) {
         const int sb = tb_ctz32(c);
         const int e = tb_ctz32(B & ~tb_upto(sb));

@@ -12,12 +12,12 @@
 // Entries are inserted exactly as configured: the reference does not lower-case the list
 // (gopher_quality.rs:46-58), only the word being looked up (:186).
 inline std::vector<SwEntry> tb_build_stop_table(const std::vector<std::string>& words, uint32_t* mask, uint32_t* maxlen,
-                                                 uint32_t* lenmask, uint32_t* firstmask) {
+                                                 uint32_t* lenmask, uint32_t* firstmask, uint32_t* secondmask) {
   uint32_t T = 16;
   while (T < 2 * words.size() + 2) T <<= 1;
   std::vector<SwEntry> tab(T);
   memset(tab.data(), 0, T * sizeof(SwEntry));
-  *maxlen = 0; *lenmask = 0; *firstmask = 0;
+  *maxlen = 0; *lenmask = 0; *firstmask = 0; *secondmask = 0;
   for (const auto& w : words) {
     LowKey k; k.init();
     for (unsigned char c : w) k.push(c);
@@ -25,6 +25,7 @@ inline std::vector<SwEntry> tb_build_stop_table(const std::vector<std::string>& 
     if (k.len > *maxlen) *maxlen = k.len;
     *lenmask |= 1u << (k.len < 31u ? k.len : 31u);
     *firstmask |= sw_first_bit((unsigned char)w[0]);
+    *secondmask |= w.size() >= 2 ? sw_first_bit((unsigned char)w[1]) : 0xFFFFFFFFu;
     uint32_t s = (uint32_t)sw_slot_hash(k.lo, k.hi, k.ext, k.len) & (T - 1);
     bool dup = false;
     while (tab[s].used) {

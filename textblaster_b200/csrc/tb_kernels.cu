@@ -19,10 +19,10 @@ __device__ __forceinline__ void load_ascii(uint16_t* s_ascii, const UcTables& uc
   __syncthreads();
 }
 // per-byte class table of the mask-based word passes (tb_tile.cuh), built once per CTA
-__device__ __forceinline__ void load_lut(LutEntry* s_lut, const UcTables& uc, int kind, uint32_t firstmask) {
+__device__ __forceinline__ void load_lut(LutEntry* s_lut, const UcTables& uc, int kind, uint64_t aux) {
   for (uint32_t i = threadIdx.x; i < 256; i += blockDim.x) {
     uint32_t ci = i < 128 ? uc.stage2[(uint32_t)uc.stage1[0] * 256u + i] : 0u;
-    s_lut[i] = tb_lut_entry(kind, i, ci, (kind == TB_LUT_C4A || kind == TB_LUT_FW) ? ((uc.wslead[i >> 5] >> (i & 31)) & 1u) : firstmask);
+    s_lut[i] = tb_lut_entry(kind, i, ci, (kind == TB_LUT_C4A || kind == TB_LUT_FW) ? (uint64_t)((uc.wslead[i >> 5] >> (i & 31)) & 1u) : aux);
   }
   __syncthreads();
 }
@@ -101,7 +101,7 @@ __global__ void __launch_bounds__(TB_BLOCK, TB_RES_GQ) k_gq(KBatch a, SwTable sw
   __shared__ uint16_t s_ascii[192];
   __shared__ LutEntry s_lut[256];
   load_ascii(s_ascii, a.uc);
-  load_lut(s_lut, a.uc, TB_LUT_GQ, sw.firstmask);
+  load_lut(s_lut, a.uc, TB_LUT_GQ, ((uint64_t)sw.secondmask << 32) | sw.firstmask);
   __shared__ uint32_t s_cand[2 * TB_GQ_STAGE];
   __shared__ SwEntry s_sw[64];  // small stop-word tables are probed in shared memory
   if (sw.mask < 64u) {

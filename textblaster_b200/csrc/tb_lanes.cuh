@@ -19,6 +19,7 @@ struct SwTable {
   const SwEntry* e; uint32_t mask, maxlen;
   uint32_t lenmask;    // bit min(len, 31) set for every entry length: cheap reject before building a key
   uint32_t firstmask;  // bit (first byte | 0x20) - 'a' for letters, bit 26 for anything else
+  uint32_t secondmask; // the same for the entries' second bytes; all ones if some entry is a single byte (no filter then)
 };
 TB_HD uint32_t sw_first_bit(uint32_t b) { uint32_t f = (b | 0x20u) - 'a'; return f < 26u ? (1u << f) : (1u << 26); }
 

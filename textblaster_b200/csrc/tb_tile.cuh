@@ -41,6 +41,7 @@
 #define TH_DASH 4  //                '-'
 #define TH_SWF 5   //                byte can start a stop word (SwTable::firstmask)
 #define TH_E2 6    //                0xE2, lead byte of U+2026 and U+2022
+#define TH_SW2 7   //                byte can be the second byte of a stop word (SwTable::secondmask)
 #define TH_P1 2    // C4 pass B: first / second / third letter of a javascript / policy pattern
 #define TH_P2 3
 #define TH_P3 4
@@ -61,10 +62,11 @@ enum { TB_LUT_GQ = 0, TB_LUT_GR = 1, TB_LUT_C4B = 2, TB_LUT_C4A = 3, TB_LUT_FW =
 
 struct __attribute__((aligned(8))) LutEntry { uint32_t lo, hi; };
 
-// table entry of byte value b; ci = cinfo of the code point b (only used for b < 128); aux: SwTable::firstmask
-// (TB_LUT_GQ) or "b is a lead byte that may begin a White_Space character" (TB_LUT_C4A, TB_LUT_FW)
-TB_HD LutEntry tb_lut_entry(int kind, uint32_t b, uint32_t ci, uint32_t aux) {
-  const uint32_t firstmask = aux;
+// table entry of byte value b; ci = cinfo of the code point b (only used for b < 128); aux: SwTable::firstmask in the low
+// and SwTable::secondmask in the high word (TB_LUT_GQ), or "b is a lead byte that may begin a White_Space character"
+// (TB_LUT_C4A, TB_LUT_FW)
+TB_HD LutEntry tb_lut_entry(int kind, uint32_t b, uint32_t ci, uint64_t aux) {
+  const uint32_t firstmask = (uint32_t)aux, secondmask = (uint32_t)(aux >> 32);
   LutEntry e; e.lo = 0; e.hi = 0;
   if (kind == TB_LUT_C4A) {
     if (b >= 0x80u) {
@@ -105,6 +107,7 @@ TB_HD LutEntry tb_lut_entry(int kind, uint32_t b, uint32_t ci, uint32_t aux) {
     // a non-ASCII first byte may change under to_lowercase(): always a candidate
     uint32_t fl = (b | 0x20u) - 'a';
     if (b >= 0x80u || (firstmask & (fl < 26u ? (1u << fl) : (1u << 26)))) e.hi |= 1u << (4 * TH_SWF);
+    if (b >= 0x80u || (secondmask & (fl < 26u ? (1u << fl) : (1u << 26)))) e.hi |= 1u << (4 * TH_SW2);
   } else if (kind == TB_LUT_FW) {
     if (b < 0x80u) {
       if (ci & CI_WS) e.hi |= 1u << (4 * FH_WS);
